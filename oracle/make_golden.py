@@ -1,0 +1,172 @@
+"""Generates tests/golden/*.pt from the UNMODIFIED reference modules  --  TEST INFRASTRUCTURE.
+
+Run in the build container (where /root/reference is mounted):
+
+    python -m oracle.make_golden
+
+The reference holds no golden vectors for this path, so these fixtures ARE
+the pin: seeded parameters (``visitron_oracle.init_params``) are loaded into the reference's own
+``PreTrainOscar`` / ``BertImgModelwithLocationEmbeds`` / ``SoftDotAttention`` / ``AttnDecoderLSTM``
+classes, run forward+backward on seeded synthetic inputs, and the outputs are stored.  Parameters
+are NOT stored (they are re-drawn from the seed); gradients are stored as (norm, sum, strided
+sample) per tensor to keep every fixture small.
+"""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import ref_shim, visitron_oracle as vo  # noqa: E402
+from visitron_b200 import synthetic  # noqa: E402
+
+GOLDEN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+SAMPLE = 257  # stride used for the per-tensor gradient sample
+
+
+def grad_digest(g: torch.Tensor) -> dict:
+    f = g.detach().float().reshape(-1)
+    return dict(norm=float(f.norm()), sum=float(f.double().sum()), sample=f[::SAMPLE][:512].clone())
+
+
+def small_cfg(**kw) -> vo.OracleConfig:
+    base = dict(vocab_size=2048, num_hidden_layers=2, max_position_embeddings=64, detector_classes=96,
+                action_space=36)
+    base.update(kw)
+    return vo.OracleConfig(**base)
+
+
+def gen_pretrain(ns, name, cfg, seed, batch_kw):
+    P = vo.init_params(cfg, seed)
+    m = ref_shim.build_pretrain(ns, cfg, P)
+    m.train()  # dropout p == 0 in cfg; train() as the loop does (vs/pretrain.py:153)
+    batch = synthetic.pretrain_batch(**batch_kw)
+    captured = {}
+    h1 = m.bert.register_forward_hook(lambda mod, i, o: captured.__setitem__("bert", o))
+    h2 = m.mlmhead.register_forward_hook(lambda mod, i, o: captured.__setitem__("mlm", o))
+    h3 = m.token_head.register_forward_hook(lambda mod, i, o: captured.__setitem__("tok", o))
+    h4 = m.next_action.register_forward_hook(lambda mod, i, o: captured.__setitem__("act", o))
+    out = m(**batch)
+    out[0].backward()
+    for h in (h1, h2, h3, h4):
+        h.remove()
+    seq, pooled = captured["bert"][0], captured["bert"][1]
+    lab, tl = batch["labels"], batch["token_labels"]
+    grads = {}
+    for k, p in m.named_parameters():
+        if k == "mlmhead.predictions.decoder.weight":
+            continue  # tied: same tensor as the word embeddings
+        grads[k] = grad_digest(p.grad)
+    fix = dict(
+        kind="pretrain", cfg=cfg.__dict__, seed=seed, batch_kw=batch_kw,
+        outputs=tuple(float(o) for o in out),
+        sequence_output=seq.detach().clone(), pooled_output=pooled.detach().clone(),
+        mlm_logits_labelled=captured["mlm"].detach()[lab != -1][:, ::16].clone(),
+        predicted_words_labelled=captured["mlm"].detach().argmax(2)[lab != -1].clone(),
+        predicted_tokens_labelled=captured["tok"].detach().argmax(2)[tl != -1].clone(),
+        action_scores=captured["act"].detach().clone(),
+        grads=grads,
+    )
+    torch.save(fix, os.path.join(GOLDEN, name + ".pt"))
+    print(name, fix["outputs"])
+
+
+def gen_finetune(ns, name, cfg, seed, batch_kw):
+    """Encoder as OscarEncoder calls it (vs/agent_models.py:267-275): text only, mask == ~uint8."""
+    P = vo.init_params(cfg, seed, pretrain_heads=False)
+    m = ns.BertImgModelwithLocationEmbeds(ref_shim.make_config(ns, cfg))
+    m.load_state_dict({k[len("bert."):]: v for k, v in P.items()}, strict=True)
+    m.train()
+    batch = synthetic.finetune_encoder_batch(**batch_kw)
+    seq, pooled = m(batch["input_ids"], token_type_ids=batch["token_type_ids"],
+                    attention_mask=batch["attention_mask"], position_ids=None)[:2]
+    g = torch.Generator().manual_seed(seed + 1)
+    proj = torch.randn(seq.shape, generator=g) / seq.numel() ** 0.5
+    (seq * proj).sum().backward()
+    grads = {"bert." + k: grad_digest(p.grad) for k, p in m.named_parameters() if p.grad is not None}
+    fix = dict(kind="finetune", cfg=cfg.__dict__, seed=seed, batch_kw=batch_kw,
+               sequence_output=seq.detach().clone(), pooled_output=pooled.detach().clone(), grads=grads)
+    torch.save(fix, os.path.join(GOLDEN, name + ".pt"))
+    print(name, float(seq.abs().mean()))
+
+
+def gen_heads(ns, name, seed):
+    g = torch.Generator().manual_seed(seed)
+    Hd, Fd = 512, 2052
+    W = vo.init_head_params(seed, Hd, Fd)
+    fix = dict(kind="heads", seed=seed)
+    # --- A14 candidate scorer: vs AttnDecoderLSTM.candidate_att_layer + vs/agent.py masking + CE
+    vb = synthetic.viewpoint_step_batch(8, seed)
+    att = ns.vs_models.SoftDotAttention(Hd, Fd)
+    att.linear_in.weight.data.copy_(W["candidate_att_layer.linear_in.weight"])
+    h = vb["h_tilde"].clone().requires_grad_(True)
+    cf = vb["cand_feat"].clone().requires_grad_(True)
+    _, logit = att(h, cf, output_prob=False)
+    C = cf.size(1)
+    cand_mask = torch.arange(C)[None, :] > (vb["cand_len"] - 1)[:, None]  # utils.length2mask
+    logit.masked_fill_(cand_mask, -float("inf"))
+    loss = torch.nn.CrossEntropyLoss(ignore_index=-100)(logit, vb["target"])
+    loss.backward()
+    fix["candidate"] = dict(logit=logit.detach().clone(), loss=float(loss),
+                            argmax=logit.argmax(1), dh=h.grad.clone(), dcand=grad_digest(cf.grad),
+                            dw_in=grad_digest(att.linear_in.weight.grad))
+    # --- A15 turn-based head: tb SoftDotAttention + decoder2action + masking + CE(ignore 7)
+    tb = synthetic.turn_step_batch(6, seed, ctx_len=48)
+    att2 = ns.tb_models.SoftDotAttention(Hd)
+    att2.linear_in.weight.data.copy_(W["attention_layer.linear_in.weight"])
+    att2.linear_out.weight.data.copy_(W["attention_layer.linear_out.weight"])
+    d2a = torch.nn.Linear(Hd, 6)
+    d2a.weight.data.copy_(W["decoder2action.weight"])
+    d2a.bias.data.copy_(W["decoder2action.bias"])
+    h2 = tb["h"].clone().requires_grad_(True)
+    ctx = tb["ctx"].clone().requires_grad_(True)
+    h_tilde, alpha = att2(h2, ctx, tb["ctx_mask"])
+    logit2 = d2a(h_tilde)
+    for i in range(logit2.size(0)):
+        if bool(tb["no_forward"][i]):
+            logit2[i, 0] = -float("inf")
+    loss2 = torch.nn.CrossEntropyLoss(ignore_index=7)(logit2, tb["target"])
+    loss2.backward()
+    fix["turn"] = dict(h_tilde=h_tilde.detach().clone(),
+                       logit=logit2.detach().clone(), loss=float(loss2), argmax=logit2.argmax(1),
+                       dh=h2.grad.clone(), dctx=grad_digest(ctx.grad),
+                       dw_in=grad_digest(att2.linear_in.weight.grad),
+                       dw_out=grad_digest(att2.linear_out.weight.grad),
+                       dw_a=d2a.weight.grad.clone(), db_a=d2a.bias.grad.clone())
+    # --- A16 QA head: question_linear + BCEWithLogits(pos_weight=5, reduction none) masked mean
+    dec = ns.vs_models.AttnDecoderLSTMwithClassifier(4, 64, Hd, 0.0)
+    ql = dec.question_linear
+    for p, k in zip((ql[0].weight, ql[0].bias, ql[2].weight, ql[2].bias),
+                    ("0.weight", "0.bias", "2.weight", "2.bias")):
+        p.data.copy_(W["question_linear." + k])
+    hq = torch.randn(8, Hd, generator=g).requires_grad_(True)
+    qt = (torch.rand(8, generator=g) < 0.4).float()
+    ignore = torch.rand(8, generator=g) < 0.25
+    crit = torch.nn.BCEWithLogitsLoss(reduction="none", pos_weight=torch.Tensor([5.0]))
+    ql_logit = ql(hq)
+    cur = crit(ql_logit.squeeze(1), qt) * ~ignore
+    loss3 = cur.sum() / (len(cur) - ignore.sum())
+    loss3.backward()
+    fix["qa"] = dict(h=hq.detach().clone(), target=qt, ignore=ignore,
+                     logit=ql_logit.detach().clone(), loss=float(loss3), dh=hq.grad.clone(),
+                     dw1=grad_digest(ql[0].weight.grad), db1=ql[0].bias.grad.clone(),
+                     dw2=ql[2].weight.grad.clone(), db2=ql[2].bias.grad.clone())
+    torch.save(fix, os.path.join(GOLDEN, name + ".pt"))
+    print(name, fix["candidate"]["loss"], fix["turn"]["loss"], fix["qa"]["loss"])
+
+
+def main():
+    if not ref_shim.available():
+        raise SystemExit("reference tree not mounted; fixtures can only be generated in the build container")
+    os.makedirs(GOLDEN, exist_ok=True)
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    ns = ref_shim.load()
+    bk = dict(batch=2, seed=88, text_len=40, regions=24, img_dim=2054, vocab=2048, detector_classes=96)
+    gen_pretrain(ns, "pretrain_small", small_cfg(), 7, bk)
+    gen_pretrain(ns, "pretrain_small_imgln", small_cfg(use_img_layernorm=1), 8, dict(bk, seed=89))
+    gen_finetune(ns, "finetune_small", small_cfg(), 9, dict(batch=2, seed=90, text_len=48, vocab=2048))
+    gen_heads(ns, "heads_small", 11)
+
+
+if __name__ == "__main__":
+    main()

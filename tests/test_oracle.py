@@ -1,0 +1,143 @@
+"""The oracle (oracle/visitron_oracle.py) against (a) the committed golden fixtures produced by the
+UNMODIFIED reference modules and (b), when /root/reference is mounted, the live reference on other
+seeds / configurations.  CPU only."""
+import os
+
+import pytest
+import torch
+
+from oracle import ref_shim, visitron_oracle as vo
+from oracle.make_golden import SAMPLE
+from visitron_b200 import synthetic
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _load(name):
+    return torch.load(os.path.join(GOLDEN, name + ".pt"), weights_only=False)
+
+
+def _check_digest(name, g, dig, rtol=2e-4):
+    f = g.detach().float().reshape(-1)
+    assert abs(float(f.norm()) - dig["norm"]) <= rtol * max(dig["norm"], 1e-6), name
+    torch.testing.assert_close(f[::SAMPLE][:512], dig["sample"], rtol=1e-3, atol=1e-6 + 1e-4 * dig["norm"] / f.numel() ** 0.5, msg=name)
+
+
+@pytest.mark.parametrize("name", ["pretrain_small", "pretrain_small_imgln"])
+def test_pretrain_golden(name):
+    fix = _load(name)
+    cfg = vo.OracleConfig(**fix["cfg"])
+    P = vo.clone_params(vo.init_params(cfg, fix["seed"]))
+    batch = synthetic.pretrain_batch(**fix["batch_kw"])
+    out, aux = vo.pretrain_forward(P, cfg, return_aux=True, **batch)
+    out[0].backward()
+    for a, b in zip(out, fix["outputs"]):
+        assert abs(float(a) - b) <= 1e-5 * max(1.0, abs(b))
+    torch.testing.assert_close(aux["sequence_output"], fix["sequence_output"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(aux["pooled_output"], fix["pooled_output"], rtol=1e-4, atol=1e-5)
+    lab, tl = batch["labels"], batch["token_labels"]
+    torch.testing.assert_close(aux["prediction_scores"][lab != -1][:, ::16], fix["mlm_logits_labelled"], rtol=1e-4, atol=1e-5)
+    assert torch.equal(aux["prediction_scores"].argmax(2)[lab != -1], fix["predicted_words_labelled"])
+    assert torch.equal(aux["token_prob"].argmax(2)[tl != -1], fix["predicted_tokens_labelled"])
+    torch.testing.assert_close(aux["action_scores"], fix["action_scores"], rtol=1e-4, atol=1e-5)
+    assert set(fix["grads"]) == set(P)
+    for k, dig in fix["grads"].items():
+        _check_digest(k, P[k].grad, dig)
+
+
+def test_finetune_golden():
+    fix = _load("finetune_small")
+    cfg = vo.OracleConfig(**fix["cfg"])
+    P = vo.clone_params(vo.init_params(cfg, fix["seed"], pretrain_heads=False))
+    batch = synthetic.finetune_encoder_batch(**fix["batch_kw"])
+    assert batch["attention_mask"].dtype == torch.uint8 and int(batch["attention_mask"].min()) == 255  # F6
+    seq, pooled = vo.bert_img_forward(P, cfg, **batch)
+    torch.testing.assert_close(seq, fix["sequence_output"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(pooled, fix["pooled_output"], rtol=1e-4, atol=1e-5)
+    g = torch.Generator().manual_seed(fix["seed"] + 1)
+    proj = torch.randn(seq.shape, generator=g) / seq.numel() ** 0.5
+    (seq * proj).sum().backward()
+    for k, dig in fix["grads"].items():
+        _check_digest(k, P[k].grad, dig)
+    # parameters the fine-tune call leaves without gradient (needs find_unused_parameters in the reference)
+    for k in ("bert.img_embedding.weight", "bert.location_embeds.weight", "bert.pooler.dense.weight"):
+        assert k not in fix["grads"] and P[k].grad is None
+
+
+def test_heads_golden():
+    fix = _load("heads_small")
+    W = vo.init_head_params(fix["seed"])
+    # A14
+    vb = synthetic.viewpoint_step_batch(8, fix["seed"])
+    w_in = W["candidate_att_layer.linear_in.weight"].clone().requires_grad_(True)
+    h = vb["h_tilde"].clone().requires_grad_(True)
+    cf = vb["cand_feat"].clone().requires_grad_(True)
+    logit, loss, am = vo.candidate_scores_ce(w_in, h, cf, vb["cand_len"], vb["target"])
+    loss.backward()
+    c = fix["candidate"]
+    torch.testing.assert_close(logit, c["logit"], rtol=1e-4, atol=1e-5)
+    assert abs(float(loss) - c["loss"]) < 1e-5 * max(1, c["loss"]) and torch.equal(am, c["argmax"])
+    torch.testing.assert_close(h.grad, c["dh"], rtol=1e-4, atol=1e-6)
+    _check_digest("dcand", cf.grad, c["dcand"])
+    _check_digest("dw_in", w_in.grad, c["dw_in"])
+    # A15
+    tb = synthetic.turn_step_batch(6, fix["seed"], ctx_len=48)
+    ws = [W[k].clone().requires_grad_(True) for k in ("attention_layer.linear_in.weight", "attention_layer.linear_out.weight", "decoder2action.weight", "decoder2action.bias")]
+    h2 = tb["h"].clone().requires_grad_(True)
+    ctx = tb["ctx"].clone().requires_grad_(True)
+    ht, logit2, loss2, am2 = vo.turn_based_head(*ws, h2, ctx, tb["ctx_mask"], tb["no_forward"], tb["target"])
+    loss2.backward()
+    t = fix["turn"]
+    torch.testing.assert_close(ht, t["h_tilde"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(logit2, t["logit"], rtol=1e-4, atol=1e-5)
+    assert abs(float(loss2) - t["loss"]) < 1e-5 and torch.equal(am2, t["argmax"])
+    torch.testing.assert_close(h2.grad, t["dh"], rtol=1e-4, atol=1e-6)
+    _check_digest("dctx", ctx.grad, t["dctx"])
+    _check_digest("dw_in", ws[0].grad, t["dw_in"])
+    _check_digest("dw_out", ws[1].grad, t["dw_out"])
+    torch.testing.assert_close(ws[2].grad, t["dw_a"], rtol=1e-4, atol=1e-6)
+    torch.testing.assert_close(ws[3].grad, t["db_a"], rtol=1e-4, atol=1e-6)
+    # A16
+    q = fix["qa"]
+    qs = [W["question_linear." + k].clone().requires_grad_(True) for k in ("0.weight", "0.bias", "2.weight", "2.bias")]
+    hq = q["h"].clone().requires_grad_(True)
+    logit3, loss3 = vo.qa_head(*qs, hq, q["target"], ~q["ignore"])
+    loss3.backward()
+    torch.testing.assert_close(logit3, q["logit"], rtol=1e-4, atol=1e-5)
+    assert abs(float(loss3) - q["loss"]) < 1e-5
+    torch.testing.assert_close(hq.grad, q["dh"], rtol=1e-4, atol=1e-6)
+    _check_digest("dw1", qs[0].grad, q["dw1"])
+    torch.testing.assert_close(qs[3].grad, q["db2"], rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.skipif(not ref_shim.available(), reason="reference tree not mounted (GPU box)")
+@pytest.mark.parametrize("seed,imgln,layers", [(21, 0, 1), (22, 1, 3)])
+def test_oracle_vs_live_reference(seed, imgln, layers):
+    """Full-tensor comparison (all gradients, not digests) on configurations the fixtures do not hold."""
+    ns = ref_shim.load()
+    cfg = vo.OracleConfig(vocab_size=1500, num_hidden_layers=layers, max_position_embeddings=40,
+                          detector_classes=50, use_img_layernorm=imgln)
+    P0 = vo.init_params(cfg, seed)
+    m = ref_shim.build_pretrain(ns, cfg, P0)
+    m.train()
+    batch = synthetic.pretrain_batch(3, seed, text_len=33, regions=16, vocab=1500, detector_classes=50)
+    ref = m(**batch)
+    ref[0].backward()
+    P = vo.clone_params(P0)
+    out = vo.pretrain_forward(P, cfg, **batch)
+    out[0].backward()
+    for a, b in zip(out, ref):
+        assert abs(float(a) - float(b)) <= 1e-5 * max(1.0, abs(float(b)))
+    for k, p in m.named_parameters():
+        if k == "mlmhead.predictions.decoder.weight":
+            continue
+        torch.testing.assert_close(P[k].grad, p.grad, rtol=2e-3, atol=1e-6, msg=k)
+
+
+def test_mask_quantisation_f6():
+    """~uint8 masks give bias (1-255)*-1e4 = +2.54e6: softmax is shift invariant but fp32 scores are
+    quantised to 0.25 -- the oracle must reproduce that, not an exact unmasked softmax."""
+    ext = vo.extended_mask(torch.full((1, 4), 255, dtype=torch.uint8), torch.float32)
+    assert float(ext[0, 0, 0, 0]) == 2540000.0
+    s = torch.tensor([0.1, 0.2, 0.3, 0.45]) + ext[0, 0, 0]
+    assert torch.equal(s - 2540000.0, torch.tensor([0.0, 0.25, 0.25, 0.5]))
