@@ -1,0 +1,60 @@
+// Library-wide state: error string, device checks.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace vt {
+
+static thread_local char g_err[512] = "";
+static int g_sms = 0;
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+  return VT_ERR_CUDA;
+}
+
+int num_sms() {
+  if (g_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sms <= 0) g_sms = 148;
+  }
+  return g_sms;
+}
+
+int resolve_driver_entry_points();
+
+}  // namespace vt
+
+extern "C" const char* vt_last_error(void) { return vt::g_err; }
+
+extern "C" int vt_num_sms(void) { return vt::num_sms(); }
+
+extern "C" int vt_init(int device) {
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    vt::set_error("no CUDA device (%s): libvisitron_b200 has no CPU fallback", cudaGetErrorString(e));
+    return VT_ERR_NO_DEVICE;
+  }
+  VT_CUDA(cudaSetDevice(device));
+  int major = 0, minor = 0;
+  VT_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+  VT_CUDA(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, device));
+  if (major != 10) {
+    vt::set_error("device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, major, minor);
+    return VT_ERR_NO_DEVICE;
+  }
+  vt::g_sms = 0;
+  vt::num_sms();
+  return vt::resolve_driver_entry_points();
+}

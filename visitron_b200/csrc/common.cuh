@@ -1,0 +1,145 @@
+// Shared device/host helpers for libvisitron_b200 (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/visitron_b200.h"
+
+namespace vt {
+
+typedef __nv_bfloat16 bf16;
+
+// ---------------------------------------------------------------------------------------------
+// error plumbing (thread-local message, negative status codes, see include/visitron_b200.h)
+// ---------------------------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define VT_CUDA(call)                                                        \
+  do {                                                                       \
+    cudaError_t e__ = (call);                                                \
+    if (e__ != cudaSuccess) return vt::cuda_fail(e__, #call, __FILE__, __LINE__); \
+  } while (0)
+
+#define VT_CHECK_LAUNCH() VT_CUDA(cudaGetLastError())
+
+#define VT_REQUIRE(cond, ...)            \
+  do {                                   \
+    if (!(cond)) {                       \
+      vt::set_error(__VA_ARGS__);        \
+      return VT_ERR_BAD_ARGUMENT;        \
+    }                                    \
+  } while (0)
+
+int num_sms();
+
+// ---------------------------------------------------------------------------------------------
+// small device utilities
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ float2 unpack_bf16(uint32_t v) {
+  __nv_bfloat162 t = *reinterpret_cast<__nv_bfloat162*>(&v);
+  return __bfloat1622float2(t);
+}
+__device__ __forceinline__ void unpack8(const uint4& q, float* f) {
+  float2 a = unpack_bf16(q.x), b = unpack_bf16(q.y), c = unpack_bf16(q.z), d = unpack_bf16(q.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 q;
+  q.x = pack_bf16(f[0], f[1]); q.y = pack_bf16(f[2], f[3]);
+  q.z = pack_bf16(f[4], f[5]); q.w = pack_bf16(f[6], f[7]);
+  return q;
+}
+
+// erf to ~1.5e-7 absolute (Abramowitz-Stegun 7.1.26): far below bf16 output rounding, and an order
+// of magnitude fewer issue slots than erff() -- the FFN-up epilogue applies it to every element.
+__device__ __forceinline__ float fast_erf(float x) {
+  float ax = fabsf(x);
+  float t = __frcp_rn(fmaf(0.3275911f, ax, 1.0f));
+  float p = fmaf(fmaf(fmaf(fmaf(1.061405429f, t, -1.453152027f), t, 1.421413741f), t, -0.284496736f), t, 0.254829592f) * t;
+  float r = 1.0f - p * __expf(-ax * ax);
+  return copysignf(r, x);
+}
+// gelu(x) = x * 0.5 * (1 + erf(x / sqrt(2)))          (hf/modeling_bert.py:136-142)
+__device__ __forceinline__ float gelu_fwd(float x) { return 0.5f * x * (1.0f + fast_erf(x * 0.70710678118654752f)); }
+// d/dx gelu(x) = 0.5 (1 + erf(x/sqrt2)) + x * exp(-x^2/2) / sqrt(2 pi)
+__device__ __forceinline__ float gelu_grad(float x) {
+  return 0.5f * (1.0f + fast_erf(x * 0.70710678118654752f)) + x * 0.3989422804014327f * __expf(-0.5f * x * x);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10 counter RNG.  Dropout masks are never stored: forward and backward regenerate them
+// from (seed, stream id, element index).  One call yields 8 x 16-bit lanes; an element is kept iff
+// its lane >= thresh16, thresh16 = round(p * 65536)  (p is thereby quantised to 1/65536).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+    uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += W0;
+    key.y += W1;
+  }
+  return ctr;
+}
+
+struct DropoutCfg {
+  uint32_t thresh16;   // 0 => dropout disabled
+  float scale;         // 1 / (1 - thresh16/65536)
+  uint32_t seed_lo, seed_hi;
+  uint32_t stream;     // distinguishes the dropout sites of one step (layer, op)
+};
+
+inline DropoutCfg make_dropout(float p, uint64_t seed, uint32_t stream) {
+  DropoutCfg d;
+  double q = p <= 0.f ? 0.0 : (double)p;
+  uint32_t t = (uint32_t)(q * 65536.0 + 0.5);
+  if (t > 65535u) t = 65535u;
+  d.thresh16 = t;
+  d.scale = (float)(1.0 / (1.0 - (double)t / 65536.0));
+  d.seed_lo = (uint32_t)seed;
+  d.seed_hi = (uint32_t)(seed >> 32);
+  d.stream = stream;
+  return d;
+}
+
+// 8 consecutive elements starting at linear index idx (idx % 8 == 0): keep-multipliers (0 or scale).
+__device__ __forceinline__ void dropout_mult8(const DropoutCfg& d, uint64_t idx, float* m) {
+  uint64_t g = idx >> 3;
+  uint4 r = philox4x32_10(make_uint4((uint32_t)g, (uint32_t)(g >> 32), 0x5eedu, d.stream), make_uint2(d.seed_lo, d.seed_hi));
+  uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    m[2 * i] = ((w[i] & 0xffffu) >= d.thresh16) ? d.scale : 0.f;
+    m[2 * i + 1] = ((w[i] >> 16) >= d.thresh16) ? d.scale : 0.f;
+  }
+}
+
+// Attention-probability dropout: the 16-bit lane of element (row i, col j) of head bh.  The counter
+// is laid out so that a thread holding the mma.sync accumulator fragment of a 16x32 score block
+// (cols 8n+2t, 8n+2t+1 for n = 4g..4g+3, t = lane%4) needs exactly ONE Philox call per row per
+// 32-column group; it is nevertheless a pure function of (bh, i, j).
+__device__ __forceinline__ uint4 attn_dropout_rand(const DropoutCfg& d, uint32_t bh, uint32_t i, uint32_t jgroup, uint32_t t) {
+  return philox4x32_10(make_uint4(jgroup * 4u + t, i, bh, d.stream), make_uint2(d.seed_lo, d.seed_hi));
+}
+
+}  // namespace vt

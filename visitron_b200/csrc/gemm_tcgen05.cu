@@ -1,0 +1,503 @@
+// bf16 GEMM for sm_100a: TMA -> 128B-swizzled shared memory -> tcgen05.mma (fp32 accumulators in
+// TMEM) -> tcgen05.ld epilogue.  One persistent CTA per SM, warp-specialised:
+//   warp 0      TMA producer (one elected lane)
+//   warp 1      MMA issuer   (one lane; tcgen05.mma is a single-thread instruction)
+//   warp 2      TMEM allocator / deallocator
+//   warps 4-11  epilogue: two warps per 32-lane TMEM quadrant, each taking half of the tile's columns
+// Three mbarrier pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue; two
+// accumulator stages so the epilogue of tile i overlaps the main loop of tile i+1).
+//
+// Operands may be K-major (contraction contiguous) or MN-major (row-major [K, MN]); the latter is
+// what lets data-gradient GEMMs reuse the forward weight and weight-gradient GEMMs read dY and X
+// in place, with no transposed copies in HBM (see include/visitron_b200.h).
+#include <atomic>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace vt {
+
+using namespace ptx;
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle span
+constexpr int UMMA_K = 16;
+constexpr int NUM_EPI_WARPS = 8;
+constexpr int GEMM_THREADS = 128 + NUM_EPI_WARPS * 32;
+
+struct GemmParams {
+  int M, N, K;
+  int m_blocks, n_blocks, k_blocks, splits, k_blocks_per_split;
+  void* D;
+  long long ldd;
+  int out_fp32, accumulate, act, vec_ok;
+  float alpha;
+  const float* alpha_dev;
+  const float* bias;
+  const bf16* residual;
+  long long ldr;
+  const bf16* aux;
+  long long ldaux;
+  bf16* aux_out;
+  long long ldaux_out;
+  DropoutCfg drop;
+  long long remap_in, remap_out, remap_off;
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+  static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + slack for 1024-B alignment
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// One 32-column slice of one output row.
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float alpha, int m, int n0, const uint32_t* v) {
+  if (m >= p.M) return;
+  const int ncols = min(32, p.N - n0);
+  if (ncols <= 0) return;
+  long long orow = m;
+  if (p.remap_in > 0) orow = (long long)(m / p.remap_in) * p.remap_out + p.remap_off + (m % p.remap_in);
+  const bool vec = p.vec_ok && ncols == 32;
+  float x[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) * alpha;
+  if (p.bias) {
+    if (vec) {
+      const float4* b4 = reinterpret_cast<const float4*>(p.bias + n0);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float4 b = __ldg(b4 + j);
+        x[4 * j] += b.x; x[4 * j + 1] += b.y; x[4 * j + 2] += b.z; x[4 * j + 3] += b.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < ncols) x[j] += __ldg(p.bias + n0 + j);
+    }
+  }
+  if (p.aux_out) {
+    bf16* ao = p.aux_out + (long long)m * p.ldaux_out + n0;
+    if (vec) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) reinterpret_cast<uint4*>(ao)[j] = pack8(x + 8 * j);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < ncols) ao[j] = __float2bfloat16(x[j]);
+    }
+  }
+  if (p.act == VT_ACT_GELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) x[j] = gelu_fwd(x[j]);
+  } else if (p.act == VT_ACT_TANH) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) x[j] = tanhf(x[j]);
+  } else if (p.act == VT_ACT_GELU_BWD || p.act == VT_ACT_TANH_BWD) {
+    const bf16* ax = p.aux + (long long)m * p.ldaux + n0;
+    float a[32];
+    if (vec) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) unpack8(__ldg(reinterpret_cast<const uint4*>(ax) + j), a + 8 * j);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) a[j] = (j < ncols) ? __bfloat162float(ax[j]) : 0.f;
+    }
+    if (p.act == VT_ACT_GELU_BWD) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) x[j] *= gelu_grad(a[j]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) x[j] *= (1.0f - a[j] * a[j]);
+    }
+  }
+  if (p.drop.thresh16) {
+    // linear index of the LOGICAL element (m, n); N % 8 == 0 is enforced on the host
+    const uint64_t idx = (uint64_t)m * (uint64_t)p.N + (uint64_t)n0;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      float mult[8];
+      dropout_mult8(p.drop, idx + 8 * g, mult);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[8 * g + j] *= mult[j];
+    }
+  }
+  if (p.residual) {
+    const bf16* r = p.residual + orow * p.ldr + n0;
+    if (vec) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float t[8];
+        unpack8(__ldg(reinterpret_cast<const uint4*>(r) + j), t);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) x[8 * j + k] += t[k];
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < ncols) x[j] += __bfloat162float(r[j]);
+    }
+  }
+  if (p.out_fp32) {
+    float* d = reinterpret_cast<float*>(p.D) + orow * p.ldd + n0;
+    if (p.accumulate) {
+      if (vec) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) red_add_v4(d + 4 * j, x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < ncols) atomicAdd(d + j, x[j]);
+      }
+    } else {
+      if (vec) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) reinterpret_cast<float4*>(d)[j] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j < ncols) d[j] = x[j];
+      }
+    }
+  } else {
+    bf16* d = reinterpret_cast<bf16*>(p.D) + orow * p.ldd + n0;
+    if (vec) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) reinterpret_cast<uint4*>(d)[j] = pack8(x + 8 * j);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < ncols) d[j] = __float2bfloat16(x[j]);
+    }
+  }
+}
+
+template <int BN, int A_MN, int B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  using Cfg = GemmCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + STAGES * Cfg::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmA);
+    prefetch_tensormap(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), NUM_EPI_WARPS);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  const int mn_tiles = p.m_blocks * p.n_blocks;
+  const int total_tiles = mn_tiles * p.splits;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int split = t / mn_tiles, mn = t % mn_tiles;
+        const int m_blk = mn / p.n_blocks, n_blk = mn % p.n_blocks;
+        const int kb0 = split * p.k_blocks_per_split;
+        const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          mbar_arrive_expect_tx(full_bar(stage), Cfg::STAGE_BYTES);
+          const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+          const uint32_t sb = sa + Cfg::A_BYTES;
+          if (A_MN) {
+#pragma unroll
+            for (int c = 0; c < BM / 64; ++c) tma_load_2d(sa + c * (64 * BK * 2), &tmA, full_bar(stage), m_blk * BM + c * 64, kb * BK);
+          } else {
+            tma_load_2d(sa, &tmA, full_bar(stage), kb * BK, m_blk * BM);
+          }
+          if (B_MN) {
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c) tma_load_2d(sb + c * (64 * BK * 2), &tmB, full_bar(stage), n_blk * BN + c * 64, kb * BK);
+          } else {
+            tma_load_2d(sb, &tmB, full_bar(stage), kb * BK, n_blk * BN);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+      // K-major, 128B swizzle: 8-row groups 1024 B apart (SBO); LBO unused (encoded 1).
+      // MN-major, 128B swizzle: 64-element MN chunks one TMA box (64*BK*2 B) apart (LBO),
+      //                         8-row K groups 1024 B apart (SBO).
+      constexpr uint32_t A_LBO = A_MN ? 64 * BK * 2 : 16, B_LBO = B_MN ? 64 * BK * 2 : 16;
+      constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;  // descriptor units of 16 B
+      constexpr uint32_t B_KSTEP = B_MN ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int split = t / mn_tiles;
+        const int kb0 = split * p.k_blocks_per_split;
+        const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks);
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+          const uint64_t a_desc = make_smem_desc(sa, A_LBO, 1024);
+          const uint64_t b_desc = make_smem_desc(sa + Cfg::A_BYTES, B_LBO, 1024);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            umma_bf16(d_tmem, a_desc + (uint64_t)(k * A_KSTEP), b_desc + (uint64_t)(k * B_KSTEP), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          umma_commit(empty_bar(stage));
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit(tfull_bar(acc));
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1u;
+      }
+    }
+  } else if (warp >= 4) {
+    const int q = warp & 3;            // TMEM lane quadrant this warp may read
+    const int half = (warp - 4) >> 2;  // which half of the tile's columns
+    constexpr int CHUNKS = BN / 32;
+    constexpr int CH_PER_HALF = (CHUNKS + 1) / 2;
+    float alpha = p.alpha;
+    if (p.alpha_dev) alpha *= __ldg(p.alpha_dev);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int mn = t % mn_tiles;
+      const int m_blk = mn / p.n_blocks, n_blk = mn % p.n_blocks;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const int m = m_blk * BM + q * 32 + lane;
+#pragma unroll 1
+      for (int i = 0; i < CH_PER_HALF; ++i) {
+        const int c = half * CH_PER_HALF + i;
+        if (c < CHUNKS) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32), v);
+          tmem_ld_wait();
+          epilogue_chunk(p, alpha, m, n_blk * BN + c * 32, v);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1u;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+static std::atomic<long long> g_launches{0};
+
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int resolve_driver_entry_points() {
+  if (g_encode) return VT_OK;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  VT_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  if (qres != cudaDriverEntryPointSuccess || !fn) {
+    set_error("cuTensorMapEncodeTiled not available from the driver");
+    return VT_ERR_CUDA;
+  }
+  g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  return VT_OK;
+}
+
+// 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld elements.
+static int make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner, uint32_t box_outer) {
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d) base=%p inner=%llu outer=%llu ld=%llu box=%ux%u", (int)r, base,
+              (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld, box_inner, box_outer);
+    return VT_ERR_CUDA;
+  }
+  return VT_OK;
+}
+
+template <int BN, int A_MN, int B_MN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t st) {
+  using Cfg = GemmCfg<BN>;
+  static bool attr_set = false;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
+  if (!attr_set) {
+    VT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, st>>>(ta, tb, p);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+template <int BN>
+static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t st) {
+  if (!a_mn && !b_mn) return launch_gemm<BN, 0, 0>(ta, tb, p, grid, st);
+  if (!a_mn && b_mn) return launch_gemm<BN, 0, 1>(ta, tb, p, grid, st);
+  if (a_mn && b_mn) return launch_gemm<BN, 1, 1>(ta, tb, p, grid, st);
+  return launch_gemm<BN, 1, 0>(ta, tb, p, grid, st);
+}
+
+static int g_force_bn = 0;
+
+}  // namespace vt
+
+using namespace vt;
+
+extern "C" void vt_debug_force_block_n(int bn) { vt::g_force_bn = bn; }
+extern "C" int64_t vt_launch_count(void) { return (int64_t)vt::g_launches.load(); }
+extern "C" void vt_reset_launch_count(void) { vt::g_launches.store(0); }
+
+extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void* B, int64_t ldb, int b_major, void* D,
+                            int64_t ldd, int64_t M, int64_t N, int64_t K, const vt_gemm_epilogue* ep, vt_stream stream) {
+  int rc = resolve_driver_entry_points();
+  if (rc) return rc;
+  VT_REQUIRE(A && B && D && ep, "vt_gemm_bf16: null pointer");
+  if (M == 0 || N == 0) return VT_OK;
+  VT_REQUIRE(M > 0 && N > 0 && K > 0 && M < (1ll << 31) && N < (1ll << 31) && K < (1ll << 31), "vt_gemm_bf16: bad sizes M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);
+  VT_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "vt_gemm_bf16: lda/ldb must be multiples of 8 elements (TMA 16-byte pitch), got %lld %lld", (long long)lda, (long long)ldb);
+  VT_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "vt_gemm_bf16: A/B must be 16-byte aligned");
+  VT_REQUIRE(lda >= (a_major ? M : K) && ldb >= (b_major ? N : K), "vt_gemm_bf16: leading dimension smaller than the row");
+  VT_REQUIRE(!ep->accumulate || ep->out_fp32, "vt_gemm_bf16: accumulate needs fp32 output");
+  VT_REQUIRE(ep->split_k <= 1 || ep->accumulate, "vt_gemm_bf16: split_k > 1 needs accumulate");
+  VT_REQUIRE(ep->dropout_p <= 0.f || N % 8 == 0, "vt_gemm_bf16: dropout epilogue needs N %% 8 == 0");
+  VT_REQUIRE(ep->dropout_p < 1.f, "vt_gemm_bf16: dropout_p must be < 1");
+  VT_REQUIRE(!((ep->act == VT_ACT_GELU_BWD || ep->act == VT_ACT_TANH_BWD) && !ep->aux), "vt_gemm_bf16: *_BWD activation needs aux");
+  const bool splitting = ep->split_k > 1 || (ep->split_k == 0 && ep->accumulate);
+  VT_REQUIRE(!splitting || (!ep->bias && ep->act == VT_ACT_NONE && !ep->residual && ep->dropout_p <= 0.f && !ep->aux_out),
+             "vt_gemm_bf16: split-K supports only the alpha epilogue");
+
+  const int sms = num_sms();
+  int BN = 256;
+  const int m_blocks = (int)((M + BM - 1) / BM);
+  if (g_force_bn) {
+    BN = g_force_bn;
+  } else {
+    if (N <= 64) BN = 64;
+    else if (N <= 128) BN = 128;
+    else if (ep->accumulate && ep->split_k != 1) BN = (N % 192 == 0) ? 192 : 256;  // weight gradients: split-K fills the SMs
+    else {
+      // widest tile that keeps every SM busy with the least padded columns (192 divides 768/2304/3072)
+      const int cand[4] = {256, 192, 128, 64};
+      double best = -1.0;
+      for (int i = 0; i < 4; ++i) {
+        const long long nb = (N + cand[i] - 1) / cand[i];
+        const double fill = (double)N / (double)(nb * cand[i]);
+        const long long tiles = (long long)m_blocks * nb;
+        const double occ = tiles >= sms ? 1.0 : (double)tiles / sms;
+        const double mma_eff = cand[i] >= 128 ? 1.0 : 0.7;  // 128x64 tiles are shared-memory bound
+        const double score = fill * occ * mma_eff;
+        if (score > best + 1e-9) { best = score; BN = cand[i]; }
+      }
+    }
+  }
+  VT_REQUIRE(BN == 64 || BN == 128 || BN == 192 || BN == 256, "vt_gemm_bf16: bad block N %d", BN);
+
+  GemmParams p;
+  p.M = (int)M; p.N = (int)N; p.K = (int)K;
+  p.m_blocks = m_blocks;
+  p.n_blocks = (int)((N + BN - 1) / BN);
+  p.k_blocks = (int)((K + BK - 1) / BK);
+  int splits = ep->split_k;
+  if (splits <= 0) {
+    splits = 1;
+    if (ep->accumulate) {
+      long long tiles = (long long)p.m_blocks * p.n_blocks;
+      splits = (int)(sms / tiles);
+      int max_splits = p.k_blocks / 4;
+      if (splits > max_splits) splits = max_splits;
+      if (splits < 1) splits = 1;
+    }
+  }
+  if (splits > p.k_blocks) splits = p.k_blocks;
+  p.k_blocks_per_split = (p.k_blocks + splits - 1) / splits;
+  p.splits = (p.k_blocks + p.k_blocks_per_split - 1) / p.k_blocks_per_split;
+  p.D = D; p.ldd = ldd;
+  p.out_fp32 = ep->out_fp32; p.accumulate = ep->accumulate; p.act = ep->act;
+  p.alpha = ep->alpha; p.alpha_dev = ep->alpha_dev; p.bias = ep->bias;
+  p.residual = (const bf16*)ep->residual; p.ldr = ep->ldr;
+  p.aux = (const bf16*)ep->aux; p.ldaux = ep->ldaux;
+  p.aux_out = (bf16*)ep->aux_out; p.ldaux_out = ep->ldaux_out;
+  p.drop = make_dropout(ep->dropout_p, ep->seed, ep->dropout_stream);
+  p.remap_in = ep->remap_rows_in; p.remap_out = ep->remap_rows_out; p.remap_off = ep->remap_row_off;
+  // 16-byte vector path: every row slice the epilogue touches must be 16-byte aligned
+  const int ob = p.out_fp32 ? 4 : 2;
+  bool vec = ((uintptr_t)D % 16 == 0) && ((ldd * ob) % 16 == 0);
+  if (p.bias) vec = vec && ((uintptr_t)p.bias % 16 == 0);
+  if (p.residual) vec = vec && ((uintptr_t)p.residual % 16 == 0) && (p.ldr % 8 == 0);
+  if (p.aux) vec = vec && ((uintptr_t)p.aux % 16 == 0) && (p.ldaux % 8 == 0);
+  if (p.aux_out) vec = vec && ((uintptr_t)p.aux_out % 16 == 0) && (p.ldaux_out % 8 == 0);
+  p.vec_ok = vec ? 1 : 0;
+
+  CUtensorMap ta, tb;
+  if (a_major) rc = make_map(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK);
+  else rc = make_map(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
+  if (rc) return rc;
+  if (b_major) rc = make_map(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK);
+  else rc = make_map(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)BN);
+  if (rc) return rc;
+
+  long long total = (long long)p.m_blocks * p.n_blocks * p.splits;
+  int grid = (int)(total < sms ? total : sms);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (BN) {
+    case 64: return dispatch_major<64>(a_major, b_major, ta, tb, p, grid, st);
+    case 128: return dispatch_major<128>(a_major, b_major, ta, tb, p, grid, st);
+    case 192: return dispatch_major<192>(a_major, b_major, ta, tb, p, grid, st);
+    default: return dispatch_major<256>(a_major, b_major, ta, tb, p, grid, st);
+  }
+}

@@ -1,0 +1,149 @@
+"""ctypes binding of libvisitron_b200.so (the C ABI in include/visitron_b200.h).
+
+PyTorch is used for device memory and streams only; every op here hands raw device pointers and
+the current CUDA stream to the hand-written sm_100a kernels.  There is NO fallback: if the shared
+library is missing or the device is not sm_100 every call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvisitron_b200.so")
+
+ACT_NONE, ACT_GELU, ACT_TANH, ACT_GELU_BWD, ACT_TANH_BWD = 0, 1, 2, 3, 4
+
+
+class VtError(RuntimeError):
+    pass
+
+
+class GemmEpilogue(C.Structure):
+    _fields_ = [
+        ("out_fp32", C.c_int), ("accumulate", C.c_int), ("split_k", C.c_int), ("act", C.c_int),
+        ("alpha", C.c_float), ("alpha_dev", C.c_void_p), ("bias", C.c_void_p),
+        ("residual", C.c_void_p), ("ldr", C.c_int64),
+        ("aux", C.c_void_p), ("ldaux", C.c_int64),
+        ("aux_out", C.c_void_p), ("ldaux_out", C.c_int64),
+        ("dropout_p", C.c_float), ("seed", C.c_uint64), ("dropout_stream", C.c_uint32),
+        ("remap_rows_in", C.c_int64), ("remap_rows_out", C.c_int64), ("remap_row_off", C.c_int64),
+    ]
+
+
+_lib = None
+_inited = set()
+
+
+def load() -> C.CDLL:
+    """Loads the shared library (no device needed); raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise VtError(
+            "libvisitron_b200.so not found at %s -- build it with `python -m visitron_b200.build`; "
+            "there is no CPU / eager fallback" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    lib.vt_last_error.restype = C.c_char_p
+    lib.vt_launch_count.restype = C.c_int64
+    from . import _signatures
+    _signatures.declare(lib)
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = ""):
+    if rc != 0:
+        raise VtError("%s failed (%d): %s" % (what, rc, load().vt_last_error().decode()))
+
+
+def init(device: Optional[int] = None) -> C.CDLL:
+    lib = load()
+    if not torch.cuda.is_available():
+        raise VtError("visitron_b200 needs a CUDA sm_100 device; there is no CPU fallback")
+    dev = torch.cuda.current_device() if device is None else int(device)
+    if dev not in _inited:
+        check(lib.vt_init(dev), "vt_init")
+        _inited.add(dev)
+    return lib
+
+
+def stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def launch_count() -> int:
+    return int(load().vt_launch_count())
+
+
+def reset_launch_count():
+    load().vt_reset_launch_count()
+
+
+def _row_major_2d(t: torch.Tensor, name: str):
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise VtError("%s must be a 2-D tensor with unit inner stride, got shape %s strides %s"
+                      % (name, tuple(t.shape), t.stride()))
+    return t.stride(0) if t.size(0) > 1 else max(t.stride(0), t.size(1))
+
+
+def gemm(A: torch.Tensor, B: torch.Tensor, *, a_major: int = 0, b_major: int = 0,
+         out: Optional[torch.Tensor] = None, out_dtype=torch.bfloat16, bias=None, act: int = ACT_NONE,
+         alpha: float = 1.0, alpha_dev=None, residual=None, aux=None, aux_out=None,
+         dropout_p: float = 0.0, seed: int = 0, dropout_stream: int = 0, accumulate: bool = False,
+         split_k: int = 0, remap=None, M=None, N=None, K=None) -> torch.Tensor:
+    """D = epilogue(alpha * A x B^T) on the tcgen05 GEMM (see vt_gemm_bf16 in the header).
+
+    a_major/b_major = 0: A is [M,K] / B is [N,K]; = 1: A is [K,M] / B is [K,N] (row-major).
+    """
+    lib = init()
+    assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16
+    lda = _row_major_2d(A, "A")
+    ldb = _row_major_2d(B, "B")
+    m, ka = (A.size(1), A.size(0)) if a_major else (A.size(0), A.size(1))
+    n, kb = (B.size(1), B.size(0)) if b_major else (B.size(0), B.size(1))
+    M = m if M is None else M
+    N = n if N is None else N
+    K = ka if K is None else K
+    if K != kb and (K > ka or K > kb):
+        raise VtError("contraction mismatch: A has %d, B has %d" % (ka, kb))
+    if out is None:
+        if remap is not None:
+            raise VtError("remap needs an explicit output tensor")
+        out = torch.empty((M, N), device=A.device, dtype=out_dtype)
+    ldd = _row_major_2d(out, "out")
+    ep = GemmEpilogue()
+    ep.out_fp32 = 1 if out.dtype == torch.float32 else 0
+    if not ep.out_fp32 and out.dtype != torch.bfloat16:
+        raise VtError("GEMM output must be bf16 or fp32")
+    ep.accumulate = 1 if accumulate else 0
+    ep.split_k = split_k
+    ep.act = act
+    ep.alpha = alpha
+    ep.alpha_dev = ptr(alpha_dev)
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.is_contiguous() and bias.numel() >= N
+    ep.bias = ptr(bias)
+    if residual is not None:
+        assert residual.dtype == torch.bfloat16
+        ep.residual, ep.ldr = ptr(residual), _row_major_2d(residual, "residual")
+    if aux is not None:
+        assert aux.dtype == torch.bfloat16
+        ep.aux, ep.ldaux = ptr(aux), _row_major_2d(aux, "aux")
+    if aux_out is not None:
+        assert aux_out.dtype == torch.bfloat16
+        ep.aux_out, ep.ldaux_out = ptr(aux_out), _row_major_2d(aux_out, "aux_out")
+    ep.dropout_p, ep.seed, ep.dropout_stream = float(dropout_p), int(seed), int(dropout_stream)
+    if remap is not None:
+        ep.remap_rows_in, ep.remap_rows_out, ep.remap_row_off = remap
+    check(lib.vt_gemm_bf16(ptr(A), lda, a_major, ptr(B), ldb, b_major, ptr(out), ldd, M, N, K,
+                           C.byref(ep), stream_ptr()), "vt_gemm_bf16")
+    return out
