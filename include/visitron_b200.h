@@ -81,6 +81,120 @@ int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void* B, int64_t
                  void* D, int64_t ldd, int64_t M, int64_t N, int64_t K, const vt_gemm_epilogue* ep,
                  vt_stream stream);
 
+/* Debug hook for tests: force the GEMM tile width (0 = heuristic; 64/128/192/256). */
+void vt_debug_force_block_n(int bn);
+
+/* ------------------------------------------------------------------------------------------
+ * Row kernels (HBM-bound, one warp per 768-wide row, 16-byte vectors).  hidden must be 768.
+ * Dropout masks are never stored: they are regenerated from (seed, dropout_stream, element index);
+ * p is quantised to 1/65536.  `remap_*` as in vt_gemm_epilogue.
+ * ------------------------------------------------------------------------------------------ */
+
+/* y[remap(m)] = dropout(BertLayerNorm(x[m]))   -- hf/modeling_bert.py:227-240 (TF style, biased
+ * variance, eps inside the sqrt); x already holds dense-output + residual (hf/modeling_bert.py:344,403).
+ * With remap: the optional image-embedding LayerNorm + dropout + torch.cat (vs/encoder.py:280-287). */
+int vt_layernorm_fwd(const void* x, int64_t ldx, const float* gamma, const float* beta, float eps, int64_t rows,
+                     int64_t hidden, void* y, int64_t ldy, float dropout_p, uint64_t seed, uint32_t dropout_stream,
+                     int64_t remap_rows_in, int64_t remap_rows_out, int64_t remap_row_off, vt_stream stream);
+
+/* Rows of fp32 workspace [vt_row_partials_rows(rows)][4][768] the LayerNorm / embedding backward need. */
+int64_t vt_row_partials_rows(int64_t rows);
+
+/* Backward of the site  x = dropout_out(h) + res ; y = LN(x)  (autograd of hf/modeling_bert.py:341-345,
+ * 400-404):  dx = LN'(dy) [bf16, the residual branch], dx_dropped = dx * mask_out [bf16, the operand
+ * of the dense layer's data/weight gradient GEMMs; may be NULL when out_dropout_p == 0],
+ * dgamma/dbeta/dbias (+)= column sums (dbias = colsum(dx_dropped) is the dense bias gradient).
+ * in_dropout_*: mask applied to dy first (sites where dropout FOLLOWS the LayerNorm, vs/encoder.py:280-284);
+ * dy is then read at the remapped row. */
+int vt_layernorm_bwd(const void* dy, int64_t lddy, const void* x, int64_t ldx, const float* gamma, float eps, int64_t rows,
+                     int64_t hidden, void* dx, int64_t lddx, void* dx_dropped, int64_t lddxd, float* partials,
+                     float* dgamma, float* dbeta, float* dbias, float in_dropout_p, uint32_t in_dropout_stream,
+                     float out_dropout_p, uint32_t out_dropout_stream, uint64_t seed, int64_t remap_rows_in,
+                     int64_t remap_rows_out, int64_t remap_row_off, vt_stream stream);
+
+/* BertEmbeddings.forward (hf/modeling_bert.py:256-271): y[s*out_rows_per_sample + t] =
+ * dropout(LN(word[ids] + pos[pos_ids or t] + type[type_ids or 0])); ids int64 [batch, T]. */
+int vt_embed_ln_fwd(const int64_t* ids, const int64_t* type_ids, const int64_t* pos_ids, const float* word,
+                    const float* pos, const float* type, const float* gamma, const float* beta, float eps,
+                    int64_t batch, int64_t T, int64_t out_rows_per_sample, int64_t hidden, void* y, float dropout_p,
+                    uint64_t seed, uint32_t dropout_stream, vt_stream stream);
+/* Its backward: scatter-adds (fp32 atomics) into dword/dpos/dtype, accumulates dgamma/dbeta. */
+int vt_embed_ln_bwd(const void* dy, const int64_t* ids, const int64_t* type_ids, const int64_t* pos_ids, const float* word,
+                    const float* pos, const float* type, const float* gamma, float eps, int64_t batch, int64_t T,
+                    int64_t out_rows_per_sample, int64_t hidden, int64_t type_vocab, float* dword, float* dpos,
+                    float* dtype, float* dgamma, float* dbeta, float* partials, float dropout_p, uint64_t seed,
+                    uint32_t dropout_stream, vt_stream stream);
+
+/* out[c] (+)= sum_r x[r, c]  for bf16 x [rows, ncols] -- bias gradients of the QKV and FFN-up layers.
+ * partials: fp32 [vt_colsum_partials_rows(rows)][roundup8(ncols)]. */
+int64_t vt_colsum_partials_rows(int64_t rows);
+int vt_colsum_bf16(const void* x, int64_t ldx, int64_t rows, int64_t ncols, float* partials, float* out, int accumulate,
+                   vt_stream stream);
+
+/* fp32 [rows, cols] -> bf16 copy (dst, may be NULL) and/or bf16 transpose (dst_t, may be NULL):
+ * the per-step cast of the fp32 master weights into tensor-core operands. */
+int vt_cast_f32_bf16(const float* src, int64_t lds, int64_t rows, int64_t cols, void* dst, int64_t ldd, void* dst_t,
+                     int64_t ldt, vt_stream stream);
+/* out[r] = bf16([a[r, 0:d0] | b[r, 0:d1] | 0...]) : img_feats and img_location_embeddings become ONE
+ * GEMM operand so that img_embedding(x) + location_embeds(l) (vs/encoder.py:277-279) is one contraction. */
+int vt_pad_cast_concat(const float* a, int64_t d0, const float* b, int64_t d1, int64_t rows, void* out, int64_t ldo,
+                       vt_stream stream);
+/* y[m] = x[remap(m)] * dropout_mask(m) */
+int vt_dropout_rows(const void* x, int64_t ldx, int64_t rows, int64_t hidden, void* y, int64_t ldy, float dropout_p,
+                    uint64_t seed, uint32_t dropout_stream, int64_t remap_rows_in, int64_t remap_rows_out,
+                    int64_t remap_row_off, vt_stream stream);
+/* dst[r] = src[idx[r]] ; dst[idx[r]] += src[r]   (compaction of the labelled rows for the MLM / token heads) */
+int vt_gather_rows(const void* src, int64_t lds, const int64_t* idx, int64_t n, int64_t hidden, void* dst, int64_t ldd,
+                   vt_stream stream);
+int vt_scatter_add_rows(const void* src, int64_t lds, const int64_t* idx, int64_t n, int64_t hidden, void* dst, int64_t ldd,
+                        vt_stream stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused masked-softmax self-attention (oscar/modeling_bert.py:52-72), head dim 64.
+ * qkv: bf16 [B*S, ld] = [Q | K | V] (each heads*64 wide) as written by the fused QKV GEMM.
+ * bias: fp32 [B, S] additive key bias from vt_mask_bias.  ctx: bf16 [B*S, heads*64].
+ * lse: fp32 [B, heads, S, 2] = (row max, 1 / sum exp) saved for backward.  dsum_ws: fp32 [B, heads, S] scratch.
+ * ------------------------------------------------------------------------------------------ */
+/* bias = (1 - mask) * -10000 in fp32 for any mask value (vs/encoder.py:226-241).
+ * mask_dtype: 0 int64, 1 uint8/bool, 2 int32, 3 fp32. */
+int vt_mask_bias(const void* mask, int mask_dtype, int64_t n, float* bias, vt_stream stream);
+int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, int64_t B, int64_t S, int64_t heads, int64_t head_dim,
+                     void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream);
+int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, const void* ctx, const void* dctx, const float* lse,
+                     float* dsum_ws, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv, float dropout_p,
+                     uint64_t seed, uint32_t dropout_stream, vt_stream stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Pre-training heads (vs/encoder.py:377-441).
+ * ------------------------------------------------------------------------------------------ */
+/* Row-wise CrossEntropy + argmax over fp32 logits [rows, ld] (every row labelled, labels in [0, ncols)).
+ * double_softmax = 1 reproduces token_head's Softmax -> CrossEntropyLoss (vs/encoder.py:323-326,381-385).
+ * stats: fp32 [rows, 2] saved for backward. */
+int vt_softmax_ce_fwd(const float* logits, int64_t ld, int64_t rows, int64_t ncols, const int64_t* labels, int double_softmax,
+                      float* row_loss, int64_t* argmax, float* stats, vt_stream stream);
+/* dlogits (bf16 [rows, ld_out], pad columns zeroed) = scale * (*scale_dev) * dLoss_row/dlogits */
+int vt_softmax_ce_bwd(const float* logits, int64_t ld, int64_t rows, int64_t ncols, const int64_t* labels, int double_softmax,
+                      const float* stats, float scale, const float* scale_dev, void* dlogits, int64_t ld_out, vt_stream stream);
+/* NextActionPrediction (vs/encoder.py:142-158) + CrossEntropy(ignore_index=-1) + argmax (:391-398):
+ * scores = log_softmax(pooled W^T + b) fp32 [B, actions]; labels may be NULL. */
+int vt_action_head_fwd(const float* pooled, const float* W, const float* bias, int64_t B, int64_t hidden, int64_t actions,
+                       const int64_t* labels, float* scores, float* row_loss, int64_t* argmax, vt_stream stream);
+/* dpooled = ..., dW += ..., dbias += ...; gradient scale = (*g_dev) / (*n_valid_dev) */
+int vt_action_head_bwd(const float* pooled, const float* W, int64_t B, int64_t hidden, int64_t actions, const int64_t* labels,
+                       const float* scores, const float* n_valid_dev, const float* g_dev, float* dpooled, float* dW, float* dbias,
+                       vt_stream stream);
+/* out8 = {loss, mask_loss, next_loss, token_loss, words_accuracy, action_accuracy, token_accuracy, n_valid_actions}
+ * (vs/encoder.py:396-441; means over labelled rows, 0/0 -> nan like the reference). */
+int vt_pretrain_finalize(const float* mlm_loss, const int64_t* mlm_arg, const int64_t* mlm_lab, int64_t n_mlm, const float* tok_loss,
+                         const int64_t* tok_arg, const int64_t* tok_lab, int64_t n_tok, const float* act_loss, const int64_t* act_arg,
+                         const int64_t* act_lab, int64_t n_act, float* out8, vt_stream stream);
+
+/* dx (bf16) = dy * (1 - y^2)  -- backward of the pooler's tanh (hf/modeling_bert.py:461-467) */
+int vt_tanh_bwd(const float* dy, const float* y, int64_t n, void* dx, vt_stream stream);
+/* module-boundary casts: bf16 -> fp32 ; bf16(x) (+ addend) */
+int vt_cast_bf16_f32(const void* x, int64_t n, float* y, vt_stream stream);
+int vt_cast_f32_bf16_add(const float* x, const void* addend, int64_t n, void* y, vt_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -8,7 +8,31 @@ SIGNATURES = {
     "vt_num_sms": (I, []),
     "vt_launch_count": (I64, []),
     "vt_reset_launch_count": (None, []),
+    "vt_debug_force_block_n": (None, [I]),
     "vt_gemm_bf16": (I, [P, I64, I, P, I64, I, P, I64, I64, I64, I64, P, P]),
+    "vt_layernorm_fwd": (I, [P, I64, P, P, F, I64, I64, P, I64, F, U64, U32, I64, I64, I64, P]),
+    "vt_row_partials_rows": (I64, [I64]),
+    "vt_layernorm_bwd": (I, [P, I64, P, I64, P, F, I64, I64, P, I64, P, I64, P, P, P, P, F, U32, F, U32, U64, I64, I64, I64, P]),
+    "vt_embed_ln_fwd": (I, [P, P, P, P, P, P, P, P, F, I64, I64, I64, I64, P, F, U64, U32, P]),
+    "vt_embed_ln_bwd": (I, [P, P, P, P, P, P, P, P, F, I64, I64, I64, I64, I64, P, P, P, P, P, P, F, U64, U32, P]),
+    "vt_colsum_partials_rows": (I64, [I64]),
+    "vt_colsum_bf16": (I, [P, I64, I64, I64, P, P, I, P]),
+    "vt_cast_f32_bf16": (I, [P, I64, I64, I64, P, I64, P, I64, P]),
+    "vt_pad_cast_concat": (I, [P, I64, P, I64, I64, P, I64, P]),
+    "vt_dropout_rows": (I, [P, I64, I64, I64, P, I64, F, U64, U32, I64, I64, I64, P]),
+    "vt_gather_rows": (I, [P, I64, P, I64, I64, P, I64, P]),
+    "vt_scatter_add_rows": (I, [P, I64, P, I64, I64, P, I64, P]),
+    "vt_mask_bias": (I, [P, I, I64, P, P]),
+    "vt_attention_fwd": (I, [P, I64, P, I64, I64, I64, I64, P, P, F, U64, U32, P]),
+    "vt_attention_bwd": (I, [P, I64, P, P, P, P, P, I64, I64, I64, I64, P, F, U64, U32, P]),
+    "vt_softmax_ce_fwd": (I, [P, I64, I64, I64, P, I, P, P, P, P]),
+    "vt_softmax_ce_bwd": (I, [P, I64, I64, I64, P, I, P, F, P, P, I64, P]),
+    "vt_action_head_fwd": (I, [P, P, P, I64, I64, I64, P, P, P, P, P]),
+    "vt_action_head_bwd": (I, [P, P, I64, I64, I64, P, P, P, P, P, P, P, P]),
+    "vt_pretrain_finalize": (I, [P, P, P, I64, P, P, P, I64, P, P, P, I64, P, P]),
+    "vt_tanh_bwd": (I, [P, P, I64, P, P]),
+    "vt_cast_bf16_f32": (I, [P, I64, P, P]),
+    "vt_cast_f32_bf16_add": (I, [P, P, I64, P, P]),
 }
 
 

@@ -1,0 +1,365 @@
+// Loss / scoring kernels of the pre-training heads (vs/encoder.py:377-441):
+//   * row-wise softmax cross-entropy + argmax over fp32 logits (masked-LM head), with the
+//     reference's DOUBLE softmax for the detector-class head (Softmax module followed by
+//     CrossEntropyLoss, vs/encoder.py:323-326,381-385) and its backward (writes bf16 dlogits);
+//   * the 36-way next-action head: Linear + LogSoftmax + CrossEntropy + argmax in one warp per
+//     sample (vs/encoder.py:142-158,391-398) and its backward;
+//   * the 7-scalar loss / accuracy assembly (vs/encoder.py:396-441);
+//   * small elementwise helpers (tanh backward, bf16 <-> fp32 casts).
+#include "common.cuh"
+
+namespace vt {
+
+void count_launch(int n);
+
+constexpr int CE_THREADS = 256;
+
+struct MaxArg {
+  float m;
+  int idx;
+};
+__device__ __forceinline__ MaxArg better(MaxArg a, MaxArg b) {  // larger value; ties -> lower index (torch.argmax)
+  return (b.m > a.m || (b.m == a.m && b.idx < a.idx)) ? b : a;
+}
+
+template <typename T>
+__device__ __forceinline__ T block_reduce(T v, T (*op)(T, T), T* scratch) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    T other;
+    unsigned char* src = reinterpret_cast<unsigned char*>(&v);
+    unsigned char* dst = reinterpret_cast<unsigned char*>(&other);
+#pragma unroll
+    for (int w = 0; w < (int)(sizeof(T) / 4); ++w) reinterpret_cast<uint32_t*>(dst)[w] = __shfl_xor_sync(0xffffffffu, reinterpret_cast<uint32_t*>(src)[w], o);
+    v = op(v, other);
+  }
+  __syncthreads();
+  if (lane == 0) scratch[warp] = v;
+  __syncthreads();
+  T r = scratch[0];
+  for (int w = 1; w < (int)(blockDim.x >> 5); ++w) r = op(r, scratch[w]);
+  return r;
+}
+__device__ __forceinline__ float fadd(float a, float b) { return a + b; }
+__device__ __forceinline__ float fmaxop(float a, float b) { return fmaxf(a, b); }
+
+// One CTA per row.  stats[row] = {lse, lse2}: lse = logsumexp(x); double softmax: lse2 = logsumexp(softmax(x)).
+__global__ void __launch_bounds__(CE_THREADS)
+softmax_ce_fwd_kernel(const float* __restrict__ logits, long long ld, int ncols, const long long* __restrict__ labels, int double_softmax,
+                      float* __restrict__ row_loss, long long* __restrict__ argmax, float* __restrict__ stats) {
+  __shared__ MaxArg s_ma[CE_THREADS / 32];
+  __shared__ float s_f[CE_THREADS / 32];
+  const long long row = blockIdx.x;
+  const float* x = logits + row * ld;
+  MaxArg ma = {-INFINITY, 0x7fffffff};
+  for (int j = threadIdx.x; j < ncols; j += CE_THREADS) ma = better(ma, MaxArg{x[j], j});
+  ma = block_reduce<MaxArg>(ma, better, s_ma);
+  float s = 0.f;
+  for (int j = threadIdx.x; j < ncols; j += CE_THREADS) s += __expf(x[j] - ma.m);
+  s = block_reduce<float>(s, fadd, s_f);
+  const float lse = ma.m + logf(s);
+  const long long y = labels[row];
+  float loss, lse2 = 0.f;
+  if (!double_softmax) {
+    loss = lse - x[y];
+  } else {
+    // probabilities are in [0,1]: no max subtraction needed for the second log-sum-exp
+    float s2 = 0.f;
+    for (int j = threadIdx.x; j < ncols; j += CE_THREADS) s2 += __expf(__expf(x[j] - lse));
+    s2 = block_reduce<float>(s2, fadd, s_f);
+    lse2 = logf(s2);
+    loss = lse2 - __expf(x[y] - lse);
+  }
+  if (threadIdx.x == 0) {
+    row_loss[row] = loss;
+    argmax[row] = ma.idx;
+    stats[2 * row] = lse;
+    stats[2 * row + 1] = lse2;
+  }
+}
+
+// dlogits[row, j] = g * dL/dx_j, g = scale * (*scale_dev); pad columns [ncols, ld_out) are zeroed.
+__global__ void __launch_bounds__(CE_THREADS)
+softmax_ce_bwd_kernel(const float* __restrict__ logits, long long ld, int ncols, const long long* __restrict__ labels, int double_softmax,
+                      const float* __restrict__ stats, float scale, const float* __restrict__ scale_dev, bf16* __restrict__ dlogits,
+                      long long ld_out) {
+  __shared__ float s_f[CE_THREADS / 32];
+  const long long row = blockIdx.x;
+  const float* x = logits + row * ld;
+  bf16* d = dlogits + row * ld_out;
+  const float g = scale * (scale_dev ? __ldg(scale_dev) : 1.0f);
+  const float lse = stats[2 * row], lse2 = stats[2 * row + 1];
+  const int y = (int)labels[row];
+  if (!double_softmax) {
+    for (int j = threadIdx.x; j < ld_out; j += CE_THREADS) {
+      float v = 0.f;
+      if (j < ncols) v = (__expf(x[j] - lse) - (j == y ? 1.f : 0.f)) * g;
+      d[j] = __float2bfloat16(v);
+    }
+  } else {
+    // L = lse2 - p_y,  p = softmax(x),  q = softmax(p):  dL/dp_k = q_k - [k == y];  dL/dx_j = p_j (dL/dp_j - sum_k dL/dp_k p_k)
+    float dot = 0.f;
+    for (int j = threadIdx.x; j < ncols; j += CE_THREADS) {
+      float pj = __expf(x[j] - lse);
+      dot += (__expf(pj - lse2) - (j == y ? 1.f : 0.f)) * pj;
+    }
+    dot = block_reduce<float>(dot, fadd, s_f);
+    for (int j = threadIdx.x; j < ld_out; j += CE_THREADS) {
+      float v = 0.f;
+      if (j < ncols) {
+        float pj = __expf(x[j] - lse);
+        v = pj * ((__expf(pj - lse2) - (j == y ? 1.f : 0.f)) - dot) * g;
+      }
+      d[j] = __float2bfloat16(v);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// next-action head: one warp per sample.  scores = log_softmax(pooled . W^T + b)  (returned),
+// loss = CrossEntropy(scores, y) = -log_softmax(scores)[y]  (the reference applies log-softmax twice)
+// ---------------------------------------------------------------------------------------------
+constexpr int MAX_ACTIONS = 64;
+
+__global__ void __launch_bounds__(128)
+action_head_fwd_kernel(const float* __restrict__ pooled, const float* __restrict__ W, const float* __restrict__ bias, int B, int Hd, int A,
+                       const long long* __restrict__ labels, float* __restrict__ scores, float* __restrict__ row_loss,
+                       long long* __restrict__ argmax) {
+  const int lane = threadIdx.x & 31;
+  const int s = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (s >= B) return;
+  const float* x = pooled + (long long)s * Hd;
+  float mine0 = -INFINITY, mine1 = -INFINITY;  // lane owns actions lane and lane + 32
+  for (int a = 0; a < A; ++a) {
+    const float* w = W + (long long)a * Hd;
+    float acc = 0.f;
+    for (int k = lane; k < Hd; k += 32) acc = fmaf(x[k], __ldg(w + k), acc);
+    acc = warp_sum(acc) + bias[a];
+    if ((a & 31) == lane) { if (a < 32) mine0 = acc; else mine1 = acc; }
+  }
+  float m = warp_max(fmaxf(mine0, mine1));
+  float e = (lane < A ? __expf(mine0 - m) : 0.f) + (lane + 32 < A ? __expf(mine1 - m) : 0.f);
+  const float lse = m + logf(warp_sum(e));
+  const float ls0 = mine0 - lse, ls1 = mine1 - lse;  // log-probabilities
+  float e2 = (lane < A ? __expf(ls0) : 0.f) + (lane + 32 < A ? __expf(ls1) : 0.f);
+  const float lse2 = logf(warp_sum(e2));
+  if (lane < A) scores[(long long)s * A + lane] = ls0;
+  if (lane + 32 < A) scores[(long long)s * A + lane + 32] = ls1;
+  // argmax with lowest-index tie break
+  float bv = lane < A ? ls0 : -INFINITY;
+  int bi = lane;
+  if (lane + 32 < A && ls1 > bv) { bv = ls1; bi = lane + 32; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+  }
+  const long long y = labels ? labels[s] : -1;
+  float ly = 0.f;
+  if (y >= 0) {
+    float cand = (y < 32) ? ls0 : ls1;
+    ly = __shfl_sync(0xffffffffu, cand, (int)(y & 31));
+  }
+  if (lane == 0) {
+    row_loss[s] = (y >= 0) ? (lse2 - ly) : 0.f;
+    argmax[s] = bi;
+  }
+}
+
+// dscore[s, a] = (exp(score[s,a]) - [a == y_s]) * g / n_valid ; then dpooled = dscore . W, dW = dscore^T . pooled, db = colsum
+__global__ void __launch_bounds__(256)
+action_head_bwd_kernel(const float* __restrict__ pooled, const float* __restrict__ W, int B, int Hd, int A, const long long* __restrict__ labels,
+                       const float* __restrict__ scores, const float* __restrict__ n_valid_dev, const float* __restrict__ g_dev,
+                       float* __restrict__ dpooled, float* __restrict__ dW, float* __restrict__ dbias) {
+  extern __shared__ float sd[];  // [B][A] dscore
+  const float nv = __ldg(n_valid_dev);
+  const float g = (g_dev ? __ldg(g_dev) : 1.0f) / nv;  // nv == 0 -> inf/nan like the reference's empty mean
+  for (int i = threadIdx.x; i < B * A; i += blockDim.x) {
+    const int s = i / A, a = i % A;
+    const long long y = labels[s];
+    sd[i] = (y >= 0) ? (__expf(scores[i]) - (a == y ? 1.f : 0.f)) * g : 0.f;
+  }
+  __syncthreads();
+  // this CTA owns the hidden columns [k0, k1)
+  const int per = (Hd + gridDim.x - 1) / gridDim.x;
+  const int k0 = blockIdx.x * per, k1 = min(Hd, k0 + per);
+  for (int i = threadIdx.x; i < B * (k1 - k0); i += blockDim.x) {
+    const int s = i / (k1 - k0), k = k0 + i % (k1 - k0);
+    float acc = 0.f;
+    for (int a = 0; a < A; ++a) acc = fmaf(sd[s * A + a], __ldg(W + (long long)a * Hd + k), acc);
+    dpooled[(long long)s * Hd + k] = acc;
+  }
+  for (int i = threadIdx.x; i < A * (k1 - k0); i += blockDim.x) {
+    const int a = i / (k1 - k0), k = k0 + i % (k1 - k0);
+    float acc = 0.f;
+    for (int s = 0; s < B; ++s) acc = fmaf(sd[s * A + a], pooled[(long long)s * Hd + k], acc);
+    dW[(long long)a * Hd + k] += acc;
+  }
+  if (blockIdx.x == 0)
+    for (int a = threadIdx.x; a < A; a += blockDim.x) {
+      float acc = 0.f;
+      for (int s = 0; s < B; ++s) acc += sd[s * A + a];
+      dbias[a] += acc;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// 7-tuple assembly (vs/encoder.py:396-441).  out = {loss, mask_loss, next_loss, token_loss,
+// words_accuracy, action_accuracy, token_accuracy, n_valid_actions}
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+pretrain_finalize_kernel(const float* __restrict__ mlm_loss, const long long* __restrict__ mlm_arg, const long long* __restrict__ mlm_lab, long long n_mlm,
+                         const float* __restrict__ tok_loss, const long long* __restrict__ tok_arg, const long long* __restrict__ tok_lab, long long n_tok,
+                         const float* __restrict__ act_loss, const long long* __restrict__ act_arg, const long long* __restrict__ act_lab, long long n_act,
+                         float* __restrict__ out) {
+  __shared__ float sf[8];
+  float a = 0.f, c = 0.f;
+  for (long long i = threadIdx.x; i < n_mlm; i += blockDim.x) { a += mlm_loss[i]; c += (mlm_arg[i] == mlm_lab[i]) ? 1.f : 0.f; }
+  const float mlm_sum = block_reduce<float>(a, fadd, sf), mlm_ok = block_reduce<float>(c, fadd, sf);
+  a = 0.f; c = 0.f;
+  for (long long i = threadIdx.x; i < n_tok; i += blockDim.x) { a += tok_loss[i]; c += (tok_arg[i] == tok_lab[i]) ? 1.f : 0.f; }
+  const float tok_sum = block_reduce<float>(a, fadd, sf), tok_ok = block_reduce<float>(c, fadd, sf);
+  a = 0.f; c = 0.f;
+  float v = 0.f;
+  for (long long i = threadIdx.x; i < n_act; i += blockDim.x) {
+    const bool valid = act_lab[i] >= 0;
+    a += valid ? act_loss[i] : 0.f;
+    v += valid ? 1.f : 0.f;
+    c += (act_arg[i] == act_lab[i]) ? 1.f : 0.f;
+  }
+  const float act_sum = block_reduce<float>(a, fadd, sf), act_ok = block_reduce<float>(c, fadd, sf), act_valid = block_reduce<float>(v, fadd, sf);
+  if (threadIdx.x == 0) {
+    const float mask_loss = mlm_sum / (float)n_mlm;     // 0/0 -> nan, as CrossEntropyLoss over an all-ignored batch
+    const float token_loss = tok_sum / (float)n_tok;
+    const float next_loss = act_sum / act_valid;
+    out[0] = mask_loss + next_loss + token_loss;
+    out[1] = mask_loss;
+    out[2] = next_loss;
+    out[3] = token_loss;
+    out[4] = mlm_ok / (float)n_mlm;
+    out[5] = act_ok / (float)n_act;
+    out[6] = tok_ok / (float)n_tok;
+    out[7] = act_valid;
+  }
+}
+
+__global__ void tanh_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, long long n, bf16* __restrict__ dx) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dx[i] = __float2bfloat16(dy[i] * (1.0f - y[i] * y[i]));
+}
+
+__global__ void cast_bf16_f32_kernel(const bf16* __restrict__ x, long long n8, float* __restrict__ y) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float v[8];
+    unpack8(__ldg(reinterpret_cast<const uint4*>(x) + i), v);
+    reinterpret_cast<float4*>(y)[2 * i] = make_float4(v[0], v[1], v[2], v[3]);
+    reinterpret_cast<float4*>(y)[2 * i + 1] = make_float4(v[4], v[5], v[6], v[7]);
+  }
+}
+// y = bf16(x) (+ bf16 add of `addend` when given)
+__global__ void cast_f32_bf16_flat_kernel(const float* __restrict__ x, const bf16* __restrict__ addend, long long n8, bf16* __restrict__ y) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float4 a = __ldg(reinterpret_cast<const float4*>(x) + 2 * i), b = __ldg(reinterpret_cast<const float4*>(x) + 2 * i + 1);
+    float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    if (addend) {
+      float w[8];
+      unpack8(__ldg(reinterpret_cast<const uint4*>(addend) + i), w);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += w[j];
+    }
+    reinterpret_cast<uint4*>(y)[i] = pack8(v);
+  }
+}
+
+}  // namespace vt
+
+using namespace vt;
+
+extern "C" int vt_softmax_ce_fwd(const float* logits, int64_t ld, int64_t rows, int64_t ncols, const int64_t* labels, int double_softmax,
+                                 float* row_loss, int64_t* argmax, float* stats, vt_stream stream) {
+  VT_REQUIRE(rows >= 0 && ncols > 0 && ncols < (1ll << 31) && ld >= ncols, "vt_softmax_ce_fwd: bad sizes");
+  if (rows == 0) return VT_OK;
+  softmax_ce_fwd_kernel<<<(unsigned)rows, CE_THREADS, 0, (cudaStream_t)stream>>>(logits, ld, (int)ncols, (const long long*)labels, double_softmax,
+                                                                                 row_loss, (long long*)argmax, stats);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_softmax_ce_bwd(const float* logits, int64_t ld, int64_t rows, int64_t ncols, const int64_t* labels, int double_softmax,
+                                 const float* stats, float scale, const float* scale_dev, void* dlogits, int64_t ld_out, vt_stream stream) {
+  VT_REQUIRE(rows >= 0 && ncols > 0 && ld >= ncols && ld_out >= ncols, "vt_softmax_ce_bwd: bad sizes");
+  if (rows == 0) return VT_OK;
+  softmax_ce_bwd_kernel<<<(unsigned)rows, CE_THREADS, 0, (cudaStream_t)stream>>>(logits, ld, (int)ncols, (const long long*)labels, double_softmax,
+                                                                                 stats, scale, scale_dev, (bf16*)dlogits, ld_out);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_action_head_fwd(const float* pooled, const float* W, const float* bias, int64_t B, int64_t hidden, int64_t actions,
+                                  const int64_t* labels, float* scores, float* row_loss, int64_t* argmax, vt_stream stream) {
+  VT_REQUIRE(actions > 0 && actions <= MAX_ACTIONS, "vt_action_head_fwd: action space %lld outside the supported envelope (<= 64)", (long long)actions);
+  if (B == 0) return VT_OK;
+  action_head_fwd_kernel<<<(unsigned)((B + 3) / 4), 128, 0, (cudaStream_t)stream>>>(pooled, W, bias, (int)B, (int)hidden, (int)actions,
+                                                                                    (const long long*)labels, scores, row_loss, (long long*)argmax);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_action_head_bwd(const float* pooled, const float* W, int64_t B, int64_t hidden, int64_t actions, const int64_t* labels,
+                                  const float* scores, const float* n_valid_dev, const float* g_dev, float* dpooled, float* dW, float* dbias,
+                                  vt_stream stream) {
+  VT_REQUIRE(actions > 0 && actions <= MAX_ACTIONS && B * actions * 4 <= 160 * 1024, "vt_action_head_bwd: batch x actions too large for one CTA's shared memory");
+  if (B == 0) return VT_OK;
+  const size_t smem = (size_t)B * actions * sizeof(float);
+  static bool attr = false;
+  if (!attr) { VT_CUDA(cudaFuncSetAttribute(action_head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)); attr = true; }
+  action_head_bwd_kernel<<<24, 256, smem, (cudaStream_t)stream>>>(pooled, W, (int)B, (int)hidden, (int)actions, (const long long*)labels, scores,
+                                                                 n_valid_dev, g_dev, dpooled, dW, dbias);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_pretrain_finalize(const float* mlm_loss, const int64_t* mlm_arg, const int64_t* mlm_lab, int64_t n_mlm, const float* tok_loss,
+                                    const int64_t* tok_arg, const int64_t* tok_lab, int64_t n_tok, const float* act_loss, const int64_t* act_arg,
+                                    const int64_t* act_lab, int64_t n_act, float* out8, vt_stream stream) {
+  pretrain_finalize_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(mlm_loss, (const long long*)mlm_arg, (const long long*)mlm_lab, n_mlm, tok_loss,
+                                                               (const long long*)tok_arg, (const long long*)tok_lab, n_tok, act_loss,
+                                                               (const long long*)act_arg, (const long long*)act_lab, n_act, out8);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_tanh_bwd(const float* dy, const float* y, int64_t n, void* dx, vt_stream stream) {
+  if (n == 0) return VT_OK;
+  tanh_bwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(dy, y, n, (bf16*)dx);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_cast_bf16_f32(const void* x, int64_t n, float* y, vt_stream stream) {
+  VT_REQUIRE(n % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0, "vt_cast_bf16_f32: n %% 8 == 0 and 16-byte alignment required");
+  if (n == 0) return VT_OK;
+  long long n8 = n / 8, g = (n8 + 255) / 256, cap = (long long)num_sms() * 16;
+  cast_bf16_f32_kernel<<<(unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream>>>((const bf16*)x, n8, y);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_cast_f32_bf16_add(const float* x, const void* addend, int64_t n, void* y, vt_stream stream) {
+  VT_REQUIRE(n % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0 && ((uintptr_t)addend & 15) == 0, "vt_cast_f32_bf16_add: n %% 8 == 0 and 16-byte alignment required");
+  if (n == 0) return VT_OK;
+  long long n8 = n / 8, g = (n8 + 255) / 256, cap = (long long)num_sms() * 16;
+  cast_f32_bf16_flat_kernel<<<(unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream>>>(x, (const bf16*)addend, n8, (bf16*)y);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}

@@ -1,0 +1,222 @@
+"""Tensor-level wrappers over the C ABI (one function per entry point of include/visitron_b200.h).
+
+These allocate outputs with torch and pass raw pointers + the current stream; no arithmetic happens
+in Python.  `lib.gemm` lives in lib.py.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import lib
+from .lib import check, init, ptr, stream_ptr
+
+H = 768
+BF16, F32 = torch.bfloat16, torch.float32
+
+_MASK_CODES = {torch.int64: 0, torch.uint8: 1, torch.bool: 1, torch.int32: 2, torch.float32: 3}
+
+
+def _ws(device, n) -> torch.Tensor:
+    return torch.empty(n, device=device, dtype=F32)
+
+
+def roundup(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+def layernorm_fwd(x, gamma, beta, eps, out=None, dropout_p=0.0, seed=0, stream_id=0, remap=(0, 0, 0)):
+    L = init()
+    rows = x.size(0)
+    if out is None:
+        out = torch.empty_like(x)
+    check(L.vt_layernorm_fwd(ptr(x), x.stride(0), ptr(gamma), ptr(beta), eps, rows, x.size(1), ptr(out), out.stride(0),
+                             dropout_p, seed, stream_id, *remap, stream_ptr()), "vt_layernorm_fwd")
+    return out
+
+
+def layernorm_bwd(dy, x, gamma, eps, dgamma, dbeta, dbias=None, want_dx=True, out_dropout_p=0.0, out_stream=0,
+                  in_dropout_p=0.0, in_stream=0, seed=0, remap=(0, 0, 0), dx=None, dxd=None):
+    """Returns (dx, dx_dropped); dx_dropped is dx itself when no output dropout is active."""
+    L = init()
+    rows = x.size(0)
+    if want_dx and dx is None:
+        dx = torch.empty_like(x)
+    if out_dropout_p > 0 and dxd is None:
+        dxd = torch.empty_like(x)
+    parts = _ws(x.device, int(L.vt_row_partials_rows(rows)) * 4 * H)
+    check(L.vt_layernorm_bwd(ptr(dy), dy.stride(0), ptr(x), x.stride(0), ptr(gamma), eps, rows, x.size(1),
+                             ptr(dx), dx.stride(0) if dx is not None else 0, ptr(dxd), dxd.stride(0) if dxd is not None else 0,
+                             ptr(parts), ptr(dgamma), ptr(dbeta), ptr(dbias), in_dropout_p, in_stream, out_dropout_p, out_stream,
+                             seed, *remap, stream_ptr()), "vt_layernorm_bwd")
+    return dx, (dxd if dxd is not None else dx)
+
+
+def embed_ln_fwd(ids, type_ids, pos_ids, word, pos, typ, gamma, beta, eps, out, rows_per_sample, dropout_p=0.0, seed=0, stream_id=0):
+    L = init()
+    b, T = ids.shape
+    check(L.vt_embed_ln_fwd(ptr(ids), ptr(type_ids), ptr(pos_ids), ptr(word), ptr(pos), ptr(typ), ptr(gamma), ptr(beta), eps,
+                            b, T, rows_per_sample, word.size(1), ptr(out), dropout_p, seed, stream_id, stream_ptr()), "vt_embed_ln_fwd")
+    return out
+
+
+def embed_ln_bwd(dy, ids, type_ids, pos_ids, word, pos, typ, gamma, eps, rows_per_sample, dword, dpos, dtype, dgamma, dbeta,
+                 dropout_p=0.0, seed=0, stream_id=0):
+    L = init()
+    b, T = ids.shape
+    parts = _ws(dy.device, int(L.vt_row_partials_rows(b * T)) * 4 * H)
+    check(L.vt_embed_ln_bwd(ptr(dy), ptr(ids), ptr(type_ids), ptr(pos_ids), ptr(word), ptr(pos), ptr(typ), ptr(gamma), eps, b, T,
+                            rows_per_sample, word.size(1), typ.size(0), ptr(dword), ptr(dpos), ptr(dtype), ptr(dgamma), ptr(dbeta),
+                            ptr(parts), dropout_p, seed, stream_id, stream_ptr()), "vt_embed_ln_bwd")
+
+
+def colsum(x, out, ncols=None, accumulate=True):
+    L = init()
+    rows = x.size(0)
+    ncols = x.size(1) if ncols is None else ncols
+    parts = _ws(x.device, int(L.vt_colsum_partials_rows(rows)) * roundup(ncols, 8))
+    check(L.vt_colsum_bf16(ptr(x), x.stride(0), rows, ncols, ptr(parts), ptr(out), 1 if accumulate else 0, stream_ptr()), "vt_colsum_bf16")
+    return out
+
+
+def cast_weight(src, dst=None, dst_t=None):
+    """fp32 [rows, cols] -> bf16 dst [rows, >=cols] and/or transposed dst_t [cols, >=rows]."""
+    L = init()
+    rows, cols = src.shape
+    check(L.vt_cast_f32_bf16(ptr(src), src.stride(0), rows, cols, ptr(dst), dst.stride(0) if dst is not None else 0,
+                             ptr(dst_t), dst_t.stride(0) if dst_t is not None else 0, stream_ptr()), "vt_cast_f32_bf16")
+
+
+def pad_cast_concat(a, b, out):
+    L = init()
+    rows = a.size(0)
+    check(L.vt_pad_cast_concat(ptr(a), a.size(1), ptr(b), b.size(1) if b is not None else 0, rows, ptr(out), out.stride(0), stream_ptr()),
+          "vt_pad_cast_concat")
+    return out
+
+
+def dropout_rows(x, rows, out, dropout_p, seed, stream_id, remap=(0, 0, 0)):
+    L = init()
+    check(L.vt_dropout_rows(ptr(x), x.stride(0), rows, H, ptr(out), out.stride(0), dropout_p, seed, stream_id, *remap, stream_ptr()),
+          "vt_dropout_rows")
+    return out
+
+
+def gather_rows(src, idx, out=None):
+    L = init()
+    n = idx.numel()
+    if out is None:
+        out = torch.empty((n, H), device=src.device, dtype=BF16)
+    check(L.vt_gather_rows(ptr(src), src.stride(0), ptr(idx), n, H, ptr(out), out.stride(0), stream_ptr()), "vt_gather_rows")
+    return out
+
+
+def scatter_add_rows(src, idx, dst):
+    L = init()
+    check(L.vt_scatter_add_rows(ptr(src), src.stride(0), ptr(idx), idx.numel(), H, ptr(dst), dst.stride(0), stream_ptr()), "vt_scatter_add_rows")
+
+
+def mask_bias(mask: torch.Tensor) -> torch.Tensor:
+    L = init()
+    if mask.dtype not in _MASK_CODES:
+        mask = mask.to(torch.float32)
+    mask = mask.contiguous()
+    out = torch.empty(mask.shape, device=mask.device, dtype=F32)
+    check(L.vt_mask_bias(ptr(mask), _MASK_CODES[mask.dtype], mask.numel(), ptr(out), stream_ptr()), "vt_mask_bias")
+    return out
+
+
+def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None):
+    L = init()
+    if ctx is None:
+        ctx = torch.empty((B * S, heads * 64), device=qkv.device, dtype=BF16)
+    lse = torch.empty((B, heads, S, 2), device=qkv.device, dtype=F32)
+    check(L.vt_attention_fwd(ptr(qkv), qkv.stride(0), ptr(bias), B, S, heads, 64, ptr(ctx), ptr(lse), dropout_p, seed, stream_id,
+                             stream_ptr()), "vt_attention_fwd")
+    return ctx, lse
+
+
+def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None):
+    L = init()
+    if dqkv is None:
+        dqkv = torch.empty_like(qkv)
+    ws = torch.empty((B, heads, S), device=qkv.device, dtype=F32)
+    check(L.vt_attention_bwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv),
+                             dropout_p, seed, stream_id, stream_ptr()), "vt_attention_bwd")
+    return dqkv
+
+
+def softmax_ce_fwd(logits, ncols, labels, double_softmax=False):
+    L = init()
+    rows = logits.size(0)
+    dev = logits.device
+    row_loss = torch.empty(rows, device=dev, dtype=F32)
+    argmax = torch.empty(rows, device=dev, dtype=torch.int64)
+    stats = torch.empty((rows, 2), device=dev, dtype=F32)
+    check(L.vt_softmax_ce_fwd(ptr(logits), logits.stride(0), rows, ncols, ptr(labels), int(double_softmax), ptr(row_loss), ptr(argmax),
+                              ptr(stats), stream_ptr()), "vt_softmax_ce_fwd")
+    return row_loss, argmax, stats
+
+
+def softmax_ce_bwd(logits, ncols, labels, stats, scale, scale_dev, double_softmax=False, ld_out=None):
+    L = init()
+    rows = logits.size(0)
+    ld_out = roundup(ncols, 8) if ld_out is None else ld_out
+    d = torch.empty((rows, ld_out), device=logits.device, dtype=BF16)
+    check(L.vt_softmax_ce_bwd(ptr(logits), logits.stride(0), rows, ncols, ptr(labels), int(double_softmax), ptr(stats), scale,
+                              ptr(scale_dev), ptr(d), ld_out, stream_ptr()), "vt_softmax_ce_bwd")
+    return d
+
+
+def action_head_fwd(pooled, W, bias, labels):
+    L = init()
+    B, Hd = pooled.shape
+    A = W.size(0)
+    scores = torch.empty((B, A), device=pooled.device, dtype=F32)
+    row_loss = torch.empty(B, device=pooled.device, dtype=F32)
+    argmax = torch.empty(B, device=pooled.device, dtype=torch.int64)
+    check(L.vt_action_head_fwd(ptr(pooled), ptr(W), ptr(bias), B, Hd, A, ptr(labels), ptr(scores), ptr(row_loss), ptr(argmax), stream_ptr()),
+          "vt_action_head_fwd")
+    return scores, row_loss, argmax
+
+
+def action_head_bwd(pooled, W, labels, scores, n_valid_dev, g_dev, dW, dbias):
+    L = init()
+    B, Hd = pooled.shape
+    dpooled = torch.empty_like(pooled)
+    check(L.vt_action_head_bwd(ptr(pooled), ptr(W), B, Hd, W.size(0), ptr(labels), ptr(scores), ptr(n_valid_dev), ptr(g_dev), ptr(dpooled),
+                               ptr(dW), ptr(dbias), stream_ptr()), "vt_action_head_bwd")
+    return dpooled
+
+
+def pretrain_finalize(mlm, tok, act):
+    """each of mlm/tok/act = (row_loss, argmax, labels); returns fp32 [8]."""
+    L = init()
+    out = torch.empty(8, device=act[0].device, dtype=F32)
+    args = []
+    for rl, am, lab in (mlm, tok, act):
+        args += [ptr(rl), ptr(am), ptr(lab), rl.numel()]
+    check(L.vt_pretrain_finalize(*args, ptr(out), stream_ptr()), "vt_pretrain_finalize")
+    return out
+
+
+def tanh_bwd(dy, y):
+    L = init()
+    dx = torch.empty(y.shape, device=y.device, dtype=BF16)
+    check(L.vt_tanh_bwd(ptr(dy), ptr(y), y.numel(), ptr(dx), stream_ptr()), "vt_tanh_bwd")
+    return dx
+
+
+def to_f32(x):
+    L = init()
+    y = torch.empty(x.shape, device=x.device, dtype=F32)
+    check(L.vt_cast_bf16_f32(ptr(x), x.numel(), ptr(y), stream_ptr()), "vt_cast_bf16_f32")
+    return y
+
+
+def to_bf16(x, addend=None):
+    L = init()
+    y = torch.empty(x.shape, device=x.device, dtype=BF16)
+    check(L.vt_cast_f32_bf16_add(ptr(x), ptr(addend), x.numel(), ptr(y), stream_ptr()), "vt_cast_f32_bf16_add")
+    return y
