@@ -184,13 +184,16 @@ int vt_action_head_bwd(const float* pooled, const float* W, int64_t B, int64_t h
                        const float* scores, const float* n_valid_dev, const float* g_dev, float* dpooled, float* dW, float* dbias,
                        vt_stream stream);
 /* out8 = {loss, mask_loss, next_loss, token_loss, words_accuracy, action_accuracy, token_accuracy, n_valid_actions}
- * (vs/encoder.py:396-441; means over labelled rows, 0/0 -> nan like the reference). */
+ * (vs/encoder.py:396-441; means over labelled rows, 0/0 -> nan like the reference; n_act == 0 means
+ * next_action was None: next_loss = 0 and action_accuracy = 0, vs/encoder.py:393-395,412-418). */
 int vt_pretrain_finalize(const float* mlm_loss, const int64_t* mlm_arg, const int64_t* mlm_lab, int64_t n_mlm, const float* tok_loss,
                          const int64_t* tok_arg, const int64_t* tok_lab, int64_t n_tok, const float* act_loss, const int64_t* act_arg,
                          const int64_t* act_lab, int64_t n_act, float* out8, vt_stream stream);
 
 /* dx (bf16) = dy * (1 - y^2)  -- backward of the pooler's tanh (hf/modeling_bert.py:461-467) */
 int vt_tanh_bwd(const float* dy, const float* y, int64_t n, void* dx, vt_stream stream);
+/* dx (bf16) = dy * gelu'(pre), flat over n elements -- backward of the MLM transform activation (hf/modeling_bert.py:480-485) */
+int vt_gelu_bwd(const void* dy, const void* pre, int64_t n, void* dx, vt_stream stream);
 /* module-boundary casts: bf16 -> fp32 ; bf16(x) (+ addend) */
 int vt_cast_bf16_f32(const void* x, int64_t n, float* y, vt_stream stream);
 int vt_cast_f32_bf16_add(const float* x, const void* addend, int64_t n, void* y, vt_stream stream);

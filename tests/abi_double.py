@@ -1,0 +1,324 @@
+"""TEST DOUBLE for the C ABI -- NOT PRODUCT, never imported by visitron_b200.
+
+The build container has no GPU, so the ``-m "not gpu"`` suite cannot call libvisitron_b200.so's
+compute entry points.  To still check the HOST logic of visitron_b200/modeling.py (operand majors,
+gradient-buffer offsets, residual / remap wiring, bucket order, autograd plumbing) on CPU, this
+module restates each tensor-level wrapper of ``visitron_b200.ops`` / ``lib.gemm`` with plain torch
+on CPU tensors, keeping the storage dtypes (bf16 activations, fp32 accumulators) so that the
+rounding points are the kernels' own.  ``install(monkeypatch)`` swaps them in for one test.
+Dropout is only emulated for p == 0 (the parity configuration); p > 0 is a GPU test.
+"""
+import math
+
+import torch
+import torch.nn.functional as F
+
+BF16, F32 = torch.bfloat16, torch.float32
+H = 768
+CALLS = []
+
+
+def _remap_rows(n, remap, device):
+    m = torch.arange(n, device=device)
+    rin, rout, off = remap
+    if rin and rin > 0:
+        return (m // rin) * rout + off + (m % rin)
+    return m
+
+
+def _no_dropout(p):
+    assert not p or p <= 0, "the CPU test double only covers dropout p == 0"
+
+
+def gemm(A, B, *, a_major=0, b_major=0, out=None, out_dtype=BF16, bias=None, act=0, alpha=1.0, alpha_dev=None,
+         residual=None, aux=None, aux_out=None, dropout_p=0.0, seed=0, dropout_stream=0, accumulate=False, split_k=0,
+         remap=None, M=None, N=None, K=None):
+    CALLS.append("gemm")
+    assert A.dtype == BF16 and B.dtype == BF16
+    _no_dropout(dropout_p)
+    Af = A.float().t() if a_major else A.float()
+    Bf = B.float() if b_major else B.float().t()
+    k = min(Af.size(1), Bf.size(0)) if K is None else K
+    r = alpha * (Af[:, :k] @ Bf[:k])
+    if M is not None:
+        r = r[:M]
+    if N is not None:
+        r = r[:, :N]
+    if alpha_dev is not None:
+        r = r * alpha_dev.float().reshape(())
+    n = r.size(1)
+    if bias is not None:
+        assert bias.dtype == F32
+        r = r + bias[:n]
+    if aux_out is not None:
+        aux_out[:, :n].copy_(r.to(BF16))
+    if act == 1:
+        r = r * 0.5 * (1.0 + torch.erf(r / math.sqrt(2.0)))
+    elif act == 2:
+        r = torch.tanh(r)
+    elif act == 3:
+        x = aux.float()[:, :n]
+        r = r * (0.5 * (1.0 + torch.erf(x / math.sqrt(2.0))) + x * torch.exp(-0.5 * x * x) / math.sqrt(2.0 * math.pi))
+    elif act == 4:
+        y = aux.float()[:, :n]
+        r = r * (1.0 - y * y)
+    rows = _remap_rows(r.size(0), remap or (0, 0, 0), r.device)
+    if residual is not None:
+        r = r + residual[rows].float()[:, :n]
+    if out is None:
+        assert remap is None
+        return r.to(out_dtype)
+    if accumulate:
+        assert out.dtype == F32
+        out[rows] = out[rows] + r
+    else:
+        out[rows] = r.to(out.dtype)
+    return out
+
+
+def _ln(x, g, b, eps):
+    u = x.mean(-1, keepdim=True)
+    s = (x - u).pow(2).mean(-1, keepdim=True)
+    return g * ((x - u) / torch.sqrt(s + eps)) + b
+
+
+def layernorm_fwd(x, gamma, beta, eps, out=None, dropout_p=0.0, seed=0, stream_id=0, remap=(0, 0, 0)):
+    CALLS.append("layernorm_fwd")
+    _no_dropout(dropout_p)
+    y = _ln(x.float(), gamma, beta, eps).to(BF16)
+    if out is None:
+        return y
+    out[_remap_rows(x.size(0), remap, x.device)] = y
+    return out
+
+
+def layernorm_bwd(dy, x, gamma, eps, dgamma, dbeta, dbias=None, want_dx=True, out_dropout_p=0.0, out_stream=0,
+                  in_dropout_p=0.0, in_stream=0, seed=0, remap=(0, 0, 0), dx=None, dxd=None):
+    CALLS.append("layernorm_bwd")
+    _no_dropout(out_dropout_p)
+    _no_dropout(in_dropout_p)
+    rows = _remap_rows(x.size(0), remap, x.device)
+    d = dy[rows].float()
+    xr = x.float().requires_grad_(True)
+    g = gamma.detach().clone().requires_grad_(True)
+    b = torch.zeros_like(g).requires_grad_(True)
+    with torch.enable_grad():
+        _ln(xr, g, b, eps).backward(d)
+    dgamma += g.grad
+    dbeta += b.grad
+    res = xr.grad.to(BF16)
+    if dbias is not None:
+        dbias += xr.grad.sum(0)
+    return res, res
+
+
+def embed_ln_fwd(ids, type_ids, pos_ids, word, pos, typ, gamma, beta, eps, out, rows_per_sample, dropout_p=0.0, seed=0, stream_id=0):
+    CALLS.append("embed_ln_fwd")
+    _no_dropout(dropout_p)
+    b, T = ids.shape
+    p = torch.arange(T)[None].expand(b, T) if pos_ids is None else pos_ids
+    e = word[ids] + pos[p] + (typ[type_ids] if type_ids is not None else typ[0])
+    out.view(b, rows_per_sample, H)[:, :T] = _ln(e, gamma, beta, eps).to(BF16)
+    return out
+
+
+def embed_ln_bwd(dy, ids, type_ids, pos_ids, word, pos, typ, gamma, eps, rows_per_sample, dword, dpos, dtype, dgamma, dbeta,
+                 dropout_p=0.0, seed=0, stream_id=0):
+    CALLS.append("embed_ln_bwd")
+    _no_dropout(dropout_p)
+    b, T = ids.shape
+    p = torch.arange(T)[None].expand(b, T) if pos_ids is None else pos_ids
+    tt = torch.zeros_like(ids) if type_ids is None else type_ids
+    ws = [t.detach().clone().requires_grad_(True) for t in (word, pos, typ, gamma)]
+    beta = torch.zeros_like(gamma).requires_grad_(True)
+    with torch.enable_grad():
+        y = _ln(ws[0][ids] + ws[1][p] + ws[2][tt], ws[3], beta, eps)
+        y.backward(dy.view(b, rows_per_sample, H)[:, :T].float())
+    dword += ws[0].grad
+    dpos += ws[1].grad
+    dtype += ws[2].grad
+    dgamma += ws[3].grad
+    dbeta += beta.grad
+
+
+def colsum(x, out, ncols=None, accumulate=True):
+    CALLS.append("colsum")
+    n = x.size(1) if ncols is None else ncols
+    s = x.float()[:, :n].sum(0)
+    if accumulate:
+        out[:n] += s
+    else:
+        out[:n] = s
+    return out
+
+
+def cast_weight(src, dst=None, dst_t=None):
+    CALLS.append("cast_weight")
+    if dst is not None:
+        dst[:, : src.size(1)] = src.to(BF16)
+    if dst_t is not None:
+        dst_t[:, : src.size(0)] = src.t().to(BF16)
+
+
+def pad_cast_concat(a, b, out):
+    CALLS.append("pad_cast_concat")
+    out.zero_()
+    out[:, : a.size(1)] = a.to(BF16)
+    if b is not None:
+        out[:, a.size(1): a.size(1) + b.size(1)] = b.to(BF16)
+    return out
+
+
+def dropout_rows(x, rows, out, dropout_p, seed, stream_id, remap=(0, 0, 0)):
+    CALLS.append("dropout_rows")
+    _no_dropout(dropout_p)
+    out[:rows] = x[_remap_rows(rows, remap, x.device)]
+    return out
+
+
+def gather_rows(src, idx, out=None):
+    CALLS.append("gather_rows")
+    r = src[idx]
+    if out is None:
+        return r.contiguous()
+    out.copy_(r)
+    return out
+
+
+def scatter_add_rows(src, idx, dst):
+    CALLS.append("scatter_add_rows")
+    dst[idx] = (dst[idx].float() + src.float()).to(BF16)
+
+
+def mask_bias(mask):
+    CALLS.append("mask_bias")
+    return (1.0 - mask.to(F32)) * -10000.0
+
+
+def _attn(qkv, bias, B, S, heads):
+    Hh = heads * 64
+    q, k, v = [t.view(B, S, heads, 64).permute(0, 2, 1, 3) for t in qkv.view(B * S, 3, Hh).unbind(1)]
+    s = q @ k.transpose(-1, -2) / 8.0 + bias[:, None, None, :]
+    p = torch.softmax(s, -1)
+    return (p @ v).permute(0, 2, 1, 3).reshape(B * S, Hh)
+
+
+def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None):
+    CALLS.append("attention_fwd")
+    _no_dropout(dropout_p)
+    out = _attn(qkv.float(), bias, B, S, heads).to(BF16)
+    return out, torch.zeros((B, heads, S, 2))
+
+
+def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None):
+    CALLS.append("attention_bwd")
+    _no_dropout(dropout_p)
+    q = qkv.float().requires_grad_(True)
+    with torch.enable_grad():
+        _attn(q, bias, B, S, heads).backward(dctx.float())
+    return q.grad.to(BF16)
+
+
+def softmax_ce_fwd(logits, ncols, labels, double_softmax=False):
+    CALLS.append("softmax_ce_fwd")
+    x = logits[:, :ncols].float()
+    inp = torch.softmax(x, -1) if double_softmax else x
+    loss = F.cross_entropy(inp, labels, reduction="none") if x.size(0) else x.new_zeros(0)
+    return loss, x.argmax(1) if x.size(0) else labels.new_zeros(0), torch.zeros((x.size(0), 2))
+
+
+def softmax_ce_bwd(logits, ncols, labels, stats, scale, scale_dev, double_softmax=False, ld_out=None):
+    CALLS.append("softmax_ce_bwd")
+    x = logits[:, :ncols].float().detach().clone().requires_grad_(True)
+    with torch.enable_grad():
+        inp = torch.softmax(x, -1) if double_softmax else x
+        (F.cross_entropy(inp, labels, reduction="sum") * scale * scale_dev.reshape(())).backward()
+    ld_out = (ncols + 7) // 8 * 8 if ld_out is None else ld_out
+    d = torch.zeros((x.size(0), ld_out), dtype=BF16)
+    d[:, :ncols] = x.grad.to(BF16)
+    return d
+
+
+def action_head_fwd(pooled, W, bias, labels):
+    CALLS.append("action_head_fwd")
+    sc = torch.log_softmax(F.linear(pooled, W, bias), -1)
+    if labels is None:
+        loss = sc.new_zeros(sc.size(0))
+    else:
+        safe = labels.clamp(min=0)
+        loss = F.cross_entropy(sc, safe, reduction="none") * (labels >= 0)
+    return sc, loss, sc.argmax(1)
+
+
+def action_head_bwd(pooled, W, labels, scores, n_valid_dev, g_dev, dW, dbias):
+    CALLS.append("action_head_bwd")
+    p = pooled.detach().clone().requires_grad_(True)
+    w = W.detach().clone().requires_grad_(True)
+    b = torch.zeros(W.size(0)).requires_grad_(True)
+    with torch.enable_grad():
+        sc = torch.log_softmax(F.linear(p, w, b), -1)
+        l = F.cross_entropy(sc, labels, ignore_index=-1, reduction="sum") / n_valid_dev.reshape(()) * g_dev.reshape(())
+        l.backward()
+    dW += w.grad
+    dbias += b.grad
+    return p.grad
+
+
+def pretrain_finalize(mlm, tok, act):
+    CALLS.append("pretrain_finalize")
+    out = torch.zeros(8)
+    (ml, ma, mlab), (tl, ta, tlab), (al, aa, alab) = mlm, tok, act
+    out[1] = ml.sum() / ml.numel() if ml.numel() else float("nan")
+    out[3] = tl.sum() / tl.numel() if tl.numel() else float("nan")
+    out[4] = (ma == mlab).float().sum() / max(ml.numel(), 1) if ml.numel() else float("nan")
+    out[6] = (ta == tlab).float().sum() / max(tl.numel(), 1) if tl.numel() else float("nan")
+    if al.numel():
+        valid = (alab >= 0).float()
+        out[7] = valid.sum()
+        out[2] = (al * valid).sum() / valid.sum()
+        out[5] = (aa == alab).float().sum() / al.numel()
+    out[0] = out[1] + out[2] + out[3]
+    return out
+
+
+def tanh_bwd(dy, y):
+    CALLS.append("tanh_bwd")
+    return (dy * (1.0 - y * y)).to(BF16)
+
+
+def gelu_bwd(dy, pre):
+    CALLS.append("gelu_bwd")
+    x = pre.float()
+    g = 0.5 * (1.0 + torch.erf(x / math.sqrt(2.0))) + x * torch.exp(-0.5 * x * x) / math.sqrt(2.0 * math.pi)
+    return (dy.float() * g).to(BF16)
+
+
+def to_f32(x):
+    CALLS.append("to_f32")
+    return x.float()
+
+
+def to_bf16(x, addend=None, out=None):
+    CALLS.append("to_bf16")
+    y = x.to(BF16) if addend is None else (x + addend.float()).to(BF16)
+    if out is None:
+        return y
+    out.copy_(y)
+    return out
+
+
+_OPS = ["layernorm_fwd", "layernorm_bwd", "embed_ln_fwd", "embed_ln_bwd", "colsum", "cast_weight", "pad_cast_concat",
+        "dropout_rows", "gather_rows", "scatter_add_rows", "mask_bias", "attention_fwd", "attention_bwd", "softmax_ce_fwd",
+        "softmax_ce_bwd", "action_head_fwd", "action_head_bwd", "pretrain_finalize", "tanh_bwd", "gelu_bwd", "to_f32", "to_bf16"]
+
+
+def install(monkeypatch):
+    """Swap the C-ABI wrappers for the CPU restatements (one test's lifetime)."""
+    from visitron_b200 import lib, ops
+    g = globals()
+    for name in _OPS:
+        assert hasattr(ops, name), name
+        monkeypatch.setattr(ops, name, g[name])
+    monkeypatch.setattr(lib, "gemm", gemm)
+    monkeypatch.setattr(lib, "require_device", lambda t: None)
+    del CALLS[:]

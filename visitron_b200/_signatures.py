@@ -31,6 +31,7 @@ SIGNATURES = {
     "vt_action_head_bwd": (I, [P, P, I64, I64, I64, P, P, P, P, P, P, P, P]),
     "vt_pretrain_finalize": (I, [P, P, P, I64, P, P, P, I64, P, P, P, I64, P, P]),
     "vt_tanh_bwd": (I, [P, P, I64, P, P]),
+    "vt_gelu_bwd": (I, [P, P, I64, P, P]),
     "vt_cast_bf16_f32": (I, [P, I64, P, P]),
     "vt_cast_f32_bf16_add": (I, [P, P, I64, P, P]),
 }

@@ -233,13 +233,15 @@ pretrain_finalize_kernel(const float* __restrict__ mlm_loss, const long long* __
   if (threadIdx.x == 0) {
     const float mask_loss = mlm_sum / (float)n_mlm;     // 0/0 -> nan, as CrossEntropyLoss over an all-ignored batch
     const float token_loss = tok_sum / (float)n_tok;
-    const float next_loss = act_sum / act_valid;
+    // n_act == 0: next_action was None -> next_loss = 0, action_accuracy = 0 (vs/encoder.py:393-395,412-418);
+    // labels given but all ignored -> 0/0 = nan like CrossEntropyLoss
+    const float next_loss = n_act > 0 ? act_sum / act_valid : 0.f;
     out[0] = mask_loss + next_loss + token_loss;
     out[1] = mask_loss;
     out[2] = next_loss;
     out[3] = token_loss;
     out[4] = mlm_ok / (float)n_mlm;
-    out[5] = act_ok / (float)n_act;
+    out[5] = n_act > 0 ? act_ok / (float)n_act : 0.f;
     out[6] = tok_ok / (float)n_tok;
     out[7] = act_valid;
   }
@@ -248,6 +250,18 @@ pretrain_finalize_kernel(const float* __restrict__ mlm_loss, const long long* __
 __global__ void tanh_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, long long n, bf16* __restrict__ dx) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dx[i] = __float2bfloat16(dy[i] * (1.0f - y[i] * y[i]));
+}
+
+// dx = dy * gelu'(pre)   (backward of the MLM transform's activation, hf/modeling_bert.py:480-485)
+__global__ void gelu_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ pre, long long n8, bf16* __restrict__ dx) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float d[8], x[8];
+    unpack8(__ldg(reinterpret_cast<const uint4*>(dy) + i), d);
+    unpack8(__ldg(reinterpret_cast<const uint4*>(pre) + i), x);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) d[j] *= gelu_grad(x[j]);
+    reinterpret_cast<uint4*>(dx)[i] = pack8(d);
+  }
 }
 
 __global__ void cast_bf16_f32_kernel(const bf16* __restrict__ x, long long n8, float* __restrict__ y) {
@@ -339,6 +353,16 @@ extern "C" int vt_pretrain_finalize(const float* mlm_loss, const int64_t* mlm_ar
 extern "C" int vt_tanh_bwd(const float* dy, const float* y, int64_t n, void* dx, vt_stream stream) {
   if (n == 0) return VT_OK;
   tanh_bwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(dy, y, n, (bf16*)dx);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_gelu_bwd(const void* dy, const void* pre, int64_t n, void* dx, vt_stream stream) {
+  VT_REQUIRE(n % 8 == 0 && ((uintptr_t)dy & 15) == 0 && ((uintptr_t)pre & 15) == 0 && ((uintptr_t)dx & 15) == 0, "vt_gelu_bwd: n %% 8 == 0 and 16-byte alignment required");
+  if (n == 0) return VT_OK;
+  long long n8 = n / 8, g = (n8 + 255) / 256, cap = (long long)num_sms() * 16;
+  gelu_bwd_kernel<<<(unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream>>>((const bf16*)dy, (const bf16*)pre, n8, (bf16*)dx);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;

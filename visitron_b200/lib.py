@@ -72,6 +72,13 @@ def init(device: Optional[int] = None) -> C.CDLL:
     return lib
 
 
+def require_device(t: torch.Tensor) -> None:
+    """Product entry points call this first: CPU tensors are refused, never emulated."""
+    if not t.is_cuda:
+        raise VtError("visitron_b200 runs on a CUDA sm_100 device only; got a %s tensor (there is no CPU fallback)" % t.device)
+    init(t.device.index)
+
+
 def stream_ptr() -> int:
     return torch.cuda.current_stream().cuda_stream
 

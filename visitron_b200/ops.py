@@ -215,8 +215,15 @@ def to_f32(x):
     return y
 
 
-def to_bf16(x, addend=None):
+def gelu_bwd(dy, pre):
     L = init()
-    y = torch.empty(x.shape, device=x.device, dtype=BF16)
+    dx = torch.empty_like(pre)
+    check(L.vt_gelu_bwd(ptr(dy), ptr(pre), pre.numel(), ptr(dx), stream_ptr()), "vt_gelu_bwd")
+    return dx
+
+
+def to_bf16(x, addend=None, out=None):
+    L = init()
+    y = torch.empty(x.shape, device=x.device, dtype=BF16) if out is None else out
     check(L.vt_cast_f32_bf16_add(ptr(x), ptr(addend), x.numel(), ptr(y), stream_ptr()), "vt_cast_f32_bf16_add")
     return y

@@ -1,0 +1,102 @@
+"""Data-parallel gradient exchange: bucketed all-reduce (average) overlapped with backward.
+
+Replaces the reference's ``DistributedDataParallel(model, find_unused_parameters=True)`` wrap
+(vs/pretrain.py:96-102, vs/train.py:98-110).  The batch is sharded over one process per GPU; the
+only exchange step of an iteration is the gradient average.  Gradients are produced directly inside
+contiguous slices of the flat gradient buffer (visitron_b200/flat.py), one slice per encoder layer
+(~28 MB fp32, DDP's own bucket size is 25 MB), in reverse execution order: heads, pooler + layer 11,
+... layer 0, image projection + embeddings.  As soon as the backward kernels of a slice have been
+enqueued, its all-reduce is enqueued on NCCL's stream (over NVLink 5 / NVSwitch), so it runs
+under the next layer's backward GEMMs; the autograd node returns only after the current stream
+has been made to wait for all of them (a stream-level wait, the host does not block).
+
+Usage (reference loop, unchanged otherwise):
+
+    model = PreTrainOscar.from_pretrained(...).to(device)
+    visitron_b200.parallel.distribute(model)          # instead of DDP(model, ...)
+
+Like DDP the reducer AVERAGES (the loops divide the loss by world size themselves as
+well; that quirk is theirs and is preserved by not compensating for it here).
+Parameters a call does not touch (fine-tuning leaves img_embedding / location_embeds / pooler
+unused) are skipped consistently on every rank: which buckets exist depends only on the call
+signature, never on data.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+
+class GradReducer:
+    def __init__(self, process_group=None, overlap: bool = True):
+        if not dist.is_available() or not dist.is_initialized():
+            raise RuntimeError("GradReducer needs an initialised torch.distributed process group")
+        self.group = process_group
+        self.world_size = dist.get_world_size(process_group)
+        self.backend = dist.get_backend(process_group)
+        self.overlap = overlap
+        self._works: List = []
+        self._pending: List[torch.Tensor] = []
+        self.bytes_reduced = 0
+        self.calls = 0
+
+    def reduce(self, bucket: torch.Tensor) -> None:
+        """Enqueue the average of ``bucket`` (a contiguous slice of the flat gradient buffer)."""
+        if self.world_size == 1 or bucket.numel() == 0:
+            return
+        self.calls += 1
+        self.bytes_reduced += bucket.numel() * bucket.element_size()
+        if self.backend == "nccl":
+            w = dist.all_reduce(bucket, op=dist.ReduceOp.AVG, group=self.group, async_op=True)
+        else:  # gloo (CPU tests): no AVG
+            w = dist.all_reduce(bucket, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            self._pending.append(bucket)
+        self._works.append(w)
+        if not self.overlap:
+            self.finish()
+
+    def finish(self) -> None:
+        """Make the current stream wait for every enqueued all-reduce (host does not block on NCCL)."""
+        for w in self._works:
+            w.wait()
+        self._works = []
+        for b in self._pending:
+            b.div_(self.world_size)
+        self._pending = []
+
+
+def distribute(model, process_group=None, overlap: bool = True):
+    """Attach a GradReducer to a visitron_b200 model (and its ``.bert`` encoder): the drop-in
+    for ``DistributedDataParallel(model, ...)``; returns the model itself (no ``.module`` wrapper,
+    ``hasattr(model, 'module')`` checks in the reference's save code, vs/pretrain.py:258-260, stay false)."""
+    reducer = GradReducer(process_group, overlap=overlap)
+    n = 0
+    for m in model.modules():
+        if hasattr(m, "_vt_set_reducer"):
+            m._vt_set_reducer(reducer)
+            n += 1
+    if n == 0:
+        raise TypeError("distribute() expects a visitron_b200 model (BertImgModelwithLocationEmbeds / PreTrainOscar / OscarEncoder)")
+    broadcast_parameters(model, process_group)
+    return model
+
+
+def broadcast_parameters(model, process_group=None, src: int = 0) -> None:
+    """Rank ``src``'s weights everywhere (what DDP's constructor does)."""
+    with torch.no_grad():
+        for p in model.parameters():
+            dist.broadcast(p.data, src=src, group=process_group)
+        for b in model.buffers():
+            dist.broadcast(b.data, src=src, group=process_group)
+
+
+def average_scalars(*values: torch.Tensor, process_group=None) -> List[torch.Tensor]:
+    """The loop's 7 scalar all-reduces (vs/pretrain.py:169-189) as ONE 7-float all-reduce."""
+    if not dist.is_initialized() or dist.get_world_size(process_group) == 1:
+        return list(values)
+    buf = torch.stack([v.detach().float().reshape(()) for v in values])
+    dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=process_group)
+    buf /= dist.get_world_size(process_group)
+    return list(buf.unbind(0))
