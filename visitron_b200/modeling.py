@@ -299,16 +299,17 @@ class BertImgModelwithLocationEmbeds(BertPreTrainedModel):
         return self._vt_store.ensure()
 
     def _img_operands(self, st: FlatStore):
-        """[W_img | W_loc | 0] as one bf16 [768, Kp] operand and b_img + b_loc: img_embedding(x) +
-        location_embeds(l) (vs/encoder.py:277-279) is ONE contraction over the concatenated input."""
+        """[W_loc | W_img | 0] as one bf16 [768, Kp] operand and b_img + b_loc: img_embedding(x) +
+        location_embeds(l) (vs/encoder.py:277-279) is ONE contraction over the concatenated input
+        (the 128 location columns come first so that both column blocks start 16-byte aligned)."""
         wi, wl = self.img_embedding.weight, self.location_embeds.weight
         bi, bl = self.img_embedding.bias, self.location_embeds.bias
         vers = (wi._version, wl._version, bi._version, bl._version, st.flat.data_ptr())
         if self._vt_img_cache is None or self._vt_img_cache[0] != vers:
             kp = ops.roundup(self.img_dim + LOC_DIM, 8)
             w = torch.zeros((H, kp), dtype=BF16, device=st.flat.device)
-            ops.cast_weight(st.w("img_embedding.weight"), w[:, : self.img_dim])
-            ops.cast_weight(st.w("location_embeds.weight"), w[:, self.img_dim: self.img_dim + LOC_DIM])
+            ops.cast_weight(st.w("location_embeds.weight"), w[:, :LOC_DIM])
+            ops.cast_weight(st.w("img_embedding.weight"), w[:, LOC_DIM: LOC_DIM + self.img_dim])
             b = (bi.detach() + bl.detach()).contiguous()
             self._vt_img_cache = (vers, w, b, kp)
         return self._vt_img_cache[1:]
@@ -409,7 +410,7 @@ def _encoder_forward(step: _Step, st: FlatStore, img_feats, img_loc):
     if step.has_img:
         wimg, bimg, kp = model._img_operands(st)
         cat = torch.empty((B * R, kp), dtype=BF16, device=dev)
-        ops.pad_cast_concat(img_feats.view(B * R, -1), img_loc.view(B * R, -1), cat)
+        ops.pad_cast_concat(img_loc.view(B * R, -1), img_feats.view(B * R, -1), cat)
         if model.use_img_layernorm:
             pre = lib.gemm(cat, wimg, bias=bimg)
             ops.layernorm_fwd(pre, st.w("LayerNorm.weight"), st.w("LayerNorm.bias"), float(cfg.img_layer_norm_eps), out=x,
@@ -504,8 +505,8 @@ def _encoder_backward(step: _Step, st: FlatStore, d, dpooled):
             ops.colsum(dimg, st.g("img_embedding.bias"))
             ops.colsum(dimg, st.g("location_embeds.bias"))
         D = model.img_dim
-        lib.gemm(dimg, cat[:, :D], a_major=1, b_major=1, out=st.g("img_embedding.weight"), accumulate=True)
-        lib.gemm(dimg, cat[:, D: D + LOC_DIM], a_major=1, b_major=1, out=st.g("location_embeds.weight"), accumulate=True)
+        lib.gemm(dimg, cat[:, LOC_DIM: LOC_DIM + D], a_major=1, b_major=1, out=st.g("img_embedding.weight"), accumulate=True)
+        lib.gemm(dimg, cat[:, :LOC_DIM], a_major=1, b_major=1, out=st.g("location_embeds.weight"), accumulate=True)
     ops.embed_ln_bwd(d, step.ids, step.tt, step.pos, st.w("embeddings.word_embeddings.weight"),
                      st.w("embeddings.position_embeddings.weight"), st.w("embeddings.token_type_embeddings.weight"),
                      st.w("embeddings.LayerNorm.weight"), eps, S, st.g("embeddings.word_embeddings.weight"),
