@@ -158,6 +158,8 @@ int vt_scatter_add_rows(const void* src, int64_t lds, const int64_t* idx, int64_
 /* bias = (1 - mask) * -10000 in fp32 for any mask value (vs/encoder.py:226-241).
  * mask_dtype: 0 int64, 1 uint8/bool, 2 int32, 3 fp32. */
 int vt_mask_bias(const void* mask, int mask_dtype, int64_t n, float* bias, vt_stream stream);
+/* Debug hook for tests: 0 = auto (tcgen05 kernels for S <= 2048), 1 = mma.sync kernels, 2 = tcgen05 kernels. */
+void vt_debug_attention_impl(int impl);
 int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, int64_t B, int64_t S, int64_t heads, int64_t head_dim,
                      void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream);
 int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, const void* ctx, const void* dctx, const float* lse,

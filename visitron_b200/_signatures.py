@@ -22,6 +22,7 @@ SIGNATURES = {
     "vt_dropout_rows": (I, [P, I64, I64, I64, P, I64, F, U64, U32, I64, I64, I64, P]),
     "vt_gather_rows": (I, [P, I64, P, I64, I64, P, I64, P]),
     "vt_scatter_add_rows": (I, [P, I64, P, I64, I64, P, I64, P]),
+    "vt_debug_attention_impl": (None, [I]),
     "vt_mask_bias": (I, [P, I, I64, P, P]),
     "vt_attention_fwd": (I, [P, I64, P, I64, I64, I64, I64, P, P, F, U64, U32, P]),
     "vt_attention_bwd": (I, [P, I64, P, P, P, P, P, I64, I64, I64, I64, P, F, U64, U32, P]),

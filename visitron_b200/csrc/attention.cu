@@ -511,9 +511,20 @@ extern "C" int vt_mask_bias(const void* mask, int mask_dtype, int64_t n, float* 
   return VT_OK;
 }
 
-extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, int64_t B, int64_t S, int64_t heads, int64_t head_dim,
-                                void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream) {
-  int rc = check_attn("vt_attention_fwd", qkv, ld, B, S, heads, head_dim);
+namespace vt {
+
+int attention_bwd_prep(const void* dctx, const void* ctx, float* dsum, int64_t B, int64_t S, int64_t heads, cudaStream_t st) {
+  const long long rows = B * S;
+  long long pg = (rows + 7) / 8, cap = (long long)num_sms() * 8;
+  attn_bwd_prep_kernel<<<(int)(pg < cap ? pg : cap), 256, 0, st>>>((const bf16*)dctx, (const bf16*)ctx, dsum, (int)B, (int)S, (int)heads, (int)(heads * HD));
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+int attention_fwd_legacy(const void* qkv, int64_t ld, const float* bias, int64_t B, int64_t S, int64_t heads, void* ctx, float* lse,
+                         float dropout_p, uint64_t seed, uint32_t dropout_stream, cudaStream_t stream) {
+  int rc = check_attn("vt_attention_fwd", qkv, ld, B, S, heads, HD);
   if (rc) return rc;
   AttnParams p = {};
   p.qkv = (const bf16*)qkv; p.ld = ld; p.B = (int)B; p.S = (int)S; p.heads = (int)heads; p.hidden = (int)(heads * HD);
@@ -529,10 +540,10 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
   return VT_OK;
 }
 
-extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, const void* ctx, const void* dctx, const float* lse,
-                                float* dsum_ws, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv, float dropout_p,
-                                uint64_t seed, uint32_t dropout_stream, vt_stream stream) {
-  int rc = check_attn("vt_attention_bwd", qkv, ld, B, S, heads, head_dim);
+int attention_bwd_legacy(const void* qkv, int64_t ld, const float* bias, const void* ctx, const void* dctx, const float* lse, float* dsum_ws,
+                         int64_t B, int64_t S, int64_t heads, void* dqkv, float dropout_p, uint64_t seed, uint32_t dropout_stream,
+                         cudaStream_t stream) {
+  int rc = check_attn("vt_attention_bwd", qkv, ld, B, S, heads, HD);
   if (rc) return rc;
   VT_REQUIRE(((uintptr_t)dqkv & 15) == 0 && ((uintptr_t)ctx & 15) == 0 && ((uintptr_t)dctx & 15) == 0, "vt_attention_bwd: 16-byte alignment required");
   AttnParams p = {};
@@ -557,3 +568,5 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
   VT_CHECK_LAUNCH();
   return VT_OK;
 }
+
+}  // namespace vt

@@ -89,10 +89,11 @@ __device__ __forceinline__ float gelu_grad(float x) {
 // from (seed, stream id, element index).  One call yields 8 x 16-bit lanes; an element is kept iff
 // its lane >= thresh16, thresh16 = round(p * 65536)  (p is thereby quantised to 1/65536).
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+template <int ROUNDS>
+__device__ __forceinline__ uint4 philox4x32(uint4 ctr, uint2 key) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
 #pragma unroll
-  for (int i = 0; i < 10; ++i) {
+  for (int i = 0; i < ROUNDS; ++i) {
     uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
     uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
     ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
@@ -101,6 +102,8 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
   }
   return ctr;
 }
+
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) { return philox4x32<10>(ctr, key); }
 
 struct DropoutCfg {
   uint32_t thresh16;   // 0 => dropout disabled
@@ -139,7 +142,9 @@ __device__ __forceinline__ void dropout_mult8(const DropoutCfg& d, uint64_t idx,
 // (cols 8n+2t, 8n+2t+1 for n = 4g..4g+3, t = lane%4) needs exactly ONE Philox call per row per
 // 32-column group; it is nevertheless a pure function of (bh, i, j).
 __device__ __forceinline__ uint4 attn_dropout_rand(const DropoutCfg& d, uint32_t bh, uint32_t i, uint32_t jgroup, uint32_t t) {
-  return philox4x32_10(make_uint4(jgroup * 4u + t, i, bh, d.stream), make_uint2(d.seed_lo, d.seed_hi));
+  // 7 rounds: the fewest for which Philox4x32 is Crush-resistant (Salmon et al. 2011); the generator is a large share
+  // of the attention kernels' issue slots (one 16-bit lane per probability)
+  return philox4x32<7>(make_uint4(jgroup * 4u + t, i, bh, d.stream), make_uint2(d.seed_lo, d.seed_hi));
 }
 
 }  // namespace vt

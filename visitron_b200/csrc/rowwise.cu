@@ -16,6 +16,12 @@ constexpr int H = 768;           // hidden size of the supported envelope (bert-
 constexpr int CH = H / (32 * 8); // 8-element chunks per lane = 3
 constexpr int ROW_WARPS = 8;     // warps (rows in flight) per CTA
 
+static int ln_bwd_grid(long long rows) {
+  long long g = (rows + ROW_WARPS - 1) / ROW_WARPS;
+  long long cap = (long long)num_sms();   // exactly one resident CTA per SM: the fewest partial rows to reduce afterwards
+  return (int)(g < cap ? (g < 1 ? 1 : g) : cap);
+}
+
 static int row_grid(long long rows) {
   long long g = (rows + ROW_WARPS - 1) / ROW_WARPS;
   long long cap = (long long)num_sms() * 8;
@@ -141,7 +147,9 @@ ln_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict
 //   partial sums per CTA: [dgamma, dbeta, colsum(dxd)]  (the last one is the bias gradient of the
 //   GEMM that produced h).
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(ROW_WARPS * 32)
+// One CTA (8 warps) per SM at ~230 registers: the next row's x and dy are prefetched (packed, 24 registers)
+// while the current row is processed, which doubles the bytes in flight per warp.
+__global__ void __launch_bounds__(ROW_WARPS * 32, 1)
 ln_bwd_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restrict__ x, long long ldx,
               const float* __restrict__ gamma, float eps, long long rows, bf16* __restrict__ dx, long long lddx,
               bf16* __restrict__ dxd, long long lddxd, float* __restrict__ partials, DropoutCfg drop_in, DropoutCfg drop_out,
@@ -156,10 +164,31 @@ ln_bwd_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restric
     for (int c = 0; c < CH; ++c)
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[a][c][j] = 0.f;
-  for (long long m = (long long)blockIdx.x * ROW_WARPS + warp; m < rows; m += (long long)gridDim.x * ROW_WARPS) {
+  const long long stride = (long long)gridDim.x * ROW_WARPS;
+  long long m = (long long)blockIdx.x * ROW_WARPS + warp;
+  uint4 xq[CH], dq[CH];
+  if (m < rows) {
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+      xq[c] = __ldg(reinterpret_cast<const uint4*>(x + m * ldx + chunk_col(lane, c)));
+      dq[c] = __ldg(reinterpret_cast<const uint4*>(dy + remap_row(m, rin, rout, roff) * lddy + chunk_col(lane, c)));
+    }
+  }
+  for (; m < rows; m += stride) {
     float v[CH][8], d[CH][8];
-    load_row_bf16(x + m * ldx, lane, v);
-    load_row_bf16(dy + remap_row(m, rin, rout, roff) * lddy, lane, d);
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+      unpack8(xq[c], v[c]);
+      unpack8(dq[c], d[c]);
+    }
+    const long long mn = m + stride;
+    if (mn < rows) {
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        xq[c] = __ldg(reinterpret_cast<const uint4*>(x + mn * ldx + chunk_col(lane, c)));
+        dq[c] = __ldg(reinterpret_cast<const uint4*>(dy + remap_row(mn, rin, rout, roff) * lddy + chunk_col(lane, c)));
+      }
+    }
     apply_dropout_row(drop_in, m, lane, d);
     float mean, rstd;
     row_stats(v, eps, mean, rstd);
@@ -309,20 +338,49 @@ embed_ln_bwd_kernel(const bf16* __restrict__ dy, const long long* __restrict__ i
 // ---------------------------------------------------------------------------------------------
 __global__ void reduce_partials_kernel(const float* __restrict__ part, long long nrows, long long row_stride, long long ncols,
                                        float* __restrict__ out, int accumulate) {
+  // grid (column blocks of 32, row splits): with more than one row split the splits meet in `out` through fp32 atomics
+  // (accumulate mode only; `out` then already holds a value to add to)
   __shared__ float red[8][33];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const long long col = (long long)blockIdx.x * 32 + tx;
   float s = 0.f;
   if (col < ncols)
-    for (long long r = ty; r < nrows; r += 8) s += part[r * row_stride + col];
+    for (long long r = (long long)blockIdx.y * 8 + ty; r < nrows; r += 8ll * gridDim.y) s += part[r * row_stride + col];
   red[ty][tx] = s;
   __syncthreads();
   if (ty == 0 && col < ncols) {
     float t = 0.f;
 #pragma unroll
     for (int i = 0; i < 8; ++i) t += red[i][tx];
-    out[col] = accumulate ? out[col] + t : t;
+    if (gridDim.y > 1) atomicAdd(out + col, t);
+    else out[col] = accumulate ? out[col] + t : t;
   }
+}
+
+// the NACC column sums a LayerNorm / embedding backward leaves in part[cta][a][H]: one launch, blockIdx.z = a
+struct ReduceOuts { float* p[4]; };
+__global__ void reduce_partials_multi_kernel(const float* __restrict__ part, long long nrows, int nacc, ReduceOuts outs) {
+  __shared__ float red[8][33];
+  float* out = outs.p[blockIdx.z];
+  if (!out) return;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const long long col = (long long)blockIdx.x * 32 + tx;
+  float s = 0.f;
+  for (long long r = (long long)blockIdx.y * 8 + ty; r < nrows; r += 8ll * gridDim.y) s += part[(r * nacc + blockIdx.z) * H + col];
+  red[ty][tx] = s;
+  __syncthreads();
+  if (ty == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][tx];
+    atomicAdd(out + col, t);
+  }
+}
+
+static inline dim3 reduce_grid(long long ncols, long long nrows, int accumulate) {
+  int splits = 1;
+  if (accumulate && nrows > 64) splits = (int)((nrows + 63) / 64 < 16 ? (nrows + 63) / 64 : 16);
+  return dim3((unsigned)((ncols + 31) / 32), (unsigned)splits);
 }
 
 // column sums of a bf16 matrix [rows, ncols] (ncols % 8 == 0): part[blockIdx.y][col]
@@ -451,7 +509,7 @@ extern "C" int vt_layernorm_bwd(const void* dy, int64_t lddy, const void* x, int
   VT_REQUIRE(aligned16(x) && aligned16(dy) && aligned16(dx) && aligned16(dx_dropped) && aligned16(gamma) && aligned16(partials), "vt_layernorm_bwd: 16-byte alignment required");
   VT_REQUIRE(partials, "vt_layernorm_bwd: partials workspace (vt_row_partials_rows(rows) x 3 x 768 fp32) required");
   if (rows == 0) return VT_OK;
-  const int grid = row_grid(rows);
+  const int grid = ln_bwd_grid(rows);
   cudaStream_t st = (cudaStream_t)stream;
   ln_bwd_kernel<<<grid, ROW_WARPS * 32, 0, st>>>((const bf16*)dy, lddy, (const bf16*)x, ldx, gamma, eps, rows, (bf16*)dx, lddx,
                                                  (bf16*)dx_dropped, lddxd, partials, make_dropout(in_dropout_p, seed, in_dropout_stream),
@@ -460,12 +518,10 @@ extern "C" int vt_layernorm_bwd(const void* dy, int64_t lddy, const void* x, int
   count_launch(1);
   VT_CHECK_LAUNCH();
   // second stage: accumulate into the fp32 gradient buffers
-  float* outs[3] = {dgamma, dbeta, dbias};
-  for (int a = 0; a < 3; ++a) {
-    if (!outs[a]) continue;
-    reduce_partials_kernel<<<(H + 31) / 32, dim3(32, 8), 0, st>>>(partials + a * H, grid, 3 * H, H, outs[a], 1);
-    count_launch(1);
-  }
+  ReduceOuts outs = {{dgamma, dbeta, dbias, nullptr}};
+  const int splits = grid > 64 ? (grid + 63) / 64 < 16 ? (grid + 63) / 64 : 16 : 1;
+  reduce_partials_multi_kernel<<<dim3(H / 32, splits, 3), dim3(32, 8), 0, st>>>(partials, grid, 3, outs);
+  count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
 }
@@ -501,12 +557,10 @@ extern "C" int vt_embed_ln_bwd(const void* dy, const int64_t* ids, const int64_t
                                                        make_dropout(dropout_p, seed, dropout_stream));
   count_launch(1);
   VT_CHECK_LAUNCH();
-  float* outs[4] = {dgamma, dbeta, dtype, type_vocab > 1 ? dtype + H : nullptr};
-  for (int a = 0; a < 4; ++a) {
-    if (!outs[a]) continue;
-    reduce_partials_kernel<<<(H + 31) / 32, dim3(32, 8), 0, st>>>(partials + a * H, grid, 4 * H, H, outs[a], 1);
-    count_launch(1);
-  }
+  ReduceOuts outs = {{dgamma, dbeta, dtype, type_vocab > 1 ? dtype + H : nullptr}};
+  const int splits = grid > 64 ? (grid + 63) / 64 < 16 ? (grid + 63) / 64 : 16 : 1;
+  reduce_partials_multi_kernel<<<dim3(H / 32, splits, 4), dim3(32, 8), 0, st>>>(partials, grid, 4, outs);
+  count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
 }
@@ -527,7 +581,7 @@ extern "C" int vt_colsum_bf16(const void* x, int64_t ldx, int64_t rows, int64_t 
   const int threads = 128;
   const int gx = (int)((npad / 8 + threads - 1) / threads);
   colsum_partial_kernel<<<dim3(gx, gy), threads, 0, st>>>((const bf16*)x, ldx, rows, npad, partials);
-  reduce_partials_kernel<<<(int)((ncols + 31) / 32), dim3(32, 8), 0, st>>>(partials, gy, npad, ncols, out, accumulate);
+  reduce_partials_kernel<<<reduce_grid(ncols, gy, accumulate), dim3(32, 8), 0, st>>>(partials, gy, npad, ncols, out, accumulate);
   count_launch(2);
   VT_CHECK_LAUNCH();
   return VT_OK;

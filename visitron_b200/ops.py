@@ -127,6 +127,11 @@ def mask_bias(mask: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def set_attention_impl(impl: int):
+    """Debug hook: 0 = auto, 1 = mma.sync kernels, 2 = tcgen05 kernels."""
+    init().vt_debug_attention_impl(int(impl))
+
+
 def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None):
     L = init()
     if ctx is None:
