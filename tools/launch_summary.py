@@ -1,14 +1,19 @@
-"""Aggregate an `ncu --metrics gpu__time_duration.sum --csv` launch list per kernel (run here, no GPU needed)."""
+"""Aggregate an `ncu --metrics gpu__time_duration.sum --csv` launch list per kernel (run here, no GPU needed).
+
+    python tools/launch_summary.py launches.csv [--step N] [title...]
+
+--step N keeps only the N-th (0-based) step, a step being the launches from one `embed_ln_fwd_kernel`
+(the first kernel of the encoder forward) up to the next one.
+"""
 import collections
 import csv
 import re
 import sys
 
 
-def main(path, title=""):
+def main(path, step=None, title=""):
     lines = [l for l in open(path) if not l.startswith("==")]
-    agg = collections.defaultdict(lambda: [0, 0.0])
-    tot = 0.0
+    rows = []
     for row in csv.DictReader(lines):
         if row.get("Metric Name") != "gpu__time_duration.sum":
             continue
@@ -16,6 +21,16 @@ def main(path, title=""):
         v = float(row["Metric Value"].replace(",", ""))
         u = row["Metric Unit"]
         v = v / 1e3 if u == "ns" else v * 1e3 if u == "ms" else v
+        rows.append((name, v))
+    if step is not None:
+        starts = [i for i, (n, _) in enumerate(rows) if "embed_ln_fwd_kernel" in n]
+        # the step's label bookkeeping (nonzero/index kernels) precedes embed_ln_fwd by a few launches: cut at embed_ln_fwd
+        lo = starts[step]
+        hi = starts[step + 1] if step + 1 < len(starts) else len(rows)
+        rows = rows[lo:hi]
+    agg = collections.defaultdict(lambda: [0, 0.0])
+    tot = 0.0
+    for name, v in rows:
         agg[name][0] += 1
         agg[name][1] += v
         tot += v
@@ -27,4 +42,10 @@ def main(path, title=""):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1], " ".join(sys.argv[2:]))
+    args = sys.argv[1:]
+    step = None
+    if "--step" in args:
+        i = args.index("--step")
+        step = int(args[i + 1])
+        del args[i:i + 2]
+    main(args[0], step, " ".join(args[1:]))
