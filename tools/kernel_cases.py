@@ -1,0 +1,136 @@
+"""Per-kernel timing of ONE encoder layer (forward + backward) at the bench shape, through the C ABI.
+
+    python tools/kernel_cases.py [--batch 32] [--seq 767] [--iters 10] [--once] [--json out.json]
+
+Each case is timed with CUDA events on the launching stream (3 warm-ups, `iters` back-to-back launches, inputs far larger
+than L2 are rotated so nothing is served from cache) and reported against its own roofline: TFLOP/s for the tcgen05
+kernels, GB/s of algorithmic bytes for the row kernels.  `--once` launches every case once untimed, then once between cudaProfilerStart/Stop (for `ncu --set full
+--profile-from-start off`).
+"""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+from visitron_b200 import lib, ops
+from visitron_b200.lib import ACT_GELU, ACT_GELU_BWD
+
+H, I, NH = 768, 3072, 12
+BF16, F32 = torch.bfloat16, torch.float32
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--seq", type=int, default=767)
+    ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--once", action="store_true")
+    ap.add_argument("--only", default="")
+    ap.add_argument("--p-hidden", type=float, default=0.3)
+    ap.add_argument("--p-attn", type=float, default=0.1)
+    ap.add_argument("--json", default="")
+    args = ap.parse_args()
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    lib.init()
+    torch.manual_seed(0)
+    B, S = args.batch, args.seq
+    M = B * S
+    ph, pa, seed = args.p_hidden, args.p_attn, 1234
+    NROT = 3  # rotate activations so that consecutive launches do not hit L2
+
+    def rnd(*shape, scale=1.0, dtype=BF16):
+        return (torch.randn(*shape, device=dev) * scale).to(dtype)
+
+    xs = [rnd(M, H) for _ in range(NROT)]
+    zs = [rnd(M, I) for _ in range(NROT)]
+    qkvs = [rnd(M, 3 * H) for _ in range(NROT)]
+    Wqkv, Wo, W1, W2 = rnd(3 * H, H, scale=0.02), rnd(H, H, scale=0.02), rnd(I, H, scale=0.02), rnd(H, I, scale=0.02)
+    bqkv, bo, b1, b2 = (torch.zeros(n, device=dev) for n in (3 * H, H, I, H))
+    gamma, beta = torch.ones(H, device=dev), torch.zeros(H, device=dev)
+    mask = torch.ones(B, S, dtype=torch.int64, device=dev)
+    mask[:, S - 76:] = 0
+    bias = ops.mask_bias(mask)
+    out_h = torch.empty(M, H, dtype=BF16, device=dev)
+    out_h2 = torch.empty(M, H, dtype=BF16, device=dev)
+    out_i = torch.empty(M, I, dtype=BF16, device=dev)
+    out_i2 = torch.empty(M, I, dtype=BF16, device=dev)
+    out_q = torch.empty(M, 3 * H, dtype=BF16, device=dev)
+    gW = torch.zeros(I * H, dtype=F32, device=dev)
+    gvec = torch.zeros(4 * I, dtype=F32, device=dev)
+    ctx0, lse0 = ops.attention_fwd(qkvs[0], bias, B, S, NH, pa, seed, 0)
+    torch.cuda.synchronize()
+
+    gemm_fl = lambda n, k: 2.0 * M * n * k
+    attn_f = 4.0 * B * NH * S * S * 64
+    cases = []
+
+    def case(name, fn, flops=0.0, bytes_=0.0):
+        cases.append((name, fn, flops, bytes_))
+
+    r = lambda L, i: L[i % NROT]
+    case("gemm qkv         [M,768]x[2304,768]  bias", lambda i: lib.gemm(r(xs, i), Wqkv, bias=bqkv, out=out_q), gemm_fl(3 * H, H))
+    case("attn fwd         S=%d d=64 p=%.1f" % (S, pa), lambda i: ops.attention_fwd(r(qkvs, i), bias, B, S, NH, pa, seed, 0, ctx=out_h), attn_f)
+    case("gemm attn-out    [M,768]x[768,768]   bias+dropout+residual",
+         lambda i: lib.gemm(r(xs, i), Wo, bias=bo, dropout_p=ph, seed=seed, dropout_stream=1, residual=r(xs, i + 1), out=out_h), gemm_fl(H, H))
+    case("ln fwd           [M,768]", lambda i: ops.layernorm_fwd(r(xs, i), gamma, beta, 1e-12, out=out_h), 0, 2.0 * M * H * 2)
+    case("gemm ffn-up      [M,768]x[3072,768]  bias+gelu+pre", lambda i: lib.gemm(r(xs, i), W1, bias=b1, act=ACT_GELU, aux_out=out_i2, out=out_i), gemm_fl(I, H))
+    case("gemm ffn-down    [M,3072]x[768,3072] bias+dropout+residual",
+         lambda i: lib.gemm(r(zs, i), W2, bias=b2, dropout_p=ph, seed=seed, dropout_stream=2, residual=r(xs, i), out=out_h), gemm_fl(H, I))
+    case("ln bwd           [M,768] (+dropped copy, dgamma/dbeta/dbias)",
+         lambda i: ops.layernorm_bwd(r(xs, i), r(xs, i + 1), gamma, 1e-12, gvec[:H], gvec[H:2 * H], gvec[2 * H:3 * H], out_dropout_p=ph, out_stream=2,
+                                     seed=seed, dx=out_h, dxd=out_h2), 0, 4.0 * M * H * 2)
+    case("wgrad ffn-down   dW[768,3072] = dY^T Z", lambda i: lib.gemm(r(xs, i), r(zs, i), a_major=1, b_major=1, out=gW.view(H, I), accumulate=True), gemm_fl(I, H))
+    case("dgrad ffn-down   [M,768]x[768,3072]  gelu'", lambda i: lib.gemm(r(xs, i), W2, b_major=1, act=ACT_GELU_BWD, aux=r(zs, i), out=out_i), gemm_fl(I, H))
+    case("colsum           [M,3072]", lambda i: ops.colsum(r(zs, i), gvec[:I]), 0, 1.0 * M * I * 2)
+    case("wgrad ffn-up     dW[3072,768] = dPre^T Y", lambda i: lib.gemm(r(zs, i), r(xs, i), a_major=1, b_major=1, out=gW.view(I, H), accumulate=True), gemm_fl(I, H))
+    case("dgrad ffn-up     [M,3072]x[3072,768] +residual", lambda i: lib.gemm(r(zs, i), W1, b_major=1, residual=r(xs, i), out=out_h), gemm_fl(I, H))
+    case("wgrad attn-out   dW[768,768]", lambda i: lib.gemm(r(xs, i), r(xs, i + 1), a_major=1, b_major=1, out=gW[:H * H].view(H, H), accumulate=True), gemm_fl(H, H))
+    case("dgrad attn-out   [M,768]x[768,768]", lambda i: lib.gemm(r(xs, i), Wo, b_major=1, out=out_h), gemm_fl(H, H))
+    case("attn bwd         (prep + dK/dV + dQ)", lambda i: ops.attention_bwd(qkvs[0], bias, ctx0, r(xs, i), lse0, B, S, NH, pa, seed, 0, dqkv=out_q), 2.5 * attn_f)
+    case("colsum           [M,2304]", lambda i: ops.colsum(r(qkvs, i), gvec[:3 * H]), 0, 1.0 * M * 3 * H * 2)
+    case("wgrad qkv        dW[2304,768]", lambda i: lib.gemm(r(qkvs, i), r(xs, i), a_major=1, b_major=1, out=gW[:3 * H * H].view(3 * H, H), accumulate=True), gemm_fl(3 * H, H))
+    case("dgrad qkv        [M,2304]x[2304,768] +residual", lambda i: lib.gemm(r(qkvs, i), Wqkv, b_major=1, residual=r(xs, i), out=out_h), gemm_fl(3 * H, H))
+
+    rows = []
+    tot = 0.0
+    if args.once:  # for `ncu --profile-from-start off`: one untimed pass, then one profiled launch of every case
+        sel = [c for c in cases if not args.only or args.only in c[0]]
+        for name, fn, fl, by in sel:
+            fn(0)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        for name, fn, fl, by in sel:
+            fn(1)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        return
+    for name, fn, fl, by in cases:
+        if args.only and args.only not in name:
+            continue
+        for i in range(3):
+            fn(i)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.iters):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / args.iters
+        tot += us
+        rate = "%7.0f TFLOP/s" % (fl / us / 1e6) if fl else "%7.0f GB/s   " % (by / us / 1e3)
+        print("%-62s %8.1f us  %s" % (name, us, rate), flush=True)
+        rows.append(dict(name=name.split("  ")[0].strip(), us=round(us, 1), tflops=round(fl / us / 1e6, 1) if fl else None,
+                         gbs=round(by / us / 1e3, 1) if by else None))
+    if not args.once:
+        print("layer total (fwd+bwd) %.1f us  -> x12 = %.2f ms" % (tot, tot * 12 / 1e3))
+    if args.json:
+        json.dump(dict(batch=B, seq=S, rows=rows, layer_total_us=tot), open(args.json, "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()

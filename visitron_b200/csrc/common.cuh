@@ -68,20 +68,28 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
   return q;
 }
 
-// erf to ~1.5e-7 absolute (Abramowitz-Stegun 7.1.26): far below bf16 output rounding, and an order
-// of magnitude fewer issue slots than erff() -- the FFN-up epilogue applies it to every element.
-__device__ __forceinline__ float fast_erf(float x) {
-  float ax = fabsf(x);
-  float t = __frcp_rn(fmaf(0.3275911f, ax, 1.0f));
-  float p = fmaf(fmaf(fmaf(fmaf(1.061405429f, t, -1.453152027f), t, 1.421413741f), t, -0.284496736f), t, 0.254829592f) * t;
-  float r = 1.0f - p * __expf(-ax * ax);
-  return copysignf(r, x);
+// Standard normal CDF, Phi(x) = 0.5 (1 + erf(x / sqrt 2)), to 1e-6 absolute: the lower tail is exp2 of a degree-5
+// polynomial in |x| (weighted least-squares fit of log2 Phi(-a) on a in [0, 6], clamped beyond, where Phi(-6) = 1e-9),
+// the upper side its complement.  One MUFU and seven FMA-pipe instructions -- the FFN-up epilogue applies it to every
+// element of [M, 3072] and has to stay below the tensor-core time of its tile; erff() costs about three times as much.
+__device__ __forceinline__ float normal_cdf(float x) {
+  const float a = fminf(fabsf(x), 6.0f);
+  float q = fmaf(-5.021095858e-04f, a, 7.289528381e-03f);
+  q = fmaf(q, a, -5.234604329e-02f);
+  q = fmaf(q, a, -4.594255686e-01f);
+  q = fmaf(q, a, -1.151043534e+00f);
+  q = fmaf(q, a, -1.000002623e+00f);
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(q));
+  return x >= 0.f ? 1.0f - e : e;
 }
 // gelu(x) = x * 0.5 * (1 + erf(x / sqrt(2)))          (hf/modeling_bert.py:136-142)
-__device__ __forceinline__ float gelu_fwd(float x) { return 0.5f * x * (1.0f + fast_erf(x * 0.70710678118654752f)); }
-// d/dx gelu(x) = 0.5 (1 + erf(x/sqrt2)) + x * exp(-x^2/2) / sqrt(2 pi)
+__device__ __forceinline__ float gelu_fwd(float x) { return x * normal_cdf(x); }
+// d/dx gelu(x) = Phi(x) + x * exp(-x^2/2) / sqrt(2 pi)
 __device__ __forceinline__ float gelu_grad(float x) {
-  return 0.5f * (1.0f + fast_erf(x * 0.70710678118654752f)) + x * 0.3989422804014327f * __expf(-0.5f * x * x);
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-0.72134752044448170f * x * x));
+  return fmaf(x * 0.3989422804014327f, e, normal_cdf(x));
 }
 
 // ---------------------------------------------------------------------------------------------

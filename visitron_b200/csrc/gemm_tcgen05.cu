@@ -49,100 +49,83 @@ struct GemmCfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
-  static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  static constexpr int EPI_BYTES = NUM_EPI_WARPS * 32 * 32 * 4;  // per-warp fp32 [32][32] transpose buffer (XOR-swizzled)
   static constexpr int BAR_BYTES = 256;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + slack for 1024-B alignment
+  static constexpr int BUDGET = 227 * 1024 - 1024 - BAR_BYTES - EPI_BYTES;  // 1024: slack for 1024-B alignment
+  static constexpr int STAGES = BUDGET / STAGE_BYTES > 8 ? 8 : BUDGET / STAGE_BYTES;
+  static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-// One 32-column slice of one output row.
-__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float alpha, int m, int n0, const uint32_t* v) {
+// Epilogue of one 32-row x 32-column slice of the accumulator, in the COALESCED layout: after the in-warp
+// shared-memory transpose lane L owns 8 consecutive columns [8 (L & 3), +8) of row (L >> 2) + 8 i, i = 0..3, so
+// one warp-wide 16-byte access covers 8 rows x 64 contiguous bytes (whole 32-byte sectors) of every bf16
+// operand -- bias, saved pre-activation, residual, output -- instead of 32 rows x 16 bytes.
+__device__ __forceinline__ void epilogue_rows8(const GemmParams& p, int m, int n0, float* x, const float* bias8) {
   if (m >= p.M) return;
-  const int ncols = min(32, p.N - n0);
+  const int ncols = min(8, p.N - n0);
   if (ncols <= 0) return;
   long long orow = m;
   if (p.remap_in > 0) orow = (long long)(m / p.remap_in) * p.remap_out + p.remap_off + (m % p.remap_in);
-  const bool vec = p.vec_ok && ncols == 32;
-  float x[32];
-#pragma unroll
-  for (int j = 0; j < 32; ++j) x[j] = __uint_as_float(v[j]) * alpha;
+  const bool vec = p.vec_ok && ncols == 8;
   if (p.bias) {
-    if (vec) {
-      const float4* b4 = reinterpret_cast<const float4*>(p.bias + n0);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float4 b = __ldg(b4 + j);
-        x[4 * j] += b.x; x[4 * j + 1] += b.y; x[4 * j + 2] += b.z; x[4 * j + 3] += b.w;
-      }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j)
-        if (j < ncols) x[j] += __ldg(p.bias + n0 + j);
-    }
+    for (int j = 0; j < 8; ++j) x[j] += bias8[j];
   }
   if (p.aux_out) {
     bf16* ao = p.aux_out + (long long)m * p.ldaux_out + n0;
     if (vec) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) reinterpret_cast<uint4*>(ao)[j] = pack8(x + 8 * j);
+      *reinterpret_cast<uint4*>(ao) = pack8(x);
     } else {
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
+      for (int j = 0; j < 8; ++j)
         if (j < ncols) ao[j] = __float2bfloat16(x[j]);
     }
   }
   if (p.act == VT_ACT_GELU) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) x[j] = gelu_fwd(x[j]);
+    for (int j = 0; j < 8; ++j) x[j] = gelu_fwd(x[j]);
   } else if (p.act == VT_ACT_TANH) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) x[j] = tanhf(x[j]);
+    for (int j = 0; j < 8; ++j) x[j] = tanhf(x[j]);
   } else if (p.act == VT_ACT_GELU_BWD || p.act == VT_ACT_TANH_BWD) {
     const bf16* ax = p.aux + (long long)m * p.ldaux + n0;
-    float a[32];
+    float a[8];
     if (vec) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) unpack8(__ldg(reinterpret_cast<const uint4*>(ax) + j), a + 8 * j);
+      unpack8(__ldg(reinterpret_cast<const uint4*>(ax)), a);
     } else {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) a[j] = (j < ncols) ? __bfloat162float(ax[j]) : 0.f;
+      for (int j = 0; j < 8; ++j) a[j] = (j < ncols) ? __bfloat162float(ax[j]) : 0.f;
     }
     if (p.act == VT_ACT_GELU_BWD) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) x[j] *= gelu_grad(a[j]);
+      for (int j = 0; j < 8; ++j) x[j] *= gelu_grad(a[j]);
     } else {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) x[j] *= (1.0f - a[j] * a[j]);
+      for (int j = 0; j < 8; ++j) x[j] *= (1.0f - a[j] * a[j]);
     }
   }
   if (p.drop.thresh16) {
     // linear index of the LOGICAL element (m, n); N % 8 == 0 is enforced on the host
-    const uint64_t idx = (uint64_t)m * (uint64_t)p.N + (uint64_t)n0;
+    float mult[8];
+    dropout_mult8(p.drop, (uint64_t)m * (uint64_t)p.N + (uint64_t)n0, mult);
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
-      float mult[8];
-      dropout_mult8(p.drop, idx + 8 * g, mult);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) x[8 * g + j] *= mult[j];
-    }
+    for (int j = 0; j < 8; ++j) x[j] *= mult[j];
   }
   if (p.residual) {
     const bf16* r = p.residual + orow * p.ldr + n0;
     if (vec) {
+      float t[8];
+      unpack8(__ldg(reinterpret_cast<const uint4*>(r)), t);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float t[8];
-        unpack8(__ldg(reinterpret_cast<const uint4*>(r) + j), t);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) x[8 * j + k] += t[k];
-      }
+      for (int j = 0; j < 8; ++j) x[j] += t[j];
     } else {
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
+      for (int j = 0; j < 8; ++j)
         if (j < ncols) x[j] += __bfloat162float(r[j]);
     }
   }
@@ -150,31 +133,30 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, float alpha,
     float* d = reinterpret_cast<float*>(p.D) + orow * p.ldd + n0;
     if (p.accumulate) {
       if (vec) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) red_add_v4(d + 4 * j, x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+        red_add_v4(d, x[0], x[1], x[2], x[3]);
+        red_add_v4(d + 4, x[4], x[5], x[6], x[7]);
       } else {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
+        for (int j = 0; j < 8; ++j)
           if (j < ncols) atomicAdd(d + j, x[j]);
       }
     } else {
       if (vec) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) reinterpret_cast<float4*>(d)[j] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+        reinterpret_cast<float4*>(d)[0] = make_float4(x[0], x[1], x[2], x[3]);
+        reinterpret_cast<float4*>(d)[1] = make_float4(x[4], x[5], x[6], x[7]);
       } else {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
+        for (int j = 0; j < 8; ++j)
           if (j < ncols) d[j] = x[j];
       }
     }
   } else {
     bf16* d = reinterpret_cast<bf16*>(p.D) + orow * p.ldd + n0;
     if (vec) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) reinterpret_cast<uint4*>(d)[j] = pack8(x + 8 * j);
+      *reinterpret_cast<uint4*>(d) = pack8(x);
     } else {
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
+      for (int j = 0; j < 8; ++j)
         if (j < ncols) d[j] = __float2bfloat16(x[j]);
     }
   }
@@ -187,7 +169,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_base = smem_base + STAGES * Cfg::STAGE_BYTES;
+  const uint32_t epi_base = smem_base + STAGES * Cfg::STAGE_BYTES;
+  const uint32_t bar_base = epi_base + Cfg::EPI_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
@@ -295,6 +278,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int half = (warp - 4) >> 2;  // which half of the tile's columns
     constexpr int CHUNKS = BN / 32;
     constexpr int CH_PER_HALF = (CHUNKS + 1) / 2;
+    const int c_begin = half * CH_PER_HALF, c_end = min(CHUNKS, c_begin + CH_PER_HALF);
+    const uint32_t stg = epi_base + (uint32_t)(warp - 4) * 4096u;
+    // transposed ownership (see epilogue_rows8): row r8 + 8 i, 16-byte fp32 chunks 2 c4 and 2 c4 + 1 of the staged row
+    const int r8 = lane >> 2, c4 = lane & 3;
     float alpha = p.alpha;
     if (p.alpha_dev) alpha *= __ldg(p.alpha_dev);
     int acc = 0;
@@ -304,20 +291,50 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int m_blk = mn / p.n_blocks, n_blk = mn % p.n_blocks;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
-      const int m = m_blk * BM + q * 32 + lane;
+      const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+      uint32_t v[32];
+      tmem_ld_32x32(t_addr + (uint32_t)(c_begin * 32), v);
+      tmem_ld_wait();
 #pragma unroll 1
-      for (int i = 0; i < CH_PER_HALF; ++i) {
-        const int c = half * CH_PER_HALF + i;
-        if (c < CHUNKS) {
-          uint32_t v[32];
-          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN + c * 32), v);
-          tmem_ld_wait();
-          epilogue_chunk(p, alpha, m, n_blk * BN + c * 32, v);
+      for (int c = c_begin; c < c_end; ++c) {
+        // row-per-lane (TMEM) layout -> staging: lane = row, 16-byte chunk j at physical chunk j ^ (row & 7)
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          st_shared_v4(stg + (uint32_t)lane * 128u + ((uint32_t)(j ^ (lane & 7)) << 4), v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+        if (c + 1 < c_end) {
+          tmem_ld_32x32(t_addr + (uint32_t)((c + 1) * 32), v);  // in flight while this chunk is post-processed
+        } else {
+          // the accumulator stage is drained: hand it back to the MMA warp before the post-processing
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty_bar(acc));
         }
+        const int n0 = n_blk * BN + c * 32 + 8 * c4;
+        float bias8[8];
+        if (p.bias) {
+          if (p.vec_ok && n0 + 8 <= p.N) {
+            const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + n0)), b1 = __ldg(reinterpret_cast<const float4*>(p.bias + n0) + 1);
+            bias8[0] = b0.x; bias8[1] = b0.y; bias8[2] = b0.z; bias8[3] = b0.w;
+            bias8[4] = b1.x; bias8[5] = b1.y; bias8[6] = b1.z; bias8[7] = b1.w;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) bias8[j] = (n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int row = r8 + 8 * i;
+          const uint32_t ra = stg + (uint32_t)row * 128u;
+          const uint4 lo = ld_shared_v4(ra + ((uint32_t)((2 * c4) ^ (row & 7)) << 4));
+          const uint4 hi = ld_shared_v4(ra + ((uint32_t)((2 * c4 + 1) ^ (row & 7)) << 4));
+          float x[8] = {__uint_as_float(lo.x) * alpha, __uint_as_float(lo.y) * alpha, __uint_as_float(lo.z) * alpha, __uint_as_float(lo.w) * alpha,
+                        __uint_as_float(hi.x) * alpha, __uint_as_float(hi.y) * alpha, __uint_as_float(hi.z) * alpha, __uint_as_float(hi.w) * alpha};
+          epilogue_rows8(p, m_blk * BM + q * 32 + row, n0, x, bias8);
+        }
+        if (c + 1 < c_end) tmem_ld_wait();
+        __syncwarp();  // staging buffer is rewritten by the next chunk
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar(acc));
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1u;
     }
@@ -456,11 +473,17 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   if (splits <= 0) {
     splits = 1;
     if (ep->accumulate) {
-      long long tiles = (long long)p.m_blocks * p.n_blocks;
-      splits = (int)(sms / tiles);
-      int max_splits = p.k_blocks / 4;
-      if (splits > max_splits) splits = max_splits;
-      if (splits < 1) splits = 1;
+      // the split count whose work items fill whole waves of the SMs best (96 tiles: 3 splits = 288 items = 1.95 waves,
+      // where floor(148 / 96) = 1 would leave a third of the SMs idle); ties go to fewer splits (less red.add traffic)
+      const long long tiles = (long long)p.m_blocks * p.n_blocks;
+      const int max_splits = p.k_blocks / 8 < 1 ? 1 : (p.k_blocks / 8 > 16 ? 16 : p.k_blocks / 8);
+      double best = -1.0;
+      for (int s = 1; s <= max_splits; ++s) {
+        const long long items = tiles * s;
+        const long long waves = (items + sms - 1) / sms;
+        const double eff = (double)items / (double)(waves * sms) - 0.004 * (s - 1);
+        if (eff > best + 1e-9) { best = eff; splits = s; }
+      }
     }
   }
   if (splits > p.k_blocks) splits = p.k_blocks;
