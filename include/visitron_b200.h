@@ -200,6 +200,45 @@ int vt_gelu_bwd(const void* dy, const void* pre, int64_t n, void* dx, vt_stream 
 int vt_cast_bf16_f32(const void* x, int64_t n, float* y, vt_stream stream);
 int vt_cast_f32_bf16_add(const float* x, const void* addend, int64_t n, void* y, vt_stream stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Fine-tuning heads around the encoder, fp32 end to end so that the
+ * action argmax agrees with the reference exactly.
+ * ------------------------------------------------------------------------------------------ */
+/* y[B,N] = act([x1 ; x2] W^T + bias): nn.Linear on a decoder step's batch, the input optionally the
+ * concatenation of two tensors (replaces torch.cat + linear_out, vs/agent_models.py:351-353).
+ * act: 0 none, 1 tanh.  Replaces SoftDotAttention.linear_in / linear_out (vs/agent_models.py:323-326),
+ * decoder2action (tb/agent_models.py:297,318), question_linear (vs/agent_models.py:455-459,503). */
+int vt_small_linear_fwd(const float* x1, int64_t ldx1, int64_t K1, const float* x2, int64_t ldx2, int64_t K2, const float* W,
+                        int64_t ldw, const float* bias, int act, float* y, int64_t ldy, int64_t B, int64_t N, vt_stream stream);
+/* dx1 / dx2 / dW / dbias may be NULL (not needed); dW, dbias are overwritten, not accumulated. */
+int vt_small_linear_bwd(const float* dy, int64_t lddy, const float* y, int64_t ldy, int act, const float* x1, int64_t ldx1, int64_t K1,
+                        const float* x2, int64_t ldx2, int64_t K2, const float* W, int64_t ldw, float* dx1, int64_t lddx1, float* dx2,
+                        int64_t lddx2, float* dW, int64_t lddw, float* dbias, int64_t B, int64_t N, vt_stream stream);
+/* Context splits P the two calls below use; workspace floats: fwd B*P*(2+D), bwd B*L + B*P*D. */
+int64_t vt_softdot_splits(int64_t B, int64_t L);
+/* SoftDotAttention core (vs/agent_models.py:335-349): logit[b,l] = ctx[b,l,:].target[b,:], positions with mask != 0
+ * set to -inf IN the returned logit (the reference's masked_fill_ aliases it), attn = softmax_l(logit),
+ * weighted[b,:] = sum_l attn[b,l] ctx[b,l,:].  ctx: [B,L,D] contiguous, D % 4 == 0, D <= 2176. */
+int vt_softdot_fwd(const float* ctx, const float* target, const uint8_t* mask, int64_t B, int64_t L, int64_t D, float* logit, float* attn,
+                   float* weighted, float* workspace, vt_stream stream);
+/* Backward: upstream gradients of weighted, of attn (output_prob=True) and of the returned logit (output_prob=False),
+ * each optional; dctx optional (candidate / view features carry no gradient in the reference). */
+int vt_softdot_bwd(const float* ctx, const float* target, const uint8_t* mask, const float* attn, const float* dweighted, const float* dattn,
+                   const float* dlogit_ext, int64_t B, int64_t L, int64_t D, float* dctx, float* dtarget, float* workspace, vt_stream stream);
+/* Action-logit masking + CrossEntropyLoss(ignore_index, mean) + argmax (vs/agent.py:396-408, tb/agent.py:150-152,316-327):
+ * columns >= valid_len[b] and, where forbid0[b], column 0 become -inf in `masked` (may alias logits);
+ * out3 = {loss, rows not ignored, sum of their losses}; lse fp32 [B] saved for backward. */
+int vt_head_ce_fwd(const float* logits, int64_t ld, int64_t B, int64_t C, const int64_t* valid_len, const uint8_t* forbid0,
+                   const int64_t* target, int64_t ignore_index, float* masked, int64_t ldm, float* lse, int64_t* argmax, float* out3,
+                   vt_stream stream);
+int vt_head_ce_bwd(const float* masked, int64_t ldm, int64_t B, int64_t C, const int64_t* target, int64_t ignore_index, const float* lse,
+                   const float* out3, const float* g, float* dlogits, int64_t ldd, vt_stream stream);
+/* BCEWithLogitsLoss(pos_weight, reduction none) masked mean (vs/classifier/agent.py:158-163,493-503): out2 = {loss, n_valid}. */
+int vt_bce_logits_fwd(const float* q, const float* target, const uint8_t* valid, int64_t B, float pos_weight, float* per_row, float* out2,
+                      vt_stream stream);
+int vt_bce_logits_bwd(const float* q, const float* target, const uint8_t* valid, int64_t B, float pos_weight, const float* out2,
+                      const float* g, float* dq, vt_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -54,3 +54,13 @@ def test_no_cpu_fallback():
         lib.init()
     rc = lib.load().vt_init(0)
     assert rc != 0 and b"no CUDA device" in lib.load().vt_last_error()
+
+
+def test_agent_heads_refuse_cpu_tensors():
+    from visitron_b200 import agent_heads as ah
+    with pytest.raises(lib.VtError):
+        ah.small_linear(torch.randn(2, 8), torch.randn(4, 8))
+    with pytest.raises(lib.VtError):
+        ah.SoftDotAttention(8)(torch.randn(2, 8), torch.randn(2, 3, 8))
+    with pytest.raises(lib.VtError):
+        ah.masked_cross_entropy(torch.randn(2, 3), torch.zeros(2, dtype=torch.long))

@@ -35,6 +35,15 @@ SIGNATURES = {
     "vt_gelu_bwd": (I, [P, P, I64, P, P]),
     "vt_cast_bf16_f32": (I, [P, I64, P, P]),
     "vt_cast_f32_bf16_add": (I, [P, P, I64, P, P]),
+    "vt_small_linear_fwd": (I, [P, I64, I64, P, I64, I64, P, I64, P, I, P, I64, I64, I64, P]),
+    "vt_small_linear_bwd": (I, [P, I64, P, I64, I, P, I64, I64, P, I64, I64, P, I64, P, I64, P, I64, P, I64, P, I64, I64, P]),
+    "vt_softdot_splits": (I64, [I64, I64]),
+    "vt_softdot_fwd": (I, [P, P, P, I64, I64, I64, P, P, P, P, P]),
+    "vt_softdot_bwd": (I, [P, P, P, P, P, P, P, I64, I64, I64, P, P, P, P]),
+    "vt_head_ce_fwd": (I, [P, I64, I64, I64, P, P, P, I64, P, I64, P, P, P, P]),
+    "vt_head_ce_bwd": (I, [P, I64, I64, I64, P, I64, P, P, P, P, I64, P]),
+    "vt_bce_logits_fwd": (I, [P, P, P, I64, F, P, P, P]),
+    "vt_bce_logits_bwd": (I, [P, P, P, I64, F, P, P, P, P]),
 }
 
 
