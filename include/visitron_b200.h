@@ -83,6 +83,10 @@ int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void* B, int64_t
 
 /* Debug hook for tests: force the GEMM tile width (0 = heuristic; 64/128/192/256). */
 void vt_debug_force_block_n(int bn);
+/* The persistent GEMM launches one CTA per SM.  While a gradient all-reduce runs beside the backward GEMMs its CTAs hold
+ * a few SMs; a full-width GEMM grid would then run its last CTAs as a second wave.  n > 0 makes the GEMM leave n SMs free
+ * (visitron_b200/parallel.py sets it for the span of the overlapped exchange); 0 restores the full grid. */
+void vt_reserve_sms(int n);
 
 /* ------------------------------------------------------------------------------------------
  * Row kernels (HBM-bound, one warp per 768-wide row, 16-byte vectors).  hidden must be 768.

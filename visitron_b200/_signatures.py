@@ -9,6 +9,7 @@ SIGNATURES = {
     "vt_launch_count": (I64, []),
     "vt_reset_launch_count": (None, []),
     "vt_debug_force_block_n": (None, [I]),
+    "vt_reserve_sms": (None, [I]),
     "vt_gemm_bf16": (I, [P, I64, I, P, I64, I, P, I64, I64, I64, I64, P, P]),
     "vt_layernorm_fwd": (I, [P, I64, P, P, F, I64, I64, P, I64, F, U64, U32, I64, I64, I64, P]),
     "vt_row_partials_rows": (I64, [I64]),

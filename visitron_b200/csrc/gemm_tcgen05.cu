@@ -61,22 +61,38 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-// Epilogue of one 32-row x 32-column slice of the accumulator, in the COALESCED layout: after the in-warp
-// shared-memory transpose lane L owns 8 consecutive columns [8 (L & 3), +8) of row (L >> 2) + 8 i, i = 0..3, so
-// one warp-wide 16-byte access covers 8 rows x 64 contiguous bytes (whole 32-byte sectors) of every bf16
-// operand -- bias, saved pre-activation, residual, output -- instead of 32 rows x 16 bytes.
-__device__ __forceinline__ void epilogue_rows8(const GemmParams& p, int m, int n0, float* x, const float* bias8) {
+// Epilogue kinds.  EPI_GENERIC reads every switch from GemmParams at run time (any output type, accumulate, row remap,
+// unaligned operands); the others are the encoder's hot combinations with the switches as template constants -- less
+// code (the generic epilogue alone is ~3500 SASS instructions, enough to miss in the instruction cache with eight
+// epilogue warps at different places), fewer registers, and the per-element operand (residual or saved pre-activation)
+// of the NEXT 32-column chunk is prefetched into registers while the current chunk is processed.
+// The fast kinds require: bf16 output, no accumulate / split-K, no row remap, 16-byte aligned operands, N % 8 == 0.
+enum { EPI_BIAS = 1, EPI_GELU = 2, EPI_GELU_BWD = 4, EPI_DROP = 8, EPI_RESID = 16, EPI_GENERIC = 32 };
+
+template <int EPI>
+struct EpiK {
+  static constexpr bool generic = (EPI & EPI_GENERIC) != 0;
+  static constexpr bool ext = !generic && (EPI & (EPI_GELU_BWD | EPI_RESID)) != 0;  // prefetched per-element operand
+};
+
+// Epilogue of 8 consecutive columns of one output row, in the COALESCED layout: after the in-warp shared-memory
+// transpose lane L owns columns [8 (L & 3), +8) of row (L >> 2) + 8 i, i = 0..3, of the 32 x 32 chunk, so one warp-wide
+// 16-byte access covers 8 rows x 64 contiguous bytes (whole 32-byte sectors) of every bf16 operand -- saved
+// pre-activation, residual, output -- instead of 32 rows x 16 bytes.  x arrives as alpha * acc.
+template <int EPI>
+__device__ __forceinline__ void epilogue_rows8(const GemmParams& p, int m, int n0, float* x, const float* bias8, const uint4& ext) {
+  constexpr bool G = EpiK<EPI>::generic;
   if (m >= p.M) return;
-  const int ncols = min(8, p.N - n0);
-  if (ncols <= 0) return;
+  const int ncols = G ? min(8, p.N - n0) : 8;
+  if (n0 >= p.N) return;
   long long orow = m;
-  if (p.remap_in > 0) orow = (long long)(m / p.remap_in) * p.remap_out + p.remap_off + (m % p.remap_in);
-  const bool vec = p.vec_ok && ncols == 8;
-  if (p.bias) {
+  if (G && p.remap_in > 0) orow = (long long)(m / p.remap_in) * p.remap_out + p.remap_off + (m % p.remap_in);
+  const bool vec = G ? (p.vec_ok && ncols == 8) : true;
+  if (G ? (p.bias != nullptr) : (EPI & EPI_BIAS) != 0) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) x[j] += bias8[j];
   }
-  if (p.aux_out) {
+  if (G ? (p.aux_out != nullptr) : (EPI & EPI_GELU) != 0) {
     bf16* ao = p.aux_out + (long long)m * p.ldaux_out + n0;
     if (vec) {
       *reinterpret_cast<uint4*>(ao) = pack8(x);
@@ -86,22 +102,26 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, int m, int n
         if (j < ncols) ao[j] = __float2bfloat16(x[j]);
     }
   }
-  if (p.act == VT_ACT_GELU) {
+  if (G ? (p.act == VT_ACT_GELU) : (EPI & EPI_GELU) != 0) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) x[j] = gelu_fwd(x[j]);
-  } else if (p.act == VT_ACT_TANH) {
+  } else if (G && p.act == VT_ACT_TANH) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) x[j] = tanhf(x[j]);
-  } else if (p.act == VT_ACT_GELU_BWD || p.act == VT_ACT_TANH_BWD) {
-    const bf16* ax = p.aux + (long long)m * p.ldaux + n0;
+  } else if (G ? (p.act == VT_ACT_GELU_BWD || p.act == VT_ACT_TANH_BWD) : (EPI & EPI_GELU_BWD) != 0) {
     float a[8];
-    if (vec) {
-      unpack8(__ldg(reinterpret_cast<const uint4*>(ax)), a);
+    if (!G) {
+      unpack8(ext, a);
     } else {
+      const bf16* ax = p.aux + (long long)m * p.ldaux + n0;
+      if (vec) {
+        unpack8(__ldg(reinterpret_cast<const uint4*>(ax)), a);
+      } else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) a[j] = (j < ncols) ? __bfloat162float(ax[j]) : 0.f;
+        for (int j = 0; j < 8; ++j) a[j] = (j < ncols) ? __bfloat162float(ax[j]) : 0.f;
+      }
     }
-    if (p.act == VT_ACT_GELU_BWD) {
+    if (!G || p.act == VT_ACT_GELU_BWD) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) x[j] *= gelu_grad(a[j]);
     } else {
@@ -109,27 +129,30 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, int m, int n
       for (int j = 0; j < 8; ++j) x[j] *= (1.0f - a[j] * a[j]);
     }
   }
-  if (p.drop.thresh16) {
+  if ((G || (EPI & EPI_DROP) != 0) && p.drop.thresh16) {
     // linear index of the LOGICAL element (m, n); N % 8 == 0 is enforced on the host
     float mult[8];
     dropout_mult8(p.drop, (uint64_t)m * (uint64_t)p.N + (uint64_t)n0, mult);
 #pragma unroll
     for (int j = 0; j < 8; ++j) x[j] *= mult[j];
   }
-  if (p.residual) {
-    const bf16* r = p.residual + orow * p.ldr + n0;
-    if (vec) {
-      float t[8];
-      unpack8(__ldg(reinterpret_cast<const uint4*>(r)), t);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) x[j] += t[j];
+  if (G ? (p.residual != nullptr) : (EPI & EPI_RESID) != 0) {
+    float t[8];
+    if (!G) {
+      unpack8(ext, t);
     } else {
+      const bf16* r = p.residual + orow * p.ldr + n0;
+      if (vec) {
+        unpack8(__ldg(reinterpret_cast<const uint4*>(r)), t);
+      } else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j)
-        if (j < ncols) x[j] += __bfloat162float(r[j]);
+        for (int j = 0; j < 8; ++j) t[j] = (j < ncols) ? __bfloat162float(r[j]) : 0.f;
+      }
     }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[j] += t[j];
   }
-  if (p.out_fp32) {
+  if (G && p.out_fp32) {
     float* d = reinterpret_cast<float*>(p.D) + orow * p.ldd + n0;
     if (p.accumulate) {
       if (vec) {
@@ -162,7 +185,7 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, int m, int n
   }
 }
 
-template <int BN, int A_MN, int B_MN>
+template <int BN, int A_MN, int B_MN, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
   using Cfg = GemmCfg<BN>;
@@ -274,6 +297,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp >= 4) {
+    constexpr bool EXT = EpiK<EPI>::ext;
+    constexpr bool G = EpiK<EPI>::generic;
     const int q = warp & 3;            // TMEM lane quadrant this warp may read
     const int half = (warp - 4) >> 2;  // which half of the tile's columns
     constexpr int CHUNKS = BN / 32;
@@ -284,8 +309,28 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int r8 = lane >> 2, c4 = lane & 3;
     float alpha = p.alpha;
     if (p.alpha_dev) alpha *= __ldg(p.alpha_dev);
+    const bf16* ext_base = nullptr;
+    long long ext_ld = 0;
+    if (EXT) {
+      ext_base = (EPI & EPI_RESID) ? p.residual : p.aux;
+      ext_ld = (EPI & EPI_RESID) ? p.ldr : p.ldaux;
+    }
+    // the per-element operand of chunk c of tile (m_blk, n_blk) in the coalesced layout: 4 rows x 16 bytes per lane
+    auto load_ext = [&](uint4* e, int m_blk, int n_blk, int c) {
+      const int n0 = n_blk * BN + c * 32 + 8 * c4;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int m = m_blk * BM + q * 32 + r8 + 8 * i;
+        e[i] = (m < p.M && n0 < p.N) ? __ldg(reinterpret_cast<const uint4*>(ext_base + (long long)m * ext_ld + n0)) : make_uint4(0u, 0u, 0u, 0u);
+      }
+    };
     int acc = 0;
     uint32_t acc_phase = 0;
+    uint4 ext[4] = {}, ext_next[4] = {};
+    if (EXT && (int)blockIdx.x < total_tiles) {
+      const int mn = (int)blockIdx.x % mn_tiles;
+      load_ext(ext, mn / p.n_blocks, mn % p.n_blocks, c_begin);
+    }
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int mn = t % mn_tiles;
       const int m_blk = mn / p.n_blocks, n_blk = mn % p.n_blocks;
@@ -304,16 +349,21 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         __syncwarp();
         if (c + 1 < c_end) {
           tmem_ld_32x32(t_addr + (uint32_t)((c + 1) * 32), v);  // in flight while this chunk is post-processed
+          if (EXT) load_ext(ext_next, m_blk, n_blk, c + 1);
         } else {
           // the accumulator stage is drained: hand it back to the MMA warp before the post-processing
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty_bar(acc));
+          if (EXT && t + (int)gridDim.x < total_tiles) {
+            const int mn2 = (t + (int)gridDim.x) % mn_tiles;
+            load_ext(ext_next, mn2 / p.n_blocks, mn2 % p.n_blocks, c_begin);
+          }
         }
         const int n0 = n_blk * BN + c * 32 + 8 * c4;
         float bias8[8];
-        if (p.bias) {
-          if (p.vec_ok && n0 + 8 <= p.N) {
+        if (G ? (p.bias != nullptr) : (EPI & EPI_BIAS) != 0) {
+          if ((!G || p.vec_ok) && n0 + 8 <= p.N) {
             const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + n0)), b1 = __ldg(reinterpret_cast<const float4*>(p.bias + n0) + 1);
             bias8[0] = b0.x; bias8[1] = b0.y; bias8[2] = b0.z; bias8[3] = b0.w;
             bias8[4] = b1.x; bias8[5] = b1.y; bias8[6] = b1.z; bias8[7] = b1.w;
@@ -322,15 +372,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int j = 0; j < 8; ++j) bias8[j] = (n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
           }
         }
+        // all four rows out of the staging buffer first, then the arithmetic of the four rows (independent chains)
+        uint4 lo[4], hi[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
           const int row = r8 + 8 * i;
           const uint32_t ra = stg + (uint32_t)row * 128u;
-          const uint4 lo = ld_shared_v4(ra + ((uint32_t)((2 * c4) ^ (row & 7)) << 4));
-          const uint4 hi = ld_shared_v4(ra + ((uint32_t)((2 * c4 + 1) ^ (row & 7)) << 4));
-          float x[8] = {__uint_as_float(lo.x) * alpha, __uint_as_float(lo.y) * alpha, __uint_as_float(lo.z) * alpha, __uint_as_float(lo.w) * alpha,
-                        __uint_as_float(hi.x) * alpha, __uint_as_float(hi.y) * alpha, __uint_as_float(hi.z) * alpha, __uint_as_float(hi.w) * alpha};
-          epilogue_rows8(p, m_blk * BM + q * 32 + row, n0, x, bias8);
+          lo[i] = ld_shared_v4(ra + ((uint32_t)((2 * c4) ^ (row & 7)) << 4));
+          hi[i] = ld_shared_v4(ra + ((uint32_t)((2 * c4 + 1) ^ (row & 7)) << 4));
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float x[8] = {__uint_as_float(lo[i].x) * alpha, __uint_as_float(lo[i].y) * alpha, __uint_as_float(lo[i].z) * alpha, __uint_as_float(lo[i].w) * alpha,
+                        __uint_as_float(hi[i].x) * alpha, __uint_as_float(hi[i].y) * alpha, __uint_as_float(hi[i].z) * alpha, __uint_as_float(hi[i].w) * alpha};
+          epilogue_rows8<EPI>(p, m_blk * BM + q * 32 + r8 + 8 * i, n0, x, bias8, ext[i]);
+        }
+        if (EXT) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) ext[i] = ext_next[i];
         }
         if (c + 1 < c_end) tmem_ld_wait();
         __syncwarp();  // staging buffer is rewritten by the next chunk
@@ -386,11 +445,11 @@ int make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, u
   return VT_OK;
 }
 
-template <int BN, int A_MN, int B_MN>
+template <int BN, int A_MN, int B_MN, int EPI = EPI_GENERIC>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t st) {
   using Cfg = GemmCfg<BN>;
   static bool attr_set = false;
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, EPI>;
   if (!attr_set) {
     VT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set = true;
@@ -410,12 +469,14 @@ static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUten
 }
 
 static int g_force_bn = 0;
+static std::atomic<int> g_reserved_sms{0};
 
 }  // namespace vt
 
 using namespace vt;
 
 extern "C" void vt_debug_force_block_n(int bn) { vt::g_force_bn = bn; }
+extern "C" void vt_reserve_sms(int n) { vt::g_reserved_sms.store(n < 0 ? 0 : n); }
 extern "C" int64_t vt_launch_count(void) { return (int64_t)vt::g_launches.load(); }
 extern "C" void vt_reset_launch_count(void) { vt::g_launches.store(0); }
 
@@ -438,7 +499,8 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   VT_REQUIRE(!splitting || (!ep->bias && ep->act == VT_ACT_NONE && !ep->residual && ep->dropout_p <= 0.f && !ep->aux_out),
              "vt_gemm_bf16: split-K supports only the alpha epilogue");
 
-  const int sms = num_sms();
+  int sms = num_sms() - g_reserved_sms.load(std::memory_order_relaxed);  // see vt_reserve_sms
+  if (sms < 16) sms = 16;
   int BN = 256;
   const int m_blocks = (int)((M + BM - 1) / BM);
   if (g_force_bn) {
@@ -517,6 +579,20 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   long long total = (long long)p.m_blocks * p.n_blocks * p.splits;
   int grid = (int)(total < sms ? total : sms);
   cudaStream_t st = (cudaStream_t)stream;
+  // the encoder's hot epilogues as compile-time kinds (see EPI_*); everything else takes the generic kernel
+  const bool fast_ok = BN == 256 && !p.out_fp32 && !p.accumulate && p.remap_in <= 0 && p.vec_ok && N % 8 == 0 && p.splits == 1;
+  if (fast_ok) {
+    const bool bias = p.bias != nullptr, drop = p.drop.thresh16 != 0, res = p.residual != nullptr, auxo = p.aux_out != nullptr;
+    if (!a_major && !b_major) {
+      if (bias && p.act == VT_ACT_NONE && !res && !drop && !auxo) return launch_gemm<256, 0, 0, EPI_BIAS>(ta, tb, p, grid, st);
+      if (bias && p.act == VT_ACT_GELU && !res && !drop && auxo) return launch_gemm<256, 0, 0, EPI_BIAS | EPI_GELU>(ta, tb, p, grid, st);
+      if (bias && p.act == VT_ACT_NONE && res && !auxo) return launch_gemm<256, 0, 0, EPI_BIAS | EPI_DROP | EPI_RESID>(ta, tb, p, grid, st);
+    } else if (!a_major && b_major && !bias && !drop && !auxo) {
+      if (p.act == VT_ACT_GELU_BWD && !res) return launch_gemm<256, 0, 1, EPI_GELU_BWD>(ta, tb, p, grid, st);
+      if (p.act == VT_ACT_NONE && res) return launch_gemm<256, 0, 1, EPI_RESID>(ta, tb, p, grid, st);
+      if (p.act == VT_ACT_NONE && !res) return launch_gemm<256, 0, 1, 0>(ta, tb, p, grid, st);
+    }
+  }
   switch (BN) {
     case 64: return dispatch_major<64>(a_major, b_major, ta, tb, p, grid, st);
     case 128: return dispatch_major<128>(a_major, b_major, ta, tb, p, grid, st);

@@ -23,19 +23,41 @@ signature, never on data.
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional
 
 import torch
 import torch.distributed as dist
+
+# CTAs (= SMs) NCCL may use for the overlapped gradient exchange; the persistent GEMM leaves as many SMs free while
+# an exchange is in flight, so that neither side waits for the other's CTAs to retire.  NVSwitch reduces in the switch
+# (NVLS), so a 28 MB bucket needs few CTAs to run far faster than the backward of the next layer.
+NCCL_MAX_CTAS = int(os.environ.get("VT_NCCL_MAX_CTAS", "8"))
+
+
+def _exchange_group():
+    """A NCCL communicator of its own for the gradient exchange, capped at NCCL_MAX_CTAS CTAs."""
+    try:
+        opts = dist.ProcessGroupNCCL.Options()
+        opts.config.max_ctas = NCCL_MAX_CTAS
+        opts.config.min_ctas = 1
+        return dist.new_group(backend="nccl", pg_options=opts)
+    except Exception:  # older torch without ncclConfig plumbing: the default communicator
+        return None
 
 
 class GradReducer:
     def __init__(self, process_group=None, overlap: bool = True):
         if not dist.is_available() or not dist.is_initialized():
             raise RuntimeError("GradReducer needs an initialised torch.distributed process group")
-        self.group = process_group
-        self.world_size = dist.get_world_size(process_group)
         self.backend = dist.get_backend(process_group)
+        self.world_size = dist.get_world_size(process_group)
+        self.reserve = 0
+        if self.backend == "nccl" and process_group is None and overlap and self.world_size > 1:
+            process_group = _exchange_group()
+            self.reserve = NCCL_MAX_CTAS if process_group is not None else 0
+        self.group = process_group
+        self._reserved = False
         self.overlap = overlap
         self._works: List = []
         self._pending: List[torch.Tensor] = []
@@ -48,6 +70,10 @@ class GradReducer:
             return
         self.calls += 1
         self.bytes_reduced += bucket.numel() * bucket.element_size()
+        if self.reserve and not self._reserved:
+            from . import lib
+            lib.load().vt_reserve_sms(self.reserve)
+            self._reserved = True
         if self.backend == "nccl":
             w = dist.all_reduce(bucket, op=dist.ReduceOp.AVG, group=self.group, async_op=True)
         else:  # gloo (CPU tests): no AVG
@@ -62,6 +88,10 @@ class GradReducer:
         for w in self._works:
             w.wait()
         self._works = []
+        if self._reserved:
+            from . import lib
+            lib.load().vt_reserve_sms(0)
+            self._reserved = False
         for b in self._pending:
             b.div_(self.world_size)
         self._pending = []
