@@ -157,7 +157,9 @@ int vt_scatter_add_rows(const void* src, int64_t lds, const int64_t* idx, int64_
  * Fused masked-softmax self-attention (oscar/modeling_bert.py:52-72), head dim 64.
  * qkv: bf16 [B*S, ld] = [Q | K | V] (each heads*64 wide) as written by the fused QKV GEMM.
  * bias: fp32 [B, S] additive key bias from vt_mask_bias.  ctx: bf16 [B*S, heads*64].
- * lse: fp32 [B, heads, S, 2] = (row max, 1 / sum exp) saved for backward.  dsum_ws: fp32 [B, heads, S] scratch.
+ * lse: fp32 [B, heads, S, 2] = (row max, 1 / sum exp) saved for backward.
+ * dsum_ws: fp32 scratch of vt_attention_bwd_workspace(B, S, heads) floats, 16-byte aligned: rowsum(dO.O) [B, heads, S], then the
+ * per-key-tile dQ partials [ceil(S/128)][B*S][heads*64] that the backward adds in a fixed order (deterministic, no atomics).
  * ------------------------------------------------------------------------------------------ */
 /* bias = (1 - mask) * -10000 in fp32 for any mask value (vs/encoder.py:226-241).
  * mask_dtype: 0 int64, 1 uint8/bool, 2 int32, 3 fp32. */
@@ -166,6 +168,7 @@ int vt_mask_bias(const void* mask, int mask_dtype, int64_t n, float* bias, vt_st
 void vt_debug_attention_impl(int impl);
 int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, int64_t B, int64_t S, int64_t heads, int64_t head_dim,
                      void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream);
+int64_t vt_attention_bwd_workspace(int64_t B, int64_t S, int64_t heads);
 int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, const void* ctx, const void* dctx, const float* lse,
                      float* dsum_ws, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv, float dropout_p,
                      uint64_t seed, uint32_t dropout_stream, vt_stream stream);

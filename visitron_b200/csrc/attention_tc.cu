@@ -42,6 +42,7 @@ struct AttnTcParams {
   bf16* out;           // fwd: ctx [B*S, hidden]
   float* lse;          // [B, heads, S, 2] = (reference max, 1 / sum)
   const float* dsum;   // [B, heads, S]
+  float* dq_ws;        // [key tiles, B*S, hidden] fp32 dQ partials
   bf16* dqkv;          // [B*S, ld]
   long long ld;
   DropoutCfg drop;
@@ -118,7 +119,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       tma_load_2d(sQ, &tmQ, q_full, h * 64, row_base + qt * FQ);
       for (int j = 0; j < nkt; ++j) {
         const int st = j & 1;
-        if (j >= 2) mbar_wait(kv_empty + 8 * st, (uint32_t)(((j >> 1) - 1) & 1));
+        if (j >= 2) mbar_wait_backoff(kv_empty + 8 * st, (uint32_t)(((j >> 1) - 1) & 1), 128);
         mbar_arrive_expect_tx(kv_full + 8 * st, 16384);
         tma_load_2d(sK + st * 8192, &tmKV, kv_full + 8 * st, p.hidden + h * 64, row_base + j * FK);
         tma_load_2d(sV + st * 8192, &tmKV, kv_full + 8 * st, 2 * p.hidden + h * 64, row_base + j * FK);
@@ -134,18 +135,18 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         for (int k = 0; k < 4; ++k) umma_bf16(tmem_base, a + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc_s, k > 0 ? 1u : 0u);
         umma_commit(s_full);
       };
-      mbar_wait(q_full, 0);
-      mbar_wait(kv_full, 0);
+      mbar_wait_backoff(q_full, 0, 32);
+      mbar_wait_backoff(kv_full, 0, 32);
       tc_fence_after();
       issue_s(0);
       for (int j = 0; j < nkt; ++j) {
         if (j + 1 < nkt) {
-          mbar_wait(kv_full + 8 * ((j + 1) & 1), (uint32_t)(((j + 1) >> 1) & 1));
-          mbar_wait(s_free, (uint32_t)(j & 1));
+          mbar_wait_backoff(kv_full + 8 * ((j + 1) & 1), (uint32_t)(((j + 1) >> 1) & 1), 32);
+          mbar_wait_backoff(s_free, (uint32_t)(j & 1), 32);
           tc_fence_after();
           issue_s(j + 1);
         }
-        mbar_wait(p_ready, (uint32_t)(j & 1));
+        mbar_wait_backoff(p_ready, (uint32_t)(j & 1), 32);
         tc_fence_after();
         const uint64_t a = make_smem_desc(sP, 16, 1024), bd = make_smem_desc(sV + (j & 1) * 8192, 8192, 1024);
 #pragma unroll
@@ -195,11 +196,22 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       }
       l += rs;
       if (p.drop.thresh16) {
+        // counter layout of attn_dropout_rand: call t of 32-column group g covers columns 8 q + 2 t (low 16-bit lane of word q)
+        // and 8 q + 2 t + 1 (high lane); keep iff lane >= thresh16.  The 1 / (1 - p) scale is applied once, to O.
+        const uint32_t thi = p.drop.thresh16 << 16;
 #pragma unroll
         for (int g = 0; g < 2; ++g) {
-          const uint32_t keep = attn_keep_mask32(p.drop, bh, (uint32_t)qi, (uint32_t)(j * 2 + g));
 #pragma unroll
-          for (int c = 0; c < 32; ++c) sv[32 * g + c] = __float_as_uint(((keep >> c) & 1u) ? __uint_as_float(sv[32 * g + c]) * p.drop.scale : 0.f);
+          for (uint32_t t = 0; t < 4; ++t) {
+            const uint4 rr = attn_dropout_rand(p.drop, bh, (uint32_t)qi, (uint32_t)(j * 2 + g), t);
+            const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const int c0 = 32 * g + 8 * q + 2 * (int)t;
+              if ((w[q] << 16) < thi) sv[c0] = 0u;
+              if (w[q] < thi) sv[c0 + 1] = 0u;
+            }
+          }
         }
       }
       if (j > 0) {
@@ -234,6 +246,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     mbar_wait(o_full, (uint32_t)((nkt - 1) & 1));
     tc_fence_after();
     const float inv = 1.0f / l;
+    const float onorm = p.drop.thresh16 ? inv * p.drop.scale : inv;
     bf16* dst = p.out + ((long long)row_base + qi) * p.hidden + h * 64;
 #pragma unroll
     for (int hh = 0; hh < 2; ++hh) {
@@ -245,7 +258,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         for (int ch = 0; ch < 4; ++ch) {
           float f[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(ov[8 * ch + e]) * inv;
+          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(ov[8 * ch + e]) * onorm;
           *reinterpret_cast<uint4*>(dst + 32 * hh + 8 * ch) = pack8(f);
         }
       }
@@ -258,32 +271,37 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
 }
 
 // ---------------------------------------------------------------------------------------------
-// backward
+// backward: ONE pass over the (query tile, key tile) pairs.  A CTA owns a 128-key tile (K_j, V_j resident, dK_j / dV_j
+// accumulating in TMEM) and streams the query tiles: S and dP are recomputed per pair, the eight element-wise warps turn
+// them into P (dropout applied) and dS once, and three accumulations consume them:
+//     dV_j += P^T.dO_i      dK_j += dS^T.Q_i      dQ_i partial = dS.K_j
+// The dQ partial of the pair goes to an fp32 workspace slice [key tile][row][hidden] (plain stores, no atomics);
+// attn_dq_reduce_kernel adds the key-tile slices in a fixed order, so the result is deterministic.
+// Constant factors are kept out of the per-element work: dS is staged without the 1/sqrt(d) and 1/(1-p) factors, P
+// without 1/(1-p); they are applied to the 64-wide outputs.
 // ---------------------------------------------------------------------------------------------
-constexpr int BWD_THREADS = 320;  // warps 0-7 element-wise, warp 8 TMA, warp 9 MMA + TMEM
-constexpr int BWD_TMEM_COLS = 512;  // S [0,128)  dP [128,256)  acc0 [256,320)  acc1 [320,384)
+constexpr int BWD_THREADS = 320;    // warps 0-7 element-wise, warp 8 TMA, warp 9 MMA + TMEM
+constexpr int BWD_TMEM_COLS = 512;  // S [0,128)  dP [128,256)  dK [256,320)  dV [320,384)  dQ partial x2 [384,448) [448,512)
 constexpr int TILE16K = 16384;
+constexpr int BWD_SMEM_TILES = 10 * TILE16K;  // K, V, Q[2], dO[2], dS (2 halves), P (2 halves)
 
-template <int MODE>  // 0: dK/dV (outer = key tile, inner = query tiles)   1: dQ (outer = query tile, inner = key tiles)
 __global__ void __launch_bounds__(BWD_THREADS, 1)
-attn_bwd_tc(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
+attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  // outer operands: MODE 0: K_j, V_j      MODE 1: Q_i, dO_i
-  // inner ring:     MODE 0: Q_i, dO_i     MODE 1: K_j, V_j
-  const uint32_t sOutA = base, sOutB = base + TILE16K;
-  const uint32_t sInA = base + 2 * TILE16K, sInB = base + 4 * TILE16K;   // 2 stages each
-  const uint32_t sDS = base + 6 * TILE16K;                               // [128 q, 128 k] bf16 as two 64-key halves
-  const uint32_t sPD = base + 8 * TILE16K;                               // MODE 0 only
-  const uint32_t bars = base + (MODE == 0 ? 10 : 8) * TILE16K;
+  const uint32_t sK = base, sV = base + TILE16K;
+  const uint32_t sQ = base + 2 * TILE16K, sDO = base + 4 * TILE16K;  // 2 stages each
+  const uint32_t sDS = base + 6 * TILE16K;                           // [128 q, 128 k] bf16 as two 64-key halves
+  const uint32_t sPD = base + 8 * TILE16K;
+  const uint32_t bars = base + 10 * TILE16K;
   const uint32_t out_full = bars, in_full = bars + 8, in_empty = bars + 24, sdp_full = bars + 40, sdp_free = bars + 48, pds_ready = bars + 56,
-                 pds_free = bars + 64, done = bars + 72, tmem_slot = bars + 80;
+                 pds_free = bars + 64, done = bars + 72, dq_full = bars + 80, dq_free = bars + 96, tmem_slot = bars + 112;
   float* sBias = reinterpret_cast<float*>(smem_raw + (bars + 128 - smem_u32(smem_raw)));
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  const int ot = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int S = p.S;
   const int nin = (S + 127) / 128;
   const int row_base = b * S;
@@ -300,19 +318,17 @@ attn_bwd_tc(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ C
     mbar_init(pds_ready, 256);
     mbar_init(pds_free, 1);
     mbar_init(done, 1);
+    mbar_init(dq_full, 1); mbar_init(dq_full + 8, 1);
+    mbar_init(dq_free, 256); mbar_init(dq_free + 8, 256);
     fence_barrier_init();
   }
   if (warp == 9) {
     tmem_alloc(tmem_slot, BWD_TMEM_COLS);
     tmem_relinquish();
   }
-  if (MODE == 0) {
-    for (int j = threadIdx.x; j < 128; j += BWD_THREADS) {
-      const int k = ot * 128 + j;
-      sBias[j] = k < S ? p.bias[(long long)b * S + k] : -INFINITY;
-    }
-  } else {
-    for (int j = threadIdx.x; j < nin * 128; j += BWD_THREADS) sBias[j] = j < S ? p.bias[(long long)b * S + j] : -INFINITY;
+  for (int j = threadIdx.x; j < 128; j += BWD_THREADS) {
+    const int k = kt * 128 + j;
+    sBias[j] = k < S ? p.bias[(long long)b * S + k] : -INFINITY;
   }
   tc_fence_before();
   __syncthreads();
@@ -322,78 +338,65 @@ attn_bwd_tc(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ C
   if (warp == 8) {
     if (lane == 0) {
       mbar_arrive_expect_tx(out_full, 2 * TILE16K);
-      if (MODE == 0) {
-        tma_load_2d(sOutA, &tmQKV, out_full, hid + h * 64, row_base + ot * 128);
-        tma_load_2d(sOutB, &tmQKV, out_full, 2 * hid + h * 64, row_base + ot * 128);
-      } else {
-        tma_load_2d(sOutA, &tmQKV, out_full, h * 64, row_base + ot * 128);
-        tma_load_2d(sOutB, &tmDO, out_full, h * 64, row_base + ot * 128);
-      }
+      tma_load_2d(sK, &tmQKV, out_full, hid + h * 64, row_base + kt * 128);
+      tma_load_2d(sV, &tmQKV, out_full, 2 * hid + h * 64, row_base + kt * 128);
       for (int t = 0; t < nin; ++t) {
         const int st = t & 1;
-        if (t >= 2) mbar_wait(in_empty + 8 * st, (uint32_t)(((t >> 1) - 1) & 1));
+        if (t >= 2) mbar_wait_backoff(in_empty + 8 * st, (uint32_t)(((t >> 1) - 1) & 1), 128);
         mbar_arrive_expect_tx(in_full + 8 * st, 2 * TILE16K);
-        if (MODE == 0) {
-          tma_load_2d(sInA + st * TILE16K, &tmQKV, in_full + 8 * st, h * 64, row_base + t * 128);
-          tma_load_2d(sInB + st * TILE16K, &tmDO, in_full + 8 * st, h * 64, row_base + t * 128);
-        } else {
-          tma_load_2d(sInA + st * TILE16K, &tmQKV, in_full + 8 * st, hid + h * 64, row_base + t * 128);
-          tma_load_2d(sInB + st * TILE16K, &tmQKV, in_full + 8 * st, 2 * hid + h * 64, row_base + t * 128);
-        }
+        tma_load_2d(sQ + st * TILE16K, &tmQKV, in_full + 8 * st, h * 64, row_base + t * 128);
+        tma_load_2d(sDO + st * TILE16K, &tmDO, in_full + 8 * st, h * 64, row_base + t * 128);
       }
     }
   } else if (warp == 9) {
     if (lane == 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);
       constexpr uint32_t idesc_t = make_idesc_bf16(128, 64, 1, 1);  // acc[128 keys, 64] += X^T (MN-major A) x Y (MN-major B)
-      constexpr uint32_t idesc_q = make_idesc_bf16(128, 64, 0, 1);  // dQ[128 q, 64]    += dS (K-major A) x K (MN-major B)
+      constexpr uint32_t idesc_q = make_idesc_bf16(128, 64, 0, 1);  // dQ[128 q, 64]    = dS (K-major A) x K (MN-major B)
       auto issue_sdp = [&](int t) {
         const int st = t & 1;
         // S = Q.K^T ; dP = dO.V^T   (A: query-side tile, B: key-side tile, both K-major over d = 64)
-        const uint32_t q = MODE == 0 ? sInA + st * TILE16K : sOutA, k = MODE == 0 ? sOutA : sInA + st * TILE16K;
-        const uint32_t dO = MODE == 0 ? sInB + st * TILE16K : sOutB, v = MODE == 0 ? sOutB : sInB + st * TILE16K;
-        const uint64_t qa = make_smem_desc(q, 16, 1024), kb = make_smem_desc(k, 16, 1024);
-        const uint64_t da = make_smem_desc(dO, 16, 1024), vb = make_smem_desc(v, 16, 1024);
+        const uint64_t qa = make_smem_desc(sQ + st * TILE16K, 16, 1024), kb = make_smem_desc(sK, 16, 1024);
+        const uint64_t da = make_smem_desc(sDO + st * TILE16K, 16, 1024), vb = make_smem_desc(sV, 16, 1024);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) umma_bf16(tmem_base, qa + (uint64_t)(2 * kk), kb + (uint64_t)(2 * kk), idesc_s, kk > 0 ? 1u : 0u);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) umma_bf16(tmem_base + 128, da + (uint64_t)(2 * kk), vb + (uint64_t)(2 * kk), idesc_s, kk > 0 ? 1u : 0u);
         umma_commit(sdp_full);
       };
-      mbar_wait(out_full, 0);
-      mbar_wait(in_full, 0);
+      mbar_wait_backoff(out_full, 0, 32);
+      mbar_wait_backoff(in_full, 0, 32);
       tc_fence_after();
       issue_sdp(0);
       for (int t = 0; t < nin; ++t) {
         if (t + 1 < nin) {
-          mbar_wait(in_full + 8 * ((t + 1) & 1), (uint32_t)(((t + 1) >> 1) & 1));
-          mbar_wait(sdp_free, (uint32_t)(t & 1));
+          mbar_wait_backoff(in_full + 8 * ((t + 1) & 1), (uint32_t)(((t + 1) >> 1) & 1), 32);
+          mbar_wait_backoff(sdp_free, (uint32_t)(t & 1), 32);
           tc_fence_after();
           issue_sdp(t + 1);
         }
-        mbar_wait(pds_ready, (uint32_t)(t & 1));
+        mbar_wait_backoff(pds_ready, (uint32_t)(t & 1), 32);
+        if (t >= 2) mbar_wait_backoff(dq_free + 8 * (t & 1), (uint32_t)(((t >> 1) - 1) & 1), 32);
         tc_fence_after();
         const int st = t & 1;
-        if (MODE == 0) {
-          // dV += Pd^T.dO_t ; dK += dS^T.Q_t : A = the [128 q, 128 k] tile read MN-major (M = keys: two 64-key chunks 16 KiB
-          // apart, K = query rows 128 B apart), B = dO_t / Q_t read MN-major (K = query rows)
-          const uint64_t pa = make_smem_desc(sPD, TILE16K, 1024), sa = make_smem_desc(sDS, TILE16K, 1024);
-          const uint64_t dob = make_smem_desc(sInB + st * TILE16K, TILE16K, 1024), qb = make_smem_desc(sInA + st * TILE16K, TILE16K, 1024);
+        // dV += P^T.dO_t ; dK += dS^T.Q_t : A = the [128 q, 128 k] tile read MN-major (M = keys: two 64-key chunks 16 KiB
+        // apart, K = query rows 128 B apart), B = dO_t / Q_t read MN-major (K = query rows)
+        const uint64_t pa = make_smem_desc(sPD, TILE16K, 1024), sa = make_smem_desc(sDS, TILE16K, 1024);
+        const uint64_t dob = make_smem_desc(sDO + st * TILE16K, TILE16K, 1024), qb = make_smem_desc(sQ + st * TILE16K, TILE16K, 1024);
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 320, pa + (uint64_t)(128 * kk), dob + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
+        for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 320, pa + (uint64_t)(128 * kk), dob + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 256, sa + (uint64_t)(128 * kk), qb + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
-        } else {
-          // dQ += dS.K_t : A = dS K-major over 128 keys (two 64-key atoms), B = K_t MN-major (K = key rows)
-          const uint64_t kb = make_smem_desc(sInA + st * TILE16K, TILE16K, 1024);
+        for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 256, sa + (uint64_t)(128 * kk), qb + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
+        // dQ_t partial = dS.K_j : A = dS K-major over 128 keys (two 64-key atoms), B = K_j MN-major (K = key rows)
+        const uint64_t kmn = make_smem_desc(sK, TILE16K, 1024);
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk) {
-            const uint64_t sa = make_smem_desc(sDS + (kk >> 2) * TILE16K + (kk & 3) * 32, 16, 1024);
-            umma_bf16(tmem_base + 256, sa, kb + (uint64_t)(128 * kk), idesc_q, (t > 0 || kk > 0) ? 1u : 0u);
-          }
+        for (int kk = 0; kk < 8; ++kk) {
+          const uint64_t dsa = make_smem_desc(sDS + (kk >> 2) * TILE16K + (kk & 3) * 32, 16, 1024);
+          umma_bf16(tmem_base + 384 + 64 * st, dsa, kmn + (uint64_t)(128 * kk), idesc_q, kk > 0 ? 1u : 0u);
         }
         umma_commit(pds_free);
         umma_commit(in_empty + 8 * st);
+        umma_commit(dq_full + 8 * st);
       }
       umma_commit(done);
     }
@@ -403,22 +406,40 @@ attn_bwd_tc(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ C
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
     const uint32_t bh = (uint32_t)(b * p.heads + h);
     const long long stat_base = ((long long)b * p.heads + h) * S;
-    float2 lse = make_float2(0.f, 0.f);
-    float dsum = 0.f;
-    if (MODE == 1) {
-      const int gi = min(ot * 128 + r, S - 1);
-      lse = *reinterpret_cast<const float2*>(p.lse + 2 * (stat_base + gi));
-      dsum = p.dsum[stat_base + gi];
-    }
-    for (int t = 0; t < nin; ++t) {
-      const int qtile = MODE == 0 ? t : ot, ktile = MODE == 0 ? ot : t;
-      const int gi = qtile * 128 + r;
-      if (MODE == 0) {
-        const int gc = min(gi, S - 1);
-        lse = *reinterpret_cast<const float2*>(p.lse + 2 * (stat_base + gc));
-        dsum = p.dsum[stat_base + gc];
+    const bool drop = p.drop.thresh16 != 0;
+    const float dscale = drop ? p.drop.scale : 1.0f;
+    const float inv_dscale = 1.0f / dscale;
+    const uint32_t thi = p.drop.thresh16 << 16;   // 0 without dropout: every unsigned lane compares >= 0, i.e. is kept
+    const float* bias = sBias + half * 64;
+    float* ws = p.dq_ws + ((long long)kt * p.B * S + row_base) * hid + h * 64 + 32 * half;  // this key tile's slice of the dQ workspace
+
+    auto drain_dq = [&](int t) {  // dQ partial of query tile t: TMEM -> workspace (this warp: 32 rows x 32 of the 64 columns)
+      const int st = t & 1;
+      mbar_wait(dq_full + 8 * st, (uint32_t)((t >> 1) & 1));
+      tc_fence_after();
+      uint32_t a[32];
+      tmem_ld_32x32(lane_addr + 384 + 64 * st + 32 * half, a);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(dq_free + 8 * st);
+      const int gi = t * 128 + r;
+      if (gi < S) {
+        float4* d = reinterpret_cast<float4*>(ws + (long long)gi * hid);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          d[j] = make_float4(__uint_as_float(a[4 * j]), __uint_as_float(a[4 * j + 1]), __uint_as_float(a[4 * j + 2]), __uint_as_float(a[4 * j + 3]));
       }
-      const float* bias = MODE == 0 ? sBias + half * 64 : sBias + t * 128 + half * 64;
+    };
+
+    for (int t = 0; t < nin; ++t) {
+      const int gi = t * 128 + r;
+      const int gc = min(gi, S - 1);
+      const float2 lse = *reinterpret_cast<const float2*>(p.lse + 2 * (stat_base + gc));
+      const float dsp = p.dsum[stat_base + gc] * inv_dscale;
+      // P = exp2(v log2e - mb) / sum with mb rounded exactly as in the forward (the F6 mask bias of 2.54e6 leaves 0.25 ulp:
+      // any other rounding of the reference point would rescale the whole row); rows past the end of the sample get P = dS = 0
+      const float mb = lse.x * kLog2e;
+      const float inv = gi < S ? lse.y : 0.f;
       mbar_wait(sdp_full, (uint32_t)(t & 1));
       tc_fence_after();
       uint32_t sv[64], dv[64];
@@ -429,28 +450,26 @@ attn_bwd_tc(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ C
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(sdp_free);
-      const bool row_ok = gi < S;
-      const float mb = lse.x * kLog2e;
 #pragma unroll
       for (int g = 0; g < 2; ++g) {
-        uint32_t keep = 0xffffffffu;
-        float dscale = 1.f;
-        if (p.drop.thresh16) {
-          keep = attn_keep_mask32(p.drop, bh, (uint32_t)gi, (uint32_t)(ktile * 4 + half * 2 + g));
-          dscale = p.drop.scale;
-        }
 #pragma unroll
-        for (int c = 0; c < 32; ++c) {
-          const int cc = 32 * g + c;
-          const float v = fmaf(__uint_as_float(sv[cc]), p.scale, bias[cc]);
-          float pr = ex2_approx(fmaf(v, kLog2e, -mb)) * lse.y;
-          const float m = ((keep >> c) & 1u) ? dscale : 0.f;
-          const float dp = __uint_as_float(dv[cc]) * m;
-          float ds = pr * (dp - dsum) * p.scale;
-          pr *= m;
-          if (!row_ok) { pr = 0.f; ds = 0.f; }
-          sv[cc] = __float_as_uint(pr);
-          dv[cc] = __float_as_uint(ds);
+        for (uint32_t tt = 0; tt < 4; ++tt) {
+          uint4 rr = make_uint4(0u, 0u, 0u, 0u);
+          if (drop) rr = attn_dropout_rand(p.drop, bh, (uint32_t)gi, (uint32_t)(kt * 4 + half * 2 + g), tt);
+          const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              const int cc = 32 * g + 8 * q + 2 * (int)tt + e;
+              const float v = fmaf(__uint_as_float(sv[cc]), p.scale, bias[cc]);
+              const float pr = ex2_approx(fmaf(v, kLog2e, -mb)) * inv;
+              const bool keep = e == 0 ? ((w[q] << 16) >= thi) : (w[q] >= thi);
+              const float dpm = keep ? __uint_as_float(dv[cc]) : 0.f;
+              sv[cc] = __float_as_uint(keep ? pr : 0.f);
+              dv[cc] = __float_as_uint(pr * (dpm - dsp));
+            }
+          }
         }
       }
       if (t > 0) mbar_wait(pds_free, (uint32_t)((t - 1) & 1));
@@ -461,52 +480,71 @@ attn_bwd_tc(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ C
                      pack_bf16(__uint_as_float(dv[8 * ch + 2]), __uint_as_float(dv[8 * ch + 3])),
                      pack_bf16(__uint_as_float(dv[8 * ch + 4]), __uint_as_float(dv[8 * ch + 5])),
                      pack_bf16(__uint_as_float(dv[8 * ch + 6]), __uint_as_float(dv[8 * ch + 7])));
-        if (MODE == 0)
-          st_shared_v4(sPD + off, pack_bf16(__uint_as_float(sv[8 * ch]), __uint_as_float(sv[8 * ch + 1])),
-                       pack_bf16(__uint_as_float(sv[8 * ch + 2]), __uint_as_float(sv[8 * ch + 3])),
-                       pack_bf16(__uint_as_float(sv[8 * ch + 4]), __uint_as_float(sv[8 * ch + 5])),
-                       pack_bf16(__uint_as_float(sv[8 * ch + 6]), __uint_as_float(sv[8 * ch + 7])));
+        st_shared_v4(sPD + off, pack_bf16(__uint_as_float(sv[8 * ch]), __uint_as_float(sv[8 * ch + 1])),
+                     pack_bf16(__uint_as_float(sv[8 * ch + 2]), __uint_as_float(sv[8 * ch + 3])),
+                     pack_bf16(__uint_as_float(sv[8 * ch + 4]), __uint_as_float(sv[8 * ch + 5])),
+                     pack_bf16(__uint_as_float(sv[8 * ch + 6]), __uint_as_float(sv[8 * ch + 7])));
       }
       fence_proxy_async();
       tc_fence_before();
       mbar_arrive(pds_ready);
+      if (t > 0) drain_dq(t - 1);  // while the MMA warp works on this pair
     }
+    drain_dq(nin - 1);
     mbar_wait(done, 0);
     tc_fence_after();
-    // accumulators -> global: row = outer-tile row (key for MODE 0, query for MODE 1); this warp takes columns [32*half, +32)
-    const int go = ot * 128 + r;
+    // dK / dV accumulators -> global: row = key; this warp takes columns [32*half, +32)
+    const int go = kt * 128 + r;
+    const float fk = p.scale * dscale, fv = dscale;
     uint32_t a0[32];
     tmem_ld_32x32(lane_addr + 256 + 32 * half, a0);
     tmem_ld_wait();
     bf16* row = p.dqkv + ((long long)row_base + go) * p.ld + h * 64 + 32 * half;
     if (go < S) {
-      bf16* d0 = row + (MODE == 0 ? hid : 0);   // dK or dQ
 #pragma unroll
       for (int ch = 0; ch < 4; ++ch) {
         float f[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(a0[8 * ch + e]);
-        *reinterpret_cast<uint4*>(d0 + 8 * ch) = pack8(f);
+        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(a0[8 * ch + e]) * fk;
+        *reinterpret_cast<uint4*>(row + hid + 8 * ch) = pack8(f);
       }
     }
-    if (MODE == 0) {
-      tmem_ld_32x32(lane_addr + 320 + 32 * half, a0);
-      tmem_ld_wait();
-      if (go < S) {
-        bf16* d1 = row + 2 * hid;               // dV
+    tmem_ld_32x32(lane_addr + 320 + 32 * half, a0);
+    tmem_ld_wait();
+    if (go < S) {
 #pragma unroll
-        for (int ch = 0; ch < 4; ++ch) {
-          float f[8];
+      for (int ch = 0; ch < 4; ++ch) {
+        float f[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(a0[8 * ch + e]);
-          *reinterpret_cast<uint4*>(d1 + 8 * ch) = pack8(f);
-        }
+        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(a0[8 * ch + e]) * fv;
+        *reinterpret_cast<uint4*>(row + 2 * hid + 8 * ch) = pack8(f);
       }
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 9) tmem_dealloc(tmem_base, BWD_TMEM_COLS);
+}
+
+// dQ[row, c] = factor * sum over key tiles of the workspace slices, in key-tile order (deterministic) -> bf16 into dqkv[:, 0:hidden]
+__global__ void __launch_bounds__(256)
+attn_dq_reduce_kernel(const float* __restrict__ ws, long long slice, int nkt, long long rows, int hidden, float factor, bf16* __restrict__ dqkv,
+                      long long ld) {
+  const long long per_row = hidden / 8;
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= rows * per_row) return;
+  const long long row = i / per_row;
+  const int c = (int)(i % per_row) * 8;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int k = 0; k < nkt; ++k) {
+    const float4* src = reinterpret_cast<const float4*>(ws + k * slice + row * hidden + c);
+    const float4 x = __ldcs(src), y = __ldcs(src + 1);
+    acc[0] += x.x; acc[1] += x.y; acc[2] += x.z; acc[3] += x.w;
+    acc[4] += y.x; acc[5] += y.y; acc[6] += y.z; acc[7] += y.w;
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] *= factor;
+  *reinterpret_cast<uint4*>(dqkv + row * ld + c) = pack8(acc);
 }
 
 static int g_attn_impl = 0;  // 0 auto, 1 mma.sync kernels, 2 tcgen05 kernels
@@ -516,6 +554,11 @@ static int g_attn_impl = 0;  // 0 auto, 1 mma.sync kernels, 2 tcgen05 kernels
 using namespace vt;
 
 extern "C" void vt_debug_attention_impl(int impl) { vt::g_attn_impl = impl; }
+
+extern "C" int64_t vt_attention_bwd_workspace(int64_t B, int64_t S, int64_t heads) {
+  const int64_t dsum_floats = (B * heads * S + 3) & ~(int64_t)3;
+  return dsum_floats + ((S + 127) / 128) * B * S * heads * 64;
+}
 
 static int check_attn_tc(const char* who, const void* qkv, int64_t ld, int64_t B, int64_t S, int64_t heads, int64_t head_dim) {
   VT_REQUIRE(head_dim == 64, "%s: head dim %lld outside the supported envelope (64)", who, (long long)head_dim);
@@ -579,20 +622,25 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
   if (rc) return rc;
   AttnTcParams p = {};
   p.B = (int)B; p.S = (int)S; p.heads = (int)heads; p.hidden = (int)hidden;
-  p.bias = bias; p.scale = 0.125f; p.lse = const_cast<float*>(lse); p.dsum = dsum_ws; p.dqkv = (bf16*)dqkv; p.ld = ld;
-  p.drop = make_dropout(dropout_p, seed, dropout_stream);
   const int nt = (int)((S + 127) / 128);
-  const size_t smem0 = 1024 + 10 * TILE16K + 128 + 128 * sizeof(float);
-  const size_t smem1 = 1024 + 8 * TILE16K + 128 + (size_t)nt * 128 * sizeof(float);
+  // workspace: [B, heads, S] rowsum(dO.O), then the dQ partial slices [key tiles][B*S][hidden] (16-byte aligned)
+  const size_t dsum_floats = ((size_t)(B * heads * S) + 3) & ~(size_t)3;
+  p.bias = bias; p.scale = 0.125f; p.lse = const_cast<float*>(lse); p.dsum = dsum_ws; p.dq_ws = dsum_ws + dsum_floats;
+  p.dqkv = (bf16*)dqkv; p.ld = ld;
+  p.drop = make_dropout(dropout_p, seed, dropout_stream);
+  VT_REQUIRE(((uintptr_t)dsum_ws & 15) == 0, "vt_attention_bwd: workspace must be 16-byte aligned");
+  const size_t smem = 1024 + BWD_SMEM_TILES + 128 + 128 * sizeof(float);
   static bool attr = false;
   if (!attr) {
-    VT_CUDA(cudaFuncSetAttribute(attn_bwd_tc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(1024 + 10 * TILE16K + 128 + 512)));
-    VT_CUDA(cudaFuncSetAttribute(attn_bwd_tc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(1024 + 8 * TILE16K + 128 + 2048 * 4)));
+    VT_CUDA(cudaFuncSetAttribute(attn_bwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(1024 + BWD_SMEM_TILES + 128 + 512)));
     attr = true;
   }
   const dim3 grid((unsigned)nt, (unsigned)heads, (unsigned)B);
-  attn_bwd_tc<0><<<grid, BWD_THREADS, smem0, st>>>(tq, tdo, p);
-  attn_bwd_tc<1><<<grid, BWD_THREADS, smem1, st>>>(tq, tdo, p);
+  attn_bwd_fused<<<grid, BWD_THREADS, smem, st>>>(tq, tdo, p);
+  const long long rows = B * S;
+  const long long items = rows * (hidden / 8);
+  attn_dq_reduce_kernel<<<(unsigned)((items + 255) / 256), 256, 0, st>>>(p.dq_ws, rows * hidden, nt, rows, (int)hidden,
+                                                                         p.scale * (p.drop.thresh16 ? p.drop.scale : 1.0f), (bf16*)dqkv, ld);
   count_launch(2);
   VT_CHECK_LAUNCH();
   return VT_OK;

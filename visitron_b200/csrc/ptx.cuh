@@ -50,6 +50,15 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// For the single-lane producer / MMA-issuer warps: their spin loops compete for issue slots with the arithmetic warps of
+// the same SM sub-partition, so after a few quick polls they back off with nanosleep.
+__device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity, uint32_t ns) {
+  int polls = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++polls > 2) __nanosleep(ns);
+  }
+}
+
 // ---------------- TMA ----------------
 __device__ __forceinline__ void prefetch_tensormap(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");

@@ -146,7 +146,7 @@ def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0,
     L = init()
     if dqkv is None:
         dqkv = torch.empty_like(qkv)
-    ws = torch.empty((B, heads, S), device=qkv.device, dtype=F32)
+    ws = torch.empty(int(L.vt_attention_bwd_workspace(B, S, heads)), device=qkv.device, dtype=F32)
     check(L.vt_attention_bwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv),
                              dropout_p, seed, stream_id, stream_ptr()), "vt_attention_bwd")
     return dqkv
