@@ -159,7 +159,7 @@ int vt_scatter_add_rows(const void* src, int64_t lds, const int64_t* idx, int64_
  * bias: fp32 [B, S] additive key bias from vt_mask_bias.  ctx: bf16 [B*S, heads*64].
  * lse: fp32 [B, heads, S, 2] = (row max, 1 / sum exp) saved for backward.
  * dsum_ws: fp32 scratch of vt_attention_bwd_workspace(B, S, heads) floats, 16-byte aligned: rowsum(dO.O) [B, heads, S], then the
- * per-key-tile dQ partials [ceil(S/128)][B*S][heads*64] that the backward adds in a fixed order (deterministic, no atomics).
+ * per-key-tile bf16 dQ partials [ceil(S/128)][B*S][heads*64] that the backward adds in a fixed order (deterministic, no atomics).
  * ------------------------------------------------------------------------------------------ */
 /* bias = (1 - mask) * -10000 in fp32 for any mask value (vs/encoder.py:226-241).
  * mask_dtype: 0 int64, 1 uint8/bool, 2 int32, 3 fp32. */

@@ -15,6 +15,8 @@
 //   Two kernels, no atomics: results are deterministic.
 // Both share the dropout counter layout of the mma.sync kernels in attention.cu (kept for S > 2048
 // and as the A/B reference), so forward and backward of either implementation are interchangeable.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -42,10 +44,11 @@ struct AttnTcParams {
   bf16* out;           // fwd: ctx [B*S, hidden]
   float* lse;          // [B, heads, S, 2] = (reference max, 1 / sum)
   const float* dsum;   // [B, heads, S]
-  float* dq_ws;        // [key tiles, B*S, hidden] fp32 dQ partials
+  bf16* dq_ws;         // [key tiles, B*S, hidden] bf16 dQ partials (summed in fp32 by attn_dq_reduce_kernel)
   bf16* dqkv;          // [B*S, ld]
   long long ld;
   DropoutCfg drop;
+  int dbg;             // timing experiments only (VT_ATTN_DBG): bit mask of pipeline pieces to skip
 };
 
 // keep-bits of 32 consecutive key columns [32*jgroup, +32) of query row i (bit c = column 32*jgroup + c),
@@ -98,8 +101,8 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     mbar_init(kv_full, 1); mbar_init(kv_full + 8, 1);
     mbar_init(kv_empty, 1); mbar_init(kv_empty + 8, 1);
     mbar_init(s_full, 1);
-    mbar_init(s_free, 128);
-    mbar_init(p_ready, 128);
+    mbar_init(s_free, 4);
+    mbar_init(p_ready, 4);
     mbar_init(o_full, 1);
     fence_barrier_init();
   }
@@ -170,7 +173,8 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       tmem_ld_32x32(lane_addr + 32, sv + 32);
       tmem_ld_wait();
       tc_fence_before();
-      mbar_arrive(s_free);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(s_free);
       float mx = -INFINITY;
 #pragma unroll
       for (int c = 0; c < 64; ++c) {
@@ -241,7 +245,8 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       }
       fence_proxy_async();
       tc_fence_before();
-      mbar_arrive(p_ready);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_ready);
     }
     mbar_wait(o_full, (uint32_t)((nkt - 1) & 1));
     tc_fence_after();
@@ -275,28 +280,32 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
 // accumulating in TMEM) and streams the query tiles: S and dP are recomputed per pair, the eight element-wise warps turn
 // them into P (dropout applied) and dS once, and three accumulations consume them:
 //     dV_j += P^T.dO_i      dK_j += dS^T.Q_i      dQ_i partial = dS.K_j
-// The dQ partial of the pair goes to an fp32 workspace slice [key tile][row][hidden] (plain stores, no atomics);
-// attn_dq_reduce_kernel adds the key-tile slices in a fixed order, so the result is deterministic.
+// The dQ partial of the pair goes to a bf16 workspace slice [key tile][row][hidden] (plain stores, no atomics; the partials
+// are the largest HBM stream of the backward, fp32 slices cost 90 us of stores per layer at b=32);
+// attn_dq_reduce_kernel adds the key-tile slices in fp32 in a fixed order, so the result is deterministic.
 // Constant factors are kept out of the per-element work: dS is staged without the 1/sqrt(d) and 1/(1-p) factors, P
 // without 1/(1-p); they are applied to the 64-wide outputs.
 // ---------------------------------------------------------------------------------------------
-constexpr int BWD_THREADS = 320;    // warps 0-7 element-wise, warp 8 TMA, warp 9 MMA + TMEM
+constexpr int BWD_EW_WARPS = 16;     // element-wise warps: TMEM quadrant = warp & 3, 32-key column group = warp >> 2
+constexpr int BWD_THREADS = (BWD_EW_WARPS + 2) * 32;  // + TMA warp + MMA / TMEM warp
 constexpr int BWD_TMEM_COLS = 512;  // S [0,128)  dP [128,256)  dK [256,320)  dV [320,384)  dQ partial x2 [384,448) [448,512)
 constexpr int TILE16K = 16384;
-constexpr int BWD_SMEM_TILES = 10 * TILE16K;  // K, V, Q[2], dO[2], dS (2 halves), P (2 halves)
+constexpr int BWD_NST = 4;                     // Q / dO ring depth: a stage is refilled only after the pair that used it has been
+                                               // multiplied, so the ring has to cover the TMA latency plus a pair's MMA time
+constexpr int BWD_SMEM_TILES = (6 + 2 * BWD_NST) * TILE16K;  // K, V, Q[NST], dO[NST], dS (2 halves), P (2 halves)
 
 __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sK = base, sV = base + TILE16K;
-  const uint32_t sQ = base + 2 * TILE16K, sDO = base + 4 * TILE16K;  // 2 stages each
-  const uint32_t sDS = base + 6 * TILE16K;                           // [128 q, 128 k] bf16 as two 64-key halves
-  const uint32_t sPD = base + 8 * TILE16K;
-  const uint32_t bars = base + 10 * TILE16K;
-  const uint32_t out_full = bars, in_full = bars + 8, in_empty = bars + 24, sdp_full = bars + 40, sdp_free = bars + 48, pds_ready = bars + 56,
-                 pds_free = bars + 64, done = bars + 72, dq_full = bars + 80, dq_free = bars + 96, tmem_slot = bars + 112;
-  float* sBias = reinterpret_cast<float*>(smem_raw + (bars + 128 - smem_u32(smem_raw)));
+  const uint32_t sQ = base + 2 * TILE16K, sDO = sQ + BWD_NST * TILE16K;  // BWD_NST stages each
+  const uint32_t sDS = sDO + BWD_NST * TILE16K;                          // [128 q, 128 k] bf16 as two 64-key halves
+  const uint32_t sPD = sDS + 2 * TILE16K;
+  const uint32_t bars = sPD + 2 * TILE16K;
+  const uint32_t out_full = bars, sdp_full = bars + 8, sdp_free = bars + 16, pds_ready = bars + 24, pds_free = bars + 32, done = bars + 40,
+                 dq_full = bars + 48, dq_free = bars + 64, tmem_slot = bars + 80, in_full = bars + 96, in_empty = in_full + 8 * BWD_NST;
+  float* sBias = reinterpret_cast<float*>(smem_raw + (bars + 256 - smem_u32(smem_raw)));
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
@@ -307,22 +316,21 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
   const int row_base = b * S;
   const int hid = p.hidden;
 
-  if (warp == 8 && lane == 0) {
+  if (warp == BWD_EW_WARPS && lane == 0) {
     prefetch_tensormap(&tmQKV);
     prefetch_tensormap(&tmDO);
     mbar_init(out_full, 1);
-    mbar_init(in_full, 1); mbar_init(in_full + 8, 1);
-    mbar_init(in_empty, 1); mbar_init(in_empty + 8, 1);
+    for (int i = 0; i < BWD_NST; ++i) { mbar_init(in_full + 8 * i, 1); mbar_init(in_empty + 8 * i, 1); }
     mbar_init(sdp_full, 1);
-    mbar_init(sdp_free, 256);
-    mbar_init(pds_ready, 256);
+    mbar_init(sdp_free, BWD_EW_WARPS);
+    mbar_init(pds_ready, BWD_EW_WARPS);
     mbar_init(pds_free, 1);
     mbar_init(done, 1);
     mbar_init(dq_full, 1); mbar_init(dq_full + 8, 1);
-    mbar_init(dq_free, 256); mbar_init(dq_free + 8, 256);
+    mbar_init(dq_free, BWD_EW_WARPS); mbar_init(dq_free + 8, BWD_EW_WARPS);
     fence_barrier_init();
   }
-  if (warp == 9) {
+  if (warp == BWD_EW_WARPS + 1) {
     tmem_alloc(tmem_slot, BWD_TMEM_COLS);
     tmem_relinquish();
   }
@@ -335,26 +343,26 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
-  if (warp == 8) {
+  if (warp == BWD_EW_WARPS) {
     if (lane == 0) {
       mbar_arrive_expect_tx(out_full, 2 * TILE16K);
       tma_load_2d(sK, &tmQKV, out_full, hid + h * 64, row_base + kt * 128);
       tma_load_2d(sV, &tmQKV, out_full, 2 * hid + h * 64, row_base + kt * 128);
       for (int t = 0; t < nin; ++t) {
-        const int st = t & 1;
-        if (t >= 2) mbar_wait_backoff(in_empty + 8 * st, (uint32_t)(((t >> 1) - 1) & 1), 128);
+        const int st = t % BWD_NST;
+        if (t >= BWD_NST) mbar_wait_backoff(in_empty + 8 * st, (uint32_t)((t / BWD_NST - 1) & 1), 64);
         mbar_arrive_expect_tx(in_full + 8 * st, 2 * TILE16K);
         tma_load_2d(sQ + st * TILE16K, &tmQKV, in_full + 8 * st, h * 64, row_base + t * 128);
         tma_load_2d(sDO + st * TILE16K, &tmDO, in_full + 8 * st, h * 64, row_base + t * 128);
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == BWD_EW_WARPS + 1) {
     if (lane == 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);
       constexpr uint32_t idesc_t = make_idesc_bf16(128, 64, 1, 1);  // acc[128 keys, 64] += X^T (MN-major A) x Y (MN-major B)
       constexpr uint32_t idesc_q = make_idesc_bf16(128, 64, 0, 1);  // dQ[128 q, 64]    = dS (K-major A) x K (MN-major B)
       auto issue_sdp = [&](int t) {
-        const int st = t & 1;
+        const int st = t % BWD_NST;
         // S = Q.K^T ; dP = dO.V^T   (A: query-side tile, B: key-side tile, both K-major over d = 64)
         const uint64_t qa = make_smem_desc(sQ + st * TILE16K, 16, 1024), kb = make_smem_desc(sK, 16, 1024);
         const uint64_t da = make_smem_desc(sDO + st * TILE16K, 16, 1024), vb = make_smem_desc(sV, 16, 1024);
@@ -370,7 +378,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       issue_sdp(0);
       for (int t = 0; t < nin; ++t) {
         if (t + 1 < nin) {
-          mbar_wait_backoff(in_full + 8 * ((t + 1) & 1), (uint32_t)(((t + 1) >> 1) & 1), 32);
+          mbar_wait_backoff(in_full + 8 * ((t + 1) % BWD_NST), (uint32_t)(((t + 1) / BWD_NST) & 1), 32);
           mbar_wait_backoff(sdp_free, (uint32_t)(t & 1), 32);
           tc_fence_after();
           issue_sdp(t + 1);
@@ -378,30 +386,30 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         mbar_wait_backoff(pds_ready, (uint32_t)(t & 1), 32);
         if (t >= 2) mbar_wait_backoff(dq_free + 8 * (t & 1), (uint32_t)(((t >> 1) - 1) & 1), 32);
         tc_fence_after();
-        const int st = t & 1;
+        const int st = t % BWD_NST, dqb = t & 1;
         // dV += P^T.dO_t ; dK += dS^T.Q_t : A = the [128 q, 128 k] tile read MN-major (M = keys: two 64-key chunks 16 KiB
         // apart, K = query rows 128 B apart), B = dO_t / Q_t read MN-major (K = query rows)
         const uint64_t pa = make_smem_desc(sPD, TILE16K, 1024), sa = make_smem_desc(sDS, TILE16K, 1024);
         const uint64_t dob = make_smem_desc(sDO + st * TILE16K, TILE16K, 1024), qb = make_smem_desc(sQ + st * TILE16K, TILE16K, 1024);
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 320, pa + (uint64_t)(128 * kk), dob + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
+        for (int kk = 0; kk < 8; ++kk) if (!(p.dbg & 1)) umma_bf16(tmem_base + 320, pa + (uint64_t)(128 * kk), dob + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 256, sa + (uint64_t)(128 * kk), qb + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
+        for (int kk = 0; kk < 8; ++kk) if (!(p.dbg & 2)) umma_bf16(tmem_base + 256, sa + (uint64_t)(128 * kk), qb + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
         // dQ_t partial = dS.K_j : A = dS K-major over 128 keys (two 64-key atoms), B = K_j MN-major (K = key rows)
         const uint64_t kmn = make_smem_desc(sK, TILE16K, 1024);
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint64_t dsa = make_smem_desc(sDS + (kk >> 2) * TILE16K + (kk & 3) * 32, 16, 1024);
-          umma_bf16(tmem_base + 384 + 64 * st, dsa, kmn + (uint64_t)(128 * kk), idesc_q, kk > 0 ? 1u : 0u);
+          if (!(p.dbg & 4)) umma_bf16(tmem_base + 384 + 64 * dqb, dsa, kmn + (uint64_t)(128 * kk), idesc_q, kk > 0 ? 1u : 0u);
         }
         umma_commit(pds_free);
         umma_commit(in_empty + 8 * st);
-        umma_commit(dq_full + 8 * st);
+        umma_commit(dq_full + 8 * dqb);
       }
       umma_commit(done);
     }
   } else {
-    const int quad = warp & 3, half = warp >> 2;
+    const int quad = warp & 3, cq = warp >> 2;    // rows [32 quad, +32) of the tile, key columns [32 cq, +32)
     const int r = quad * 32 + lane;               // query row within the tile
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
     const uint32_t bh = (uint32_t)(b * p.heads + h);
@@ -410,72 +418,86 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
     const float dscale = drop ? p.drop.scale : 1.0f;
     const float inv_dscale = 1.0f / dscale;
     const uint32_t thi = p.drop.thresh16 << 16;   // 0 without dropout: every unsigned lane compares >= 0, i.e. is kept
-    const float* bias = sBias + half * 64;
-    float* ws = p.dq_ws + ((long long)kt * p.B * S + row_base) * hid + h * 64 + 32 * half;  // this key tile's slice of the dQ workspace
+    const float* bias = sBias + cq * 32;
+    // this warp's 16 of the 64 dQ columns in this key tile's slice of the workspace
+    bf16* ws = p.dq_ws + ((long long)kt * p.B * S + row_base) * hid + h * 64 + 16 * cq;
+    const uint32_t st_off = (uint32_t)(cq >> 1) * TILE16K + (uint32_t)r * 128u;  // row r of the 64-key half this group lies in
+    const uint32_t ch0 = (uint32_t)(cq & 1) * 4u;                                 // first 16-byte chunk of the group in that row
 
-    auto drain_dq = [&](int t) {  // dQ partial of query tile t: TMEM -> workspace (this warp: 32 rows x 32 of the 64 columns)
+    auto drain_dq = [&](int t) {  // dQ partial of query tile t: TMEM -> workspace
       const int st = t & 1;
       mbar_wait(dq_full + 8 * st, (uint32_t)((t >> 1) & 1));
       tc_fence_after();
-      uint32_t a[32];
-      tmem_ld_32x32(lane_addr + 384 + 64 * st + 32 * half, a);
+      uint32_t a[16];
+      tmem_ld_32x16(lane_addr + 384 + 64 * st + 16 * cq, a);
       tmem_ld_wait();
       tc_fence_before();
-      mbar_arrive(dq_free + 8 * st);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(dq_free + 8 * st);
       const int gi = t * 128 + r;
-      if (gi < S) {
-        float4* d = reinterpret_cast<float4*>(ws + (long long)gi * hid);
+      if (gi < S && !(p.dbg & 16)) {
+        uint4* d = reinterpret_cast<uint4*>(ws + (long long)gi * hid);  // 32 bytes per lane: one whole sector
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          d[j] = make_float4(__uint_as_float(a[4 * j]), __uint_as_float(a[4 * j + 1]), __uint_as_float(a[4 * j + 2]), __uint_as_float(a[4 * j + 3]));
+        for (int j = 0; j < 2; ++j) {
+          float f[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(a[8 * j + e]);
+          d[j] = pack8(f);
+        }
       }
     };
+    auto load_stats = [&](int t, float2& lse, float& ds) {
+      const int gc = min(t * 128 + r, S - 1);
+      lse = *reinterpret_cast<const float2*>(p.lse + 2 * (stat_base + gc));
+      ds = p.dsum[stat_base + gc];
+    };
 
+    float2 lse_n;
+    float dsum_n;
+    load_stats(0, lse_n, dsum_n);
     for (int t = 0; t < nin; ++t) {
       const int gi = t * 128 + r;
-      const int gc = min(gi, S - 1);
-      const float2 lse = *reinterpret_cast<const float2*>(p.lse + 2 * (stat_base + gc));
-      const float dsp = p.dsum[stat_base + gc] * inv_dscale;
+      const float2 lse = lse_n;
+      const float dsp = dsum_n * inv_dscale;
+      if (t + 1 < nin) load_stats(t + 1, lse_n, dsum_n);  // a tile ahead: the loads are off the critical path
       // P = exp2(v log2e - mb) / sum with mb rounded exactly as in the forward (the F6 mask bias of 2.54e6 leaves 0.25 ulp:
       // any other rounding of the reference point would rescale the whole row); rows past the end of the sample get P = dS = 0
       const float mb = lse.x * kLog2e;
       const float inv = gi < S ? lse.y : 0.f;
       mbar_wait(sdp_full, (uint32_t)(t & 1));
       tc_fence_after();
-      uint32_t sv[64], dv[64];
-      tmem_ld_32x32(lane_addr + half * 64, sv);
-      tmem_ld_32x32(lane_addr + half * 64 + 32, sv + 32);
-      tmem_ld_32x32(lane_addr + 128 + half * 64, dv);
-      tmem_ld_32x32(lane_addr + 128 + half * 64 + 32, dv + 32);
+      uint32_t sv[32], dv[32];
+      tmem_ld_32x32(lane_addr + cq * 32, sv);
+      tmem_ld_32x32(lane_addr + 128 + cq * 32, dv);
       tmem_ld_wait();
       tc_fence_before();
-      mbar_arrive(sdp_free);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(sdp_free);
 #pragma unroll
-      for (int g = 0; g < 2; ++g) {
+      if (!(p.dbg & 8))
 #pragma unroll
-        for (uint32_t tt = 0; tt < 4; ++tt) {
-          uint4 rr = make_uint4(0u, 0u, 0u, 0u);
-          if (drop) rr = attn_dropout_rand(p.drop, bh, (uint32_t)gi, (uint32_t)(kt * 4 + half * 2 + g), tt);
-          const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
+      for (uint32_t tt = 0; tt < 4; ++tt) {
+        uint4 rr = make_uint4(0u, 0u, 0u, 0u);
+        if (drop && !(p.dbg & 32)) rr = attn_dropout_rand(p.drop, bh, (uint32_t)gi, (uint32_t)(kt * 4 + cq), tt);
+        const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < 4; ++q) {
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              const int cc = 32 * g + 8 * q + 2 * (int)tt + e;
-              const float v = fmaf(__uint_as_float(sv[cc]), p.scale, bias[cc]);
-              const float pr = ex2_approx(fmaf(v, kLog2e, -mb)) * inv;
-              const bool keep = e == 0 ? ((w[q] << 16) >= thi) : (w[q] >= thi);
-              const float dpm = keep ? __uint_as_float(dv[cc]) : 0.f;
-              sv[cc] = __float_as_uint(keep ? pr : 0.f);
-              dv[cc] = __float_as_uint(pr * (dpm - dsp));
-            }
+          for (int e = 0; e < 2; ++e) {
+            const int cc = 8 * q + 2 * (int)tt + e;
+            const float v = fmaf(__uint_as_float(sv[cc]), p.scale, bias[cc]);
+            const float pr = ex2_approx(fmaf(v, kLog2e, -mb)) * inv;
+            const bool keep = e == 0 ? ((w[q] << 16) >= thi) : (w[q] >= thi);
+            const float dpm = keep ? __uint_as_float(dv[cc]) : 0.f;
+            sv[cc] = __float_as_uint(keep ? pr : 0.f);
+            dv[cc] = __float_as_uint(pr * (dpm - dsp));
           }
         }
       }
       if (t > 0) mbar_wait(pds_free, (uint32_t)((t - 1) & 1));
 #pragma unroll
-      for (int ch = 0; ch < 8; ++ch) {
-        const uint32_t off = (uint32_t)half * TILE16K + r * 128 + (((uint32_t)ch ^ (uint32_t)(r & 7)) << 4);
+      for (uint32_t ch = 0; ch < 4; ++ch) {
+        const uint32_t off = st_off + (((ch0 + ch) ^ (uint32_t)(r & 7)) << 4);
         st_shared_v4(sDS + off, pack_bf16(__uint_as_float(dv[8 * ch]), __uint_as_float(dv[8 * ch + 1])),
                      pack_bf16(__uint_as_float(dv[8 * ch + 2]), __uint_as_float(dv[8 * ch + 3])),
                      pack_bf16(__uint_as_float(dv[8 * ch + 4]), __uint_as_float(dv[8 * ch + 5])),
@@ -487,48 +509,42 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       }
       fence_proxy_async();
       tc_fence_before();
-      mbar_arrive(pds_ready);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pds_ready);
       if (t > 0) drain_dq(t - 1);  // while the MMA warp works on this pair
     }
     drain_dq(nin - 1);
     mbar_wait(done, 0);
     tc_fence_after();
-    // dK / dV accumulators -> global: row = key; this warp takes columns [32*half, +32)
+    // dK / dV accumulators -> global: row = key; this warp takes columns [16 cq, +16)
     const int go = kt * 128 + r;
     const float fk = p.scale * dscale, fv = dscale;
-    uint32_t a0[32];
-    tmem_ld_32x32(lane_addr + 256 + 32 * half, a0);
-    tmem_ld_wait();
-    bf16* row = p.dqkv + ((long long)row_base + go) * p.ld + h * 64 + 32 * half;
-    if (go < S) {
+    bf16* row = p.dqkv + ((long long)row_base + go) * p.ld + h * 64 + 16 * cq;
 #pragma unroll
-      for (int ch = 0; ch < 4; ++ch) {
-        float f[8];
+    for (int which = 0; which < 2; ++which) {
+      uint32_t a0[16];
+      tmem_ld_32x16(lane_addr + 256 + 64 * which + 16 * cq, a0);
+      tmem_ld_wait();
+      if (go < S) {
+        const float f0 = which ? fv : fk;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(a0[8 * ch + e]) * fk;
-        *reinterpret_cast<uint4*>(row + hid + 8 * ch) = pack8(f);
-      }
-    }
-    tmem_ld_32x32(lane_addr + 320 + 32 * half, a0);
-    tmem_ld_wait();
-    if (go < S) {
+        for (int ch = 0; ch < 2; ++ch) {
+          float f[8];
 #pragma unroll
-      for (int ch = 0; ch < 4; ++ch) {
-        float f[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(a0[8 * ch + e]) * fv;
-        *reinterpret_cast<uint4*>(row + 2 * hid + 8 * ch) = pack8(f);
+          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(a0[8 * ch + e]) * f0;
+          *reinterpret_cast<uint4*>(row + (which + 1) * hid + 8 * ch) = pack8(f);
+        }
       }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) tmem_dealloc(tmem_base, BWD_TMEM_COLS);
+  if (warp == BWD_EW_WARPS + 1) tmem_dealloc(tmem_base, BWD_TMEM_COLS);
 }
 
 // dQ[row, c] = factor * sum over key tiles of the workspace slices, in key-tile order (deterministic) -> bf16 into dqkv[:, 0:hidden]
 __global__ void __launch_bounds__(256)
-attn_dq_reduce_kernel(const float* __restrict__ ws, long long slice, int nkt, long long rows, int hidden, float factor, bf16* __restrict__ dqkv,
+attn_dq_reduce_kernel(const bf16* __restrict__ ws, long long slice, int nkt, long long rows, int hidden, float factor, bf16* __restrict__ dqkv,
                       long long ld) {
   const long long per_row = hidden / 8;
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
@@ -537,10 +553,10 @@ attn_dq_reduce_kernel(const float* __restrict__ ws, long long slice, int nkt, lo
   const int c = (int)(i % per_row) * 8;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   for (int k = 0; k < nkt; ++k) {
-    const float4* src = reinterpret_cast<const float4*>(ws + k * slice + row * hidden + c);
-    const float4 x = __ldcs(src), y = __ldcs(src + 1);
-    acc[0] += x.x; acc[1] += x.y; acc[2] += x.z; acc[3] += x.w;
-    acc[4] += y.x; acc[5] += y.y; acc[6] += y.z; acc[7] += y.w;
+    float f[8];
+    unpack8(__ldcs(reinterpret_cast<const uint4*>(ws + k * slice + row * hidden + c)), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] += f[j];
   }
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] *= factor;
@@ -557,7 +573,7 @@ extern "C" void vt_debug_attention_impl(int impl) { vt::g_attn_impl = impl; }
 
 extern "C" int64_t vt_attention_bwd_workspace(int64_t B, int64_t S, int64_t heads) {
   const int64_t dsum_floats = (B * heads * S + 3) & ~(int64_t)3;
-  return dsum_floats + ((S + 127) / 128) * B * S * heads * 64;
+  return dsum_floats + ((S + 127) / 128) * B * S * heads * 64 / 2;  // the dQ partials are bf16
 }
 
 static int check_attn_tc(const char* who, const void* qkv, int64_t ld, int64_t B, int64_t S, int64_t heads, int64_t head_dim) {
@@ -625,14 +641,15 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
   const int nt = (int)((S + 127) / 128);
   // workspace: [B, heads, S] rowsum(dO.O), then the dQ partial slices [key tiles][B*S][hidden] (16-byte aligned)
   const size_t dsum_floats = ((size_t)(B * heads * S) + 3) & ~(size_t)3;
-  p.bias = bias; p.scale = 0.125f; p.lse = const_cast<float*>(lse); p.dsum = dsum_ws; p.dq_ws = dsum_ws + dsum_floats;
+  p.bias = bias; p.scale = 0.125f; p.lse = const_cast<float*>(lse); p.dsum = dsum_ws; p.dq_ws = reinterpret_cast<bf16*>(dsum_ws + dsum_floats);
   p.dqkv = (bf16*)dqkv; p.ld = ld;
   p.drop = make_dropout(dropout_p, seed, dropout_stream);
+  { const char* e = getenv("VT_ATTN_DBG"); p.dbg = e ? atoi(e) : 0; }
   VT_REQUIRE(((uintptr_t)dsum_ws & 15) == 0, "vt_attention_bwd: workspace must be 16-byte aligned");
-  const size_t smem = 1024 + BWD_SMEM_TILES + 128 + 128 * sizeof(float);
+  const size_t smem = 1024 + BWD_SMEM_TILES + 256 + 128 * sizeof(float);
   static bool attr = false;
   if (!attr) {
-    VT_CUDA(cudaFuncSetAttribute(attn_bwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(1024 + BWD_SMEM_TILES + 128 + 512)));
+    VT_CUDA(cudaFuncSetAttribute(attn_bwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(1024 + BWD_SMEM_TILES + 256 + 512)));
     attr = true;
   }
   const dim3 grid((unsigned)nt, (unsigned)heads, (unsigned)B);
