@@ -1,1 +1,1 @@
-for d in 0 1 2 4 7 8 16 32 40 47 63; do echo -n "dbg=$d "; VT_ATTN_DBG=$d python tools/kernel_cases.py --only "attn bwd" 2>&1 | grep "attn bwd" | awk '{print $(NF-3), $(NF-2)}'; done
+for d in 0 511; do echo -n "dbg=$d "; VT_ATTN_DBG=$d python tools/kernel_cases.py --only "attn" 2>&1 | grep "attn [fb]" | cut -c1-8,60- | tr "\n" " "; echo; done

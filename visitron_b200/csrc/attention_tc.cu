@@ -34,6 +34,7 @@ int attention_bwd_legacy(const void* qkv, int64_t ld, const float* bias, const v
                          cudaStream_t st);
 int attention_bwd_prep(const void* dctx, const void* ctx, float* dsum, int64_t B, int64_t S, int64_t heads, cudaStream_t st);
 
+constexpr uint32_t MMA_POLL_NS = 0;  // the MMA-issuing lane spins: a nanosleep here sits on the critical path of every tile
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kRescaleTau = 5.545177444f;  // ln(2^8): rescale O only when the row max grew by more than this
 
@@ -48,7 +49,6 @@ struct AttnTcParams {
   bf16* dqkv;          // [B*S, ld]
   long long ld;
   DropoutCfg drop;
-  int dbg;             // timing experiments only (VT_ATTN_DBG): bit mask of pipeline pieces to skip
 };
 
 // keep-bits of 32 consecutive key columns [32*jgroup, +32) of query row i (bit c = column 32*jgroup + c),
@@ -138,18 +138,18 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         for (int k = 0; k < 4; ++k) umma_bf16(tmem_base, a + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc_s, k > 0 ? 1u : 0u);
         umma_commit(s_full);
       };
-      mbar_wait_backoff(q_full, 0, 32);
-      mbar_wait_backoff(kv_full, 0, 32);
+      mbar_wait_backoff(q_full, 0, MMA_POLL_NS);
+      mbar_wait_backoff(kv_full, 0, MMA_POLL_NS);
       tc_fence_after();
       issue_s(0);
       for (int j = 0; j < nkt; ++j) {
         if (j + 1 < nkt) {
-          mbar_wait_backoff(kv_full + 8 * ((j + 1) & 1), (uint32_t)(((j + 1) >> 1) & 1), 32);
-          mbar_wait_backoff(s_free, (uint32_t)(j & 1), 32);
+          mbar_wait_backoff(kv_full + 8 * ((j + 1) & 1), (uint32_t)(((j + 1) >> 1) & 1), MMA_POLL_NS);
+          mbar_wait_backoff(s_free, (uint32_t)(j & 1), MMA_POLL_NS);
           tc_fence_after();
           issue_s(j + 1);
         }
-        mbar_wait_backoff(p_ready, (uint32_t)(j & 1), 32);
+        mbar_wait_backoff(p_ready, (uint32_t)(j & 1), MMA_POLL_NS);
         tc_fence_after();
         const uint64_t a = make_smem_desc(sP, 16, 1024), bd = make_smem_desc(sV + (j & 1) * 8192, 8192, 1024);
 #pragma unroll
@@ -290,42 +290,47 @@ constexpr int BWD_EW_WARPS = 16;     // element-wise warps: TMEM quadrant = warp
 constexpr int BWD_THREADS = (BWD_EW_WARPS + 2) * 32;  // + TMA warp + MMA / TMEM warp
 constexpr int BWD_TMEM_COLS = 512;  // S [0,128)  dP [128,256)  dK [256,320)  dV [320,384)  dQ partial x2 [384,448) [448,512)
 constexpr int TILE16K = 16384;
-constexpr int BWD_NST = 4;                     // Q / dO ring depth: a stage is refilled only after the pair that used it has been
-                                               // multiplied, so the ring has to cover the TMA latency plus a pair's MMA time
-constexpr int BWD_SMEM_TILES = (6 + 2 * BWD_NST) * TILE16K;  // K, V, Q[NST], dO[NST], dS (2 halves), P (2 halves)
+constexpr int BWD_NST = 3;          // Q / dO ring depth
+constexpr int BWD_SMEM_TILES = (8 + 2 * BWD_NST) * TILE16K;  // K[2], V[2], Q[NST], dO[NST], dS (2 halves), P (2 halves)
 
+// The kernel is PERSISTENT: one CTA per SM walks the (key tile, head, sample) items round-robin.  A CTA needs all 512
+// TMEM columns and 224 KB of shared memory, so two cannot share an SM; as one-item CTAs the launch, TMEM allocation and the
+// cold K / V / Q / dO loads of every item (~8k cycles for ~12k of work) were exposed.  Here the TMA warp runs ahead across
+// item boundaries (K / V double-buffered), so the next item's operands are resident when the current one drains.
 __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sK = base, sV = base + TILE16K;
-  const uint32_t sQ = base + 2 * TILE16K, sDO = sQ + BWD_NST * TILE16K;  // BWD_NST stages each
+  const uint32_t sK = base, sV = base + 2 * TILE16K;                      // 2 buffers each (item parity)
+  const uint32_t sQ = base + 4 * TILE16K, sDO = sQ + BWD_NST * TILE16K;  // BWD_NST stages each
   const uint32_t sDS = sDO + BWD_NST * TILE16K;                          // [128 q, 128 k] bf16 as two 64-key halves
   const uint32_t sPD = sDS + 2 * TILE16K;
   const uint32_t bars = sPD + 2 * TILE16K;
-  const uint32_t out_full = bars, sdp_full = bars + 8, sdp_free = bars + 16, pds_ready = bars + 24, pds_free = bars + 32, done = bars + 40,
-                 dq_full = bars + 48, dq_free = bars + 64, tmem_slot = bars + 80, in_full = bars + 96, in_empty = in_full + 8 * BWD_NST;
-  float* sBias = reinterpret_cast<float*>(smem_raw + (bars + 256 - smem_u32(smem_raw)));
+  const uint32_t sdp_full = bars, sdp_free = bars + 8, pds_ready = bars + 16, pds_free = bars + 24, acc_full = bars + 32, acc_free = bars + 40,
+                 dq_full = bars + 48, dq_free = bars + 64, tmem_slot = bars + 80, kv_full = bars + 96, kv_empty = bars + 112,
+                 in_full = bars + 128, in_empty = in_full + 8 * BWD_NST;
+  float* sBias = reinterpret_cast<float*>(smem_raw + (bars + 256 - smem_u32(smem_raw)));  // [2][128]
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int S = p.S;
-  const int nin = (S + 127) / 128;
-  const int row_base = b * S;
+  const int nin = (S + 127) / 128;       // query tiles of a sample == key tiles of a sample
   const int hid = p.hidden;
+  const int n_items = nin * p.heads * p.B;
+  auto decode = [&](int id, int& kt, int& h, int& b) { kt = id % nin; h = (id / nin) % p.heads; b = id / (nin * p.heads); };
 
   if (warp == BWD_EW_WARPS && lane == 0) {
     prefetch_tensormap(&tmQKV);
     prefetch_tensormap(&tmDO);
-    mbar_init(out_full, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(kv_full + 8 * i, 1); mbar_init(kv_empty + 8 * i, 1); }
     for (int i = 0; i < BWD_NST; ++i) { mbar_init(in_full + 8 * i, 1); mbar_init(in_empty + 8 * i, 1); }
     mbar_init(sdp_full, 1);
     mbar_init(sdp_free, BWD_EW_WARPS);
     mbar_init(pds_ready, BWD_EW_WARPS);
     mbar_init(pds_free, 1);
-    mbar_init(done, 1);
+    mbar_init(acc_full, 1);
+    mbar_init(acc_free, BWD_EW_WARPS);
     mbar_init(dq_full, 1); mbar_init(dq_full + 8, 1);
     mbar_init(dq_free, BWD_EW_WARPS); mbar_init(dq_free + 8, BWD_EW_WARPS);
     fence_barrier_init();
@@ -334,109 +339,123 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
     tmem_alloc(tmem_slot, BWD_TMEM_COLS);
     tmem_relinquish();
   }
-  for (int j = threadIdx.x; j < 128; j += BWD_THREADS) {
-    const int k = kt * 128 + j;
-    sBias[j] = k < S ? p.bias[(long long)b * S + k] : -INFINITY;
-  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
   if (warp == BWD_EW_WARPS) {
+    // ---------------- TMA producer ----------------
     if (lane == 0) {
-      mbar_arrive_expect_tx(out_full, 2 * TILE16K);
-      tma_load_2d(sK, &tmQKV, out_full, hid + h * 64, row_base + kt * 128);
-      tma_load_2d(sV, &tmQKV, out_full, 2 * hid + h * 64, row_base + kt * 128);
-      for (int t = 0; t < nin; ++t) {
-        const int st = t % BWD_NST;
-        if (t >= BWD_NST) mbar_wait_backoff(in_empty + 8 * st, (uint32_t)((t / BWD_NST - 1) & 1), 64);
-        mbar_arrive_expect_tx(in_full + 8 * st, 2 * TILE16K);
-        tma_load_2d(sQ + st * TILE16K, &tmQKV, in_full + 8 * st, h * 64, row_base + t * 128);
-        tma_load_2d(sDO + st * TILE16K, &tmDO, in_full + 8 * st, h * 64, row_base + t * 128);
+      int n = 0, it = 0;
+      for (int id = blockIdx.x; id < n_items; id += gridDim.x, ++it) {
+        int kt, h, b;
+        decode(id, kt, h, b);
+        const int row_base = b * S, kvb = it & 1;
+        if (it >= 2) mbar_wait_backoff(kv_empty + 8 * kvb, (uint32_t)(((it >> 1) - 1) & 1), 64);
+        mbar_arrive_expect_tx(kv_full + 8 * kvb, 2 * TILE16K);
+        tma_load_2d(sK + kvb * TILE16K, &tmQKV, kv_full + 8 * kvb, hid + h * 64, row_base + kt * 128);
+        tma_load_2d(sV + kvb * TILE16K, &tmQKV, kv_full + 8 * kvb, 2 * hid + h * 64, row_base + kt * 128);
+        for (int t = 0; t < nin; ++t, ++n) {
+          const int st = n % BWD_NST;
+          if (n >= BWD_NST) mbar_wait_backoff(in_empty + 8 * st, (uint32_t)((n / BWD_NST - 1) & 1), 64);
+          mbar_arrive_expect_tx(in_full + 8 * st, 2 * TILE16K);
+          tma_load_2d(sQ + st * TILE16K, &tmQKV, in_full + 8 * st, h * 64, row_base + t * 128);
+          tma_load_2d(sDO + st * TILE16K, &tmDO, in_full + 8 * st, h * 64, row_base + t * 128);
+        }
       }
     }
   } else if (warp == BWD_EW_WARPS + 1) {
+    // ---------------- MMA issuer ----------------
     if (lane == 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);
       constexpr uint32_t idesc_t = make_idesc_bf16(128, 64, 1, 1);  // acc[128 keys, 64] += X^T (MN-major A) x Y (MN-major B)
       constexpr uint32_t idesc_q = make_idesc_bf16(128, 64, 0, 1);  // dQ[128 q, 64]    = dS (K-major A) x K (MN-major B)
-      auto issue_sdp = [&](int t) {
-        const int st = t % BWD_NST;
+      const int my_items = n_items > (int)blockIdx.x ? (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+      const int n_pairs = my_items * nin;
+      // pair n of this CTA: item n / nin (K / V buffer (n / nin) & 1), query tile n % nin, ring stage n % BWD_NST
+      auto issue_sdp = [&](int n) {
+        const int st = n % BWD_NST, kvb = (n / nin) & 1;
         // S = Q.K^T ; dP = dO.V^T   (A: query-side tile, B: key-side tile, both K-major over d = 64)
-        const uint64_t qa = make_smem_desc(sQ + st * TILE16K, 16, 1024), kb = make_smem_desc(sK, 16, 1024);
-        const uint64_t da = make_smem_desc(sDO + st * TILE16K, 16, 1024), vb = make_smem_desc(sV, 16, 1024);
+        const uint64_t qa = make_smem_desc(sQ + st * TILE16K, 16, 1024), kb = make_smem_desc(sK + kvb * TILE16K, 16, 1024);
+        const uint64_t da = make_smem_desc(sDO + st * TILE16K, 16, 1024), vb = make_smem_desc(sV + kvb * TILE16K, 16, 1024);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) umma_bf16(tmem_base, qa + (uint64_t)(2 * kk), kb + (uint64_t)(2 * kk), idesc_s, kk > 0 ? 1u : 0u);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) umma_bf16(tmem_base + 128, da + (uint64_t)(2 * kk), vb + (uint64_t)(2 * kk), idesc_s, kk > 0 ? 1u : 0u);
         umma_commit(sdp_full);
       };
-      mbar_wait_backoff(out_full, 0, 32);
-      mbar_wait_backoff(in_full, 0, 32);
-      tc_fence_after();
-      issue_sdp(0);
-      for (int t = 0; t < nin; ++t) {
-        if (t + 1 < nin) {
-          mbar_wait_backoff(in_full + 8 * ((t + 1) % BWD_NST), (uint32_t)(((t + 1) / BWD_NST) & 1), 32);
-          mbar_wait_backoff(sdp_free, (uint32_t)(t & 1), 32);
-          tc_fence_after();
-          issue_sdp(t + 1);
-        }
-        mbar_wait_backoff(pds_ready, (uint32_t)(t & 1), 32);
-        if (t >= 2) mbar_wait_backoff(dq_free + 8 * (t & 1), (uint32_t)(((t >> 1) - 1) & 1), 32);
+      if (n_pairs > 0) {
+        mbar_wait_backoff(kv_full, 0, MMA_POLL_NS);
+        mbar_wait_backoff(in_full, 0, MMA_POLL_NS);
         tc_fence_after();
-        const int st = t % BWD_NST, dqb = t & 1;
+        issue_sdp(0);
+      }
+      for (int n = 0; n < n_pairs; ++n) {
+        const int it = n / nin, t = n % nin, kvb = it & 1;
+        if (n + 1 < n_pairs) {
+          const int it1 = (n + 1) / nin;
+          if ((n + 1) % nin == 0) mbar_wait_backoff(kv_full + 8 * (it1 & 1), (uint32_t)((it1 >> 1) & 1), MMA_POLL_NS);
+          mbar_wait_backoff(in_full + 8 * ((n + 1) % BWD_NST), (uint32_t)(((n + 1) / BWD_NST) & 1), MMA_POLL_NS);
+          mbar_wait_backoff(sdp_free, (uint32_t)(n & 1), MMA_POLL_NS);
+          tc_fence_after();
+          issue_sdp(n + 1);
+        }
+        mbar_wait_backoff(pds_ready, (uint32_t)(n & 1), MMA_POLL_NS);
+        if (n >= 2) mbar_wait_backoff(dq_free + 8 * (n & 1), (uint32_t)(((n >> 1) - 1) & 1), MMA_POLL_NS);
+        if (t == 0 && it > 0) mbar_wait_backoff(acc_free, (uint32_t)((it - 1) & 1), MMA_POLL_NS);  // dK / dV of the previous item read out
+        tc_fence_after();
+        const int st = n % BWD_NST, dqb = n & 1;
         // dV += P^T.dO_t ; dK += dS^T.Q_t : A = the [128 q, 128 k] tile read MN-major (M = keys: two 64-key chunks 16 KiB
         // apart, K = query rows 128 B apart), B = dO_t / Q_t read MN-major (K = query rows)
         const uint64_t pa = make_smem_desc(sPD, TILE16K, 1024), sa = make_smem_desc(sDS, TILE16K, 1024);
         const uint64_t dob = make_smem_desc(sDO + st * TILE16K, TILE16K, 1024), qb = make_smem_desc(sQ + st * TILE16K, TILE16K, 1024);
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) if (!(p.dbg & 1)) umma_bf16(tmem_base + 320, pa + (uint64_t)(128 * kk), dob + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
+        for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 320, pa + (uint64_t)(128 * kk), dob + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) if (!(p.dbg & 2)) umma_bf16(tmem_base + 256, sa + (uint64_t)(128 * kk), qb + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
+        for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 256, sa + (uint64_t)(128 * kk), qb + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
         // dQ_t partial = dS.K_j : A = dS K-major over 128 keys (two 64-key atoms), B = K_j MN-major (K = key rows)
-        const uint64_t kmn = make_smem_desc(sK, TILE16K, 1024);
+        const uint64_t kmn = make_smem_desc(sK + kvb * TILE16K, TILE16K, 1024);
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint64_t dsa = make_smem_desc(sDS + (kk >> 2) * TILE16K + (kk & 3) * 32, 16, 1024);
-          if (!(p.dbg & 4)) umma_bf16(tmem_base + 384 + 64 * dqb, dsa, kmn + (uint64_t)(128 * kk), idesc_q, kk > 0 ? 1u : 0u);
+          umma_bf16(tmem_base + 384 + 64 * dqb, dsa, kmn + (uint64_t)(128 * kk), idesc_q, kk > 0 ? 1u : 0u);
         }
         umma_commit(pds_free);
         umma_commit(in_empty + 8 * st);
         umma_commit(dq_full + 8 * dqb);
+        if (t == nin - 1) {
+          umma_commit(acc_full);
+          umma_commit(kv_empty + 8 * kvb);
+        }
       }
-      umma_commit(done);
     }
   } else {
+    // ---------------- element-wise warps ----------------
     const int quad = warp & 3, cq = warp >> 2;    // rows [32 quad, +32) of the tile, key columns [32 cq, +32)
     const int r = quad * 32 + lane;               // query row within the tile
+    const int ew_tid = (int)threadIdx.x;          // 0 .. 511
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
-    const uint32_t bh = (uint32_t)(b * p.heads + h);
-    const long long stat_base = ((long long)b * p.heads + h) * S;
     const bool drop = p.drop.thresh16 != 0;
     const float dscale = drop ? p.drop.scale : 1.0f;
     const float inv_dscale = 1.0f / dscale;
     const uint32_t thi = p.drop.thresh16 << 16;   // 0 without dropout: every unsigned lane compares >= 0, i.e. is kept
-    const float* bias = sBias + cq * 32;
-    // this warp's 16 of the 64 dQ columns in this key tile's slice of the workspace
-    bf16* ws = p.dq_ws + ((long long)kt * p.B * S + row_base) * hid + h * 64 + 16 * cq;
     const uint32_t st_off = (uint32_t)(cq >> 1) * TILE16K + (uint32_t)r * 128u;  // row r of the 64-key half this group lies in
     const uint32_t ch0 = (uint32_t)(cq & 1) * 4u;                                 // first 16-byte chunk of the group in that row
 
-    auto drain_dq = [&](int t) {  // dQ partial of query tile t: TMEM -> workspace
-      const int st = t & 1;
-      mbar_wait(dq_full + 8 * st, (uint32_t)((t >> 1) & 1));
+    // dQ partial of pair n: TMEM -> workspace (this warp: 32 rows x 16 of the 64 columns; 32 bytes per lane = one sector)
+    auto drain_dq = [&](int n, bf16* dst) {
+      const int dqb = n & 1;
+      mbar_wait(dq_full + 8 * dqb, (uint32_t)((n >> 1) & 1));
       tc_fence_after();
       uint32_t a[16];
-      tmem_ld_32x16(lane_addr + 384 + 64 * st + 16 * cq, a);
+      tmem_ld_32x16(lane_addr + 384 + 64 * dqb + 16 * cq, a);
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(dq_free + 8 * st);
-      const int gi = t * 128 + r;
-      if (gi < S && !(p.dbg & 16)) {
-        uint4* d = reinterpret_cast<uint4*>(ws + (long long)gi * hid);  // 32 bytes per lane: one whole sector
+      if (lane == 0) mbar_arrive(dq_free + 8 * dqb);
+      if (dst) {
+        uint4* d = reinterpret_cast<uint4*>(dst);
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
           float f[8];
@@ -446,96 +465,116 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         }
       }
     };
-    auto load_stats = [&](int t, float2& lse, float& ds) {
-      const int gc = min(t * 128 + r, S - 1);
-      lse = *reinterpret_cast<const float2*>(p.lse + 2 * (stat_base + gc));
-      ds = p.dsum[stat_base + gc];
-    };
 
-    float2 lse_n;
-    float dsum_n;
-    load_stats(0, lse_n, dsum_n);
-    for (int t = 0; t < nin; ++t) {
-      const int gi = t * 128 + r;
-      const float2 lse = lse_n;
-      const float dsp = dsum_n * inv_dscale;
-      if (t + 1 < nin) load_stats(t + 1, lse_n, dsum_n);  // a tile ahead: the loads are off the critical path
-      // P = exp2(v log2e - mb) / sum with mb rounded exactly as in the forward (the F6 mask bias of 2.54e6 leaves 0.25 ulp:
-      // any other rounding of the reference point would rescale the whole row); rows past the end of the sample get P = dS = 0
-      const float mb = lse.x * kLog2e;
-      const float inv = gi < S ? lse.y : 0.f;
-      mbar_wait(sdp_full, (uint32_t)(t & 1));
-      tc_fence_after();
-      uint32_t sv[32], dv[32];
-      tmem_ld_32x32(lane_addr + cq * 32, sv);
-      tmem_ld_32x32(lane_addr + 128 + cq * 32, dv);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(sdp_free);
+    int n = 0, it = 0;
+    bf16* pend = nullptr;  // where the dQ partial of pair n - 1 goes (null: row past the end of the sample)
+    for (int id = blockIdx.x; id < n_items; id += gridDim.x, ++it) {
+      int kt, h, b;
+      decode(id, kt, h, b);
+      const int row_base = b * S;
+      const uint32_t bh = (uint32_t)(b * p.heads + h);
+      const long long stat_base = ((long long)b * p.heads + h) * S;
+      float* sB = sBias + (it & 1) * 128;
+      if (ew_tid < 128) {
+        const int k = kt * 128 + ew_tid;
+        sB[ew_tid] = k < S ? p.bias[(long long)b * S + k] : -INFINITY;
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(BWD_EW_WARPS * 32) : "memory");  // element-wise warps only
+      const float* bias = sB + cq * 32;
+      // this warp's 16 of the 64 dQ columns in this key tile's slice of the workspace
+      bf16* ws = p.dq_ws + ((long long)kt * p.B * S + row_base) * hid + h * 64 + 16 * cq;
+      auto load_stats = [&](int t, float2& lse, float& ds) {
+        const int gc = min(t * 128 + r, S - 1);
+        lse = *reinterpret_cast<const float2*>(p.lse + 2 * (stat_base + gc));
+        ds = p.dsum[stat_base + gc];
+      };
+      float2 lse_n;
+      float dsum_n;
+      load_stats(0, lse_n, dsum_n);
+      for (int t = 0; t < nin; ++t, ++n) {
+        const int gi = t * 128 + r;
+        const float2 lse = lse_n;
+        const float dsp = dsum_n * inv_dscale;
+        if (t + 1 < nin) load_stats(t + 1, lse_n, dsum_n);  // a tile ahead: the loads are off the critical path
+        // P = exp2(v log2e - mb) / sum with mb rounded exactly as in the forward (the F6 mask bias of 2.54e6 leaves 0.25 ulp:
+        // any other rounding of the reference point would rescale the whole row); rows past the end of the sample get P = dS = 0
+        const float mb = lse.x * kLog2e;
+        const float inv = gi < S ? lse.y : 0.f;
+        mbar_wait(sdp_full, (uint32_t)(n & 1));
+        tc_fence_after();
+        uint32_t sv[32], dv[32];
+        tmem_ld_32x32(lane_addr + cq * 32, sv);
+        tmem_ld_32x32(lane_addr + 128 + cq * 32, dv);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(sdp_free);
 #pragma unroll
-      if (!(p.dbg & 8))
+        for (uint32_t tt = 0; tt < 4; ++tt) {
+          uint4 rr = make_uint4(0u, 0u, 0u, 0u);
+          if (drop) rr = attn_dropout_rand(p.drop, bh, (uint32_t)gi, (uint32_t)(kt * 4 + cq), tt);
+          const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
-      for (uint32_t tt = 0; tt < 4; ++tt) {
-        uint4 rr = make_uint4(0u, 0u, 0u, 0u);
-        if (drop && !(p.dbg & 32)) rr = attn_dropout_rand(p.drop, bh, (uint32_t)gi, (uint32_t)(kt * 4 + cq), tt);
-        const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
+          for (int q = 0; q < 4; ++q) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int cc = 8 * q + 2 * (int)tt + e;
-            const float v = fmaf(__uint_as_float(sv[cc]), p.scale, bias[cc]);
-            const float pr = ex2_approx(fmaf(v, kLog2e, -mb)) * inv;
-            const bool keep = e == 0 ? ((w[q] << 16) >= thi) : (w[q] >= thi);
-            const float dpm = keep ? __uint_as_float(dv[cc]) : 0.f;
-            sv[cc] = __float_as_uint(keep ? pr : 0.f);
-            dv[cc] = __float_as_uint(pr * (dpm - dsp));
+            for (int e = 0; e < 2; ++e) {
+              const int cc = 8 * q + 2 * (int)tt + e;
+              const float v = fmaf(__uint_as_float(sv[cc]), p.scale, bias[cc]);
+              const float pr = ex2_approx(fmaf(v, kLog2e, -mb)) * inv;
+              const bool keep = e == 0 ? ((w[q] << 16) >= thi) : (w[q] >= thi);
+              const float dpm = keep ? __uint_as_float(dv[cc]) : 0.f;
+              sv[cc] = __float_as_uint(keep ? pr : 0.f);
+              dv[cc] = __float_as_uint(pr * (dpm - dsp));
+            }
           }
         }
-      }
-      if (t > 0) mbar_wait(pds_free, (uint32_t)((t - 1) & 1));
+        if (n > 0) mbar_wait(pds_free, (uint32_t)((n - 1) & 1));
 #pragma unroll
-      for (uint32_t ch = 0; ch < 4; ++ch) {
-        const uint32_t off = st_off + (((ch0 + ch) ^ (uint32_t)(r & 7)) << 4);
-        st_shared_v4(sDS + off, pack_bf16(__uint_as_float(dv[8 * ch]), __uint_as_float(dv[8 * ch + 1])),
-                     pack_bf16(__uint_as_float(dv[8 * ch + 2]), __uint_as_float(dv[8 * ch + 3])),
-                     pack_bf16(__uint_as_float(dv[8 * ch + 4]), __uint_as_float(dv[8 * ch + 5])),
-                     pack_bf16(__uint_as_float(dv[8 * ch + 6]), __uint_as_float(dv[8 * ch + 7])));
-        st_shared_v4(sPD + off, pack_bf16(__uint_as_float(sv[8 * ch]), __uint_as_float(sv[8 * ch + 1])),
-                     pack_bf16(__uint_as_float(sv[8 * ch + 2]), __uint_as_float(sv[8 * ch + 3])),
-                     pack_bf16(__uint_as_float(sv[8 * ch + 4]), __uint_as_float(sv[8 * ch + 5])),
-                     pack_bf16(__uint_as_float(sv[8 * ch + 6]), __uint_as_float(sv[8 * ch + 7])));
+        for (uint32_t ch = 0; ch < 4; ++ch) {
+          const uint32_t off = st_off + (((ch0 + ch) ^ (uint32_t)(r & 7)) << 4);
+          st_shared_v4(sDS + off, pack_bf16(__uint_as_float(dv[8 * ch]), __uint_as_float(dv[8 * ch + 1])),
+                       pack_bf16(__uint_as_float(dv[8 * ch + 2]), __uint_as_float(dv[8 * ch + 3])),
+                       pack_bf16(__uint_as_float(dv[8 * ch + 4]), __uint_as_float(dv[8 * ch + 5])),
+                       pack_bf16(__uint_as_float(dv[8 * ch + 6]), __uint_as_float(dv[8 * ch + 7])));
+          st_shared_v4(sPD + off, pack_bf16(__uint_as_float(sv[8 * ch]), __uint_as_float(sv[8 * ch + 1])),
+                       pack_bf16(__uint_as_float(sv[8 * ch + 2]), __uint_as_float(sv[8 * ch + 3])),
+                       pack_bf16(__uint_as_float(sv[8 * ch + 4]), __uint_as_float(sv[8 * ch + 5])),
+                       pack_bf16(__uint_as_float(sv[8 * ch + 6]), __uint_as_float(sv[8 * ch + 7])));
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(pds_ready);
+        if (n > 0) drain_dq(n - 1, pend);  // while the MMA warp works on this pair
+        pend = gi < S ? ws + (long long)gi * hid : nullptr;
       }
-      fence_proxy_async();
+      // item epilogue: dK / dV accumulators -> global (row = key; this warp takes columns [16 cq, +16))
+      mbar_wait(acc_full, (uint32_t)(it & 1));
+      tc_fence_after();
+      uint32_t a0[16], a1[16];
+      tmem_ld_32x16(lane_addr + 256 + 16 * cq, a0);
+      tmem_ld_32x16(lane_addr + 320 + 16 * cq, a1);
+      tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(pds_ready);
-      if (t > 0) drain_dq(t - 1);  // while the MMA warp works on this pair
-    }
-    drain_dq(nin - 1);
-    mbar_wait(done, 0);
-    tc_fence_after();
-    // dK / dV accumulators -> global: row = key; this warp takes columns [16 cq, +16)
-    const int go = kt * 128 + r;
-    const float fk = p.scale * dscale, fv = dscale;
-    bf16* row = p.dqkv + ((long long)row_base + go) * p.ld + h * 64 + 16 * cq;
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {
-      uint32_t a0[16];
-      tmem_ld_32x16(lane_addr + 256 + 64 * which + 16 * cq, a0);
-      tmem_ld_wait();
+      if (lane == 0) mbar_arrive(acc_free);
+      const int go = kt * 128 + r;
       if (go < S) {
-        const float f0 = which ? fv : fk;
+        const float fk = p.scale * dscale, fv = dscale;
+        bf16* row = p.dqkv + ((long long)row_base + go) * p.ld + h * 64 + 16 * cq;
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
           float f[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(a0[8 * ch + e]) * f0;
-          *reinterpret_cast<uint4*>(row + (which + 1) * hid + 8 * ch) = pack8(f);
+          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(a0[8 * ch + e]) * fk;
+          *reinterpret_cast<uint4*>(row + hid + 8 * ch) = pack8(f);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(a1[8 * ch + e]) * fv;
+          *reinterpret_cast<uint4*>(row + 2 * hid + 8 * ch) = pack8(f);
         }
       }
     }
+    if (n > 0) drain_dq(n - 1, pend);
   }
   tc_fence_before();
   __syncthreads();
@@ -644,16 +683,16 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
   p.bias = bias; p.scale = 0.125f; p.lse = const_cast<float*>(lse); p.dsum = dsum_ws; p.dq_ws = reinterpret_cast<bf16*>(dsum_ws + dsum_floats);
   p.dqkv = (bf16*)dqkv; p.ld = ld;
   p.drop = make_dropout(dropout_p, seed, dropout_stream);
-  { const char* e = getenv("VT_ATTN_DBG"); p.dbg = e ? atoi(e) : 0; }
   VT_REQUIRE(((uintptr_t)dsum_ws & 15) == 0, "vt_attention_bwd: workspace must be 16-byte aligned");
-  const size_t smem = 1024 + BWD_SMEM_TILES + 256 + 128 * sizeof(float);
+  const size_t smem = 1024 + BWD_SMEM_TILES + 256 + 2 * 128 * sizeof(float);
   static bool attr = false;
   if (!attr) {
-    VT_CUDA(cudaFuncSetAttribute(attn_bwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(1024 + BWD_SMEM_TILES + 256 + 512)));
+    VT_CUDA(cudaFuncSetAttribute(attn_bwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(1024 + BWD_SMEM_TILES + 256 + 1024)));
     attr = true;
   }
-  const dim3 grid((unsigned)nt, (unsigned)heads, (unsigned)B);
-  attn_bwd_fused<<<grid, BWD_THREADS, smem, st>>>(tq, tdo, p);
+  const long long n_items = (long long)nt * heads * B;
+  const int sms = num_sms();
+  attn_bwd_fused<<<(unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st>>>(tq, tdo, p);
   const long long rows = B * S;
   const long long items = rows * (hidden / 8);
   attn_dq_reduce_kernel<<<(unsigned)((items + 255) / 256), 256, 0, st>>>(p.dq_ws, rows * hidden, nt, rows, (int)hidden,

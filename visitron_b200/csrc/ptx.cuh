@@ -55,7 +55,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity, uint32_t ns) {
   int polls = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++polls > 2) __nanosleep(ns);
+    if (ns && ++polls > 2) __nanosleep(ns);
   }
 }
 
