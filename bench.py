@@ -105,12 +105,88 @@ def build_model(args, device):
     cfg = BertConfig(V, hidden_dropout_prob=args.dropout, attention_probs_dropout_prob=0.1 if args.dropout > 0 else 0.0)
     cfg.img_feature_dim, cfg.detector_classes, cfg.action_space = IMG, DC, A
     torch.manual_seed(88)
-    model = modeling.PreTrainOscar(cfg)     # random-init bert-base (hf/modeling_bert.py:550-561), no checkpoint
+    if args.workload == "viewpoint_select":
+        model = modeling.BertImgModelwithLocationEmbeds(cfg)   # what train.py hands the agent as `model.bert` (vs/train.py:47)
+    else:
+        model = modeling.PreTrainOscar(cfg)     # random-init bert-base (hf/modeling_bert.py:550-561), no checkpoint
     return model.to(device).train()
 
 
+VS_STEPS, VS_CAND, VS_FEAT, VS_HID = 10, 12, 2052, 512   # decoder steps, candidates incl. STOP, 2048+4 features, LSTM width
+
+
+class Workload:
+    """One step of the hot path for `--workload`: host batches, the step function and the algorithmic FLOPs."""
+
+    def __init__(self, args, device, rank, world):
+        from visitron_b200 import agent_heads, synthetic
+        self.args, self.device, self.world = args, device, world
+        self.model = build_model(args, device)
+        b, n_host = args.batch, 4
+        self.extra_params = []
+        if args.workload == "viewpoint_select":
+            # BASELINE configs[1]: the encoder call of OscarEncoder (A13, S = 511 text-only, token types, the ~uint8 mask)
+            # + the candidate scorer with its masked CE (A14) at each of the 10 decoder steps.  The stock torch.nn LSTM
+            # encoder / decoder between them is SURVEY 8f-N1 (not built): the decoder state of step t is stood in for by
+            # sequence_output[:, t, :512], which keeps every head gradient flowing into the encoder.
+            g = torch.Generator().manual_seed(88)
+            self.w_in = torch.nn.Parameter((0.02 * torch.randn(VS_FEAT, VS_HID, generator=g)).to(device))
+            self.extra_params = [self.w_in]
+            host = []
+            for i in range(n_host):
+                hb = synthetic.finetune_encoder_batch(b, seed=88 + rank + 1000 * i)
+                steps = [synthetic.viewpoint_step_batch(b, seed=88 + rank + 1000 * i + 17 * t, candidates=VS_CAND, feat=VS_FEAT) for t in range(VS_STEPS)]
+                hb["cand_feat"] = torch.stack([s["cand_feat"] for s in steps])       # [10, b, 12, 2052]
+                hb["cand_len"] = torch.stack([s["cand_len"] for s in steps])
+                hb["target"] = torch.stack([s["target"] for s in steps])
+                host.append(hb)
+            self.S, self.R = 511, 0
+            self.labelled = (0.0, 0.0)
+            self.heads_flops = VS_STEPS * (2 * VS_HID * VS_FEAT + 2 * VS_CAND * VS_FEAT)
+            self.desc = ("viewpoint_select_step: BertImgModelwithLocationEmbeds fwd+bwd as OscarEncoder calls it (T=511 text-only, token types, "
+                         "~uint8 mask) + SoftDotAttention candidate scorer + masked CE at 10 decoder steps (12 candidates x 2052), bert-base "
+                         "random init [BASELINE configs[1]; the stock LSTM encoder/decoder of the agent is not part of the path, SURVEY 8f-N1]")
+        else:
+            host = [synthetic.pretrain_batch(b, seed=88 + rank + 1000 * i) for i in range(n_host)]  # per-rank shard, seed 88+rank
+            self.S, self.R = 767, 256
+            self.labelled = (sum(int((hb["labels"] != -1).sum()) for hb in host) / (n_host * b),
+                             sum(int((hb["token_labels"] != -1).sum()) for hb in host) / (n_host * b))
+            self.heads_flops = None
+            self.desc = ("pretrain_step: PreTrainOscar fwd+bwd, bert-base random init, NDH-shaped batch (T=511 text + R=256 region slots, "
+                         "img_feature_dim 2054, 15% MLM + masked detector-class + 36-way action labels), all objectives [BASELINE configs[2]; "
+                         "configs[1] = --workload viewpoint_select]")
+        self.host = [{k: v.pin_memory() for k, v in hb.items()} for hb in host]
+        self.n_host = n_host
+        self.params = list(self.model.parameters()) + self.extra_params
+        self._heads = agent_heads
+
+    def step(self, batch):
+        for p in self.params:
+            p.grad = None
+        if self.args.workload != "viewpoint_select":
+            out = self.model(**batch)
+            out[0].backward()
+            return out
+        seq, _ = self.model(batch["input_ids"], token_type_ids=batch["token_type_ids"], attention_mask=batch["attention_mask"])
+        loss = None
+        for t in range(VS_STEPS):
+            _, l, _ = self._heads.candidate_scores_ce(self.w_in, seq[:, t, :VS_HID], batch["cand_feat"][t], batch["cand_len"][t], batch["target"][t])
+            loss = l if loss is None else loss + l
+        loss.backward()
+        if self.world > 1:   # the scorer's weight is outside the encoder's flat buffer: one small all-reduce of its own
+            torch.distributed.all_reduce(self.w_in.grad, op=torch.distributed.ReduceOp.AVG)
+        return (loss,)
+
+    def flops(self, executed=False):
+        fl = flops_per_sample(self.S, self.R, all_rows_heads=not executed, labelled=self.labelled)
+        if self.heads_flops is not None:   # no pre-training heads, no image projection on this workload
+            fl["total"] += self.heads_flops - fl["heads"] - fl["img"]
+            fl["heads"], fl["img"] = self.heads_flops, 0
+        return fl
+
+
 def run_ours(args):
-    from visitron_b200 import lib, parallel, synthetic
+    from visitron_b200 import lib, parallel
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -121,28 +197,19 @@ def run_ours(args):
     device = torch.device("cuda", local)
     if world > 1:
         torch.distributed.init_process_group("nccl", device_id=device)
-    model = build_model(args, device)
+    wl = Workload(args, device, rank, world)
+    model = wl.model
     if world > 1:
         parallel.distribute(model)
     b = args.batch
-    n_host = 4
-    host = [synthetic.pretrain_batch(b, seed=88 + rank + 1000 * i) for i in range(n_host)]  # per-rank shard, seed 88+rank
-    host = [{k: v.pin_memory() for k, v in hb.items()} for hb in host]
+    n_host, host, step = wl.n_host, wl.host, wl.step
     dev_batches = [{k: v.to(device) for k, v in hb.items()} for hb in host]
-    labelled = (sum(int((hb["labels"] != -1).sum()) for hb in host) / (n_host * b),
-                sum(int((hb["token_labels"] != -1).sum()) for hb in host) / (n_host * b))
+    labelled = wl.labelled
 
     def barrier():
         if world > 1:
             torch.distributed.barrier()
         torch.cuda.synchronize()
-
-    def step(batch):
-        for p in model.parameters():
-            p.grad = None
-        out = model(**batch)
-        out[0].backward()
-        return out
 
     def timed(fn, steps):
         barrier()
@@ -190,7 +257,7 @@ def run_ours(args):
         out = step(batch)
         for t in batch.values():
             t.record_stream(torch.cuda.current_stream())
-        return torch.stack([o.detach() for o in out]).cpu()   # D2H read of the 7 scalars (host sync, as the loop's .item())
+        return torch.stack([o.detach().float() for o in out]).cpu()   # D2H read of the step's scalars (host sync, as the loop's .item())
 
     e2e_step(0)
     slots = [None, None]
@@ -222,21 +289,19 @@ def run_ours(args):
         if world > 1:
             torch.distributed.destroy_process_group()
         return
-    S, R = 767, 256
-    fl = flops_per_sample(S, R)
-    fl_done = flops_per_sample(S, R, all_rows_heads=False, labelled=labelled)
+    S = wl.S
+    fl, fl_done = wl.flops(), wl.flops(executed=True)
+    n_out = 7 if args.workload == "pretrain" else 1
     pk = peaks()
     line = dict(
         metric=METRIC, value=round(value, 2), unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
         ms_per_step=round(ms / args.steps, 3), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16",
         data="synthetic",
-        config=dict(workload="pretrain_step: PreTrainOscar fwd+bwd, bert-base random init, NDH-shaped batch (T=511 text + R=256 region slots, "
-                             "img_feature_dim 2054, 15% MLM + masked detector-class + 36-way action labels), all objectives [BASELINE configs[2]; "
-                             "configs[1]'s encoder is the same kernels at S=511: --workload finetune_encoder]",
+        config=dict(workload=wl.desc,
                     per_gpu_batch=b, global_batch=b * world, seq_len=S, parallelism="dp%d" % world, dropout=args.dropout,
                     l2="per-step working set (%.1f GB of activations) >> 126 MB L2; 4 rotating batches" % (b * S * 24.5e3 * 12 / 1e9),
                     grad_allreduce="fp32, one bucket per encoder layer, overlapped with backward" if world > 1 else "none (1 GPU)"),
-        e2e=dict(value=round(e2e_value, 2), unit=UNIT, h2d_bytes_per_step=h2d_bytes, d2h_bytes_per_step=28,
+        e2e=dict(value=round(e2e_value, 2), unit=UNIT, h2d_bytes_per_step=h2d_bytes, d2h_bytes_per_step=4 * n_out,
                  ms_per_step=round(e2e_ms / args.steps, 3)),
         gpu_launches=int(launches),
         clocks=clocks,
@@ -265,18 +330,35 @@ def cpu_baseline(args, steps):
     threads = int(os.environ.get("VT_CPU_THREADS", cores))
     torch.set_num_threads(threads)
     oc = vo.OracleConfig(hidden_dropout_prob=args.dropout, attention_probs_dropout_prob=0.1 if args.dropout > 0 else 0.0)
-    P = vo.clone_params(vo.init_params(oc, 88, perturb=False))
-    b = 2
-    batch = synthetic.pretrain_batch(b, 88)
     drop = vo.train_dropout if args.dropout > 0 else None
-    vo.pretrain_step(P, oc, batch, drop)
+    b = 2
+    if args.workload == "viewpoint_select":
+        P = vo.clone_params(vo.init_params(oc, 88, pretrain_heads=False, perturb=False))
+        w_in = vo.clone_params(vo.init_head_params(88))["candidate_att_layer.linear_in.weight"]
+        enc = synthetic.finetune_encoder_batch(b, 88)
+        vsb = [synthetic.viewpoint_step_batch(b, 88 + 17 * t, candidates=VS_CAND, feat=VS_FEAT) for t in range(VS_STEPS)]
+
+        def one():
+            for v in list(P.values()) + [w_in]:
+                v.grad = None
+            seq, _ = vo.bert_img_forward(P, oc, enc["input_ids"], enc["token_type_ids"], enc["attention_mask"], drop=drop)
+            loss = sum(vo.candidate_scores_ce(w_in, seq[:, t, :VS_HID], s["cand_feat"], s["cand_len"], s["target"])[1] for t, s in enumerate(vsb))
+            loss.backward()
+        what = "viewpoint_select workload at b=%d (S=511 encoder + 10 candidate-scorer steps)" % b
+    else:
+        P = vo.clone_params(vo.init_params(oc, 88, perturb=False))
+        batch = synthetic.pretrain_batch(b, 88)
+
+        def one():
+            vo.pretrain_step(P, oc, batch, drop)
+        what = "pre-training workload at b=%d (S=767, all rows through the MLM head as the reference does)" % b
+    one()
     t0 = time.perf_counter()
     for _ in range(steps):
-        vo.pretrain_step(P, oc, batch, drop)
+        one()
     dt = (time.perf_counter() - t0) / steps
     return dict(value=round(b / dt, 4), unit=UNIT, cores=threads, kind="port",
-                sample="%d fwd+bwd steps of the same pre-training workload at b=%d (S=767, all rows through the MLM head as the reference does), "
-                       "fp32 torch CPU, %d threads of %d host cores; %.2f s/step" % (steps, b, threads, cores, dt))
+                sample="%d fwd+bwd steps of the same %s, fp32 torch CPU, %d threads of %d host cores; %.2f s/step" % (steps, what, threads, cores, dt))
 
 
 def run_reference(args):
@@ -287,8 +369,8 @@ def run_reference(args):
     cb = cpu_baseline(args, steps)
     line = dict(impl="reference", metric=METRIC, value=cb["value"], unit=UNIT, n_gpus=args.gpus, steps=steps, warmup=1,
                 ms_per_step=round(2 / cb["value"] * 1e3, 1), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload="pretrain_step (same workload as the default arm; bounded sample b=2 per step on the host CPU)",
-                            per_gpu_batch=2, seq_len=767),
+                config=dict(workload="%s step (same workload as the default arm; bounded sample b=2 per step on the host CPU)" % args.workload,
+                            per_gpu_batch=2, seq_len=767 if args.workload == "pretrain" else 511),
                 cpu_baseline=cb, e2e=dict(value=cb["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
     print(json.dumps(line), flush=True)
 
@@ -301,6 +383,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=32, help="per-GPU batch (the reference scripts use 2; 32 fills the tensor cores)")
     ap.add_argument("--dropout", type=float, default=0.3, help="hidden dropout (run_scripts/pretrain/pretrain_ndh_r2r.sh:43 uses 0.3)")
+    ap.add_argument("--workload", default="pretrain", choices=["pretrain", "viewpoint_select"],
+                    help="pretrain = BASELINE configs[2] (the data-parallel headline); viewpoint_select = configs[1] (encoder at S=511 + candidate scorer)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     args = ap.parse_args()

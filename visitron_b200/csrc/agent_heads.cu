@@ -77,35 +77,57 @@ small_linear_fwd_kernel(const float* __restrict__ x1, long long ldx1, int K1, co
   }
 }
 
-// dx[b, k] = sum_n dy'(b, n) W[n, k]  with  dy' = dy * act'(y);  one thread per (tile of LIN_BT rows, 4 columns k)
+// dx[b, k] = sum_n dy'(b, n) W[n, k]  with  dy' = dy * act'(y).
+// One CTA per (32 columns k, tile of LIN_BT rows): 8 threads x float4 cover the columns, the 32 thread groups stride the
+// output features n (W is read once per row tile, 128 contiguous bytes per group), and the groups' partial sums are added
+// through shared memory in group order, so the result is deterministic.  (One thread per output looping over all n left a
+// decoder step's dx on 4 CTAs: 2.1 ms for [32, 2052] x [2052, 512].)
+constexpr int DX_KT = 32, DX_NG = 32;
+
 __global__ void __launch_bounds__(256)
 small_linear_dx_kernel(const float* __restrict__ dy, long long lddy, const float* __restrict__ y, long long ldy, int act,
-                       const float* __restrict__ W, long long ldw, int koff, float* __restrict__ dx, long long lddx, int B, int N, int K) {
-  const int k = (blockIdx.x * 256 + threadIdx.x) * 4;
+                       const float* __restrict__ W, long long ldw, int koff, float* __restrict__ dx, long long lddx, int B, int N, int K, int vec) {
+  __shared__ float red[DX_NG][LIN_BT][DX_KT + 1];
+  const int kq = threadIdx.x & 7, g = threadIdx.x >> 3;
+  const int k = blockIdx.x * DX_KT + kq * 4;
   const int b0 = blockIdx.y * LIN_BT;
-  if (k >= K) return;
   float acc[LIN_BT][4];
 #pragma unroll
   for (int j = 0; j < LIN_BT; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
-  const int kw = min(4, K - k);
-  for (int n = 0; n < N; ++n) {
+  const int kw = max(0, min(4, K - k));
+  for (int n = g; n < N; n += DX_NG) {
     float wv[4];
+    const float* wp = W + (long long)n * ldw + koff + k;
+    if (vec && kw == 4) {
+      const float4 t = __ldg(reinterpret_cast<const float4*>(wp));
+      wv[0] = t.x; wv[1] = t.y; wv[2] = t.z; wv[3] = t.w;
+    } else {
 #pragma unroll
-    for (int c = 0; c < 4; ++c) wv[c] = c < kw ? __ldg(W + (long long)n * ldw + koff + k + c) : 0.f;
+      for (int c = 0; c < 4; ++c) wv[c] = c < kw ? __ldg(wp + c) : 0.f;
+    }
 #pragma unroll
     for (int j = 0; j < LIN_BT; ++j) {
       if (b0 + j < B) {
-        float g = __ldg(dy + (long long)(b0 + j) * lddy + n);
-        if (act) g *= act_grad_from_y(act, __ldg(y + (long long)(b0 + j) * ldy + n));
+        float gr = __ldg(dy + (long long)(b0 + j) * lddy + n);
+        if (act) gr *= act_grad_from_y(act, __ldg(y + (long long)(b0 + j) * ldy + n));
 #pragma unroll
-        for (int c = 0; c < 4; ++c) acc[j][c] = fmaf(g, wv[c], acc[j][c]);
+        for (int c = 0; c < 4; ++c) acc[j][c] = fmaf(gr, wv[c], acc[j][c]);
       }
     }
   }
 #pragma unroll
   for (int j = 0; j < LIN_BT; ++j)
-    if (b0 + j < B)
-      for (int c = 0; c < kw; ++c) dx[(long long)(b0 + j) * lddx + k + c] = acc[j][c];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) red[g][j][kq * 4 + c] = acc[j][c];
+  __syncthreads();
+  const int j = threadIdx.x >> 5, c = threadIdx.x & 31;   // 8 rows x 32 columns
+  const int ko = blockIdx.x * DX_KT + c;
+  if (b0 + j < B && ko < K) {
+    float sum = 0.f;
+#pragma unroll 8
+    for (int gg = 0; gg < DX_NG; ++gg) sum += red[gg][j][c];
+    dx[(long long)(b0 + j) * lddx + ko] = sum;
+  }
 }
 
 // dW[n, koff + k] = sum_b dy'(b, n) x[b, k];  dbias[n] = sum_b dy'(b, n)   (one thread per (n, k); b in order: deterministic)
@@ -526,8 +548,9 @@ extern "C" int vt_small_linear_bwd(const float* dy, int64_t lddy, const float* y
     float* dx = seg ? dx2 : dx1;
     const int koff = seg ? (int)K1 : 0;
     if (dx) {
-      dim3 grid((unsigned)((K + 1023) / 1024), (unsigned)((B + LIN_BT - 1) / LIN_BT));
-      small_linear_dx_kernel<<<grid, 256, 0, st>>>(dy, lddy, y, ldy, act, W, ldw, koff, dx, seg ? lddx2 : lddx1, (int)B, (int)N, (int)K);
+      dim3 grid((unsigned)((K + DX_KT - 1) / DX_KT), (unsigned)((B + LIN_BT - 1) / LIN_BT));
+      const int vec = (((uintptr_t)W & 15) == 0 && ldw % 4 == 0 && koff % 4 == 0) ? 1 : 0;
+      small_linear_dx_kernel<<<grid, 256, 0, st>>>(dy, lddy, y, ldy, act, W, ldw, koff, dx, seg ? lddx2 : lddx1, (int)B, (int)N, (int)K, vec);
       ++launches;
     }
     if (dW) {

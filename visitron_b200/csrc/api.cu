@@ -2,12 +2,15 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace vt {
 
 static thread_local char g_err[512] = "";
 static int g_sms = 0;
+static std::atomic<int> g_reserved_sms{0};  // SMs left to an overlapped NCCL exchange by the persistent kernels (vt_reserve_sms)
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -31,6 +34,13 @@ int num_sms() {
   return g_sms;
 }
 
+// SMs a persistent kernel should occupy: while a gradient exchange is in flight its CTAs hold `reserved` SMs, and a
+// persistent CTA queued behind one of them would start only when the exchange kernel retires (a whole-kernel tail).
+int usable_sms() {
+  int sms = num_sms() - g_reserved_sms.load(std::memory_order_relaxed);
+  return sms < 16 ? 16 : sms;
+}
+
 int resolve_driver_entry_points();
 
 }  // namespace vt
@@ -38,6 +48,7 @@ int resolve_driver_entry_points();
 extern "C" const char* vt_last_error(void) { return vt::g_err; }
 
 extern "C" int vt_num_sms(void) { return vt::num_sms(); }
+extern "C" void vt_reserve_sms(int n) { vt::g_reserved_sms.store(n < 0 ? 0 : n); }
 
 extern "C" int vt_init(int device) {
   int count = 0;

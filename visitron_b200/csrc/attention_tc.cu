@@ -297,6 +297,9 @@ constexpr int BWD_SMEM_TILES = (8 + 2 * BWD_NST) * TILE16K;  // K[2], V[2], Q[NS
 // TMEM columns and 224 KB of shared memory, so two cannot share an SM; as one-item CTAs the launch, TMEM allocation and the
 // cold K / V / Q / dO loads of every item (~8k cycles for ~12k of work) were exposed.  Here the TMA warp runs ahead across
 // item boundaries (K / V double-buffered), so the next item's operands are resident when the current one drains.
+// Registers: a CTA is allocated in whole warpgroups, so 18 warps cost as much as 20 and cap every thread at 96 registers
+// (a setmaxnreg split does not help: the MMA-issuing warp itself needs ~90).  The element-wise loop is arranged to fit: the
+// next tile's row statistics are requested only after the pair's arithmetic, when the S / dP values are dead.
 __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -468,6 +471,19 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
 
     int n = 0, it = 0;
     bf16* pend = nullptr;  // where the dQ partial of pair n - 1 goes (null: row past the end of the sample)
+    // mask bias of the item's 128 keys: copied into the other half of sBias one item ahead with cp.async (no register is
+    // held across the item and the global-load latency is not exposed at the item boundary)
+    auto fetch_bias = [&](int id2, int slot) {
+      if (ew_tid < 128 && id2 < n_items) {
+        int kt2, h2, b2;
+        decode(id2, kt2, h2, b2);
+        const int k = kt2 * 128 + ew_tid;
+        float* dst = sBias + slot * 128 + ew_tid;
+        if (k < S) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(p.bias + (long long)b2 * S + k) : "memory");
+        else *dst = -INFINITY;
+      }
+    };
+    fetch_bias((int)blockIdx.x, 0);
     for (int id = blockIdx.x; id < n_items; id += gridDim.x, ++it) {
       int kt, h, b;
       decode(id, kt, h, b);
@@ -475,11 +491,9 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       const uint32_t bh = (uint32_t)(b * p.heads + h);
       const long long stat_base = ((long long)b * p.heads + h) * S;
       float* sB = sBias + (it & 1) * 128;
-      if (ew_tid < 128) {
-        const int k = kt * 128 + ew_tid;
-        sB[ew_tid] = k < S ? p.bias[(long long)b * S + k] : -INFINITY;
-      }
+      asm volatile("cp.async.wait_all;" ::: "memory");
       asm volatile("bar.sync 1, %0;" ::"n"(BWD_EW_WARPS * 32) : "memory");  // element-wise warps only
+      fetch_bias(id + (int)gridDim.x, (it + 1) & 1);  // that half was last read in item it - 1, which every warp has left
       const float* bias = sB + cq * 32;
       // this warp's 16 of the 64 dQ columns in this key tile's slice of the workspace
       bf16* ws = p.dq_ws + ((long long)kt * p.B * S + row_base) * hid + h * 64 + 16 * cq;
@@ -495,51 +509,64 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         const int gi = t * 128 + r;
         const float2 lse = lse_n;
         const float dsp = dsum_n * inv_dscale;
-        if (t + 1 < nin) load_stats(t + 1, lse_n, dsum_n);  // a tile ahead: the loads are off the critical path
         // P = exp2(v log2e - mb) / sum with mb rounded exactly as in the forward (the F6 mask bias of 2.54e6 leaves 0.25 ulp:
         // any other rounding of the reference point would rescale the whole row); rows past the end of the sample get P = dS = 0
         const float mb = lse.x * kLog2e;
         const float inv = gi < S ? lse.y : 0.f;
         mbar_wait(sdp_full, (uint32_t)(n & 1));
         tc_fence_after();
-        uint32_t sv[32], dv[32];
-        tmem_ld_32x32(lane_addr + cq * 32, sv);
-        tmem_ld_32x32(lane_addr + 128 + cq * 32, dv);
-        tmem_ld_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(sdp_free);
+        // Two halves of 16 columns, chosen to match the dropout counter layout (half hf = Philox calls 2 hf and 2 hf + 1 =
+        // columns 8 q + 4 hf .. + 3 of each 8-column chunk q): only 16 + 16 accumulator values are live at a time, and the
+        // first half is already packed to bf16 when the second is loaded (the whole tile at once needed > 96 registers).
+        uint32_t pk_p[2][8], pk_d[2][8];   // [half][2 q + (0: columns +0,+1 | 1: columns +2,+3)]
 #pragma unroll
-        for (uint32_t tt = 0; tt < 4; ++tt) {
-          uint4 rr = make_uint4(0u, 0u, 0u, 0u);
-          if (drop) rr = attn_dropout_rand(p.drop, bh, (uint32_t)gi, (uint32_t)(kt * 4 + cq), tt);
-          const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
+        for (int hf = 0; hf < 2; ++hf) {
+          uint32_t sv[16], dv[16];         // index 4 q + j  <->  column 8 q + 4 hf + j
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
+            tmem_ld_32x4(lane_addr + cq * 32 + 8 * q + 4 * hf, sv + 4 * q);
+            tmem_ld_32x4(lane_addr + 128 + cq * 32 + 8 * q + 4 * hf, dv + 4 * q);
+          }
+          tmem_ld_wait();
+          if (hf == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sdp_free);
+          }
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              const int cc = 8 * q + 2 * (int)tt + e;
-              const float v = fmaf(__uint_as_float(sv[cc]), p.scale, bias[cc]);
-              const float pr = ex2_approx(fmaf(v, kLog2e, -mb)) * inv;
-              const bool keep = e == 0 ? ((w[q] << 16) >= thi) : (w[q] >= thi);
-              const float dpm = keep ? __uint_as_float(dv[cc]) : 0.f;
-              sv[cc] = __float_as_uint(keep ? pr : 0.f);
-              dv[cc] = __float_as_uint(pr * (dpm - dsp));
+          for (int t2 = 0; t2 < 2; ++t2) {
+            const uint32_t tt = (uint32_t)(2 * hf + t2);
+            uint4 rr = make_uint4(0u, 0u, 0u, 0u);
+            if (drop) rr = attn_dropout_rand(p.drop, bh, (uint32_t)gi, (uint32_t)(kt * 4 + cq), tt);
+            const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              float pe[2], de[2];
+#pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                const int cc = 8 * q + 2 * (int)tt + e;     // column within the warp's 32
+                const int ix = 4 * q + 2 * t2 + e;
+                const float v = fmaf(__uint_as_float(sv[ix]), p.scale, bias[cc]);
+                const float pr = ex2_approx(fmaf(v, kLog2e, -mb)) * inv;
+                const bool keep = e == 0 ? ((w[q] << 16) >= thi) : (w[q] >= thi);
+                const float dpm = keep ? __uint_as_float(dv[ix]) : 0.f;
+                pe[e] = keep ? pr : 0.f;
+                de[e] = pr * (dpm - dsp);
+              }
+              pk_p[hf][2 * q + t2] = pack_bf16(pe[0], pe[1]);
+              pk_d[hf][2 * q + t2] = pack_bf16(de[0], de[1]);
             }
           }
         }
+        // next tile's statistics: requested here, where the S / dP registers are dead, and covered by the stores, the
+        // barrier round trip and the dQ drain below
+        if (t + 1 < nin) load_stats(t + 1, lse_n, dsum_n);
         if (n > 0) mbar_wait(pds_free, (uint32_t)((n - 1) & 1));
 #pragma unroll
         for (uint32_t ch = 0; ch < 4; ++ch) {
           const uint32_t off = st_off + (((ch0 + ch) ^ (uint32_t)(r & 7)) << 4);
-          st_shared_v4(sDS + off, pack_bf16(__uint_as_float(dv[8 * ch]), __uint_as_float(dv[8 * ch + 1])),
-                       pack_bf16(__uint_as_float(dv[8 * ch + 2]), __uint_as_float(dv[8 * ch + 3])),
-                       pack_bf16(__uint_as_float(dv[8 * ch + 4]), __uint_as_float(dv[8 * ch + 5])),
-                       pack_bf16(__uint_as_float(dv[8 * ch + 6]), __uint_as_float(dv[8 * ch + 7])));
-          st_shared_v4(sPD + off, pack_bf16(__uint_as_float(sv[8 * ch]), __uint_as_float(sv[8 * ch + 1])),
-                       pack_bf16(__uint_as_float(sv[8 * ch + 2]), __uint_as_float(sv[8 * ch + 3])),
-                       pack_bf16(__uint_as_float(sv[8 * ch + 4]), __uint_as_float(sv[8 * ch + 5])),
-                       pack_bf16(__uint_as_float(sv[8 * ch + 6]), __uint_as_float(sv[8 * ch + 7])));
+          st_shared_v4(sDS + off, pk_d[0][2 * ch], pk_d[0][2 * ch + 1], pk_d[1][2 * ch], pk_d[1][2 * ch + 1]);
+          st_shared_v4(sPD + off, pk_p[0][2 * ch], pk_p[0][2 * ch + 1], pk_p[1][2 * ch], pk_p[1][2 * ch + 1]);
         }
         fence_proxy_async();
         tc_fence_before();
@@ -691,7 +718,7 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
     attr = true;
   }
   const long long n_items = (long long)nt * heads * B;
-  const int sms = num_sms();
+  const int sms = usable_sms();  // leaves the SMs of an overlapped gradient exchange alone (vt_reserve_sms)
   attn_bwd_fused<<<(unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st>>>(tq, tdo, p);
   const long long rows = B * S;
   const long long items = rows * (hidden / 8);

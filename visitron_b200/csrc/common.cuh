@@ -34,6 +34,7 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
   } while (0)
 
 int num_sms();
+int usable_sms();
 
 // ---------------------------------------------------------------------------------------------
 // small device utilities

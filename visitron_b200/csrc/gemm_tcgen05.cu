@@ -469,14 +469,12 @@ static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUten
 }
 
 static int g_force_bn = 0;
-static std::atomic<int> g_reserved_sms{0};
 
 }  // namespace vt
 
 using namespace vt;
 
 extern "C" void vt_debug_force_block_n(int bn) { vt::g_force_bn = bn; }
-extern "C" void vt_reserve_sms(int n) { vt::g_reserved_sms.store(n < 0 ? 0 : n); }
 extern "C" int64_t vt_launch_count(void) { return (int64_t)vt::g_launches.load(); }
 extern "C" void vt_reset_launch_count(void) { vt::g_launches.store(0); }
 
@@ -499,8 +497,7 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   VT_REQUIRE(!splitting || (!ep->bias && ep->act == VT_ACT_NONE && !ep->residual && ep->dropout_p <= 0.f && !ep->aux_out),
              "vt_gemm_bf16: split-K supports only the alpha epilogue");
 
-  int sms = num_sms() - g_reserved_sms.load(std::memory_order_relaxed);  // see vt_reserve_sms
-  if (sms < 16) sms = 16;
+  const int sms = usable_sms();  // see vt_reserve_sms
   int BN = 256;
   const int m_blocks = (int)((M + BM - 1) / BM);
   if (g_force_bn) {

@@ -122,6 +122,10 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t* v) {
       : "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ void tmem_ld_32x4(uint32_t taddr, uint32_t* v) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]) : "r"(taddr));
+}
 // registers -> 32 lanes x 32 consecutive fp32 columns (inverse of tmem_ld_32x32)
 __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t* v) {
   asm volatile(
