@@ -49,6 +49,7 @@ struct AttnTcParams {
   bf16* dqkv;          // [B*S, ld]
   long long ld;
   DropoutCfg drop;
+  int dbg;             // timing ablations only (VT_ATTN_DBG, results are garbage): 1 skip the element-wise arithmetic, 2 skip the exponentials
 };
 
 // keep-bits of 32 consecutive key columns [32*jgroup, +32) of query row i (bit c = column 32*jgroup + c),
@@ -72,207 +73,287 @@ __device__ __forceinline__ uint32_t attn_keep_mask32(const DropoutCfg& d, uint32
 // forward
 // ---------------------------------------------------------------------------------------------
 constexpr int FQ = 128, FK = 64;
-constexpr int FWD_THREADS = 192;  // warps 0-3 softmax, warp 4 TMA, warp 5 MMA + TMEM
-constexpr int FWD_SMEM_TILES = 16384 + 2 * 8192 + 2 * 8192 + 16384;  // Q, K[2], V[2], P
-constexpr int FWD_TMEM_COLS = 128;                                    // S: [0,64)  O: [64,128)
+constexpr int FWD_SM_WARPS = 8;   // softmax warps: TMEM lane quadrant = warp & 3, 32-key column half of the tile = warp >> 2
+constexpr int FWD_THREADS = (FWD_SM_WARPS + 2) * 32;  // + TMA warp + MMA / TMEM warp
+constexpr int FWD_QB = 1;         // Q buffers (2 lets the TMA lane run ahead across the items of a persistent CTA)
+constexpr int FWD_KV = 3;         // K and V ring depths (separate rings: S runs two key tiles ahead of P.V)
+constexpr bool FWD_PERSISTENT = false;
+constexpr int FWD_SMEM_TILES = FWD_QB * 16384 + 2 * FWD_KV * 8192 + 2 * 16384;  // Q[QB], K[KV], V[KV], P[2]
+constexpr int FWD_TMEM_COLS = 256;                                            // S: [0,64) [64,128)   O: [128,192)
+constexpr int FWD_MAX_S = 2048;
 
+// Pipeline.  Timing ablations (tools/attn_dbg.sh) showed what bound the first version (S and P single-buffered): 131 of its
+// 204 us remained with the arithmetic AND the MMAs removed, i.e. the round trip softmax warps -> mbarrier -> MMA-issuing lane
+// -> tcgen05.commit -> mbarrier -> softmax warps once per key tile.  Hence:
+//  * S is double-buffered in TMEM and P in shared memory: the MMA lane issues S(g+2) as soon as the softmax warps have pulled
+//    S(g) into registers and P.V(g) as soon as P(g) is staged; the softmax warps only wait for events two tiles old;
+//  * K and V stream through separate FWD_KV-deep rings; a CTA walks a contiguous range of (query tile, head, sample) items.
+//    Measured at b=32, S=767 (p=0.1 / p=0): one item per CTA with 3-deep rings 200 / 144 us; persistent (two CTAs per SM, Q
+//    double-buffered, which leaves shared memory for 2-deep rings only) 218 / 171 us: the TMA latency of a 2-deep ring costs
+//    more than the per-CTA launch / TMEM allocation / cold loads, so FWD_PERSISTENT is off;
+//  * two threads per query row (32 of the tile's 64 keys each) give every scheduler 4 softmax warps; the halves agree on the
+//    row maximum through shared memory and a 64-thread named barrier per tile and add their row sums once per item.
 __global__ void __launch_bounds__(FWD_THREADS, 2)
 attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sQ = base, sK = base + 16384, sV = sK + 2 * 8192, sP = sV + 2 * 8192;
-  const uint32_t bars = sP + 16384;
-  const uint32_t q_full = bars, kv_full = bars + 8, kv_empty = bars + 24, s_full = bars + 40, s_free = bars + 48, p_ready = bars + 56,
-                 o_full = bars + 64, tmem_slot = bars + 72;
-  float* sBias = reinterpret_cast<float*>(smem_raw + (bars + 128 - smem_u32(smem_raw)));
+  const uint32_t sQ = base, sK = base + FWD_QB * 16384, sV = sK + FWD_KV * 8192, sP = sV + FWD_KV * 8192;
+  const uint32_t bars = sP + 2 * 16384;
+  static_assert(FWD_QB <= 2 && FWD_KV <= 4, "barrier slots");
+  const uint32_t q_full = bars, q_empty = bars + 16, k_full = bars + 32, k_empty = bars + 64, v_full = bars + 96, v_empty = bars + 128,
+                 s_full = bars + 160, s_free = bars + 176, p_ready = bars + 192, p_free = bars + 208, o_free = bars + 224, tmem_slot = bars + 232;
+  float* sXch = reinterpret_cast<float*>(smem_raw + (bars + 256 - smem_u32(smem_raw)));   // [3][2 halves][128 rows]
+  float* sBias = sXch + 768;                                                               // [key tiles * 64]
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int S = p.S;
-  const int nkt = (S + FK - 1) / FK;
-  const int row_base = b * S;
+  const int nkt = (S + FK - 1) / FK, nqt = (S + FQ - 1) / FQ;
+  const int n_items = nqt * p.heads * p.B;
+  const int item0 = (int)((long long)n_items * blockIdx.x / gridDim.x), item1 = (int)((long long)n_items * (blockIdx.x + 1) / gridDim.x);
+  const int my_items = item1 - item0;
+  const int G = my_items * nkt;   // key tiles this CTA walks, numbered g = item * nkt + j
+  auto decode = [&](int id, int& qt, int& h, int& b) { qt = id % nqt; h = (id / nqt) % p.heads; b = id / (nqt * p.heads); };
 
-  if (warp == 4 && lane == 0) {
+  if (warp == FWD_SM_WARPS && lane == 0) {
     prefetch_tensormap(&tmQ);
     prefetch_tensormap(&tmKV);
-    mbar_init(q_full, 1);
-    mbar_init(kv_full, 1); mbar_init(kv_full + 8, 1);
-    mbar_init(kv_empty, 1); mbar_init(kv_empty + 8, 1);
-    mbar_init(s_full, 1);
-    mbar_init(s_free, 4);
-    mbar_init(p_ready, 4);
-    mbar_init(o_full, 1);
+    for (int i = 0; i < FWD_QB; ++i) { mbar_init(q_full + 8 * i, 1); mbar_init(q_empty + 8 * i, 1); }
+    for (int i = 0; i < FWD_KV; ++i) {
+      mbar_init(k_full + 8 * i, 1); mbar_init(k_empty + 8 * i, 1);
+      mbar_init(v_full + 8 * i, 1); mbar_init(v_empty + 8 * i, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(s_full + 8 * i, 1); mbar_init(s_free + 8 * i, FWD_SM_WARPS);
+      mbar_init(p_ready + 8 * i, FWD_SM_WARPS); mbar_init(p_free + 8 * i, 1);
+    }
+    mbar_init(o_free, FWD_SM_WARPS);
     fence_barrier_init();
   }
-  if (warp == 5) {
+  if (warp == FWD_SM_WARPS + 1) {
     tmem_alloc(tmem_slot, FWD_TMEM_COLS);
     tmem_relinquish();
   }
-  for (int j = threadIdx.x; j < nkt * FK; j += FWD_THREADS) sBias[j] = j < S ? p.bias[(long long)b * S + j] : -INFINITY;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  const uint32_t tmem_o = tmem_base + 128;
 
-  if (warp == 4) {
+  if (warp == FWD_SM_WARPS) {
+    // ---------------- TMA producer: runs ahead of the consumers across items, bounded by the rings ----------------
     if (lane == 0) {
-      mbar_arrive_expect_tx(q_full, 16384);
-      tma_load_2d(sQ, &tmQ, q_full, h * 64, row_base + qt * FQ);
-      for (int j = 0; j < nkt; ++j) {
-        const int st = j & 1;
-        if (j >= 2) mbar_wait_backoff(kv_empty + 8 * st, (uint32_t)(((j >> 1) - 1) & 1), 128);
-        mbar_arrive_expect_tx(kv_full + 8 * st, 16384);
-        tma_load_2d(sK + st * 8192, &tmKV, kv_full + 8 * st, p.hidden + h * 64, row_base + j * FK);
-        tma_load_2d(sV + st * 8192, &tmKV, kv_full + 8 * st, 2 * p.hidden + h * 64, row_base + j * FK);
+      int g = 0;
+      for (int it = 0; it < my_items; ++it) {
+        int qt, h, b;
+        decode(item0 + it, qt, h, b);
+        const int row_base = b * S;
+        const int qb = it % FWD_QB;
+        if (it >= FWD_QB) mbar_wait_backoff(q_empty + 8 * qb, (uint32_t)((it / FWD_QB - 1) & 1), 32);
+        mbar_arrive_expect_tx(q_full + 8 * qb, 16384);
+        tma_load_2d(sQ + qb * 16384, &tmQ, q_full + 8 * qb, h * 64, row_base + qt * FQ);
+        for (int j = 0; j < nkt; ++j, ++g) {
+          const int st = g % FWD_KV;
+          const uint32_t ph = (uint32_t)((g / FWD_KV - 1) & 1);
+          if (g >= FWD_KV) mbar_wait_backoff(k_empty + 8 * st, ph, 32);
+          mbar_arrive_expect_tx(k_full + 8 * st, 8192);
+          tma_load_2d(sK + st * 8192, &tmKV, k_full + 8 * st, p.hidden + h * 64, row_base + j * FK);
+          if (g >= FWD_KV) mbar_wait_backoff(v_empty + 8 * st, ph, 32);
+          mbar_arrive_expect_tx(v_full + 8 * st, 8192);
+          tma_load_2d(sV + st * 8192, &tmKV, v_full + 8 * st, 2 * p.hidden + h * 64, row_base + j * FK);
+        }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == FWD_SM_WARPS + 1) {
+    // ---------------- MMA issuer ----------------
     if (lane == 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(128, FK, 0, 0);   // S[128 q, 64 keys] = Q (K-major) x K (K-major)
       constexpr uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);   // O[128 q, 64 d]   = P (K-major) x V (MN-major)
-      auto issue_s = [&](int j) {
-        const uint64_t a = make_smem_desc(sQ, 16, 1024), bd = make_smem_desc(sK + (j & 1) * 8192, 16, 1024);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) umma_bf16(tmem_base, a + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc_s, k > 0 ? 1u : 0u);
-        umma_commit(s_full);
-      };
-      mbar_wait_backoff(q_full, 0, MMA_POLL_NS);
-      mbar_wait_backoff(kv_full, 0, MMA_POLL_NS);
-      tc_fence_after();
-      issue_s(0);
-      for (int j = 0; j < nkt; ++j) {
-        if (j + 1 < nkt) {
-          mbar_wait_backoff(kv_full + 8 * ((j + 1) & 1), (uint32_t)(((j + 1) >> 1) & 1), MMA_POLL_NS);
-          mbar_wait_backoff(s_free, (uint32_t)(j & 1), MMA_POLL_NS);
-          tc_fence_after();
-          issue_s(j + 1);
-        }
-        mbar_wait_backoff(p_ready, (uint32_t)(j & 1), MMA_POLL_NS);
+      auto issue_s = [&](int g) {   // S(g) -> TMEM buffer g & 1; frees K stage g & 1 (and the item's Q buffer after its last tile)
+        const int it = g / nkt, j = g - it * nkt, st = g % FWD_KV, qb = it % FWD_QB;
+        if (j == 0) mbar_wait_backoff(q_full + 8 * qb, (uint32_t)((it / FWD_QB) & 1), MMA_POLL_NS);
+        mbar_wait_backoff(k_full + 8 * st, (uint32_t)((g / FWD_KV) & 1), MMA_POLL_NS);
         tc_fence_after();
-        const uint64_t a = make_smem_desc(sP, 16, 1024), bd = make_smem_desc(sV + (j & 1) * 8192, 8192, 1024);
+        const uint64_t a = make_smem_desc(sQ + qb * 16384, 16, 1024), bd = make_smem_desc(sK + st * 8192, 16, 1024);
+        if (!(p.dbg & 128)) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          umma_bf16(tmem_base + 64, a + (uint64_t)(2 * k), bd + (uint64_t)(128 * k), idesc_o, (j > 0 || k > 0) ? 1u : 0u);
-        umma_commit(o_full);
-        umma_commit(kv_empty + 8 * (j & 1));
+          for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + 64 * (g & 1), a + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc_s, k > 0 ? 1u : 0u);
+        }
+        umma_commit(s_full + 8 * (g & 1));
+        umma_commit(k_empty + 8 * st);
+        if (j == nkt - 1) umma_commit(q_empty + 8 * qb);
+      };
+      if (G > 0) issue_s(0);
+      if (G > 1) issue_s(1);
+      int it = 0, j = 0;
+      for (int g = 0; g < G; ++g) {
+        const int bf = g & 1;
+        if (g + 2 < G) {   // S(g + 2) reuses S(g)'s TMEM buffer: the softmax warps have pulled S(g) into registers
+          mbar_wait_backoff(s_free + 8 * bf, (uint32_t)((g >> 1) & 1), MMA_POLL_NS);
+          issue_s(g + 2);
+        }
+        mbar_wait_backoff(p_ready + 8 * bf, (uint32_t)((g >> 1) & 1), MMA_POLL_NS);
+        const int vst = g % FWD_KV;
+        mbar_wait_backoff(v_full + 8 * vst, (uint32_t)((g / FWD_KV) & 1), MMA_POLL_NS);
+        if (j == 0 && it > 0) mbar_wait_backoff(o_free, (uint32_t)((it - 1) & 1), MMA_POLL_NS);   // previous item's O drained
+        tc_fence_after();
+        const uint64_t a = make_smem_desc(sP + bf * 16384, 16, 1024), bd = make_smem_desc(sV + vst * 8192, 8192, 1024);
+        if (!(p.dbg & 16)) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma_bf16(tmem_o, a + (uint64_t)(2 * k), bd + (uint64_t)(128 * k), idesc_o, (j > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(p_free + 8 * bf);      // P buffer bf consumed, O holds the item's tiles 0 .. j
+        umma_commit(v_empty + 8 * vst);
+        if (++j == nkt) { j = 0; ++it; }
       }
     }
   } else {
-    const int r = warp * 32 + lane;
-    const int qi = qt * FQ + r;
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
-    const uint32_t bh = (uint32_t)(b * p.heads + h);
-    float m_used = -INFINITY, l = 0.f;
-    for (int j = 0; j < nkt; ++j) {
-      mbar_wait(s_full, (uint32_t)(j & 1));
-      tc_fence_after();
-      uint32_t sv[64];
-      tmem_ld_32x32(lane_addr, sv);
-      tmem_ld_32x32(lane_addr + 32, sv + 32);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(s_free);
-      float mx = -INFINITY;
-#pragma unroll
-      for (int c = 0; c < 64; ++c) {
-        const float v = fmaf(__uint_as_float(sv[c]), p.scale, sBias[j * FK + c]);
-        sv[c] = __float_as_uint(v);
-        mx = fmaxf(mx, v);
+    // ---------------- softmax warps ----------------
+    const int quad = warp & 3, half = warp >> 2;
+    const int r = quad * 32 + lane;
+    const int sm_tid = (int)threadIdx.x;   // 0 .. 255
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
+    const uint32_t lane_o = tmem_o + ((uint32_t)(quad * 32) << 16) + 32 * half;   // this thread's 32 columns of O
+    int g = 0, b_loaded = -1;
+    for (int it = 0; it < my_items; ++it) {
+      int qt, h, b;
+      decode(item0 + it, qt, h, b);
+      const int row_base = b * S;
+      const int qi = qt * FQ + r;
+      const uint32_t bh = (uint32_t)(b * p.heads + h);
+      if (b != b_loaded) {   // a contiguous item range changes sample at most a few times per CTA
+        asm volatile("bar.sync 9, 256;" ::: "memory");   // every softmax warp has left the previous sample's last tile
+        for (int k = sm_tid; k < nkt * FK; k += FWD_SM_WARPS * 32) sBias[k] = k < S ? p.bias[(long long)b * S + k] : -INFINITY;
+        asm volatile("bar.sync 9, 256;" ::: "memory");
+        b_loaded = b;
       }
-      bool resc = false;
-      float alpha = 1.f;
-      if (mx > m_used + kRescaleTau) {
-        alpha = ex2_approx((m_used - mx) * kLog2e);
-        l *= alpha;
-        m_used = mx;
-        resc = j > 0;
-      }
-      const float mb = m_used * kLog2e;
-      float rs = 0.f;
+      float m_used = -INFINITY, l = 0.f;   // l: sum over this thread's columns only
+      for (int j = 0; j < nkt; ++j, ++g) {
+        const int bf = g & 1;
+        mbar_wait(s_full + 8 * bf, (uint32_t)((g >> 1) & 1));
+        tc_fence_after();
+        uint32_t sv[32];
+        tmem_ld_32x32(lane_addr + 64 * bf + 32 * half, sv);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(s_free + 8 * bf);
+        const float* bias = sBias + j * FK + 32 * half;
+        float mx = -INFINITY;
+        if (!(p.dbg & 1)) {
 #pragma unroll
-      for (int c = 0; c < 64; ++c) {
-        const float e = ex2_approx(fmaf(__uint_as_float(sv[c]), kLog2e, -mb));
-        rs += e;
-        sv[c] = __float_as_uint(e);
-      }
-      l += rs;
-      if (p.drop.thresh16) {
-        // counter layout of attn_dropout_rand: call t of 32-column group g covers columns 8 q + 2 t (low 16-bit lane of word q)
-        // and 8 q + 2 t + 1 (high lane); keep iff lane >= thresh16.  The 1 / (1 - p) scale is applied once, to O.
-        const uint32_t thi = p.drop.thresh16 << 16;
+          for (int c = 0; c < 32; ++c) {
+            const float v = fmaf(__uint_as_float(sv[c]), p.scale, bias[c]);
+            sv[c] = __float_as_uint(v);
+            mx = fmaxf(mx, v);
+          }
+        }
+        // the row maximum of the whole tile: exchange with the thread that holds the other 32 keys of this row
+        float* xch = sXch + bf * 256;
+        xch[half * 128 + r] = mx;
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
+        mx = fmaxf(mx, xch[(half ^ 1) * 128 + r]);
+        bool resc = false;
+        float alpha = 1.f;
+        if (mx > m_used + kRescaleTau) {
+          alpha = ex2_approx((m_used - mx) * kLog2e);
+          l *= alpha;
+          m_used = mx;
+          resc = j > 0;
+        }
+        const float mb = m_used * kLog2e;
+        float rs = 0.f;
+        if (!(p.dbg & 1)) {
 #pragma unroll
-        for (int g = 0; g < 2; ++g) {
+          for (int c = 0; c < 32; ++c) {
+            const float x = fmaf(__uint_as_float(sv[c]), kLog2e, -mb);
+            const float e = (p.dbg & 2) ? x : ex2_approx(x);
+            rs += e;
+            sv[c] = __float_as_uint(e);
+          }
+        }
+        l += rs;
+        if (p.drop.thresh16 && !(p.dbg & 1)) {
+          // counter layout of attn_dropout_rand: call t of 32-column group g covers columns 8 q + 2 t (low 16-bit lane of word q)
+          // and 8 q + 2 t + 1 (high lane); keep iff lane >= thresh16.  The 1 / (1 - p) scale is applied once, to O.
+          const uint32_t thi = p.drop.thresh16 << 16;
 #pragma unroll
           for (uint32_t t = 0; t < 4; ++t) {
-            const uint4 rr = attn_dropout_rand(p.drop, bh, (uint32_t)qi, (uint32_t)(j * 2 + g), t);
+            const uint4 rr = attn_dropout_rand(p.drop, bh, (uint32_t)qi, (uint32_t)(j * 2 + half), t);
             const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-              const int c0 = 32 * g + 8 * q + 2 * (int)t;
+              const int c0 = 8 * q + 2 * (int)t;
               if ((w[q] << 16) < thi) sv[c0] = 0u;
               if (w[q] < thi) sv[c0 + 1] = 0u;
             }
           }
         }
-      }
-      if (j > 0) {
-        mbar_wait(o_full, (uint32_t)((j - 1) & 1));
-        tc_fence_after();
         if (__any_sync(0xffffffffu, resc)) {
+          // O must hold exactly the item's tiles 0 .. j-1 while it is rescaled: P.V(g-1) complete (p_free of the other buffer),
+          // and P.V(g) cannot start before this warp's p_ready below.  Same rows, same decision in the partner warp: each
+          // rescales its 32 columns.
+          mbar_wait(p_free + 8 * (bf ^ 1), (uint32_t)(((g - 1) >> 1) & 1));
+          tc_fence_after();
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
-            uint32_t ov[32];
-            tmem_ld_32x32(lane_addr + 64 + 32 * hh, ov);
+            uint32_t ov[16];
+            tmem_ld_32x16(lane_o + 16 * hh, ov);
             tmem_ld_wait();
 #pragma unroll
-            for (int c = 0; c < 32; ++c) ov[c] = __float_as_uint(__uint_as_float(ov[c]) * alpha);
-            tmem_st_32x32(lane_addr + 64 + 32 * hh, ov);
+            for (int c = 0; c < 16; ++c) ov[c] = __float_as_uint(__uint_as_float(ov[c]) * alpha);
+            tmem_st_32x16(lane_o + 16 * hh, ov);
           }
           tmem_st_wait();
         }
-      }
-      // P row (64 keys = 128 B) into the K-major 128B-swizzled tile
+        if (g >= 2) mbar_wait(p_free + 8 * bf, (uint32_t)(((g - 2) >> 1) & 1));   // P.V(g-2) has read this P buffer
+        // this thread's 32 keys (64 B) of row r of the K-major 128B-swizzled P tile
 #pragma unroll
-      for (int ch = 0; ch < 8; ++ch) {
-        const uint32_t addr = sP + r * 128 + (((uint32_t)ch ^ (uint32_t)(r & 7)) << 4);
-        st_shared_v4(addr, pack_bf16(__uint_as_float(sv[8 * ch]), __uint_as_float(sv[8 * ch + 1])),
-                     pack_bf16(__uint_as_float(sv[8 * ch + 2]), __uint_as_float(sv[8 * ch + 3])),
-                     pack_bf16(__uint_as_float(sv[8 * ch + 4]), __uint_as_float(sv[8 * ch + 5])),
-                     pack_bf16(__uint_as_float(sv[8 * ch + 6]), __uint_as_float(sv[8 * ch + 7])));
+        for (int ch = 0; ch < 4; ++ch) {
+          const uint32_t addr = sP + bf * 16384 + r * 128 + (((uint32_t)(4 * half + ch) ^ (uint32_t)(r & 7)) << 4);
+          st_shared_v4(addr, pack_bf16(__uint_as_float(sv[8 * ch]), __uint_as_float(sv[8 * ch + 1])),
+                       pack_bf16(__uint_as_float(sv[8 * ch + 2]), __uint_as_float(sv[8 * ch + 3])),
+                       pack_bf16(__uint_as_float(sv[8 * ch + 4]), __uint_as_float(sv[8 * ch + 5])),
+                       pack_bf16(__uint_as_float(sv[8 * ch + 6]), __uint_as_float(sv[8 * ch + 7])));
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(p_ready + 8 * bf);
       }
-      fence_proxy_async();
+      // item epilogue.  Row sum = the two halves' sums (same reference maximum in both); third exchange buffer, so that it
+      // cannot collide with the tile buffers of the neighbouring tiles
+      float* xch = sXch + 512;
+      xch[half * 128 + r] = l;
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory");
+      l += xch[(half ^ 1) * 128 + r];
+      mbar_wait(p_free + 8 * ((g - 1) & 1), (uint32_t)(((g - 1) >> 1) & 1));   // the item's last P.V
+      tc_fence_after();
+      uint32_t ov[32];
+      tmem_ld_32x32(lane_o, ov);
+      tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(p_ready);
-    }
-    mbar_wait(o_full, (uint32_t)((nkt - 1) & 1));
-    tc_fence_after();
-    const float inv = 1.0f / l;
-    const float onorm = p.drop.thresh16 ? inv * p.drop.scale : inv;
-    bf16* dst = p.out + ((long long)row_base + qi) * p.hidden + h * 64;
-#pragma unroll
-    for (int hh = 0; hh < 2; ++hh) {
-      uint32_t ov[32];
-      tmem_ld_32x32(lane_addr + 64 + 32 * hh, ov);
-      tmem_ld_wait();
+      if (lane == 0) mbar_arrive(o_free);   // the next item's first P.V may overwrite O
+      const float inv = 1.0f / l;
+      const float onorm = p.drop.thresh16 ? inv * p.drop.scale : inv;
       if (qi < S) {
+        bf16* dst = p.out + ((long long)row_base + qi) * p.hidden + h * 64 + 32 * half;
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
           float f[8];
 #pragma unroll
           for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(ov[8 * ch + e]) * onorm;
-          *reinterpret_cast<uint4*>(dst + 32 * hh + 8 * ch) = pack8(f);
+          *reinterpret_cast<uint4*>(dst + 8 * ch) = pack8(f);
         }
+        if (half == 0) *reinterpret_cast<float2*>(p.lse + 2 * (((long long)b * p.heads + h) * S + qi)) = make_float2(m_used, inv);
       }
     }
-    if (qi < S) *reinterpret_cast<float2*>(p.lse + 2 * (((long long)b * p.heads + h) * S + qi)) = make_float2(m_used, inv);
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) tmem_dealloc(tmem_base, FWD_TMEM_COLS);
+  if (warp == FWD_SM_WARPS + 1) tmem_dealloc(tmem_base, FWD_TMEM_COLS);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -362,6 +443,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         for (int t = 0; t < nin; ++t, ++n) {
           const int st = n % BWD_NST;
           if (n >= BWD_NST) mbar_wait_backoff(in_empty + 8 * st, (uint32_t)((n / BWD_NST - 1) & 1), 64);
+          if ((p.dbg & 512) && n >= BWD_NST) { mbar_arrive(in_full + 8 * st); continue; }
           mbar_arrive_expect_tx(in_full + 8 * st, 2 * TILE16K);
           tma_load_2d(sQ + st * TILE16K, &tmQKV, in_full + 8 * st, h * 64, row_base + t * 128);
           tma_load_2d(sDO + st * TILE16K, &tmDO, in_full + 8 * st, h * 64, row_base + t * 128);
@@ -382,10 +464,12 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         // S = Q.K^T ; dP = dO.V^T   (A: query-side tile, B: key-side tile, both K-major over d = 64)
         const uint64_t qa = make_smem_desc(sQ + st * TILE16K, 16, 1024), kb = make_smem_desc(sK + kvb * TILE16K, 16, 1024);
         const uint64_t da = make_smem_desc(sDO + st * TILE16K, 16, 1024), vb = make_smem_desc(sV + kvb * TILE16K, 16, 1024);
+        if (!(p.dbg & 128)) {
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) umma_bf16(tmem_base, qa + (uint64_t)(2 * kk), kb + (uint64_t)(2 * kk), idesc_s, kk > 0 ? 1u : 0u);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) umma_bf16(tmem_base + 128, da + (uint64_t)(2 * kk), vb + (uint64_t)(2 * kk), idesc_s, kk > 0 ? 1u : 0u);
+        }
         umma_commit(sdp_full);
       };
       if (n_pairs > 0) {
@@ -413,12 +497,17 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         // apart, K = query rows 128 B apart), B = dO_t / Q_t read MN-major (K = query rows)
         const uint64_t pa = make_smem_desc(sPD, TILE16K, 1024), sa = make_smem_desc(sDS, TILE16K, 1024);
         const uint64_t dob = make_smem_desc(sDO + st * TILE16K, TILE16K, 1024), qb = make_smem_desc(sQ + st * TILE16K, TILE16K, 1024);
+        if (!(p.dbg & 16)) {
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 320, pa + (uint64_t)(128 * kk), dob + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
+        }
+        if (!(p.dbg & 32)) {
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 256, sa + (uint64_t)(128 * kk), qb + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
+        }
         // dQ_t partial = dS.K_j : A = dS K-major over 128 keys (two 64-key atoms), B = K_j MN-major (K = key rows)
         const uint64_t kmn = make_smem_desc(sK + kvb * TILE16K, TILE16K, 1024);
+        if (!(p.dbg & 64))
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint64_t dsa = make_smem_desc(sDS + (kk >> 2) * TILE16K + (kk & 3) * 32, 16, 1024);
@@ -457,7 +546,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(dq_free + 8 * dqb);
-      if (dst) {
+      if (dst && !(p.dbg & 256)) {
         uint4* d = reinterpret_cast<uint4*>(dst);
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
@@ -533,6 +622,11 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
             __syncwarp();
             if (lane == 0) mbar_arrive(sdp_free);
           }
+          if (p.dbg & 1) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { pk_p[hf][i] = sv[i]; pk_d[hf][i] = dv[i]; }
+            continue;
+          }
 #pragma unroll
           for (int t2 = 0; t2 < 2; ++t2) {
             const uint32_t tt = (uint32_t)(2 * hf + t2);
@@ -547,7 +641,8 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
                 const int cc = 8 * q + 2 * (int)tt + e;     // column within the warp's 32
                 const int ix = 4 * q + 2 * t2 + e;
                 const float v = fmaf(__uint_as_float(sv[ix]), p.scale, bias[cc]);
-                const float pr = ex2_approx(fmaf(v, kLog2e, -mb)) * inv;
+                const float x = fmaf(v, kLog2e, -mb);
+                const float pr = ((p.dbg & 2) ? x : ex2_approx(x)) * inv;
                 const bool keep = e == 0 ? ((w[q] << 16) >= thi) : (w[q] >= thi);
                 const float dpm = keep ? __uint_as_float(dv[ix]) : 0.f;
                 pe[e] = keep ? pr : 0.f;
@@ -650,6 +745,12 @@ static int check_attn_tc(const char* who, const void* qkv, int64_t ld, int64_t B
   return VT_OK;
 }
 
+static int attn_dbg() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("VT_ATTN_DBG"); v = e ? atoi(e) : 0; }
+  return v;
+}
+
 static bool use_tc(int64_t S) { return g_attn_impl == 2 || (g_attn_impl == 0 && S <= 2048); }
 
 extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, int64_t B, int64_t S, int64_t heads, int64_t head_dim,
@@ -661,6 +762,7 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
   rc = resolve_driver_entry_points();
   if (rc) return rc;
   VT_REQUIRE(((uintptr_t)ctx & 15) == 0, "vt_attention_fwd: ctx must be 16-byte aligned");
+  VT_REQUIRE(S <= FWD_MAX_S, "vt_attention_fwd: the tcgen05 kernel keeps the mask bias of a sample in shared memory (S <= %d)", FWD_MAX_S);
   const int64_t hidden = heads * 64;
   CUtensorMap tq, tkv;
   rc = make_map(&tq, qkv, (uint64_t)(3 * hidden), (uint64_t)(B * S), (uint64_t)ld, 64, FQ);
@@ -671,14 +773,17 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
   p.B = (int)B; p.S = (int)S; p.heads = (int)heads; p.hidden = (int)hidden;
   p.bias = bias; p.scale = 0.125f; p.out = (bf16*)ctx; p.lse = lse; p.ld = ld;
   p.drop = make_dropout(dropout_p, seed, dropout_stream);
+  p.dbg = attn_dbg();
   const int nkt = (int)((S + FK - 1) / FK);
-  const size_t smem = 1024 + FWD_SMEM_TILES + 128 + (size_t)nkt * FK * sizeof(float);
+  const size_t smem = 1024 + FWD_SMEM_TILES + 256 + 3072 + (size_t)nkt * FK * sizeof(float);
   static bool attr = false;
   if (!attr) {
-    VT_CUDA(cudaFuncSetAttribute(attn_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 + FWD_SMEM_TILES + 128 + 2048 * 4 + 256));
+    VT_CUDA(cudaFuncSetAttribute(attn_fwd_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 + FWD_SMEM_TILES + 256 + 3072 + FWD_MAX_S * 4 + 256));
     attr = true;
   }
-  attn_fwd_tc<<<dim3((unsigned)((S + FQ - 1) / FQ), (unsigned)heads, (unsigned)B), FWD_THREADS, smem, st>>>(tq, tkv, p);
+  const long long n_items = ((S + FQ - 1) / FQ) * heads * B;
+  const long long ctas = (FWD_PERSISTENT || (p.dbg & 32768)) ? 2ll * usable_sms() : n_items;   // persistent: two CTAs per SM, each a contiguous range of items
+  attn_fwd_tc<<<(unsigned)(n_items < ctas ? n_items : ctas), FWD_THREADS, smem, st>>>(tq, tkv, p);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -710,6 +815,7 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
   p.bias = bias; p.scale = 0.125f; p.lse = const_cast<float*>(lse); p.dsum = dsum_ws; p.dq_ws = reinterpret_cast<bf16*>(dsum_ws + dsum_floats);
   p.dqkv = (bf16*)dqkv; p.ld = ld;
   p.drop = make_dropout(dropout_p, seed, dropout_stream);
+  p.dbg = attn_dbg();
   VT_REQUIRE(((uintptr_t)dsum_ws & 15) == 0, "vt_attention_bwd: workspace must be 16-byte aligned");
   const size_t smem = 1024 + BWD_SMEM_TILES + 256 + 2 * 128 * sizeof(float);
   static bool attr = false;
