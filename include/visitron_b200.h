@@ -246,6 +246,31 @@ int vt_bce_logits_fwd(const float* q, const float* target, const uint8_t* valid,
 int vt_bce_logits_bwd(const float* q, const float* target, const uint8_t* valid, int64_t B, float pos_weight, const float* out2,
                       const float* g, float* dq, vt_stream stream);
 
+/* ---- the step after backward: multi-tensor AdamW and gradient-norm clipping ----
+ * Replace transformers/pytorch_transformers/optimization.py:141-189 (AdamW.step, ~10 ATen launches per parameter) and
+ * torch.nn.utils.clip_grad_norm_ at tasks/viewpoint_select/agent.py:514-518.
+ * A segment table lives in DEVICE memory (the caller builds it once and reuses it while the pointers stay put): */
+typedef struct {
+  float* p;            /* parameter (fp32 master), n elements */
+  float* g;            /* its gradient */
+  float* m;            /* exp_avg */
+  float* v;            /* exp_avg_sq */
+  int64_t n;
+  int32_t group;       /* parameter group 0..7: selects step_size[] / lr_decay[] */
+  int32_t first_chunk; /* prefix sum of ceil(n / vt_opt_chunk()) over the preceding segments */
+} vt_opt_segment;
+int64_t vt_opt_chunk(void);
+/* One launch for every segment: m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= step_size[group] m / (sqrt(v) + eps);
+ * p -= lr_decay[group] p  (step_size = lr sqrt(1-b2^t)/(1-b1^t) with correct_bias, else lr; lr_decay = lr * weight_decay; host arrays).
+ * beta1 / beta2 / eps are doubles so that (1 - beta) is formed exactly as the reference's Python scalars form it.
+ * grad_scale_dev: optional device scalar multiplied into every gradient on the fly (the clip coefficient below). */
+int vt_adamw_step(const void* segments_dev, int64_t n_segments, int64_t n_chunks, int64_t n_groups, const float* step_size,
+                  const float* lr_decay, double beta1, double beta2, double eps, const float* grad_scale_dev, vt_stream stream);
+/* norm_and_coef[0] = L2 norm over all segments' gradients (deterministic), [1] = min(1, max_norm / (norm + 1e-6));
+ * partials: fp32 [n_chunks] workspace; scale_in_place != 0 multiplies the gradients by the coefficient (clip_grad_norm_). */
+int vt_clip_grad_norm(const void* segments_dev, int64_t n_segments, int64_t n_chunks, float max_norm, float* partials,
+                      float* norm_and_coef, int scale_in_place, vt_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -155,6 +155,36 @@ def gen_heads(ns, name, seed):
     print(name, fix["candidate"]["loss"], fix["turn"]["loss"], fix["qa"]["loss"])
 
 
+def gen_adamw(ns, name, seed):
+    """The reference's AdamW + WarmupLinearSchedule (pytorch_transformers/optimization.py) for 4 steps on seeded tensors in the two
+    parameter groups of vs/pretrain.py:109-127, and torch's clip_grad_norm_ as vs/agent.py:514-518 calls it."""
+    g = torch.Generator().manual_seed(seed)
+    shapes = [(37, 19), (5,), (1023,), (64, 33), (1,), (8200,)]
+    p0 = [0.1 * torch.randn(*s, generator=g) for s in shapes]
+    grads = [[torch.randn(*s, generator=g) * (0.5 + i) for s in shapes] for i in range(4)]
+    params = [torch.nn.Parameter(t.clone()) for t in p0]
+    groups = [dict(params=params[0::2], weight_decay=0.05), dict(params=params[1::2], weight_decay=0.0)]
+    opt = ns.optimization.AdamW(groups, lr=1e-3, eps=1e-6)
+    sched = ns.optimization.WarmupLinearSchedule(opt, warmup_steps=2, t_total=6)
+    lrs = []
+    for i in range(4):
+        for p, gr in zip(params, grads[i]):
+            p.grad = gr.clone()
+        lrs.append([grp["lr"] for grp in opt.param_groups])
+        opt.step()
+        sched.step()
+    clip_in = [t.clone() for t in grads[1]]
+    holders = [torch.nn.Parameter(torch.zeros_like(t)) for t in clip_in]
+    for h, t in zip(holders, clip_in):
+        h.grad = t.clone()
+    norm = torch.nn.utils.clip_grad_norm_(holders, 40.0)
+    fix = dict(seed=seed, shapes=shapes, p0=p0, grads=grads, lrs=lrs, p=[p.detach().clone() for p in params],
+               m=[opt.state[p]["exp_avg"].clone() for p in params], v=[opt.state[p]["exp_avg_sq"].clone() for p in params],
+               clip_norm=float(norm), clipped=[h.grad.clone() for h in holders])
+    torch.save(fix, os.path.join(GOLDEN, name + ".pt"))
+    print(name, lrs, float(norm))
+
+
 def main():
     if not ref_shim.available():
         raise SystemExit("reference tree not mounted; fixtures can only be generated in the build container")
@@ -166,6 +196,7 @@ def main():
     gen_pretrain(ns, "pretrain_small_imgln", small_cfg(use_img_layernorm=1), 8, dict(bk, seed=89))
     gen_finetune(ns, "finetune_small", small_cfg(), 9, dict(batch=2, seed=90, text_len=48, vocab=2048))
     gen_heads(ns, "heads_small", 11)
+    gen_adamw(ns, "adamw_small", 13)
 
 
 if __name__ == "__main__":

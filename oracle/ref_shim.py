@@ -49,6 +49,7 @@ def load():
     sys.path[:0] = [REFERENCE_ROOT, vs]
     try:
         hf = importlib.import_module("transformers.pytorch_transformers.modeling_bert")
+        opt = importlib.import_module("transformers.pytorch_transformers.optimization")
         enc = importlib.import_module("encoder")            # tasks/viewpoint_select/encoder.py
         vs_models = importlib.import_module("agent_models")  # tasks/viewpoint_select/agent_models.py
         spec = importlib.util.spec_from_file_location("tb_agent_models", os.path.join(tb, "agent_models.py"))
@@ -58,7 +59,7 @@ def load():
         sys.path.remove(REFERENCE_ROOT)
         sys.path.remove(vs)
     ns = types.SimpleNamespace(
-        BertConfig=hf.BertConfig, hf=hf, encoder=enc, vs_models=vs_models, tb_models=tb_models,
+        BertConfig=hf.BertConfig, hf=hf, optimization=opt, encoder=enc, vs_models=vs_models, tb_models=tb_models,
         PreTrainOscar=enc.PreTrainOscar, BertImgModelwithLocationEmbeds=enc.BertImgModelwithLocationEmbeds)
     _loaded["ns"] = ns
     # keep the vendored namespace registered under a private alias and restore the real package

@@ -354,6 +354,40 @@ def init_head_params(seed: int, hidden: int = 512, feat: int = 2052) -> Params:
 
 
 # --------------------------------------------------------------------------------------------
+# the step after backward
+# --------------------------------------------------------------------------------------------
+def adamw_update(p, g, m, v, step: int, lr: float, beta1=0.9, beta2=0.999, eps=1e-6, weight_decay=0.0, correct_bias=True):
+    """One AdamW update of one tensor, transformers/pytorch_transformers/optimization.py:165-187: moments, eps OUTSIDE
+    the square root, optional bias correction folded into the step size, then the decoupled decay with the
+    un-corrected lr applied to the already updated weights.  ``step`` is the 1-based update count.
+    Returns new (p, m, v); inputs are not modified."""
+    m = m * beta1 + (1.0 - beta1) * g
+    v = v * beta2 + (1.0 - beta2) * g * g
+    denom = v.sqrt() + eps
+    step_size = lr
+    if correct_bias:
+        step_size = step_size * math.sqrt(1.0 - beta2 ** step) / (1.0 - beta1 ** step)
+    p = p - step_size * (m / denom)
+    if weight_decay > 0.0:
+        p = p - lr * weight_decay * p
+    return p, m, v
+
+
+def warmup_linear(step: int, warmup_steps: int, t_total: int) -> float:
+    """WarmupLinearSchedule.lr_lambda, optimization.py:59-62."""
+    if step < warmup_steps:
+        return float(step) / float(max(1, warmup_steps))
+    return max(0.0, float(t_total - step) / float(max(1.0, t_total - warmup_steps)))
+
+
+def clip_grad_norm(grads, max_norm: float):
+    """torch.nn.utils.clip_grad_norm_ (L2) as called at vs/agent.py:514-518: returns (total norm, scaled grads)."""
+    total = torch.sqrt(sum((g.double() ** 2).sum() for g in grads)).float()
+    coef = torch.clamp(max_norm / (total + 1e-6), max=1.0)
+    return total, [g * coef for g in grads]
+
+
+# --------------------------------------------------------------------------------------------
 # helpers for tests / bench
 # --------------------------------------------------------------------------------------------
 def clone_params(P: Params, requires_grad=True, dtype=None, device=None) -> Params:

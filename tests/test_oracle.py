@@ -141,3 +141,28 @@ def test_mask_quantisation_f6():
     assert float(ext[0, 0, 0, 0]) == 2540000.0
     s = torch.tensor([0.1, 0.2, 0.3, 0.45]) + ext[0, 0, 0]
     assert torch.equal(s - 2540000.0, torch.tensor([0.0, 0.25, 0.25, 0.5]))
+
+
+def test_adamw_oracle_matches_reference_fixture():
+    """oracle.adamw_update / warmup_linear / clip_grad_norm against the reference's AdamW + WarmupLinearSchedule run
+    (tests/golden/adamw_small.pt, generated by oracle/make_golden.py from pytorch_transformers/optimization.py)."""
+    fix = torch.load(os.path.join(GOLDEN, "adamw_small.pt"), weights_only=False)
+    n = len(fix["shapes"])
+    p = [t.clone() for t in fix["p0"]]
+    m = [torch.zeros_like(t) for t in p]
+    v = [torch.zeros_like(t) for t in p]
+    for step in range(4):
+        lr = 1e-3 * vo.warmup_linear(step, 2, 6)
+        assert abs(lr - fix["lrs"][step][0]) < 1e-12
+        for i in range(n):
+            wd = 0.05 if i % 2 == 0 else 0.0   # groups: params[0::2] decay, params[1::2] none
+            p[i], m[i], v[i] = vo.adamw_update(p[i], fix["grads"][step][i], m[i], v[i], step + 1, lr, eps=1e-6, weight_decay=wd)
+    for i in range(n):
+        # fp32 rounding only (the restatement is functional, the reference updates in place): a few ulps
+        torch.testing.assert_close(p[i], fix["p"][i], rtol=2e-6, atol=2e-7)
+        torch.testing.assert_close(m[i], fix["m"][i], rtol=2e-6, atol=2e-7)
+        torch.testing.assert_close(v[i], fix["v"][i], rtol=2e-6, atol=2e-7)
+    norm, clipped = vo.clip_grad_norm(fix["grads"][1], 40.0)
+    assert abs(float(norm) - fix["clip_norm"]) < 1e-4 * fix["clip_norm"]
+    for a, b in zip(clipped, fix["clipped"]):
+        torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-7)

@@ -1,7 +1,7 @@
 """argtypes / restype for every symbol declared in include/visitron_b200.h."""
 import ctypes as C
 
-P, I, I64, F, U64, U32 = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_uint64, C.c_uint32
+P, I, I64, F, U64, U32, D = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_uint64, C.c_uint32, C.c_double
 
 SIGNATURES = {
     "vt_init": (I, [I]),
@@ -46,6 +46,9 @@ SIGNATURES = {
     "vt_head_ce_bwd": (I, [P, I64, I64, I64, P, I64, P, P, P, P, I64, P]),
     "vt_bce_logits_fwd": (I, [P, P, P, I64, F, P, P, P]),
     "vt_bce_logits_bwd": (I, [P, P, P, I64, F, P, P, P, P]),
+    "vt_opt_chunk": (I64, []),
+    "vt_adamw_step": (I, [P, I64, I64, I64, P, P, D, D, D, P, P]),
+    "vt_clip_grad_norm": (I, [P, I64, I64, F, P, P, I, P]),
 }
 
 
