@@ -20,7 +20,6 @@ import argparse
 import json
 import os
 import statistics
-import subprocess
 import sys
 import threading
 import time
@@ -59,44 +58,55 @@ def peaks():
 
 
 class ClockSampler:
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock / power / throttle reasons DURING the timed region, sampled in-process through NVML every 50 ms.
+    (A `nvidia-smi -lms` subprocess started at the top of the timed region was tried first: its start-up and queries contend
+    for the driver with the kernel launches and slowed the region it was observing by 5-300 %.)"""
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.rows, self.on, self.alive, self.h, self.nv = [], False, False, None, None
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            pr = torch.cuda.get_device_properties(index)
+            bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+            self.h, self.nv = nv.nvmlDeviceGetHandleByPciBusId(bus.encode()), nv
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
+            self.alive = True
+            self.t = threading.Thread(target=self._run, daemon=True)
+            self.t.start()
+        except Exception as e:   # no NVML: say so in the JSON line
+            self.err = "%s: %s" % (type(e).__name__, e)
+
+    def _one(self):
+        nv = self.nv
+        try:
+            mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        except Exception:
+            mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        return (float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)), nv.nvmlDeviceGetPowerUsage(self.h) / 1e3, int(mask))
+
+    def _run(self):
+        while self.alive:
+            if self.on:
+                try:
+                    self.rows.append(self._one())
+                except Exception:
+                    pass
+            time.sleep(0.05)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
-        except Exception:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+        self.rows, self.on = [], True
 
     def stop(self):
-        if not self.proc:
-            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, mx, pw, reasons = [], [], [], set()
-        for r in self.rows:
-            try:
-                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
-            except Exception:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return dict(sm_mhz=statistics.median(sm) if sm else None, sm_max_mhz=max(mx) if mx else None,
-                    power_w_max=max(pw) if pw else None, samples=len(sm), reasons=sorted(reasons))
+        self.on = False
+        if self.h is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["NVML unavailable (%s)" % getattr(self, "err", "?")])
+        rows = list(self.rows)
+        reasons = sorted({name for _, _, m in rows for bit, name in self.REASONS if m & bit})
+        sm = [r[0] for r in rows]
+        return dict(sm_mhz=statistics.median(sm) if sm else None, sm_max_mhz=self.max_mhz, power_w_max=max((r[1] for r in rows), default=None),
+                    samples=len(rows), reasons=reasons)
 
 
 def build_model(args, device):
@@ -105,7 +115,7 @@ def build_model(args, device):
     cfg = BertConfig(V, hidden_dropout_prob=args.dropout, attention_probs_dropout_prob=0.1 if args.dropout > 0 else 0.0)
     cfg.img_feature_dim, cfg.detector_classes, cfg.action_space = IMG, DC, A
     torch.manual_seed(88)
-    if args.workload == "viewpoint_select":
+    if args.workload != "pretrain":
         model = modeling.BertImgModelwithLocationEmbeds(cfg)   # what train.py hands the agent as `model.bert` (vs/train.py:47)
     else:
         model = modeling.PreTrainOscar(cfg)     # random-init bert-base (hf/modeling_bert.py:550-561), no checkpoint
@@ -113,6 +123,7 @@ def build_model(args, device):
 
 
 VS_STEPS, VS_CAND, VS_FEAT, VS_HID = 10, 12, 2052, 512   # decoder steps, candidates incl. STOP, 2048+4 features, LSTM width
+TB_STEPS = 40                                            # turn_based episode length (run_scripts/turn_based_train/ndh_rxr.sh)
 
 
 class Workload:
@@ -124,6 +135,7 @@ class Workload:
         self.model = build_model(args, device)
         b, n_host = args.batch, 4
         self.extra_params = []
+        self.flop_mult = 3.0   # forward + backward
         if args.workload == "viewpoint_select":
             # BASELINE configs[1]: the encoder call of OscarEncoder (A13, S = 511 text-only, token types, the ~uint8 mask)
             # + the candidate scorer with its masked CE (A14) at each of the 10 decoder steps.  The stock torch.nn LSTM
@@ -146,6 +158,45 @@ class Workload:
             self.desc = ("viewpoint_select_step: BertImgModelwithLocationEmbeds fwd+bwd as OscarEncoder calls it (T=511 text-only, token types, "
                          "~uint8 mask) + SoftDotAttention candidate scorer + masked CE at 10 decoder steps (12 candidates x 2052), bert-base "
                          "random init [BASELINE configs[1]; the stock LSTM encoder/decoder of the agent is not part of the path, SURVEY 8f-N1]")
+        elif args.workload in ("turn_based", "qa_classifier"):
+            # BASELINE configs[3]: the encoder at the full RxR text length + the turn-based head (context attention over the 511
+            # positions -> h~ -> 6-way logits, forward masked where no location is navigable, CE(ignore 7)) at 40 decoder steps.
+            # BASELINE configs[4]: the encoder forward-only under no_grad + question_linear / masked BCE forward + backward
+            # (vs/classifier/agent.py:158-163,493-503), swept over --batch.  The agent's LSTM encoder / decoder is
+            # stood in for by slices of sequence_output as in viewpoint_select.
+            g = torch.Generator().manual_seed(88)
+            mk = lambda *s: torch.nn.Parameter((0.05 * torch.randn(*s, generator=g)).to(device))  # noqa: E731
+            if args.workload == "turn_based":
+                self.tb = dict(w_in=mk(VS_HID, VS_HID), w_out=mk(VS_HID, 2 * VS_HID), w_a=mk(6, VS_HID), b_a=mk(6))
+                self.extra_params = list(self.tb.values())
+            else:
+                self.qa = dict(w1=mk(VS_HID // 2, VS_HID), b1=mk(VS_HID // 2), w2=mk(1, VS_HID // 2), b2=mk(1))
+                self.extra_params = list(self.qa.values())
+            host = []
+            for i in range(n_host):
+                hb = synthetic.finetune_encoder_batch(b, seed=88 + rank + 1000 * i, valid_len=511)
+                gi = torch.Generator().manual_seed(88 + rank + 1000 * i)
+                if args.workload == "turn_based":
+                    hb["no_forward"] = torch.rand(TB_STEPS, b, generator=gi) < 0.25
+                    tgt = torch.randint(0, 6, (TB_STEPS, b), generator=gi)
+                    hb["target"] = torch.where(hb["no_forward"] & (tgt == 0), torch.ones_like(tgt), tgt)
+                    hb["target"][:, -1] = 7   # an ended episode: <ignore>
+                else:
+                    hb["target"] = (torch.rand(b, generator=gi) < 0.4).float()
+                    hb["valid"] = (torch.rand(b, generator=gi) >= 0.25).to(torch.uint8)
+                host.append(hb)
+            self.S, self.R = 511, 0
+            self.labelled = (0.0, 0.0)
+            if args.workload == "turn_based":
+                self.heads_flops = TB_STEPS * 2 * (VS_HID * VS_HID + 2 * 511 * VS_HID + 2 * VS_HID * VS_HID + 6 * VS_HID)
+                self.desc = ("turn_based_step: encoder fwd+bwd at the full RxR text length (T=511 valid tokens) + turn-based head (SoftDotAttention over "
+                             "the 511 context positions, tanh(W_out[.;h]), 6-way logits, forward masked, CE ignore 7) at 40 decoder steps, bert-base "
+                             "random init [BASELINE configs[3]; LSTM encoder/decoder stood in for by slices of sequence_output, SURVEY 8f-N1]")
+            else:
+                self.heads_flops = 2 * (VS_HID * VS_HID // 2 + VS_HID // 2)
+                self.flop_mult = 1.0
+                self.desc = ("qa_classifier_step: encoder forward-only under no_grad (T=511) + question_linear (512->256->1, tanh) with "
+                             "BCEWithLogits(pos_weight 5) masked mean, forward + backward [BASELINE configs[4]: sweep --batch]")
         else:
             host = [synthetic.pretrain_batch(b, seed=88 + rank + 1000 * i) for i in range(n_host)]  # per-rank shard, seed 88+rank
             self.S, self.R = 767, 256
@@ -163,10 +214,33 @@ class Workload:
     def step(self, batch):
         for p in self.params:
             p.grad = None
-        if self.args.workload != "viewpoint_select":
+        wk = self.args.workload
+        if wk == "pretrain":
             out = self.model(**batch)
             out[0].backward()
             return out
+        if wk == "qa_classifier":
+            with torch.no_grad():   # vs/classifier: the encoder is frozen
+                seq, _ = self.model(batch["input_ids"], token_type_ids=batch["token_type_ids"], attention_mask=batch["attention_mask"])
+            q = self.qa
+            _, loss = self._heads.qa_head(q["w1"], q["b1"], q["w2"], q["b2"], seq[:, 0, :VS_HID], batch["target"], batch["valid"])
+            loss.backward()
+            return (loss,)
+        if wk == "turn_based":
+            seq, _ = self.model(batch["input_ids"], token_type_ids=batch["token_type_ids"], attention_mask=batch["attention_mask"])
+            ctx = seq[:, :, :VS_HID].contiguous()
+            ctx_mask = torch.zeros(ctx.shape[:2], dtype=torch.bool, device=ctx.device)
+            t_ = self.tb
+            loss = None
+            for t in range(TB_STEPS):
+                _, _, l, _ = self._heads.turn_based_head(t_["w_in"], t_["w_out"], t_["w_a"], t_["b_a"], seq[:, t, :VS_HID], ctx, ctx_mask,
+                                                         batch["no_forward"][t], batch["target"][t])
+                loss = l if loss is None else loss + l
+            loss.backward()
+            if self.world > 1:
+                for p in self.extra_params:
+                    torch.distributed.all_reduce(p.grad, op=torch.distributed.ReduceOp.AVG)
+            return (loss,)
         seq, _ = self.model(batch["input_ids"], token_type_ids=batch["token_type_ids"], attention_mask=batch["attention_mask"])
         loss = None
         for t in range(VS_STEPS):
@@ -195,6 +269,9 @@ def run_ours(args):
             raise SystemExit("--gpus %d needs torchrun (one process per GPU)" % args.gpus)
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    saved_stdout = os.dup(1)
+    sys.stdout.flush()
+    os.dup2(2, 1)   # NCCL prints its version banner on stdout: stdout carries ONE JSON line, everything else goes to stderr
     if world > 1:
         torch.distributed.init_process_group("nccl", device_id=device)
     wl = Workload(args, device, rank, world)
@@ -226,10 +303,19 @@ def run_ours(args):
             ms = float(t)
         return ms
 
-    for i in range(max(args.warmup, 3)):
-        step(dev_batches[i % n_host])
+    # warm-up: at least 3 steps AND every rotating batch once (their labelled-row counts differ, so a batch seen for the first
+    # time inside the timed region would pay the caching allocator's cudaMalloc there)
+    # ... and for at least --min-warm-s of wall time: the first ~0.2 s after a cold start run below the steady clocks (a timed
+    # region right behind 3 steps measured 10-25 % low against the same region a second later)
+    sampler = ClockSampler(local) if (rank == 0 and not args.no_clocks) else None   # NVML is initialised here, well before the timed region
+    n_warm, t0 = 0, time.perf_counter()
+    while n_warm < max(args.warmup, 3, n_host + 1) or time.perf_counter() - t0 < args.min_warm_s:
+        step(dev_batches[n_warm % n_host])
+        torch.cuda.synchronize()
+        n_warm += 1
+        if n_warm == 1:
+            t0 = time.perf_counter()   # the first step carries module loading and allocator growth: the clock starts after it
     # ---- device-resident throughput (`value`) ----
-    sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
     lib.reset_launch_count()
@@ -288,12 +374,13 @@ def run_ours(args):
     # ---- the step after backward, reported separately (the metric is fwd+bwd): fused AdamW, one launch ----
     from visitron_b200 import optimization as vopt
     no_decay = ["bias", "LayerNorm.weight"]
-    named = [(n, p) for n, p in model.named_parameters() if p.grad is not None]
+    named = [(n, p) for n, p in model.named_parameters() if p.grad is not None] + [("head.weight", p) for p in wl.extra_params if p.grad is not None]
     opt = vopt.AdamW([dict(params=[p for n, p in named if not any(nd in n for nd in no_decay)], weight_decay=0.01),
                       dict(params=[p for n, p in named if any(nd in n for nd in no_decay)], weight_decay=0.0)], lr=5e-5, eps=1e-8)
     opt.step()
     opt_ms = timed(lambda i: opt.step(), 5) / 5
     opt_elems = sum(p.numel() for _, p in named)
+    # (qa_classifier updates only the 131 k parameters of question_linear: the figure is launch latency there)
 
     if rank != 0:
         if world > 1:
@@ -304,7 +391,7 @@ def run_ours(args):
     n_out = 7 if args.workload == "pretrain" else 1
     pk = peaks()
     line = dict(
-        metric=METRIC, value=round(value, 2), unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
+        metric=METRIC, value=round(value, 2), unit=UNIT, n_gpus=world, steps=args.steps, warmup=n_warm,
         ms_per_step=round(ms / args.steps, 3), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16",
         data="synthetic",
         config=dict(workload=wl.desc,
@@ -315,11 +402,11 @@ def run_ours(args):
                  ms_per_step=round(e2e_ms / args.steps, 3)),
         gpu_launches=int(launches),
         clocks=clocks,
-        model_flops=dict(per_sample_fwd_bwd_all_rows_GF=round(3 * fl["total"] / 1e9, 1),
-                         per_sample_fwd_bwd_executed_GF=round(3 * fl_done["total"] / 1e9, 1),
-                         achieved_TFLOPs_per_gpu_all_rows=round(value / world * 3 * fl["total"] / 1e12, 1),
-                         achieved_TFLOPs_per_gpu_executed=round(value / world * 3 * fl_done["total"] / 1e12, 1),
-                         frac_of_peak_executed=round(value / world * 3 * fl_done["total"] / 1e12 / pk["tflops"], 4),
+        model_flops=dict(per_sample_fwd_bwd_all_rows_GF=round(wl.flop_mult * fl["total"] / 1e9, 1),
+                         per_sample_fwd_bwd_executed_GF=round(wl.flop_mult * fl_done["total"] / 1e9, 1),
+                         achieved_TFLOPs_per_gpu_all_rows=round(value / world * wl.flop_mult * fl["total"] / 1e12, 1),
+                         achieved_TFLOPs_per_gpu_executed=round(value / world * wl.flop_mult * fl_done["total"] / 1e12, 1),
+                         frac_of_peak_executed=round(value / world * wl.flop_mult * fl_done["total"] / 1e12 / pk["tflops"], 4),
                          labelled_rows_per_sample=dict(mlm=round(labelled[0], 1), token=round(labelled[1], 1))),
     )
     line["optimizer"] = dict(kernel="adamw_kernel (multi-tensor, 1 launch)", ms_per_step=round(opt_ms, 3), elements=opt_elems,
@@ -327,9 +414,12 @@ def run_ours(args):
                              note="not part of `value` (metric is fwd+bwd); 28 algorithmic bytes per element (read p,g,m,v; write p,m,v)")
     if roof:
         line["roofline"] = roof
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline and args.workload in ("pretrain", "viewpoint_select"):
         line["cpu_baseline"] = cpu_baseline(args, steps=2)
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
+    os.dup2(2, 1)
     if world > 1:
         torch.distributed.destroy_process_group()
 
@@ -396,8 +486,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=32, help="per-GPU batch (the reference scripts use 2; 32 fills the tensor cores)")
     ap.add_argument("--dropout", type=float, default=0.3, help="hidden dropout (run_scripts/pretrain/pretrain_ndh_r2r.sh:43 uses 0.3)")
-    ap.add_argument("--workload", default="pretrain", choices=["pretrain", "viewpoint_select"],
-                    help="pretrain = BASELINE configs[2] (the data-parallel headline); viewpoint_select = configs[1] (encoder at S=511 + candidate scorer)")
+    ap.add_argument("--workload", default="pretrain", choices=["pretrain", "viewpoint_select", "turn_based", "qa_classifier"],
+                    help="pretrain = BASELINE configs[2] (the data-parallel headline); viewpoint_select = configs[1] (encoder at S=511 + candidate scorer); "
+                         "turn_based = configs[3]; qa_classifier = configs[4] (sweep --batch)")
+    ap.add_argument("--min-warm-s", type=float, default=1.0, help="keep warming up until this much wall time has passed")
+    ap.add_argument("--no-clocks", action="store_true", help="diagnosis: do not sample clocks during the timed region")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     args = ap.parse_args()
