@@ -61,6 +61,10 @@ class FlatStore:
         self._grad: List[Optional[torch.Tensor]] = [None, None]
         self._versions = None
         self._cur = 0
+        # view caches (a step asks for ~400 parameter / operand / gradient views; slicing + view cost ~4 us each on the host)
+        self._wc: Dict = {}
+        self._wbc: Dict = {}
+        self._gc: List[Dict] = [{}, {}]
 
     # ------------------------------------------------------------------------------------
     def _aliased(self) -> bool:
@@ -95,6 +99,7 @@ class FlatStore:
         self.bf16 = None
         self._grad = [None, None]
         self._versions = None
+        self._wc, self._wbc, self._gc = {}, {}, [{}, {}]
         return self
 
     def refresh_bf16(self) -> None:
@@ -104,33 +109,50 @@ class FlatStore:
             return
         if self.bf16 is None:
             self.bf16 = torch.empty(self.total, dtype=torch.bfloat16, device=self.flat.device)
+            self._wbc = {}
         ops.to_bf16(self.flat, out=self.bf16)
         self._versions = vers
 
     # ------------------------------------------------------------------------------------
     def w(self, name: str) -> torch.Tensor:
-        o = self.offset[name]
-        return self.flat[o: o + self.numel[name]].view(self.shape[name])
+        t = self._wc.get(name)
+        if t is None:
+            o = self.offset[name]
+            t = self._wc[name] = self.flat[o: o + self.numel[name]].view(self.shape[name])
+        return t
 
     def wb(self, name: str, rows: Optional[int] = None, cols: Optional[int] = None) -> torch.Tensor:
         """bf16 operand view; (rows, cols) overrides the shape to span adjacent parameters."""
-        o = self.offset[name]
-        if rows is None:
-            return self.bf16[o: o + self.numel[name]].view(self.shape[name])
-        return self.bf16[o: o + rows * cols].view(rows, cols)
+        key = (name, rows, cols)
+        t = self._wbc.get(key)
+        if t is None:
+            o = self.offset[name]
+            if rows is None:
+                t = self.bf16[o: o + self.numel[name]].view(self.shape[name])
+            else:
+                t = self.bf16[o: o + rows * cols].view(rows, cols)
+            self._wbc[key] = t
+        return t
 
     def wspan(self, name: str, n: int) -> torch.Tensor:
         o = self.offset[name]
         return self.flat[o: o + n]
 
     def g(self, name: str, rows: Optional[int] = None, cols: Optional[int] = None) -> torch.Tensor:
-        buf = self._grad[self._cur]
-        o = self.offset[name]
-        if rows is None:
-            return buf[o: o + self.numel[name]].view(self.shape[name])
-        if cols is None:
-            return buf[o: o + rows]
-        return buf[o: o + rows * cols].view(rows, cols)
+        cache = self._gc[self._cur]
+        key = (name, rows, cols)
+        t = cache.get(key)
+        if t is None:
+            buf = self._grad[self._cur]
+            o = self.offset[name]
+            if rows is None:
+                t = buf[o: o + self.numel[name]].view(self.shape[name])
+            elif cols is None:
+                t = buf[o: o + rows]
+            else:
+                t = buf[o: o + rows * cols].view(rows, cols)
+            cache[key] = t
+        return t
 
     def grad_bucket(self, i: int) -> torch.Tensor:
         s, e = self.buckets[i]
@@ -157,6 +179,7 @@ class FlatStore:
                     break
         if self._grad[k] is None:
             self._grad[k] = torch.empty(self.total, dtype=torch.float32, device=self.flat.device)
+            self._gc[k] = {}
         self._grad[k].zero_()
         self._cur = k
 
@@ -167,8 +190,9 @@ class FlatStore:
         for name, p in zip(self.names, self.params):
             if not p.requires_grad or (used is not None and name not in used):
                 out.append(None)
-            else:
-                out.append(self.g(name))
+            else:   # NOT through the cache of g(): a cached view is a second reference and AccumulateGrad would copy
+                o = self.offset[name]
+                out.append(self._grad[self._cur][o: o + self.numel[name]].view(self.shape[name]))
         return out
 
 

@@ -8,6 +8,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import threading
 from typing import Optional
 
 import torch
@@ -64,7 +65,17 @@ def check(rc: int, what: str = ""):
         raise VtError("%s failed (%d): %s" % (what, rc, load().vt_last_error().decode()))
 
 
+_cur_dev = torch._C._cuda_getDevice if hasattr(torch._C, "_cuda_getDevice") else None
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def init(device: Optional[int] = None) -> C.CDLL:
+    """The library handle, initialised for `device` (default: the current one).  On the hot path this is two dictionary /
+    C lookups: a step makes ~400 calls, and `torch.cuda.is_available()` alone cost 2 ms per step there."""
+    if _lib is not None and _inited:
+        dev = (_cur_dev() if _cur_dev is not None else torch.cuda.current_device()) if device is None else int(device)
+        if dev in _inited:
+            return _lib
     lib = load()
     if not torch.cuda.is_available():
         raise VtError("visitron_b200 needs a CUDA sm_100 device; there is no CPU fallback")
@@ -83,6 +94,10 @@ def require_device(t: torch.Tensor) -> None:
 
 
 def stream_ptr() -> int:
+    """Raw handle of the current stream of the current device (the private fast path costs ~0.3 us, `torch.cuda.current_stream()`
+    builds a Stream object every call: 14 us x 280 launches per step)."""
+    if _raw_stream is not None:
+        return _raw_stream(_cur_dev() if _cur_dev is not None else torch.cuda.current_device())
     return torch.cuda.current_stream().cuda_stream
 
 
@@ -99,10 +114,14 @@ def reset_launch_count():
 
 
 def _row_major_2d(t: torch.Tensor, name: str):
-    if t.dim() != 2 or t.stride(1) != 1:
+    st = t.stride()
+    if len(st) != 2 or st[1] != 1:
         raise VtError("%s must be a 2-D tensor with unit inner stride, got shape %s strides %s"
                       % (name, tuple(t.shape), t.stride()))
-    return t.stride(0) if t.size(0) > 1 else max(t.stride(0), t.size(1))
+    return st[0] if t.size(0) > 1 else max(st[0], t.size(1))
+
+
+_TLS = threading.local()   # one epilogue struct per thread, re-filled per call (a new ctypes Structure per GEMM cost ~8 us x 160 GEMMs per step)
 
 
 def gemm(A: torch.Tensor, B: torch.Tensor, *, a_major: int = 0, b_major: int = 0,
@@ -130,35 +149,46 @@ def gemm(A: torch.Tensor, B: torch.Tensor, *, a_major: int = 0, b_major: int = 0
             raise VtError("remap needs an explicit output tensor")
         out = torch.empty((M, N), device=A.device, dtype=out_dtype)
     ldd = _row_major_2d(out, "out")
-    ep = GemmEpilogue()
-    ep.out_fp32 = 1 if out.dtype == torch.float32 else 0
-    if not ep.out_fp32 and out.dtype != torch.bfloat16:
+    ep = getattr(_TLS, "ep", None)
+    if ep is None:
+        ep = _TLS.ep = GemmEpilogue()
+    odt = out.dtype
+    if odt is not torch.float32 and odt is not torch.bfloat16:
         raise VtError("GEMM output must be bf16 or fp32")
+    ep.out_fp32 = 1 if odt is torch.float32 else 0
     ep.accumulate = 1 if accumulate else 0
     ep.split_k = split_k
     ep.act = act
     ep.alpha = alpha
-    ep.alpha_dev = ptr(alpha_dev)
+    ep.alpha_dev = None if alpha_dev is None else alpha_dev.data_ptr()
     if bias is not None:
-        assert bias.dtype == torch.float32 and bias.is_contiguous() and bias.numel() >= N
-    ep.bias = ptr(bias)
+        assert bias.dtype is torch.float32 and bias.is_contiguous() and bias.numel() >= N
+        ep.bias = bias.data_ptr()
+    else:
+        ep.bias = None
     if residual is not None:
-        assert residual.dtype == torch.bfloat16
-        ep.residual, ep.ldr = ptr(residual), _row_major_2d(residual, "residual")
+        assert residual.dtype is torch.bfloat16
+        ep.residual, ep.ldr = residual.data_ptr(), _row_major_2d(residual, "residual")
+    else:
+        ep.residual, ep.ldr = None, 0
     if aux is not None:
-        assert aux.dtype == torch.bfloat16
-        ep.aux, ep.ldaux = ptr(aux), _row_major_2d(aux, "aux")
+        assert aux.dtype is torch.bfloat16
+        ep.aux, ep.ldaux = aux.data_ptr(), _row_major_2d(aux, "aux")
+    else:
+        ep.aux, ep.ldaux = None, 0
     if aux_out is not None:
-        assert aux_out.dtype == torch.bfloat16
-        ep.aux_out, ep.ldaux_out = ptr(aux_out), _row_major_2d(aux_out, "aux_out")
-    ep.dropout_p, ep.seed, ep.dropout_stream = float(dropout_p), int(seed), int(dropout_stream)
-    if remap is not None:
-        ep.remap_rows_in, ep.remap_rows_out, ep.remap_row_off = remap
+        assert aux_out.dtype is torch.bfloat16
+        ep.aux_out, ep.ldaux_out = aux_out.data_ptr(), _row_major_2d(aux_out, "aux_out")
+    else:
+        ep.aux_out, ep.ldaux_out = None, 0
+    ep.dropout_p, ep.seed, ep.dropout_stream = dropout_p, seed, dropout_stream
+    ep.remap_rows_in, ep.remap_rows_out, ep.remap_row_off = remap if remap is not None else (0, 0, 0)
     if GEMM_EVENTS is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-    check(lib.vt_gemm_bf16(ptr(A), lda, a_major, ptr(B), ldb, b_major, ptr(out), ldd, M, N, K,
-                           C.byref(ep), stream_ptr()), "vt_gemm_bf16")
+    rc = lib.vt_gemm_bf16(A.data_ptr(), lda, a_major, B.data_ptr(), ldb, b_major, out.data_ptr(), ldd, M, N, K, C.byref(ep), stream_ptr())
+    if rc:
+        check(rc, "vt_gemm_bf16")
     if GEMM_EVENTS is not None:
         e1.record()
         GEMM_EVENTS.append((e0, e1, 2.0 * M * N * K))

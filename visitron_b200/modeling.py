@@ -513,7 +513,7 @@ def _encoder_backward(step: _Step, st: FlatStore, d, dpooled):
                      st.g("embeddings.position_embeddings.weight"), st.g("embeddings.token_type_embeddings.weight"),
                      st.g("embeddings.LayerNorm.weight"), st.g("embeddings.LayerNorm.bias"), step.p_hidden, step.seed, STREAM_EMB)
     if red is not None:
-        red.reduce(st.grad_bucket(0))  # embeddings (+ the tied MLM decoder's contribution) and the image projection
+        red.reduce(st.grad_bucket(0), tail=True)  # embeddings (+ the tied MLM decoder's contribution) and the image projection
         red.finish()
 
 

@@ -53,9 +53,14 @@ class GradReducer:
         self.backend = dist.get_backend(process_group)
         self.world_size = dist.get_world_size(process_group)
         self.reserve = 0
+        caller_group = process_group
         if self.backend == "nccl" and process_group is None and overlap and self.world_size > 1:
             process_group = _exchange_group()
             self.reserve = NCCL_MAX_CTAS if process_group is not None else 0
+        # the LAST bucket of a step (embeddings, 101 MB) has no backward kernels left to hide behind: it goes through the
+        # caller's (uncapped) communicator at full speed instead of the 8-CTA one
+        self.tail_group = caller_group
+        self.tail_full_speed = os.environ.get("VT_TAIL_FULL_SPEED", "1") != "0"
         self.group = process_group
         self._reserved = False
         self.overlap = overlap
@@ -64,12 +69,15 @@ class GradReducer:
         self.bytes_reduced = 0
         self.calls = 0
 
-    def reduce(self, bucket: torch.Tensor) -> None:
-        """Enqueue the average of ``bucket`` (a contiguous slice of the flat gradient buffer)."""
+    def reduce(self, bucket: torch.Tensor, tail: bool = False) -> None:
+        """Enqueue the average of ``bucket`` (a contiguous slice of the flat gradient buffer); ``tail``: the step's last."""
         if self.world_size == 1 or bucket.numel() == 0:
             return
         self.calls += 1
         self.bytes_reduced += bucket.numel() * bucket.element_size()
+        if tail and self.tail_full_speed and self.reserve and self.backend == "nccl":
+            self._works.append(dist.all_reduce(bucket, op=dist.ReduceOp.AVG, group=self.tail_group, async_op=True))
+            return
         if self.reserve and not self._reserved:
             from . import lib
             lib.load().vt_reserve_sms(self.reserve)
