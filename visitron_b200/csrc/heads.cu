@@ -131,12 +131,26 @@ action_head_fwd_kernel(const float* __restrict__ pooled, const float* __restrict
   if (s >= B) return;
   const float* x = pooled + (long long)s * Hd;
   float mine0 = -INFINITY, mine1 = -INFINITY;  // lane owns actions lane and lane + 32
-  for (int a = 0; a < A; ++a) {
-    const float* w = W + (long long)a * Hd;
-    float acc = 0.f;
-    for (int k = lane; k < Hd; k += 32) acc = fmaf(x[k], __ldg(w + k), acc);
-    acc = warp_sum(acc) + bias[a];
-    if ((a & 31) == lane) { if (a < 32) mine0 = acc; else mine1 = acc; }
+  // four actions per pass: their loads and shuffle reductions interleave (one action at a time was a chain of dependent
+  // load -> fma -> 5 shuffles, 36 times: 137 us for a 32 x 768 x 36 product)
+  for (int a0 = 0; a0 < A; a0 += 4) {
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int k = lane; k < Hd; k += 32) {
+      const float xv = x[k];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (a0 + u < A) acc[u] = fmaf(xv, __ldg(W + (long long)(a0 + u) * Hd + k), acc[u]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) acc[u] += __shfl_xor_sync(0xffffffffu, acc[u], o);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int a = a0 + u;
+      if (a < A && (a & 31) == lane) { if (a < 32) mine0 = acc[u] + bias[a]; else mine1 = acc[u] + bias[a]; }
+    }
   }
   float m = warp_max(fmaxf(mine0, mine1));
   float e = (lane < A ? __expf(mine0 - m) : 0.f) + (lane + 32 < A ? __expf(mine1 - m) : 0.f);

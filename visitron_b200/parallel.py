@@ -31,8 +31,9 @@ import torch.distributed as dist
 
 # CTAs (= SMs) NCCL may use for the overlapped gradient exchange; the persistent GEMM leaves as many SMs free while
 # an exchange is in flight, so that neither side waits for the other's CTAs to retire.  NVSwitch reduces in the switch
-# (NVLS), so a 28 MB bucket needs few CTAs to run far faster than the backward of the next layer.
-NCCL_MAX_CTAS = int(os.environ.get("VT_NCCL_MAX_CTAS", "8"))
+# (NVLS), so a 28 MB bucket needs few CTAs to run far faster than the backward of the next layer.  Measured at b = 32 per GPU
+# (ms per step, cap 2 / 4 / 8 / 16): 2 GPUs 25.0 / 24.7 / 26.5 / 25.9; 8 GPUs - / 25.3 / 26.7 / - (1 GPU: 23.7-24.1).
+NCCL_MAX_CTAS = int(os.environ.get("VT_NCCL_MAX_CTAS", "4"))
 
 
 def _exchange_group():
