@@ -257,7 +257,9 @@ def pretrain_forward(P: Params, cfg: OracleConfig, input_ids, token_type_ids=Non
     token_loss = F.cross_entropy(tok_prob.view(-1, Dc), token_labels.view(-1), ignore_index=-1)    # :381-385
     mask_loss = F.cross_entropy(pred_scores.view(-1, V), labels.view(-1), ignore_index=-1)         # :387-389
     act = F.log_softmax(F.linear(pooled, P["next_action.linear.weight"], P["next_action.linear.bias"]), -1)  # :152-158
-    next_loss = F.cross_entropy(act, next_action, ignore_index=-1)                                 # :391-395
+    next_loss = 0                                                                                  # :392 (a Python int without next_action)
+    if next_action is not None:
+        next_loss = F.cross_entropy(act, next_action, ignore_index=-1)                             # :393-394
     loss = mask_loss + next_loss + token_loss                                                      # :396
     pa = act.argmax(1)
     pw = pred_scores.argmax(2)
@@ -266,7 +268,9 @@ def pretrain_forward(P: Params, cfg: OracleConfig, input_ids, token_type_ids=Non
     ign_w = (labels == -1).sum()
     words_left = (labels.numel() - ign_w).float()
     words_acc = ((pw == labels).sum() - ign_w) / words_left                                        # :408-410
-    action_acc = (pa == next_action).sum().float() / pa.shape[0]                                   # :412-416
+    action_acc = 0                                                                                 # :417-418
+    if next_action is not None:
+        action_acc = (pa == next_action).sum().float() / pa.shape[0]                               # :412-416
     pt[token_labels == -1] = -1                                                                    # :420
     ign_t = (token_labels == -1).sum()
     tokens_left = (pt.numel() - ign_t).float()

@@ -32,7 +32,11 @@ def test_finetune_golden_fixture():
 
 
 def _to(batch, dev):
-    return {k: v.to(dev) for k, v in batch.items()}
+    return {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in batch.items()}
+
+
+def _f(x):
+    return float(x.detach()) if torch.is_tensor(x) else float(x)
 
 
 def _oracle_step(oc, P, batch):
@@ -228,3 +232,43 @@ def test_eval_no_grad_and_save_load_roundtrip(tmp_path):
     bert = m2.bert
     seq, pooled = bert(batch["input_ids"], attention_mask=batch["attention_mask"][:, :48])
     assert tuple(seq.shape) == (2, 48, 768) and tuple(pooled.shape) == (2, 768) and seq.dtype == torch.float32
+
+
+@pytest.mark.parametrize("b,text_len,regions,drop_labels", [(1, 37, 5, ""), (3, 50, 1, "token"), (2, 8, 19, "mlm"), (2, 33, 7, "action")])
+def test_ragged_shapes_and_missing_objectives_vs_oracle(b, text_len, regions, drop_labels):
+    """Edge cases of the boundary: a single sample, sequence lengths that are no multiple of any tile (S = 42, 51, 27, 40), one
+    region slot, and batches in which an objective has NO labelled row / no next_action at all -- outputs (NaN where the
+    reference's mean over zero rows is NaN) and every gradient against the fp32 oracle on the same GPU."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    oc = vo.OracleConfig(vocab_size=2048, num_hidden_layers=2, max_position_embeddings=64, detector_classes=96)
+    P = vo.init_params(oc, 5 + b)
+    batch = synthetic.pretrain_batch(b, 17 + text_len, text_len=text_len, regions=regions, vocab=2048, detector_classes=96)
+    if drop_labels == "token":
+        batch["token_labels"].fill_(-1)
+    if drop_labels == "mlm":
+        batch["labels"].fill_(-1)
+    if drop_labels == "action":
+        batch["next_action"] = None
+    ref_out, _, Pg = _oracle_step(oc, P, batch)
+    model = modeling.PreTrainOscar(make_config(oc))
+    load_params(model, P)
+    model.to(DEV).train()
+    out = model(**_to(batch, DEV))
+    assert len(out) == len(ref_out)
+    for name, a, r in zip(("loss", "mask", "next", "token", "wacc", "aacc", "tacc"), out, ref_out):
+        a, r = _f(a), _f(r)
+        assert (a != a) == (r != r), (name, a, r)   # NaN exactly where the reference has it
+        if r == r:
+            assert abs(a - r) <= LOSS_RTOL * max(1.0, abs(r)), (name, a, r)
+    if _f(ref_out[0]) == _f(ref_out[0]):   # a NaN loss has no gradients worth comparing
+        out[0].backward()
+        torch.cuda.synchronize()
+        for k, p in model.named_parameters():
+            if k == "mlmhead.predictions.decoder.weight":
+                continue
+            ref = Pg[k].grad
+            if ref is None or float(ref.abs().max()) == 0.0:
+                assert p.grad is None or float(p.grad.abs().max()) == 0.0, k
+                continue
+            grad_close(k, p.grad, ref, floor=1e-4)

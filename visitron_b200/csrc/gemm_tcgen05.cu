@@ -482,8 +482,15 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
                             int64_t ldd, int64_t M, int64_t N, int64_t K, const vt_gemm_epilogue* ep, vt_stream stream) {
   int rc = resolve_driver_entry_points();
   if (rc) return rc;
-  VT_REQUIRE(A && B && D && ep, "vt_gemm_bf16: null pointer");
-  if (M == 0 || N == 0) return VT_OK;
+  VT_REQUIRE(ep, "vt_gemm_bf16: null epilogue");
+  if (M == 0 || N == 0) return VT_OK;   // e.g. an objective without a single labelled row: nothing to compute (pointers may be null)
+  if (K == 0) {                          // empty contraction (weight gradient over zero rows): the product is zero
+    if (ep->accumulate) return VT_OK;
+    VT_REQUIRE(D, "vt_gemm_bf16: null output");
+    VT_CUDA(cudaMemset2DAsync(D, (size_t)ldd * (ep->out_fp32 ? 4 : 2), 0, (size_t)N * (ep->out_fp32 ? 4 : 2), (size_t)M, (cudaStream_t)stream));
+    return VT_OK;
+  }
+  VT_REQUIRE(A && B && D, "vt_gemm_bf16: null pointer");
   VT_REQUIRE(M > 0 && N > 0 && K > 0 && M < (1ll << 31) && N < (1ll << 31) && K < (1ll << 31), "vt_gemm_bf16: bad sizes M=%lld N=%lld K=%lld", (long long)M, (long long)N, (long long)K);
   VT_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "vt_gemm_bf16: lda/ldb must be multiples of 8 elements (TMA 16-byte pitch), got %lld %lld", (long long)lda, (long long)ldb);
   VT_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "vt_gemm_bf16: A/B must be 16-byte aligned");
