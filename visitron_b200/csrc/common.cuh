@@ -94,7 +94,7 @@ __device__ __forceinline__ float gelu_grad(float x) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Philox4x32-10 counter RNG.  Dropout masks are never stored: forward and backward regenerate them
+// Philox4x32-7 counter RNG.  Dropout masks are never stored: forward and backward regenerate them
 // from (seed, stream id, element index).  One call yields 8 x 16-bit lanes; an element is kept iff
 // its lane >= thresh16, thresh16 = round(p * 65536)  (p is thereby quantised to 1/65536).
 // ---------------------------------------------------------------------------------------------
@@ -112,7 +112,10 @@ __device__ __forceinline__ uint4 philox4x32(uint4 ctr, uint2 key) {
   return ctr;
 }
 
-__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) { return philox4x32<10>(ctr, key); }
+// 7 rounds everywhere: the fewest for which Philox4x32 is Crush-resistant (Salmon et al. 2011).  (Host-computed round keys
+// passed as kernel parameters were tried: -3 us on the attn-out GEMM's dropout epilogue, but the larger parameter block cost
+// the attention kernels 13 us per layer in a same-box A/B, so the keys are bumped in registers.)
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) { return philox4x32<7>(ctr, key); }
 
 struct DropoutCfg {
   uint32_t thresh16;   // 0 => dropout disabled
