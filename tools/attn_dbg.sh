@@ -1,3 +1,4 @@
+# needs an ablation build:  VT_BUILD_ABLATE=1 python -m visitron_b200.build --force   (and a plain --force build afterwards)
 # timing ablations of the tcgen05 attention kernels (results of dbg != 0 are garbage).  VT_ATTN_DBG bits: 1 no element-wise arithmetic,
 # 2 no exponentials, 16 no dV (fwd: no P.V) MMA, 32 no dK MMA, 64 no dQ MMA, 128 no S / dP MMA, 256 no dQ-partial stores,
 # 512 no K/V (Q/dO) loads after the first ring fill, 1024 no maximum exchange, 2048 no proxy fence, 4096 no P stores, 8192 no TMEM loads of S,

@@ -16,6 +16,8 @@ LIB = os.path.join(HERE, "libvisitron_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
+if os.environ.get("VT_BUILD_ABLATE"):   # timing-ablation switches of the attention kernels (tools/attn_dbg.sh); rebuild with --force
+    FLAGS.append("-DVT_ATTN_ABLATE")
 
 
 def _sources():

@@ -20,6 +20,14 @@
 #include "common.cuh"
 #include "ptx.cuh"
 
+// Timing-ablation switches (tools/attn_dbg.sh): compiled in only with -DVT_ATTN_ABLATE (VT_BUILD_ABLATE=1 python -m
+// visitron_b200.build); in the product build every VT_DBG(bit) is a compile-time 0 and the branches vanish.
+#ifdef VT_ATTN_ABLATE
+#define VT_DBG(bit) ((p.dbg & (bit)) != 0)
+#else
+#define VT_DBG(bit) false
+#endif
+
 namespace vt {
 
 using namespace ptx;
@@ -179,7 +187,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         mbar_wait_backoff(k_full + 8 * st, (uint32_t)((g / FWD_KV) & 1), MMA_POLL_NS);
         tc_fence_after();
         const uint64_t a = make_smem_desc(sQ + qb * 16384, 16, 1024), bd = make_smem_desc(sK + st * 8192, 16, 1024);
-        if (!(p.dbg & 128)) {
+        if (!VT_DBG(128)) {
 #pragma unroll
           for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + 64 * (g & 1), a + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc_s, k > 0 ? 1u : 0u);
         }
@@ -202,7 +210,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         if (j == 0 && it > 0) mbar_wait_backoff(o_free, (uint32_t)((it - 1) & 1), MMA_POLL_NS);   // previous item's O drained
         tc_fence_after();
         const uint64_t a = make_smem_desc(sP + bf * 16384, 16, 1024), bd = make_smem_desc(sV + vst * 8192, 8192, 1024);
-        if (!(p.dbg & 16)) {
+        if (!VT_DBG(16)) {
 #pragma unroll
           for (int k = 0; k < 4; ++k) umma_bf16(tmem_o, a + (uint64_t)(2 * k), bd + (uint64_t)(128 * k), idesc_o, (j > 0 || k > 0) ? 1u : 0u);
         }
@@ -245,7 +253,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         if (lane == 0) mbar_arrive(s_free + 8 * bf);
         const float* bias = sBias + j * FK + COLS * half;
         float mx = -INFINITY;
-        if (!(p.dbg & 1)) {
+        if (!VT_DBG(1)) {
 #pragma unroll
           for (int c = 0; c < COLS; ++c) {
             const float v = fmaf(__uint_as_float(sv[c]), p.scale, bias[c]);
@@ -270,17 +278,17 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         }
         const float mb = m_used * kLog2e;
         float rs = 0.f;
-        if (!(p.dbg & 1)) {
+        if (!VT_DBG(1)) {
 #pragma unroll
           for (int c = 0; c < COLS; ++c) {
             const float x = fmaf(__uint_as_float(sv[c]), kLog2e, -mb);
-            const float e = (p.dbg & 2) ? x : ex2_approx(x);
+            const float e = VT_DBG(2) ? x : ex2_approx(x);
             rs += e;
             sv[c] = __float_as_uint(e);
           }
         }
         l += rs;
-        if (p.drop.thresh16 && !(p.dbg & 1)) {
+        if (p.drop.thresh16 && !VT_DBG(1)) {
           // counter layout of attn_dropout_rand: call t of 32-column group g covers columns 8 q + 2 t (low 16-bit lane of word q)
           // and 8 q + 2 t + 1 (high lane); keep iff lane >= thresh16.  The 1 / (1 - p) scale is applied once, to O.
           const uint32_t thi = p.drop.thresh16 << 16;
@@ -455,7 +463,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         for (int t = 0; t < nin; ++t, ++n) {
           const int st = n % BWD_NST;
           if (n >= BWD_NST) mbar_wait_backoff(in_empty + 8 * st, (uint32_t)((n / BWD_NST - 1) & 1), 64);
-          if ((p.dbg & 512) && n >= BWD_NST) { mbar_arrive(in_full + 8 * st); continue; }
+          if (VT_DBG(512) && n >= BWD_NST) { mbar_arrive(in_full + 8 * st); continue; }
           mbar_arrive_expect_tx(in_full + 8 * st, 2 * TILE16K);
           tma_load_2d(sQ + st * TILE16K, &tmQKV, in_full + 8 * st, h * 64, row_base + t * 128);
           tma_load_2d(sDO + st * TILE16K, &tmDO, in_full + 8 * st, h * 64, row_base + t * 128);
@@ -476,7 +484,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         // S = Q.K^T ; dP = dO.V^T   (A: query-side tile, B: key-side tile, both K-major over d = 64)
         const uint64_t qa = make_smem_desc(sQ + st * TILE16K, 16, 1024), kb = make_smem_desc(sK + kvb * TILE16K, 16, 1024);
         const uint64_t da = make_smem_desc(sDO + st * TILE16K, 16, 1024), vb = make_smem_desc(sV + kvb * TILE16K, 16, 1024);
-        if (!(p.dbg & 128)) {
+        if (!VT_DBG(128)) {
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk) umma_bf16(tmem_base, qa + (uint64_t)(2 * kk), kb + (uint64_t)(2 * kk), idesc_s, kk > 0 ? 1u : 0u);
 #pragma unroll
@@ -509,17 +517,17 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         // apart, K = query rows 128 B apart), B = dO_t / Q_t read MN-major (K = query rows)
         const uint64_t pa = make_smem_desc(sPD, TILE16K, 1024), sa = make_smem_desc(sDS, TILE16K, 1024);
         const uint64_t dob = make_smem_desc(sDO + st * TILE16K, TILE16K, 1024), qb = make_smem_desc(sQ + st * TILE16K, TILE16K, 1024);
-        if (!(p.dbg & 16)) {
+        if (!VT_DBG(16)) {
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 320, pa + (uint64_t)(128 * kk), dob + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
         }
-        if (!(p.dbg & 32)) {
+        if (!VT_DBG(32)) {
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) umma_bf16(tmem_base + 256, sa + (uint64_t)(128 * kk), qb + (uint64_t)(128 * kk), idesc_t, (t > 0 || kk > 0) ? 1u : 0u);
         }
         // dQ_t partial = dS.K_j : A = dS K-major over 128 keys (two 64-key atoms), B = K_j MN-major (K = key rows)
         const uint64_t kmn = make_smem_desc(sK + kvb * TILE16K, TILE16K, 1024);
-        if (!(p.dbg & 64))
+        if (!VT_DBG(64))
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           const uint64_t dsa = make_smem_desc(sDS + (kk >> 2) * TILE16K + (kk & 3) * 32, 16, 1024);
@@ -558,7 +566,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(dq_free + 8 * dqb);
-      if (dst && !(p.dbg & 256)) {
+      if (dst && !VT_DBG(256)) {
         uint4* d = reinterpret_cast<uint4*>(dst);
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
@@ -662,7 +670,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
             __syncwarp();
             if (lane == 0) mbar_arrive(sdp_free);
           }
-          if (p.dbg & 1) {
+          if (VT_DBG(1)) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) { pk_p[hf][i] = sv[i]; pk_d[hf][i] = dv[i]; }
             continue;
@@ -682,7 +690,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
                 const int ix = 4 * q + 2 * t2 + e;
                 const float v = fmaf(__uint_as_float(sv[ix]), p.scale, bias[cc]);
                 const float x = fmaf(v, kLog2e, -mb);
-                const float pr = ((p.dbg & 2) ? x : ex2_approx(x)) * inv;
+                const float pr = (VT_DBG(2) ? x : ex2_approx(x)) * inv;
                 const bool keep = e == 0 ? ((w[q] << 16) >= thi) : (w[q] >= thi);
                 const float dpm = keep ? __uint_as_float(dv[ix]) : 0.f;
                 pe[e] = keep ? pr : 0.f;
@@ -815,11 +823,11 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
     attr = true;
   }
   const long long n_items = ((S + FQ - 1) / FQ) * heads * B;
-  const long long ctas = (FWD_PERSISTENT || (p.dbg & 32768)) ? 2ll * usable_sms() : n_items;   // persistent: two CTAs per SM, each a contiguous range of items
+  const long long ctas = (FWD_PERSISTENT || VT_DBG(32768)) ? 2ll * usable_sms() : n_items;   // persistent: two CTAs per SM, each a contiguous range of items
   // one thread per row executes 28 % fewer instructions than two (ncu: 96.6 M vs 123.4 M warp instructions; the per-tile
   // bookkeeping and the maximum exchange are not duplicated) and measured faster with and without dropout
   // (197 vs 213 us at p = 0.1, 143 vs 147 us at p = 0); the two-thread variant stays selectable for ablations
-  const bool two = (p.dbg & 16384) != 0;
+  const bool two = VT_DBG(16384);
   if (two) attn_fwd_tc<2><<<(unsigned)(n_items < ctas ? n_items : ctas), 10 * 32, smem, st>>>(tq, tkv, p);
   else attn_fwd_tc<1><<<(unsigned)(n_items < ctas ? n_items : ctas), 6 * 32, smem, st>>>(tq, tkv, p);
   count_launch(1);
