@@ -271,6 +271,18 @@ int vt_adamw_step(const void* segments_dev, int64_t n_segments, int64_t n_chunks
 int vt_clip_grad_norm(const void* segments_dev, int64_t n_segments, int64_t n_chunks, float max_norm, float* partials,
                       float* norm_and_coef, int scale_in_place, vt_stream stream);
 
+/* ---- the step before forward: on-device masked-LM masking ----
+ * Replaces PretrainDataset._mask_tokens, tasks/viewpoint_select/data_loader_pretrain.py:549-612, for a whole batch in one
+ * launch: masked = (u1 < p_mask and id not special) or token_class != -1; label = id where masked and token_class == -1,
+ * else -1; id' = mask_id if (u2 < 0.8 and masked) or token_class != -1, else a random word if u3 < 0.5 and masked, else id;
+ * attention = id != pad_id.  special_lut: uint8 [vocab], 1 for tokenizer.all_special_ids; token_classes may be null
+ * (masked_token_prediction off).  One Philox4x32-7 call per token keyed on (seed, token index). */
+int vt_mlm_mask(const int64_t* ids, const int64_t* token_classes, const uint8_t* special_lut, int64_t n, int64_t vocab,
+                int64_t mask_id, int64_t pad_id, float p_mask, uint64_t seed, int64_t* ids_out, int64_t* labels,
+                uint8_t* attention_mask, vt_stream stream);
+/* The draws vt_mlm_mask uses for (seed, n, vocab): u fp32 [3][n] (u1, u2, u3), r int64 [n]; for the parity tests. */
+int vt_mlm_draws(int64_t n, int64_t vocab, uint64_t seed, float* u, int64_t* r, vt_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -185,6 +185,66 @@ def gen_adamw(ns, name, seed):
     print(name, lrs, float(norm))
 
 
+def gen_mlm_mask(name, seed):
+    """The reference's own _mask_tokens on seeded token rows, with its random draws recorded (torch.bernoulli / torch.randint are
+    wrapped while it runs), with and without masked_token_prediction."""
+    import types as _t
+    fn = ref_shim.load_mask_tokens()
+    V, MASK, PAD, CLS, SEP, UNK = 2048, 103, 0, 101, 102, 100
+    tok = _t.SimpleNamespace(all_special_ids=[UNK, SEP, PAD, CLS, MASK], pad_token_id=PAD, mask_token="[MASK]",
+                             convert_tokens_to_ids=lambda t: MASK)
+    tok_len = V
+
+    class _Tok:
+        all_special_ids = tok.all_special_ids
+        pad_token_id = PAD
+        mask_token = "[MASK]"
+
+        def convert_tokens_to_ids(self, t):
+            return MASK
+
+        def __len__(self):
+            return tok_len
+
+    cases = []
+    g = torch.Generator().manual_seed(seed)
+    for mtp in (False, True):
+        for L in (64, 511):
+            ids = torch.randint(200, V, (L,), generator=g)
+            ids[0] = CLS
+            n_valid = int(L * 0.8)
+            ids[n_valid - 1] = SEP
+            ids[n_valid:] = PAD
+            tc = torch.full((L,), -1, dtype=torch.long)
+            pos = torch.randperm(n_valid - 2, generator=g)[: max(2, L // 16)] + 1
+            tc[pos] = torch.randint(0, 96, (pos.numel(),), generator=g)
+            rec = []
+            ob, orr = torch.bernoulli, torch.randint
+
+            def bern(p, *a, **k):
+                out = ob(p, *a, **k)
+                rec.append(out.clone().bool())
+                return out
+
+            def rint(*a, **k):
+                out = orr(*a, **k)
+                rec.append(out.clone())
+                return out
+
+            self_ = _t.SimpleNamespace(args=_t.SimpleNamespace(mlm_probability=0.15, masked_token_prediction=mtp), tokenizer=_Tok())
+            torch.manual_seed(seed + L + int(mtp))
+            torch.bernoulli, torch.randint = bern, rint
+            try:
+                out_ids, labels, att = fn(self_, ids.clone(), tc.clone())
+            finally:
+                torch.bernoulli, torch.randint = ob, orr
+            assert len(rec) == 4
+            cases.append(dict(mtp=mtp, ids=ids, token_classes=tc, chosen=rec[0], as_mask=rec[1], as_random=rec[2], random_words=rec[3],
+                              out_ids=out_ids.clone(), labels=labels.clone(), attention=att.clone()))
+    torch.save(dict(seed=seed, vocab=V, mask_id=MASK, pad_id=PAD, special=[UNK, SEP, PAD, CLS, MASK], cases=cases), os.path.join(GOLDEN, name + ".pt"))
+    print(name, [(c["mtp"], int((c["labels"] != -1).sum())) for c in cases])
+
+
 def main():
     if not ref_shim.available():
         raise SystemExit("reference tree not mounted; fixtures can only be generated in the build container")
@@ -197,6 +257,7 @@ def main():
     gen_finetune(ns, "finetune_small", small_cfg(), 9, dict(batch=2, seed=90, text_len=48, vocab=2048))
     gen_heads(ns, "heads_small", 11)
     gen_adamw(ns, "adamw_small", 13)
+    gen_mlm_mask("mlm_mask_small", 17)
 
 
 if __name__ == "__main__":

@@ -90,3 +90,21 @@ def build_pretrain(ns, cfg, params):
     missing, unexpected = m.load_state_dict(sd, strict=True), None
     m.tie_weights()
     return m
+
+
+def load_mask_tokens():
+    """The reference's ``PretrainDataset._mask_tokens`` (tasks/viewpoint_select/data_loader_pretrain.py:549-612) as an unbound
+    function; the data-loader module's unrelated imports that are missing here (lmdb, networkx, ...) are stubbed."""
+    load()
+    vs = os.path.join(REFERENCE_ROOT, "tasks", "viewpoint_select")
+    for n in ("lmdb", "networkx", "jsonlines", "tensorboardX", "MatterSim"):
+        try:
+            importlib.import_module(n)
+        except Exception:
+            sys.modules.setdefault(n, types.ModuleType(n))
+    sys.path[:0] = [vs]
+    try:
+        mod = importlib.import_module("data_loader_pretrain")
+    finally:
+        sys.path.remove(vs)
+    return mod.PretrainDataset._mask_tokens

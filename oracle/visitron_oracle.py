@@ -392,6 +392,34 @@ def clip_grad_norm(grads, max_norm: float):
 
 
 # --------------------------------------------------------------------------------------------
+# the step before forward
+# --------------------------------------------------------------------------------------------
+def mlm_mask(inputs, token_classes, special_mask, chosen, as_mask, as_random, random_words, mask_id, pad_id):
+    """PretrainDataset._mask_tokens, vs/data_loader_pretrain.py:549-612, as a function of its random draws:
+    ``chosen`` = bernoulli(0.15), ``as_mask`` = bernoulli(0.8), ``as_random`` = bernoulli(0.5) (bool tensors),
+    ``random_words`` = randint(len(tokenizer)); ``token_classes`` None = masked_token_prediction off.
+    Returns (inputs', labels, attention_mask)."""
+    inputs = inputs.clone()
+    labels = inputs.clone()
+    masked = chosen & ~special_mask                                   # :555-566 (probability 0 on special tokens)
+    tc = None if token_classes is None else token_classes != -1
+    if tc is not None:
+        masked = masked | tc                                          # :568-571
+    attention = inputs != pad_id                                      # :573-575
+    labels[~masked] = -1                                              # :577
+    if tc is not None:
+        labels[tc] = -1                                               # :579-580
+    replaced = as_mask & masked                                       # :583-586
+    inputs[replaced] = mask_id                                        # :588-590
+    if tc is not None:
+        replaced = replaced | tc                                      # :591-597
+        inputs[tc] = mask_id
+    rnd = as_random & masked & ~replaced                              # :600-604
+    inputs[rnd] = random_words[rnd]                                   # :606-610
+    return inputs, labels, attention
+
+
+# --------------------------------------------------------------------------------------------
 # helpers for tests / bench
 # --------------------------------------------------------------------------------------------
 def clone_params(P: Params, requires_grad=True, dtype=None, device=None) -> Params:

@@ -1,0 +1,106 @@
+"""The step before forward on the B200 kernel, through the C ABI: masked-LM masking of a whole batch in one
+launch against the oracle restatement of PretrainDataset._mask_tokens (itself pinned to the reference by
+tests/golden/mlm_mask_small.pt) run on the kernel's own draws.  Integer work: bit-exact."""
+import pytest
+import torch
+
+from oracle import visitron_oracle as vo
+from parity_common import load_fixture
+from visitron_b200 import input_pipeline as ip, lib
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+V, MASK, PAD, SPECIAL = 30522, 103, 0, [100, 102, 0, 101, 103]
+
+
+def _batch(b, L, seed, with_classes=True):
+    g = torch.Generator().manual_seed(seed)
+    ids = torch.randint(1000, V, (b, L), generator=g)
+    tc = torch.full((b, L), -1, dtype=torch.long)
+    ids[:, 0] = 101
+    for r in range(b):
+        n = int(torch.randint(L // 4, L + 1, (1,), generator=g)) if L > 4 else L
+        ids[r, n - 1] = 102
+        ids[r, n:] = PAD
+        if with_classes and n > 4:
+            pos = torch.randperm(n - 2, generator=g)[: max(1, n // 16)] + 1
+            tc[r, pos] = torch.randint(0, 1601, (pos.numel(),), generator=g)
+    return ids, (tc if with_classes else None)
+
+
+def _oracle(ids, tc, seed, p=0.15, vocab=V, special=SPECIAL):
+    u, r = ip.draws(ids.numel(), vocab, seed, DEV)
+    u, r = u.cpu().reshape(3, *ids.shape), r.cpu().reshape(ids.shape)
+    sp = torch.zeros(vocab, dtype=torch.bool)
+    sp[torch.tensor(special)] = True
+    return vo.mlm_mask(ids, tc, sp[ids], u[0] < p, u[1] < 0.8, u[2] < 0.5, r, MASK, PAD), u, r
+
+
+@pytest.mark.parametrize("b,L,classes", [(32, 511, True), (3, 80, False), (1, 1, True), (7, 333, True)])
+def test_mlm_mask_matches_oracle_bit_exact(b, L, classes):
+    ids, tc = _batch(b, L, 11 + b, classes)
+    lut = ip.special_lut(V, SPECIAL, DEV)
+    n0 = lib.launch_count()
+    out, labels, att = ip.mask_tokens(ids.to(DEV), None if tc is None else tc.to(DEV), lut, MASK, PAD, seed=1234 + L)
+    assert lib.launch_count() - n0 == 1, "the whole batch in ONE launch"
+    (w_ids, w_labels, w_att), _, _ = _oracle(ids, tc, 1234 + L)
+    assert torch.equal(out.cpu(), w_ids) and torch.equal(labels.cpu(), w_labels) and torch.equal(att.cpu(), w_att)
+    assert att.dtype == torch.bool and out.dtype == torch.int64 and labels.dtype == torch.int64
+
+
+def test_mlm_mask_on_the_reference_fixture_rows():
+    """The rows (and vocabulary) of the reference fixture through the kernel: same rule as the reference's outputs wherever the draws
+    agree is covered by the oracle test; here the kernel == oracle on those very rows, and the rule's invariants hold."""
+    fix = load_fixture("mlm_mask_small")
+    lut = ip.special_lut(fix["vocab"], fix["special"], DEV)
+    for k, c in enumerate(fix["cases"]):
+        tc = c["token_classes"] if c["mtp"] else None
+        out, labels, att = ip.mask_tokens(c["ids"].to(DEV), None if tc is None else tc.to(DEV), lut, fix["mask_id"], fix["pad_id"], seed=k)
+        (w_ids, w_labels, w_att), _, _ = _oracle(c["ids"], tc, k, vocab=fix["vocab"], special=fix["special"])
+        assert torch.equal(out.cpu(), w_ids) and torch.equal(labels.cpu(), w_labels) and torch.equal(att.cpu(), w_att)
+        assert torch.equal(att.cpu(), c["attention"]), "attention mask does not depend on the draws"
+        sp = torch.isin(c["ids"], torch.tensor(fix["special"]))
+        free = sp & (c["token_classes"] == -1) if c["mtp"] else sp
+        assert bool((labels.cpu()[sp] == -1).all()) and torch.equal(out.cpu()[free], c["ids"][free])
+
+
+def test_mlm_mask_statistics_and_determinism_full_batch():
+    """BASELINE-size text block (b=256 x 511 tokens): 15 % chosen, 80 / 10 / 10 split, specials untouched, forced region-label
+    positions, same seed -> same result, another seed -> another mask; the input tensor is left alone."""
+    ids, tc = _batch(256, 511, 5, True)
+    d_ids, d_tc = ids.to(DEV), tc.to(DEV)
+    lut = ip.special_lut(V, SPECIAL, DEV)
+    keep = d_ids.clone()
+    out, labels, att = ip.mask_tokens(d_ids, d_tc, lut, MASK, PAD, seed=99)
+    out2, labels2, _ = ip.mask_tokens(d_ids, d_tc, lut, MASK, PAD, seed=99)
+    out3, _, _ = ip.mask_tokens(d_ids, d_tc, lut, MASK, PAD, seed=100)
+    assert torch.equal(d_ids, keep)
+    assert torch.equal(out, out2) and torch.equal(labels, labels2) and not torch.equal(out, out3)
+    out, labels = out.cpu(), labels.cpu()
+    special = torch.isin(ids, torch.tensor(SPECIAL))
+    forced = tc != -1
+    assert bool((out[forced] == MASK).all()) and bool((labels[forced] == -1).all())
+    assert torch.equal(out[special & ~forced], ids[special & ~forced]) and bool((labels[special] == -1).all())
+    assert torch.equal(att.cpu(), ids != PAD)
+    cand = ~special & ~forced
+    chosen = labels != -1
+    assert bool((labels[chosen] == ids[chosen]).all()) and not bool((chosen & ~cand).any())
+    rate = chosen.sum().item() / cand.sum().item()
+    assert abs(rate - 0.15) < 0.005, rate
+    n = chosen.sum().item()
+    as_mask = (out[chosen] == MASK).sum().item() / n
+    changed = ((out[chosen] != MASK) & (out[chosen] != ids[chosen])).sum().item() / n
+    assert abs(as_mask - 0.8) < 0.01 and abs(changed - 0.1) < 0.01, (as_mask, changed)
+    assert bool((out[~chosen & ~forced] == ids[~chosen & ~forced]).all())
+    rnd = out[chosen & (out != MASK) & (out != ids)]
+    assert int(rnd.min()) >= 0 and int(rnd.max()) < V and rnd.float().mean().item() == pytest.approx(V / 2, rel=0.05)
+
+
+def test_mlm_mask_refuses_cpu_and_bad_dtypes():
+    lut = ip.special_lut(V, SPECIAL, DEV)
+    with pytest.raises(lib.VtError):
+        ip.mask_tokens(torch.zeros(4, dtype=torch.long), None, lut, MASK, PAD, seed=0)
+    with pytest.raises(lib.VtError):
+        ip.mask_tokens(torch.zeros(4, dtype=torch.int32, device=DEV), None, lut, MASK, PAD, seed=0)
+    out, labels, att = ip.mask_tokens(torch.zeros((0, 8), dtype=torch.long, device=DEV), None, lut, MASK, PAD, seed=0)
+    assert out.shape == (0, 8) and labels.shape == (0, 8) and att.shape == (0, 8)

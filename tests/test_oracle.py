@@ -166,3 +166,21 @@ def test_adamw_oracle_matches_reference_fixture():
     assert abs(float(norm) - fix["clip_norm"]) < 1e-4 * fix["clip_norm"]
     for a, b in zip(clipped, fix["clipped"]):
         torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-7)
+
+
+def test_mlm_mask_oracle_matches_reference_fixture():
+    """oracle.mlm_mask against the reference's own PretrainDataset._mask_tokens (tests/golden/mlm_mask_small.pt: its inputs, the
+    bernoulli / randint draws it made, and its outputs; generated by oracle/make_golden.py), with and without
+    masked_token_prediction.  Integer work: bit-exact."""
+    fix = torch.load(os.path.join(GOLDEN, "mlm_mask_small.pt"), weights_only=False)
+    assert len(fix["cases"]) == 4
+    for c in fix["cases"]:
+        special = torch.zeros(fix["vocab"], dtype=torch.bool)
+        special[torch.tensor(fix["special"])] = True
+        # the reference draws bernoulli(0) on special tokens, so `chosen` is already clear there; the oracle takes raw draws
+        ids, labels, att = vo.mlm_mask(c["ids"], c["token_classes"] if c["mtp"] else None, special[c["ids"]], c["chosen"], c["as_mask"],
+                                       c["as_random"], c["random_words"], fix["mask_id"], fix["pad_id"])
+        assert torch.equal(ids, c["out_ids"]) and torch.equal(labels, c["labels"]) and torch.equal(att, c["attention"])
+        if c["mtp"]:
+            forced = c["token_classes"] != -1
+            assert bool((ids[forced] == fix["mask_id"]).all()) and bool((labels[forced] == -1).all())

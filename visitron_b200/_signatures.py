@@ -49,6 +49,8 @@ SIGNATURES = {
     "vt_opt_chunk": (I64, []),
     "vt_adamw_step": (I, [P, I64, I64, I64, P, P, D, D, D, P, P]),
     "vt_clip_grad_norm": (I, [P, I64, I64, F, P, P, I, P]),
+    "vt_mlm_mask": (I, [P, P, P, I64, I64, I64, I64, F, U64, P, P, P, P]),
+    "vt_mlm_draws": (I, [I64, I64, U64, P, P, P]),
 }
 
 
