@@ -282,6 +282,12 @@ int vt_mlm_mask(const int64_t* ids, const int64_t* token_classes, const uint8_t*
                 uint8_t* attention_mask, vt_stream stream);
 /* The draws vt_mlm_mask uses for (seed, n, vocab): u fp32 [3][n] (u1, u2, u3), r int64 [n]; for the parity tests. */
 int vt_mlm_draws(int64_t n, int64_t vocab, uint64_t seed, float* u, int64_t* r, vt_stream stream);
+/* Ragged per-sample region rows -> the padded [samples, regions, *] feature / location blocks of the model batch, replacing the per-sample
+ * slicing, torch.zeros and torch.cat of PretrainDataset._preprocess_item (data_loader_pretrain.py:656-690): sample s owns rows
+ * [offsets[s], offsets[s+1]) of the packed fp32 arrays; more than `regions` rows keeps the LAST `regions`, fewer pads with zeros.
+ * attention_tail (optional, int64, row pitch ld_attention) receives 1 for a kept row and 0 for padding. */
+int vt_pack_regions(const float* feats, int64_t d_feat, const float* loc, int64_t d_loc, const int64_t* offsets, int64_t samples,
+                    int64_t regions, float* out_feats, float* out_loc, int64_t* attention_tail, int64_t ld_attention, vt_stream stream);
 
 #ifdef __cplusplus
 }

@@ -245,6 +245,67 @@ def gen_mlm_mask(name, seed):
     print(name, [(c["mtp"], int((c["labels"] != -1).sum())) for c in cases])
 
 
+def gen_preprocess_item(name, seed):
+    """The reference's own _preprocess_item (with its real _mask_tokens, draws recorded; the LMDB feature read replaced by seeded
+    ragged arrays) for samples with fewer, exactly and more regions than max_img_seq_length."""
+    import types as _t
+    import numpy as np
+    mask_fn, item_fn = ref_shim.load_mask_tokens(), ref_shim.load_preprocess_item()
+    V, MASK, PAD, CLS, SEP, UNK, T, R, D, DL = 2048, 103, 0, 101, 102, 100, 48, 12, 70, 12
+
+    class _Tok:
+        all_special_ids = [UNK, SEP, PAD, CLS, MASK]
+        pad_token_id = PAD
+        mask_token = "[MASK]"
+
+        def convert_tokens_to_ids(self, t):
+            return MASK
+
+        def __len__(self):
+            return V
+
+    g = torch.Generator().manual_seed(seed)
+    cases = []
+    for k, (n, mtp, nag) in enumerate([(5, True, False), (12, True, False), (17, True, True), (0, False, False), (30, False, False)]):
+        ids = torch.randint(200, V, (T,), generator=g)
+        ids[0], ids[T - 9], ids[T - 8:] = CLS, SEP, PAD
+        tc = torch.full((T,), -1, dtype=torch.long)
+        tc[torch.tensor([5, 9, 20])] = torch.randint(0, 96, (3,), generator=g)
+        feats = torch.randn(n, D, generator=g).numpy().astype(np.float32)
+        loc = torch.randn(n, DL, generator=g).numpy().astype(np.float32)
+        rec = []
+        ob, orr = torch.bernoulli, torch.randint
+
+        def bern(p, *a, **kw):
+            out = ob(p, *a, **kw)
+            rec.append(out.clone().bool())
+            return out
+
+        def rint(*a, **kw):
+            out = orr(*a, **kw)
+            rec.append(out.clone())
+            return out
+
+        self_ = _t.SimpleNamespace(args=_t.SimpleNamespace(mlm_probability=0.15, masked_token_prediction=mtp, max_img_seq_length=R,
+                                                          no_action_grounding=nag, debug=False), tokenizer=_Tok())
+        self_._mask_tokens = lambda inputs, token_classes, _s=self_: mask_fn(_s, inputs, token_classes)
+        self_._extract_img_features = lambda scan, vp, vi, _f=feats, _l=loc: (_f.copy(), _l.copy())
+        item = dict(target_dialog_tokens_id=ids.clone(), token_classes=tc.clone(), scan="s", viewpoint="v", current_view_index=3,
+                    target_rel_view_index=7 + k)
+        torch.manual_seed(seed + k)
+        torch.bernoulli, torch.randint = bern, rint
+        try:
+            out = item_fn(self_, item)
+        finally:
+            torch.bernoulli, torch.randint = ob, orr
+        out = {kk: (v.clone() if torch.is_tensor(v) else v) for kk, v in out.items()}
+        cases.append(dict(n=n, mtp=mtp, no_action_grounding=nag, ids=ids, token_classes=tc, feats=torch.from_numpy(feats), loc=torch.from_numpy(loc),
+                          next_action=7 + k, chosen=rec[0], as_mask=rec[1], as_random=rec[2], random_words=rec[3], out=out))
+    torch.save(dict(seed=seed, vocab=V, mask_id=MASK, pad_id=PAD, special=[UNK, SEP, PAD, CLS, MASK], R=R, cases=cases),
+               os.path.join(GOLDEN, name + ".pt"))
+    print(name, [(c["n"], tuple(c["out"]["img_feats"].shape), sum(c["out"]["attention_mask"])) for c in cases])
+
+
 def main():
     if not ref_shim.available():
         raise SystemExit("reference tree not mounted; fixtures can only be generated in the build container")
@@ -258,6 +319,7 @@ def main():
     gen_heads(ns, "heads_small", 11)
     gen_adamw(ns, "adamw_small", 13)
     gen_mlm_mask("mlm_mask_small", 17)
+    gen_preprocess_item("preprocess_item_small", 19)
 
 
 if __name__ == "__main__":

@@ -108,3 +108,9 @@ def load_mask_tokens():
     finally:
         sys.path.remove(vs)
     return mod.PretrainDataset._mask_tokens
+
+
+def load_preprocess_item():
+    """``PretrainDataset._preprocess_item`` (data_loader_pretrain.py:636-712), unbound."""
+    load_mask_tokens()
+    return sys.modules["data_loader_pretrain"].PretrainDataset._preprocess_item

@@ -419,6 +419,34 @@ def mlm_mask(inputs, token_classes, special_mask, chosen, as_mask, as_random, ra
     return inputs, labels, attention
 
 
+def preprocess_item(masked, token_classes, img_features, location_embeddings, next_action, max_img_seq_length,
+                    masked_token_prediction=True, no_action_grounding=False):
+    """PretrainDataset._preprocess_item, vs/data_loader_pretrain.py:636-712, after its _mask_tokens call (``masked`` = that call's
+    (inputs, labels, attention_mask)) and its feature read (``img_features`` [n, D], ``location_embeddings`` [n, Dl])."""
+    inputs, labels, attention = masked
+    R = max_img_seq_length
+    n = img_features.shape[0]
+    attention = [int(a) for a in attention.tolist()]
+    if n > R:                                                          # :656-665 keep the LAST R rows
+        img_features, location_embeddings = img_features[n - R:] if R > 0 else img_features[n:], \
+            location_embeddings[n - R:] if R > 0 else location_embeddings[n:]
+        if R > 0:
+            attention = attention + [1] * img_features.shape[0]
+    else:                                                              # :666-690 zero padding, attention 0 on it
+        if R > 0:
+            attention = attention + [1] * n
+        img_features = torch.cat([img_features, torch.zeros(R - n, img_features.shape[1], dtype=img_features.dtype)], 0)
+        location_embeddings = torch.cat([location_embeddings, torch.zeros(R - n, location_embeddings.shape[1],
+                                                                          dtype=location_embeddings.dtype)], 0)
+        if R > 0:
+            attention = attention + [0] * (R - n)
+    tail = [-1] * img_features.shape[0]
+    return dict(input_ids=inputs, labels=torch.tensor(labels.tolist() + tail, dtype=torch.long),                       # :692-693
+                token_labels=torch.tensor(token_classes.tolist() + tail, dtype=torch.long) if masked_token_prediction else None,   # :697-702
+                attention_mask=attention, img_feats=img_features, img_location_embeddings=location_embeddings,
+                next_action=-1 if no_action_grounding else next_action)                                                 # :695-696
+
+
 # --------------------------------------------------------------------------------------------
 # helpers for tests / bench
 # --------------------------------------------------------------------------------------------

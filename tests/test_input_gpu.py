@@ -104,3 +104,82 @@ def test_mlm_mask_refuses_cpu_and_bad_dtypes():
         ip.mask_tokens(torch.zeros(4, dtype=torch.int32, device=DEV), None, lut, MASK, PAD, seed=0)
     out, labels, att = ip.mask_tokens(torch.zeros((0, 8), dtype=torch.long, device=DEV), None, lut, MASK, PAD, seed=0)
     assert out.shape == (0, 8) and labels.shape == (0, 8) and att.shape == (0, 8)
+
+
+# ---- region packing and the whole-batch collation -----------------------------------------------------------------------
+def _ragged(counts, D, DL, seed):
+    g = torch.Generator().manual_seed(seed)
+    n = int(sum(counts))
+    feats, loc = torch.randn(n, D, generator=g), torch.randn(n, DL, generator=g)
+    off = torch.zeros(len(counts) + 1, dtype=torch.long)
+    off[1:] = torch.tensor(counts, dtype=torch.long).cumsum(0)
+    return feats, loc, off
+
+
+@pytest.mark.parametrize("counts,R,D,DL", [([180, 256, 300, 0, 1, 255, 257, 90], 256, 2054, 128), ([3, 0, 9], 4, 7, 5), ([0, 0], 3, 8, 2),
+                                           ([5], 1, 2054, 2052)])
+def test_pack_regions_matches_oracle_bit_exact(counts, R, D, DL):
+    feats, loc, off = _ragged(counts, D, DL, 3)
+    B, T = len(counts), 5
+    att = torch.full((B, T + R), 7, dtype=torch.long, device=DEV)
+    n0 = lib.launch_count()
+    img, lo = ip.pack_regions(feats.to(DEV), loc.to(DEV), off.to(DEV), R, attention_out=att, attention_col=T)
+    assert lib.launch_count() - n0 == 1
+    dummy = (torch.zeros(T, dtype=torch.long), torch.zeros(T, dtype=torch.long), torch.full((T,), 7))
+    for b, n in enumerate(counts):
+        a, e = int(off[b]), int(off[b + 1])
+        want = vo.preprocess_item(dummy, torch.zeros(T, dtype=torch.long), feats[a:e], loc[a:e], 0, R)
+        assert torch.equal(img[b].cpu(), want["img_feats"]) and torch.equal(lo[b].cpu(), want["img_location_embeddings"]), b
+        assert att[b].tolist() == want["attention_mask"], b
+
+
+def test_collate_pretrain_on_the_reference_fixture():
+    """The samples of the reference's _preprocess_item fixture as ONE device batch: features, locations, attention and token labels equal
+    the reference's outputs bit for bit (they do not depend on the random draws); ids / labels equal the oracle on the kernel's draws."""
+    fix = load_fixture("preprocess_item_small")
+    R = fix["R"]
+    for mtp in (True, False):
+        cs = [c for c in fix["cases"] if c["mtp"] == mtp and not c["no_action_grounding"]]
+        ids = torch.stack([c["ids"] for c in cs])
+        tc = torch.stack([c["token_classes"] for c in cs])
+        feats, loc = torch.cat([c["feats"] for c in cs]), torch.cat([c["loc"] for c in cs])
+        off = torch.tensor([0] + [c["n"] for c in cs]).cumsum(0)
+        lut = ip.special_lut(fix["vocab"], fix["special"], DEV)
+        na = torch.tensor([c["next_action"] for c in cs])
+        batch = ip.collate_pretrain(ids.to(DEV), tc.to(DEV), feats.to(DEV), loc.to(DEV), off.to(DEV), na.to(DEV), lut, fix["mask_id"], fix["pad_id"],
+                                    seed=5, max_img_seq_length=R, masked_token_prediction=mtp)
+        (w_ids, w_labels, _), _, _ = _oracle(ids, tc if mtp else None, 5, vocab=fix["vocab"], special=fix["special"])
+        T = ids.shape[1]
+        assert torch.equal(batch["input_ids"].cpu(), w_ids) and torch.equal(batch["labels"][:, :T].cpu(), w_labels)
+        assert bool((batch["labels"][:, T:] == -1).all())
+        for b, c in enumerate(cs):
+            want = c["out"]
+            assert torch.equal(batch["img_feats"][b].cpu(), want["img_feats"])
+            assert torch.equal(batch["img_location_embeddings"][b].cpu(), want["img_location_embeddings"])
+            assert batch["attention_mask"][b].tolist() == [int(a) for a in want["attention_mask"]]
+            assert int(batch["next_action"][b]) == want["next_action"]
+            if mtp:
+                assert torch.equal(batch["token_labels"][b].cpu(), want["token_labels"])
+            else:
+                assert batch["token_labels"] is None and want["token_labels"] is None
+    nag = ip.collate_pretrain(ids.to(DEV), tc.to(DEV), feats.to(DEV), loc.to(DEV), off.to(DEV), na.to(DEV), lut, fix["mask_id"], fix["pad_id"], seed=5,
+                              max_img_seq_length=R, no_action_grounding=True)
+    assert bool((nag["next_action"] == -1).all())
+
+
+def test_collated_batch_runs_through_the_model():
+    """collate_pretrain's dictionary is what PreTrainOscar.forward takes (same keys as the reference's loader output)."""
+    from visitron_b200 import modeling
+    from visitron_b200.pretrained import BertConfig
+    cfg = BertConfig(30522, num_hidden_layers=1, hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+    cfg.img_feature_dim, cfg.detector_classes, cfg.action_space = 2054, 1601, 36
+    torch.manual_seed(0)
+    model = modeling.PreTrainOscar(cfg).to(DEV).train()
+    ids, tc = _batch(4, 64, 21, True)
+    feats, loc, off = _ragged([10, 32, 40, 0], 2054, 128, 4)
+    lut = ip.special_lut(V, SPECIAL, DEV)
+    batch = ip.collate_pretrain(ids.to(DEV), tc.to(DEV), feats.to(DEV), loc.to(DEV), off.to(DEV), torch.tensor([1, 5, 35, 0], device=DEV), lut, MASK,
+                                PAD, seed=8, max_img_seq_length=32)
+    out = model(**batch)
+    out[0].backward()
+    assert torch.isfinite(out[0]) and model.bert.embeddings.word_embeddings.weight.grad is not None

@@ -184,3 +184,23 @@ def test_mlm_mask_oracle_matches_reference_fixture():
         if c["mtp"]:
             forced = c["token_classes"] != -1
             assert bool((ids[forced] == fix["mask_id"]).all()) and bool((labels[forced] == -1).all())
+
+
+def test_preprocess_item_oracle_matches_reference_fixture():
+    """oracle.mlm_mask + oracle.preprocess_item against the reference's own PretrainDataset._preprocess_item
+    (tests/golden/preprocess_item_small.pt): samples with fewer / exactly / more regions than max_img_seq_length and none at all,
+    with and without masked_token_prediction / no_action_grounding.  Bit-exact."""
+    fix = torch.load(os.path.join(GOLDEN, "preprocess_item_small.pt"), weights_only=False)
+    special = torch.zeros(fix["vocab"], dtype=torch.bool)
+    special[torch.tensor(fix["special"])] = True
+    for c in fix["cases"]:
+        masked = vo.mlm_mask(c["ids"], c["token_classes"] if c["mtp"] else None, special[c["ids"]], c["chosen"], c["as_mask"], c["as_random"],
+                             c["random_words"], fix["mask_id"], fix["pad_id"])
+        got = vo.preprocess_item(masked, c["token_classes"], c["feats"], c["loc"], c["next_action"], fix["R"], c["mtp"], c["no_action_grounding"])
+        want = c["out"]
+        assert set(got) == set(want)
+        for k, v in want.items():
+            if torch.is_tensor(v):
+                assert torch.equal(got[k], v), (c["n"], k)
+            else:
+                assert got[k] == v or (k == "attention_mask" and [int(a) for a in v] == got[k]), (c["n"], k)

@@ -51,6 +51,7 @@ SIGNATURES = {
     "vt_clip_grad_norm": (I, [P, I64, I64, F, P, P, I, P]),
     "vt_mlm_mask": (I, [P, P, P, I64, I64, I64, I64, F, U64, P, P, P, P]),
     "vt_mlm_draws": (I, [I64, I64, U64, P, P, P]),
+    "vt_pack_regions": (I, [P, I64, P, I64, P, I64, I64, P, P, P, I64, P]),
 }
 
 

@@ -53,6 +53,35 @@ mlm_draws_kernel(long long n, long long vocab, uint64_t seed, float* __restrict_
   }
 }
 
+// Ragged region features -> the fixed [B, R, *] block of the model batch (data_loader_pretrain.py:656-690): sample b owns rows
+// [offsets[b], offsets[b+1]) of the packed arrays; if it has more than R rows the LAST R are kept, otherwise the tail is zero
+// padding with attention 0.  One CTA per output row, both arrays (features, location embeddings) in the same launch; 8-byte
+// vector copies (row pitches of 2054 and 2052 floats are 8- but not 16-byte aligned).  HBM-bound: read + write of every row.
+template <typename V>
+__global__ void __launch_bounds__(128)
+pack_regions_kernel(const float* __restrict__ a, int da, const float* __restrict__ b, int db, const long long* __restrict__ offsets,
+                    int R, float* __restrict__ out_a, float* __restrict__ out_b, long long* __restrict__ att, long long ld_att) {
+  constexpr int W = sizeof(V) / 4;
+  const int s = blockIdx.x / R, r = blockIdx.x % R;
+  const long long lo = offsets[s], n = offsets[s + 1] - lo;
+  const long long kept = n < R ? n : R, src = lo + (n - kept) + r;
+  const bool valid = r < kept;
+  V* oa = reinterpret_cast<V*>(out_a + (long long)blockIdx.x * da);
+  V* ob = reinterpret_cast<V*>(out_b + (long long)blockIdx.x * db);
+  V zero;
+  memset(&zero, 0, sizeof(V));
+  if (valid) {
+    const V* ia = reinterpret_cast<const V*>(a + src * da);
+    const V* ib = reinterpret_cast<const V*>(b + src * db);
+    for (int i = threadIdx.x; i < da / W; i += 128) oa[i] = __ldg(ia + i);
+    for (int i = threadIdx.x; i < db / W; i += 128) ob[i] = __ldg(ib + i);
+  } else {
+    for (int i = threadIdx.x; i < da / W; i += 128) oa[i] = zero;
+    for (int i = threadIdx.x; i < db / W; i += 128) ob[i] = zero;
+  }
+  if (att && threadIdx.x == 0) att[(long long)s * ld_att + r] = valid ? 1 : 0;
+}
+
 }  // namespace vt
 
 using namespace vt;
@@ -78,6 +107,26 @@ extern "C" int vt_mlm_draws(int64_t n, int64_t vocab, uint64_t seed, float* u, i
   VT_REQUIRE(u && r, "vt_mlm_draws: null pointer");
   long long g = (n + 255) / 256, cap = (long long)num_sms() * 8;
   mlm_draws_kernel<<<(unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream>>>(n, vocab, seed, u, (long long*)r);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_pack_regions(const float* feats, int64_t d_feat, const float* loc, int64_t d_loc, const int64_t* offsets, int64_t samples,
+                               int64_t regions, float* out_feats, float* out_loc, int64_t* attention_tail, int64_t ld_attention,
+                               vt_stream stream) {
+  VT_REQUIRE(samples >= 0 && regions >= 0 && d_feat > 0 && d_loc > 0 && d_feat < (1 << 30) && d_loc < (1 << 30), "vt_pack_regions: bad sizes");
+  if (samples == 0 || regions == 0) return VT_OK;
+  VT_REQUIRE(offsets && out_feats && out_loc, "vt_pack_regions: null pointer");   // feats / loc may be null when every sample is empty
+  VT_REQUIRE(samples * regions < (1ll << 31), "vt_pack_regions: too many rows for one launch");
+  const unsigned grid = (unsigned)(samples * regions);
+  const bool v2 = d_feat % 2 == 0 && d_loc % 2 == 0 && ((uintptr_t)feats | (uintptr_t)loc | (uintptr_t)out_feats | (uintptr_t)out_loc) % 8 == 0;
+  if (v2)
+    pack_regions_kernel<float2><<<grid, 128, 0, (cudaStream_t)stream>>>(feats, (int)d_feat, loc, (int)d_loc, (const long long*)offsets, (int)regions,
+                                                                        out_feats, out_loc, (long long*)attention_tail, ld_attention);
+  else
+    pack_regions_kernel<float><<<grid, 128, 0, (cudaStream_t)stream>>>(feats, (int)d_feat, loc, (int)d_loc, (const long long*)offsets, (int)regions,
+                                                                       out_feats, out_loc, (long long*)attention_tail, ld_attention);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;

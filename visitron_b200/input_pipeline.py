@@ -50,3 +50,49 @@ def draws(n: int, vocab_size: int, seed: int, device) -> Tuple[torch.Tensor, tor
         lib.check(lib.init(torch.device(device).index).vt_mlm_draws(n, vocab_size, int(seed) & (2 ** 64 - 1), u.data_ptr(), r.data_ptr(),
                                                                    lib.stream_ptr()), "vt_mlm_draws")
     return u, r
+
+
+def pack_regions(feats: torch.Tensor, loc: torch.Tensor, offsets: torch.Tensor, regions: int,
+                 attention_out: Optional[torch.Tensor] = None, attention_col: int = 0) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Ragged region rows -> ([B, regions, D], [B, regions, Dl]): keep the LAST ``regions`` rows of a sample that has more, zero-pad
+    one that has fewer (data_loader_pretrain.py:656-690), one launch for both arrays.  ``offsets`` int64 [B + 1] on the device;
+    with ``attention_out`` ([B, >= attention_col + regions] int64) columns [attention_col, attention_col + regions) receive 1 / 0."""
+    lib.require_device(feats)
+    if feats.dtype != torch.float32 or loc.dtype != torch.float32 or offsets.dtype != torch.int64:
+        raise lib.VtError("pack_regions expects fp32 rows and int64 offsets")
+    if feats.dim() != 2 or loc.dim() != 2 or feats.shape[0] != loc.shape[0]:
+        raise ValueError("feats [rows, D] and loc [rows, Dl] must have the same number of rows")
+    feats, loc, offsets = feats.contiguous(), loc.contiguous(), offsets.contiguous()
+    B = offsets.numel() - 1
+    out_f = torch.empty((B, regions, feats.shape[1]), dtype=torch.float32, device=feats.device)
+    out_l = torch.empty((B, regions, loc.shape[1]), dtype=torch.float32, device=feats.device)
+    att_ptr, ld = None, 0
+    if attention_out is not None:
+        if attention_out.dtype != torch.int64 or attention_out.stride(-1) != 1 or attention_out.shape[1] < attention_col + regions:
+            raise lib.VtError("attention_out must be a row-major int64 [B, >= attention_col + regions] tensor")
+        att_ptr, ld = attention_out.data_ptr() + 8 * attention_col, attention_out.stride(0)
+    with torch.cuda.device(feats.device):
+        lib.check(lib.init(feats.device.index).vt_pack_regions(lib.ptr(feats) or None, feats.shape[1], lib.ptr(loc) or None, loc.shape[1], offsets.data_ptr(), B,
+                                                               regions, lib.ptr(out_f) or None, lib.ptr(out_l) or None, att_ptr, ld, lib.stream_ptr()),
+                  "vt_pack_regions")
+    return out_f, out_l
+
+
+def collate_pretrain(token_ids: torch.Tensor, token_classes: torch.Tensor, feats: torch.Tensor, loc: torch.Tensor, offsets: torch.Tensor,
+                     next_action: torch.Tensor, lut: torch.Tensor, mask_token_id: int, pad_token_id: int, seed: int, max_img_seq_length: int,
+                     masked_token_prediction: bool = True, no_action_grounding: bool = False, mlm_probability: float = 0.15) -> dict:
+    """A whole pre-training batch from its raw pieces, on the device, in two launches plus three small concatenations:
+    what ``PretrainDataset._preprocess_item`` (data_loader_pretrain.py:636-712) does per sample on the host, with the same keys
+    (``PreTrainOscar.forward(**batch)`` takes them as they are)."""
+    B, T = token_ids.shape
+    R = int(max_img_seq_length)
+    ids, labels, att_text = mask_tokens(token_ids, token_classes if masked_token_prediction else None, lut, mask_token_id, pad_token_id, seed,
+                                        mlm_probability)
+    attention = torch.empty((B, T + R), dtype=torch.int64, device=ids.device)
+    attention[:, :T] = att_text
+    img, loc_out = pack_regions(feats, loc, offsets, R, attention_out=attention, attention_col=T)
+    tail = torch.full((B, R), -1, dtype=torch.int64, device=ids.device)
+    batch = dict(input_ids=ids, labels=torch.cat([labels, tail], 1), attention_mask=attention, img_feats=img, img_location_embeddings=loc_out,
+                 token_labels=torch.cat([token_classes, tail], 1) if masked_token_prediction else None,
+                 next_action=torch.full_like(next_action, -1) if no_action_grounding else next_action)
+    return batch
