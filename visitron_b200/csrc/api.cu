@@ -1,3 +1,4 @@
+#include <stdlib.h>
 // Library-wide state: error string, device checks.
 #include <stdarg.h>
 #include <string.h>
@@ -36,6 +37,10 @@ int num_sms() {
 
 // SMs a persistent kernel should occupy: while a gradient exchange is in flight its CTAs hold `reserved` SMs, and a
 // persistent CTA queued behind one of them would start only when the exchange kernel retires (a whole-kernel tail).
+bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("VT_PDL"); return e && e[0] == '1'; }();   // off unless VT_PDL=1, see common.cuh
+  return on;
+}
 int usable_sms() {
   int sms = num_sms() - g_reserved_sms.load(std::memory_order_relaxed);
   return sms < 16 ? 16 : sms;

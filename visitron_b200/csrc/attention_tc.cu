@@ -149,6 +149,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_sync();   // the prologue above overlapped the tail of the previous kernel; global memory is touched only below
   const uint32_t tmem_base = *tmem_slot_ptr;
   const uint32_t tmem_o = tmem_base + 128;
 
@@ -446,6 +447,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_sync();   // the prologue above overlapped the tail of the previous kernel; global memory is touched only below
   const uint32_t tmem_base = *tmem_slot_ptr;
 
   if (warp == BWD_EW_WARPS) {
@@ -747,6 +749,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
 __global__ void __launch_bounds__(256)
 attn_dq_reduce_kernel(const bf16* __restrict__ ws, long long slice, int nkt, long long rows, int hidden, float factor, bf16* __restrict__ dqkv,
                       long long ld) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   const long long per_row = hidden / 8;
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= rows * per_row) return;
@@ -828,8 +831,8 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
   // bookkeeping and the maximum exchange are not duplicated) and measured faster with and without dropout
   // (197 vs 213 us at p = 0.1, 143 vs 147 us at p = 0); the two-thread variant stays selectable for ablations
   const bool two = VT_DBG(16384);
-  if (two) attn_fwd_tc<2><<<(unsigned)(n_items < ctas ? n_items : ctas), 10 * 32, smem, st>>>(tq, tkv, p);
-  else attn_fwd_tc<1><<<(unsigned)(n_items < ctas ? n_items : ctas), 6 * 32, smem, st>>>(tq, tkv, p);
+  if (two) launch_pdl(attn_fwd_tc<2>, (unsigned)(n_items < ctas ? n_items : ctas), 10 * 32, smem, st, tq, tkv, p);
+  else launch_pdl(attn_fwd_tc<1>, (unsigned)(n_items < ctas ? n_items : ctas), 6 * 32, smem, st, tq, tkv, p);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -871,10 +874,10 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
   }
   const long long n_items = (long long)nt * heads * B;
   const int sms = usable_sms();  // leaves the SMs of an overlapped gradient exchange alone (vt_reserve_sms)
-  attn_bwd_fused<<<(unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st>>>(tq, tdo, p);
+  launch_pdl(attn_bwd_fused, (unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st, tq, tdo, p);
   const long long rows = B * S;
   const long long items = rows * (hidden / 8);
-  attn_dq_reduce_kernel<<<(unsigned)((items + 255) / 256), 256, 0, st>>>(p.dq_ws, rows * hidden, nt, rows, (int)hidden,
+  launch_pdl(attn_dq_reduce_kernel, (unsigned)((items + 255) / 256), 256, 0, st, p.dq_ws, rows * hidden, nt, rows, (int)hidden,
                                                                          p.scale * (p.drop.thresh16 ? p.drop.scale : 1.0f), (bf16*)dqkv, ld);
   count_launch(2);
   VT_CHECK_LAUNCH();

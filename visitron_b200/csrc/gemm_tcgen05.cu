@@ -226,6 +226,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_sync();   // the prologue above overlapped the tail of the previous kernel; global memory is touched only below
   const uint32_t tmem_base = *tmem_slot_ptr;
 
   const int mn_tiles = p.m_blocks * p.n_blocks;
@@ -454,7 +455,7 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
     VT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set = true;
   }
-  kern<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, st>>>(ta, tb, p);
+  launch_pdl(kern, grid, GEMM_THREADS, Cfg::SMEM_BYTES, st, ta, tb, p);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;

@@ -48,6 +48,7 @@ __device__ __forceinline__ float fmaxop(float a, float b) { return fmaxf(a, b); 
 __global__ void __launch_bounds__(CE_THREADS)
 softmax_ce_fwd_kernel(const float* __restrict__ logits, long long ld, int ncols, const long long* __restrict__ labels, int double_softmax,
                       float* __restrict__ row_loss, long long* __restrict__ argmax, float* __restrict__ stats) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   __shared__ MaxArg s_ma[CE_THREADS / 32];
   __shared__ float s_f[CE_THREADS / 32];
   const long long row = blockIdx.x;
@@ -84,6 +85,7 @@ __global__ void __launch_bounds__(CE_THREADS)
 softmax_ce_bwd_kernel(const float* __restrict__ logits, long long ld, int ncols, const long long* __restrict__ labels, int double_softmax,
                       const float* __restrict__ stats, float scale, const float* __restrict__ scale_dev, bf16* __restrict__ dlogits,
                       long long ld_out) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   __shared__ float s_f[CE_THREADS / 32];
   const long long row = blockIdx.x;
   const float* x = logits + row * ld;
@@ -126,6 +128,7 @@ __global__ void __launch_bounds__(128)
 action_head_fwd_kernel(const float* __restrict__ pooled, const float* __restrict__ W, const float* __restrict__ bias, int B, int Hd, int A,
                        const long long* __restrict__ labels, float* __restrict__ scores, float* __restrict__ row_loss,
                        long long* __restrict__ argmax) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   const int lane = threadIdx.x & 31;
   const int s = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (s >= B) return;
@@ -187,6 +190,7 @@ __global__ void __launch_bounds__(256)
 action_head_bwd_kernel(const float* __restrict__ pooled, const float* __restrict__ W, int B, int Hd, int A, const long long* __restrict__ labels,
                        const float* __restrict__ scores, const float* __restrict__ n_valid_dev, const float* __restrict__ g_dev,
                        float* __restrict__ dpooled, float* __restrict__ dW, float* __restrict__ dbias) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   extern __shared__ float sd[];  // [B][A] dscore
   const float nv = __ldg(n_valid_dev);
   const float g = (g_dev ? __ldg(g_dev) : 1.0f) / nv;  // nv == 0 -> inf/nan like the reference's empty mean
@@ -228,6 +232,7 @@ pretrain_finalize_kernel(const float* __restrict__ mlm_loss, const long long* __
                          const float* __restrict__ tok_loss, const long long* __restrict__ tok_arg, const long long* __restrict__ tok_lab, long long n_tok,
                          const float* __restrict__ act_loss, const long long* __restrict__ act_arg, const long long* __restrict__ act_lab, long long n_act,
                          float* __restrict__ out) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   __shared__ float sf[8];
   float a = 0.f, c = 0.f;
   for (long long i = threadIdx.x; i < n_mlm; i += blockDim.x) { a += mlm_loss[i]; c += (mlm_arg[i] == mlm_lab[i]) ? 1.f : 0.f; }
@@ -262,12 +267,14 @@ pretrain_finalize_kernel(const float* __restrict__ mlm_loss, const long long* __
 }
 
 __global__ void tanh_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, long long n, bf16* __restrict__ dx) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dx[i] = __float2bfloat16(dy[i] * (1.0f - y[i] * y[i]));
 }
 
 // dx = dy * gelu'(pre)   (backward of the MLM transform's activation, hf/modeling_bert.py:480-485)
 __global__ void gelu_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ pre, long long n8, bf16* __restrict__ dx) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
     float d[8], x[8];
     unpack8(__ldg(reinterpret_cast<const uint4*>(dy) + i), d);
@@ -279,6 +286,7 @@ __global__ void gelu_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restr
 }
 
 __global__ void cast_bf16_f32_kernel(const bf16* __restrict__ x, long long n8, float* __restrict__ y) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
     float v[8];
     unpack8(__ldg(reinterpret_cast<const uint4*>(x) + i), v);
@@ -288,6 +296,7 @@ __global__ void cast_bf16_f32_kernel(const bf16* __restrict__ x, long long n8, f
 }
 // y = bf16(x) (+ bf16 add of `addend` when given)
 __global__ void cast_f32_bf16_flat_kernel(const float* __restrict__ x, const bf16* __restrict__ addend, long long n8, bf16* __restrict__ y) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
     float4 a = __ldg(reinterpret_cast<const float4*>(x) + 2 * i), b = __ldg(reinterpret_cast<const float4*>(x) + 2 * i + 1);
     float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
@@ -309,7 +318,7 @@ extern "C" int vt_softmax_ce_fwd(const float* logits, int64_t ld, int64_t rows, 
                                  float* row_loss, int64_t* argmax, float* stats, vt_stream stream) {
   VT_REQUIRE(rows >= 0 && ncols > 0 && ncols < (1ll << 31) && ld >= ncols, "vt_softmax_ce_fwd: bad sizes");
   if (rows == 0) return VT_OK;
-  softmax_ce_fwd_kernel<<<(unsigned)rows, CE_THREADS, 0, (cudaStream_t)stream>>>(logits, ld, (int)ncols, (const long long*)labels, double_softmax,
+  launch_pdl(softmax_ce_fwd_kernel, (unsigned)rows, CE_THREADS, 0, (cudaStream_t)stream, logits, ld, (int)ncols, (const long long*)labels, double_softmax,
                                                                                  row_loss, (long long*)argmax, stats);
   count_launch(1);
   VT_CHECK_LAUNCH();
@@ -320,7 +329,7 @@ extern "C" int vt_softmax_ce_bwd(const float* logits, int64_t ld, int64_t rows, 
                                  const float* stats, float scale, const float* scale_dev, void* dlogits, int64_t ld_out, vt_stream stream) {
   VT_REQUIRE(rows >= 0 && ncols > 0 && ld >= ncols && ld_out >= ncols, "vt_softmax_ce_bwd: bad sizes");
   if (rows == 0) return VT_OK;
-  softmax_ce_bwd_kernel<<<(unsigned)rows, CE_THREADS, 0, (cudaStream_t)stream>>>(logits, ld, (int)ncols, (const long long*)labels, double_softmax,
+  launch_pdl(softmax_ce_bwd_kernel, (unsigned)rows, CE_THREADS, 0, (cudaStream_t)stream, logits, ld, (int)ncols, (const long long*)labels, double_softmax,
                                                                                  stats, scale, scale_dev, (bf16*)dlogits, ld_out);
   count_launch(1);
   VT_CHECK_LAUNCH();
@@ -331,7 +340,7 @@ extern "C" int vt_action_head_fwd(const float* pooled, const float* W, const flo
                                   const int64_t* labels, float* scores, float* row_loss, int64_t* argmax, vt_stream stream) {
   VT_REQUIRE(actions > 0 && actions <= MAX_ACTIONS, "vt_action_head_fwd: action space %lld outside the supported envelope (<= 64)", (long long)actions);
   if (B == 0) return VT_OK;
-  action_head_fwd_kernel<<<(unsigned)((B + 3) / 4), 128, 0, (cudaStream_t)stream>>>(pooled, W, bias, (int)B, (int)hidden, (int)actions,
+  launch_pdl(action_head_fwd_kernel, (unsigned)((B + 3) / 4), 128, 0, (cudaStream_t)stream, pooled, W, bias, (int)B, (int)hidden, (int)actions,
                                                                                     (const long long*)labels, scores, row_loss, (long long*)argmax);
   count_launch(1);
   VT_CHECK_LAUNCH();
@@ -346,7 +355,7 @@ extern "C" int vt_action_head_bwd(const float* pooled, const float* W, int64_t B
   const size_t smem = (size_t)B * actions * sizeof(float);
   static bool attr = false;
   if (!attr) { VT_CUDA(cudaFuncSetAttribute(action_head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)); attr = true; }
-  action_head_bwd_kernel<<<24, 256, smem, (cudaStream_t)stream>>>(pooled, W, (int)B, (int)hidden, (int)actions, (const long long*)labels, scores,
+  launch_pdl(action_head_bwd_kernel, 24, 256, smem, (cudaStream_t)stream, pooled, W, (int)B, (int)hidden, (int)actions, (const long long*)labels, scores,
                                                                  n_valid_dev, g_dev, dpooled, dW, dbias);
   count_launch(1);
   VT_CHECK_LAUNCH();
@@ -356,7 +365,7 @@ extern "C" int vt_action_head_bwd(const float* pooled, const float* W, int64_t B
 extern "C" int vt_pretrain_finalize(const float* mlm_loss, const int64_t* mlm_arg, const int64_t* mlm_lab, int64_t n_mlm, const float* tok_loss,
                                     const int64_t* tok_arg, const int64_t* tok_lab, int64_t n_tok, const float* act_loss, const int64_t* act_arg,
                                     const int64_t* act_lab, int64_t n_act, float* out8, vt_stream stream) {
-  pretrain_finalize_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(mlm_loss, (const long long*)mlm_arg, (const long long*)mlm_lab, n_mlm, tok_loss,
+  launch_pdl(pretrain_finalize_kernel, 1, 256, 0, (cudaStream_t)stream, mlm_loss, (const long long*)mlm_arg, (const long long*)mlm_lab, n_mlm, tok_loss,
                                                                (const long long*)tok_arg, (const long long*)tok_lab, n_tok, act_loss,
                                                                (const long long*)act_arg, (const long long*)act_lab, n_act, out8);
   count_launch(1);
@@ -366,7 +375,7 @@ extern "C" int vt_pretrain_finalize(const float* mlm_loss, const int64_t* mlm_ar
 
 extern "C" int vt_tanh_bwd(const float* dy, const float* y, int64_t n, void* dx, vt_stream stream) {
   if (n == 0) return VT_OK;
-  tanh_bwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(dy, y, n, (bf16*)dx);
+  launch_pdl(tanh_bwd_kernel, (unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream, dy, y, n, (bf16*)dx);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -376,7 +385,7 @@ extern "C" int vt_gelu_bwd(const void* dy, const void* pre, int64_t n, void* dx,
   VT_REQUIRE(n % 8 == 0 && ((uintptr_t)dy & 15) == 0 && ((uintptr_t)pre & 15) == 0 && ((uintptr_t)dx & 15) == 0, "vt_gelu_bwd: n %% 8 == 0 and 16-byte alignment required");
   if (n == 0) return VT_OK;
   long long n8 = n / 8, g = (n8 + 255) / 256, cap = (long long)num_sms() * 16;
-  gelu_bwd_kernel<<<(unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream>>>((const bf16*)dy, (const bf16*)pre, n8, (bf16*)dx);
+  launch_pdl(gelu_bwd_kernel, (unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream, (const bf16*)dy, (const bf16*)pre, n8, (bf16*)dx);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -386,7 +395,7 @@ extern "C" int vt_cast_bf16_f32(const void* x, int64_t n, float* y, vt_stream st
   VT_REQUIRE(n % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0, "vt_cast_bf16_f32: n %% 8 == 0 and 16-byte alignment required");
   if (n == 0) return VT_OK;
   long long n8 = n / 8, g = (n8 + 255) / 256, cap = (long long)num_sms() * 16;
-  cast_bf16_f32_kernel<<<(unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream>>>((const bf16*)x, n8, y);
+  launch_pdl(cast_bf16_f32_kernel, (unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream, (const bf16*)x, n8, y);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -396,7 +405,7 @@ extern "C" int vt_cast_f32_bf16_add(const float* x, const void* addend, int64_t 
   VT_REQUIRE(n % 8 == 0 && ((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0 && ((uintptr_t)addend & 15) == 0, "vt_cast_f32_bf16_add: n %% 8 == 0 and 16-byte alignment required");
   if (n == 0) return VT_OK;
   long long n8 = n / 8, g = (n8 + 255) / 256, cap = (long long)num_sms() * 16;
-  cast_f32_bf16_flat_kernel<<<(unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream>>>(x, (const bf16*)addend, n8, (bf16*)y);
+  launch_pdl(cast_f32_bf16_flat_kernel, (unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream, x, (const bf16*)addend, n8, (bf16*)y);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;

@@ -121,6 +121,7 @@ __global__ void __launch_bounds__(ROW_WARPS * 32)
 ln_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict__ gamma, const float* __restrict__ beta,
               float eps, long long rows, bf16* __restrict__ y, long long ldy, DropoutCfg drop, long long rin, long long rout,
               long long roff) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float g[CH][8], b[CH][8];
   load_vec_f32(gamma, lane, g);
@@ -154,6 +155,7 @@ ln_bwd_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restric
               const float* __restrict__ gamma, float eps, long long rows, bf16* __restrict__ dx, long long lddx,
               bf16* __restrict__ dxd, long long lddxd, float* __restrict__ partials, DropoutCfg drop_in, DropoutCfg drop_out,
               long long rin, long long rout, long long roff) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float g[CH][8];
   load_vec_f32(gamma, lane, g);
@@ -233,6 +235,7 @@ embed_ln_fwd_kernel(const long long* __restrict__ ids, const long long* __restri
                     const float* __restrict__ word, const float* __restrict__ pos, const float* __restrict__ type,
                     const float* __restrict__ gamma, const float* __restrict__ beta, float eps, long long batch, long long T,
                     long long S_out, bf16* __restrict__ y, DropoutCfg drop) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float g[CH][8], b[CH][8];
   load_vec_f32(gamma, lane, g);
@@ -274,6 +277,7 @@ embed_ln_bwd_kernel(const bf16* __restrict__ dy, const long long* __restrict__ i
                     const float* __restrict__ type, const float* __restrict__ gamma, float eps, long long batch, long long T,
                     long long S_out, float* __restrict__ dword, float* __restrict__ dpos, float* __restrict__ dtype,
                     float* __restrict__ partials, DropoutCfg drop) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float g[CH][8];
   load_vec_f32(gamma, lane, g);
@@ -338,6 +342,7 @@ embed_ln_bwd_kernel(const bf16* __restrict__ dy, const long long* __restrict__ i
 // ---------------------------------------------------------------------------------------------
 __global__ void reduce_partials_kernel(const float* __restrict__ part, long long nrows, long long row_stride, long long ncols,
                                        float* __restrict__ out, int accumulate) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   // grid (column blocks of 32, row splits): with more than one row split the splits meet in `out` through fp32 atomics
   // (accumulate mode only; `out` then already holds a value to add to)
   __shared__ float red[8][33];
@@ -360,6 +365,7 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, long long
 // the NACC column sums a LayerNorm / embedding backward leaves in part[cta][a][H]: one launch, blockIdx.z = a
 struct ReduceOuts { float* p[4]; };
 __global__ void reduce_partials_multi_kernel(const float* __restrict__ part, long long nrows, int nacc, ReduceOuts outs) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   __shared__ float red[8][33];
   float* out = outs.p[blockIdx.z];
   if (!out) return;
@@ -386,6 +392,7 @@ static inline dim3 reduce_grid(long long ncols, long long nrows, int accumulate)
 // column sums of a bf16 matrix [rows, ncols] (ncols % 8 == 0): part[blockIdx.y][col]
 __global__ void __launch_bounds__(256)
 colsum_partial_kernel(const bf16* __restrict__ x, long long ldx, long long rows, long long ncols, float* __restrict__ part) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   const long long col = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8;
   if (col >= ncols) return;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -405,6 +412,7 @@ colsum_partial_kernel(const bf16* __restrict__ x, long long ldx, long long rows,
 // ---------------------------------------------------------------------------------------------
 __global__ void cast_transpose_kernel(const float* __restrict__ src, long long lds, long long rows, long long cols,
                                       bf16* __restrict__ dst, long long ldd, bf16* __restrict__ dst_t, long long ldt) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   __shared__ float tile[32][33];
   const long long c0 = (long long)blockIdx.x * 32, r0 = (long long)blockIdx.y * 32;
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
@@ -424,6 +432,7 @@ __global__ void cast_transpose_kernel(const float* __restrict__ src, long long l
 // out[r, 0:d0] = a[r], out[r, d0:d0+d1] = b[r], out[r, d0+d1:ldo] = 0   (fp32 -> bf16)
 __global__ void pad_cast_concat_kernel(const float* __restrict__ a, long long d0, const float* __restrict__ b, long long d1,
                                        long long rows, bf16* __restrict__ out, long long ldo) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
     const float* ar = a + r * d0;
     const float* br = b ? b + r * d1 : nullptr;
@@ -442,6 +451,7 @@ __global__ void pad_cast_concat_kernel(const float* __restrict__ a, long long d0
 __global__ void __launch_bounds__(ROW_WARPS * 32)
 dropout_rows_kernel(const bf16* __restrict__ x, long long ldx, long long rows, bf16* __restrict__ y, long long ldy, DropoutCfg drop,
                     long long rin, long long rout, long long roff) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (long long m = (long long)blockIdx.x * ROW_WARPS + warp; m < rows; m += (long long)gridDim.x * ROW_WARPS) {
     float v[CH][8];
@@ -454,6 +464,7 @@ dropout_rows_kernel(const bf16* __restrict__ x, long long ldx, long long rows, b
 // dst[r] = src[idx[r]]   /  dst[idx[r]] += src[r]      (768-wide bf16 rows; idx rows are unique)
 __global__ void __launch_bounds__(ROW_WARPS * 32)
 gather_rows_kernel(const bf16* __restrict__ src, long long lds, const long long* __restrict__ idx, long long n, bf16* __restrict__ dst, long long ldd) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (long long r = (long long)blockIdx.x * ROW_WARPS + warp; r < n; r += (long long)gridDim.x * ROW_WARPS) {
     const bf16* s = src + idx[r] * lds;
@@ -464,6 +475,7 @@ gather_rows_kernel(const bf16* __restrict__ src, long long lds, const long long*
 }
 __global__ void __launch_bounds__(ROW_WARPS * 32)
 scatter_add_rows_kernel(const bf16* __restrict__ src, long long lds, const long long* __restrict__ idx, long long n, bf16* __restrict__ dst, long long ldd) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (long long r = (long long)blockIdx.x * ROW_WARPS + warp; r < n; r += (long long)gridDim.x * ROW_WARPS) {
     float a[CH][8], b[CH][8];
@@ -490,8 +502,7 @@ extern "C" int vt_layernorm_fwd(const void* x, int64_t ldx, const float* gamma, 
   VT_REQUIRE(hidden == H, "vt_layernorm_fwd: hidden size %lld outside the supported envelope (768)", (long long)hidden);
   VT_REQUIRE(aligned16(x) && aligned16(y) && aligned16(gamma) && aligned16(beta) && ldx % 8 == 0 && ldy % 8 == 0, "vt_layernorm_fwd: 16-byte alignment required");
   if (rows == 0) return VT_OK;
-  ln_fwd_kernel<<<row_grid(rows), ROW_WARPS * 32, 0, (cudaStream_t)stream>>>(
-      (const bf16*)x, ldx, gamma, beta, eps, rows, (bf16*)y, ldy, make_dropout(dropout_p, seed, dropout_stream), remap_rows_in,
+  launch_pdl(ln_fwd_kernel, row_grid(rows), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const bf16*)x, ldx, gamma, beta, eps, rows, (bf16*)y, ldy, make_dropout(dropout_p, seed, dropout_stream), remap_rows_in,
       remap_rows_out, remap_row_off);
   count_launch(1);
   VT_CHECK_LAUNCH();
@@ -511,7 +522,7 @@ extern "C" int vt_layernorm_bwd(const void* dy, int64_t lddy, const void* x, int
   if (rows == 0) return VT_OK;
   const int grid = ln_bwd_grid(rows);
   cudaStream_t st = (cudaStream_t)stream;
-  ln_bwd_kernel<<<grid, ROW_WARPS * 32, 0, st>>>((const bf16*)dy, lddy, (const bf16*)x, ldx, gamma, eps, rows, (bf16*)dx, lddx,
+  launch_pdl(ln_bwd_kernel, grid, ROW_WARPS * 32, 0, st, (const bf16*)dy, lddy, (const bf16*)x, ldx, gamma, eps, rows, (bf16*)dx, lddx,
                                                  (bf16*)dx_dropped, lddxd, partials, make_dropout(in_dropout_p, seed, in_dropout_stream),
                                                  make_dropout(out_dropout_p, seed, out_dropout_stream), remap_rows_in, remap_rows_out,
                                                  remap_row_off);
@@ -520,7 +531,7 @@ extern "C" int vt_layernorm_bwd(const void* dy, int64_t lddy, const void* x, int
   // second stage: accumulate into the fp32 gradient buffers
   ReduceOuts outs = {{dgamma, dbeta, dbias, nullptr}};
   const int splits = grid > 64 ? (grid + 63) / 64 < 16 ? (grid + 63) / 64 : 16 : 1;
-  reduce_partials_multi_kernel<<<dim3(H / 32, splits, 3), dim3(32, 8), 0, st>>>(partials, grid, 3, outs);
+  launch_pdl(reduce_partials_multi_kernel, dim3(H / 32, splits, 3), dim3(32, 8), 0, st, partials, grid, 3, outs);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -533,8 +544,7 @@ extern "C" int vt_embed_ln_fwd(const int64_t* ids, const int64_t* type_ids, cons
   VT_REQUIRE(hidden == H, "vt_embed_ln_fwd: hidden size %lld outside the supported envelope (768)", (long long)hidden);
   VT_REQUIRE(aligned16(word) && aligned16(pos) && aligned16(type) && aligned16(y) && aligned16(gamma) && aligned16(beta), "vt_embed_ln_fwd: 16-byte alignment required");
   if (batch * T == 0) return VT_OK;
-  embed_ln_fwd_kernel<<<row_grid(batch * T), ROW_WARPS * 32, 0, (cudaStream_t)stream>>>(
-      (const long long*)ids, (const long long*)type_ids, (const long long*)pos_ids, word, pos, type, gamma, beta, eps, batch, T,
+  launch_pdl(embed_ln_fwd_kernel, row_grid(batch * T), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const long long*)ids, (const long long*)type_ids, (const long long*)pos_ids, word, pos, type, gamma, beta, eps, batch, T,
       out_rows_per_sample, (bf16*)y, make_dropout(dropout_p, seed, dropout_stream));
   count_launch(1);
   VT_CHECK_LAUNCH();
@@ -551,7 +561,7 @@ extern "C" int vt_embed_ln_bwd(const void* dy, const int64_t* ids, const int64_t
   if (batch * T == 0) return VT_OK;
   const int grid = row_grid(batch * T);
   cudaStream_t st = (cudaStream_t)stream;
-  embed_ln_bwd_kernel<<<grid, ROW_WARPS * 32, 0, st>>>((const bf16*)dy, (const long long*)ids, (const long long*)type_ids,
+  launch_pdl(embed_ln_bwd_kernel, grid, ROW_WARPS * 32, 0, st, (const bf16*)dy, (const long long*)ids, (const long long*)type_ids,
                                                        (const long long*)pos_ids, word, pos, type, gamma, eps, batch, T,
                                                        out_rows_per_sample, dword, dpos, dtype, partials,
                                                        make_dropout(dropout_p, seed, dropout_stream));
@@ -559,7 +569,7 @@ extern "C" int vt_embed_ln_bwd(const void* dy, const int64_t* ids, const int64_t
   VT_CHECK_LAUNCH();
   ReduceOuts outs = {{dgamma, dbeta, dtype, type_vocab > 1 ? dtype + H : nullptr}};
   const int splits = grid > 64 ? (grid + 63) / 64 < 16 ? (grid + 63) / 64 : 16 : 1;
-  reduce_partials_multi_kernel<<<dim3(H / 32, splits, 4), dim3(32, 8), 0, st>>>(partials, grid, 4, outs);
+  launch_pdl(reduce_partials_multi_kernel, dim3(H / 32, splits, 4), dim3(32, 8), 0, st, partials, grid, 4, outs);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -580,8 +590,8 @@ extern "C" int vt_colsum_bf16(const void* x, int64_t ldx, int64_t rows, int64_t 
   const int gy = (int)vt_colsum_partials_rows(rows);
   const int threads = 128;
   const int gx = (int)((npad / 8 + threads - 1) / threads);
-  colsum_partial_kernel<<<dim3(gx, gy), threads, 0, st>>>((const bf16*)x, ldx, rows, npad, partials);
-  reduce_partials_kernel<<<reduce_grid(ncols, gy, accumulate), dim3(32, 8), 0, st>>>(partials, gy, npad, ncols, out, accumulate);
+  launch_pdl(colsum_partial_kernel, dim3(gx, gy), threads, 0, st, (const bf16*)x, ldx, rows, npad, partials);
+  launch_pdl(reduce_partials_kernel, reduce_grid(ncols, gy, accumulate), dim3(32, 8), 0, st, partials, gy, npad, ncols, out, accumulate);
   count_launch(2);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -592,7 +602,7 @@ extern "C" int vt_cast_f32_bf16(const float* src, int64_t lds, int64_t rows, int
   VT_REQUIRE(src && (dst || dst_t), "vt_cast_f32_bf16: null pointer");
   if (rows == 0 || cols == 0) return VT_OK;
   dim3 grid((unsigned)((cols + 31) / 32), (unsigned)((rows + 31) / 32));
-  cast_transpose_kernel<<<grid, dim3(32, 8), 0, (cudaStream_t)stream>>>(src, lds, rows, cols, (bf16*)dst, ldd, (bf16*)dst_t, ldt);
+  launch_pdl(cast_transpose_kernel, grid, dim3(32, 8), 0, (cudaStream_t)stream, src, lds, rows, cols, (bf16*)dst, ldd, (bf16*)dst_t, ldt);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -603,7 +613,7 @@ extern "C" int vt_pad_cast_concat(const float* a, int64_t d0, const float* b, in
   VT_REQUIRE(a && out && ldo % 2 == 0 && ldo >= d0 + d1 && ((uintptr_t)out & 3) == 0, "vt_pad_cast_concat: bad arguments");
   if (rows == 0) return VT_OK;
   long long cap = (long long)num_sms() * 8;
-  pad_cast_concat_kernel<<<(int)(rows < cap ? rows : cap), 256, 0, (cudaStream_t)stream>>>(a, d0, b, d1, rows, (bf16*)out, ldo);
+  launch_pdl(pad_cast_concat_kernel, (int)(rows < cap ? rows : cap), 256, 0, (cudaStream_t)stream, a, d0, b, d1, rows, (bf16*)out, ldo);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -614,8 +624,7 @@ extern "C" int vt_dropout_rows(const void* x, int64_t ldx, int64_t rows, int64_t
                                int64_t remap_row_off, vt_stream stream) {
   VT_REQUIRE(hidden == H && ldx % 8 == 0 && ldy % 8 == 0 && aligned16(x) && aligned16(y), "vt_dropout_rows: bad arguments");
   if (rows == 0) return VT_OK;
-  dropout_rows_kernel<<<row_grid(rows), ROW_WARPS * 32, 0, (cudaStream_t)stream>>>(
-      (const bf16*)x, ldx, rows, (bf16*)y, ldy, make_dropout(dropout_p, seed, dropout_stream), remap_rows_in, remap_rows_out, remap_row_off);
+  launch_pdl(dropout_rows_kernel, row_grid(rows), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const bf16*)x, ldx, rows, (bf16*)y, ldy, make_dropout(dropout_p, seed, dropout_stream), remap_rows_in, remap_rows_out, remap_row_off);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -625,7 +634,7 @@ extern "C" int vt_gather_rows(const void* src, int64_t lds, const int64_t* idx, 
                               vt_stream stream) {
   VT_REQUIRE(hidden == H && lds % 8 == 0 && ldd % 8 == 0 && aligned16(src) && aligned16(dst), "vt_gather_rows: bad arguments");
   if (n == 0) return VT_OK;
-  gather_rows_kernel<<<row_grid(n), ROW_WARPS * 32, 0, (cudaStream_t)stream>>>((const bf16*)src, lds, (const long long*)idx, n, (bf16*)dst, ldd);
+  launch_pdl(gather_rows_kernel, row_grid(n), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const bf16*)src, lds, (const long long*)idx, n, (bf16*)dst, ldd);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -635,7 +644,7 @@ extern "C" int vt_scatter_add_rows(const void* src, int64_t lds, const int64_t* 
                                    vt_stream stream) {
   VT_REQUIRE(hidden == H && lds % 8 == 0 && ldd % 8 == 0 && aligned16(src) && aligned16(dst), "vt_scatter_add_rows: bad arguments");
   if (n == 0) return VT_OK;
-  scatter_add_rows_kernel<<<row_grid(n), ROW_WARPS * 32, 0, (cudaStream_t)stream>>>((const bf16*)src, lds, (const long long*)idx, n, (bf16*)dst, ldd);
+  launch_pdl(scatter_add_rows_kernel, row_grid(n), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const bf16*)src, lds, (const long long*)idx, n, (bf16*)dst, ldd);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
