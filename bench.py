@@ -84,7 +84,7 @@ class ClockSampler:
             mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
         except Exception:
             mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-        return (float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)), nv.nvmlDeviceGetPowerUsage(self.h) / 1e3, int(mask))
+        return (float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)), nv.nvmlDeviceGetPowerUsage(self.h) / 1e3, int(mask), time.perf_counter())
 
     def _run(self):
         while self.alive:
@@ -98,12 +98,17 @@ class ClockSampler:
     def start(self):
         self.rows, self.on = [], True
 
+    def window(self, t0, t1):
+        """median SM clock / max power of the samples taken between two host times"""
+        rows = [r for r in list(self.rows) if t0 <= r[3] <= t1]
+        return (statistics.median(r[0] for r in rows), round(max(r[1] for r in rows), 1)) if rows else (None, None)
+
     def stop(self):
         self.on = False
         if self.h is None:
             return dict(sm_mhz=None, sm_max_mhz=None, reasons=["NVML unavailable (%s)" % getattr(self, "err", "?")])
         rows = list(self.rows)
-        reasons = sorted({name for _, _, m in rows for bit, name in self.REASONS if m & bit})
+        reasons = sorted({name for _, _, m, _ in rows for bit, name in self.REASONS if m & bit})
         sm = [r[0] for r in rows]
         return dict(sm_mhz=statistics.median(sm) if sm else None, sm_max_mhz=self.max_mhz, power_w_max=max((r[1] for r in rows), default=None),
                     samples=len(rows), reasons=reasons)
@@ -319,13 +324,22 @@ def run_ours(args):
     if sampler:
         sampler.start()
     # --repeats regions of EXACTLY --steps steps each, every one bracketed as the contract says; `value` is the MEDIAN region and
-    # all of them are listed in the line (a single 0.24 s region caught a one-off 100 ms stall on one box in ten: 34.9 ms/step
-    # against 23.6 for the regions before and after it)
-    regions = []
+    # all of them are listed in the line with the SM clock and board power sampled inside each.  Why: about one 0.24 s region in
+    # ten is hit by a 100-300 ms stall of the HOST thread on the shared box (profiles/r1_region_diag.txt: the slow regions show
+    # HIGHER clocks and LOWER power, i.e. an idle GPU, with and without Python's cyclic GC) -- e.g. 34.9 or 57.9 ms per step
+    # between regions of 23.7.  The median of 5 ignores up to two such regions; `e2e` is measured the same way.
+    regions, region_clk = [], []
+    if args.manual_gc:   # diagnosis: keep the cyclic collector out of the timed regions
+        import gc
+        gc.collect()
+        gc.freeze()
+        gc.disable()
     for _ in range(max(1, args.repeats)):
         lib.reset_launch_count()
+        h0 = time.perf_counter()
         regions.append(timed(lambda i: step(dev_batches[i % n_host]), args.steps))
         launches = lib.launch_count()
+        region_clk.append(sampler.window(h0, time.perf_counter()) if sampler else (None, None))
     ms = statistics.median(regions)
     clocks = sampler.stop() if sampler else None
     value = world * b * args.steps / (ms / 1e3)
@@ -352,8 +366,11 @@ def run_ours(args):
         return torch.stack([o.detach().float() for o in out]).cpu()   # D2H read of the step's scalars (host sync, as the loop's .item())
 
     e2e_step(0)
-    slots = [None, None]
-    e2e_ms = timed(e2e_step, args.steps)
+    e2e_regions = []
+    for _ in range(max(1, args.repeats)):
+        slots = [None, None]
+        e2e_regions.append(timed(e2e_step, args.steps))
+    e2e_ms = statistics.median(e2e_regions)
     e2e_value = world * b * args.steps / (e2e_ms / 1e3)
 
     # ---- roofline of the dominant kernel: per-launch CUDA events around every GEMM, same K steps ----
@@ -400,13 +417,13 @@ def run_ours(args):
         metric=METRIC, value=round(value, 2), unit=UNIT, n_gpus=world, steps=args.steps, warmup=n_warm,
         ms_per_step=round(ms / args.steps, 3), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16",
         data="synthetic", timed_regions=dict(n=len(regions), steps_each=args.steps, ms_per_step=[round(r / args.steps, 3) for r in regions],
-                                             reported="median"),
+                                             sm_mhz=[c[0] for c in region_clk], power_w_max=[c[1] for c in region_clk], reported="median"),
         config=dict(workload=wl.desc,
                     per_gpu_batch=b, global_batch=b * world, seq_len=S, parallelism="dp%d" % world, dropout=args.dropout,
                     l2="per-step working set (%.1f GB of activations) >> 126 MB L2; 4 rotating batches" % (b * S * 24.5e3 * 12 / 1e9),
                     grad_allreduce="fp32, one bucket per encoder layer, overlapped with backward" if world > 1 else "none (1 GPU)"),
         e2e=dict(value=round(e2e_value, 2), unit=UNIT, h2d_bytes_per_step=h2d_bytes, d2h_bytes_per_step=4 * n_out,
-                 ms_per_step=round(e2e_ms / args.steps, 3)),
+                 ms_per_step=round(e2e_ms / args.steps, 3), regions_ms_per_step=[round(r / args.steps, 3) for r in e2e_regions], reported="median"),
         gpu_launches=int(launches),
         clocks=clocks,
         model_flops=dict(per_sample_fwd_bwd_all_rows_GF=round(wl.flop_mult * fl["total"] / 1e9, 1),
@@ -497,7 +514,8 @@ def main():
                     help="pretrain = BASELINE configs[2] (the data-parallel headline); viewpoint_select = configs[1] (encoder at S=511 + candidate scorer); "
                          "turn_based = configs[3]; qa_classifier = configs[4] (sweep --batch)")
     ap.add_argument("--min-warm-s", type=float, default=1.0, help="keep warming up until this much wall time has passed")
-    ap.add_argument("--repeats", type=int, default=3, help="timed regions of --steps steps each; the median is reported, all are listed")
+    ap.add_argument("--repeats", type=int, default=5, help="timed regions of --steps steps each; the median is reported, all are listed")
+    ap.add_argument("--manual-gc", action="store_true", help="diagnosis: gc.freeze() + gc.disable() around the timed regions")
     ap.add_argument("--no-clocks", action="store_true", help="diagnosis: do not sample clocks during the timed region")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
