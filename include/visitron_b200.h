@@ -166,12 +166,17 @@ int vt_scatter_add_rows(const void* src, int64_t lds, const int64_t* idx, int64_
 int vt_mask_bias(const void* mask, int mask_dtype, int64_t n, float* bias, vt_stream stream);
 /* Debug hook for tests: 0 = auto (tcgen05 kernels for S <= 2048), 1 = mma.sync kernels, 2 = tcgen05 kernels. */
 void vt_debug_attention_impl(int impl);
-int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, int64_t B, int64_t S, int64_t heads, int64_t head_dim,
-                     void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream);
+/* Optional plan of the key tiles worth visiting: key_tiles[b] bit t = the 64-key tile t of sample b holds a key whose bias is within
+ * 5000 of the sample's largest (an unmasked key).  The probabilities of the other tiles are exactly 0 in the reference's fp32 softmax
+ * (exp(-10000 + ...) underflows), so the kernels skip them without changing a bit of ctx or of any gradient.  S <= 2048.
+ * Pass NULL as key_tiles to visit every tile. */
+int vt_attention_key_tiles(const float* bias, int64_t B, int64_t S, uint32_t* key_tiles, vt_stream stream);
+int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, int64_t B, int64_t S, int64_t heads,
+                     int64_t head_dim, void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream);
 int64_t vt_attention_bwd_workspace(int64_t B, int64_t S, int64_t heads);
-int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, const void* ctx, const void* dctx, const float* lse,
-                     float* dsum_ws, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv, float dropout_p,
-                     uint64_t seed, uint32_t dropout_stream, vt_stream stream);
+int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, const void* ctx, const void* dctx,
+                     const float* lse, float* dsum_ws, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv,
+                     float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream);
 
 /* ------------------------------------------------------------------------------------------
  * Pre-training heads (vs/encoder.py:377-441).

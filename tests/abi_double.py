@@ -203,14 +203,19 @@ def _attn(qkv, bias, B, S, heads):
     return (p @ v).permute(0, 2, 1, 3).reshape(B * S, Hh)
 
 
-def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None):
+def attention_key_tiles(bias):
+    CALLS.append("attention_key_tiles")
+    return None
+
+
+def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None, key_tiles=None):
     CALLS.append("attention_fwd")
     _no_dropout(dropout_p)
     out = _attn(qkv.float(), bias, B, S, heads).to(BF16)
     return out, torch.zeros((B, heads, S, 2))
 
 
-def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None):
+def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None, key_tiles=None):
     CALLS.append("attention_bwd")
     _no_dropout(dropout_p)
     q = qkv.float().requires_grad_(True)
@@ -308,7 +313,7 @@ def to_bf16(x, addend=None, out=None):
 
 
 _OPS = ["layernorm_fwd", "layernorm_bwd", "embed_ln_fwd", "embed_ln_bwd", "colsum", "cast_weight", "pad_cast_concat",
-        "dropout_rows", "gather_rows", "scatter_add_rows", "mask_bias", "attention_fwd", "attention_bwd", "softmax_ce_fwd",
+        "dropout_rows", "gather_rows", "scatter_add_rows", "mask_bias", "attention_key_tiles", "attention_fwd", "attention_bwd", "softmax_ce_fwd",
         "softmax_ce_bwd", "action_head_fwd", "action_head_bwd", "pretrain_finalize", "tanh_bwd", "gelu_bwd", "to_f32", "to_bf16"]
 
 

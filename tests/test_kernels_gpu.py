@@ -356,3 +356,38 @@ def test_action_head_and_finalize():
     y = torch.tanh(torch.randn(4, 768, device=DEV))
     dy = torch.randn(4, 768, device=DEV)
     close(ops.tanh_bwd(dy, y), dy * (1 - y * y), what="tanh bwd")
+
+
+@pytest.mark.parametrize("B,S,heads,p", [(3, 767, 2, 0.0), (4, 767, 3, 0.1), (2, 511, 2, 0.1), (2, 100, 1, 0.0), (2, 2048, 1, 0.1)])
+def test_attention_key_tile_plan_changes_no_bit(B, S, heads, p):
+    """Skipping the key tiles that are masked as a whole (vt_attention_key_tiles) must leave ctx, the saved row statistics and every
+    gradient bit-identical to the kernels that visit all tiles: masked keys have probability exactly 0 (exp(-10000 + ...) underflows)."""
+    g = torch.Generator().manual_seed(B * S)
+    mask = torch.zeros(B, S, dtype=torch.long)
+    T = min(511, S)
+    for b in range(B):                       # [text | pad | regions | pad] like the loader's batches; sample 0 has a one-token text
+        lt = 1 if b == 0 else int(torch.randint(T // 5, T + 1, (1,), generator=g))
+        mask[b, :lt] = 1
+        if S > T:
+            mask[b, T:T + int(torch.randint(1, S - T + 1, (1,), generator=g))] = 1
+    if B > 2:
+        mask[2] = 0                          # a sample with EVERY key masked: uniform softmax over all keys, every tile stays live
+    mask = mask.to(DEV)
+    qkv = (torch.randn(B * S, 3 * heads * 64, generator=g) * 0.7).to(DEV).to(torch.bfloat16)
+    dctx = (torch.randn(B * S, heads * 64, generator=g)).to(DEV).to(torch.bfloat16)
+    bias = ops.mask_bias(mask)
+    plan = ops.attention_key_tiles(bias)
+    nkt = (S + 63) // 64
+    want = []
+    for b in range(B):
+        m = mask[b].cpu()
+        bits = sum(1 << t for t in range(nkt) if bool(m[t * 64:(t + 1) * 64].any()))
+        want.append(bits if bits else (1 << nkt) - 1)
+    assert [int(x) & 0xffffffff for x in plan.tolist()] == want
+    assert any(bin(w).count("1") < nkt for w in want), "the test must skip something"
+    ctx0, lse0 = ops.attention_fwd(qkv, bias, B, S, heads, dropout_p=p, seed=7, stream_id=3)
+    ctx1, lse1 = ops.attention_fwd(qkv, bias, B, S, heads, dropout_p=p, seed=7, stream_id=3, key_tiles=plan)
+    assert torch.equal(ctx0, ctx1) and torch.equal(lse0, lse1)
+    d0 = ops.attention_bwd(qkv, bias, ctx0, dctx, lse0, B, S, heads, dropout_p=p, seed=7, stream_id=3)
+    d1 = ops.attention_bwd(qkv, bias, ctx0, dctx, lse0, B, S, heads, dropout_p=p, seed=7, stream_id=3, key_tiles=plan)
+    assert torch.equal(d0, d1)

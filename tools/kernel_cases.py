@@ -62,6 +62,12 @@ def main():
     gW = torch.zeros(I * H, dtype=F32, device=dev)
     gvec = torch.zeros(4 * I, dtype=F32, device=dev)
     ctx0, lse0 = ops.attention_fwd(qkvs[0], bias, B, S, NH, pa, seed, 0)
+    # the bench's own padding ([text 40-100 % of 511 | 180 of 256 regions]) and its key-tile plan
+    from visitron_b200 import synthetic
+    bmask = synthetic.pretrain_batch(B, 88)["attention_mask"].to(dev) if S == 767 else mask
+    bbias = ops.mask_bias(bmask)
+    plan = ops.attention_key_tiles(bbias)
+    ctx1, lse1 = ops.attention_fwd(qkvs[0], bbias, B, S, NH, pa, seed, 0, key_tiles=plan)
     torch.cuda.synchronize()
 
     gemm_fl = lambda n, k: 2.0 * M * n * k
@@ -74,6 +80,7 @@ def main():
     r = lambda L, i: L[i % NROT]
     case("gemm qkv         [M,768]x[2304,768]  bias", lambda i: lib.gemm(r(xs, i), Wqkv, bias=bqkv, out=out_q), gemm_fl(3 * H, H))
     case("attn fwd         S=%d d=64 p=%.1f" % (S, pa), lambda i: ops.attention_fwd(r(qkvs, i), bias, B, S, NH, pa, seed, 0, ctx=out_h), attn_f)
+    case("attn fwd         bench padding, masked key tiles skipped", lambda i: ops.attention_fwd(r(qkvs, i), bbias, B, S, NH, pa, seed, 0, ctx=out_h, key_tiles=plan), attn_f)
     case("gemm attn-out    [M,768]x[768,768]   bias+dropout+residual",
          lambda i: lib.gemm(r(xs, i), Wo, bias=bo, dropout_p=ph, seed=seed, dropout_stream=1, residual=r(xs, i + 1), out=out_h), gemm_fl(H, H))
     case("ln fwd           [M,768]", lambda i: ops.layernorm_fwd(r(xs, i), gamma, beta, 1e-12, out=out_h), 0, 2.0 * M * H * 2)
@@ -91,6 +98,8 @@ def main():
     case("wgrad attn-out   dW[768,768]", lambda i: lib.gemm(r(xs, i), r(xs, i + 1), a_major=1, b_major=1, out=gW[:H * H].view(H, H), accumulate=True), gemm_fl(H, H))
     case("dgrad attn-out   [M,768]x[768,768]", lambda i: lib.gemm(r(xs, i), Wo, b_major=1, out=out_h), gemm_fl(H, H))
     case("attn bwd         (prep + dK/dV + dQ)", lambda i: ops.attention_bwd(qkvs[0], bias, ctx0, r(xs, i), lse0, B, S, NH, pa, seed, 0, dqkv=out_q), 2.5 * attn_f)
+    case("attn bwd         bench padding, masked key tiles skipped",
+         lambda i: ops.attention_bwd(qkvs[0], bbias, ctx1, r(xs, i), lse1, B, S, NH, pa, seed, 0, dqkv=out_q, key_tiles=plan), 2.5 * attn_f)
     case("colsum           [M,2304]", lambda i: ops.colsum(r(qkvs, i), gvec[:3 * H]), 0, 1.0 * M * 3 * H * 2)
     case("wgrad qkv        dW[2304,768]", lambda i: lib.gemm(r(qkvs, i), r(xs, i), a_major=1, b_major=1, out=gW[:3 * H * H].view(3 * H, H), accumulate=True), gemm_fl(3 * H, H))
     case("dgrad qkv        [M,2304]x[2304,768] +residual", lambda i: lib.gemm(r(qkvs, i), Wqkv, b_major=1, residual=r(xs, i), out=out_h), gemm_fl(3 * H, H))
@@ -125,7 +134,7 @@ def main():
         if args.only and args.only not in name:
             continue
         if ci == n_layer:
-            print("layer total (fwd+bwd) %.1f us  -> x12 = %.2f ms" % (tot, tot * 12 / 1e3))
+            print("layer total (fwd+bwd, attention with the key-tile plan) %.1f us  -> x12 = %.2f ms" % (tot, tot * 12 / 1e3))
             layer_tot = tot
         for i in range(3):
             fn(i)
@@ -137,7 +146,7 @@ def main():
         e1.record()
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) * 1e3 / args.iters
-        tot += us if ci < n_layer else 0.0
+        tot += us if ci < n_layer and not (name.startswith("attn") and "skipped" not in name) else 0.0
         rate = "%7.0f TFLOP/s" % (fl / us / 1e6) if fl else "%7.0f GB/s   " % (by / us / 1e3)
         print("%-62s %8.1f us  %s" % (name, us, rate), flush=True)
         rows.append(dict(name=name.split("  ")[0].strip(), us=round(us, 1), tflops=round(fl / us / 1e6, 1) if fl else None,

@@ -25,9 +25,10 @@ SIGNATURES = {
     "vt_scatter_add_rows": (I, [P, I64, P, I64, I64, P, I64, P]),
     "vt_debug_attention_impl": (None, [I]),
     "vt_mask_bias": (I, [P, I, I64, P, P]),
-    "vt_attention_fwd": (I, [P, I64, P, I64, I64, I64, I64, P, P, F, U64, U32, P]),
+    "vt_attention_key_tiles": (I, [P, I64, I64, P, P]),
+    "vt_attention_fwd": (I, [P, I64, P, P, I64, I64, I64, I64, P, P, F, U64, U32, P]),
     "vt_attention_bwd_workspace": (I64, [I64, I64, I64]),
-    "vt_attention_bwd": (I, [P, I64, P, P, P, P, P, I64, I64, I64, I64, P, F, U64, U32, P]),
+    "vt_attention_bwd": (I, [P, I64, P, P, P, P, P, P, I64, I64, I64, I64, P, F, U64, U32, P]),
     "vt_softmax_ce_fwd": (I, [P, I64, I64, I64, P, I, P, P, P, P]),
     "vt_softmax_ce_bwd": (I, [P, I64, I64, I64, P, I, P, F, P, P, I64, P]),
     "vt_action_head_fwd": (I, [P, P, P, I64, I64, I64, P, P, P, P, P]),

@@ -49,6 +49,7 @@ constexpr float kRescaleTau = 5.545177444f;  // ln(2^8): rescale O only when the
 struct AttnTcParams {
   int B, S, heads, hidden;
   const float* bias;   // [B, S]
+  const uint32_t* key_tiles;   // [B] bit t = the 64-key tile t of the sample has an unmasked key (vt_attention_key_tiles); null = all
   float scale;
   bf16* out;           // fwd: ctx [B*S, hidden]
   float* lse;          // [B, heads, S, 2] = (reference max, 1 / sum)
@@ -102,6 +103,69 @@ constexpr int FWD_MAX_S = 2048;
 //  * HV threads per query row: HV = 2 gives every scheduler 4 softmax warps and was meant to hide latency, but with S / P
 //    double-buffered there is little left to hide and its duplicated per-tile bookkeeping costs more than it gains, so the
 //    host launches HV = 1.
+// ---------------------------------------------------------------------------------------------
+// Key tiles that are masked out as a whole are skipped.  The reference adds -10000 to the scores of masked keys
+// (vs/encoder.py:226-241), so their probabilities underflow to exactly 0 in fp32 as soon as the row has one unmasked key:
+// a 64-key tile without any such key contributes nothing to the row sums, to O, or to any gradient, and leaving it out
+// changes no bit of the result.  The batches of this workload are padded to fixed lengths ([text <= 511 | regions <= 256]),
+// so typically a quarter of the key tiles go.  key_tile_plan_kernel marks a tile as live when its largest bias is within
+// 5000 of the sample's largest bias (robust for any mask value; a sample with every key masked keeps all its tiles and
+// gets the same uniform softmax as the reference).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+key_tile_plan_kernel(const float* __restrict__ bias, int S, uint32_t* __restrict__ plan) {
+  __shared__ float tmax[32];
+  const int b = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nkt = (S + 63) / 64;
+  for (int t = warp; t < 32; t += 4) {
+    float m = -INFINITY;
+    if (t < nkt) {
+      const int k0 = t * 64 + lane, k1 = k0 + 32;
+      if (k0 < S) m = bias[(long long)b * S + k0];
+      if (k1 < S) m = fmaxf(m, bias[(long long)b * S + k1]);
+    }
+    m = warp_max(m);
+    if (lane == 0) tmax[t] = m;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const float m = warp_max(tmax[lane]);
+    const uint32_t live = __ballot_sync(0xffffffffu, tmax[lane] > m - 5000.0f && lane < nkt);
+    if (lane == 0) plan[b] = live ? live : (nkt == 32 ? 0xffffffffu : (1u << nkt) - 1u);
+  }
+}
+
+// walks the live key tiles of a CTA's items in order (same sequence in the TMA, MMA and softmax roles)
+struct TileCursor {
+  const uint32_t* plan;
+  int item0, my_items, items_per_sample;
+  uint32_t dense;
+  int it;
+  uint32_t full, rem;
+  __device__ __forceinline__ void load() {
+    if (it < my_items) {
+      full = plan ? __ldg(plan + (item0 + it) / items_per_sample) : dense;
+      rem = full;
+    } else {
+      full = rem = 0;
+    }
+  }
+  __device__ __forceinline__ void init(const uint32_t* pl, int i0, int n, int ips, int nkt) {
+    plan = pl; item0 = i0; my_items = n; items_per_sample = ips;
+    dense = nkt == 32 ? 0xffffffffu : (1u << nkt) - 1u;
+    it = 0;
+    load();
+  }
+  __device__ __forceinline__ bool done() const { return it >= my_items; }
+  __device__ __forceinline__ int tile() const { return __ffs((int)rem) - 1; }
+  __device__ __forceinline__ bool first() const { return rem == full; }
+  __device__ __forceinline__ bool last() const { return (rem & (rem - 1)) == 0; }
+  __device__ __forceinline__ void next() {
+    rem &= rem - 1;
+    if (!rem) { ++it; load(); }
+  }
+};
+
 template <int HV>
 __global__ void __launch_bounds__((4 * HV + 2) * 32, 2)
 attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const AttnTcParams p) {
@@ -124,7 +188,6 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   const int n_items = nqt * p.heads * p.B;
   const int item0 = (int)((long long)n_items * blockIdx.x / gridDim.x), item1 = (int)((long long)n_items * (blockIdx.x + 1) / gridDim.x);
   const int my_items = item1 - item0;
-  const int G = my_items * nkt;   // key tiles this CTA walks, numbered g = item * nkt + j
   auto decode = [&](int id, int& qt, int& h, int& b) { qt = id % nqt; h = (id / nqt) % p.heads; b = id / (nqt * p.heads); };
 
   if (warp == FWD_SM_WARPS && lane == 0) {
@@ -156,25 +219,26 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   if (warp == FWD_SM_WARPS) {
     // ---------------- TMA producer: runs ahead of the consumers across items, bounded by the rings ----------------
     if (lane == 0) {
-      int g = 0;
-      for (int it = 0; it < my_items; ++it) {
-        int qt, h, b;
-        decode(item0 + it, qt, h, b);
-        const int row_base = b * S;
-        const int qb = it % FWD_QB;
-        if (it >= FWD_QB) mbar_wait_backoff(q_empty + 8 * qb, (uint32_t)((it / FWD_QB - 1) & 1), 32);
-        mbar_arrive_expect_tx(q_full + 8 * qb, 16384);
-        tma_load_2d(sQ + qb * 16384, &tmQ, q_full + 8 * qb, h * 64, row_base + qt * FQ);
-        for (int j = 0; j < nkt; ++j, ++g) {
-          const int st = g % FWD_KV;
-          const uint32_t ph = (uint32_t)((g / FWD_KV - 1) & 1);
-          if (g >= FWD_KV) mbar_wait_backoff(k_empty + 8 * st, ph, 32);
-          mbar_arrive_expect_tx(k_full + 8 * st, 8192);
-          tma_load_2d(sK + st * 8192, &tmKV, k_full + 8 * st, p.hidden + h * 64, row_base + j * FK);
-          if (g >= FWD_KV) mbar_wait_backoff(v_empty + 8 * st, ph, 32);
-          mbar_arrive_expect_tx(v_full + 8 * st, 8192);
-          tma_load_2d(sV + st * 8192, &tmKV, v_full + 8 * st, 2 * p.hidden + h * 64, row_base + j * FK);
+      TileCursor c;
+      c.init(p.key_tiles, item0, my_items, nqt * p.heads, nkt);
+      int qt = 0, h = 0, b = 0;
+      for (int g = 0; !c.done(); ++g, c.next()) {
+        if (c.first()) {
+          const int it = c.it, qb = it % FWD_QB;
+          decode(item0 + it, qt, h, b);
+          if (it >= FWD_QB) mbar_wait_backoff(q_empty + 8 * qb, (uint32_t)((it / FWD_QB - 1) & 1), 32);
+          mbar_arrive_expect_tx(q_full + 8 * qb, 16384);
+          tma_load_2d(sQ + qb * 16384, &tmQ, q_full + 8 * qb, h * 64, b * S + qt * FQ);
         }
+        const int j = c.tile(), row_base = b * S;
+        const int st = g % FWD_KV;
+        const uint32_t ph = (uint32_t)((g / FWD_KV - 1) & 1);
+        if (g >= FWD_KV) mbar_wait_backoff(k_empty + 8 * st, ph, 32);
+        mbar_arrive_expect_tx(k_full + 8 * st, 8192);
+        tma_load_2d(sK + st * 8192, &tmKV, k_full + 8 * st, p.hidden + h * 64, row_base + j * FK);
+        if (g >= FWD_KV) mbar_wait_backoff(v_empty + 8 * st, ph, 32);
+        mbar_arrive_expect_tx(v_full + 8 * st, 8192);
+        tma_load_2d(sV + st * 8192, &tmKV, v_full + 8 * st, 2 * p.hidden + h * 64, row_base + j * FK);
       }
     }
   } else if (warp == FWD_SM_WARPS + 1) {
@@ -182,42 +246,47 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     if (lane == 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(128, FK, 0, 0);   // S[128 q, 64 keys] = Q (K-major) x K (K-major)
       constexpr uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);   // O[128 q, 64 d]   = P (K-major) x V (MN-major)
-      auto issue_s = [&](int g) {   // S(g) -> TMEM buffer g & 1; frees K stage g & 1 (and the item's Q buffer after its last tile)
-        const int it = g / nkt, j = g - it * nkt, st = g % FWD_KV, qb = it % FWD_QB;
-        if (j == 0) mbar_wait_backoff(q_full + 8 * qb, (uint32_t)((it / FWD_QB) & 1), MMA_POLL_NS);
-        mbar_wait_backoff(k_full + 8 * st, (uint32_t)((g / FWD_KV) & 1), MMA_POLL_NS);
+      TileCursor ci, cc;   // ci: the next S to issue (runs two tiles ahead), cc: the next P.V
+      ci.init(p.key_tiles, item0, my_items, nqt * p.heads, nkt);
+      cc.init(p.key_tiles, item0, my_items, nqt * p.heads, nkt);
+      int gi = 0;
+      auto issue_s = [&]() {   // S(gi) -> TMEM buffer gi & 1; frees its K stage (and the item's Q buffer after its last tile)
+        const int it = ci.it, st = gi % FWD_KV, qb = it % FWD_QB;
+        if (ci.first()) mbar_wait_backoff(q_full + 8 * qb, (uint32_t)((it / FWD_QB) & 1), MMA_POLL_NS);
+        mbar_wait_backoff(k_full + 8 * st, (uint32_t)((gi / FWD_KV) & 1), MMA_POLL_NS);
         tc_fence_after();
         const uint64_t a = make_smem_desc(sQ + qb * 16384, 16, 1024), bd = make_smem_desc(sK + st * 8192, 16, 1024);
         if (!VT_DBG(128)) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + 64 * (g & 1), a + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc_s, k > 0 ? 1u : 0u);
+          for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + 64 * (gi & 1), a + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc_s, k > 0 ? 1u : 0u);
         }
-        umma_commit(s_full + 8 * (g & 1));
+        umma_commit(s_full + 8 * (gi & 1));
         umma_commit(k_empty + 8 * st);
-        if (j == nkt - 1) umma_commit(q_empty + 8 * qb);
+        if (ci.last()) umma_commit(q_empty + 8 * qb);
+        ++gi;
+        ci.next();
       };
-      if (G > 0) issue_s(0);
-      if (G > 1) issue_s(1);
-      int it = 0, j = 0;
-      for (int g = 0; g < G; ++g) {
+      if (!ci.done()) issue_s();
+      if (!ci.done()) issue_s();
+      for (int g = 0; !cc.done(); ++g, cc.next()) {
         const int bf = g & 1;
-        if (g + 2 < G) {   // S(g + 2) reuses S(g)'s TMEM buffer: the softmax warps have pulled S(g) into registers
+        if (!ci.done()) {   // S(g + 2) reuses S(g)'s TMEM buffer: the softmax warps have pulled S(g) into registers
           mbar_wait_backoff(s_free + 8 * bf, (uint32_t)((g >> 1) & 1), MMA_POLL_NS);
-          issue_s(g + 2);
+          issue_s();
         }
         mbar_wait_backoff(p_ready + 8 * bf, (uint32_t)((g >> 1) & 1), MMA_POLL_NS);
         const int vst = g % FWD_KV;
         mbar_wait_backoff(v_full + 8 * vst, (uint32_t)((g / FWD_KV) & 1), MMA_POLL_NS);
-        if (j == 0 && it > 0) mbar_wait_backoff(o_free, (uint32_t)((it - 1) & 1), MMA_POLL_NS);   // previous item's O drained
+        const bool first = cc.first();
+        if (first && cc.it > 0) mbar_wait_backoff(o_free, (uint32_t)((cc.it - 1) & 1), MMA_POLL_NS);   // previous item's O drained
         tc_fence_after();
         const uint64_t a = make_smem_desc(sP + bf * 16384, 16, 1024), bd = make_smem_desc(sV + vst * 8192, 8192, 1024);
         if (!VT_DBG(16)) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) umma_bf16(tmem_o, a + (uint64_t)(2 * k), bd + (uint64_t)(128 * k), idesc_o, (j > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < 4; ++k) umma_bf16(tmem_o, a + (uint64_t)(2 * k), bd + (uint64_t)(128 * k), idesc_o, (!first || k > 0) ? 1u : 0u);
         }
-        umma_commit(p_free + 8 * bf);      // P buffer bf consumed, O holds the item's tiles 0 .. j
+        umma_commit(p_free + 8 * bf);      // P buffer bf consumed, O holds the item's live tiles so far
         umma_commit(v_empty + 8 * vst);
-        if (++j == nkt) { j = 0; ++it; }
       }
     }
   } else {
@@ -241,7 +310,9 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         b_loaded = b;
       }
       float m_used = -INFINITY, l = 0.f;   // l: sum over this thread's columns only
-      for (int j = 0; j < nkt; ++j, ++g) {
+      const uint32_t live = p.key_tiles ? __ldg(p.key_tiles + b) : (nkt == 32 ? 0xffffffffu : (1u << nkt) - 1u);
+      for (uint32_t rem = live; rem; rem &= rem - 1, ++g) {
+        const int j = __ffs((int)rem) - 1;   // the tile's real index: bias columns and dropout counters do not move
         const int bf = g & 1;
         mbar_wait(s_full + 8 * bf, (uint32_t)((g >> 1) & 1));
         tc_fence_after();
@@ -275,7 +346,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
           alpha = ex2_approx((m_used - mx) * kLog2e);
           l *= alpha;
           m_used = mx;
-          resc = j > 0;
+          resc = rem != live;
         }
         const float mb = m_used * kLog2e;
         float rs = 0.f;
@@ -796,8 +867,18 @@ static int attn_dbg() {
 
 static bool use_tc(int64_t S) { return g_attn_impl == 2 || (g_attn_impl == 0 && S <= 2048); }
 
-extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, int64_t B, int64_t S, int64_t heads, int64_t head_dim,
-                                void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream) {
+extern "C" int vt_attention_key_tiles(const float* bias, int64_t B, int64_t S, uint32_t* key_tiles, vt_stream stream) {
+  VT_REQUIRE(bias && key_tiles && B > 0 && S > 0, "vt_attention_key_tiles: bad arguments");
+  VT_REQUIRE(S <= 2048, "vt_attention_key_tiles: a plan is 32 tiles of 64 keys (S <= 2048); pass no plan for longer sequences");
+  launch_pdl(key_tile_plan_kernel, (unsigned)B, 128, 0, (cudaStream_t)stream, bias, (int)S, key_tiles);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, int64_t B, int64_t S, int64_t heads,
+                                int64_t head_dim, void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream,
+                                vt_stream stream) {
   int rc = check_attn_tc("vt_attention_fwd", qkv, ld, B, S, heads, head_dim);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
@@ -814,7 +895,7 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
   if (rc) return rc;
   AttnTcParams p = {};
   p.B = (int)B; p.S = (int)S; p.heads = (int)heads; p.hidden = (int)hidden;
-  p.bias = bias; p.scale = 0.125f; p.out = (bf16*)ctx; p.lse = lse; p.ld = ld;
+  p.bias = bias; p.key_tiles = key_tiles; p.scale = 0.125f; p.out = (bf16*)ctx; p.lse = lse; p.ld = ld;
   p.drop = make_dropout(dropout_p, seed, dropout_stream);
   p.dbg = attn_dbg();
   const int nkt = (int)((S + FK - 1) / FK);
@@ -838,9 +919,9 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
   return VT_OK;
 }
 
-extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, const void* ctx, const void* dctx, const float* lse,
-                                float* dsum_ws, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv, float dropout_p,
-                                uint64_t seed, uint32_t dropout_stream, vt_stream stream) {
+extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, const void* ctx, const void* dctx,
+                                const float* lse, float* dsum_ws, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv,
+                                float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream) {
   int rc = check_attn_tc("vt_attention_bwd", qkv, ld, B, S, heads, head_dim);
   if (rc) return rc;
   VT_REQUIRE(((uintptr_t)dqkv & 15) == 0 && ((uintptr_t)ctx & 15) == 0 && ((uintptr_t)dctx & 15) == 0, "vt_attention_bwd: 16-byte alignment required");

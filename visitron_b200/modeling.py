@@ -201,7 +201,7 @@ class BertPreTrainedModel(PreTrainedModel):
 # per-call state shared by the encoder node and the heads node
 # ------------------------------------------------------------------------------------------------
 class _Step:
-    __slots__ = ("B", "T", "R", "S", "M", "seed", "p_hidden", "p_attn", "ids", "tt", "pos", "bias", "has_img",
+    __slots__ = ("B", "T", "R", "S", "M", "seed", "p_hidden", "p_attn", "ids", "tt", "pos", "bias", "key_tiles", "has_img",
                  "img_cat", "img_pre", "layers", "seq", "pooled", "began", "model", "need_grad")
 
     def __init__(self):
@@ -363,6 +363,7 @@ class BertImgModelwithLocationEmbeds(BertPreTrainedModel):
         if tuple(attention_mask.shape) != (B, step.S):
             raise ValueError("attention_mask must be [batch, text_len + regions] = %s, got %s" % ((B, step.S), tuple(attention_mask.shape)))
         step.bias = ops.mask_bias(attention_mask)
+        step.key_tiles = ops.attention_key_tiles(step.bias)   # once per step: the same padding for all layers, forward and backward
         if step.has_img:
             if img_location_embeddings is None:
                 raise ValueError("img_location_embeddings is required with img_feats (vs/encoder.py:277-279)")
@@ -423,7 +424,7 @@ def _encoder_forward(step: _Step, st: FlatStore, img_feats, img_loc):
     for l in range(cfg.num_hidden_layers):
         p = "encoder.layer.%d." % l
         qkv = lib.gemm(x, st.wb(p + "attention.self.query.weight", 3 * H, H), bias=st.wspan(p + "attention.self.query.bias", 3 * H))
-        ctx, lse = ops.attention_fwd(qkv, step.bias, B, S, nh, step.p_attn, step.seed, 4 * l)
+        ctx, lse = ops.attention_fwd(qkv, step.bias, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles)
         x1 = lib.gemm(ctx, st.wb(p + "attention.output.dense.weight"), bias=st.w(p + "attention.output.dense.bias"),
                       dropout_p=step.p_hidden, seed=step.seed, dropout_stream=4 * l + 1, residual=x)
         y1 = ops.layernorm_fwd(x1, st.w(p + "attention.output.LayerNorm.weight"), st.w(p + "attention.output.LayerNorm.bias"), eps)
@@ -485,7 +486,7 @@ def _encoder_backward(step: _Step, st: FlatStore, d, dpooled):
                                       st.g(p + "attention.output.dense.bias"), out_dropout_p=ph, out_stream=4 * l + 1, seed=step.seed)
         lib.gemm(dx1d, ctx, a_major=1, b_major=1, out=st.g(p + "attention.output.dense.weight"), accumulate=True)
         dctx = lib.gemm(dx1d, st.wb(p + "attention.output.dense.weight"), b_major=1)
-        dqkv = ops.attention_bwd(qkv, step.bias, ctx, dctx, lse, B, S, nh, step.p_attn, step.seed, 4 * l)
+        dqkv = ops.attention_bwd(qkv, step.bias, ctx, dctx, lse, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles)
         ops.colsum(dqkv, st.g(p + "attention.self.query.bias", 3 * H))
         lib.gemm(dqkv, x_in, a_major=1, b_major=1, out=st.g(p + "attention.self.query.weight", 3 * H, H), accumulate=True)
         d = lib.gemm(dqkv, st.wb(p + "attention.self.query.weight", 3 * H, H), b_major=1, residual=dx1)

@@ -132,22 +132,33 @@ def set_attention_impl(impl: int):
     init().vt_debug_attention_impl(int(impl))
 
 
-def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None):
+def attention_key_tiles(bias: torch.Tensor) -> Optional[torch.Tensor]:
+    """uint32-as-int32 [B]: which 64-key tiles of every sample hold an unmasked key; the attention kernels skip the others (exactly-zero
+    probabilities in the reference's fp32 softmax, so no bit of the result changes).  None for S > 2048 (every tile is visited)."""
+    B, S = bias.shape
+    if S > 2048:
+        return None
+    plan = torch.empty(B, device=bias.device, dtype=torch.int32)
+    check(init().vt_attention_key_tiles(ptr(bias), B, S, ptr(plan), stream_ptr()), "vt_attention_key_tiles")
+    return plan
+
+
+def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None, key_tiles=None):
     L = init()
     if ctx is None:
         ctx = torch.empty((B * S, heads * 64), device=qkv.device, dtype=BF16)
     lse = torch.empty((B, heads, S, 2), device=qkv.device, dtype=F32)
-    check(L.vt_attention_fwd(ptr(qkv), qkv.stride(0), ptr(bias), B, S, heads, 64, ptr(ctx), ptr(lse), dropout_p, seed, stream_id,
+    check(L.vt_attention_fwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(key_tiles), B, S, heads, 64, ptr(ctx), ptr(lse), dropout_p, seed, stream_id,
                              stream_ptr()), "vt_attention_fwd")
     return ctx, lse
 
 
-def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None):
+def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None, key_tiles=None):
     L = init()
     if dqkv is None:
         dqkv = torch.empty_like(qkv)
     ws = torch.empty(int(L.vt_attention_bwd_workspace(B, S, heads)), device=qkv.device, dtype=F32)
-    check(L.vt_attention_bwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv),
+    check(L.vt_attention_bwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(key_tiles), ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv),
                              dropout_p, seed, stream_id, stream_ptr()), "vt_attention_bwd")
     return dqkv
 
