@@ -169,7 +169,8 @@ void vt_debug_attention_impl(int impl);
 /* Optional plan of the key tiles worth visiting: key_tiles[b] bit t = the 64-key tile t of sample b holds a key whose bias is within
  * 5000 of the sample's largest (an unmasked key).  The probabilities of the other tiles are exactly 0 in the reference's fp32 softmax
  * (exp(-10000 + ...) underflows), so the kernels skip them without changing a bit of ctx or of any gradient.  S <= 2048.
- * Pass NULL as key_tiles to visit every tile. */
+ * Pass NULL as key_tiles to visit every tile.  vt_attention_fwd (64-key tiles) uses the plan; vt_attention_bwd accepts it and visits
+ * every one of its 128-key tiles (at the loader's padding they are almost never dead as a whole; measured, no gain). */
 int vt_attention_key_tiles(const float* bias, int64_t B, int64_t S, uint32_t* key_tiles, vt_stream stream);
 int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, int64_t B, int64_t S, int64_t heads,
                      int64_t head_dim, void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream);

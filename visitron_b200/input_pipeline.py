@@ -34,12 +34,12 @@ def mask_tokens(inputs: torch.Tensor, token_classes: Optional[torch.Tensor], lut
     if tc is not None and tc.shape != ids.shape:
         raise ValueError("token_classes must have the shape of inputs")
     out, labels = torch.empty_like(ids), torch.empty_like(ids)
-    att = torch.empty(ids.shape, dtype=torch.uint8, device=ids.device)
+    att = torch.empty(ids.shape, dtype=torch.bool, device=ids.device)   # the kernel writes 0 / 1 bytes
     with torch.cuda.device(ids.device):
         lib.check(lib.init(ids.device.index).vt_mlm_mask(ids.data_ptr(), lib.ptr(tc), lut.data_ptr(), ids.numel(), lut.numel(), int(mask_token_id),
                                                          int(pad_token_id), float(mlm_probability), int(seed) & (2 ** 64 - 1), out.data_ptr(),
                                                          labels.data_ptr(), att.data_ptr(), lib.stream_ptr()), "vt_mlm_mask")
-    return out, labels, att.bool()
+    return out, labels, att
 
 
 def draws(n: int, vocab_size: int, seed: int, device) -> Tuple[torch.Tensor, torch.Tensor]:
