@@ -345,30 +345,24 @@ def run_ours(args):
     value = world * b * args.steps / (ms / 1e3)
 
     # ---- end to end from pinned host memory through the public API (`e2e`) ----
-    copy_stream = torch.cuda.Stream()
+    from visitron_b200 import input_pipeline
     h2d_bytes = sum(v.numel() * v.element_size() for v in host[0].values())
-    slots = [None, None]
 
-    def prefetch(i):
-        with torch.cuda.stream(copy_stream):
-            slots[i % 2] = ({k: v.to(device, non_blocking=True) for k, v in host[i % n_host].items()}, copy_stream.record_event())
+    def host_stream():   # the loader: pinned host batches, for ever
+        i = 0
+        while True:
+            yield host[i % n_host]
+            i += 1
+
+    feed = input_pipeline.DevicePrefetcher(host_stream(), device)   # next batch's H2D overlaps this step's compute
 
     def e2e_step(i):
-        if slots[i % 2] is None:
-            prefetch(i)
-        batch, ev = slots[i % 2]
-        slots[i % 2] = None
-        prefetch(i + 1)                       # next batch's H2D overlaps this step's compute
-        torch.cuda.current_stream().wait_event(ev)
-        out = step(batch)
-        for t in batch.values():
-            t.record_stream(torch.cuda.current_stream())
+        out = step(next(feed))
         return torch.stack([o.detach().float() for o in out]).cpu()   # D2H read of the step's scalars (host sync, as the loop's .item())
 
     e2e_step(0)
     e2e_regions = []
     for _ in range(max(1, args.repeats)):
-        slots = [None, None]
         e2e_regions.append(timed(e2e_step, args.steps))
     e2e_ms = statistics.median(e2e_regions)
     e2e_value = world * b * args.steps / (e2e_ms / 1e3)

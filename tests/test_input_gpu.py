@@ -183,3 +183,15 @@ def test_collated_batch_runs_through_the_model():
     out = model(**batch)
     out[0].backward()
     assert torch.isfinite(out[0]) and model.bert.embeddings.word_embeddings.weight.grad is not None
+
+
+def test_device_prefetcher_yields_every_batch_in_order():
+    host = [dict(a=torch.full((64, 1024), float(i)), b=torch.arange(10) + i, c=None) for i in range(5)]
+    seen = 0
+    for i, dev in enumerate(ip.DevicePrefetcher(host, DEV)):
+        assert dev["a"].is_cuda and dev["c"] is None
+        assert torch.equal(dev["a"].cpu(), host[i]["a"]) and torch.equal(dev["b"].cpu(), host[i]["b"])
+        seen += 1
+    assert seen == 5
+    with pytest.raises(lib.VtError):
+        ip.DevicePrefetcher(host, "cpu")

@@ -96,3 +96,47 @@ def collate_pretrain(token_ids: torch.Tensor, token_classes: torch.Tensor, feats
                  token_labels=torch.cat([token_classes, tail], 1) if masked_token_prediction else None,
                  next_action=torch.full_like(next_action, -1) if no_action_grounding else next_action)
     return batch
+
+
+class DevicePrefetcher:
+    """Pinned host batches -> device, one batch ahead, on a copy stream (the loader side of vs/pretrain.py:166-176, where
+    every tensor of a batch is moved with a blocking ``.to(device)`` at the top of the step).  Iterating yields device dictionaries whose
+    H2D copy overlapped the previous step's compute; the consumer's stream waits on the copy's event and the tensors are tied to it with
+    ``record_stream`` so the caching allocator does not hand their memory to the next copy early.  ``None`` values pass through."""
+
+    def __init__(self, batches, device, pin: bool = True):
+        self.it = iter(batches)
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise lib.VtError("DevicePrefetcher moves batches to a CUDA device (there is no CPU path)")
+        self.pin = pin
+        self.stream = torch.cuda.Stream(self.device)
+        self.slot = None
+        self._fetch()
+
+    def _fetch(self):
+        try:
+            host = next(self.it)
+        except StopIteration:
+            self.slot = None
+            return
+        if self.pin:
+            host = {k: (v if v is None or not torch.is_tensor(v) or v.is_pinned() else v.pin_memory()) for k, v in host.items()}
+        with torch.cuda.stream(self.stream):
+            dev = {k: (v.to(self.device, non_blocking=True) if torch.is_tensor(v) else v) for k, v in host.items()}
+            self.slot = (dev, self.stream.record_event(), host)   # the pinned source stays referenced until the copy has been consumed
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        if self.slot is None:
+            raise StopIteration
+        dev, ev, _ = self.slot
+        self._fetch()                                   # the next batch's copy overlaps this step
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(ev)
+        for t in dev.values():
+            if torch.is_tensor(t):
+                t.record_stream(cur)
+        return dev
