@@ -88,6 +88,8 @@ constexpr int FWD_QB = 1;         // Q buffers (2 lets the TMA lane run ahead ac
 constexpr int FWD_KV = 3;         // K and V ring depths (separate rings: S runs two key tiles ahead of P.V)
 constexpr bool FWD_PERSISTENT = false;
 constexpr int FWD_SMEM_TILES = FWD_QB * 16384 + 2 * FWD_KV * 8192 + 2 * 16384;  // Q[QB], K[KV], V[KV], P[2]
+constexpr int FWD_ITEMS_PER_CTA = 2;   // query tiles per CTA: 2 measured 197 -> 191 us (dense) / 171 -> 168 us (key-tile plan), 3 and 6 lose to
+                                       // wave quantisation (209 / 230 us); VT_FWD_ITEMS_PER_CTA overrides for A/B runs
 constexpr int FWD_TMEM_COLS = 256;                                            // S: [0,64) [64,128)   O: [128,192)
 constexpr int FWD_MAX_S = 2048;
 
@@ -907,7 +909,8 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
     attr = true;
   }
   const long long n_items = ((S + FQ - 1) / FQ) * heads * B;
-  const long long ctas = (FWD_PERSISTENT || VT_DBG(32768)) ? 2ll * usable_sms() : n_items;   // persistent: two CTAs per SM, each a contiguous range of items
+  static const int per_cta = [] { const char* e = getenv("VT_FWD_ITEMS_PER_CTA"); const int v = e ? atoi(e) : FWD_ITEMS_PER_CTA; return v > 0 ? v : 1; }();
+  const long long ctas = (FWD_PERSISTENT || VT_DBG(32768)) ? 2ll * usable_sms() : (n_items + per_cta - 1) / per_cta;   // each CTA a contiguous range of items
   // one thread per row executes 28 % fewer instructions than two (ncu: 96.6 M vs 123.4 M warp instructions; the per-tile
   // bookkeeping and the maximum exchange are not duplicated) and measured faster with and without dropout
   // (197 vs 213 us at p = 0.1, 143 vs 147 us at p = 0); the two-thread variant stays selectable for ablations
