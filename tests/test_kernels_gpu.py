@@ -226,7 +226,8 @@ def attn_impl(request):
 
 
 @pytest.mark.parametrize("B,S,heads,mask_kind", [(2, 767, 12, "pad"), (3, 511, 12, "f6"), (1, 64, 2, "pad"), (2, 100, 3, "none"), (1, 1, 1, "none"),
-                                                 (1, 129, 1, "pad"), (2, 1000, 2, "pad")])
+                                                 (1, 129, 1, "pad"), (2, 1000, 2, "pad"),
+                                                 (9, 767, 12, "pad")])   # enough items for two query tiles per CTA in the forward
 def test_attention_fwd_bwd(B, S, heads, mask_kind, attn_impl):
     torch.manual_seed(8)
     Hh = heads * 64
@@ -358,7 +359,7 @@ def test_action_head_and_finalize():
     close(ops.tanh_bwd(dy, y), dy * (1 - y * y), what="tanh bwd")
 
 
-@pytest.mark.parametrize("B,S,heads,p", [(3, 767, 2, 0.0), (4, 767, 3, 0.1), (2, 511, 2, 0.1), (2, 100, 1, 0.0), (2, 2048, 1, 0.1)])
+@pytest.mark.parametrize("B,S,heads,p", [(3, 767, 2, 0.0), (4, 767, 3, 0.1), (2, 511, 2, 0.1), (2, 100, 1, 0.0), (2, 2048, 1, 0.1), (9, 767, 12, 0.1)])
 def test_attention_key_tile_plan_changes_no_bit(B, S, heads, p):
     """Skipping the key tiles that are masked as a whole (vt_attention_key_tiles) must leave ctx, the saved row statistics and every
     gradient bit-identical to the kernels that visit all tiles: masked keys have probability exactly 0 (exp(-10000 + ...) underflows)."""
