@@ -52,7 +52,10 @@ void vt_reset_launch_count(void);
  * vs/encoder.py:324 (token head) and their autograd backward.
  * Epilogue order: acc*alpha -> +bias[n] -> (store aux_out) -> activation -> dropout -> +residual -> store.
  * ------------------------------------------------------------------------------------------ */
-enum { VT_ACT_NONE = 0, VT_ACT_GELU = 1, VT_ACT_TANH = 2, VT_ACT_GELU_BWD = 3, VT_ACT_TANH_BWD = 4 };
+enum { VT_ACT_NONE = 0, VT_ACT_GELU = 1, VT_ACT_TANH = 2, VT_ACT_GELU_BWD = 3, VT_ACT_TANH_BWD = 4,
+       /* the encoder's FFN pair: the forward GEMM writes gelu(x) to D and gelu'(x) -- evaluated on the fp32 accumulator -- to aux_out
+        * (instead of x), so that the backward GEMM's epilogue is one multiply by aux (VT_ACT_MUL_AUX) instead of re-evaluating gelu' */
+       VT_ACT_GELU_SAVE_GRAD = 5, VT_ACT_MUL_AUX = 6 };
 
 typedef struct {
   int out_fp32;           /* 0: D is bf16, 1: D is fp32 */

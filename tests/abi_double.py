@@ -50,9 +50,10 @@ def gemm(A, B, *, a_major=0, b_major=0, out=None, out_dtype=BF16, bias=None, act
     if bias is not None:
         assert bias.dtype == F32
         r = r + bias[:n]
+    _dgelu = lambda x: 0.5 * (1.0 + torch.erf(x / math.sqrt(2.0))) + x * torch.exp(-0.5 * x * x) / math.sqrt(2.0 * math.pi)  # noqa: E731
     if aux_out is not None:
-        aux_out[:, :n].copy_(r.to(BF16))
-    if act == 1:
+        aux_out[:, :n].copy_((_dgelu(r) if act == 5 else r).to(BF16))
+    if act in (1, 5):
         r = r * 0.5 * (1.0 + torch.erf(r / math.sqrt(2.0)))
     elif act == 2:
         r = torch.tanh(r)
@@ -62,6 +63,8 @@ def gemm(A, B, *, a_major=0, b_major=0, out=None, out_dtype=BF16, bias=None, act
     elif act == 4:
         y = aux.float()[:, :n]
         r = r * (1.0 - y * y)
+    elif act == 6:
+        r = r * aux.float()[:, :n]
     rows = _remap_rows(r.size(0), remap or (0, 0, 0), r.device)
     if residual is not None:
         r = r + residual[rows].float()[:, :n]

@@ -63,6 +63,13 @@ def test_gemm_epilogues_and_splitk():
     x = pre.float().requires_grad_(True)
     torch.nn.functional.gelu(x).sum().backward()
     close(lib.gemm(A, B, act=lib.ACT_GELU_BWD, aux=pre), (A.float() @ B.float().t()) * x.grad, what="gelu_bwd")
+    # the FFN pair: forward saves gelu'(x) from the fp32 accumulator, backward multiplies by it
+    dg = torch.empty_like(aux)
+    close(lib.gemm(A, B, bias=bias, act=lib.ACT_GELU_SAVE_GRAD, aux_out=dg), torch.nn.functional.gelu(base), what="gelu (save grad)")
+    xb = base.detach().clone().requires_grad_(True)
+    torch.nn.functional.gelu(xb).sum().backward()
+    close(dg, xb.grad, what="saved gelu'")
+    close(lib.gemm(A, B, act=lib.ACT_MUL_AUX, aux=dg), (A.float() @ B.float().t()) * dg.float(), what="mul aux")
     # weight-gradient shape: both operands MN-major, split-K with fp32 atomics, accumulating into a live buffer
     dY = (torch.randn(4096, 768, device=DEV) * 0.1).to(BF)
     X = (torch.randn(4096, 3072, device=DEV) * 0.1).to(BF)

@@ -16,7 +16,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 
 from visitron_b200 import lib, ops
-from visitron_b200.lib import ACT_GELU, ACT_GELU_BWD
+from visitron_b200.lib import ACT_GELU_SAVE_GRAD, ACT_MUL_AUX
 
 H, I, NH = 768, 3072, 12
 BF16, F32 = torch.bfloat16, torch.float32
@@ -84,14 +84,14 @@ def main():
     case("gemm attn-out    [M,768]x[768,768]   bias+dropout+residual",
          lambda i: lib.gemm(r(xs, i), Wo, bias=bo, dropout_p=ph, seed=seed, dropout_stream=1, residual=r(xs, i + 1), out=out_h), gemm_fl(H, H))
     case("ln fwd           [M,768]", lambda i: ops.layernorm_fwd(r(xs, i), gamma, beta, 1e-12, out=out_h), 0, 2.0 * M * H * 2)
-    case("gemm ffn-up      [M,768]x[3072,768]  bias+gelu+pre", lambda i: lib.gemm(r(xs, i), W1, bias=b1, act=ACT_GELU, aux_out=out_i2, out=out_i), gemm_fl(I, H))
+    case("gemm ffn-up      [M,768]x[3072,768]  bias+gelu, saves gelu'", lambda i: lib.gemm(r(xs, i), W1, bias=b1, act=ACT_GELU_SAVE_GRAD, aux_out=out_i2, out=out_i), gemm_fl(I, H))
     case("gemm ffn-down    [M,3072]x[768,3072] bias+dropout+residual",
          lambda i: lib.gemm(r(zs, i), W2, bias=b2, dropout_p=ph, seed=seed, dropout_stream=2, residual=r(xs, i), out=out_h), gemm_fl(H, I))
     case("ln bwd           [M,768] (+dropped copy, dgamma/dbeta/dbias)",
          lambda i: ops.layernorm_bwd(r(xs, i), r(xs, i + 1), gamma, 1e-12, gvec[:H], gvec[H:2 * H], gvec[2 * H:3 * H], out_dropout_p=ph, out_stream=2,
                                      seed=seed, dx=out_h, dxd=out_h2), 0, 4.0 * M * H * 2)
     case("wgrad ffn-down   dW[768,3072] = dY^T Z", lambda i: lib.gemm(r(xs, i), r(zs, i), a_major=1, b_major=1, out=gW.view(H, I), accumulate=True), gemm_fl(I, H))
-    case("dgrad ffn-down   [M,768]x[768,3072]  gelu'", lambda i: lib.gemm(r(xs, i), W2, b_major=1, act=ACT_GELU_BWD, aux=r(zs, i), out=out_i), gemm_fl(I, H))
+    case("dgrad ffn-down   [M,768]x[768,3072]  x saved gelu'", lambda i: lib.gemm(r(xs, i), W2, b_major=1, act=ACT_MUL_AUX, aux=r(zs, i), out=out_i), gemm_fl(I, H))
     case("colsum           [M,3072]", lambda i: ops.colsum(r(zs, i), gvec[:I]), 0, 1.0 * M * I * 2)
     case("wgrad ffn-up     dW[3072,768] = dPre^T Y", lambda i: lib.gemm(r(zs, i), r(xs, i), a_major=1, b_major=1, out=gW.view(I, H), accumulate=True), gemm_fl(I, H))
     case("dgrad ffn-up     [M,3072]x[3072,768] +residual", lambda i: lib.gemm(r(zs, i), W1, b_major=1, residual=r(xs, i), out=out_h), gemm_fl(I, H))

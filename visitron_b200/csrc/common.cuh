@@ -125,6 +125,15 @@ __device__ __forceinline__ float gelu_grad(float x) {
   return fmaf(x * 0.3989422804014327f, e, normal_cdf(x));
 }
 
+// gelu(x) and d/dx gelu(x) together (one CDF evaluation)
+__device__ __forceinline__ void gelu_fwd_grad(float x, float& y, float& dy) {
+  const float c = normal_cdf(x);
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-0.72134752044448170f * x * x));
+  y = x * c;
+  dy = fmaf(x * 0.3989422804014327f, e, c);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Philox4x32-7 counter RNG.  Dropout masks are never stored: forward and backward regenerate them
 // from (seed, stream id, element index).  One call yields 8 x 16-bit lanes; an element is kept iff

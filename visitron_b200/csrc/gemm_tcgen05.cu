@@ -67,12 +67,12 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 // epilogue warps at different places), fewer registers, and the per-element operand (residual or saved pre-activation)
 // of the NEXT 32-column chunk is prefetched into registers while the current chunk is processed.
 // The fast kinds require: bf16 output, no accumulate / split-K, no row remap, 16-byte aligned operands, N % 8 == 0.
-enum { EPI_BIAS = 1, EPI_GELU = 2, EPI_GELU_BWD = 4, EPI_DROP = 8, EPI_RESID = 16, EPI_GENERIC = 32 };
+enum { EPI_BIAS = 1, EPI_GELU = 2, EPI_GELU_BWD = 4, EPI_DROP = 8, EPI_RESID = 16, EPI_GENERIC = 32, EPI_GELU_SG = 64, EPI_MUL_AUX = 128 };
 
 template <int EPI>
 struct EpiK {
   static constexpr bool generic = (EPI & EPI_GENERIC) != 0;
-  static constexpr bool ext = !generic && (EPI & (EPI_GELU_BWD | EPI_RESID)) != 0;  // prefetched per-element operand
+  static constexpr bool ext = !generic && (EPI & (EPI_GELU_BWD | EPI_MUL_AUX | EPI_RESID)) != 0;  // prefetched per-element operand
 };
 
 // Epilogue of 8 consecutive columns of one output row, in the COALESCED layout: after the in-warp shared-memory
@@ -92,7 +92,20 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, int m, int n
 #pragma unroll
     for (int j = 0; j < 8; ++j) x[j] += bias8[j];
   }
-  if (G ? (p.aux_out != nullptr) : (EPI & EPI_GELU) != 0) {
+  const bool save_grad = G ? (p.act == VT_ACT_GELU_SAVE_GRAD) : (EPI & EPI_GELU_SG) != 0;
+  if (save_grad) {   // D = gelu(x), aux_out = gelu'(x)
+    float dy[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) gelu_fwd_grad(x[j], x[j], dy[j]);
+    bf16* ao = p.aux_out + (long long)m * p.ldaux_out + n0;
+    if (vec) {
+      *reinterpret_cast<uint4*>(ao) = pack8(dy);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (j < ncols) ao[j] = __float2bfloat16(dy[j]);
+    }
+  } else if (G ? (p.aux_out != nullptr) : (EPI & EPI_GELU) != 0) {
     bf16* ao = p.aux_out + (long long)m * p.ldaux_out + n0;
     if (vec) {
       *reinterpret_cast<uint4*>(ao) = pack8(x);
@@ -102,13 +115,14 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, int m, int n
         if (j < ncols) ao[j] = __float2bfloat16(x[j]);
     }
   }
-  if (G ? (p.act == VT_ACT_GELU) : (EPI & EPI_GELU) != 0) {
+  if (save_grad) {
+  } else if (G ? (p.act == VT_ACT_GELU) : (EPI & EPI_GELU) != 0) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) x[j] = gelu_fwd(x[j]);
   } else if (G && p.act == VT_ACT_TANH) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) x[j] = tanhf(x[j]);
-  } else if (G ? (p.act == VT_ACT_GELU_BWD || p.act == VT_ACT_TANH_BWD) : (EPI & EPI_GELU_BWD) != 0) {
+  } else if (G ? (p.act == VT_ACT_GELU_BWD || p.act == VT_ACT_TANH_BWD || p.act == VT_ACT_MUL_AUX) : (EPI & (EPI_GELU_BWD | EPI_MUL_AUX)) != 0) {
     float a[8];
     if (!G) {
       unpack8(ext, a);
@@ -121,7 +135,10 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, int m, int n
         for (int j = 0; j < 8; ++j) a[j] = (j < ncols) ? __bfloat162float(ax[j]) : 0.f;
       }
     }
-    if (!G || p.act == VT_ACT_GELU_BWD) {
+    if (G ? (p.act == VT_ACT_MUL_AUX) : (EPI & EPI_MUL_AUX) != 0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x[j] *= a[j];
+    } else if (!G || p.act == VT_ACT_GELU_BWD) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) x[j] *= gelu_grad(a[j]);
     } else {
@@ -500,7 +517,9 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   VT_REQUIRE(ep->split_k <= 1 || ep->accumulate, "vt_gemm_bf16: split_k > 1 needs accumulate");
   VT_REQUIRE(ep->dropout_p <= 0.f || N % 8 == 0, "vt_gemm_bf16: dropout epilogue needs N %% 8 == 0");
   VT_REQUIRE(ep->dropout_p < 1.f, "vt_gemm_bf16: dropout_p must be < 1");
-  VT_REQUIRE(!((ep->act == VT_ACT_GELU_BWD || ep->act == VT_ACT_TANH_BWD) && !ep->aux), "vt_gemm_bf16: *_BWD activation needs aux");
+  VT_REQUIRE(!((ep->act == VT_ACT_GELU_BWD || ep->act == VT_ACT_TANH_BWD || ep->act == VT_ACT_MUL_AUX) && !ep->aux), "vt_gemm_bf16: *_BWD / MUL_AUX activation needs aux");
+  VT_REQUIRE(!(ep->act == VT_ACT_GELU_SAVE_GRAD && !ep->aux_out), "vt_gemm_bf16: VT_ACT_GELU_SAVE_GRAD needs aux_out");
+  VT_REQUIRE(ep->act >= VT_ACT_NONE && ep->act <= VT_ACT_MUL_AUX, "vt_gemm_bf16: unknown activation %d", ep->act);
   const bool splitting = ep->split_k > 1 || (ep->split_k == 0 && ep->accumulate);
   VT_REQUIRE(!splitting || (!ep->bias && ep->act == VT_ACT_NONE && !ep->residual && ep->dropout_p <= 0.f && !ep->aux_out),
              "vt_gemm_bf16: split-K supports only the alpha epilogue");
@@ -591,9 +610,11 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
     if (!a_major && !b_major) {
       if (bias && p.act == VT_ACT_NONE && !res && !drop && !auxo) return launch_gemm<256, 0, 0, EPI_BIAS>(ta, tb, p, grid, st);
       if (bias && p.act == VT_ACT_GELU && !res && !drop && auxo) return launch_gemm<256, 0, 0, EPI_BIAS | EPI_GELU>(ta, tb, p, grid, st);
+      if (bias && p.act == VT_ACT_GELU_SAVE_GRAD && !res && !drop && auxo) return launch_gemm<256, 0, 0, EPI_BIAS | EPI_GELU_SG>(ta, tb, p, grid, st);
       if (bias && p.act == VT_ACT_NONE && res && !auxo) return launch_gemm<256, 0, 0, EPI_BIAS | EPI_DROP | EPI_RESID>(ta, tb, p, grid, st);
     } else if (!a_major && b_major && !bias && !drop && !auxo) {
       if (p.act == VT_ACT_GELU_BWD && !res) return launch_gemm<256, 0, 1, EPI_GELU_BWD>(ta, tb, p, grid, st);
+      if (p.act == VT_ACT_MUL_AUX && !res) return launch_gemm<256, 0, 1, EPI_MUL_AUX>(ta, tb, p, grid, st);
       if (p.act == VT_ACT_NONE && res) return launch_gemm<256, 0, 1, EPI_RESID>(ta, tb, p, grid, st);
       if (p.act == VT_ACT_NONE && !res) return launch_gemm<256, 0, 1, 0>(ta, tb, p, grid, st);
     }

@@ -16,7 +16,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libvisitron_b200.so")
 
-ACT_NONE, ACT_GELU, ACT_TANH, ACT_GELU_BWD, ACT_TANH_BWD = 0, 1, 2, 3, 4
+ACT_NONE, ACT_GELU, ACT_TANH, ACT_GELU_BWD, ACT_TANH_BWD, ACT_GELU_SAVE_GRAD, ACT_MUL_AUX = 0, 1, 2, 3, 4, 5, 6
 
 
 class VtError(RuntimeError):

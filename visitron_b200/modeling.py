@@ -25,7 +25,7 @@ from torch import nn
 
 from . import lib, ops
 from .flat import FlatStore
-from .lib import ACT_GELU, ACT_GELU_BWD, ACT_TANH
+from .lib import ACT_GELU, ACT_GELU_BWD, ACT_GELU_SAVE_GRAD, ACT_MUL_AUX, ACT_TANH
 from .pretrained import PreTrainedModel, check_envelope
 
 logger = logging.getLogger(__name__)
@@ -428,8 +428,11 @@ def _encoder_forward(step: _Step, st: FlatStore, img_feats, img_loc):
         x1 = lib.gemm(ctx, st.wb(p + "attention.output.dense.weight"), bias=st.w(p + "attention.output.dense.bias"),
                       dropout_p=step.p_hidden, seed=step.seed, dropout_stream=4 * l + 1, residual=x)
         y1 = ops.layernorm_fwd(x1, st.w(p + "attention.output.LayerNorm.weight"), st.w(p + "attention.output.LayerNorm.bias"), eps)
+        # when the backward will run, the FFN-up epilogue saves gelu'(pre) (from the fp32 accumulator) instead of pre: the backward GEMM's
+        # epilogue is then one multiply
         pre = torch.empty((M, I), dtype=BF16, device=dev) if save else None
-        z = lib.gemm(y1, st.wb(p + "intermediate.dense.weight"), bias=st.w(p + "intermediate.dense.bias"), act=ACT_GELU, aux_out=pre)
+        z = lib.gemm(y1, st.wb(p + "intermediate.dense.weight"), bias=st.w(p + "intermediate.dense.bias"),
+                     act=ACT_GELU_SAVE_GRAD if save else ACT_GELU, aux_out=pre)
         x2 = lib.gemm(z, st.wb(p + "output.dense.weight"), bias=st.w(p + "output.dense.bias"),
                       dropout_p=step.p_hidden, seed=step.seed, dropout_stream=4 * l + 2, residual=y1)
         y2 = ops.layernorm_fwd(x2, st.w(p + "output.LayerNorm.weight"), st.w(p + "output.LayerNorm.bias"), eps)
@@ -475,7 +478,7 @@ def _encoder_backward(step: _Step, st: FlatStore, d, dpooled):
                                       st.g(p + "output.LayerNorm.bias"), st.g(p + "output.dense.bias"),
                                       out_dropout_p=ph, out_stream=4 * l + 2, seed=step.seed)
         lib.gemm(dx2d, z, a_major=1, b_major=1, out=st.g(p + "output.dense.weight"), accumulate=True)
-        dpre = lib.gemm(dx2d, st.wb(p + "output.dense.weight"), b_major=1, act=ACT_GELU_BWD, aux=pre)
+        dpre = lib.gemm(dx2d, st.wb(p + "output.dense.weight"), b_major=1, act=ACT_MUL_AUX, aux=pre)   # pre holds gelu'(pre-activation)
         ops.colsum(dpre, st.g(p + "intermediate.dense.bias"))
         lib.gemm(dpre, y1, a_major=1, b_major=1, out=st.g(p + "intermediate.dense.weight"), accumulate=True)
         dy1 = lib.gemm(dpre, st.wb(p + "intermediate.dense.weight"), b_major=1, residual=dx2)
