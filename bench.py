@@ -204,6 +204,9 @@ class Workload:
                              "BCEWithLogits(pos_weight 5) masked mean, forward + backward [BASELINE configs[4]: sweep --batch]")
         else:
             host = [synthetic.pretrain_batch(b, seed=88 + rank + 1000 * i) for i in range(n_host)]  # per-rank shard, seed 88+rank
+            if args.feat_bf16:   # a bf16 feature cache: half the H2D bytes; the default is the loader's fp32
+                for hb in host:
+                    hb["img_feats"], hb["img_location_embeddings"] = hb["img_feats"].bfloat16(), hb["img_location_embeddings"].bfloat16()
             self.S, self.R = 767, 256
             self.labelled = (sum(int((hb["labels"] != -1).sum()) for hb in host) / (n_host * b),
                              sum(int((hb["token_labels"] != -1).sum()) for hb in host) / (n_host * b))
@@ -510,6 +513,7 @@ def main():
     ap.add_argument("--min-warm-s", type=float, default=1.0, help="keep warming up until this much wall time has passed")
     ap.add_argument("--repeats", type=int, default=5, help="timed regions of --steps steps each; the median is reported, all are listed")
     ap.add_argument("--manual-gc", action="store_true", help="diagnosis: gc.freeze() + gc.disable() around the timed regions")
+    ap.add_argument("--feat-bf16", action="store_true", help="region features / location embeddings come from a bf16 cache (pretrain workload)")
     ap.add_argument("--no-clocks", action="store_true", help="diagnosis: do not sample clocks during the timed region")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")

@@ -146,6 +146,9 @@ int vt_cast_f32_bf16(const float* src, int64_t lds, int64_t rows, int64_t cols, 
  * GEMM operand so that img_embedding(x) + location_embeds(l) (vs/encoder.py:277-279) is one contraction. */
 int vt_pad_cast_concat(const float* a, int64_t d0, const float* b, int64_t d1, int64_t rows, void* out, int64_t ldo,
                        vt_stream stream);
+/* the same with either source in bf16 (a_bf16 / b_bf16 = 1): region features kept in a bf16 cache skip the fp32 detour */
+int vt_pad_cast_concat_mixed(const void* a, int a_bf16, int64_t d0, const void* b, int b_bf16, int64_t d1, int64_t rows, void* out,
+                             int64_t ldo, vt_stream stream);
 /* y[m] = x[remap(m)] * dropout_mask(m) */
 int vt_dropout_rows(const void* x, int64_t ldx, int64_t rows, int64_t hidden, void* y, int64_t ldy, float dropout_p,
                     uint64_t seed, uint32_t dropout_stream, int64_t remap_rows_in, int64_t remap_rows_out,

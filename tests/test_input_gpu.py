@@ -195,3 +195,27 @@ def test_device_prefetcher_yields_every_batch_in_order():
     assert seen == 5
     with pytest.raises(lib.VtError):
         ip.DevicePrefetcher(host, "cpu")
+
+
+def test_bf16_feature_cache_gives_the_same_step():
+    """Region features / location embeddings handed over in bf16 (a feature cache: half the H2D bytes) == the same values in fp32,
+    bit for bit: the first thing the projection does with them is the bf16 cast."""
+    from visitron_b200 import modeling, synthetic
+    from visitron_b200.pretrained import BertConfig
+    cfg = BertConfig(30522, num_hidden_layers=1, hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+    cfg.img_feature_dim, cfg.detector_classes, cfg.action_space = 2054, 1601, 36
+    torch.manual_seed(0)
+    model = modeling.PreTrainOscar(cfg).to(DEV).train()
+    batch = {k: v.to(DEV) for k, v in synthetic.pretrain_batch(2, 5, text_len=64, regions=16).items()}
+    batch["img_feats"] = batch["img_feats"].bfloat16().float()
+    batch["img_location_embeddings"] = batch["img_location_embeddings"].bfloat16().float()
+    res = []
+    for cached in (False, True):
+        b = dict(batch)
+        if cached:
+            b["img_feats"], b["img_location_embeddings"] = b["img_feats"].bfloat16(), b["img_location_embeddings"].bfloat16()
+        model.zero_grad(set_to_none=True)
+        out = model(**b)
+        out[0].backward()
+        res.append((out[0].detach().clone(), model.bert.img_embedding.weight.grad.detach().clone()))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])

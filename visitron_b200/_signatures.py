@@ -20,6 +20,7 @@ SIGNATURES = {
     "vt_colsum_bf16": (I, [P, I64, I64, I64, P, P, I, P]),
     "vt_cast_f32_bf16": (I, [P, I64, I64, I64, P, I64, P, I64, P]),
     "vt_pad_cast_concat": (I, [P, I64, P, I64, I64, P, I64, P]),
+    "vt_pad_cast_concat_mixed": (I, [P, I, I64, P, I, I64, I64, P, I64, P]),
     "vt_dropout_rows": (I, [P, I64, I64, I64, P, I64, F, U64, U32, I64, I64, I64, P]),
     "vt_gather_rows": (I, [P, I64, P, I64, I64, P, I64, P]),
     "vt_scatter_add_rows": (I, [P, I64, P, I64, I64, P, I64, P]),

@@ -429,19 +429,22 @@ __global__ void cast_transpose_kernel(const float* __restrict__ src, long long l
   }
 }
 
-// out[r, 0:d0] = a[r], out[r, d0:d0+d1] = b[r], out[r, d0+d1:ldo] = 0   (fp32 -> bf16)
-__global__ void pad_cast_concat_kernel(const float* __restrict__ a, long long d0, const float* __restrict__ b, long long d1,
+// out[r, 0:d0] = a[r], out[r, d0:d0+d1] = b[r], out[r, d0+d1:ldo] = 0   (fp32 or bf16 -> bf16; a bf16 feature cache skips the fp32 detour)
+__device__ __forceinline__ float ld_f32(const float* p) { return *p; }
+__device__ __forceinline__ float ld_f32(const bf16* p) { return __bfloat162float(*p); }
+template <typename TA, typename TB>
+__global__ void pad_cast_concat_kernel(const TA* __restrict__ a, long long d0, const TB* __restrict__ b, long long d1,
                                        long long rows, bf16* __restrict__ out, long long ldo) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
-    const float* ar = a + r * d0;
-    const float* br = b ? b + r * d1 : nullptr;
+    const TA* ar = a + r * d0;
+    const TB* br = b ? b + r * d1 : nullptr;
     bf16* o = out + r * ldo;
     for (long long c = threadIdx.x * 2; c < ldo; c += blockDim.x * 2) {
       float v0 = 0.f, v1 = 0.f;
       long long c1 = c + 1;
-      if (c < d0) v0 = ar[c]; else if (br && c < d0 + d1) v0 = br[c - d0];
-      if (c1 < d0) v1 = ar[c1]; else if (br && c1 < d0 + d1) v1 = br[c1 - d0];
+      if (c < d0) v0 = ld_f32(ar + c); else if (br && c < d0 + d1) v0 = ld_f32(br + (c - d0));
+      if (c1 < d0) v1 = ld_f32(ar + c1); else if (br && c1 < d0 + d1) v1 = ld_f32(br + (c1 - d0));
       *reinterpret_cast<uint32_t*>(o + c) = pack_bf16(v0, v1);
     }
   }
@@ -608,15 +611,26 @@ extern "C" int vt_cast_f32_bf16(const float* src, int64_t lds, int64_t rows, int
   return VT_OK;
 }
 
-extern "C" int vt_pad_cast_concat(const float* a, int64_t d0, const float* b, int64_t d1, int64_t rows, void* out, int64_t ldo,
-                                  vt_stream stream) {
+extern "C" int vt_pad_cast_concat_mixed(const void* a, int a_bf16, int64_t d0, const void* b, int b_bf16, int64_t d1, int64_t rows, void* out,
+                                        int64_t ldo, vt_stream stream) {
   VT_REQUIRE(a && out && ldo % 2 == 0 && ldo >= d0 + d1 && ((uintptr_t)out & 3) == 0, "vt_pad_cast_concat: bad arguments");
   if (rows == 0) return VT_OK;
   long long cap = (long long)num_sms() * 8;
-  launch_pdl(pad_cast_concat_kernel, (int)(rows < cap ? rows : cap), 256, 0, (cudaStream_t)stream, a, d0, b, d1, rows, (bf16*)out, ldo);
+  const int grid = (int)(rows < cap ? rows : cap);
+  cudaStream_t st = (cudaStream_t)stream;
+  bf16* o = (bf16*)out;
+  if (a_bf16 && b_bf16) launch_pdl(pad_cast_concat_kernel<bf16, bf16>, grid, 256, 0, st, (const bf16*)a, d0, (const bf16*)b, d1, rows, o, ldo);
+  else if (a_bf16) launch_pdl(pad_cast_concat_kernel<bf16, float>, grid, 256, 0, st, (const bf16*)a, d0, (const float*)b, d1, rows, o, ldo);
+  else if (b_bf16) launch_pdl(pad_cast_concat_kernel<float, bf16>, grid, 256, 0, st, (const float*)a, d0, (const bf16*)b, d1, rows, o, ldo);
+  else launch_pdl(pad_cast_concat_kernel<float, float>, grid, 256, 0, st, (const float*)a, d0, (const float*)b, d1, rows, o, ldo);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
+}
+
+extern "C" int vt_pad_cast_concat(const float* a, int64_t d0, const float* b, int64_t d1, int64_t rows, void* out, int64_t ldo,
+                                  vt_stream stream) {
+  return vt_pad_cast_concat_mixed(a, 0, d0, b, 0, d1, rows, out, ldo, stream);
 }
 
 extern "C" int vt_dropout_rows(const void* x, int64_t ldx, int64_t rows, int64_t hidden, void* y, int64_t ldy, float dropout_p,

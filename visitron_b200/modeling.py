@@ -374,7 +374,8 @@ class BertImgModelwithLocationEmbeds(BertPreTrainedModel):
         step.need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in store.params)
         imgs = []
         if step.has_img:
-            imgs = [img_feats.contiguous().float(), img_location_embeddings.contiguous().float()]
+            # fp32 as the loader delivers them, or bf16 from a feature cache (read as it is: half the H2D bytes, no fp32 detour)
+            imgs = [t.contiguous() if t.dtype == BF16 else t.contiguous().float() for t in (img_feats, img_location_embeddings)]
         seq, pooled = _EncoderFn.apply(step, store, *imgs, *store.params)
         return seq, pooled, step
 

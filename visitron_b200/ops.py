@@ -89,10 +89,14 @@ def cast_weight(src, dst=None, dst_t=None):
 
 
 def pad_cast_concat(a, b, out):
+    """out[:, :d0] = a, out[:, d0:d0+d1] = b, zero padding behind; a / b fp32 or bf16 (a bf16 feature cache is read as it is)."""
     L = init()
     rows = a.size(0)
-    check(L.vt_pad_cast_concat(ptr(a), a.size(1), ptr(b), b.size(1) if b is not None else 0, rows, ptr(out), out.stride(0), stream_ptr()),
-          "vt_pad_cast_concat")
+    for t in (a, b):
+        if t is not None and t.dtype not in (F32, BF16):
+            raise lib.VtError("pad_cast_concat takes fp32 or bf16 sources, got %s" % t.dtype)
+    check(L.vt_pad_cast_concat_mixed(ptr(a), int(a.dtype == BF16), a.size(1), ptr(b), int(b is not None and b.dtype == BF16),
+                                     b.size(1) if b is not None else 0, rows, ptr(out), out.stride(0), stream_ptr()), "vt_pad_cast_concat")
     return out
 
 
