@@ -399,3 +399,26 @@ def test_attention_key_tile_plan_changes_no_bit(B, S, heads, p):
     d0 = ops.attention_bwd(qkv, bias, ctx0, dctx, lse0, B, S, heads, dropout_p=p, seed=7, stream_id=3)
     d1 = ops.attention_bwd(qkv, bias, ctx0, dctx, lse0, B, S, heads, dropout_p=p, seed=7, stream_id=3, key_tiles=plan)
     assert torch.equal(d0, d1)
+
+
+def test_attention_key_tile_plan_with_fractional_masks():
+    """Mask values other than 0 / 1 (bias = (1 - m) * -10000, vs/encoder.py:226-241): a tile is dead only when ALL its biases are at
+    least 5000 below the sample's largest; anything closer is visited.  Same bits with and without the plan."""
+    B, S, heads = 2, 511, 2
+    g = torch.Generator().manual_seed(5)
+    mask = torch.ones(B, S)
+    mask[0, 64:128] = 0.5      # bias -5000: dead (probabilities underflow to exactly 0)
+    mask[0, 128:192] = 0.6     # bias -4000: live by the rule
+    mask[0, 192:256] = 0.0
+    mask[1, :] = 0.25          # every key at -7500: the largest bias of the sample, all tiles live
+    mask[1, 300:] = -0.5       # bias -15000: 7500 below -> dead
+    mask = mask.to(DEV)
+    qkv = (torch.randn(B * S, 3 * heads * 64, generator=g) * 0.7).to(DEV).to(torch.bfloat16)
+    bias = ops.mask_bias(mask)
+    plan = [int(x) & 0xffffffff for x in ops.attention_key_tiles(bias).tolist()]
+    assert plan[0] == 0b11110101 and plan[1] == 0b00011111, [bin(x) for x in plan]
+    pl = ops.attention_key_tiles(bias)
+    for p in (0.0, 0.1):
+        a = ops.attention_fwd(qkv, bias, B, S, heads, dropout_p=p, seed=3, stream_id=1)
+        b = ops.attention_fwd(qkv, bias, B, S, heads, dropout_p=p, seed=3, stream_id=1, key_tiles=pl)
+        assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
