@@ -411,7 +411,7 @@ def run_ours(args):
     n_out = 7 if args.workload == "pretrain" else 1
     pk = peaks()
     line = dict(
-        metric=METRIC, value=round(value, 2), unit=UNIT, n_gpus=world, steps=args.steps, warmup=n_warm,
+        metric=METRIC, value=round(value, 2), unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup, warmup_run=n_warm,
         ms_per_step=round(ms / args.steps, 3), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16",
         data="synthetic", timed_regions=dict(n=len(regions), steps_each=args.steps, ms_per_step=[round(r / args.steps, 3) for r in regions],
                                              sm_mhz=[c[0] for c in region_clk], power_w_max=[c[1] for c in region_clk], reported="median"),
