@@ -445,7 +445,7 @@ def run_ours(args):
         torch.distributed.destroy_process_group()
 
 
-def cpu_baseline(args, steps):
+def cpu_baseline(args, steps, warmup=1):
     """The oracle port (fp32 PyTorch restatement of the reference's `cpu` mode, run_scripts/pretrain/pretrain_ndh_r2r.sh:7-9)
     on the host cores, bounded sample: b = 2 (the script's per-GPU batch), 1 warm-up + `steps` timed fwd+bwd."""
     from oracle import visitron_oracle as vo
@@ -476,7 +476,8 @@ def cpu_baseline(args, steps):
         def one():
             vo.pretrain_step(P, oc, batch, drop)
         what = "pre-training workload at b=%d (S=767, all rows through the MLM head as the reference does)" % b
-    one()
+    for _ in range(max(1, warmup)):
+        one()
     t0 = time.perf_counter()
     for _ in range(steps):
         one()
@@ -489,9 +490,11 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps = max(1, min(args.steps, 5))
-    cb = cpu_baseline(args, steps)
-    line = dict(impl="reference", metric=METRIC, value=cb["value"], unit=UNIT, n_gpus=args.gpus, steps=steps, warmup=1,
+    # every step is a bounded sample (b = 2) of the workload, ~2.5 s on 16 host cores: --steps / --warmup are honoured up to 40 / 5
+    # so that the whole run stays within a couple of minutes
+    steps, warm = max(1, min(args.steps, 40)), max(1, min(args.warmup, 5))
+    cb = cpu_baseline(args, steps, warm)
+    line = dict(impl="reference", metric=METRIC, value=cb["value"], unit=UNIT, n_gpus=args.gpus, steps=steps, warmup=warm,
                 ms_per_step=round(2 / cb["value"] * 1e3, 1), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
                 config=dict(workload="%s step (same workload as the default arm; bounded sample b=2 per step on the host CPU)" % args.workload,
                             per_gpu_batch=2, seq_len=767 if args.workload == "pretrain" else 511),
