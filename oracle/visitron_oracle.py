@@ -473,4 +473,4 @@ def pretrain_step(P: Params, cfg: OracleConfig, batch: dict, drop=None):
         v.grad = None
     out = pretrain_forward(P, cfg, drop=drop, **batch)
     out[0].backward()
-    return tuple(float(o) for o in out), {k: v.grad for k, v in P.items()}
+    return tuple(float(o.detach()) for o in out), {k: v.grad for k, v in P.items()}
