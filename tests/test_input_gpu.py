@@ -219,3 +219,60 @@ def test_bf16_feature_cache_gives_the_same_step():
         out[0].backward()
         res.append((out[0].detach().clone(), model.bert.img_embedding.weight.grad.detach().clone()))
     assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+
+
+def test_new_kernels_stay_inside_their_buffers():
+    """Guard bands around every output of the input-row kernels and of the key-tile plan (the pool has no compute-sanitizer): the C ABI is
+    called with pointers into the middle of sentinel-filled buffers and the bands must come back untouched."""
+    from visitron_b200 import ops
+    L = lib.init()
+    st = lib.stream_ptr()
+    G = 4096   # guard elements on either side
+
+    def banded(n, dtype, fill):
+        buf = torch.full((n + 2 * G,), fill, dtype=dtype, device=DEV)
+        return buf, buf[G:G + n]
+
+    def intact(buf, n, fill):
+        return bool((buf[:G] == fill).all()) and bool((buf[G + n:] == fill).all())
+
+    # masking: n = 7 * 333 tokens (not a multiple of the block size)
+    ids, tc = _batch(7, 333, 3, True)
+    n = ids.numel()
+    d_ids, d_tc, lut = ids.to(DEV), tc.to(DEV), ip.special_lut(V, SPECIAL, DEV)
+    b_out, out = banded(n, torch.int64, -77)
+    b_lab, lab = banded(n, torch.int64, -77)
+    b_att, att = banded(n, torch.uint8, 99)
+    lib.check(L.vt_mlm_mask(d_ids.data_ptr(), d_tc.data_ptr(), lut.data_ptr(), n, V, MASK, PAD, 0.15, 5, out.data_ptr(), lab.data_ptr(),
+                            att.data_ptr(), st), "vt_mlm_mask")
+    b_u, u = banded(3 * n, torch.float32, -5.0)
+    b_r, r = banded(n, torch.int64, -77)
+    lib.check(L.vt_mlm_draws(n, V, 5, u.data_ptr(), r.data_ptr(), st), "vt_mlm_draws")
+    torch.cuda.synchronize()
+    assert intact(b_out, n, -77) and intact(b_lab, n, -77) and intact(b_att, n, 99) and intact(b_u, 3 * n, -5.0) and intact(b_r, n, -77)
+    assert bool((att <= 1).all()) and bool((u >= 0).all()) and bool((u < 1).all()) and int(r.min()) >= 0 and int(r.max()) < V
+
+    # region packing: odd widths (scalar path) and the even widths of the model (vector path); ragged counts incl. 0 and > R
+    for D, DL in ((7, 5), (2054, 128)):
+        counts, R = [3, 0, 9, 40], 8
+        feats, loc, off = _ragged(counts, D, DL, 1)
+        B = len(counts)
+        b_f, f = banded(B * R * D, torch.float32, -5.0)
+        b_l, l_ = banded(B * R * DL, torch.float32, -5.0)
+        b_a, a = banded(B * (2 + R), torch.int64, -77)
+        lib.check(L.vt_pack_regions(feats.to(DEV).data_ptr(), D, loc.to(DEV).data_ptr(), DL, off.to(DEV).data_ptr(), B, R, f.data_ptr(), l_.data_ptr(),
+                                    a.data_ptr() + 16, 2 + R, st), "vt_pack_regions")
+        torch.cuda.synchronize()
+        assert intact(b_f, B * R * D, -5.0) and intact(b_l, B * R * DL, -5.0) and intact(b_a, B * (2 + R), -77)
+        av = a.view(B, 2 + R)
+        assert bool((av[:, :2] == -77).all()), "the columns left of the attention tail belong to the caller"
+        assert av[:, 2:].sum(1).tolist() == [min(c, R) for c in counts]
+
+    # key-tile plan: B = 5 samples, S = 700 (11 tiles, the last one ragged)
+    mask = torch.ones(5, 700, dtype=torch.long)
+    mask[1, 100:] = 0
+    bias = ops.mask_bias(mask.to(DEV))
+    b_p, plan = banded(5, torch.int32, -77)
+    lib.check(L.vt_attention_key_tiles(bias.data_ptr(), 5, 700, plan.data_ptr(), st), "vt_attention_key_tiles")
+    torch.cuda.synchronize()
+    assert intact(b_p, 5, -77) and plan.tolist() == [2047, 3, 2047, 2047, 2047]
