@@ -422,3 +422,27 @@ def test_attention_key_tile_plan_with_fractional_masks():
         a = ops.attention_fwd(qkv, bias, B, S, heads, dropout_p=p, seed=3, stream_id=1)
         b = ops.attention_fwd(qkv, bias, B, S, heads, dropout_p=p, seed=3, stream_id=1, key_tiles=pl)
         assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+
+
+def test_attention_with_plan_stays_inside_ctx_and_dqkv():
+    """Guard bands around ctx and dqkv (no compute-sanitizer on the pool): sentinel rows before and behind stay untouched."""
+    B, S, heads = 3, 767, 2
+    Hh = heads * 64
+    g = torch.Generator().manual_seed(1)
+    mask = torch.ones(B, S, dtype=torch.long)
+    mask[0, 70:511] = 0
+    mask[1, 600:] = 0
+    mask = mask.to(DEV)
+    qkv = (torch.randn(B * S, 3 * Hh, generator=g) * 0.7).to(DEV).to(torch.bfloat16)
+    dctx = torch.randn(B * S, Hh, generator=g).to(DEV).to(torch.bfloat16)
+    bias = ops.mask_bias(mask)
+    plan = ops.attention_key_tiles(bias)
+    G = 64
+    big = torch.full((B * S + 2 * G, Hh), 7.0, dtype=torch.bfloat16, device=DEV)
+    ctx, lse = ops.attention_fwd(qkv, bias, B, S, heads, dropout_p=0.1, seed=2, stream_id=0, ctx=big[G:G + B * S], key_tiles=plan)
+    bigd = torch.full((B * S + 2 * G, 3 * Hh), 7.0, dtype=torch.bfloat16, device=DEV)
+    ops.attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.1, seed=2, stream_id=0, dqkv=bigd[G:G + B * S], key_tiles=plan)
+    torch.cuda.synchronize()
+    for t in (big, bigd):
+        assert bool((t[:G] == 7.0).all()) and bool((t[G + B * S:] == 7.0).all())
+    assert bool(torch.isfinite(ctx.float()).all()) and bool(torch.isfinite(bigd[G:G + B * S].float()).all())
