@@ -240,8 +240,9 @@ class Workload:
             ctx_mask = torch.zeros(ctx.shape[:2], dtype=torch.bool, device=ctx.device)
             t_ = self.tb
             loss = None
+            dec = seq[:, :TB_STEPS, :VS_HID].contiguous()   # the stand-in decoder states: ONE slice of the encoder output, not one per step
             for t in range(TB_STEPS):
-                _, _, l, _ = self._heads.turn_based_head(t_["w_in"], t_["w_out"], t_["w_a"], t_["b_a"], seq[:, t, :VS_HID], ctx, ctx_mask,
+                _, _, l, _ = self._heads.turn_based_head(t_["w_in"], t_["w_out"], t_["w_a"], t_["b_a"], dec[:, t], ctx, ctx_mask,
                                                          batch["no_forward"][t], batch["target"][t])
                 loss = l if loss is None else loss + l
             loss.backward()
@@ -251,8 +252,9 @@ class Workload:
             return (loss,)
         seq, _ = self.model(batch["input_ids"], token_type_ids=batch["token_type_ids"], attention_mask=batch["attention_mask"])
         loss = None
+        dec = seq[:, :VS_STEPS, :VS_HID].contiguous()   # the stand-in decoder states: ONE slice of the encoder output, not one per step
         for t in range(VS_STEPS):
-            _, l, _ = self._heads.candidate_scores_ce(self.w_in, seq[:, t, :VS_HID], batch["cand_feat"][t], batch["cand_len"][t], batch["target"][t])
+            _, l, _ = self._heads.candidate_scores_ce(self.w_in, dec[:, t], batch["cand_feat"][t], batch["cand_len"][t], batch["target"][t])
             loss = l if loss is None else loss + l
         loss.backward()
         if self.world > 1:   # the scorer's weight is outside the encoder's flat buffer: one small all-reduce of its own
