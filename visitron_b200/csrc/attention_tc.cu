@@ -911,7 +911,10 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
   const long long n_items = ((S + FQ - 1) / FQ) * heads * B;
   static const int per_cta = [] { const char* e = getenv("VT_FWD_ITEMS_PER_CTA"); const int v = e ? atoi(e) : FWD_ITEMS_PER_CTA; return v > 0 ? v : 1; }();
   // each CTA a contiguous range of items; small launches (fewer CTAs than the two-per-SM slots) keep one item per CTA
-  const long long per = n_items >= 2ll * per_cta * usable_sms() ? per_cta : 1;
+  // ... and take two only when that does not cost a wave: ceil(items / k / slots) * k item-times, slots = two CTAs per SM
+  const long long slots = 2ll * usable_sms();
+  auto waves = [&](long long k) { return ((n_items + k - 1) / k + slots - 1) / slots * k; };
+  const long long per = (n_items >= per_cta * slots && waves(per_cta) <= waves(1)) ? per_cta : 1;
   const long long ctas = (FWD_PERSISTENT || VT_DBG(32768)) ? 2ll * usable_sms() : (n_items + per - 1) / per;
   // one thread per row executes 28 % fewer instructions than two (ncu: 96.6 M vs 123.4 M warp instructions; the per-tile
   // bookkeeping and the maximum exchange are not duplicated) and measured faster with and without dropout
