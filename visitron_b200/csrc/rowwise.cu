@@ -126,9 +126,22 @@ ln_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict
   float g[CH][8], b[CH][8];
   load_vec_f32(gamma, lane, g);
   load_vec_f32(beta, lane, b);
-  for (long long m = (long long)blockIdx.x * ROW_WARPS + warp; m < rows; m += (long long)gridDim.x * ROW_WARPS) {
+  // the next row is requested (packed, 12 registers) before the current one is reduced: twice the bytes in flight per warp
+  const long long stride = (long long)gridDim.x * ROW_WARPS;
+  long long m = (long long)blockIdx.x * ROW_WARPS + warp;
+  uint4 xq[CH];
+  if (m < rows) {
+#pragma unroll
+    for (int c = 0; c < CH; ++c) xq[c] = __ldg(reinterpret_cast<const uint4*>(x + m * ldx + chunk_col(lane, c)));
+  }
+  for (; m < rows; m += stride) {
     float v[CH][8];
-    load_row_bf16(x + m * ldx, lane, v);
+#pragma unroll
+    for (int c = 0; c < CH; ++c) unpack8(xq[c], v[c]);
+    if (m + stride < rows) {
+#pragma unroll
+      for (int c = 0; c < CH; ++c) xq[c] = __ldg(reinterpret_cast<const uint4*>(x + (m + stride) * ldx + chunk_col(lane, c)));
+    }
     float mean, rstd;
     row_stats(v, eps, mean, rstd);
 #pragma unroll
