@@ -18,7 +18,7 @@ def main():
     ap.add_argument("--batch", type=int, default=2)
     ap.add_argument("--steps", type=int, default=20)
     a = ap.parse_args()
-    args = argparse.Namespace(workload="pretrain", batch=a.batch, dropout=0.3)
+    args = argparse.Namespace(workload="pretrain", batch=a.batch, dropout=0.3, feat_bf16=False)
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
     wl = bench.Workload(args, dev, 0, 1)
