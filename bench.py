@@ -219,47 +219,49 @@ class Workload:
         self.params = list(self.model.parameters()) + self.extra_params
         self._heads = agent_heads
 
-    def step(self, batch):
-        for p in self.params:
-            p.grad = None
+    def forward(self, batch):
+        """The step's forward: a tuple of 0-d tensors, the loss first (what GraphedStep captures and the eager step runs)."""
         wk = self.args.workload
         if wk == "pretrain":
-            out = self.model(**batch)
-            out[0].backward()
-            return out
+            return self.model(**batch)
         if wk == "qa_classifier":
             with torch.no_grad():   # vs/classifier: the encoder is frozen
                 seq, _ = self.model(batch["input_ids"], token_type_ids=batch["token_type_ids"], attention_mask=batch["attention_mask"])
             q = self.qa
             _, loss = self._heads.qa_head(q["w1"], q["b1"], q["w2"], q["b2"], seq[:, 0, :VS_HID], batch["target"], batch["valid"])
-            loss.backward()
             return (loss,)
+        seq, _ = self.model(batch["input_ids"], token_type_ids=batch["token_type_ids"], attention_mask=batch["attention_mask"])
+        loss = None
         if wk == "turn_based":
-            seq, _ = self.model(batch["input_ids"], token_type_ids=batch["token_type_ids"], attention_mask=batch["attention_mask"])
             ctx = seq[:, :, :VS_HID].contiguous()
             ctx_mask = torch.zeros(ctx.shape[:2], dtype=torch.bool, device=ctx.device)
             t_ = self.tb
-            loss = None
             dec = seq[:, :TB_STEPS, :VS_HID].contiguous()   # the stand-in decoder states: ONE slice of the encoder output, not one per step
             for t in range(TB_STEPS):
                 _, _, l, _ = self._heads.turn_based_head(t_["w_in"], t_["w_out"], t_["w_a"], t_["b_a"], dec[:, t], ctx, ctx_mask,
                                                          batch["no_forward"][t], batch["target"][t])
                 loss = l if loss is None else loss + l
-            loss.backward()
-            if self.world > 1:
-                for p in self.extra_params:
-                    torch.distributed.all_reduce(p.grad, op=torch.distributed.ReduceOp.AVG)
             return (loss,)
-        seq, _ = self.model(batch["input_ids"], token_type_ids=batch["token_type_ids"], attention_mask=batch["attention_mask"])
-        loss = None
         dec = seq[:, :VS_STEPS, :VS_HID].contiguous()   # the stand-in decoder states: ONE slice of the encoder output, not one per step
         for t in range(VS_STEPS):
             _, l, _ = self._heads.candidate_scores_ce(self.w_in, dec[:, t], batch["cand_feat"][t], batch["cand_len"][t], batch["target"][t])
             loss = l if loss is None else loss + l
-        loss.backward()
-        if self.world > 1:   # the scorer's weight is outside the encoder's flat buffer: one small all-reduce of its own
-            torch.distributed.all_reduce(self.w_in.grad, op=torch.distributed.ReduceOp.AVG)
         return (loss,)
+
+    def post_backward(self):
+        """The head parameters live outside the encoder's flat buffer: one small all-reduce each (pre-training has none)."""
+        if self.world > 1:
+            for p in self.extra_params:
+                if p.grad is not None:
+                    torch.distributed.all_reduce(p.grad, op=torch.distributed.ReduceOp.AVG)
+
+    def step(self, batch):
+        for p in self.params:
+            p.grad = None
+        out = self.forward(batch)
+        out[0].backward()
+        self.post_backward()
+        return out
 
     def flops(self, executed=False):
         fl = flops_per_sample(self.S, self.R, all_rows_heads=not executed, labelled=self.labelled)
@@ -267,6 +269,38 @@ class Workload:
             fl["total"] += self.heads_flops - fl["heads"] - fl["img"]
             fl["heads"], fl["img"] = self.heads_flops, 0
         return fl
+
+
+def workload_desc(args):
+    wk = args.workload
+    if wk == "viewpoint_select":
+        return ("viewpoint_select_step: BertImgModelwithLocationEmbeds fwd+bwd as OscarEncoder calls it (T=511 text-only, token types, "
+                "~uint8 mask) + SoftDotAttention candidate scorer + masked CE at 10 decoder steps (12 candidates x 2052), bert-base "
+                "random init [BASELINE configs[1]; the agent's LSTM encoder/decoder are timed by --workload agent_vs, SURVEY 8f-N1]"), 511
+    if wk == "turn_based":
+        return ("turn_based_step: encoder fwd+bwd at the full RxR text length (T=511 valid tokens) + turn-based head (SoftDotAttention over "
+                "the 511 context positions, tanh(W_out[.;h]), 6-way logits, forward masked, CE ignore 7) at 40 decoder steps, bert-base "
+                "random init [BASELINE configs[3]; the agent's LSTM encoder/decoder are timed by --workload agent_tb, SURVEY 8f-N1]"), 511
+    if wk == "qa_classifier":
+        return ("qa_classifier_step: encoder forward-only under no_grad (T=511) + question_linear (512->256->1, tanh) with "
+                "BCEWithLogits(pos_weight 5) masked mean, forward + backward [BASELINE configs[4]: sweep --batch]"), 511
+    if wk in ("agent_vs", "agent_tb"):
+        return AGENT_DESC[wk], 511
+    return ("pretrain_step: PreTrainOscar fwd+bwd, bert-base random init, NDH-shaped batch (T=511 text + R=256 region slots, "
+            "img_feature_dim 2054, 15% MLM + masked detector-class + 36-way action labels), all objectives [BASELINE configs[2]; "
+            "configs[1] = --workload viewpoint_select]"), 767
+
+
+AGENT_DESC = {}
+
+
+def make_config(args, world):
+    """The `config` object of the JSON line: shared by both arms (the reference arm times bounded samples of THIS workload)."""
+    desc, S = workload_desc(args)
+    b = args.batch
+    return dict(workload=desc, per_gpu_batch=b, global_batch=b * world, seq_len=S, parallelism="dp%d" % world, dropout=args.dropout,
+                l2="per-step working set (%.1f GB of activations) >> 126 MB L2; 4 rotating batches" % (b * S * 24.5e3 * 12 / 1e9),
+                grad_allreduce="fp32, one bucket per encoder layer, overlapped with backward" if world > 1 else "none (1 GPU)")
 
 
 def run_ours(args):
@@ -325,6 +359,34 @@ def run_ours(args):
         n_warm += 1
         if n_warm == 1:
             t0 = time.perf_counter()   # the first step carries module loading and allocator growth: the clock starts after it
+    # ---- the step as ONE CUDA graph (visitron_b200/graph.py): fixed launch sequence, no host sync, one cudaGraphLaunch per step ----
+    graphed, graph_err = None, None
+    if not args.no_graph:
+        from visitron_b200 import graph as vgraph
+        try:
+            graphed = vgraph.GraphedStep(model, dev_batches[0], step_fn=lambda m, bt: wl.forward(bt), extra_params=wl.extra_params,
+                                         post_backward=wl.post_backward if (world > 1 and wl.extra_params) else None)
+        except Exception as e:   # reported in the line, the eager path is timed instead
+            graph_err = "%s: %s" % (type(e).__name__, str(e)[:300])
+            torch.cuda.synchronize()
+        if world > 1:   # every rank must take the same path
+            ok = torch.tensor([1.0 if graphed is not None else 0.0], device=device)
+            torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN)
+            if float(ok) == 0.0:
+                graphed = None
+                graph_err = graph_err or "capture failed on another rank"
+
+    def run_step(bt):
+        if graphed is None:
+            return torch.stack([o.detach().float() for o in step(bt)])
+        graphed.load(bt)
+        return graphed.replay()
+
+    for i in range(n_host):   # once more over every batch on the path that is timed
+        run_step(dev_batches[i])
+    torch.cuda.synchronize()
+    # eager comparison point (the public API without the graph): one region
+    eager_ms = timed(lambda i: step(dev_batches[i % n_host]), args.steps) / args.steps if graphed is not None else None
     # ---- device-resident throughput (`value`) ----
     if sampler:
         sampler.start()
@@ -342,8 +404,8 @@ def run_ours(args):
     for _ in range(max(1, args.repeats)):
         lib.reset_launch_count()
         h0 = time.perf_counter()
-        regions.append(timed(lambda i: step(dev_batches[i % n_host]), args.steps))
-        launches = lib.launch_count()
+        regions.append(timed(lambda i: run_step(dev_batches[i % n_host]), args.steps))
+        launches = lib.launch_count() if graphed is None else graphed.launches_per_step * args.steps
         region_clk.append(sampler.window(h0, time.perf_counter()) if sampler else (None, None))
     ms = statistics.median(regions)
     clocks = sampler.stop() if sampler else None
@@ -362,8 +424,7 @@ def run_ours(args):
     feed = input_pipeline.DevicePrefetcher(host_stream(), device)   # next batch's H2D overlaps this step's compute
 
     def e2e_step(i):
-        out = step(next(feed))
-        return torch.stack([o.detach().float() for o in out]).cpu()   # D2H read of the step's scalars (host sync, as the loop's .item())
+        return run_step(next(feed)).cpu()   # D2H read of the step's scalars (host sync, as the loop's .item())
 
     e2e_step(0)
     e2e_regions = []
@@ -404,6 +465,9 @@ def run_ours(args):
     opt_elems = sum(p.numel() for _, p in named)
     # (qa_classifier updates only the 131 k parameters of question_linear: the figure is launch latency there)
 
+    # ---- N > 1: are the exchanged gradients the same on every rank, and are they the mean of the per-rank gradients? ----
+    sync_check = grad_sync_check(wl, model, dev_batches[0], device, world) if world > 1 else None
+
     if rank != 0:
         if world > 1:
             torch.distributed.destroy_process_group()
@@ -417,13 +481,14 @@ def run_ours(args):
         ms_per_step=round(ms / args.steps, 3), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="bf16",
         data="synthetic", timed_regions=dict(n=len(regions), steps_each=args.steps, ms_per_step=[round(r / args.steps, 3) for r in regions],
                                              sm_mhz=[c[0] for c in region_clk], power_w_max=[c[1] for c in region_clk], reported="median"),
-        config=dict(workload=wl.desc,
-                    per_gpu_batch=b, global_batch=b * world, seq_len=S, parallelism="dp%d" % world, dropout=args.dropout,
-                    l2="per-step working set (%.1f GB of activations) >> 126 MB L2; 4 rotating batches" % (b * S * 24.5e3 * 12 / 1e9),
-                    grad_allreduce="fp32, one bucket per encoder layer, overlapped with backward" if world > 1 else "none (1 GPU)"),
+        config=make_config(args, world),
         e2e=dict(value=round(e2e_value, 2), unit=UNIT, h2d_bytes_per_step=h2d_bytes, d2h_bytes_per_step=4 * n_out,
                  ms_per_step=round(e2e_ms / args.steps, 3), regions_ms_per_step=[round(r / args.steps, 3) for r in e2e_regions], reported="median"),
         gpu_launches=int(launches),
+        graph=dict(enabled=graphed is not None, launches_per_step=(graphed.launches_per_step if graphed is not None else None), error=graph_err,
+                   eager_ms_per_step=(round(eager_ms, 3) if eager_ms is not None else None),
+                   note="value / e2e replay ONE captured CUDA graph per step (visitron_b200.graph.GraphedStep: device-side row compaction and "
+                        "dropout seed, no host sync); eager_ms_per_step = the same step through ~400 ctypes launches"),
         clocks=clocks,
         model_flops=dict(per_sample_fwd_bwd_all_rows_GF=round(wl.flop_mult * fl["total"] / 1e9, 1),
                          per_sample_fwd_bwd_executed_GF=round(wl.flop_mult * fl_done["total"] / 1e9, 1),
@@ -437,6 +502,10 @@ def run_ours(args):
                              note="not part of `value` (metric is fwd+bwd); 28 algorithmic bytes per element (read p,g,m,v; write p,m,v)")
     if roof:
         line["roofline"] = roof
+    if sync_check is not None:
+        line["grad_sync"] = sync_check
+    if world == 1 and not args.no_gpu_eager and args.workload == "pretrain":
+        line["gpu_eager_baseline"] = gpu_eager_baseline(args, device, value)
     if world == 1 and not args.no_cpu_baseline and args.workload in ("pretrain", "viewpoint_select"):
         line["cpu_baseline"] = cpu_baseline(args, steps=2)
     sys.stdout.flush()
@@ -445,6 +514,88 @@ def run_ours(args):
     os.dup2(2, 1)
     if world > 1:
         torch.distributed.destroy_process_group()
+
+
+def grad_sync_check(wl, model, batch, device, world):
+    """Correctness of the data-parallel exchange on real NCCL ranks (DDP's contract, vs/pretrain.py:96-102): on a fixed batch per
+    rank with dropout off, (a) every rank ends the step with bit-identical gradients, (b) they equal the mean over ranks of the
+    gradients each rank computes on its own (the same step with the reducer detached, averaged by one plain all-reduce)."""
+    dist = torch.distributed
+    was_training = model.training
+    model.eval()     # dropout off: the two passes draw no masks
+    try:
+        def flat_grads():
+            return torch.cat([p.grad.detach().float().reshape(-1) for p in model.parameters() if p.grad is not None])
+
+        def one():
+            for p in wl.params:
+                p.grad = None
+            with torch.enable_grad():
+                out = wl.forward(batch)
+                out[0].backward()
+            torch.cuda.synchronize()
+            return flat_grads()
+        synced = one()
+        reducers = [(m, m._vt_reducer) for m in model.modules() if getattr(m, "_vt_reducer", None) is not None]
+        for m, _ in reducers:
+            m._vt_reducer = None
+        try:
+            local = one()
+        finally:
+            for m, r in reducers:
+                m._vt_reducer = r
+        mean = local.clone()
+        dist.all_reduce(mean, op=dist.ReduceOp.SUM)
+        mean /= world
+        lo, hi = synced.clone(), synced.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        identical = bool(torch.equal(lo, hi))
+        rel = float((synced - mean).norm() / mean.norm().clamp_min(1e-30))
+        return dict(grad_sync_ok=bool(identical and rel < 1e-3), identical_across_ranks=identical, rel_l2_vs_mean_of_local=rel, elements=int(synced.numel()),
+                    note="fixed batch per rank, dropout off; rel_l2 > 0 only from the fp32 summation order (split-K red.add, NCCL's reduction tree)")
+    finally:
+        model.train(was_training)
+
+
+def gpu_eager_baseline(args, device, our_value):
+    """SURVEY 8d-D5's comparison bar: the reference's eager graph (here the pinned fp32 restatement in oracle/, all rows through
+    the MLM head as the reference does) on the SAME B200 at the SAME batch, fp32 and under autocast(bf16); CUDA events, outside the
+    timed regions of `value`.  Reported baseline, not a target."""
+    from oracle import visitron_oracle as vo
+    from visitron_b200 import synthetic
+    out = {}
+    oc = vo.OracleConfig(hidden_dropout_prob=args.dropout, attention_probs_dropout_prob=0.1 if args.dropout > 0 else 0.0)
+    drop = vo.train_dropout if args.dropout > 0 else None
+    for b in (args.batch, 8):
+        try:
+            P = vo.clone_params(vo.init_params(oc, 88, perturb=False), device=device)
+            batch = {k: v.to(device) for k, v in synthetic.pretrain_batch(b, 88).items()}
+            for name, ctx in (("fp32", torch.autocast("cuda", enabled=False)), ("autocast_bf16", torch.autocast("cuda", dtype=torch.bfloat16))):
+                def one():
+                    for v in P.values():
+                        v.grad = None
+                    with ctx:
+                        vo.pretrain_step(P, oc, batch, drop)
+                one()
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                n = 3
+                e0.record()
+                for _ in range(n):
+                    one()
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / n
+                out[name] = dict(samples_per_s=round(b / (ms / 1e3), 2), ms_per_step=round(ms, 2), per_gpu_batch=b,
+                                 ours_over_this=round(our_value / (b / (ms / 1e3)), 2))
+            out["kind"] = "port (oracle/visitron_oracle.py on cuda:0; TF32 matmul %s)" % ("on" if torch.backends.cuda.matmul.allow_tf32 else "off")
+            break
+        except torch.cuda.OutOfMemoryError:
+            out = {"note": "b=%d did not fit beside the product's buffers; retried smaller" % b}
+            P = batch = None
+            torch.cuda.empty_cache()
+    return out
 
 
 def cpu_baseline(args, steps, warmup=1):
@@ -498,8 +649,7 @@ def run_reference(args):
     cb = cpu_baseline(args, steps, warm)
     line = dict(impl="reference", metric=METRIC, value=cb["value"], unit=UNIT, n_gpus=args.gpus, steps=steps, warmup=warm,
                 ms_per_step=round(2 / cb["value"] * 1e3, 1), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload="%s step (same workload as the default arm; bounded sample b=2 per step on the host CPU)" % args.workload,
-                            per_gpu_batch=2, seq_len=767 if args.workload == "pretrain" else 511),
+                config=make_config(args, args.gpus),
                 cpu_baseline=cb, e2e=dict(value=cb["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
     print(json.dumps(line), flush=True)
 
@@ -521,6 +671,8 @@ def main():
     ap.add_argument("--feat-bf16", action="store_true", help="region features / location embeddings come from a bf16 cache (pretrain workload)")
     ap.add_argument("--no-clocks", action="store_true", help="diagnosis: do not sample clocks during the timed region")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-eager", action="store_true", help="skip the oracle-on-the-GPU comparison leg (SURVEY 8d-D5)")
+    ap.add_argument("--no-graph", action="store_true", help="time the eager path (~400 ctypes launches per step) instead of the captured CUDA graph")
     ap.add_argument("--no-roofline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -40,6 +40,36 @@ int64_t vt_launch_count(void);
 void vt_reset_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------
+ * Device-resident step state: what lets a whole training step run without a host <-> device sync and be captured in a
+ * CUDA graph (the reference's loop syncs only at its .item() reads, vs/pretrain.py:195-201).
+ *
+ * Seeds.  Every op with dropout takes a 64-bit `seed` BY VALUE; a graph bakes it in at capture.  With a seed source set, the
+ * kernels XOR the 64-bit word at `seed_dev` (device memory) into that seed when they run, so each replay draws fresh masks.
+ * vt_seed_advance is the first node of a captured step: state[0] += 0x9E3779B97F4A7C15, state[1] = splitmix64(state[0]);
+ * the seed source is &state[1].  The source is process-wide (forward runs on the caller's thread, backward on autograd's);
+ * NULL (the default) restores by-value seeds.
+ *
+ * Row limit.  The pre-training heads run on the labelled rows only, and how many there are is known on the device only
+ * (vt_compact_labels).  While a row limit is set ON THE CALLING THREAD, every launch below that walks activation rows --
+ * vt_gemm_bf16 (M when A is [M,K]; the contraction K when A is [K,M], i.e. the weight-gradient form), vt_layernorm_fwd/bwd,
+ * vt_colsum_bf16, vt_gather_rows, vt_scatter_add_rows, vt_gelu_bwd, vt_softmax_ce_fwd/bwd -- is sized on the host for the
+ * caller's bound (the capacity) and clips itself on the device to rows_dev[0] (the count rounded up to 128; padding rows are
+ * zeros so that they add nothing to a contraction); the cross-entropy kernels use rows_dev[1] (the true count) for the rows
+ * that exist and for the mean.  NULL clears the limit.
+ * ------------------------------------------------------------------------------------------ */
+void vt_set_seed_source(const uint64_t* seed_dev);
+int vt_seed_advance(uint64_t* state /* device uint64[2] */, vt_stream stream);
+void vt_set_row_limit(const int32_t* rows_dev /* device int32[2] = {rows padded to 128, rows} */);
+/* Compaction of the labelled rows (replaces torch.nonzero(labels != -1) + labels[idx] in front of the MLM / token heads,
+ * vs/encoder.py:387-389,381-385, whose data-dependent sizes cost a sync per step).  For each of the two label arrays
+ * (int64 [n]; either may be NULL): idx[r] / lab[r] = position / label of the r-th label != ignore_index in ascending order
+ * (torch.nonzero's order), padding rows up to the next multiple of 128 get idx = -1, lab = 0;
+ * counts[4 a + {0,1,2}] = {padded count, count, labels outside [0, classes) or beyond capacity}.  capacity: rows of idx / lab. */
+int vt_compact_labels(const int64_t* labels_a, int64_t classes_a, const int64_t* labels_b, int64_t classes_b, int64_t n,
+                      int64_t ignore_index, int64_t capacity, int64_t* idx_a, int64_t* lab_a, int64_t* idx_b, int64_t* lab_b,
+                      int32_t* counts /* device int32[8] */, vt_stream stream);
+
+/* ------------------------------------------------------------------------------------------
  * Dense projections: one tcgen05/TMEM GEMM fed by TMA.
  *   D[M,N] = epilogue( alpha * sum_k A(m,k) * B(n,k) )
  * a_major / b_major: 0 = the contraction dim k is contiguous in memory (A is [M,K], B is [N,K],
@@ -153,7 +183,8 @@ int vt_pad_cast_concat_mixed(const void* a, int a_bf16, int64_t d0, const void* 
 int vt_dropout_rows(const void* x, int64_t ldx, int64_t rows, int64_t hidden, void* y, int64_t ldy, float dropout_p,
                     uint64_t seed, uint32_t dropout_stream, int64_t remap_rows_in, int64_t remap_rows_out,
                     int64_t remap_row_off, vt_stream stream);
-/* dst[r] = src[idx[r]] ; dst[idx[r]] += src[r]   (compaction of the labelled rows for the MLM / token heads) */
+/* dst[r] = src[idx[r]] ; dst[idx[r]] += src[r]   (compaction of the labelled rows for the MLM / token heads);
+ * idx[r] < 0 (a padding row of vt_compact_labels): gathered as zeros, skipped by the scatter */
 int vt_gather_rows(const void* src, int64_t lds, const int64_t* idx, int64_t n, int64_t hidden, void* dst, int64_t ldd,
                    vt_stream stream);
 int vt_scatter_add_rows(const void* src, int64_t lds, const int64_t* idx, int64_t n, int64_t hidden, void* dst, int64_t ldd,
@@ -170,8 +201,6 @@ int vt_scatter_add_rows(const void* src, int64_t lds, const int64_t* idx, int64_
 /* bias = (1 - mask) * -10000 in fp32 for any mask value (vs/encoder.py:226-241).
  * mask_dtype: 0 int64, 1 uint8/bool, 2 int32, 3 fp32. */
 int vt_mask_bias(const void* mask, int mask_dtype, int64_t n, float* bias, vt_stream stream);
-/* Debug hook for tests: 0 = auto (tcgen05 kernels for S <= 2048), 1 = mma.sync kernels, 2 = tcgen05 kernels. */
-void vt_debug_attention_impl(int impl);
 /* Optional plan of the key tiles worth visiting: key_tiles[b] bit t = the 64-key tile t of sample b holds a key whose bias is within
  * 5000 of the sample's largest (an unmasked key).  The probabilities of the other tiles are exactly 0 in the reference's fp32 softmax
  * (exp(-10000 + ...) underflows), so the kernels skip them without changing a bit of ctx or of any gradient.  S <= 2048.
@@ -210,6 +239,12 @@ int vt_action_head_bwd(const float* pooled, const float* W, int64_t B, int64_t h
 int vt_pretrain_finalize(const float* mlm_loss, const int64_t* mlm_arg, const int64_t* mlm_lab, int64_t n_mlm, const float* tok_loss,
                          const int64_t* tok_arg, const int64_t* tok_lab, int64_t n_tok, const float* act_loss, const int64_t* act_arg,
                          const int64_t* act_lab, int64_t n_act, float* out8, vt_stream stream);
+
+/* the same with the two label counts read from vt_compact_labels' counts (no host knowledge of them); a label outside its class
+ * range turns the loss NaN (torch's CrossEntropyLoss raises a device assert there) */
+int vt_pretrain_finalize_counted(const float* mlm_loss, const int64_t* mlm_arg, const int64_t* mlm_lab, const float* tok_loss,
+                                 const int64_t* tok_arg, const int64_t* tok_lab, const float* act_loss, const int64_t* act_arg,
+                                 const int64_t* act_lab, int64_t n_act, const int32_t* counts, float* out8, vt_stream stream);
 
 /* dx (bf16) = dy * (1 - y^2)  -- backward of the pooler's tanh (hf/modeling_bert.py:461-467) */
 int vt_tanh_bwd(const float* dy, const float* y, int64_t n, void* dx, vt_stream stream);
@@ -267,6 +302,7 @@ typedef struct {
   float* g;            /* its gradient */
   float* m;            /* exp_avg */
   float* v;            /* exp_avg_sq */
+  void* p_bf16;        /* optional bf16 copy of p (the tensor-core operand of the next forward), written in the same pass; NULL: none */
   int64_t n;
   int32_t group;       /* parameter group 0..7: selects step_size[] / lr_decay[] */
   int32_t first_chunk; /* prefix sum of ceil(n / vt_opt_chunk()) over the preceding segments */

@@ -237,11 +237,14 @@ def bert_img_forward(P: Params, cfg: OracleConfig, input_ids, token_type_ids=Non
 # pre-training heads
 # --------------------------------------------------------------------------------------------
 def mlm_logits(P: Params, cfg, h):
-    """BertOnlyMLMHead, hf/modeling_bert.py:470-513; decoder weight tied to the word embeddings."""
+    """BertOnlyMLMHead, hf/modeling_bert.py:470-513; decoder weight tied to the word embeddings -- unless
+    resize_embeddings has replaced the embedding table (vs/encoder.py:337-345 does not re-tie): the decoder then keeps the
+    old table as a parameter of its own, here the optional entry "mlmhead.predictions.decoder.weight"."""
     t = F.linear(h, P["mlmhead.predictions.transform.dense.weight"], P["mlmhead.predictions.transform.dense.bias"])
     t = bert_layer_norm(gelu_erf(t), P["mlmhead.predictions.transform.LayerNorm.weight"],
                         P["mlmhead.predictions.transform.LayerNorm.bias"], cfg.layer_norm_eps)
-    return F.linear(t, P["bert.embeddings.word_embeddings.weight"]) + P["mlmhead.predictions.bias"]
+    dec = P.get("mlmhead.predictions.decoder.weight", P["bert.embeddings.word_embeddings.weight"])
+    return F.linear(t, dec) + P["mlmhead.predictions.bias"]
 
 
 def pretrain_forward(P: Params, cfg: OracleConfig, input_ids, token_type_ids=None, attention_mask=None,

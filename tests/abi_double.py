@@ -26,6 +26,50 @@ def _remap_rows(n, remap, device):
     return m
 
 
+# ---- device-resident row counts (ops.compact_labels / ops.row_limit): rows past the padded count are never touched by the
+# kernels, so the double fills them with NaN -- any host logic that lets one leak into a result fails the test ----
+_LIMIT = None   # (rows padded to 128, rows) while a row_limit is active
+
+
+def _rows(n):
+    return n if _LIMIT is None else min(n, _LIMIT[0])
+
+
+def _nan_like(shape, dtype):
+    return torch.full(shape, float("nan"), dtype=dtype)
+
+
+def compact_labels(labels_a, classes_a, labels_b, classes_b, capacity, ignore_index=-1):
+    CALLS.append("compact_labels")
+    outs, counts = [], torch.zeros(8, dtype=torch.int32)
+    for w, (lab, classes) in enumerate(((labels_a, classes_a), (labels_b, classes_b))):
+        idx = torch.full((capacity,), -12345, dtype=torch.int64)   # garbage past the padded count
+        val = torch.full((capacity,), -12345, dtype=torch.int64)
+        nz = torch.nonzero(lab != ignore_index).squeeze(1)
+        n = min(int(nz.numel()), capacity)
+        npad = min(capacity, (n + 127) // 128 * 128)
+        idx[:n], val[:n] = nz[:n], lab[nz[:n]]
+        idx[n:npad], val[n:npad] = -1, 0
+        counts[4 * w], counts[4 * w + 1] = npad, n
+        counts[4 * w + 2] = int(((val[:n] < 0) | (val[:n] >= classes)).sum()) + int(nz.numel() > capacity)
+        outs += [idx, val]
+    return outs[0], outs[1], outs[2], outs[3], counts
+
+
+class row_limit:
+    def __init__(self, counts, which=0):
+        self.v = (int(counts[4 * which]), int(counts[4 * which + 1]))
+
+    def __enter__(self):
+        global _LIMIT
+        _LIMIT = self.v
+
+    def __exit__(self, *exc):
+        global _LIMIT
+        _LIMIT = None
+        return False
+
+
 def _no_dropout(p):
     assert not p or p <= 0, "the CPU test double only covers dropout p == 0"
 
@@ -39,6 +83,12 @@ def gemm(A, B, *, a_major=0, b_major=0, out=None, out_dtype=BF16, bias=None, act
     Af = A.float().t() if a_major else A.float()
     Bf = B.float() if b_major else B.float().t()
     k = min(Af.size(1), Bf.size(0)) if K is None else K
+    m_full = Af.size(0)
+    if _LIMIT is not None:
+        if a_major:
+            k = min(k, _LIMIT[0])      # weight-gradient form: the contraction runs over the rows
+        else:
+            Af = Af[: _LIMIT[0]]
     r = alpha * (Af[:, :k] @ Bf[:k])
     if M is not None:
         r = r[:M]
@@ -70,6 +120,10 @@ def gemm(A, B, *, a_major=0, b_major=0, out=None, out_dtype=BF16, bias=None, act
         r = r + residual[rows].float()[:, :n]
     if out is None:
         assert remap is None
+        if r.size(0) < m_full and not a_major:
+            full = _nan_like((m_full, r.size(1)), out_dtype)
+            full[: r.size(0)] = r.to(out_dtype)
+            return full
         return r.to(out_dtype)
     if accumulate:
         assert out.dtype == F32
@@ -88,10 +142,15 @@ def _ln(x, g, b, eps):
 def layernorm_fwd(x, gamma, beta, eps, out=None, dropout_p=0.0, seed=0, stream_id=0, remap=(0, 0, 0)):
     CALLS.append("layernorm_fwd")
     _no_dropout(dropout_p)
-    y = _ln(x.float(), gamma, beta, eps).to(BF16)
+    n = _rows(x.size(0))
+    y = _ln(x[:n].float(), gamma, beta, eps).to(BF16)
     if out is None:
+        if n < x.size(0):
+            full = _nan_like(tuple(x.shape), BF16)
+            full[:n] = y
+            return full
         return y
-    out[_remap_rows(x.size(0), remap, x.device)] = y
+    out[_remap_rows(n, remap, x.device)] = y
     return out
 
 
@@ -100,9 +159,10 @@ def layernorm_bwd(dy, x, gamma, eps, dgamma, dbeta, dbias=None, want_dx=True, ou
     CALLS.append("layernorm_bwd")
     _no_dropout(out_dropout_p)
     _no_dropout(in_dropout_p)
-    rows = _remap_rows(x.size(0), remap, x.device)
+    n = _rows(x.size(0))
+    rows = _remap_rows(n, remap, x.device)
     d = dy[rows].float()
-    xr = x.float().requires_grad_(True)
+    xr = x[:n].float().requires_grad_(True)
     g = gamma.detach().clone().requires_grad_(True)
     b = torch.zeros_like(g).requires_grad_(True)
     with torch.enable_grad():
@@ -112,6 +172,10 @@ def layernorm_bwd(dy, x, gamma, eps, dgamma, dbeta, dbias=None, want_dx=True, ou
     res = xr.grad.to(BF16)
     if dbias is not None:
         dbias += xr.grad.sum(0)
+    if n < x.size(0):
+        full = _nan_like(tuple(x.shape), BF16)
+        full[:n] = res
+        res = full
     return res, res
 
 
@@ -147,7 +211,7 @@ def embed_ln_bwd(dy, ids, type_ids, pos_ids, word, pos, typ, gamma, eps, rows_pe
 def colsum(x, out, ncols=None, accumulate=True):
     CALLS.append("colsum")
     n = x.size(1) if ncols is None else ncols
-    s = x.float()[:, :n].sum(0)
+    s = x.float()[: _rows(x.size(0)), :n].sum(0)
     if accumulate:
         out[:n] += s
     else:
@@ -181,7 +245,10 @@ def dropout_rows(x, rows, out, dropout_p, seed, stream_id, remap=(0, 0, 0)):
 
 def gather_rows(src, idx, out=None):
     CALLS.append("gather_rows")
-    r = src[idx]
+    n = _rows(idx.numel())
+    r = _nan_like((idx.numel(), src.size(1)), src.dtype)
+    live = idx[:n]
+    r[:n] = torch.where((live >= 0)[:, None], src[live.clamp_min(0)], torch.zeros((), dtype=src.dtype))
     if out is None:
         return r.contiguous()
     out.copy_(r)
@@ -190,7 +257,10 @@ def gather_rows(src, idx, out=None):
 
 def scatter_add_rows(src, idx, dst):
     CALLS.append("scatter_add_rows")
-    dst[idx] = (dst[idx].float() + src.float()).to(BF16)
+    n = _rows(idx.numel())
+    keep = idx[:n] >= 0
+    ii = idx[:n][keep]
+    dst[ii] = (dst[ii].float() + src[:n][keep].float()).to(BF16)
 
 
 def mask_bias(mask):
@@ -229,21 +299,33 @@ def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0,
 
 def softmax_ce_fwd(logits, ncols, labels, double_softmax=False):
     CALLS.append("softmax_ce_fwd")
-    x = logits[:, :ncols].float()
+    rows = logits.size(0)
+    n = rows if _LIMIT is None else min(rows, _LIMIT[1])
+    x = logits[:n, :ncols].float()
     inp = torch.softmax(x, -1) if double_softmax else x
-    loss = F.cross_entropy(inp, labels, reduction="none") if x.size(0) else x.new_zeros(0)
-    return loss, x.argmax(1) if x.size(0) else labels.new_zeros(0), torch.zeros((x.size(0), 2))
+    loss = _nan_like((rows,), F32)
+    arg = torch.full((rows,), -12345, dtype=torch.int64)
+    if n:
+        loss[:n] = F.cross_entropy(inp, labels[:n], reduction="none")
+        arg[:n] = x.argmax(1)
+    return loss, arg, torch.zeros((rows, 2))
 
 
 def softmax_ce_bwd(logits, ncols, labels, stats, scale, scale_dev, double_softmax=False, ld_out=None):
     CALLS.append("softmax_ce_bwd")
-    x = logits[:, :ncols].float().detach().clone().requires_grad_(True)
-    with torch.enable_grad():
-        inp = torch.softmax(x, -1) if double_softmax else x
-        (F.cross_entropy(inp, labels, reduction="sum") * scale * scale_dev.reshape(())).backward()
+    rows = logits.size(0)
+    n, npad = (rows, rows) if _LIMIT is None else (min(rows, _LIMIT[1]), min(rows, _LIMIT[0]))
+    if _LIMIT is not None:
+        scale = scale / max(n, 1)      # the mean's 1 / n is applied on the device
+    x = logits[:n, :ncols].float().detach().clone().requires_grad_(True)
     ld_out = (ncols + 7) // 8 * 8 if ld_out is None else ld_out
-    d = torch.zeros((x.size(0), ld_out), dtype=BF16)
-    d[:, :ncols] = x.grad.to(BF16)
+    d = _nan_like((rows, ld_out), BF16)
+    d[:npad] = 0
+    if n:
+        with torch.enable_grad():
+            inp = torch.softmax(x, -1) if double_softmax else x
+            (F.cross_entropy(inp, labels[:n], reduction="sum") * scale * scale_dev.reshape(())).backward()
+        d[:n, :ncols] = x.grad.to(BF16)
     return d
 
 
@@ -289,6 +371,15 @@ def pretrain_finalize(mlm, tok, act):
     return out
 
 
+def pretrain_finalize_counted(mlm, tok, act, counts):
+    CALLS.append("pretrain_finalize_counted")
+    n, nt = int(counts[1]), int(counts[5])
+    out = pretrain_finalize(tuple(t[:n] for t in mlm), tuple(t[:nt] for t in tok), act)
+    if int(counts[2]) or int(counts[6]):
+        out[0] = float("nan")
+    return out
+
+
 def tanh_bwd(dy, y):
     CALLS.append("tanh_bwd")
     return (dy * (1.0 - y * y)).to(BF16)
@@ -296,9 +387,12 @@ def tanh_bwd(dy, y):
 
 def gelu_bwd(dy, pre):
     CALLS.append("gelu_bwd")
-    x = pre.float()
+    n = _rows(pre.size(0))
+    x = pre[:n].float()
     g = 0.5 * (1.0 + torch.erf(x / math.sqrt(2.0))) + x * torch.exp(-0.5 * x * x) / math.sqrt(2.0 * math.pi)
-    return (dy.float() * g).to(BF16)
+    out = _nan_like(tuple(pre.shape), BF16)
+    out[:n] = (dy[:n].float() * g).to(BF16)
+    return out
 
 
 def to_f32(x):
@@ -317,7 +411,8 @@ def to_bf16(x, addend=None, out=None):
 
 _OPS = ["layernorm_fwd", "layernorm_bwd", "embed_ln_fwd", "embed_ln_bwd", "colsum", "cast_weight", "pad_cast_concat",
         "dropout_rows", "gather_rows", "scatter_add_rows", "mask_bias", "attention_key_tiles", "attention_fwd", "attention_bwd", "softmax_ce_fwd",
-        "softmax_ce_bwd", "action_head_fwd", "action_head_bwd", "pretrain_finalize", "tanh_bwd", "gelu_bwd", "to_f32", "to_bf16"]
+        "softmax_ce_bwd", "action_head_fwd", "action_head_bwd", "pretrain_finalize", "pretrain_finalize_counted", "compact_labels", "row_limit",
+        "tanh_bwd", "gelu_bwd", "to_f32", "to_bf16"]
 
 
 def install(monkeypatch):

@@ -225,17 +225,10 @@ def _attn_ref(qkv, bias, B, S, heads, mask=None, scale_drop=1.0):
     return (p @ v).permute(0, 2, 1, 3).reshape(B * S, heads * 64)
 
 
-@pytest.fixture(params=[1, 2], ids=["mma_sync", "tcgen05"])
-def attn_impl(request):
-    ops.set_attention_impl(request.param)
-    yield request.param
-    ops.set_attention_impl(0)
-
-
 @pytest.mark.parametrize("B,S,heads,mask_kind", [(2, 767, 12, "pad"), (3, 511, 12, "f6"), (1, 64, 2, "pad"), (2, 100, 3, "none"), (1, 1, 1, "none"),
                                                  (1, 129, 1, "pad"), (2, 1000, 2, "pad"),
                                                  (9, 767, 12, "pad")])   # enough items for two query tiles per CTA in the forward
-def test_attention_fwd_bwd(B, S, heads, mask_kind, attn_impl):
+def test_attention_fwd_bwd(B, S, heads, mask_kind):
     torch.manual_seed(8)
     Hh = heads * 64
     qkv = torch.randn(B * S, 3 * Hh, device=DEV).to(BF)
@@ -261,30 +254,7 @@ def test_attention_fwd_bwd(B, S, heads, mask_kind, attn_impl):
     assert rel_l2(dqkv, qr.grad) < 2e-2
 
 
-def test_attention_implementations_agree_including_dropout():
-    """The tcgen05 and mma.sync kernels share the dropout counter layout: outputs must agree to bf16 rounding, and
-    either backward must accept the other's forward statistics."""
-    torch.manual_seed(12)
-    B, S, heads, p, seed, sid = 2, 300, 3, 0.1, 77, 9
-    qkv = torch.randn(B * S, 3 * heads * 64, device=DEV).to(BF)
-    mask = torch.ones(B, S, dtype=torch.long, device=DEV)
-    mask[1, 200:] = 0
-    bias = ops.mask_bias(mask)
-    dctx = torch.randn(B * S, heads * 64, device=DEV).to(BF)
-    res = {}
-    for impl in (1, 2):
-        ops.set_attention_impl(impl)
-        ctx, lse = ops.attention_fwd(qkv, bias, B, S, heads, dropout_p=p, seed=seed, stream_id=sid)
-        res[impl] = (ctx, lse, ops.attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=p, seed=seed, stream_id=sid))
-    ops.set_attention_impl(1)
-    cross = ops.attention_bwd(qkv, bias, res[2][0], dctx, res[2][1], B, S, heads, dropout_p=p, seed=seed, stream_id=sid)
-    ops.set_attention_impl(0)
-    close(res[2][0], res[1][0], what="ctx tc vs mma.sync")
-    assert rel_l2(res[2][2], res[1][2]) < 1e-2
-    assert rel_l2(cross, res[1][2]) < 1e-2
-
-
-def test_attention_dropout_fwd_bwd_same_mask(attn_impl):
+def test_attention_dropout_fwd_bwd_same_mask():
     """Recover the dropout mask with one-hot V, then check fwd and bwd against autograd with that mask."""
     torch.manual_seed(9)
     B, S, heads, p, seed, sid = 2, 128, 2, 0.1, 99, 5

@@ -10,6 +10,11 @@ SIGNATURES = {
     "vt_reset_launch_count": (None, []),
     "vt_debug_force_block_n": (None, [I]),
     "vt_reserve_sms": (None, [I]),
+    "vt_set_seed_source": (None, [P]),
+    "vt_seed_advance": (I, [P, P]),
+    "vt_set_row_limit": (None, [P]),
+    "vt_compact_labels": (I, [P, I64, P, I64, I64, I64, I64, P, P, P, P, P, P]),
+    "vt_pretrain_finalize_counted": (I, [P, P, P, P, P, P, P, P, P, I64, P, P, P]),
     "vt_gemm_bf16": (I, [P, I64, I, P, I64, I, P, I64, I64, I64, I64, P, P]),
     "vt_layernorm_fwd": (I, [P, I64, P, P, F, I64, I64, P, I64, F, U64, U32, I64, I64, I64, P]),
     "vt_row_partials_rows": (I64, [I64]),
@@ -24,7 +29,6 @@ SIGNATURES = {
     "vt_dropout_rows": (I, [P, I64, I64, I64, P, I64, F, U64, U32, I64, I64, I64, P]),
     "vt_gather_rows": (I, [P, I64, P, I64, I64, P, I64, P]),
     "vt_scatter_add_rows": (I, [P, I64, P, I64, I64, P, I64, P]),
-    "vt_debug_attention_impl": (None, [I]),
     "vt_mask_bias": (I, [P, I, I64, P, P]),
     "vt_attention_key_tiles": (I, [P, I64, I64, P, P]),
     "vt_attention_fwd": (I, [P, I64, P, P, I64, I64, I64, I64, P, P, F, U64, U32, P]),

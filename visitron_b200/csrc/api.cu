@@ -47,6 +47,22 @@ int usable_sms() {
 }
 
 int resolve_driver_entry_points();
+void count_launch(int n);
+
+// Device-resident step state for sync-free / CUDA-graph steps (see the header): one process-wide seed source (forward runs on the
+// caller's thread, backward on autograd's, both must see it) and a per-thread row limit (set and cleared around a group of launches).
+static std::atomic<const uint32_t*> g_seed_source{nullptr};
+static thread_local const int32_t* g_row_limit = nullptr;
+const uint32_t* seed_source() { return g_seed_source.load(std::memory_order_relaxed); }
+const int32_t* row_limit() { return g_row_limit; }
+
+// state[0] += golden ratio; state[1] = splitmix64(state[0]): one thread, first node of a captured step
+__global__ void seed_advance_kernel(unsigned long long* state) {
+  unsigned long long z = (state[0] += 0x9E3779B97F4A7C15ull);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  state[1] = z ^ (z >> 31);
+}
 
 }  // namespace vt
 
@@ -54,6 +70,16 @@ extern "C" const char* vt_last_error(void) { return vt::g_err; }
 
 extern "C" int vt_num_sms(void) { return vt::num_sms(); }
 extern "C" void vt_reserve_sms(int n) { vt::g_reserved_sms.store(n < 0 ? 0 : n); }
+
+extern "C" void vt_set_seed_source(const uint64_t* seed_dev) { vt::g_seed_source.store(reinterpret_cast<const uint32_t*>(seed_dev)); }
+extern "C" void vt_set_row_limit(const int32_t* rows_dev) { vt::g_row_limit = rows_dev; }
+extern "C" int vt_seed_advance(uint64_t* state, vt_stream stream) {
+  VT_REQUIRE(state && ((uintptr_t)state & 7) == 0, "vt_seed_advance: state must be an 8-byte aligned device uint64[2]");
+  vt::seed_advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(reinterpret_cast<unsigned long long*>(state));
+  vt::count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
 
 extern "C" int vt_init(int device) {
   int count = 0;

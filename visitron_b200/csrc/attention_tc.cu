@@ -13,8 +13,7 @@
 //     MODE 0 (one CTA per key tile):    dV += P^T.dO,  dK += dS^T.Q   (operands read MN-major in place)
 //     MODE 1 (one CTA per query tile):  dQ += dS.K
 //   Two kernels, no atomics: results are deterministic.
-// Both share the dropout counter layout of the mma.sync kernels in attention.cu (kept for S > 2048
-// and as the A/B reference), so forward and backward of either implementation are interchangeable.
+// (The round-1 mma.sync kernels that served as the A/B reference are gone: the path never exceeds S = 767.)
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -35,12 +34,35 @@ using namespace ptx;
 void count_launch(int n);
 int resolve_driver_entry_points();
 int make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner, uint32_t box_outer);
-int attention_fwd_legacy(const void* qkv, int64_t ld, const float* bias, int64_t B, int64_t S, int64_t heads, void* ctx, float* lse,
-                         float dropout_p, uint64_t seed, uint32_t dropout_stream, cudaStream_t st);
-int attention_bwd_legacy(const void* qkv, int64_t ld, const float* bias, const void* ctx, const void* dctx, const float* lse, float* dsum_ws,
-                         int64_t B, int64_t S, int64_t heads, void* dqkv, float dropout_p, uint64_t seed, uint32_t dropout_stream,
-                         cudaStream_t st);
-int attention_bwd_prep(const void* dctx, const void* ctx, float* dsum, int64_t B, int64_t S, int64_t heads, cudaStream_t st);
+
+// bias[i] = (1 - (float)mask[i]) * -10000     (vs/encoder.py:238-241; any integer / float mask value)
+template <typename T>
+__global__ void mask_bias_kernel(const T* __restrict__ mask, long long n, float* __restrict__ bias) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) bias[i] = (1.0f - (float)mask[i]) * -10000.0f;
+}
+
+// backward prep: dsum[b, h, i] = sum_d dO[i, h, d] * O[i, h, d]
+__global__ void __launch_bounds__(256)
+attn_bwd_prep_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ out, float* __restrict__ dsum, int B, int S, int heads, int hidden) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long long rows = (long long)B * S;
+  for (long long m = (long long)blockIdx.x * 8 + warp; m < rows; m += (long long)gridDim.x * 8) {
+    const long long b = m / S, i = m % S;
+    for (int c = lane; c < hidden / 8; c += 32) {  // 8 lanes cover one 64-wide head
+      float a[8], o[8];
+      unpack8(__ldg(reinterpret_cast<const uint4*>(dout + m * hidden + c * 8)), a);
+      unpack8(__ldg(reinterpret_cast<const uint4*>(out + m * hidden + c * 8)), o);
+      float s = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += a[j] * o[j];
+      s += __shfl_xor_sync(0xffffffffu, s, 1);
+      s += __shfl_xor_sync(0xffffffffu, s, 2);
+      s += __shfl_xor_sync(0xffffffffu, s, 4);
+      if ((lane & 7) == 0) dsum[(b * heads + c / 8) * S + i] = s;
+    }
+  }
+}
 
 constexpr uint32_t MMA_POLL_NS = 0;  // the MMA-issuing lane spins: a nanosleep here sits on the critical path of every tile
 constexpr float kLog2e = 1.4426950408889634f;
@@ -298,6 +320,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     const int sm_tid = (int)threadIdx.x;   // 0 .. 255
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
     const uint32_t lane_o = tmem_o + ((uint32_t)(quad * 32) << 16) + COLS * half;   // this thread's columns of O
+    const DropoutCfg dcfg = resolve_dropout(p.drop);
     int g = 0, b_loaded = -1;
     for (int it = 0; it < my_items; ++it) {
       int qt, h, b;
@@ -362,15 +385,15 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
           }
         }
         l += rs;
-        if (p.drop.thresh16 && !VT_DBG(1)) {
+        if (dcfg.thresh16 && !VT_DBG(1)) {
           // counter layout of attn_dropout_rand: call t of 32-column group g covers columns 8 q + 2 t (low 16-bit lane of word q)
           // and 8 q + 2 t + 1 (high lane); keep iff lane >= thresh16.  The 1 / (1 - p) scale is applied once, to O.
-          const uint32_t thi = p.drop.thresh16 << 16;
+          const uint32_t thi = dcfg.thresh16 << 16;
 #pragma unroll
           for (int gq = 0; gq < COLS / 32; ++gq) {
 #pragma unroll
             for (uint32_t t = 0; t < 4; ++t) {
-              const uint4 rr = attn_dropout_rand(p.drop, bh, (uint32_t)qi, (uint32_t)(j * 2 + (HV == 2 ? half : gq)), t);
+              const uint4 rr = attn_dropout_rand(dcfg, bh, (uint32_t)qi, (uint32_t)(j * 2 + (HV == 2 ? half : gq)), t);
               const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
@@ -431,7 +454,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       __syncwarp();
       if (lane == 0) mbar_arrive(o_free);   // the next item's first P.V may overwrite O
       const float inv = 1.0f / l;
-      const float onorm = p.drop.thresh16 ? inv * p.drop.scale : inv;
+      const float onorm = dcfg.thresh16 ? inv * dcfg.scale : inv;
       if (qi < S) {
         bf16* dst = p.out + ((long long)row_base + qi) * p.hidden + h * 64 + COLS * half;
 #pragma unroll
@@ -623,10 +646,11 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
     const int r = quad * 32 + lane;               // query row within the tile
     const int ew_tid = (int)threadIdx.x;          // 0 .. 511
     const uint32_t lane_addr = tmem_base + ((uint32_t)(quad * 32) << 16);
-    const bool drop = p.drop.thresh16 != 0;
-    const float dscale = drop ? p.drop.scale : 1.0f;
+    const DropoutCfg dcfg = resolve_dropout(p.drop);
+    const bool drop = dcfg.thresh16 != 0;
+    const float dscale = drop ? dcfg.scale : 1.0f;
     const float inv_dscale = 1.0f / dscale;
-    const uint32_t thi = p.drop.thresh16 << 16;   // 0 without dropout: every unsigned lane compares >= 0, i.e. is kept
+    const uint32_t thi = dcfg.thresh16 << 16;   // 0 without dropout: every unsigned lane compares >= 0, i.e. is kept
     const uint32_t st_off = (uint32_t)(cq >> 1) * TILE16K + (uint32_t)r * 128u;  // row r of the 64-key half this group lies in
     const uint32_t ch0 = (uint32_t)(cq & 1) * 4u;                                 // first 16-byte chunk of the group in that row
 
@@ -754,7 +778,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
           for (int t2 = 0; t2 < 2; ++t2) {
             const uint32_t tt = (uint32_t)(2 * hf + t2);
             uint4 rr = make_uint4(0u, 0u, 0u, 0u);
-            if (drop) rr = attn_dropout_rand(p.drop, bh, (uint32_t)gi, (uint32_t)(kt * 4 + cq), tt);
+            if (drop) rr = attn_dropout_rand(dcfg, bh, (uint32_t)gi, (uint32_t)(kt * 4 + cq), tt);
             const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -840,13 +864,27 @@ attn_dq_reduce_kernel(const bf16* __restrict__ ws, long long slice, int nkt, lon
   *reinterpret_cast<uint4*>(dqkv + row * ld + c) = pack8(acc);
 }
 
-static int g_attn_impl = 0;  // 0 auto, 1 mma.sync kernels, 2 tcgen05 kernels
-
 }  // namespace vt
 
 using namespace vt;
 
-extern "C" void vt_debug_attention_impl(int impl) { vt::g_attn_impl = impl; }
+extern "C" int vt_mask_bias(const void* mask, int mask_dtype, int64_t n, float* bias, vt_stream stream) {
+  VT_REQUIRE(mask && bias, "vt_mask_bias: null pointer");
+  if (n == 0) return VT_OK;
+  const int th = 256;
+  const int gr = (int)((n + th - 1) / th);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (mask_dtype) {
+    case 0: mask_bias_kernel<long long><<<gr, th, 0, st>>>((const long long*)mask, n, bias); break;
+    case 1: mask_bias_kernel<unsigned char><<<gr, th, 0, st>>>((const unsigned char*)mask, n, bias); break;
+    case 2: mask_bias_kernel<int><<<gr, th, 0, st>>>((const int*)mask, n, bias); break;
+    case 3: mask_bias_kernel<float><<<gr, th, 0, st>>>((const float*)mask, n, bias); break;
+    default: VT_REQUIRE(false, "vt_mask_bias: unknown mask dtype code %d", mask_dtype);
+  }
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
 
 extern "C" int64_t vt_attention_bwd_workspace(int64_t B, int64_t S, int64_t heads) {
   const int64_t dsum_floats = (B * heads * S + 3) & ~(int64_t)3;
@@ -855,7 +893,8 @@ extern "C" int64_t vt_attention_bwd_workspace(int64_t B, int64_t S, int64_t head
 
 static int check_attn_tc(const char* who, const void* qkv, int64_t ld, int64_t B, int64_t S, int64_t heads, int64_t head_dim) {
   VT_REQUIRE(head_dim == 64, "%s: head dim %lld outside the supported envelope (64)", who, (long long)head_dim);
-  VT_REQUIRE(B > 0 && S > 0 && heads > 0 && S <= 4096, "%s: bad sizes B=%lld S=%lld heads=%lld", who, (long long)B, (long long)S, (long long)heads);
+  VT_REQUIRE(B > 0 && S > 0 && heads > 0, "%s: bad sizes B=%lld S=%lld heads=%lld", who, (long long)B, (long long)S, (long long)heads);
+  VT_REQUIRE(S <= FWD_MAX_S, "%s: S = %lld outside the supported envelope (<= %d; the path's position tables end at 767)", who, (long long)S, FWD_MAX_S);
   VT_REQUIRE(ld % 8 == 0 && ld >= 3 * heads * 64 && ((uintptr_t)qkv & 15) == 0, "%s: qkv must be 16-byte aligned with ld %% 8 == 0", who);
   VT_REQUIRE(B <= 65535 && heads <= 65535 && B * S < (1ll << 31), "%s: grid limits", who);
   return VT_OK;
@@ -866,8 +905,6 @@ static int attn_dbg() {
   if (v < 0) { const char* e = getenv("VT_ATTN_DBG"); v = e ? atoi(e) : 0; }
   return v;
 }
-
-static bool use_tc(int64_t S) { return g_attn_impl == 2 || (g_attn_impl == 0 && S <= 2048); }
 
 extern "C" int vt_attention_key_tiles(const float* bias, int64_t B, int64_t S, uint32_t* key_tiles, vt_stream stream) {
   VT_REQUIRE(bias && key_tiles && B > 0 && S > 0, "vt_attention_key_tiles: bad arguments");
@@ -884,7 +921,6 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
   int rc = check_attn_tc("vt_attention_fwd", qkv, ld, B, S, heads, head_dim);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  if (!use_tc(S)) return attention_fwd_legacy(qkv, ld, bias, B, S, heads, ctx, lse, dropout_p, seed, dropout_stream, st);
   rc = resolve_driver_entry_points();
   if (rc) return rc;
   VT_REQUIRE(((uintptr_t)ctx & 15) == 0, "vt_attention_fwd: ctx must be 16-byte aligned");
@@ -934,7 +970,6 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
   if (rc) return rc;
   VT_REQUIRE(((uintptr_t)dqkv & 15) == 0 && ((uintptr_t)ctx & 15) == 0 && ((uintptr_t)dctx & 15) == 0, "vt_attention_bwd: 16-byte alignment required");
   cudaStream_t st = (cudaStream_t)stream;
-  if (!use_tc(S)) return attention_bwd_legacy(qkv, ld, bias, ctx, dctx, lse, dsum_ws, B, S, heads, dqkv, dropout_p, seed, dropout_stream, st);
   rc = resolve_driver_entry_points();
   if (rc) return rc;
   const int64_t hidden = heads * 64;
@@ -943,8 +978,13 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
   if (rc) return rc;
   rc = make_map(&tdo, dctx, (uint64_t)hidden, (uint64_t)(B * S), (uint64_t)hidden, 64, 128);
   if (rc) return rc;
-  rc = attention_bwd_prep(dctx, ctx, dsum_ws, B, S, heads, st);
-  if (rc) return rc;
+  {
+    const long long prows = B * S;
+    long long pg = (prows + 7) / 8, cap = (long long)num_sms() * 8;
+    attn_bwd_prep_kernel<<<(int)(pg < cap ? pg : cap), 256, 0, st>>>((const bf16*)dctx, (const bf16*)ctx, dsum_ws, (int)B, (int)S, (int)heads, (int)hidden);
+    count_launch(1);
+    VT_CHECK_LAUNCH();
+  }
   AttnTcParams p = {};
   p.B = (int)B; p.S = (int)S; p.heads = (int)heads; p.hidden = (int)hidden;
   const int nt = (int)((S + 127) / 128);

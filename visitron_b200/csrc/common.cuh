@@ -163,10 +163,32 @@ struct DropoutCfg {
   float scale;         // 1 / (1 - thresh16/65536)
   uint32_t seed_lo, seed_hi;
   uint32_t stream;     // distinguishes the dropout sites of one step (layer, op)
+  // Optional DEVICE-resident 64-bit seed (vt_set_seed_source) XORed into (seed_lo, seed_hi) by the kernel: a CUDA graph bakes
+  // every by-value argument in at capture, so a replayed step can only get a fresh dropout mask from device memory.
+  const uint32_t* seed_dev;
 };
+
+const uint32_t* seed_source();   // api.cu: the pointer set by vt_set_seed_source (null = seeds are passed by value only)
+const int32_t* row_limit();      // api.cu: the calling thread's device-resident row count {rows_padded, rows} (vt_set_row_limit) or null
+
+// every kernel that draws dropout masks calls this once on its copy of the configuration
+__device__ __forceinline__ DropoutCfg resolve_dropout(DropoutCfg d) {
+  if (d.thresh16 && d.seed_dev) {
+    d.seed_lo ^= __ldg(d.seed_dev);
+    d.seed_hi ^= __ldg(d.seed_dev + 1);
+  }
+  return d;
+}
+// rows of a launch under a device-resident row limit: min(host rows, limit[which]); which = 0 padded count, 1 true count
+__device__ __forceinline__ long long limited_rows(long long rows, const int32_t* limit, int which = 0) {
+  if (!limit) return rows;
+  const long long l = (long long)__ldg(limit + which);
+  return l < rows ? l : rows;
+}
 
 inline DropoutCfg make_dropout(float p, uint64_t seed, uint32_t stream) {
   DropoutCfg d;
+  d.seed_dev = seed_source();
   double q = p <= 0.f ? 0.0 : (double)p;
   uint32_t t = (uint32_t)(q * 65536.0 + 0.5);
   if (t > 65535u) t = 65535u;

@@ -42,6 +42,8 @@ struct GemmParams {
   long long ldaux_out;
   DropoutCfg drop;
   long long remap_in, remap_out, remap_off;
+  // device-resident row count of the A operand (vt_set_row_limit): limits M when A is [M, K], K when A is [K, M]
+  const int32_t* rows_dev;
 };
 
 template <int BN>
@@ -80,9 +82,10 @@ struct EpiK {
 // 16-byte access covers 8 rows x 64 contiguous bytes (whole 32-byte sectors) of every bf16 operand -- saved
 // pre-activation, residual, output -- instead of 32 rows x 16 bytes.  x arrives as alpha * acc.
 template <int EPI>
-__device__ __forceinline__ void epilogue_rows8(const GemmParams& p, int m, int n0, float* x, const float* bias8, const uint4& ext) {
+__device__ __forceinline__ void epilogue_rows8(const GemmParams& p, const DropoutCfg& drop, int M, int m, int n0, float* x, const float* bias8,
+                                               const uint4& ext) {
   constexpr bool G = EpiK<EPI>::generic;
-  if (m >= p.M) return;
+  if (m >= M) return;
   const int ncols = G ? min(8, p.N - n0) : 8;
   if (n0 >= p.N) return;
   long long orow = m;
@@ -146,10 +149,10 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, int m, int n
       for (int j = 0; j < 8; ++j) x[j] *= (1.0f - a[j] * a[j]);
     }
   }
-  if ((G || (EPI & EPI_DROP) != 0) && p.drop.thresh16) {
+  if ((G || (EPI & EPI_DROP) != 0) && drop.thresh16) {
     // linear index of the LOGICAL element (m, n); N % 8 == 0 is enforced on the host
     float mult[8];
-    dropout_mult8(p.drop, (uint64_t)m * (uint64_t)p.N + (uint64_t)n0, mult);
+    dropout_mult8(drop, (uint64_t)m * (uint64_t)p.N + (uint64_t)n0, mult);
 #pragma unroll
     for (int j = 0; j < 8; ++j) x[j] *= mult[j];
   }
@@ -246,8 +249,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   pdl_sync();   // the prologue above overlapped the tail of the previous kernel; global memory is touched only below
   const uint32_t tmem_base = *tmem_slot_ptr;
 
-  const int mn_tiles = p.m_blocks * p.n_blocks;
-  const int total_tiles = mn_tiles * p.splits;
+  // tile counts: the host's, or recomputed from the device-resident row count of A (sync-free steps / CUDA graphs: the number
+  // of labelled rows the pre-training heads run on is only known on the device); the grid was sized for the host's bound
+  int M = p.M, m_blocks = p.m_blocks, k_blocks = p.k_blocks, kbps = p.k_blocks_per_split, splits = p.splits;
+  if (p.rows_dev) {
+    const int lim = __ldg(p.rows_dev);
+    if (A_MN) {
+      const int K = min(p.K, lim);
+      k_blocks = (K + BK - 1) / BK;
+      kbps = (k_blocks + p.splits - 1) / p.splits;
+      splits = kbps > 0 ? (k_blocks + kbps - 1) / kbps : 0;
+    } else {
+      M = min(p.M, lim);
+      m_blocks = (M + BM - 1) / BM;
+    }
+  }
+  const int mn_tiles = m_blocks * p.n_blocks;
+  const int total_tiles = mn_tiles * splits;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -256,8 +274,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int split = t / mn_tiles, mn = t % mn_tiles;
         const int m_blk = mn / p.n_blocks, n_blk = mn % p.n_blocks;
-        const int kb0 = split * p.k_blocks_per_split;
-        const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks);
+        const int kb0 = split * kbps;
+        const int kb1 = min(kb0 + kbps, k_blocks);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           mbar_arrive_expect_tx(full_bar(stage), Cfg::STAGE_BYTES);
@@ -292,8 +310,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0, acc_phase = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int split = t / mn_tiles;
-        const int kb0 = split * p.k_blocks_per_split;
-        const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks);
+        const int kb0 = split * kbps;
+        const int kb1 = min(kb0 + kbps, k_blocks);
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
@@ -327,6 +345,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int r8 = lane >> 2, c4 = lane & 3;
     float alpha = p.alpha;
     if (p.alpha_dev) alpha *= __ldg(p.alpha_dev);
+    const DropoutCfg drop = resolve_dropout(p.drop);
     const bf16* ext_base = nullptr;
     long long ext_ld = 0;
     if (EXT) {
@@ -339,7 +358,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int m = m_blk * BM + q * 32 + r8 + 8 * i;
-        e[i] = (m < p.M && n0 < p.N) ? __ldg(reinterpret_cast<const uint4*>(ext_base + (long long)m * ext_ld + n0)) : make_uint4(0u, 0u, 0u, 0u);
+        e[i] = (m < M && n0 < p.N) ? __ldg(reinterpret_cast<const uint4*>(ext_base + (long long)m * ext_ld + n0)) : make_uint4(0u, 0u, 0u, 0u);
       }
     };
     int acc = 0;
@@ -403,7 +422,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int i = 0; i < 4; ++i) {
           float x[8] = {__uint_as_float(lo[i].x) * alpha, __uint_as_float(lo[i].y) * alpha, __uint_as_float(lo[i].z) * alpha, __uint_as_float(lo[i].w) * alpha,
                         __uint_as_float(hi[i].x) * alpha, __uint_as_float(hi[i].y) * alpha, __uint_as_float(hi[i].z) * alpha, __uint_as_float(hi[i].w) * alpha};
-          epilogue_rows8<EPI>(p, m_blk * BM + q * 32 + r8 + 8 * i, n0, x, bias8, ext[i]);
+          epilogue_rows8<EPI>(p, drop, M, m_blk * BM + q * 32 + r8 + 8 * i, n0, x, bias8, ext[i]);
         }
         if (EXT) {
 #pragma unroll
@@ -583,6 +602,7 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   p.aux_out = (bf16*)ep->aux_out; p.ldaux_out = ep->ldaux_out;
   p.drop = make_dropout(ep->dropout_p, ep->seed, ep->dropout_stream);
   p.remap_in = ep->remap_rows_in; p.remap_out = ep->remap_rows_out; p.remap_off = ep->remap_row_off;
+  p.rows_dev = row_limit();
   // 16-byte vector path: every row slice the epilogue touches must be 16-byte aligned
   const int ob = p.out_fp32 ? 4 : 2;
   bool vec = ((uintptr_t)D % 16 == 0) && ((ldd * ob) % 16 == 0);

@@ -47,11 +47,13 @@ __device__ __forceinline__ float fmaxop(float a, float b) { return fmaxf(a, b); 
 // One CTA per row.  stats[row] = {lse, lse2}: lse = logsumexp(x); double softmax: lse2 = logsumexp(softmax(x)).
 __global__ void __launch_bounds__(CE_THREADS)
 softmax_ce_fwd_kernel(const float* __restrict__ logits, long long ld, int ncols, const long long* __restrict__ labels, int double_softmax,
-                      float* __restrict__ row_loss, long long* __restrict__ argmax, float* __restrict__ stats) {
+                      float* __restrict__ row_loss, long long* __restrict__ argmax, float* __restrict__ stats,
+                      const int32_t* __restrict__ limit) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   __shared__ MaxArg s_ma[CE_THREADS / 32];
   __shared__ float s_f[CE_THREADS / 32];
   const long long row = blockIdx.x;
+  if (limit && row >= (long long)__ldg(limit + 1)) return;   // device-counted rows: only the labelled ones exist
   const float* x = logits + row * ld;
   MaxArg ma = {-INFINITY, 0x7fffffff};
   for (int j = threadIdx.x; j < ncols; j += CE_THREADS) ma = better(ma, MaxArg{x[j], j});
@@ -60,7 +62,8 @@ softmax_ce_fwd_kernel(const float* __restrict__ logits, long long ld, int ncols,
   for (int j = threadIdx.x; j < ncols; j += CE_THREADS) s += __expf(x[j] - ma.m);
   s = block_reduce<float>(s, fadd, s_f);
   const float lse = ma.m + logf(s);
-  const long long y = labels[row];
+  long long y = labels[row];
+  y = y < 0 ? 0 : (y >= ncols ? ncols - 1 : y);   // memory safety only: out-of-range labels are reported by vt_compact_labels
   float loss, lse2 = 0.f;
   if (!double_softmax) {
     loss = lse - x[y];
@@ -84,15 +87,27 @@ softmax_ce_fwd_kernel(const float* __restrict__ logits, long long ld, int ncols,
 __global__ void __launch_bounds__(CE_THREADS)
 softmax_ce_bwd_kernel(const float* __restrict__ logits, long long ld, int ncols, const long long* __restrict__ labels, int double_softmax,
                       const float* __restrict__ stats, float scale, const float* __restrict__ scale_dev, bf16* __restrict__ dlogits,
-                      long long ld_out) {
+                      long long ld_out, const int32_t* __restrict__ limit) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   __shared__ float s_f[CE_THREADS / 32];
   const long long row = blockIdx.x;
   const float* x = logits + row * ld;
   bf16* d = dlogits + row * ld_out;
+  if (limit) {
+    // device-counted rows {padded, true}: rows past the padded count do not exist; the padding rows [true, padded) are
+    // written as zeros (they are contraction rows of the weight-gradient GEMM); the mean's 1 / n comes from the device
+    const long long n_pad = __ldg(limit), n = __ldg(limit + 1);
+    if (row >= n_pad) return;
+    if (row >= n) {
+      for (int j = threadIdx.x; j < ld_out; j += CE_THREADS) d[j] = __float2bfloat16(0.f);
+      return;
+    }
+    scale /= (float)n;
+  }
   const float g = scale * (scale_dev ? __ldg(scale_dev) : 1.0f);
   const float lse = stats[2 * row], lse2 = stats[2 * row + 1];
-  const int y = (int)labels[row];
+  int y = (int)labels[row];
+  y = y < 0 ? 0 : (y >= ncols ? ncols - 1 : y);
   if (!double_softmax) {
     for (int j = threadIdx.x; j < ld_out; j += CE_THREADS) {
       float v = 0.f;
@@ -231,9 +246,15 @@ __global__ void __launch_bounds__(256)
 pretrain_finalize_kernel(const float* __restrict__ mlm_loss, const long long* __restrict__ mlm_arg, const long long* __restrict__ mlm_lab, long long n_mlm,
                          const float* __restrict__ tok_loss, const long long* __restrict__ tok_arg, const long long* __restrict__ tok_lab, long long n_tok,
                          const float* __restrict__ act_loss, const long long* __restrict__ act_arg, const long long* __restrict__ act_lab, long long n_act,
-                         float* __restrict__ out) {
+                         const int32_t* __restrict__ counts, float* __restrict__ out) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   __shared__ float sf[8];
+  bool bad = false;
+  if (counts) {   // vt_compact_labels' {mlm padded, mlm, mlm out of range, -, token padded, token, token out of range, -}
+    n_mlm = counts[1];
+    n_tok = counts[5];
+    bad = counts[2] != 0 || counts[6] != 0;
+  }
   float a = 0.f, c = 0.f;
   for (long long i = threadIdx.x; i < n_mlm; i += blockDim.x) { a += mlm_loss[i]; c += (mlm_arg[i] == mlm_lab[i]) ? 1.f : 0.f; }
   const float mlm_sum = block_reduce<float>(a, fadd, sf), mlm_ok = block_reduce<float>(c, fadd, sf);
@@ -255,7 +276,8 @@ pretrain_finalize_kernel(const float* __restrict__ mlm_loss, const long long* __
     // n_act == 0: next_action was None -> next_loss = 0, action_accuracy = 0 (vs/encoder.py:393-395,412-418);
     // labels given but all ignored -> 0/0 = nan like CrossEntropyLoss
     const float next_loss = n_act > 0 ? act_sum / act_valid : 0.f;
-    out[0] = mask_loss + next_loss + token_loss;
+    // a label outside [0, classes) makes torch's CrossEntropyLoss raise a device assert; here the loss turns NaN (loud, no sync)
+    out[0] = bad ? __int_as_float(0x7fc00000) : mask_loss + next_loss + token_loss;
     out[1] = mask_loss;
     out[2] = next_loss;
     out[3] = token_loss;
@@ -266,6 +288,82 @@ pretrain_finalize_kernel(const float* __restrict__ mlm_loss, const long long* __
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Labelled-row compaction on the device (replaces torch.nonzero + fancy indexing, whose size-dependent output forced a
+// host <-> device sync at the top of every step).  One CTA per label array: each thread counts a contiguous chunk, a block
+// scan gives its offset, the labelled rows are written in ascending row order (the order torch.nonzero gives, so every
+// downstream sum keeps its order).  counts[4 a ..] = {n rounded up to 128 (capped), n, labels outside [0, classes), 0};
+// the padding rows [n, padded) get idx = -1 / label = 0.
+// ---------------------------------------------------------------------------------------------
+struct CompactArgs {
+  const long long* labels[2];
+  long long* idx[2];
+  long long* lab[2];
+  long long classes[2];
+};
+__global__ void __launch_bounds__(1024)
+compact_labels_kernel(CompactArgs a, long long n, long long ignore, long long cap, int32_t* __restrict__ counts) {
+  pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
+  __shared__ int s_warp[32];
+  __shared__ int s_bad;
+  const int w = blockIdx.x;
+  const long long* lab = a.labels[w];
+  if (!lab) {
+    if (threadIdx.x < 4) counts[4 * w + threadIdx.x] = 0;
+    return;
+  }
+  if (threadIdx.x == 0) s_bad = 0;
+  const long long per = (n + blockDim.x - 1) / blockDim.x;
+  const long long i0 = min(n, per * threadIdx.x), i1 = min(n, i0 + per);
+  int cnt = 0, bad = 0;
+  for (long long i = i0; i < i1; ++i) {
+    const long long y = lab[i];
+    if (y != ignore) {
+      ++cnt;
+      if (y < 0 || y >= a.classes[w]) ++bad;
+    }
+  }
+  // block-wide exclusive scan of cnt
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int inc = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    int v = lane < (int)(blockDim.x >> 5) ? s_warp[lane] : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += t;
+    }
+    s_warp[lane] = v;   // inclusive over warps
+  }
+  if (bad) atomicAdd(&s_bad, bad);
+  __syncthreads();
+  const int total = s_warp[(blockDim.x >> 5) - 1];
+  long long pos = (long long)(inc - cnt) + (warp ? s_warp[warp - 1] : 0);
+  for (long long i = i0; i < i1; ++i) {
+    const long long y = lab[i];
+    if (y != ignore) {
+      if (pos < cap) { a.idx[w][pos] = i; a.lab[w][pos] = y; }
+      ++pos;
+    }
+  }
+  const long long n_lab = min((long long)total, cap);
+  const long long n_pad = min(cap, (n_lab + 127) / 128 * 128);
+  for (long long r = n_lab + threadIdx.x; r < n_pad; r += blockDim.x) { a.idx[w][r] = -1; a.lab[w][r] = 0; }
+  if (threadIdx.x == 0) {
+    counts[4 * w] = (int32_t)n_pad;
+    counts[4 * w + 1] = (int32_t)n_lab;
+    counts[4 * w + 2] = s_bad + (total > cap ? 1 : 0);
+    counts[4 * w + 3] = 0;
+  }
+}
+
 __global__ void tanh_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, long long n, bf16* __restrict__ dx) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -273,8 +371,10 @@ __global__ void tanh_bwd_kernel(const float* __restrict__ dy, const float* __res
 }
 
 // dx = dy * gelu'(pre)   (backward of the MLM transform's activation, hf/modeling_bert.py:480-485)
-__global__ void gelu_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ pre, long long n8, bf16* __restrict__ dx) {
+__global__ void gelu_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ pre, long long n8, bf16* __restrict__ dx,
+                                long long row8, const int32_t* __restrict__ limit) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
+  if (limit) n8 = min(n8, (long long)__ldg(limit) * row8);   // row8 = 16-byte chunks per row
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
     float d[8], x[8];
     unpack8(__ldg(reinterpret_cast<const uint4*>(dy) + i), d);
@@ -319,7 +419,7 @@ extern "C" int vt_softmax_ce_fwd(const float* logits, int64_t ld, int64_t rows, 
   VT_REQUIRE(rows >= 0 && ncols > 0 && ncols < (1ll << 31) && ld >= ncols, "vt_softmax_ce_fwd: bad sizes");
   if (rows == 0) return VT_OK;
   launch_pdl(softmax_ce_fwd_kernel, (unsigned)rows, CE_THREADS, 0, (cudaStream_t)stream, logits, ld, (int)ncols, (const long long*)labels, double_softmax,
-                                                                                 row_loss, (long long*)argmax, stats);
+                                                                                 row_loss, (long long*)argmax, stats, row_limit());
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -330,7 +430,7 @@ extern "C" int vt_softmax_ce_bwd(const float* logits, int64_t ld, int64_t rows, 
   VT_REQUIRE(rows >= 0 && ncols > 0 && ld >= ncols && ld_out >= ncols, "vt_softmax_ce_bwd: bad sizes");
   if (rows == 0) return VT_OK;
   launch_pdl(softmax_ce_bwd_kernel, (unsigned)rows, CE_THREADS, 0, (cudaStream_t)stream, logits, ld, (int)ncols, (const long long*)labels, double_softmax,
-                                                                                 stats, scale, scale_dev, (bf16*)dlogits, ld_out);
+                                                                                 stats, scale, scale_dev, (bf16*)dlogits, ld_out, row_limit());
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -362,12 +462,40 @@ extern "C" int vt_action_head_bwd(const float* pooled, const float* W, int64_t B
   return VT_OK;
 }
 
+static int finalize(const float* mlm_loss, const int64_t* mlm_arg, const int64_t* mlm_lab, int64_t n_mlm, const float* tok_loss,
+                    const int64_t* tok_arg, const int64_t* tok_lab, int64_t n_tok, const float* act_loss, const int64_t* act_arg,
+                    const int64_t* act_lab, int64_t n_act, const int32_t* counts, float* out8, vt_stream stream) {
+  launch_pdl(pretrain_finalize_kernel, 1, 256, 0, (cudaStream_t)stream, mlm_loss, (const long long*)mlm_arg, (const long long*)mlm_lab, (long long)n_mlm, tok_loss,
+                                                               (const long long*)tok_arg, (const long long*)tok_lab, (long long)n_tok, act_loss,
+                                                               (const long long*)act_arg, (const long long*)act_lab, (long long)n_act, counts, out8);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
 extern "C" int vt_pretrain_finalize(const float* mlm_loss, const int64_t* mlm_arg, const int64_t* mlm_lab, int64_t n_mlm, const float* tok_loss,
                                     const int64_t* tok_arg, const int64_t* tok_lab, int64_t n_tok, const float* act_loss, const int64_t* act_arg,
                                     const int64_t* act_lab, int64_t n_act, float* out8, vt_stream stream) {
-  launch_pdl(pretrain_finalize_kernel, 1, 256, 0, (cudaStream_t)stream, mlm_loss, (const long long*)mlm_arg, (const long long*)mlm_lab, n_mlm, tok_loss,
-                                                               (const long long*)tok_arg, (const long long*)tok_lab, n_tok, act_loss,
-                                                               (const long long*)act_arg, (const long long*)act_lab, n_act, out8);
+  return finalize(mlm_loss, mlm_arg, mlm_lab, n_mlm, tok_loss, tok_arg, tok_lab, n_tok, act_loss, act_arg, act_lab, n_act, nullptr, out8, stream);
+}
+
+extern "C" int vt_pretrain_finalize_counted(const float* mlm_loss, const int64_t* mlm_arg, const int64_t* mlm_lab, const float* tok_loss,
+                                            const int64_t* tok_arg, const int64_t* tok_lab, const float* act_loss, const int64_t* act_arg,
+                                            const int64_t* act_lab, int64_t n_act, const int32_t* counts, float* out8, vt_stream stream) {
+  VT_REQUIRE(counts, "vt_pretrain_finalize_counted: counts (vt_compact_labels) required");
+  return finalize(mlm_loss, mlm_arg, mlm_lab, 0, tok_loss, tok_arg, tok_lab, 0, act_loss, act_arg, act_lab, n_act, counts, out8, stream);
+}
+
+extern "C" int vt_compact_labels(const int64_t* labels_a, int64_t classes_a, const int64_t* labels_b, int64_t classes_b, int64_t n, int64_t ignore_index,
+                                 int64_t capacity, int64_t* idx_a, int64_t* lab_a, int64_t* idx_b, int64_t* lab_b, int32_t* counts, vt_stream stream) {
+  VT_REQUIRE(counts && n >= 0 && n < (1ll << 31) && capacity > 0 && capacity % 128 == 0, "vt_compact_labels: counts required, capacity a positive multiple of 128");
+  VT_REQUIRE((!labels_a || (idx_a && lab_a)) && (!labels_b || (idx_b && lab_b)), "vt_compact_labels: output arrays required for every label array");
+  CompactArgs a;
+  a.labels[0] = (const long long*)labels_a; a.labels[1] = (const long long*)labels_b;
+  a.idx[0] = (long long*)idx_a; a.idx[1] = (long long*)idx_b;
+  a.lab[0] = (long long*)lab_a; a.lab[1] = (long long*)lab_b;
+  a.classes[0] = classes_a; a.classes[1] = classes_b;
+  launch_pdl(compact_labels_kernel, 2, 1024, 0, (cudaStream_t)stream, a, (long long)n, (long long)ignore_index, (long long)capacity, counts);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -385,7 +513,7 @@ extern "C" int vt_gelu_bwd(const void* dy, const void* pre, int64_t n, void* dx,
   VT_REQUIRE(n % 8 == 0 && ((uintptr_t)dy & 15) == 0 && ((uintptr_t)pre & 15) == 0 && ((uintptr_t)dx & 15) == 0, "vt_gelu_bwd: n %% 8 == 0 and 16-byte alignment required");
   if (n == 0) return VT_OK;
   long long n8 = n / 8, g = (n8 + 255) / 256, cap = (long long)num_sms() * 16;
-  launch_pdl(gelu_bwd_kernel, (unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream, (const bf16*)dy, (const bf16*)pre, n8, (bf16*)dx);
+  launch_pdl(gelu_bwd_kernel, (unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream, (const bf16*)dy, (const bf16*)pre, n8, (bf16*)dx, (long long)(768 / 8), row_limit());
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;

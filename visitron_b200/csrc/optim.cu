@@ -20,6 +20,7 @@ struct OptSeg {        // mirrors vt_opt_segment
   float* g;
   float* m;
   float* v;
+  bf16* p_bf16;        // optional bf16 shadow of p (the tensor-core operand): written in the same pass, so no cast launch follows
   long long n;
   int group;
   int first_chunk;     // prefix sum of ceil(n / OPT_CHUNK)
@@ -61,7 +62,8 @@ adamw_kernel(const OptSeg* __restrict__ segs, int n_segs, AdamGroups gr, AdamHyp
   const float step = gr.step_size[s.group], lrd = gr.lr_decay[s.group];
   const float gs = gscale ? *gscale : 1.0f;   // clip coefficient of vt_clip_coef (1 when the norm is below the bound)
   float* p = s.p + off; const float* g = s.g + off; float* m = s.m + off; float* v = s.v + off;
-  const bool vec = (((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0;
+  bf16* pb = s.p_bf16 ? s.p_bf16 + off : nullptr;
+  const bool vec = (((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0 && ((uintptr_t)pb & 7) == 0;
   if (vec && n == OPT_CHUNK) {
     // full chunk: 8 float4 per thread in batches of 4, so that 16 independent 16-byte loads are in flight per thread
 #pragma unroll
@@ -81,6 +83,7 @@ adamw_kernel(const OptSeg* __restrict__ segs, int n_segs, AdamGroups gr, AdamHyp
         adamw_one(pv[u].z, gv[u].z * gs, mv[u].z, vv[u].z, hp, step, lrd);
         adamw_one(pv[u].w, gv[u].w * gs, mv[u].w, vv[u].w, hp, step, lrd);
         reinterpret_cast<float4*>(p)[i] = pv[u]; reinterpret_cast<float4*>(m)[i] = mv[u]; reinterpret_cast<float4*>(v)[i] = vv[u];
+        if (pb) reinterpret_cast<uint2*>(pb)[i] = make_uint2(pack_bf16(pv[u].x, pv[u].y), pack_bf16(pv[u].z, pv[u].w));
       }
     }
   } else if (vec) {
@@ -93,10 +96,17 @@ adamw_kernel(const OptSeg* __restrict__ segs, int n_segs, AdamGroups gr, AdamHyp
       adamw_one(pv.z, gv.z * gs, mv.z, vv.z, hp, step, lrd);
       adamw_one(pv.w, gv.w * gs, mv.w, vv.w, hp, step, lrd);
       reinterpret_cast<float4*>(p)[i] = pv; reinterpret_cast<float4*>(m)[i] = mv; reinterpret_cast<float4*>(v)[i] = vv;
+      if (pb) reinterpret_cast<uint2*>(pb)[i] = make_uint2(pack_bf16(pv.x, pv.y), pack_bf16(pv.z, pv.w));
     }
-    for (long long i = (n4 << 2) + threadIdx.x; i < n; i += OPT_THREADS) adamw_one(p[i], g[i] * gs, m[i], v[i], hp, step, lrd);
+    for (long long i = (n4 << 2) + threadIdx.x; i < n; i += OPT_THREADS) {
+      adamw_one(p[i], g[i] * gs, m[i], v[i], hp, step, lrd);
+      if (pb) pb[i] = __float2bfloat16(p[i]);
+    }
   } else {
-    for (long long i = threadIdx.x; i < n; i += OPT_THREADS) adamw_one(p[i], g[i] * gs, m[i], v[i], hp, step, lrd);
+    for (long long i = threadIdx.x; i < n; i += OPT_THREADS) {
+      adamw_one(p[i], g[i] * gs, m[i], v[i], hp, step, lrd);
+      if (pb) pb[i] = __float2bfloat16(p[i]);
+    }
   }
 }
 

@@ -120,8 +120,10 @@ __device__ __forceinline__ void flush_partials(float (*acc)[CH][8], float* part,
 __global__ void __launch_bounds__(ROW_WARPS * 32)
 ln_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict__ gamma, const float* __restrict__ beta,
               float eps, long long rows, bf16* __restrict__ y, long long ldy, DropoutCfg drop, long long rin, long long rout,
-              long long roff) {
+              long long roff, const int32_t* __restrict__ limit) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
+  drop = resolve_dropout(drop);
+  rows = limited_rows(rows, limit);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float g[CH][8], b[CH][8];
   load_vec_f32(gamma, lane, g);
@@ -167,8 +169,11 @@ __global__ void __launch_bounds__(ROW_WARPS * 32, 1)
 ln_bwd_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restrict__ x, long long ldx,
               const float* __restrict__ gamma, float eps, long long rows, bf16* __restrict__ dx, long long lddx,
               bf16* __restrict__ dxd, long long lddxd, float* __restrict__ partials, DropoutCfg drop_in, DropoutCfg drop_out,
-              long long rin, long long rout, long long roff) {
+              long long rin, long long rout, long long roff, const int32_t* __restrict__ limit) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
+  drop_in = resolve_dropout(drop_in);
+  drop_out = resolve_dropout(drop_out);
+  rows = limited_rows(rows, limit);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float g[CH][8];
   load_vec_f32(gamma, lane, g);
@@ -249,6 +254,7 @@ embed_ln_fwd_kernel(const long long* __restrict__ ids, const long long* __restri
                     const float* __restrict__ gamma, const float* __restrict__ beta, float eps, long long batch, long long T,
                     long long S_out, bf16* __restrict__ y, DropoutCfg drop) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
+  drop = resolve_dropout(drop);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float g[CH][8], b[CH][8];
   load_vec_f32(gamma, lane, g);
@@ -291,6 +297,7 @@ embed_ln_bwd_kernel(const bf16* __restrict__ dy, const long long* __restrict__ i
                     long long S_out, float* __restrict__ dword, float* __restrict__ dpos, float* __restrict__ dtype,
                     float* __restrict__ partials, DropoutCfg drop) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
+  drop = resolve_dropout(drop);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float g[CH][8];
   load_vec_f32(gamma, lane, g);
@@ -404,8 +411,10 @@ static inline dim3 reduce_grid(long long ncols, long long nrows, int accumulate)
 
 // column sums of a bf16 matrix [rows, ncols] (ncols % 8 == 0): part[blockIdx.y][col]
 __global__ void __launch_bounds__(256)
-colsum_partial_kernel(const bf16* __restrict__ x, long long ldx, long long rows, long long ncols, float* __restrict__ part) {
+colsum_partial_kernel(const bf16* __restrict__ x, long long ldx, long long rows, long long ncols, float* __restrict__ part,
+                      const int32_t* __restrict__ limit) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
+  rows = limited_rows(rows, limit);
   const long long col = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8;
   if (col >= ncols) return;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -468,6 +477,7 @@ __global__ void __launch_bounds__(ROW_WARPS * 32)
 dropout_rows_kernel(const bf16* __restrict__ x, long long ldx, long long rows, bf16* __restrict__ y, long long ldy, DropoutCfg drop,
                     long long rin, long long rout, long long roff) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
+  drop = resolve_dropout(drop);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (long long m = (long long)blockIdx.x * ROW_WARPS + warp; m < rows; m += (long long)gridDim.x * ROW_WARPS) {
     float v[CH][8];
@@ -477,23 +487,31 @@ dropout_rows_kernel(const bf16* __restrict__ x, long long ldx, long long rows, b
   }
 }
 
-// dst[r] = src[idx[r]]   /  dst[idx[r]] += src[r]      (768-wide bf16 rows; idx rows are unique)
+// dst[r] = src[idx[r]]   /  dst[idx[r]] += src[r]      (768-wide bf16 rows; idx rows are unique; idx < 0 = a padding row of a
+// device-counted compaction (vt_compact_labels): gathered as zeros, skipped by the scatter)
 __global__ void __launch_bounds__(ROW_WARPS * 32)
-gather_rows_kernel(const bf16* __restrict__ src, long long lds, const long long* __restrict__ idx, long long n, bf16* __restrict__ dst, long long ldd) {
+gather_rows_kernel(const bf16* __restrict__ src, long long lds, const long long* __restrict__ idx, long long n, bf16* __restrict__ dst, long long ldd,
+                   const int32_t* __restrict__ limit) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
+  n = limited_rows(n, limit);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (long long r = (long long)blockIdx.x * ROW_WARPS + warp; r < n; r += (long long)gridDim.x * ROW_WARPS) {
-    const bf16* s = src + idx[r] * lds;
+    const long long i = idx[r];
+    const bf16* s = src + i * lds;
     bf16* d = dst + r * ldd;
 #pragma unroll
-    for (int c = 0; c < CH; ++c) *reinterpret_cast<uint4*>(d + chunk_col(lane, c)) = __ldg(reinterpret_cast<const uint4*>(s + chunk_col(lane, c)));
+    for (int c = 0; c < CH; ++c)
+      *reinterpret_cast<uint4*>(d + chunk_col(lane, c)) = i >= 0 ? __ldg(reinterpret_cast<const uint4*>(s + chunk_col(lane, c))) : make_uint4(0u, 0u, 0u, 0u);
   }
 }
 __global__ void __launch_bounds__(ROW_WARPS * 32)
-scatter_add_rows_kernel(const bf16* __restrict__ src, long long lds, const long long* __restrict__ idx, long long n, bf16* __restrict__ dst, long long ldd) {
+scatter_add_rows_kernel(const bf16* __restrict__ src, long long lds, const long long* __restrict__ idx, long long n, bf16* __restrict__ dst, long long ldd,
+                        const int32_t* __restrict__ limit) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
+  n = limited_rows(n, limit);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (long long r = (long long)blockIdx.x * ROW_WARPS + warp; r < n; r += (long long)gridDim.x * ROW_WARPS) {
+    if (idx[r] < 0) continue;
     float a[CH][8], b[CH][8];
     load_row_bf16(src + r * lds, lane, a);
     bf16* d = dst + idx[r] * ldd;
@@ -519,7 +537,7 @@ extern "C" int vt_layernorm_fwd(const void* x, int64_t ldx, const float* gamma, 
   VT_REQUIRE(aligned16(x) && aligned16(y) && aligned16(gamma) && aligned16(beta) && ldx % 8 == 0 && ldy % 8 == 0, "vt_layernorm_fwd: 16-byte alignment required");
   if (rows == 0) return VT_OK;
   launch_pdl(ln_fwd_kernel, row_grid(rows), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const bf16*)x, ldx, gamma, beta, eps, rows, (bf16*)y, ldy, make_dropout(dropout_p, seed, dropout_stream), remap_rows_in,
-      remap_rows_out, remap_row_off);
+      remap_rows_out, remap_row_off, row_limit());
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -541,7 +559,7 @@ extern "C" int vt_layernorm_bwd(const void* dy, int64_t lddy, const void* x, int
   launch_pdl(ln_bwd_kernel, grid, ROW_WARPS * 32, 0, st, (const bf16*)dy, lddy, (const bf16*)x, ldx, gamma, eps, rows, (bf16*)dx, lddx,
                                                  (bf16*)dx_dropped, lddxd, partials, make_dropout(in_dropout_p, seed, in_dropout_stream),
                                                  make_dropout(out_dropout_p, seed, out_dropout_stream), remap_rows_in, remap_rows_out,
-                                                 remap_row_off);
+                                                 remap_row_off, row_limit());
   count_launch(1);
   VT_CHECK_LAUNCH();
   // second stage: accumulate into the fp32 gradient buffers
@@ -606,7 +624,7 @@ extern "C" int vt_colsum_bf16(const void* x, int64_t ldx, int64_t rows, int64_t 
   const int gy = (int)vt_colsum_partials_rows(rows);
   const int threads = 128;
   const int gx = (int)((npad / 8 + threads - 1) / threads);
-  launch_pdl(colsum_partial_kernel, dim3(gx, gy), threads, 0, st, (const bf16*)x, ldx, rows, npad, partials);
+  launch_pdl(colsum_partial_kernel, dim3(gx, gy), threads, 0, st, (const bf16*)x, ldx, rows, npad, partials, row_limit());
   launch_pdl(reduce_partials_kernel, reduce_grid(ncols, gy, accumulate), dim3(32, 8), 0, st, partials, gy, npad, ncols, out, accumulate);
   count_launch(2);
   VT_CHECK_LAUNCH();
@@ -661,7 +679,7 @@ extern "C" int vt_gather_rows(const void* src, int64_t lds, const int64_t* idx, 
                               vt_stream stream) {
   VT_REQUIRE(hidden == H && lds % 8 == 0 && ldd % 8 == 0 && aligned16(src) && aligned16(dst), "vt_gather_rows: bad arguments");
   if (n == 0) return VT_OK;
-  launch_pdl(gather_rows_kernel, row_grid(n), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const bf16*)src, lds, (const long long*)idx, n, (bf16*)dst, ldd);
+  launch_pdl(gather_rows_kernel, row_grid(n), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const bf16*)src, lds, (const long long*)idx, n, (bf16*)dst, ldd, row_limit());
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -671,7 +689,7 @@ extern "C" int vt_scatter_add_rows(const void* src, int64_t lds, const int64_t* 
                                    vt_stream stream) {
   VT_REQUIRE(hidden == H && lds % 8 == 0 && ldd % 8 == 0 && aligned16(src) && aligned16(dst), "vt_scatter_add_rows: bad arguments");
   if (n == 0) return VT_OK;
-  launch_pdl(scatter_add_rows_kernel, row_grid(n), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const bf16*)src, lds, (const long long*)idx, n, (bf16*)dst, ldd);
+  launch_pdl(scatter_add_rows_kernel, row_grid(n), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const bf16*)src, lds, (const long long*)idx, n, (bf16*)dst, ldd, row_limit());
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;

@@ -202,15 +202,23 @@ class BertPreTrainedModel(PreTrainedModel):
 # ------------------------------------------------------------------------------------------------
 class _Step:
     __slots__ = ("B", "T", "R", "S", "M", "seed", "p_hidden", "p_attn", "ids", "tt", "pos", "bias", "key_tiles", "has_img",
-                 "img_cat", "img_pre", "layers", "seq", "pooled", "began", "model", "need_grad")
+                 "img_cat", "img_pre", "layers", "seq", "pooled", "began", "model", "need_grad", "hidden")
 
     def __init__(self):
         self.layers = []
         self.img_cat = self.img_pre = None
         self.began = False
+        self.hidden = None
+
+
+# Set by visitron_b200.graph while a step is being captured: the dropout seed then lives in device memory (ops.set_seed_source)
+# and is advanced by the first node of the graph; the by-value seed of every launch is a constant.
+_CAPTURING = False
 
 
 def _draw_seed() -> int:
+    if _CAPTURING:
+        return 0x5EED
     # CPU generator: reproducible under torch.manual_seed (vs/utils.py:24-29), no device sync
     s = int(torch.randint(0, 2 ** 62, (1,)).item())
     if torch.distributed.is_available() and torch.distributed.is_initialized():
@@ -302,16 +310,18 @@ class BertImgModelwithLocationEmbeds(BertPreTrainedModel):
         """[W_loc | W_img | 0] as one bf16 [768, Kp] operand and b_img + b_loc: img_embedding(x) +
         location_embeds(l) (vs/encoder.py:277-279) is ONE contraction over the concatenated input
         (the 128 location columns come first so that both column blocks start 16-byte aligned)."""
-        wi, wl = self.img_embedding.weight, self.location_embeds.weight
-        bi, bl = self.img_embedding.bias, self.location_embeds.bias
-        vers = (wi._version, wl._version, bi._version, bl._version, st.flat.data_ptr())
-        if self._vt_img_cache is None or self._vt_img_cache[0] != vers:
+        # re-cast at EVERY forward (two small launches + one add): like FlatStore.refresh_bf16, nothing the host can observe
+        # proves that the masters did not change since the last call (in-place updates through p.data)
+        key = (st.flat.data_ptr(), self.img_dim)
+        if self._vt_img_cache is None or self._vt_img_cache[0] != key:
             kp = ops.roundup(self.img_dim + LOC_DIM, 8)
             w = torch.zeros((H, kp), dtype=BF16, device=st.flat.device)
-            ops.cast_weight(st.w("location_embeds.weight"), w[:, :LOC_DIM])
-            ops.cast_weight(st.w("img_embedding.weight"), w[:, LOC_DIM: LOC_DIM + self.img_dim])
-            b = (bi.detach() + bl.detach()).contiguous()
-            self._vt_img_cache = (vers, w, b, kp)
+            b = torch.empty(H, dtype=F32, device=st.flat.device)
+            self._vt_img_cache = (key, w, b, kp)
+        _, w, b, kp = self._vt_img_cache
+        ops.cast_weight(st.w("location_embeds.weight"), w[:, :LOC_DIM])
+        ops.cast_weight(st.w("img_embedding.weight"), w[:, LOC_DIM: LOC_DIM + self.img_dim])
+        torch.add(st.w("img_embedding.bias"), st.w("location_embeds.bias"), out=b)
         return self._vt_img_cache[1:]
 
     # -- forward ---------------------------------------------------------------------------------
@@ -320,6 +330,11 @@ class BertImgModelwithLocationEmbeds(BertPreTrainedModel):
         seq, pooled, step = self._vt_forward(input_ids, token_type_ids, attention_mask, position_ids, head_mask,
                                              img_feats, img_location_embeddings, encoder_history_states)
         sequence_output = _ToF32.apply(seq).view(step.B, step.S, H)
+        if step.hidden is not None:
+            # config.output_hidden_states (oscar/modeling_bert.py:146-160): the embedding output and every layer's output, which the
+            # fused path holds anyway; returned as fp32 COPIES outside the autograd graph (gradients flow through sequence_output)
+            hs = tuple(ops.to_f32(h).view(step.B, step.S, H) for h in step.hidden[:-1]) + (sequence_output.detach(),)
+            return (sequence_output, pooled, hs)
         return (sequence_output, pooled)
 
     def _vt_forward(self, input_ids, token_type_ids=None, attention_mask=None, position_ids=None, head_mask=None,
@@ -331,8 +346,9 @@ class BertImgModelwithLocationEmbeds(BertPreTrainedModel):
         if encoder_history_states:
             assert img_feats is None, "Cannot take image features while using encoder history states"
             raise NotImplementedError("encoder_history_states is not supported (no reference caller passes it)")
-        if getattr(cfg, "output_hidden_states", False) or getattr(cfg, "output_attentions", False):
-            raise NotImplementedError("output_hidden_states / output_attentions are not supported on the fused path")
+        if getattr(cfg, "output_attentions", False):
+            raise NotImplementedError("output_attentions would materialise the S x S probabilities the fused attention kernel never "
+                                      "writes (no reference caller sets it)")
         lib.require_device(input_ids)
         if input_ids.dim() != 2:
             raise ValueError("input_ids must be [batch, text_len]")
@@ -372,6 +388,8 @@ class BertImgModelwithLocationEmbeds(BertPreTrainedModel):
         store = self._store()
         store.refresh_bf16()
         step.need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in store.params)
+        if getattr(cfg, "output_hidden_states", False):
+            step.hidden = []
         imgs = []
         if step.has_img:
             # fp32 as the loader delivers them, or bf16 from a feature cache (read as it is: half the H2D bytes, no fp32 detour)
@@ -424,6 +442,8 @@ def _encoder_forward(step: _Step, st: FlatStore, img_feats, img_loc):
         step.img_cat = cat if save else None
     for l in range(cfg.num_hidden_layers):
         p = "encoder.layer.%d." % l
+        if step.hidden is not None:
+            step.hidden.append(x)
         qkv = lib.gemm(x, st.wb(p + "attention.self.query.weight", 3 * H, H), bias=st.wspan(p + "attention.self.query.bias", 3 * H))
         ctx, lse = ops.attention_fwd(qkv, step.bias, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles)
         x1 = lib.gemm(ctx, st.wb(p + "attention.output.dense.weight"), bias=st.w(p + "attention.output.dense.bias"),
@@ -440,6 +460,8 @@ def _encoder_forward(step: _Step, st: FlatStore, img_feats, img_loc):
         if save:
             step.layers.append((x, qkv, ctx, lse, x1, y1, pre, z, x2))
         x = y2
+    if step.hidden is not None:
+        step.hidden.append(x)
     pooled = lib.gemm(x[::S], st.wb("pooler.dense.weight"), bias=st.w("pooler.dense.bias"), act=ACT_TANH, out_dtype=F32)
     step.seq, step.pooled = x, pooled
     return x, pooled
@@ -571,7 +593,9 @@ class PreTrainOscar(BertPreTrainedModel):
         self.apply(self.init_weights)
         self.tie_weights()
         self._vt_store: Optional[FlatStore] = None
+        self._vt_store_key = None
         self._vt_reducer = None
+        self._vt_aux_raw = None
 
     def tie_weights(self):
         self._tie_or_clone_weights(self.mlmhead.predictions.decoder, self.bert.embeddings.word_embeddings)
@@ -586,7 +610,10 @@ class PreTrainOscar(BertPreTrainedModel):
         self._vt_reducer = reducer
 
     def _store(self) -> FlatStore:
-        if self._vt_store is None:
+        dec = self.mlmhead.predictions.decoder.weight
+        tied = dec is self.bert.embeddings.word_embeddings.weight
+        key = (tied, id(dec), tuple(dec.shape))
+        if self._vt_store is None or self._vt_store_key != key:
             t = self.mlmhead.predictions.transform
             named = [("mlmhead.predictions.transform.dense.weight", t.dense.weight), ("mlmhead.predictions.transform.dense.bias", t.dense.bias),
                      ("mlmhead.predictions.transform.LayerNorm.weight", t.LayerNorm.weight),
@@ -594,7 +621,12 @@ class PreTrainOscar(BertPreTrainedModel):
                      ("mlmhead.predictions.bias", self.mlmhead.predictions.bias),
                      ("token_head.0.weight", self.token_head[0].weight), ("token_head.0.bias", self.token_head[0].bias),
                      ("next_action.linear.weight", self.next_action.linear.weight), ("next_action.linear.bias", self.next_action.linear.bias)]
+            if not tied:
+                # after resize_embeddings (vs/model_utils.py:101-109, `--no_oscar_setting`) the decoder keeps pointing at the OLD
+                # [30522, 768] table (vs/encoder.py:337-345 does not re-tie): it is then a parameter of its own, trained as one
+                named.append(("mlmhead.predictions.decoder.weight", dec))
             self._vt_store = FlatStore(named)
+            self._vt_store_key = key
         return self._vt_store.ensure()
 
     def forward(self, input_ids, token_type_ids=None, attention_mask=None, labels=None, token_labels=None, position_ids=None,
@@ -609,78 +641,94 @@ class PreTrainOscar(BertPreTrainedModel):
         lib.require_device(input_ids)
         dec = self.mlmhead.predictions.decoder.weight
         V = dec.size(0)
-        if dec is not self.bert.embeddings.word_embeddings.weight:
-            raise NotImplementedError("the MLM decoder is no longer tied to the word embeddings (resize_embeddings does not "
-                                      "re-tie, vs/encoder.py:337-345); the fused MLM head needs the tied weight")
-        # labelled rows first: the only host<->device sync of the step, issued while the stream is idle
-        lab = labels.reshape(-1)
-        tok = token_labels.reshape(-1)
-        idx_mlm = torch.nonzero(lab != -1).squeeze(1)
-        idx_tok = torch.nonzero(tok != -1).squeeze(1)
-        lab_mlm = lab[idx_mlm].contiguous()
-        lab_tok = tok[idx_tok].contiguous()
+        if self.mlmhead.predictions.bias.numel() != V:
+            raise ValueError("mlmhead.predictions.bias has %d entries for a decoder of %d rows" % (self.mlmhead.predictions.bias.numel(), V))
+        lab = labels.reshape(-1).contiguous().long()
+        tok = token_labels.reshape(-1).contiguous().long()
         seq, pooled, step = self.bert._vt_forward(input_ids, token_type_ids, attention_mask, position_ids, head_mask,
                                                   img_feats, img_location_embeddings)
-        if lab.numel() != step.M:
+        if lab.numel() != step.M or tok.numel() != step.M:
             raise ValueError("labels / token_labels must be [batch, text_len + regions]")
         hs = self._store()
         hs.refresh_bf16()
         na = None if next_action is None else next_action.contiguous().long()
-        out8 = _HeadsFn.apply(self, step, hs, (idx_mlm, lab_mlm, idx_tok, lab_tok, na, V), seq, pooled, *hs.params)
+        # the heads save their activations whenever ANY gradient can flow: a frozen encoder with trainable heads included
+        save = torch.is_grad_enabled() and (step.need_grad or any(p.requires_grad for p in hs.params))
+        out8 = _HeadsFn.apply(self, step, hs, (lab, tok, na, V, save), seq, pooled, *hs.params)
         return (out8[0], out8[1], out8[2], out8[3], out8[4], out8[5], out8[6])
+
+    @property
+    def _vt_last_aux(self):
+        """Head outputs of the last forward, cut to the labelled rows (test / debugging accessor: reads the row counts, i.e. SYNCS)."""
+        raw = self._vt_aux_raw
+        c = raw["counts"].cpu()
+        n, nt = int(c[1]), int(c[5])
+        return dict(predicted_words=raw["predicted_words"][:n], predicted_tokens=raw["predicted_tokens"][:nt],
+                    predicted_action=raw["predicted_action"], action_scores=raw["action_scores"],
+                    mlm_logits=raw["mlm_logits"][:n], token_logits=raw["token_logits"][:nt],
+                    mlm_rows=raw["idx_mlm"][:n], token_rows=raw["idx_tok"][:nt], label_errors=int(c[2]) + int(c[6]))
 
 
 class _HeadsFn(torch.autograd.Function):
+    """The three pre-training heads and the loss assembly (vs/encoder.py:377-441) on the LABELLED rows only.  Which rows those
+    are is decided on the device (ops.compact_labels); every buffer is sized for the bound (all M rows, rounded up to 128)
+    and every launch clips itself to the device-resident count (ops.row_limit), so the step has no host <-> device sync and a
+    fixed launch sequence (CUDA-graph capturable)."""
+
     @staticmethod
     def forward(ctx, model: PreTrainOscar, step: _Step, hs: FlatStore, meta, seq, pooled, *params):
-        idx_mlm, lab_mlm, idx_tok, lab_tok, next_action, V = meta
+        lab, tok, next_action, V, save = meta
         cfg = model.config
         bs: FlatStore = step.model._vt_store
         eps = float(cfg.layer_norm_eps)
         Dc = cfg.detector_classes
         dev = seq.device
-        save = step.need_grad
+        cap = ops.roundup(step.M, 128)
+        idx_mlm, lab_mlm, idx_tok, lab_tok, counts = ops.compact_labels(lab, V, tok, Dc, cap)
+        tied = "mlmhead.predictions.decoder.weight" not in hs.offset
+        E = bs.wb("embeddings.word_embeddings.weight") if tied else hs.wb("mlmhead.predictions.decoder.weight")
         # masked-LM head on the labelled rows (the only rows that reach loss, accuracy or gradients)
-        hm = ops.gather_rows(seq, idx_mlm)
-        n = hm.size(0)
-        pre_t = torch.empty((n, H), dtype=BF16, device=dev)
-        a = lib.gemm(hm, hs.wb("mlmhead.predictions.transform.dense.weight"), bias=hs.w("mlmhead.predictions.transform.dense.bias"),
-                     act=ACT_GELU, aux_out=pre_t)
-        tl = ops.layernorm_fwd(a, hs.w("mlmhead.predictions.transform.LayerNorm.weight"),
-                               hs.w("mlmhead.predictions.transform.LayerNorm.bias"), eps)
         ldv = ops.roundup(V, 8)
-        logits = torch.empty((n, ldv), dtype=F32, device=dev)
-        E = bs.wb("embeddings.word_embeddings.weight")
-        lib.gemm(tl, E, bias=hs.w("mlmhead.predictions.bias"), out=logits[:, :V])
-        mlm_loss, mlm_arg, mlm_stats = ops.softmax_ce_fwd(logits[:, :V], V, lab_mlm)
+        logits = torch.empty((cap, ldv), dtype=F32, device=dev)
+        pre_t = torch.empty((cap, H), dtype=BF16, device=dev)
+        with ops.row_limit(counts, 0):
+            hm = ops.gather_rows(seq, idx_mlm)
+            a = lib.gemm(hm, hs.wb("mlmhead.predictions.transform.dense.weight"), bias=hs.w("mlmhead.predictions.transform.dense.bias"),
+                         act=ACT_GELU, aux_out=pre_t)
+            tl = ops.layernorm_fwd(a, hs.w("mlmhead.predictions.transform.LayerNorm.weight"),
+                                   hs.w("mlmhead.predictions.transform.LayerNorm.bias"), eps)
+            lib.gemm(tl, E, bias=hs.w("mlmhead.predictions.bias"), out=logits[:, :V])
+            mlm_loss, mlm_arg, mlm_stats = ops.softmax_ce_fwd(logits[:, :V], V, lab_mlm)
         # detector-class head (double softmax)
-        ht = ops.gather_rows(seq, idx_tok)
-        nt = ht.size(0)
         ldt = ops.roundup(Dc, 8)
-        tlogits = torch.empty((nt, ldt), dtype=F32, device=dev)
-        lib.gemm(ht, hs.wb("token_head.0.weight"), bias=hs.w("token_head.0.bias"), out=tlogits[:, :Dc])
-        tok_loss, tok_arg, tok_stats = ops.softmax_ce_fwd(tlogits[:, :Dc], Dc, lab_tok, double_softmax=True)
+        tlogits = torch.empty((cap, ldt), dtype=F32, device=dev)
+        with ops.row_limit(counts, 1):
+            ht = ops.gather_rows(seq, idx_tok)
+            lib.gemm(ht, hs.wb("token_head.0.weight"), bias=hs.w("token_head.0.bias"), out=tlogits[:, :Dc])
+            tok_loss, tok_arg, tok_stats = ops.softmax_ce_fwd(tlogits[:, :Dc], Dc, lab_tok, double_softmax=True)
         # next-action head
         scores, act_loss, act_arg = ops.action_head_fwd(pooled, hs.w("next_action.linear.weight"), hs.w("next_action.linear.bias"),
                                                         next_action)
-        out8 = ops.pretrain_finalize((mlm_loss, mlm_arg, lab_mlm), (tok_loss, tok_arg, lab_tok),
-                                     (act_loss, act_arg, next_action) if next_action is not None else (act_loss[:0], act_arg[:0], None))
-        ctx.model, ctx.step, ctx.hs, ctx.meta = model, step, hs, meta
-        if save:
-            ctx.saved = (hm, pre_t, a, tl, logits, mlm_stats, ht, tlogits, tok_stats, scores, out8, pooled)
-        ctx.shapes = (n, nt, ldv, ldt)
-        ctx.aux = dict(predicted_words=mlm_arg, predicted_tokens=tok_arg, predicted_action=act_arg, action_scores=scores,
-                       mlm_logits=logits[:, :V], token_logits=tlogits[:, :Dc])
-        model._vt_last_aux = ctx.aux
+        out8 = ops.pretrain_finalize_counted((mlm_loss, mlm_arg, lab_mlm), (tok_loss, tok_arg, lab_tok),
+                                             (act_loss, act_arg, next_action) if next_action is not None else (act_loss[:0], act_arg[:0], None),
+                                             counts)
+        ctx.model, ctx.step, ctx.hs = model, step, hs
+        ctx.meta = (idx_mlm, lab_mlm, idx_tok, lab_tok, next_action, V, counts, tied)
+        ctx.saved = (hm, pre_t, a, tl, logits, mlm_stats, ht, tlogits, tok_stats, scores, out8, pooled) if save else None
+        ctx.shapes = (cap, ldv, ldt)
+        model._vt_aux_raw = dict(predicted_words=mlm_arg, predicted_tokens=tok_arg, predicted_action=act_arg, action_scores=scores,
+                                 mlm_logits=logits[:, :V], token_logits=tlogits[:, :Dc], counts=counts, idx_mlm=idx_mlm, idx_tok=idx_tok)
         return out8
 
     @staticmethod
     def backward(ctx, g8):
         model, step, hs = ctx.model, ctx.step, ctx.hs
-        idx_mlm, lab_mlm, idx_tok, lab_tok, next_action, V = ctx.meta
+        idx_mlm, lab_mlm, idx_tok, lab_tok, next_action, V, counts, tied = ctx.meta
+        if ctx.saved is None:
+            raise RuntimeError("PreTrainOscar: backward through a forward that ran without gradients enabled")
         hm, pre_t, a, tl, logits, mlm_stats, ht, tlogits, tok_stats, scores, out8, pooled = ctx.saved
         ctx.saved = None
-        n, nt, ldv, ldt = ctx.shapes
+        cap, ldv, ldt = ctx.shapes
         cfg = model.config
         bs: FlatStore = step.model._vt_store
         eps = float(cfg.layer_norm_eps)
@@ -691,11 +739,13 @@ class _HeadsFn(torch.autograd.Function):
         g_next = (g8[0:1] + g8[2:3]).contiguous()
         g_tok = (g8[0:1] + g8[3:4]).contiguous()
         dseq = torch.zeros((step.M, H), dtype=BF16, device=hm.device)
-        if n > 0:
-            E = bs.wb("embeddings.word_embeddings.weight")
-            dlog = ops.softmax_ce_bwd(logits[:, :V], V, lab_mlm, mlm_stats, 1.0 / n, g_mlm, ld_out=ldv)
+        E = bs.wb("embeddings.word_embeddings.weight") if tied else hs.wb("mlmhead.predictions.decoder.weight")
+        dE = bs.g("embeddings.word_embeddings.weight") if tied else hs.g("mlmhead.predictions.decoder.weight")
+        with ops.row_limit(counts, 0):
+            # the mean's 1 / n is applied on the device (the count lives there); padding rows of dlog are zeros
+            dlog = ops.softmax_ce_bwd(logits[:, :V], V, lab_mlm, mlm_stats, 1.0, g_mlm, ld_out=ldv)
             ops.colsum(dlog, hs.g("mlmhead.predictions.bias"), ncols=V)
-            lib.gemm(dlog[:, :V], tl, a_major=1, b_major=1, out=bs.g("embeddings.word_embeddings.weight"), accumulate=True)
+            lib.gemm(dlog[:, :V], tl, a_major=1, b_major=1, out=dE, accumulate=True)
             dtl = lib.gemm(dlog[:, :V], E, b_major=1)
             del dlog
             da, _ = ops.layernorm_bwd(dtl, a, hs.w("mlmhead.predictions.transform.LayerNorm.weight"), eps,
@@ -706,8 +756,8 @@ class _HeadsFn(torch.autograd.Function):
             lib.gemm(dpre, hm, a_major=1, b_major=1, out=hs.g("mlmhead.predictions.transform.dense.weight"), accumulate=True)
             dhm = lib.gemm(dpre, hs.wb("mlmhead.predictions.transform.dense.weight"), b_major=1)
             ops.scatter_add_rows(dhm, idx_mlm, dseq)
-        if nt > 0:
-            dlt = ops.softmax_ce_bwd(tlogits[:, :Dc], Dc, lab_tok, tok_stats, 1.0 / nt, g_tok, double_softmax=True, ld_out=ldt)
+        with ops.row_limit(counts, 1):
+            dlt = ops.softmax_ce_bwd(tlogits[:, :Dc], Dc, lab_tok, tok_stats, 1.0, g_tok, double_softmax=True, ld_out=ldt)
             ops.colsum(dlt, hs.g("token_head.0.bias"), ncols=Dc)
             lib.gemm(dlt[:, :Dc], ht, a_major=1, b_major=1, out=hs.g("token_head.0.weight"), accumulate=True)
             dht = lib.gemm(dlt[:, :Dc], hs.wb("token_head.0.weight"), b_major=1)

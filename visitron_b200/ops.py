@@ -131,11 +131,6 @@ def mask_bias(mask: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def set_attention_impl(impl: int):
-    """Debug hook: 0 = auto, 1 = mma.sync kernels, 2 = tcgen05 kernels."""
-    init().vt_debug_attention_impl(int(impl))
-
-
 def attention_key_tiles(bias: torch.Tensor) -> Optional[torch.Tensor]:
     """uint32-as-int32 [B]: which 64-key tiles of every sample hold an unmasked key; the attention kernels skip the others (exactly-zero
     probabilities in the reference's fp32 softmax, so no bit of the result changes).  None for S > 2048 (every tile is visited)."""
@@ -165,6 +160,48 @@ def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0,
     check(L.vt_attention_bwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(key_tiles), ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv),
                              dropout_p, seed, stream_id, stream_ptr()), "vt_attention_bwd")
     return dqkv
+
+
+# ------------------------------------------------------------------------------------------------
+# device-resident step state (sync-free steps, CUDA graphs): see the first section of include/visitron_b200.h
+# ------------------------------------------------------------------------------------------------
+def compact_labels(labels_a, classes_a, labels_b, classes_b, capacity, ignore_index=-1):
+    """Labelled-row compaction on the device: (idx_a, lab_a, idx_b, lab_b, counts int32[8]); no host sync.
+    counts[0:2] / counts[4:6] = (padded count, count) of a / b -- the row limits of the launches that follow."""
+    L = init()
+    n = labels_a.numel()
+    dev = labels_a.device
+    idx = torch.empty((2, 2, capacity), device=dev, dtype=torch.int64)
+    counts = torch.empty(8, device=dev, dtype=torch.int32)
+    check(L.vt_compact_labels(ptr(labels_a), classes_a, ptr(labels_b), classes_b, n, ignore_index, capacity, ptr(idx[0, 0]), ptr(idx[0, 1]),
+                              ptr(idx[1, 0]), ptr(idx[1, 1]), ptr(counts), stream_ptr()), "vt_compact_labels")
+    return idx[0, 0], idx[0, 1], idx[1, 0], idx[1, 1], counts
+
+
+class row_limit:
+    """`with row_limit(counts, which):` -- the launches inside clip their row extent on the device to counts[4 which] (padded) /
+    counts[4 which + 1] (true count).  Thread-local in the library: forward and backward each bracket their own launches."""
+
+    def __init__(self, counts, which=0):
+        self.p = counts.data_ptr() + 16 * which
+
+    def __enter__(self):
+        init().vt_set_row_limit(self.p)
+        return self
+
+    def __exit__(self, *exc):
+        init().vt_set_row_limit(None)
+        return False
+
+
+def seed_advance(state):
+    """state: int64[2] on the device = (counter, seed); one tiny launch, the first node of a captured step."""
+    check(init().vt_seed_advance(ptr(state), stream_ptr()), "vt_seed_advance")
+
+
+def set_seed_source(state):
+    """Dropout kernels XOR the device word state[1] into their by-value seed from now on (None: by-value seeds only)."""
+    init().vt_set_seed_source(None if state is None else state.data_ptr() + 8)
 
 
 def softmax_ce_fwd(logits, ncols, labels, double_softmax=False):
@@ -218,6 +255,19 @@ def pretrain_finalize(mlm, tok, act):
     for rl, am, lab in (mlm, tok, act):
         args += [ptr(rl), ptr(am), ptr(lab), rl.numel()]
     check(L.vt_pretrain_finalize(*args, ptr(out), stream_ptr()), "vt_pretrain_finalize")
+    return out
+
+
+def pretrain_finalize_counted(mlm, tok, act, counts):
+    """pretrain_finalize with the MLM / token row counts read from compact_labels' counts on the device."""
+    L = init()
+    out = torch.empty(8, device=counts.device, dtype=F32)
+    args = []
+    for rl, am, lab in (mlm, tok):
+        args += [ptr(rl), ptr(am), ptr(lab)]
+    rl, am, lab = act
+    args += [ptr(rl), ptr(am), ptr(lab), rl.numel()]
+    check(L.vt_pretrain_finalize_counted(*args, ptr(counts), ptr(out), stream_ptr()), "vt_pretrain_finalize_counted")
     return out
 
 

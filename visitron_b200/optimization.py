@@ -32,7 +32,7 @@ MAX_GROUPS = 8
 
 
 class _Segment(C.Structure):  # vt_opt_segment
-    _fields_ = [("p", C.c_void_p), ("g", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p), ("n", C.c_int64),
+    _fields_ = [("p", C.c_void_p), ("g", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p), ("p_bf16", C.c_void_p), ("n", C.c_int64),
                 ("group", C.c_int32), ("first_chunk", C.c_int32)]
 
 
@@ -44,9 +44,16 @@ class _Table:
         self.dev: Optional[torch.Tensor] = None
         self.n_segments = 0
         self.n_chunks = 0
+        self.stores = {}
 
-    def update(self, entries, device) -> "_Table":
-        key = tuple((p.data_ptr(), g.data_ptr(), 0 if m is None else m.data_ptr(), p.numel(), grp) for p, g, m, _, grp in entries)
+    def update(self, entries, device, with_shadow: bool = False) -> "_Table":
+        shadows = [None] * len(entries)
+        if with_shadow:
+            from . import flat
+            shadows = [flat.shadow_of(e[0]) for e in entries]
+        key = tuple((p.data_ptr(), g.data_ptr(), 0 if m is None else m.data_ptr(), p.numel(), grp, 0 if sh is None else sh[1].data_ptr())
+                    for (p, g, m, _, grp), sh in zip(entries, shadows))
+        self.stores = {id(sh[0]): sh[0] for sh in shadows if sh is not None}
         if key == self.key:
             return self
         chunk = int(lib.load().vt_opt_chunk())
@@ -56,6 +63,7 @@ class _Table:
             arr[i].p, arr[i].g = p.data_ptr(), g.data_ptr()
             arr[i].m = 0 if m is None else m.data_ptr()
             arr[i].v = 0 if v is None else v.data_ptr()
+            arr[i].p_bf16 = 0 if shadows[i] is None else shadows[i][1].data_ptr()
             arr[i].n, arr[i].group, arr[i].first_chunk = p.numel(), grp, first
             first += (p.numel() + chunk - 1) // chunk
         raw = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
@@ -130,7 +138,7 @@ class AdamW(Optimizer):
                 entries.append((p, p.grad, st["exp_avg"], st["exp_avg_sq"], gi))
         dev = entries[0][0].device
         with torch.cuda.device(dev):
-            t = self._table.update(entries, dev)
+            t = self._table.update(entries, dev, with_shadow=True)
             fs = (C.c_float * len(steps))(*steps)
             fd = (C.c_float * len(decays))(*decays)
             lib.check(lib.init(dev.index).vt_adamw_step(t.dev.data_ptr(), t.n_segments, t.n_chunks, len(steps), fs, fd, b1, b2, eps,
@@ -139,6 +147,8 @@ class AdamW(Optimizer):
         # the kernel wrote the parameters behind autograd's back: bump their version counters, so that saved-tensor checks
         # and the bf16 operand cache (flat.FlatStore.refresh_bf16) see the update
         torch.autograd.graph.increment_version([e[0] for e in entries])
+        for st in t.stores.values():   # the launch wrote the bf16 operand of every weight it updated: the next forward skips its cast
+            st.mark_fresh()
         return loss
 
 
