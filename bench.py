@@ -505,7 +505,10 @@ def run_ours(args):
     if sync_check is not None:
         line["grad_sync"] = sync_check
     if world == 1 and not args.no_gpu_eager and args.workload == "pretrain":
-        line["gpu_eager_baseline"] = gpu_eager_baseline(args, device, value)
+        try:
+            line["gpu_eager_baseline"] = gpu_eager_baseline(args, device, value)
+        except Exception as e:   # a comparison leg must never cost the line
+            line["gpu_eager_baseline"] = dict(error="%s: %s" % (type(e).__name__, str(e)[:200]))
     if world == 1 and not args.no_cpu_baseline and args.workload in ("pretrain", "viewpoint_select"):
         line["cpu_baseline"] = cpu_baseline(args, steps=2)
     sys.stdout.flush()

@@ -125,6 +125,7 @@ def test_graphed_step_equals_eager_step():
         out = model(**bt)
         out[0].backward()
         eager.append((torch.stack([o.detach() for o in out]).cpu(), {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None}))
+    del out
     step = vgraph.GraphedStep(model, batches[0])
     assert step.launches_per_step > 50
     for bt, (ref_out, ref_g) in zip(batches + batches[:1], eager + eager[:1]):   # different label counts per batch, and a re-run

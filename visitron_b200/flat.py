@@ -247,5 +247,18 @@ class FlatStore:
         return out
 
 
+    def assign_grads(self, used: Optional[set] = None) -> None:
+        """Hands the gradient views to the parameters WITHOUT autograd's AccumulateGrad nodes (used while a step is captured in a
+        CUDA graph: a node that outlived an earlier iteration carries that iteration's stream, and the engine's stream sync
+        would invalidate the capture).  Same semantics: adopt the view, or add it to a gradient that is already there."""
+        for view, p in zip(self.grad_views(used), self.params):
+            if view is None:
+                continue
+            if p.grad is None:
+                p.grad = view
+            else:
+                p.grad.add_(view)
+
+
 class _LayoutChanged(Exception):
     pass

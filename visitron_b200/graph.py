@@ -63,6 +63,7 @@ class GraphedStep:
                 out[0].backward()
                 if post_backward is not None:
                     post_backward()
+                del out      # a live loss keeps this iteration's AccumulateGrad nodes (and their stream) alive into the capture
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         self._clear_grads()

@@ -571,6 +571,9 @@ class _EncoderFn(torch.autograd.Function):
         if dpooled is None:
             used = (set(store.names) if used is None else used) - {"pooler.dense.weight", "pooler.dense.bias"}
         step.layers = None
+        if _CAPTURING:
+            store.assign_grads(used)
+            return (None, None) + (None,) * ctx.n_img + (None,) * len(store.params)
         return (None, None) + (None,) * ctx.n_img + tuple(store.grad_views(used))
 
 
@@ -772,4 +775,7 @@ class _HeadsFn(torch.autograd.Function):
         used = set(hs.names)
         if next_action is None:
             used -= {"next_action.linear.weight", "next_action.linear.bias"}
+        if _CAPTURING:
+            hs.assign_grads(used)
+            return (None, None, None, None, dseq, dpooled) + (None,) * len(hs.params)
         return (None, None, None, None, dseq, dpooled) + tuple(hs.grad_views(used))
