@@ -293,6 +293,34 @@ int vt_bce_logits_fwd(const float* q, const float* target, const uint8_t* valid,
 int vt_bce_logits_bwd(const float* q, const float* target, const uint8_t* valid, int64_t B, float pos_weight, const float* out2,
                       const float* g, float* dq, vt_stream stream);
 
+/* ------------------------------------------------------------------------------------------
+ * The agents' recurrent middle, hidden size 512, fp32 state.
+ * ------------------------------------------------------------------------------------------ */
+/* OscarEncoder's nn.LSTM(768 -> 512, 1 layer, batch_first) over all T encoder positions (vs/agent_models.py:223-230,283-287 ==
+ * tb/agent_models.py:148-155,208-212) behind pack_padded_sequence / pad_packed_sequence (:284,305).
+ * gates [B,T,2048]: IN the input projection x W_ih^T + b_ih + b_hh of every step (one vt_gemm_bf16, gate order i,f,g,o as
+ * nn.LSTM), OUT the activated gates (saved for backward).  w_hh: fp32 [2048,512].  lengths: device int64 [B] or NULL (= T):
+ * sample b advances for t < lengths[b], ctx [B,T,512] is 0 behind its end, (h_last, c_last) [B,512] are its last valid state.
+ * c_all [B,T,512] fp32 and hprev_bf16 [B,T,512] (= bf16(h_{t-1}), the operand of dW_hh) are saved for backward.
+ * One 16-CTA thread-block cluster per 8 samples; W_hh stays in shared memory for the whole sequence. */
+int vt_lstm_seq_fwd(float* gates, const float* w_hh, const int64_t* lengths, int64_t B, int64_t T, int64_t hidden, float* ctx,
+                    float* c_all, void* hprev_bf16, float* h_last, float* c_last, vt_stream stream);
+/* Backward through the recurrence: dA_bf16 [B,T,2048] = gradient of the gate pre-activations (0 behind a sample's end).  The
+ * caller finishes with GEMMs over all steps: dW_ih += dA^T X, dW_hh += dA^T hprev, dX = dA W_ih, db_ih = db_hh = colsum(dA).
+ * dh_last / dc_last: gradients of the returned final state (NULL = none). */
+int vt_lstm_seq_bwd(const float* gates, const float* c_all, const float* w_hh, const int64_t* lengths, const float* dctx,
+                    const float* dh_last, const float* dc_last, int64_t B, int64_t T, int64_t hidden, void* dA_bf16, vt_stream stream);
+/* nn.LSTMCell of the decoders (vs/agent_models.py:380,414 ; tb/agent_models.py:295,313): gates = ga + gb, the two halves
+ * x W_ih^T + b_ih and h W_hh^T + b_hh from vt_small_linear_fwd; gates_act [B,4H] keeps the activated gates for backward. */
+int vt_lstm_cell_fwd(const float* ga, const float* gb, const float* c0, int64_t B, int64_t hidden, float* gates_act, float* h1, float* c1,
+                     vt_stream stream);
+/* dgates [B,4H] (the gradient of both halves), dc0 [B,H]; dh1 / dc1 may be NULL. */
+int vt_lstm_cell_bwd(const float* gates_act, const float* c0, const float* c1, const float* dh1, const float* dc1, int64_t B, int64_t hidden,
+                     float* dgates, float* dc0, vt_stream stream);
+/* nn.Dropout on a flat fp32 array (the agents' self.drop, p = 0.5, vs/agent_models.py:216,379): y = x * keep / (1 - p); the
+ * backward is the same call on the gradient -- the mask is a function of (seed, dropout_stream, index), never stored. */
+int vt_dropout_f32(const float* x, int64_t n, float dropout_p, uint64_t seed, uint32_t dropout_stream, float* y, vt_stream stream);
+
 /* ---- the step after backward: multi-tensor AdamW and gradient-norm clipping ----
  * Replace transformers/pytorch_transformers/optimization.py:141-189 (AdamW.step, ~10 ATen launches per parameter) and
  * torch.nn.utils.clip_grad_norm_ at tasks/viewpoint_select/agent.py:514-518.

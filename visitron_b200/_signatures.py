@@ -52,6 +52,11 @@ SIGNATURES = {
     "vt_head_ce_bwd": (I, [P, I64, I64, I64, P, I64, P, P, P, P, I64, P]),
     "vt_bce_logits_fwd": (I, [P, P, P, I64, F, P, P, P]),
     "vt_bce_logits_bwd": (I, [P, P, P, I64, F, P, P, P, P]),
+    "vt_lstm_seq_fwd": (I, [P, P, P, I64, I64, I64, P, P, P, P, P, P]),
+    "vt_lstm_seq_bwd": (I, [P, P, P, P, P, P, P, I64, I64, I64, P, P]),
+    "vt_lstm_cell_fwd": (I, [P, P, P, I64, I64, P, P, P, P]),
+    "vt_lstm_cell_bwd": (I, [P, P, P, P, P, I64, I64, P, P, P]),
+    "vt_dropout_f32": (I, [P, I64, F, U64, U32, P, P]),
     "vt_opt_chunk": (I64, []),
     "vt_adamw_step": (I, [P, I64, I64, I64, P, P, D, D, D, P, P]),
     "vt_clip_grad_norm": (I, [P, I64, I64, F, P, P, I, P]),

@@ -66,5 +66,382 @@ __device__ __forceinline__ void mma_bf16(float* c, const uint32_t* a, uint32_t b
 }
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
 
+
+struct SeqParams {
+  float* gates;            // [B, T, 4H] in: x W_ih^T + b_ih + b_hh (gate order i, f, g, o as nn.LSTM); out: the ACTIVATED gates (saved for backward)
+  const float* w_hh;       // [4H, H] fp32 master
+  const long long* lengths;  // [B] valid steps per sample, or null (all T)
+  int B, T;
+  float* ctx;              // [B, T, H]  h_t, 0 behind the sample's end (pad_packed_sequence)
+  float* c_all;            // [B, T, H]  c_t (saved for backward)
+  bf16* hprev;             // [B, T, H]  bf16(h_{t-1}): the operand of dW_hh = dA^T H_prev
+  float* h_last;           // [B, H]
+  float* c_last;           // [B, H]
+  // backward
+  const float* dctx;       // [B, T, H]
+  const float* dh_last;    // [B, H] or null
+  const float* dc_last;    // [B, H] or null
+  bf16* dA;                // [B, T, 4H] gate pre-activation gradients (0 behind the sample's end)
+};
+
+// ---------------------------------------------------------------------------------------------
+// forward
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(THREADS, 1)
+lstm_seq_fwd_kernel(const SeqParams p) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint8_t* sW = smem;                                   // [128 rows][WROW]: row 16 w + 4 gate + ul  <->  W_hh[gate * 512 + 32 j + 4 w + ul, :]
+  uint8_t* sH = sW + 4 * U * WROW;                      // [buffer 2][hi / lo 2][sample 8][WROW]
+  uint8_t* sStage = sH + 2 * 2 * NS * WROW;             // [hi / lo 2][sample 8][32 units] bf16
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t j = cluster_rank();
+  const int sample0 = (blockIdx.x / CL) * NS;
+
+  // W slice -> shared memory (fp32 -> bf16), once
+  for (int i = tid; i < 4 * U * (H / 4); i += THREADS) {
+    const int row = i / (H / 4), c4 = i % (H / 4);
+    const int w = row >> 4, r = row & 15, gate = r >> 2, ul = r & 3;
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p.w_hh + (long long)(gate * H + U * (int)j + 4 * w + ul) * H) + c4);
+    uint2 o = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+    *reinterpret_cast<uint2*>(sW + row * WROW + c4 * 8) = o;
+  }
+  for (int i = tid; i < 2 * 2 * NS * WROW / 4; i += THREADS) reinterpret_cast<uint32_t*>(sH)[i] = 0u;   // h_{-1} = 0
+  __syncthreads();
+  cluster_sync_all();   // every CTA's buffers are initialised before anyone pushes h into them
+
+  // this thread's (unit, sample): the four gates of unit 4 warp + ul meet in lanes (lane, lane ^ 16)
+  const int r0 = lane >> 2, g0 = r0 >> 2, ul = r0 & 3;
+  const int n = 2 * (lane & 3) + g0;                    // sample within the cluster's 8
+  const int ucta = 4 * warp + ul;                       // unit within the CTA's 32
+  const int unit = U * (int)j + ucta;
+  const int b = sample0 + n;
+  const bool exists = b < p.B;
+  const int len = exists ? (p.lengths ? (int)min((long long)p.T, max(0ll, p.lengths[b])) : p.T) : 0;
+  float c = 0.f, h = 0.f;
+  const long long gbase = exists ? ((long long)b * p.T) * G + unit : 0;
+  const long long hbase = exists ? ((long long)b * p.T) * H + unit : 0;
+  float gx[4] = {0.f, 0.f, 0.f, 0.f};
+  if (len > 0) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) gx[q] = p.gates[gbase + q * H];
+  }
+  const uint32_t sW_u = smem_addr(sW), sH_u = smem_addr(sH), sStage_u = smem_addr(sStage);
+  // ldmatrix row address of this lane: row (lane % 8) + 8 ((lane / 8) % 2) of the warp's 16, k offset 8 (lane / 16)
+  const uint32_t a_lane = sW_u + (uint32_t)(16 * warp + (lane & 7) + 8 * ((lane >> 3) & 1)) * WROW + (uint32_t)(lane >> 4) * 16u;
+  const uint32_t b_lane = (uint32_t)(lane >> 2) * WROW + (uint32_t)(lane & 3) * 4u;   // B fragment: sample lane / 4, k pair lane % 4
+
+  for (int t = 0; t < p.T; ++t) {
+    const uint32_t hb = sH_u + (uint32_t)(t & 1) * (2 * NS * WROW);
+    float acc[4] = {0.f, 0.f, 0.f, 0.f}, acc2[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 8
+    for (int kk = 0; kk < H / 16; ++kk) {
+      uint32_t a[4];
+      ldmatrix_x4(a_lane + kk * 32, a);
+      const uint32_t bo = hb + b_lane + kk * 32;
+      mma_bf16(acc, a, lds32(bo), lds32(bo + 16));                              // h hi
+      mma_bf16(acc2, a, lds32(bo + NS * WROW), lds32(bo + NS * WROW + 16));     // h lo
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) acc[q] += acc2[q];
+    // gate exchange: lanes with g0 == 0 finish column n0 = 2 (lane % 4), their partners (lane ^ 16) column n0 + 1
+    const float s0 = g0 == 0 ? acc[1] : acc[0], s1 = g0 == 0 ? acc[3] : acc[2];
+    const float r_a = __shfl_xor_sync(0xffffffffu, s0, 16), r_b = __shfl_xor_sync(0xffffffffu, s1, 16);
+    float pi, pf, pg, po;   // recurrent parts of the pre-activations
+    if (g0 == 0) { pi = acc[0]; pg = acc[2]; pf = r_a; po = r_b; }
+    else         { pf = acc[1]; po = acc[3]; pi = r_a; pg = r_b; }
+    const bool active = t < len;
+    // next step's input projections: requested now, consumed after the next step's MMAs
+    float gn[4] = {0.f, 0.f, 0.f, 0.f};
+    if (t + 1 < len) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) gn[q] = p.gates[gbase + (long long)(t + 1) * G + q * H];
+    }
+    if (active) {
+      p.hprev[hbase + (long long)t * H] = __float2bfloat16(h);
+      const float ig = sigmoidf_(gx[0] + pi), fg = sigmoidf_(gx[1] + pf), gg = tanhf(gx[2] + pg), og = sigmoidf_(gx[3] + po);
+      c = fg * c + ig * gg;
+      h = og * tanhf(c);
+      float* gs = p.gates + gbase + (long long)t * G;
+      gs[0] = ig; gs[H] = fg; gs[2 * H] = gg; gs[3 * H] = og;
+      p.c_all[hbase + (long long)t * H] = c;
+      p.ctx[hbase + (long long)t * H] = h;
+    } else if (exists) {
+      p.ctx[hbase + (long long)t * H] = 0.f;
+      p.hprev[hbase + (long long)t * H] = __float2bfloat16(0.f);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) gx[q] = gn[q];
+    if (t + 1 == p.T) break;
+    // h (frozen for finished samples) as a bf16 hi + lo pair -> staging -> every CTA's next-step buffer
+    const bf16 hi = __float2bfloat16(h);
+    const bf16 lo = __float2bfloat16(h - __bfloat162float(hi));
+    reinterpret_cast<bf16*>(sStage)[(0 * NS + n) * U + ucta] = hi;
+    reinterpret_cast<bf16*>(sStage)[(1 * NS + n) * U + ucta] = lo;
+    __syncthreads();
+    {
+      // 2 x 8 x 64 B = 64 chunks of 16 B, to 16 CTAs: 4 remote stores per thread
+      const uint32_t dst_cta = (uint32_t)(tid >> 4);
+      const uint32_t nb = sH_u + (uint32_t)((t + 1) & 1) * (2 * NS * WROW);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int ch = (tid & 15) + 16 * k;           // chunk: hl = ch / 32, sample = (ch / 4) % 8, part = ch % 4
+        const int hl = ch >> 5, sn = (ch >> 2) & 7, part = ch & 3;
+        const uint4 v = *reinterpret_cast<const uint4*>(sStage + ((hl * NS + sn) * U + part * 8) * 2);
+        const uint32_t local = nb + (uint32_t)(hl * NS + sn) * WROW + (uint32_t)(U * (int)j + part * 8) * 2u;
+        st_remote_v4(map_remote(local, dst_cta), v);
+      }
+    }
+    cluster_sync_all();
+  }
+  if (exists) {
+    p.h_last[(long long)b * H + unit] = h;
+    p.c_last[(long long)b * H + unit] = c;
+  }
+  cluster_sync_all();   // no CTA exits while a peer may still address its shared memory
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// backward: t = T-1 .. 0.  Thread (unit u = tid / 8, sample n = tid % 8) carries dc and receives dh_{t} of its pair.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(THREADS, 1)
+lstm_seq_bwd_kernel(const SeqParams p) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint8_t* sWT = smem;                                  // [32 rows k][DROW]: row k  <->  W_hh[:, 32 j + k]  (W_hh^T slice)
+  uint8_t* sD = sWT + U * DROW;                         // [buffer 2][sample 8][DROW]: dA_t of ALL 2048 gates, bf16
+  float* sPart = reinterpret_cast<float*>(sD + 2 * NS * DROW);    // [warp 8][32 units][8 samples]
+  uint8_t* sStage = reinterpret_cast<uint8_t*>(sPart + 8 * U * NS);   // [sample 8][gate 4][32 units] bf16
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t j = cluster_rank();
+  const int sample0 = (blockIdx.x / CL) * NS;
+
+  // W_hh^T slice: sWT[k][g] = W_hh[g][32 j + k]; a warp reads 32 consecutive floats of one row of W_hh (128 B) per step
+  for (int g = warp; g < G; g += THREADS / 32) {
+    const float v = __ldg(p.w_hh + (long long)g * H + U * (int)j + lane);
+    *reinterpret_cast<bf16*>(sWT + lane * DROW + g * 2) = __float2bfloat16(v);
+  }
+  __syncthreads();
+  cluster_sync_all();
+
+  const int ucta = tid >> 3, n = tid & 7;
+  const int unit = U * (int)j + ucta;
+  const int b = sample0 + n;
+  const bool exists = b < p.B;
+  const int len = exists ? (p.lengths ? (int)min((long long)p.T, max(0ll, p.lengths[b])) : p.T) : 0;
+  const long long gbase = exists ? ((long long)b * p.T) * G + unit : 0;
+  const long long hbase = exists ? ((long long)b * p.T) * H + unit : 0;
+  float dc = 0.f, dh_rec = 0.f;
+  const uint32_t sWT_u = smem_addr(sWT), sD_u = smem_addr(sD);
+  // A fragment rows: m-tile mt covers units 16 mt .. + 15; this warp contracts over gates [256 warp, + 256)
+  const uint32_t a_lane = sWT_u + (uint32_t)((lane & 7) + 8 * ((lane >> 3) & 1)) * DROW + (uint32_t)(lane >> 4) * 16u + (uint32_t)warp * 512u;
+  const uint32_t b_lane = (uint32_t)(lane >> 2) * DROW + (uint32_t)(lane & 3) * 4u + (uint32_t)warp * 512u;
+
+  for (int t = p.T - 1; t >= 0; --t) {
+    const bool active = t < len;
+    float da[4] = {0.f, 0.f, 0.f, 0.f};
+    if (active) {
+      const float* gs = p.gates + gbase + (long long)t * G;
+      const float ig = gs[0], fg = gs[H], gg = gs[2 * H], og = gs[3 * H];
+      const float ct = p.c_all[hbase + (long long)t * H];
+      const float cp = t > 0 ? p.c_all[hbase + (long long)(t - 1) * H] : 0.f;
+      float dh = p.dctx[hbase + (long long)t * H] + dh_rec;
+      if (t == len - 1) {
+        if (p.dh_last) dh += p.dh_last[(long long)b * H + unit];
+        if (p.dc_last) dc += p.dc_last[(long long)b * H + unit];
+      }
+      const float tc = tanhf(ct);
+      const float dct = dc + dh * og * (1.f - tc * tc);
+      da[0] = dct * gg * ig * (1.f - ig);       // i
+      da[1] = dct * cp * fg * (1.f - fg);       // f
+      da[2] = dct * ig * (1.f - gg * gg);       // g
+      da[3] = dh * tc * og * (1.f - og);        // o
+      dc = dct * fg;
+    }
+    if (exists) {
+      bf16* dst = p.dA + gbase + (long long)t * G;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) dst[q * H] = __float2bfloat16(da[q]);
+    }
+    if (t == 0) break;      // dh_{-1} is nobody's gradient (h_{-1} = 0 is a constant)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) reinterpret_cast<bf16*>(sStage)[(n * 4 + q) * U + ucta] = __float2bfloat16(da[q]);
+    __syncthreads();
+    {
+      // 8 samples x 4 gates x 64 B = 128 chunks of 16 B, to 16 CTAs: 8 remote stores per thread
+      const uint32_t dst_cta = (uint32_t)(tid >> 4);
+      const uint32_t nb = sD_u + (uint32_t)(t & 1) * (NS * DROW);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int ch = (tid & 15) + 16 * k;           // chunk: sample = ch / 16, gate = (ch / 4) % 4, part = ch % 4
+        const int sn = ch >> 4, q = (ch >> 2) & 3, part = ch & 3;
+        const uint4 v = *reinterpret_cast<const uint4*>(sStage + ((sn * 4 + q) * U + part * 8) * 2);
+        const uint32_t local = nb + (uint32_t)sn * DROW + (uint32_t)(q * H + U * (int)j + part * 8) * 2u;
+        st_remote_v4(map_remote(local, dst_cta), v);
+      }
+    }
+    cluster_sync_all();
+    // dh_{t-1}[unit, sample] = sum_g W_hh[g, unit] dA_t[sample, g]: this warp's 256-gate slice, both 16-unit tiles
+    const uint32_t db = sD_u + (uint32_t)(t & 1) * (NS * DROW);
+    float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+    for (int kk = 0; kk < 16; ++kk) {
+      uint32_t a0[4], a1[4];
+      ldmatrix_x4(a_lane + kk * 32, a0);
+      ldmatrix_x4(a_lane + 16 * DROW + kk * 32, a1);
+      const uint32_t bo = db + b_lane + kk * 32;
+      const uint32_t b0 = lds32(bo), b1 = lds32(bo + 16);
+      mma_bf16(acc0, a0, b0, b1);
+      mma_bf16(acc1, a1, b0, b1);
+    }
+    {
+      // fragment (row = lane / 4 (+ 8), col = 2 (lane % 4) (+ 1)) -> sPart[warp][unit][sample]
+      float* pw = sPart + warp * (U * NS);
+      const int r = lane >> 2, cc = 2 * (lane & 3);
+      pw[r * NS + cc] = acc0[0]; pw[r * NS + cc + 1] = acc0[1];
+      pw[(r + 8) * NS + cc] = acc0[2]; pw[(r + 8) * NS + cc + 1] = acc0[3];
+      pw[(r + 16) * NS + cc] = acc1[0]; pw[(r + 16) * NS + cc + 1] = acc1[1];
+      pw[(r + 24) * NS + cc] = acc1[2]; pw[(r + 24) * NS + cc + 1] = acc1[3];
+    }
+    __syncthreads();
+    float sum = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) sum += sPart[w * (U * NS) + tid];   // [unit][sample] flat index == tid; fixed order
+    dh_rec = sum;
+    // (the next iteration's __syncthreads orders these reads before sPart is written again)
+  }
+  cluster_sync_all();
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// LSTMCell of the decoders (one step): the two gate halves x W_ih^T + b_ih and h W_hh^T + b_hh come from the step-sized
+// linears of agent_heads.cu; this is the element-wise part and its backward.  gates_act keeps (i, f, g, o) activated.
+// ---------------------------------------------------------------------------------------------
+__global__ void lstm_cell_fwd_kernel(const float* __restrict__ ga, const float* __restrict__ gb, const float* __restrict__ c0, int B, int Hh,
+                                     float* __restrict__ act, float* __restrict__ h1, float* __restrict__ c1) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * Hh) return;
+  const int s = i / Hh, u = i % Hh;
+  const long long g = (long long)s * 4 * Hh + u;
+  const float ig = sigmoidf_(ga[g] + gb[g]), fg = sigmoidf_(ga[g + Hh] + gb[g + Hh]);
+  const float gg = tanhf(ga[g + 2 * Hh] + gb[g + 2 * Hh]), og = sigmoidf_(ga[g + 3 * Hh] + gb[g + 3 * Hh]);
+  const float c = fg * c0[i] + ig * gg;
+  act[g] = ig; act[g + Hh] = fg; act[g + 2 * Hh] = gg; act[g + 3 * Hh] = og;
+  c1[i] = c;
+  h1[i] = og * tanhf(c);
+}
+
+__global__ void lstm_cell_bwd_kernel(const float* __restrict__ act, const float* __restrict__ c0, const float* __restrict__ c1,
+                                     const float* __restrict__ dh1, const float* __restrict__ dc1, int B, int Hh,
+                                     float* __restrict__ dgates, float* __restrict__ dc0) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * Hh) return;
+  const int s = i / Hh, u = i % Hh;
+  const long long g = (long long)s * 4 * Hh + u;
+  const float ig = act[g], fg = act[g + Hh], gg = act[g + 2 * Hh], og = act[g + 3 * Hh];
+  const float tc = tanhf(c1[i]);
+  const float dh = dh1 ? dh1[i] : 0.f;
+  const float dct = (dc1 ? dc1[i] : 0.f) + dh * og * (1.f - tc * tc);
+  dgates[g] = dct * gg * ig * (1.f - ig);
+  dgates[g + Hh] = dct * c0[i] * fg * (1.f - fg);
+  dgates[g + 2 * Hh] = dct * ig * (1.f - gg * gg);
+  dgates[g + 3 * Hh] = dh * tc * og * (1.f - og);
+  dc0[i] = dct * fg;
+}
+
+// y = x * keep / (1 - p) over a flat fp32 array: nn.Dropout of the agents' modules (vs/agent_models.py:216,379 ; p = 0.5); the
+// backward is the same call on the gradient (the mask is regenerated from (seed, stream, index), never stored)
+__global__ void dropout_f32_kernel(const float* __restrict__ x, long long n, DropoutCfg drop, float* __restrict__ y) {
+  drop = resolve_dropout(drop);
+  for (long long g8 = (long long)blockIdx.x * blockDim.x + threadIdx.x; g8 * 8 < n; g8 += (long long)gridDim.x * blockDim.x) {
+    float m[8];
+    dropout_mult8(drop, (uint64_t)g8 * 8, m);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const long long i = g8 * 8 + e;
+      if (i < n) y[i] = x[i] * m[e];
+    }
+  }
+}
+
 }  // namespace lstm
 }  // namespace vt
+
+using namespace vt;
+using namespace vt::lstm;
+
+static int launch_seq(void (*kern)(const SeqParams), int smem_bytes, const SeqParams& p, cudaStream_t st, const char* who) {
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+  if (e != cudaSuccess) return cuda_fail(e, who, __FILE__, __LINE__);
+  e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);   // 16 CTAs per cluster (8 is the portable limit)
+  if (e != cudaSuccess) return cuda_fail(e, who, __FILE__, __LINE__);
+  cudaLaunchConfig_t cfg = {};
+  const int clusters = (p.B + NS - 1) / NS;
+  cfg.gridDim = dim3((unsigned)(clusters * CL));
+  cfg.blockDim = dim3(THREADS);
+  cfg.dynamicSmemBytes = (size_t)smem_bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  e = cudaLaunchKernelEx(&cfg, kern, p);
+  if (e != cudaSuccess) return cuda_fail(e, who, __FILE__, __LINE__);
+  count_launch(1);
+  return VT_OK;
+}
+
+extern "C" int vt_lstm_seq_fwd(float* gates, const float* w_hh, const int64_t* lengths, int64_t B, int64_t T, int64_t hidden, float* ctx,
+                               float* c_all, void* hprev_bf16, float* h_last, float* c_last, vt_stream stream) {
+  VT_REQUIRE(hidden == H, "vt_lstm_seq_fwd: hidden size %lld outside the supported envelope (512, vs/params.py rnn_dim)", (long long)hidden);
+  VT_REQUIRE(gates && w_hh && ctx && c_all && hprev_bf16 && h_last && c_last && B > 0 && T > 0 && B * T < (1ll << 31), "vt_lstm_seq_fwd: bad arguments");
+  VT_REQUIRE(((uintptr_t)w_hh & 15) == 0, "vt_lstm_seq_fwd: w_hh must be 16-byte aligned");
+  SeqParams p = {};
+  p.gates = gates; p.w_hh = w_hh; p.lengths = (const long long*)lengths; p.B = (int)B; p.T = (int)T;
+  p.ctx = ctx; p.c_all = c_all; p.hprev = (bf16*)hprev_bf16; p.h_last = h_last; p.c_last = c_last;
+  return launch_seq(lstm_seq_fwd_kernel, FWD_SMEM, p, (cudaStream_t)stream, "vt_lstm_seq_fwd");
+}
+
+extern "C" int vt_lstm_seq_bwd(const float* gates, const float* c_all, const float* w_hh, const int64_t* lengths, const float* dctx,
+                               const float* dh_last, const float* dc_last, int64_t B, int64_t T, int64_t hidden, void* dA_bf16, vt_stream stream) {
+  VT_REQUIRE(hidden == H, "vt_lstm_seq_bwd: hidden size %lld outside the supported envelope (512)", (long long)hidden);
+  VT_REQUIRE(gates && c_all && w_hh && dctx && dA_bf16 && B > 0 && T > 0 && B * T < (1ll << 31), "vt_lstm_seq_bwd: bad arguments");
+  SeqParams p = {};
+  p.gates = const_cast<float*>(gates); p.c_all = const_cast<float*>(c_all); p.w_hh = w_hh; p.lengths = (const long long*)lengths;
+  p.B = (int)B; p.T = (int)T; p.dctx = dctx; p.dh_last = dh_last; p.dc_last = dc_last; p.dA = (bf16*)dA_bf16;
+  return launch_seq(lstm_seq_bwd_kernel, BWD_SMEM, p, (cudaStream_t)stream, "vt_lstm_seq_bwd");
+}
+
+extern "C" int vt_lstm_cell_fwd(const float* ga, const float* gb, const float* c0, int64_t B, int64_t hidden, float* gates_act, float* h1,
+                                float* c1, vt_stream stream) {
+  VT_REQUIRE(ga && gb && c0 && gates_act && h1 && c1 && B >= 0 && hidden > 0 && B * hidden < (1ll << 31), "vt_lstm_cell_fwd: bad arguments");
+  if (B == 0) return VT_OK;
+  const int n = (int)(B * hidden);
+  lstm_cell_fwd_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(ga, gb, c0, (int)B, (int)hidden, gates_act, h1, c1);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_lstm_cell_bwd(const float* gates_act, const float* c0, const float* c1, const float* dh1, const float* dc1, int64_t B,
+                                int64_t hidden, float* dgates, float* dc0, vt_stream stream) {
+  VT_REQUIRE(gates_act && c0 && c1 && dgates && dc0 && B >= 0 && hidden > 0 && B * hidden < (1ll << 31), "vt_lstm_cell_bwd: bad arguments");
+  if (B == 0) return VT_OK;
+  const int n = (int)(B * hidden);
+  lstm_cell_bwd_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(gates_act, c0, c1, dh1, dc1, (int)B, (int)hidden, dgates, dc0);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_dropout_f32(const float* x, int64_t n, float dropout_p, uint64_t seed, uint32_t dropout_stream, float* y, vt_stream stream) {
+  VT_REQUIRE(x && y && n >= 0 && dropout_p >= 0.f && dropout_p < 1.f, "vt_dropout_f32: bad arguments");
+  if (n == 0) return VT_OK;
+  const long long groups = (n + 7) / 8;
+  long long g = (groups + 255) / 256, cap = (long long)num_sms() * 8;
+  dropout_f32_kernel<<<(unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream>>>(x, (long long)n, make_dropout(dropout_p, seed, dropout_stream), y);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}

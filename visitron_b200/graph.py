@@ -19,6 +19,7 @@ working beside the graph (e.g. validation).  Shapes are baked in: a batch of ano
 """
 from __future__ import annotations
 
+import gc
 from typing import Callable, Dict, Iterable, Optional, Sequence
 
 import torch
@@ -67,6 +68,9 @@ class GraphedStep:
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         self._clear_grads()
+        # no autograd graph of an earlier iteration may survive into the capture: its AccumulateGrad nodes carry the stream they
+        # were created on, and the engine's end-of-backward sync with that stream would invalidate the capture
+        gc.collect()
         self.graph = torch.cuda.CUDAGraph()
         n0 = lib.launch_count()
         modeling._CAPTURING = True

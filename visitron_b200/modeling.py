@@ -463,7 +463,10 @@ def _encoder_forward(step: _Step, st: FlatStore, img_feats, img_loc):
     if step.hidden is not None:
         step.hidden.append(x)
     pooled = lib.gemm(x[::S], st.wb("pooler.dense.weight"), bias=st.w("pooler.dense.bias"), act=ACT_TANH, out_dtype=F32)
-    step.seq, step.pooled = x, pooled
+    # detached ALIASES: autograd attaches this node to the returned tensor objects themselves, and node -> ctx.step -> step.seq
+    # -> grad_fn -> node would be a reference cycle that keeps every finished iteration's graph (and its AccumulateGrad nodes)
+    # alive until the cyclic collector runs
+    step.seq, step.pooled = x.detach(), pooled.detach()
     return x, pooled
 
 
@@ -717,7 +720,8 @@ class _HeadsFn(torch.autograd.Function):
                                              counts)
         ctx.model, ctx.step, ctx.hs = model, step, hs
         ctx.meta = (idx_mlm, lab_mlm, idx_tok, lab_tok, next_action, V, counts, tied)
-        ctx.saved = (hm, pre_t, a, tl, logits, mlm_stats, ht, tlogits, tok_stats, scores, out8, pooled) if save else None
+        # out8.detach(): the returned out8 gets this node as grad_fn; saving the object itself would be a reference cycle
+        ctx.saved = (hm, pre_t, a, tl, logits, mlm_stats, ht, tlogits, tok_stats, scores, out8.detach(), pooled) if save else None
         ctx.shapes = (cap, ldv, ldt)
         model._vt_aux_raw = dict(predicted_words=mlm_arg, predicted_tokens=tok_arg, predicted_action=act_arg, action_scores=scores,
                                  mlm_logits=logits[:, :V], token_logits=tlogits[:, :Dc], counts=counts, idx_mlm=idx_mlm, idx_tok=idx_tok)
