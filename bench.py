@@ -184,7 +184,7 @@ class Workload:
                 if args.workload == "turn_based":
                     hb["no_forward"] = torch.rand(TB_STEPS, b, generator=gi) < 0.25
                     tgt = torch.randint(0, 6, (TB_STEPS, b), generator=gi)
-                    hb["target"] = torch.where(hb["no_forward"] & (tgt == 0), torch.ones_like(tgt), tgt)
+                    hb["target"] = torch.where(hb["no_forward"] & (tgt == 4), torch.ones_like(tgt), tgt)
                     hb["target"][:, -1] = 7   # an ended episode: <ignore>
                 else:
                     hb["target"] = (torch.rand(b, generator=gi) < 0.4).float()

@@ -280,10 +280,11 @@ int vt_softdot_fwd(const float* ctx, const float* target, const uint8_t* mask, i
 int vt_softdot_bwd(const float* ctx, const float* target, const uint8_t* mask, const float* attn, const float* dweighted, const float* dattn,
                    const float* dlogit_ext, int64_t B, int64_t L, int64_t D, float* dctx, float* dtarget, float* workspace, vt_stream stream);
 /* Action-logit masking + CrossEntropyLoss(ignore_index, mean) + argmax (vs/agent.py:396-408, tb/agent.py:150-152,316-327):
- * columns >= valid_len[b] and, where forbid0[b], column 0 become -inf in `masked` (may alias logits);
- * out3 = {loss, rows not ignored, sum of their losses}; lse fp32 [B] saved for backward. */
-int vt_head_ce_fwd(const float* logits, int64_t ld, int64_t B, int64_t C, const int64_t* valid_len, const uint8_t* forbid0,
-                   const int64_t* target, int64_t ignore_index, float* masked, int64_t ldm, float* lse, int64_t* argmax, float* out3,
+ * columns >= valid_len[b] and, where forbid[b], column forbid_col ("forward" = 4 in tb/agent.py:71-80) become -inf in `masked` (may alias logits);
+ * out3 = {loss, rows not ignored, sum of their losses}; lse fp32 [B] saved for backward.  A step whose rows are ALL ignored gives
+ * nan like torch, or 0 with empty_is_zero (rollouts: the reference leaves the episode loop before such a step, vs/agent.py:466-468). */
+int vt_head_ce_fwd(const float* logits, int64_t ld, int64_t B, int64_t C, const int64_t* valid_len, const uint8_t* forbid,
+                   int64_t forbid_col, int empty_is_zero, const int64_t* target, int64_t ignore_index, float* masked, int64_t ldm, float* lse, int64_t* argmax, float* out3,
                    vt_stream stream);
 int vt_head_ce_bwd(const float* masked, int64_t ldm, int64_t B, int64_t C, const int64_t* target, int64_t ignore_index, const float* lse,
                    const float* out3, const float* g, float* dlogits, int64_t ldd, vt_stream stream);
@@ -320,6 +321,19 @@ int vt_lstm_cell_bwd(const float* gates_act, const float* c0, const float* c1, c
 /* nn.Dropout on a flat fp32 array (the agents' self.drop, p = 0.5, vs/agent_models.py:216,379): y = x * keep / (1 - p); the
  * backward is the same call on the gradient -- the mask is a function of (seed, dropout_stream, index), never stored. */
 int vt_dropout_f32(const float* x, int64_t n, float dropout_p, uint64_t seed, uint32_t dropout_stream, float* y, vt_stream stream);
+
+/* nn.Embedding of the turn-based decoder's previous action (tb/agent_models.py:292,308): y[b] = W[idx[b]] (fp32 [V,D]); the backward
+ * OVERWRITES dW with the per-row sums, samples in ascending order (deterministic). */
+int vt_embedding_f32_fwd(const float* W, const int64_t* idx, int64_t B, int64_t V, int64_t D, float* y, vt_stream stream);
+int vt_embedding_f32_bwd(const float* dy, const int64_t* idx, int64_t B, int64_t V, int64_t D, float* dW, vt_stream stream);
+/* Action feedback of one rollout step ON THE DEVICE (vs/agent.py:410-441 and tb/agent.py:329-346 do it on the host
+ * behind a .cpu() / .item() sync per decoder step).  mode 0: a = target (teacher forcing); 1: argmax of the masked logits; 2: a sample
+ * of softmax(masked logits) drawn with the counter RNG keyed on (seed, rng_stream, step, sample).  ended[b] |= a is the stop action
+ * (stop_len[b] - 1, i.e. the <end> candidate, when stop_len is given; else stop_const) or the ignore id.  a_out [B]: the action.
+ * next_target_eff (optional): ended[b] ? ignore_index : next_target[b] -- the teacher's answer for a finished episode. */
+int vt_rollout_feedback(const float* masked_logits, int64_t ld, int64_t B, int64_t C, const int64_t* target, const int64_t* stop_len,
+                        int64_t stop_const, int64_t ignore_index, int mode, uint64_t seed, uint32_t rng_stream, uint32_t step, uint8_t* ended,
+                        int64_t* a_out, const int64_t* next_target, int64_t* next_target_eff, vt_stream stream);
 
 /* ---- the step after backward: multi-tensor AdamW and gradient-norm clipping ----
  * Replace transformers/pytorch_transformers/optimization.py:141-189 (AdamW.step, ~10 ATen launches per parameter) and

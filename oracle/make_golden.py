@@ -124,7 +124,7 @@ def gen_heads(ns, name, seed):
     logit2 = d2a(h_tilde)
     for i in range(logit2.size(0)):
         if bool(tb["no_forward"][i]):
-            logit2[i, 0] = -float("inf")
+            logit2[i, 4] = -float("inf")   # self.model_actions.index("forward"), tb/agent.py:71-80,316-318
     loss2 = torch.nn.CrossEntropyLoss(ignore_index=7)(logit2, tb["target"])
     loss2.backward()
     fix["turn"] = dict(h_tilde=h_tilde.detach().clone(),
@@ -306,6 +306,88 @@ def gen_preprocess_item(name, seed):
     print(name, [(c["n"], tuple(c["out"]["img_feats"].shape), sum(c["out"]["attention_mask"])) for c in cases])
 
 
+
+def _load(module, params):
+    sd = module.state_dict()
+    for k, v in params.items():
+        assert k in sd and tuple(sd[k].shape) == tuple(v.shape), (k, tuple(v.shape))
+        sd[k] = v.clone()
+    module.load_state_dict(sd, strict=True)
+
+
+def gen_agents(ns, name, seed):
+    """the UNMODIFIED OscarEncoder + AttnDecoderLSTM of both action spaces (vs/agent_models.py, tb/agent_models.py)
+    driven by the rollout loops of vs/agent.py:334-474 and tb/agent.py:259-392 restated over a recorded trace (agent.py itself
+    needs MatterSim), teacher forcing, dropout 0: context, initial state, per-step logits, loss, gradient digests."""
+    import types
+    cfg = small_cfg()
+    P = vo.init_params(cfg, seed, pretrain_heads=False)
+    A, Dv, Dt = vo.init_agent_params(seed + 1)
+    T, B, steps = 48, 3, 4
+    args = types.SimpleNamespace(device="cpu")
+    fix = dict(kind="agents", cfg=cfg.__dict__, seed=seed, T=T, B=B, steps=steps)
+    for space in ("vs", "tb"):
+        mods = ns.vs_models if space == "vs" else ns.tb_models
+        bert = ns.BertImgModelwithLocationEmbeds(ref_shim.make_config(ns, cfg))
+        bert.load_state_dict({k[len("bert."):]: v.clone() for k, v in P.items()}, strict=True)
+        enc = mods.OscarEncoder(args, bert, 512, 512, 0.0)
+        _load(enc, {k: v for k, v in A.items()})
+        if space == "vs":
+            dec = mods.AttnDecoderLSTM(4, 64, 512, 0.0, 2052)
+            _load(dec, Dv)
+        else:
+            dec = mods.AttnDecoderLSTM(8, 6, 32, 512, 0.0, 2048)
+            _load(dec, Dt)
+        enc.train()
+        dec.train()
+        batch = synthetic.agent_batch(B, seed + 2, text_len=T, vocab=cfg.vocab_size, ragged=True)
+        lengths, mask = batch["lengths"], batch["mask"]
+        ctx, h_t, c_t = enc(batch["input_ids"], lengths, mask, token_type_ids=batch["token_type_ids"])
+        out = dict(ctx=ctx.detach().clone(), decoder_init=h_t.detach().clone(), c_t=c_t.detach().clone())
+        loss, logits = 0.0, []
+        ended = torch.zeros(B, dtype=torch.bool)
+        if space == "vs":
+            tr = synthetic.viewpoint_trace(steps, B, seed + 3, candidates=6)
+            crit = torch.nn.CrossEntropyLoss(ignore_index=-100)
+            h1 = h_t
+            for t in range(steps):
+                h_t, c_t, logit, h1 = dec(tr["input_a_t"][t], tr["f_t"][t], tr["cand_feat"][t], h_t, h1, c_t, ctx, mask)
+                cand_mask = torch.arange(logit.size(1))[None, :] > (tr["cand_len"][t] - 1)[:, None]     # utils.length2mask
+                logit.masked_fill_(cand_mask, -float("inf"))
+                target = torch.where(ended, torch.full_like(tr["target"][t], -100), tr["target"][t])
+                loss = loss + crit(logit, target)
+                ended = ended | (target == tr["cand_len"][t] - 1) | (target == -100)
+                logits.append(logit.detach().clone())
+                if bool(ended.all()):
+                    break
+        else:
+            tr = synthetic.turn_trace(steps, B, seed + 3)
+            crit = torch.nn.CrossEntropyLoss(ignore_index=7)
+            a_t = torch.full((B,), 6, dtype=torch.long)
+            for t in range(steps):
+                h_t, c_t, alpha, logit = dec(a_t.view(-1, 1), tr["f_t"][t], h_t, c_t, ctx, mask)
+                for i in range(B):
+                    if bool(tr["no_forward"][t, i]):
+                        logit[i, 4] = -float("inf")          # model_actions.index("forward")
+                target = torch.where(ended, torch.full_like(tr["target"][t], 7), tr["target"][t])
+                loss = loss + crit(logit, target)
+                a_t = target
+                ended = ended | (a_t == 5)
+                logits.append(logit.detach().clone())
+                if bool(ended.all()):
+                    break
+        loss = loss / steps
+        loss.backward()
+        out.update(loss=float(loss), logits=logits,
+                   enc_grads={k: grad_digest(p.grad) for k, p in enc.named_parameters() if p.grad is not None and not k.startswith("bert.")},
+                   dec_grads={k: grad_digest(p.grad) for k, p in dec.named_parameters() if p.grad is not None},
+                   bert_grads={k: grad_digest(p.grad) for k, p in enc.bert.named_parameters()
+                               if p.grad is not None and ("layer.0.attention.self.query" in k or "word_embeddings" in k or "layer.1.output.dense.weight" in k)})
+        fix[space] = out
+        print(name, space, float(loss))
+    torch.save(fix, os.path.join(GOLDEN, name + ".pt"))
+
+
 def main():
     if not ref_shim.available():
         raise SystemExit("reference tree not mounted; fixtures can only be generated in the build container")
@@ -317,6 +399,7 @@ def main():
     gen_pretrain(ns, "pretrain_small_imgln", small_cfg(use_img_layernorm=1), 8, dict(bk, seed=89))
     gen_finetune(ns, "finetune_small", small_cfg(), 9, dict(batch=2, seed=90, text_len=48, vocab=2048))
     gen_heads(ns, "heads_small", 11)
+    gen_agents(ns, "agents_small", 23)
     gen_adamw(ns, "adamw_small", 13)
     gen_mlm_mask("mlm_mask_small", 17)
     gen_preprocess_item("preprocess_item_small", 19)

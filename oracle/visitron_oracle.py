@@ -318,15 +318,18 @@ def candidate_scores_ce(w_in, h_tilde, cand_feat, cand_len, target, ignore_index
     return logit, loss, logit.argmax(1)
 
 
+FORWARD_ACTION = 4   # tb/agent.py:71-80: model_actions = [left, right, up, down, forward, <end>, <start>, <ignore>]
+
+
 def turn_based_head(w_in, w_out, w_a, b_a, h, ctx, ctx_mask, no_forward, target, ignore_index=7):
     """tb/agent_models.py:253-274,297,316-318 + tb/agent.py:150-152,316-327: ctx attention ->
-    h_tilde -> decoder2action logits [B,6]; logit[:,0] (forward) -> -inf where no navigable
-    location; CE(ignore_index=7)."""
+    h_tilde -> decoder2action logits [B,6]; logit[:, 4] (model_actions.index("forward"), tb/agent.py:71-80) -> -inf where
+    no navigable location; CE(ignore_index=7)."""
     h_tilde, _ = soft_dot_attention(w_in, w_out, h, ctx, ctx_mask)
     logit = F.linear(h_tilde, w_a, b_a)
     if no_forward is not None:
         logit = logit.clone()
-        logit[:, 0] = logit[:, 0].masked_fill(no_forward.bool(), -float("inf"))
+        logit[:, FORWARD_ACTION] = logit[:, FORWARD_ACTION].masked_fill(no_forward.bool(), -float("inf"))
     loss = F.cross_entropy(logit, target, ignore_index=ignore_index)
     return h_tilde, logit, loss, logit.argmax(1)
 
@@ -340,6 +343,142 @@ def qa_head(w1, b1, w2, b2, h_tilde, target, valid, pos_weight=5.0):
         pos_weight=torch.tensor(pos_weight, dtype=q.dtype, device=q.device))
     v = valid.to(per.dtype)
     return q, (per * v).sum() / v.sum().clamp(min=1.0)
+
+
+# --------------------------------------------------------------------------------------------
+# the agents' recurrent middle and rollouts
+# --------------------------------------------------------------------------------------------
+def lstm_cell(x, h, c, w_ih, w_hh, b_ih, b_hh):
+    """nn.LSTMCell / one step of nn.LSTM (gate order i, f, g, o): vs/agent_models.py:380,414 ; :223-230."""
+    g = F.linear(x, w_ih, b_ih) + F.linear(h, w_hh, b_hh)
+    i, f, gg, o = g.chunk(4, 1)
+    c1 = torch.sigmoid(f) * c + torch.sigmoid(i) * torch.tanh(gg)
+    return torch.sigmoid(o) * torch.tanh(c1), c1
+
+
+def lstm_sequence(x, lengths, w_ih, w_hh, b_ih, b_hh):
+    """pack_padded_sequence -> nn.LSTM(batch_first) -> pad_packed_sequence, vs/agent_models.py:283-305, as an explicit loop:
+    sample b advances while t < lengths[b]; ctx is 0 behind its end and as long as the longest sample; (h, c) are the last
+    valid states.  x [B, T, in] -> ctx [B, max(lengths), H], h [B, H], c [B, H]."""
+    B, T, _ = x.shape
+    Hh = w_hh.size(1)
+    lengths = torch.as_tensor(lengths, device=x.device)
+    h = x.new_zeros(B, Hh)
+    c = x.new_zeros(B, Hh)
+    outs = []
+    for t in range(int(lengths.max())):
+        h1, c1 = lstm_cell(x[:, t], h, c, w_ih, w_hh, b_ih, b_hh)
+        live = (t < lengths)[:, None]
+        h, c = torch.where(live, h1, h), torch.where(live, c1, c)
+        outs.append(torch.where(live, h1, torch.zeros_like(h1)))
+    return torch.stack(outs, 1), h, c
+
+
+def oscar_encoder_forward(P: Params, cfg, A: Params, inputs, lengths, mask, token_type_ids=None, position_ids=None, drop=None,
+                          agent_drop=None, p_agent=0.5):
+    """OscarEncoder.forward, vs/agent_models.py:254-310 (hidden == decoder hidden: c_t is passed through, :300-301)."""
+    att_mask = ~mask                                                                               # :268 (uint8 -> 255, F6)
+    seq, _ = bert_img_forward(P, cfg, inputs, token_type_ids, att_mask, position_ids, drop=drop)   # :270-277
+    ctx, h_t, c_t = lstm_sequence(seq, lengths, A["lstm.weight_ih_l0"], A["lstm.weight_hh_l0"], A["lstm.bias_ih_l0"], A["lstm.bias_hh_l0"])
+    decoder_init = torch.tanh(F.linear(h_t, A["encoder_lstm2decoder_ht.weight"], A["encoder_lstm2decoder_ht.bias"]))   # :299
+    if agent_drop is not None:
+        ctx = agent_drop(ctx, p_agent)                                                             # :307
+    return ctx, decoder_init, c_t
+
+
+def attn_decoder_step_vs(D: Params, action, feature, cand_feat, h_0, prev_h1, c_0, ctx, ctx_mask=None, drop=None, p=0.5):
+    """AttnDecoderLSTM.forward of viewpoint select, vs/agent_models.py:384-428 -> (h_1, c_1, logit, h_tilde)."""
+    dr = (lambda t: drop(t, p)) if drop is not None else (lambda t: t)
+    action_embeds = dr(torch.tanh(F.linear(action, D["embedding.0.weight"], D["embedding.0.bias"])))
+    attn_feat, _ = soft_dot_attention(D["feat_att_layer.linear_in.weight"], None, dr(prev_h1), feature, output_tilde=False)
+    h_1, c_1 = lstm_cell(torch.cat((action_embeds, attn_feat), 1), prev_h1, c_0, D["lstm.weight_ih"], D["lstm.weight_hh"],
+                         D["lstm.bias_ih"], D["lstm.bias_hh"])
+    h_tilde, _ = soft_dot_attention(D["attention_layer.linear_in.weight"], D["attention_layer.linear_out.weight"], dr(h_1), ctx, ctx_mask)
+    _, logit = soft_dot_attention(D["candidate_att_layer.linear_in.weight"], None, dr(h_tilde), cand_feat, output_tilde=False,
+                                  output_prob=False)
+    return h_1, c_1, logit, h_tilde
+
+
+def attn_decoder_step_tb(D: Params, action, feature, h_0, c_0, ctx, ctx_mask=None, drop=None, p=0.5):
+    """AttnDecoderLSTM.forward of turn based, tb/agent_models.py:299-319 -> (h_1, c_1, alpha, logit)."""
+    dr = (lambda t: drop(t, p)) if drop is not None else (lambda t: t)
+    x = dr(torch.cat((D["embedding.weight"][action.view(-1)], feature), 1))
+    h_1, c_1 = lstm_cell(x, h_0, c_0, D["lstm.weight_ih"], D["lstm.weight_hh"], D["lstm.bias_ih"], D["lstm.bias_hh"])
+    h_tilde, alpha = soft_dot_attention(D["attention_layer.linear_in.weight"], D["attention_layer.linear_out.weight"], dr(h_1), ctx, ctx_mask)
+    return h_1, c_1, alpha, F.linear(h_tilde, D["decoder2action.weight"], D["decoder2action.bias"])
+
+
+def _feedback(logit, target, feedback):
+    if feedback == "teacher":
+        return target
+    if feedback == "argmax":
+        return logit.max(1)[1].detach()
+    raise ValueError("the oracle restates the deterministic feedback modes (teacher, argmax)")
+
+
+def rollout_vs(P, cfg, A, D, batch, trace, episode_len, feedback="teacher", ignore_index=-100):
+    """Agent.rollout of viewpoint select, vs/agent.py:334-474, over a RECORDED trace (observations per step instead of the
+    simulator): loss = sum_t CE(masked logit_t, target_t) / episode_len; a finished episode's targets are ignored."""
+    ctx, h_t, c_t = oscar_encoder_forward(P, cfg, A, batch["input_ids"], batch["lengths"], batch["mask"], batch["token_type_ids"])
+    ctx_mask = batch["mask"][:, :ctx.size(1)]
+    h1 = h_t
+    ended = torch.zeros(ctx.size(0), dtype=torch.bool, device=ctx.device)
+    loss, logits = 0.0, []
+    for t in range(episode_len):
+        h_t, c_t, logit, h1 = attn_decoder_step_vs(D, trace["input_a_t"][t], trace["f_t"][t], trace["cand_feat"][t], h_t, h1, c_t, ctx, ctx_mask)
+        leng = trace["cand_len"][t]
+        invalid = torch.arange(logit.size(1), device=leng.device)[None, :] >= leng[:, None]       # utils.length2mask, :396-403
+        logit = logit.masked_fill(invalid, -float("inf"))
+        target = torch.where(ended, torch.full_like(trace["target"][t], ignore_index), trace["target"][t])   # _teacher_action(obs, ended)
+        loss = loss + F.cross_entropy(logit, target, ignore_index=ignore_index)                    # :405-409
+        a_t = _feedback(logit, target, feedback)                                                   # :411-423
+        ended = ended | (a_t == leng - 1) | (a_t == ignore_index)                                  # :429-441
+        logits.append(logit)
+        if bool(ended.all()):                                                                      # :466-468
+            break
+    return loss / episode_len, logits                                                              # :472-474
+
+
+def rollout_tb(P, cfg, A, D, batch, trace, episode_len, feedback="teacher", ignore_index=7, start_action=6, end_action=5):
+    """Agent.rollout of turn based, tb/agent.py:259-392, over a recorded trace."""
+    ctx, h_t, c_t = oscar_encoder_forward(P, cfg, A, batch["input_ids"], batch["lengths"], batch["mask"], batch["token_type_ids"])
+    ctx_mask = batch["mask"][:, :ctx.size(1)]
+    B = ctx.size(0)
+    a_t = torch.full((B,), start_action, dtype=torch.long, device=ctx.device)                      # :287-290
+    ended = torch.zeros(B, dtype=torch.bool, device=ctx.device)
+    loss, logits = 0.0, []
+    for t in range(episode_len):
+        h_t, c_t, _, logit = attn_decoder_step_tb(D, a_t.view(-1, 1), trace["f_t"][t], h_t, c_t, ctx, ctx_mask)
+        logit = logit.clone()
+        logit[:, FORWARD_ACTION] = logit[:, FORWARD_ACTION].masked_fill(trace["no_forward"][t].bool(), -float("inf"))   # :316-318
+        target = torch.where(ended, torch.full_like(trace["target"][t], ignore_index), trace["target"][t])
+        loss = loss + F.cross_entropy(logit, target, ignore_index=ignore_index)
+        a_t = _feedback(logit, target, feedback)
+        ended = ended | (a_t == end_action)                                                        # :343-346
+        logits.append(logit)
+        if bool(ended.all()):                                                                      # :388-390
+            break
+    return loss / episode_len, logits
+
+
+def init_agent_params(seed: int, hidden: int = 512, feat: int = 2052, angle: int = 4, emb: int = 64, tb_feat: int = 2048, tb_emb: int = 32,
+                      scale: float = 0.05):
+    """Seeded weights of OscarEncoder's LSTM part (A), the viewpoint-select decoder (Dv) and the turn-based decoder (Dt); key names =
+    the reference modules' state_dict keys."""
+    g = torch.Generator().manual_seed(seed)
+    r = lambda *s: scale * torch.randn(*s, generator=g)  # noqa: E731
+    A = {"lstm.weight_ih_l0": r(4 * hidden, 768), "lstm.weight_hh_l0": r(4 * hidden, hidden), "lstm.bias_ih_l0": r(4 * hidden),
+         "lstm.bias_hh_l0": r(4 * hidden), "encoder_lstm2decoder_ht.weight": r(hidden, hidden), "encoder_lstm2decoder_ht.bias": r(hidden),
+         "encoder_lstm2decoder_ct.weight": r(hidden, hidden), "encoder_lstm2decoder_ct.bias": r(hidden)}
+    Dv = {"embedding.0.weight": r(emb, angle), "embedding.0.bias": r(emb), "lstm.weight_ih": r(4 * hidden, emb + feat),
+          "lstm.weight_hh": r(4 * hidden, hidden), "lstm.bias_ih": r(4 * hidden), "lstm.bias_hh": r(4 * hidden),
+          "feat_att_layer.linear_in.weight": r(feat, hidden), "feat_att_layer.linear_out.weight": r(hidden, hidden + feat),
+          "attention_layer.linear_in.weight": r(hidden, hidden), "attention_layer.linear_out.weight": r(hidden, 2 * hidden),
+          "candidate_att_layer.linear_in.weight": r(feat, hidden), "candidate_att_layer.linear_out.weight": r(hidden, hidden + feat)}
+    Dt = {"embedding.weight": r(8, tb_emb), "lstm.weight_ih": r(4 * hidden, tb_emb + tb_feat), "lstm.weight_hh": r(4 * hidden, hidden),
+          "lstm.bias_ih": r(4 * hidden), "lstm.bias_hh": r(4 * hidden), "attention_layer.linear_in.weight": r(hidden, hidden),
+          "attention_layer.linear_out.weight": r(hidden, 2 * hidden), "decoder2action.weight": r(6, hidden), "decoder2action.bias": r(6)}
+    return A, Dv, Dt
 
 
 def init_head_params(seed: int, hidden: int = 512, feat: int = 2052) -> Params:

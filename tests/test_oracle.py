@@ -204,3 +204,41 @@ def test_preprocess_item_oracle_matches_reference_fixture():
                 assert torch.equal(got[k], v), (c["n"], k)
             else:
                 assert got[k] == v or (k == "attention_mask" and [int(a) for a in v] == got[k]), (c["n"], k)
+
+
+@pytest.mark.parametrize("space", ["vs", "tb"])
+def test_agents_golden(space):
+    """the oracle's OscarEncoder LSTM, decoder steps and rollout loops against the fixture produced by the
+    UNMODIFIED OscarEncoder / AttnDecoderLSTM of tasks/{viewpoint_select,turn_based}/agent_models.py (teacher forcing, ragged
+    lengths through pack_padded_sequence, an episode that ends early)."""
+    fix = _load("agents_small")
+    cfg = vo.OracleConfig(**fix["cfg"])
+    seed, T, B, steps = fix["seed"], fix["T"], fix["B"], fix["steps"]
+    P = vo.clone_params(vo.init_params(cfg, seed, pretrain_heads=False))
+    A, Dv, Dt = vo.init_agent_params(seed + 1)
+    A, D = vo.clone_params(A), vo.clone_params(Dv if space == "vs" else Dt)
+    batch = synthetic.agent_batch(B, seed + 2, text_len=T, vocab=cfg.vocab_size, ragged=True)
+    ref = fix[space]
+    ctx, h0, c0 = vo.oscar_encoder_forward(P, cfg, A, batch["input_ids"], batch["lengths"], batch["mask"], batch["token_type_ids"])
+    torch.testing.assert_close(ctx, ref["ctx"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(h0, ref["decoder_init"], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(c0, ref["c_t"], rtol=1e-4, atol=1e-5)
+    if space == "vs":
+        trace = synthetic.viewpoint_trace(steps, B, seed + 3, candidates=6)
+        loss, logits = vo.rollout_vs(P, cfg, A, D, batch, trace, steps)
+    else:
+        trace = synthetic.turn_trace(steps, B, seed + 3)
+        loss, logits = vo.rollout_tb(P, cfg, A, D, batch, trace, steps)
+    assert len(logits) == len(ref["logits"])
+    for a, b in zip(logits, ref["logits"]):
+        torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5)
+    assert abs(float(loss) - ref["loss"]) <= 1e-5 * max(1.0, abs(ref["loss"]))
+    loss.backward()
+    for k, dig in ref["enc_grads"].items():
+        if k in ("encoder_lstm2decoder_ct.weight", "encoder_lstm2decoder_ct.bias"):
+            continue
+        _check_digest(k, A[k].grad, dig)
+    for k, dig in ref["dec_grads"].items():
+        _check_digest(k, D[k].grad, dig)
+    for k, dig in ref["bert_grads"].items():
+        _check_digest(k, P["bert." + k].grad, dig)

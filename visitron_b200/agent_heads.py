@@ -168,7 +168,7 @@ class SoftDotAttention(nn.Module):
 # ------------------------------------------------------------------------------------------------
 class _HeadCEFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, logits, valid_len, forbid0, target, ignore_index: int):
+    def forward(ctx, logits, valid_len, forbid0, target, ignore_index: int, forbid_col: int = 4, empty_is_zero: bool = False):
         lib.require_device(logits)
         L = init()
         logits = _f32c(logits)
@@ -181,7 +181,7 @@ class _HeadCEFn(torch.autograd.Function):
         lse = torch.empty(B, device=dev, dtype=F32)
         argmax = torch.empty(B, device=dev, dtype=torch.int64)
         out3 = torch.empty(3, device=dev, dtype=F32)
-        check(L.vt_head_ce_fwd(ptr(logits), logits.stride(0), B, C, ptr(vl), ptr(f0), ptr(target), ignore_index, ptr(masked), C, ptr(lse),
+        check(L.vt_head_ce_fwd(ptr(logits), logits.stride(0), B, C, ptr(vl), ptr(f0), forbid_col, int(empty_is_zero), ptr(target), ignore_index, ptr(masked), C, ptr(lse),
                                ptr(argmax), ptr(out3), stream_ptr()), "vt_head_ce_fwd")
         ctx.save_for_backward(masked, target, lse, out3)
         ctx.ignore_index = ignore_index
@@ -197,16 +197,20 @@ class _HeadCEFn(torch.autograd.Function):
         d = torch.empty_like(masked)
         check(L.vt_head_ce_bwd(ptr(masked), C, B, C, ptr(target), ctx.ignore_index, ptr(lse), ptr(out3), ptr(g), ptr(d), C, stream_ptr()),
               "vt_head_ce_bwd")
-        return d, None, None, None, None
+        return d, None, None, None, None, None, None
 
 
-def masked_cross_entropy(logit, target, valid_len=None, forbid_first=None, ignore_index: int = -100):
+FORWARD_ACTION = 4   # tb/agent.py:71-80: model_actions = [left, right, up, down, forward, <end>, <start>, <ignore>]
+
+
+def masked_cross_entropy(logit, target, valid_len=None, forbid=None, ignore_index: int = -100, forbid_col: int = FORWARD_ACTION,
+                         empty_is_zero: bool = False):
     """masked_fill(-inf) of the impossible actions + CrossEntropyLoss(ignore_index) + argmax in one pass.
 
     valid_len [B]: columns >= valid_len[b] are impossible (candidate_leng, vs/agent.py:396-403);
-    forbid_first [B] bool: column 0 ("forward") is impossible (tb/agent.py:316-318).
+    forbid [B] bool: column `forbid_col` (model_actions.index("forward") = 4) is impossible (tb/agent.py:316-318).
     Returns (loss, masked_logit, argmax)."""
-    return _HeadCEFn.apply(logit, valid_len, forbid_first, target, int(ignore_index))
+    return _HeadCEFn.apply(logit, valid_len, forbid, target, int(ignore_index), int(forbid_col), bool(empty_is_zero))
 
 
 class _BCEFn(torch.autograd.Function):
@@ -261,7 +265,7 @@ def turn_based_head(w_in, w_out, w_a, b_a, h, ctx, ctx_mask, no_forward, target,
     weighted, _, _ = _SoftDotFn.apply(ctx, t, ctx_mask)
     h_tilde = small_linear(weighted, w_out, act="tanh", x2=h)
     logit = small_linear(h_tilde, w_a, b_a)
-    loss, masked, am = masked_cross_entropy(logit, target, forbid_first=no_forward, ignore_index=ignore_index)
+    loss, masked, am = masked_cross_entropy(logit, target, forbid=no_forward, ignore_index=ignore_index)
     return h_tilde, masked, loss, am
 
 

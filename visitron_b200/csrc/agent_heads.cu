@@ -378,14 +378,15 @@ sum_partials_kernel(const float* __restrict__ part, int P, int D, float* __restr
 // ---------------------------------------------------------------------------------------------
 // Action-logit masking + CrossEntropyLoss(ignore_index, reduction = mean) + argmax over [B, C] fp32 logits:
 //   columns >= valid_len[b] -> -inf (utils.length2mask + masked_fill_, vs/agent.py:396-403);
-//   column 0 -> -inf where forbid0[b] (no navigable location: "forward" is impossible, tb/agent.py:316-318).
+//   column forbid_col (model_actions.index("forward") = 4, tb/agent.py:71-80) -> -inf where forbid[b] (no navigable location:
+//   "forward" is impossible, tb/agent.py:316-318).
 // One CTA (a decoder step has at most a few hundred rows); one warp per row; out3 = {loss, n_valid, sum of row losses}.
 // ---------------------------------------------------------------------------------------------
 constexpr int HCE_WARPS = 16;
 
 __global__ void __launch_bounds__(HCE_WARPS * 32)
 head_ce_fwd_kernel(const float* __restrict__ logits, long long ld, int B, int C, const long long* __restrict__ valid_len,
-                   const uint8_t* __restrict__ forbid0, const long long* __restrict__ target, long long ignore_index,
+                   const uint8_t* __restrict__ forbid0, int fcol, int empty_zero, const long long* __restrict__ target, long long ignore_index,
                    float* __restrict__ masked, long long ldm, float* __restrict__ lse_out, long long* __restrict__ argmax,
                    float* __restrict__ out3) {
   __shared__ float s_loss[HCE_WARPS];
@@ -400,7 +401,7 @@ head_ce_fwd_kernel(const float* __restrict__ logits, long long ld, int B, int C,
     int arg = 0x7fffffff;
     for (int c = lane; c < C; c += 32) {
       float v = logits[(long long)b * ld + c];
-      if (c >= vl || (f0 && c == 0)) v = -INFINITY;
+      if (c >= vl || (f0 && c == fcol)) v = -INFINITY;
       masked[(long long)b * ldm + c] = v;
       if (arg == 0x7fffffff || v > mx) { mx = v; arg = c; }  // c ascends within a lane: ties keep the lowest index
     }
@@ -413,7 +414,7 @@ head_ce_fwd_kernel(const float* __restrict__ logits, long long ld, int B, int C,
     float se = 0.f;
     for (int c = lane; c < C; c += 32) {
       float v = logits[(long long)b * ld + c];
-      if (c >= vl || (f0 && c == 0)) v = -INFINITY;
+      if (c >= vl || (f0 && c == fcol)) v = -INFINITY;
       se += expf(v - mx);
     }
     se = warp_sum(se);
@@ -424,7 +425,7 @@ head_ce_fwd_kernel(const float* __restrict__ logits, long long ld, int B, int C,
       argmax[b] = arg;
       if (t != ignore_index) {
         float vt_ = (t >= 0 && t < C) ? logits[(long long)b * ld + t] : NAN;
-        if (t >= vl || (f0 && t == 0)) vt_ = -INFINITY;
+        if (t >= vl || (f0 && t == fcol)) vt_ = -INFINITY;
         loss_acc += lse - vt_;
         cnt += 1;
       }
@@ -436,7 +437,9 @@ head_ce_fwd_kernel(const float* __restrict__ logits, long long ld, int B, int C,
     float tot = 0.f;
     int n = 0;
     for (int i = 0; i < HCE_WARPS; ++i) { tot += s_loss[i]; n += s_cnt[i]; }
-    out3[0] = tot / (float)n;  // 0/0 = nan when every row is ignored, like torch
+    // 0/0 = nan when every row is ignored, like torch -- unless the caller is a rollout, which the reference leaves before
+    // such a step (`if ended.all(): break`, vs/agent.py:466-468): the step then adds nothing
+    out3[0] = (n == 0 && empty_zero) ? 0.f : tot / (float)n;
     out3[1] = (float)n;
     out3[2] = tot;
   }
@@ -623,10 +626,10 @@ extern "C" int vt_softdot_bwd(const float* ctx, const float* target, const uint8
 }
 
 extern "C" int vt_head_ce_fwd(const float* logits, int64_t ld, int64_t B, int64_t C, const int64_t* valid_len, const uint8_t* forbid0,
-                              const int64_t* target, int64_t ignore_index, float* masked, int64_t ldm, float* lse, int64_t* argmax, float* out3,
+                              int64_t forbid_col, int empty_is_zero, const int64_t* target, int64_t ignore_index, float* masked, int64_t ldm, float* lse, int64_t* argmax, float* out3,
                               vt_stream stream) {
   VT_REQUIRE(logits && target && masked && lse && argmax && out3 && B > 0 && C > 0 && ld >= C && ldm >= C, "vt_head_ce_fwd: bad arguments");
-  head_ce_fwd_kernel<<<1, HCE_WARPS * 32, 0, (cudaStream_t)stream>>>(logits, ld, (int)B, (int)C, (const long long*)valid_len, forbid0,
+  head_ce_fwd_kernel<<<1, HCE_WARPS * 32, 0, (cudaStream_t)stream>>>(logits, ld, (int)B, (int)C, (const long long*)valid_len, forbid0, (int)forbid_col, empty_is_zero,
                                                                       (const long long*)target, (long long)ignore_index, masked, ldm, lse,
                                                                       (long long*)argmax, out3);
   count_launch(1);

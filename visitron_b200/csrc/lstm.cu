@@ -364,6 +364,64 @@ __global__ void dropout_f32_kernel(const float* __restrict__ x, long long n, Dro
   }
 }
 
+
+// nn.Embedding lookup of the turn-based decoder's previous action (tb/agent_models.py:292,308): y[b] = W[idx[b]]; backward
+// dW[v] = sum over b with idx[b] == v of dy[b], samples in ascending order (deterministic, no atomics; the vocabulary is 8)
+__global__ void embedding_f32_fwd_kernel(const float* __restrict__ W, const long long* __restrict__ idx, int B, int V, int D, float* __restrict__ y) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * D) return;
+  long long v = idx[i / D];
+  v = v < 0 ? 0 : (v >= V ? V - 1 : v);
+  y[i] = W[v * D + i % D];
+}
+__global__ void embedding_f32_bwd_kernel(const float* __restrict__ dy, const long long* __restrict__ idx, int B, int V, int D, float* __restrict__ dW) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= V * D) return;
+  const int v = i / D, d = i % D;
+  float acc = 0.f;
+  for (int b = 0; b < B; ++b)
+    if (idx[b] == v) acc += dy[(long long)b * D + d];
+  dW[i] = acc;
+}
+
+// Action feedback of one rollout step, on the device (vs/agent.py:410-441 ; tb/agent.py:329-346 do this on the host after a
+// .cpu() / .item() sync per step): a_t = the teacher's action | argmax of the masked logits | a sample of softmax(masked logits);
+// ended[b] |= a_t is the stop action (candidate_leng[b] - 1 when stop_len is given, else the constant <end>) or the ignore id;
+// next_target_eff[b] = ended[b] ? ignore : next_target[b]  (what _teacher_action(obs, ended) returns for a finished episode).
+__global__ void rollout_feedback_kernel(const float* __restrict__ logits, long long ld, int B, int C, const long long* __restrict__ target,
+                                        const long long* __restrict__ stop_len, long long stop_const, long long ignore, int mode,
+                                        DropoutCfg rng, unsigned step, unsigned char* __restrict__ ended, long long* __restrict__ a_out,
+                                        const long long* __restrict__ next_target, long long* __restrict__ next_target_eff) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  rng = resolve_dropout(rng);
+  const float* x = logits + (long long)b * ld;
+  long long a = target[b];
+  if (mode != 0) {
+    float mx = -INFINITY;
+    int arg = 0;
+    for (int c = 0; c < C; ++c)
+      if (x[c] > mx) { mx = x[c]; arg = c; }          // ties keep the lowest index, like torch.max
+    a = arg;
+    if (mode == 2) {
+      float se = 0.f;
+      for (int c = 0; c < C; ++c) se += __expf(x[c] - mx);
+      const uint4 r = philox4x32<7>(make_uint4((unsigned)b, step, 0x5a3c1eu, rng.stream), make_uint2(rng.seed_lo, rng.seed_hi));
+      const float u = (float)(r.x >> 8) * (1.0f / 16777216.0f) * se;   // uniform in [0, sum)
+      float cum = 0.f;
+      for (int c = 0; c < C; ++c) {
+        const float e = __expf(x[c] - mx);
+        if (e > 0.f) { a = c; cum += e; if (u < cum) break; }
+      }
+    }
+  }
+  const long long stop = stop_len ? stop_len[b] - 1 : stop_const;
+  const bool fin = ended[b] || a == stop || a == ignore;
+  ended[b] = fin ? 1 : 0;
+  a_out[b] = a;
+  if (next_target_eff) next_target_eff[b] = fin ? ignore : next_target[b];
+}
+
 }  // namespace lstm
 }  // namespace vt
 
@@ -441,6 +499,38 @@ extern "C" int vt_dropout_f32(const float* x, int64_t n, float dropout_p, uint64
   const long long groups = (n + 7) / 8;
   long long g = (groups + 255) / 256, cap = (long long)num_sms() * 8;
   dropout_f32_kernel<<<(unsigned)(g < cap ? g : cap), 256, 0, (cudaStream_t)stream>>>(x, (long long)n, make_dropout(dropout_p, seed, dropout_stream), y);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_embedding_f32_fwd(const float* W, const int64_t* idx, int64_t B, int64_t V, int64_t D, float* y, vt_stream stream) {
+  VT_REQUIRE(W && idx && y && B >= 0 && V > 0 && D > 0 && B * D < (1ll << 31), "vt_embedding_f32_fwd: bad arguments");
+  if (B == 0) return VT_OK;
+  const int n = (int)(B * D);
+  embedding_f32_fwd_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(W, (const long long*)idx, (int)B, (int)V, (int)D, y);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_embedding_f32_bwd(const float* dy, const int64_t* idx, int64_t B, int64_t V, int64_t D, float* dW, vt_stream stream) {
+  VT_REQUIRE(dy && idx && dW && B >= 0 && V > 0 && D > 0 && V * D < (1ll << 31), "vt_embedding_f32_bwd: bad arguments");
+  const int n = (int)(V * D);
+  embedding_f32_bwd_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(dy, (const long long*)idx, (int)B, (int)V, (int)D, dW);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_rollout_feedback(const float* masked_logits, int64_t ld, int64_t B, int64_t C, const int64_t* target, const int64_t* stop_len,
+                                   int64_t stop_const, int64_t ignore_index, int mode, uint64_t seed, uint32_t rng_stream, uint32_t step,
+                                   uint8_t* ended, int64_t* a_out, const int64_t* next_target, int64_t* next_target_eff, vt_stream stream) {
+  VT_REQUIRE(masked_logits && target && ended && a_out && B > 0 && C > 0 && ld >= C && mode >= 0 && mode <= 2, "vt_rollout_feedback: bad arguments");
+  VT_REQUIRE(!next_target_eff || next_target, "vt_rollout_feedback: next_target_eff needs next_target");
+  rollout_feedback_kernel<<<(unsigned)((B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+      masked_logits, ld, (int)B, (int)C, (const long long*)target, (const long long*)stop_len, (long long)stop_const, (long long)ignore_index, mode,
+      make_dropout(0.5f, seed, rng_stream), step, ended, (long long*)a_out, (const long long*)next_target, (long long*)next_target_eff);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;

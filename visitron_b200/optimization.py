@@ -47,15 +47,19 @@ class _Table:
         self.stores = {}
 
     def update(self, entries, device, with_shadow: bool = False) -> "_Table":
-        shadows = [None] * len(entries)
+        base = tuple((p.data_ptr(), g.data_ptr(), 0 if m is None else m.data_ptr(), p.numel(), grp) for p, g, m, _, grp in entries)
         if with_shadow:
             from . import flat
-            shadows = [flat.shadow_of(e[0]) for e in entries]
-        key = tuple((p.data_ptr(), g.data_ptr(), 0 if m is None else m.data_ptr(), p.numel(), grp, 0 if sh is None else sh[1].data_ptr())
-                    for (p, g, m, _, grp), sh in zip(entries, shadows))
-        self.stores = {id(sh[0]): sh[0] for sh in shadows if sh is not None}
+            live = tuple((id(st), 0 if st.bf16 is None else st.bf16.data_ptr()) for st in list(flat._STORES))
+        else:
+            live = ()
+        key = (base, live)     # the shadow pointers are a function of the parameter pointers and of the stores' bf16 buffers
         if key == self.key:
             return self
+        shadows = [None] * len(entries)
+        if with_shadow:
+            shadows = [flat.shadow_of(e[0]) for e in entries]
+        self.stores = {id(sh[0]): sh[0] for sh in shadows if sh is not None}
         chunk = int(lib.load().vt_opt_chunk())
         arr = (_Segment * len(entries))()
         first = 0

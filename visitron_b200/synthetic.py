@@ -132,6 +132,65 @@ def turn_step_batch(batch: int, seed: int = 88, ctx_len: int = 511, hidden: int 
     ctx_mask = torch.arange(ctx_len)[None, :] >= lens[:, None]
     no_forward = torch.rand(batch, generator=g) < 0.25
     target = torch.randint(0, 6, (batch,), generator=g)
-    target = torch.where(no_forward & (target == 0), torch.ones_like(target), target)
+    target = torch.where(no_forward & (target == 4), torch.ones_like(target), target)   # the teacher never goes "forward" (4) where it is impossible
     target[-1] = 7  # <ignore>
     return dict(h=h, ctx=ctx, ctx_mask=ctx_mask, no_forward=no_forward, target=target)
+
+
+def agent_batch(batch: int, seed: int = 88, text_len: int = 511, vocab: int = 30522, ragged: bool = False) -> Dict[str, torch.Tensor]:
+    """What Agent._sort_batch hands to OscarEncoder (vs/agent.py:143-184): ids, segment ids, the uint8 padding mask and the lengths.
+    Default = the scripts' situation (SURVEY.md F6: no id equals pad_token_id, every length is 511, the mask is all zero);
+    ragged=True draws shorter samples with a real padding mask, sorted by descending length as pack_padded_sequence needs."""
+    enc = finetune_encoder_batch(batch, seed, text_len=text_len, vocab=vocab)
+    g = torch.Generator().manual_seed(seed + 7)
+    if ragged:
+        lengths = torch.randint(max(2, text_len // 3), text_len + 1, (batch,), generator=g).sort(descending=True).values
+        lengths[0] = text_len
+    else:
+        lengths = torch.full((batch,), text_len, dtype=torch.long)
+    mask = (torch.arange(text_len)[None, :] >= lengths[:, None]).to(torch.uint8)
+    return dict(input_ids=enc["input_ids"], token_type_ids=enc["token_type_ids"], mask=mask, lengths=lengths)
+
+
+def viewpoint_trace(steps: int, batch: int, seed: int = 88, candidates: int = 12, feat: int = 2052, views: int = 36,
+                    angle: int = 4) -> Dict[str, torch.Tensor]:
+    """A recorded viewpoint-select episode (vs/agent.py:186-228,380-441): per step the heading feature, the 36 view features, the
+    candidate features (zero beyond candidate_leng, the last valid one = <end> = zeros) and the teacher's action; an episode ends
+    when the teacher picks <end>, after which its targets are the ignore id -100."""
+    g = torch.Generator().manual_seed(seed)
+    leng = torch.randint(2, candidates + 1, (steps, batch), generator=g)
+    cand = 0.3 * torch.randn(steps, batch, candidates, feat, generator=g)
+    c_idx = torch.arange(candidates)[None, None, :, None]
+    cand = cand * (c_idx < (leng - 1)[:, :, None, None])          # the <end> candidate and the padding are zero rows
+    f_t = 0.3 * torch.randn(steps, batch, views, feat, generator=g)
+    heading = torch.rand(steps, batch, generator=g) * 6.283
+    elev = (torch.rand(steps, batch, generator=g) - 0.5)
+    a_in = torch.stack([heading.sin(), heading.cos(), elev.sin(), elev.cos()], -1)[..., :angle]
+    target = (torch.rand(steps, batch, generator=g) * leng).long().clamp(max=candidates - 1)
+    end_at = torch.randint(max(1, steps // 2), steps + 1, (batch,), generator=g)       # the step at which the teacher stops
+    for b in range(batch):
+        e = int(end_at[b])
+        for t in range(steps):
+            if t == e - 1:
+                target[t, b] = leng[t, b] - 1
+            elif t >= e:
+                target[t, b] = -100
+            elif target[t, b] == leng[t, b] - 1:
+                target[t, b] = 0
+    return dict(input_a_t=a_in.contiguous(), f_t=f_t, cand_feat=cand, cand_len=leng, target=target)
+
+
+def turn_trace(steps: int, batch: int, seed: int = 88, feat: int = 2048) -> Dict[str, torch.Tensor]:
+    """A recorded turn-based episode (tb/agent.py:301-346): per step the single-view feature, whether "forward" is impossible and the
+    teacher's action in [left, right, up, down, forward, <end>]; after <end> the targets are <ignore> = 7."""
+    g = torch.Generator().manual_seed(seed)
+    f_t = 0.3 * torch.randn(steps, batch, feat, generator=g)
+    no_forward = torch.rand(steps, batch, generator=g) < 0.25
+    target = torch.randint(0, 5, (steps, batch), generator=g)
+    target = torch.where(no_forward & (target == 4), torch.ones_like(target), target)
+    end_at = torch.randint(max(1, steps // 2), steps + 1, (batch,), generator=g)
+    for b in range(batch):
+        e = int(end_at[b])
+        target[e - 1, b] = 5
+        target[e:, b] = 7
+    return dict(f_t=f_t, no_forward=no_forward, target=target)
