@@ -322,10 +322,11 @@ def gen_agents(ns, name, seed):
     import types
     cfg = small_cfg()
     P = vo.init_params(cfg, seed, pretrain_heads=False)
-    A, Dv, Dt = vo.init_agent_params(seed + 1)
+    scale = 0.02      # ~ nn.Linear's default init range for a 2052-wide input: logits of O(1), as in a trained agent
+    A, Dv, Dt = vo.init_agent_params(seed + 1, scale=scale)
     T, B, steps = 48, 3, 4
     args = types.SimpleNamespace(device="cpu")
-    fix = dict(kind="agents", cfg=cfg.__dict__, seed=seed, T=T, B=B, steps=steps)
+    fix = dict(kind="agents", cfg=cfg.__dict__, seed=seed, T=T, B=B, steps=steps, scale=scale)
     for space in ("vs", "tb"):
         mods = ns.vs_models if space == "vs" else ns.tb_models
         bert = ns.BertImgModelwithLocationEmbeds(ref_shim.make_config(ns, cfg))

@@ -430,7 +430,8 @@ def rollout_vs(P, cfg, A, D, batch, trace, episode_len, feedback="teacher", igno
         invalid = torch.arange(logit.size(1), device=leng.device)[None, :] >= leng[:, None]       # utils.length2mask, :396-403
         logit = logit.masked_fill(invalid, -float("inf"))
         target = torch.where(ended, torch.full_like(trace["target"][t], ignore_index), trace["target"][t])   # _teacher_action(obs, ended)
-        loss = loss + F.cross_entropy(logit, target, ignore_index=ignore_index)                    # :405-409
+        if bool((target != ignore_index).any()):    # (a recorded trace can ignore every sample of a step; the live teacher cannot)
+            loss = loss + F.cross_entropy(logit, target, ignore_index=ignore_index)                # :405-409
         a_t = _feedback(logit, target, feedback)                                                   # :411-423
         ended = ended | (a_t == leng - 1) | (a_t == ignore_index)                                  # :429-441
         logits.append(logit)
@@ -452,7 +453,8 @@ def rollout_tb(P, cfg, A, D, batch, trace, episode_len, feedback="teacher", igno
         logit = logit.clone()
         logit[:, FORWARD_ACTION] = logit[:, FORWARD_ACTION].masked_fill(trace["no_forward"][t].bool(), -float("inf"))   # :316-318
         target = torch.where(ended, torch.full_like(trace["target"][t], ignore_index), trace["target"][t])
-        loss = loss + F.cross_entropy(logit, target, ignore_index=ignore_index)
+        if bool((target != ignore_index).any()):
+            loss = loss + F.cross_entropy(logit, target, ignore_index=ignore_index)
         a_t = _feedback(logit, target, feedback)
         ended = ended | (a_t == end_action)                                                        # :343-346
         logits.append(logit)

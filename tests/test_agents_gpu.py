@@ -21,6 +21,20 @@ def _dev(d):
     return {k: (v.to(DEV) if torch.is_tensor(v) else v) for k, v in d.items()}
 
 
+def _logit_tol(r):
+    """Action logits are bilinear scores cand . (W h~) of magnitude ~10 here; their bf16-level error scales with the ROW's scale,
+    so the tolerance is the absolute logit tolerance plus 2 % of the row's largest finite magnitude."""
+    fin = torch.isfinite(r)
+    return 2 * LOGIT_TOL + 2e-2 * torch.where(fin, r.abs(), torch.zeros_like(r)).max(1, keepdim=True).values
+
+
+def _logits_close(mine, r, t):
+    fin = torch.isfinite(r)
+    assert torch.equal(torch.isfinite(mine), fin), t
+    err = torch.where(fin, (mine - r).abs(), torch.zeros_like(r))
+    assert bool((err <= _logit_tol(r)).all()), (t, float(err.max()))
+
+
 def _build(oc, P, A, D, space, dropout=0.0):
     bert = modeling.BertImgModelwithLocationEmbeds(make_config(oc))
     bert.load_state_dict({k[len("bert."):]: v.clone() for k, v in P.items()}, strict=True)
@@ -68,7 +82,7 @@ def test_agents_golden_fixture(space):
     oc = vo.OracleConfig(**fix["cfg"])
     seed, T, B, steps = fix["seed"], fix["T"], fix["B"], fix["steps"]
     P = vo.init_params(oc, seed, pretrain_heads=False)
-    A, Dv, Dt = vo.init_agent_params(seed + 1)
+    A, Dv, Dt = vo.init_agent_params(seed + 1, scale=fix["scale"])
     D = Dv if space == "vs" else Dt
     enc, dec = _build(oc, P, A, D, space)
     batch = _dev(synthetic.agent_batch(B, seed + 2, text_len=T, vocab=oc.vocab_size, ragged=True))
@@ -85,9 +99,9 @@ def test_agents_golden_fixture(space):
         mine = logits[t].cpu()
         fin = torch.isfinite(r)
         assert torch.equal(torch.isfinite(mine), fin)
-        assert float((mine[fin] - r[fin]).abs().max()) < 2 * LOGIT_TOL, t
+        _logits_close(mine, r, t)
         top2 = r.topk(2, 1).values
-        decided = (top2[:, 0] - top2[:, 1]) > 4 * LOGIT_TOL
+        decided = (top2[:, 0] - top2[:, 1]) > 2 * _logit_tol(r)[:, 0]
         assert torch.equal(mine.argmax(1)[decided], r.argmax(1)[decided])
     loss.backward()
     got = dict(enc.named_parameters())
@@ -130,7 +144,7 @@ def test_rollout_vs_oracle_full_length(space, B, feedback):
     if feedback == "teacher":     # under argmax a near-tie may legitimately pick another action and change the later steps
         for t, r in enumerate(rlogits):
             fin = torch.isfinite(r)
-            assert float((logits[t][fin] - r[fin]).abs().max()) < 2 * LOGIT_TOL, t
+            _logits_close(logits[t], r, t)
     worst = 0.0
     for k, p in list(enc.named_parameters()) + list(dec.named_parameters()):
         if k.startswith("bert."):

@@ -215,7 +215,7 @@ def test_agents_golden(space):
     cfg = vo.OracleConfig(**fix["cfg"])
     seed, T, B, steps = fix["seed"], fix["T"], fix["B"], fix["steps"]
     P = vo.clone_params(vo.init_params(cfg, seed, pretrain_heads=False))
-    A, Dv, Dt = vo.init_agent_params(seed + 1)
+    A, Dv, Dt = vo.init_agent_params(seed + 1, scale=fix["scale"])
     A, D = vo.clone_params(A), vo.clone_params(Dv if space == "vs" else Dt)
     batch = synthetic.agent_batch(B, seed + 2, text_len=T, vocab=cfg.vocab_size, ragged=True)
     ref = fix[space]
