@@ -128,6 +128,7 @@ def build_model(args, device):
 
 
 VS_STEPS, VS_CAND, VS_FEAT, VS_HID = 10, 12, 2052, 512   # decoder steps, candidates incl. STOP, 2048+4 features, LSTM width
+AGENT_DROPOUT = 0.5                                      # --dropout of the agents' modules (vs/params.py:300, every run script)
 TB_STEPS = 40                                            # turn_based episode length (run_scripts/turn_based_train/ndh_rxr.sh)
 
 
@@ -135,73 +136,62 @@ class Workload:
     """One step of the hot path for `--workload`: host batches, the step function and the algorithmic FLOPs."""
 
     def __init__(self, args, device, rank, world):
-        from visitron_b200 import agent_heads, synthetic
+        from visitron_b200 import agent_heads, agent_models, synthetic
         self.args, self.device, self.world = args, device, world
         self.model = build_model(args, device)
         b, n_host = args.batch, 4
         self.extra_params = []
         self.flop_mult = 3.0   # forward + backward
-        if args.workload == "viewpoint_select":
-            # BASELINE configs[1]: the encoder call of OscarEncoder (A13, S = 511 text-only, token types, the ~uint8 mask)
-            # + the candidate scorer with its masked CE (A14) at each of the 10 decoder steps.  The stock torch.nn LSTM
-            # encoder / decoder between them is SURVEY 8f-N1 (not built): the decoder state of step t is stood in for by
-            # sequence_output[:, t, :512], which keeps every head gradient flowing into the encoder.
-            g = torch.Generator().manual_seed(88)
-            self.w_in = torch.nn.Parameter((0.02 * torch.randn(VS_FEAT, VS_HID, generator=g)).to(device))
-            self.extra_params = [self.w_in]
+        self.S, self.R = 511, 0
+        self.labelled = (0.0, 0.0)
+        self.trace = None
+        wk = args.workload
+        if wk in ("viewpoint_select", "turn_based"):
+            # BASELINE configs[1] / configs[3]: one fine-tuning iteration of the reference's agent (vs/agent.py:493-518, tb/agent.py:
+            # 405-430) -- OscarEncoder (encoder at S = 511 text-only with token types and the ~uint8 mask, the 511-step LSTM, the
+            # decoder's initial state), then the rollout of AttnDecoderLSTM over a recorded trace on the device (10 steps of
+            # feature attention over 36 views + LSTMCell + context attention over 511 + candidate scorer over 12 candidates; resp.
+            # 40 steps of action embedding + LSTMCell + context attention + 6-way logits), teacher forcing, masked CE per step,
+            # loss / episode_len, backward through everything.  Dropout: the encoder's --drop_out, the agent modules' 0.5.
+            torch.manual_seed(88)
+            steps = VS_STEPS if wk == "viewpoint_select" else TB_STEPS
+            self.steps = steps
+            self.encoder = agent_models.OscarEncoder(None, self.model, VS_HID, VS_HID, AGENT_DROPOUT if args.dropout > 0 else 0.0).to(device).train()
+            if wk == "viewpoint_select":
+                self.decoder = agent_models.AttnDecoderLSTM(4, 64, VS_HID, AGENT_DROPOUT if args.dropout > 0 else 0.0, VS_FEAT).to(device).train()
+                mk = lambda i: synthetic.viewpoint_trace(steps, b, seed=88 + rank + 1000 * i, candidates=VS_CAND, feat=VS_FEAT)  # noqa: E731
+                dec_flops = (2 * 4 * 64 + 2 * VS_HID * VS_FEAT + 4 * 36 * VS_FEAT + 2 * (64 + VS_FEAT + VS_HID) * 4 * VS_HID
+                             + 2 * VS_HID * VS_HID + 4 * 511 * VS_HID + 4 * VS_HID * VS_HID + 2 * VS_HID * VS_FEAT + 2 * VS_CAND * VS_FEAT)
+            else:
+                self.decoder = agent_models.TurnAttnDecoderLSTM(8, 6, 32, VS_HID, AGENT_DROPOUT if args.dropout > 0 else 0.0, 2048).to(device).train()
+                mk = lambda i: synthetic.turn_trace(steps, b, seed=88 + rank + 1000 * i)  # noqa: E731
+                dec_flops = (2 * (32 + 2048 + VS_HID) * 4 * VS_HID + 2 * VS_HID * VS_HID + 4 * 511 * VS_HID + 4 * VS_HID * VS_HID + 2 * 6 * VS_HID)
+            for m in (self.encoder, self.decoder):      # nn.LSTM / nn.Linear default init
+                pass
+            self.extra_params = [p for n, p in self.encoder.named_parameters() if not n.startswith("bert.")] + list(self.decoder.parameters())
             host = []
             for i in range(n_host):
-                hb = synthetic.finetune_encoder_batch(b, seed=88 + rank + 1000 * i)
-                steps = [synthetic.viewpoint_step_batch(b, seed=88 + rank + 1000 * i + 17 * t, candidates=VS_CAND, feat=VS_FEAT) for t in range(VS_STEPS)]
-                hb["cand_feat"] = torch.stack([s["cand_feat"] for s in steps])       # [10, b, 12, 2052]
-                hb["cand_len"] = torch.stack([s["cand_len"] for s in steps])
-                hb["target"] = torch.stack([s["target"] for s in steps])
+                hb = synthetic.agent_batch(b, seed=88 + rank + 1000 * i)     # the scripts' situation: every length 511, mask all zero (F6)
+                hb.update(mk(i))
                 host.append(hb)
-            self.S, self.R = 511, 0
-            self.labelled = (0.0, 0.0)
-            self.heads_flops = VS_STEPS * (2 * VS_HID * VS_FEAT + 2 * VS_CAND * VS_FEAT)
-            self.desc = ("viewpoint_select_step: BertImgModelwithLocationEmbeds fwd+bwd as OscarEncoder calls it (T=511 text-only, token types, "
-                         "~uint8 mask) + SoftDotAttention candidate scorer + masked CE at 10 decoder steps (12 candidates x 2052), bert-base "
-                         "random init [BASELINE configs[1]; the stock LSTM encoder/decoder of the agent is not part of the path, SURVEY 8f-N1]")
-        elif args.workload in ("turn_based", "qa_classifier"):
-            # BASELINE configs[3]: the encoder at the full RxR text length + the turn-based head (context attention over the 511
-            # positions -> h~ -> 6-way logits, forward masked where no location is navigable, CE(ignore 7)) at 40 decoder steps.
+            lstm_flops = 511 * 2 * (768 + VS_HID) * 4 * VS_HID
+            self.heads_flops = lstm_flops + steps * dec_flops
+        elif wk == "qa_classifier":
             # BASELINE configs[4]: the encoder forward-only under no_grad + question_linear / masked BCE forward + backward
-            # (vs/classifier/agent.py:158-163,493-503), swept over --batch.  The agent's LSTM encoder / decoder (SURVEY 8f-N1) is
-            # stood in for by slices of sequence_output as in viewpoint_select.
+            # (vs/classifier/agent.py:158-163,493-503), swept over --batch.
             g = torch.Generator().manual_seed(88)
             mk = lambda *s: torch.nn.Parameter((0.05 * torch.randn(*s, generator=g)).to(device))  # noqa: E731
-            if args.workload == "turn_based":
-                self.tb = dict(w_in=mk(VS_HID, VS_HID), w_out=mk(VS_HID, 2 * VS_HID), w_a=mk(6, VS_HID), b_a=mk(6))
-                self.extra_params = list(self.tb.values())
-            else:
-                self.qa = dict(w1=mk(VS_HID // 2, VS_HID), b1=mk(VS_HID // 2), w2=mk(1, VS_HID // 2), b2=mk(1))
-                self.extra_params = list(self.qa.values())
+            self.qa = dict(w1=mk(VS_HID // 2, VS_HID), b1=mk(VS_HID // 2), w2=mk(1, VS_HID // 2), b2=mk(1))
+            self.extra_params = list(self.qa.values())
             host = []
             for i in range(n_host):
                 hb = synthetic.finetune_encoder_batch(b, seed=88 + rank + 1000 * i, valid_len=511)
                 gi = torch.Generator().manual_seed(88 + rank + 1000 * i)
-                if args.workload == "turn_based":
-                    hb["no_forward"] = torch.rand(TB_STEPS, b, generator=gi) < 0.25
-                    tgt = torch.randint(0, 6, (TB_STEPS, b), generator=gi)
-                    hb["target"] = torch.where(hb["no_forward"] & (tgt == 4), torch.ones_like(tgt), tgt)
-                    hb["target"][:, -1] = 7   # an ended episode: <ignore>
-                else:
-                    hb["target"] = (torch.rand(b, generator=gi) < 0.4).float()
-                    hb["valid"] = (torch.rand(b, generator=gi) >= 0.25).to(torch.uint8)
+                hb["target"] = (torch.rand(b, generator=gi) < 0.4).float()
+                hb["valid"] = (torch.rand(b, generator=gi) >= 0.25).to(torch.uint8)
                 host.append(hb)
-            self.S, self.R = 511, 0
-            self.labelled = (0.0, 0.0)
-            if args.workload == "turn_based":
-                self.heads_flops = TB_STEPS * 2 * (VS_HID * VS_HID + 2 * 511 * VS_HID + 2 * VS_HID * VS_HID + 6 * VS_HID)
-                self.desc = ("turn_based_step: encoder fwd+bwd at the full RxR text length (T=511 valid tokens) + turn-based head (SoftDotAttention over "
-                             "the 511 context positions, tanh(W_out[.;h]), 6-way logits, forward masked, CE ignore 7) at 40 decoder steps, bert-base "
-                             "random init [BASELINE configs[3]; LSTM encoder/decoder stood in for by slices of sequence_output, SURVEY 8f-N1]")
-            else:
-                self.heads_flops = 2 * (VS_HID * VS_HID // 2 + VS_HID // 2)
-                self.flop_mult = 1.0
-                self.desc = ("qa_classifier_step: encoder forward-only under no_grad (T=511) + question_linear (512->256->1, tanh) with "
-                             "BCEWithLogits(pos_weight 5) masked mean, forward + backward [BASELINE configs[4]: sweep --batch]")
+            self.heads_flops = 2 * (VS_HID * VS_HID // 2 + VS_HID // 2)
+            self.flop_mult = 1.0
         else:
             host = [synthetic.pretrain_batch(b, seed=88 + rank + 1000 * i) for i in range(n_host)]  # per-rank shard, seed 88+rank
             if args.feat_bf16:   # a bf16 feature cache (SURVEY 8f-N4): half the H2D bytes; the default is the loader's fp32
@@ -211,9 +201,6 @@ class Workload:
             self.labelled = (sum(int((hb["labels"] != -1).sum()) for hb in host) / (n_host * b),
                              sum(int((hb["token_labels"] != -1).sum()) for hb in host) / (n_host * b))
             self.heads_flops = None
-            self.desc = ("pretrain_step: PreTrainOscar fwd+bwd, bert-base random init, NDH-shaped batch (T=511 text + R=256 region slots, "
-                         "img_feature_dim 2054, 15% MLM + masked detector-class + 36-way action labels), all objectives [BASELINE configs[2]; "
-                         "configs[1] = --workload viewpoint_select]")
         self.host = [{k: v.pin_memory() for k, v in hb.items()} for hb in host]
         self.n_host = n_host
         self.params = list(self.model.parameters()) + self.extra_params
@@ -230,22 +217,12 @@ class Workload:
             q = self.qa
             _, loss = self._heads.qa_head(q["w1"], q["b1"], q["w2"], q["b2"], seq[:, 0, :VS_HID], batch["target"], batch["valid"])
             return (loss,)
-        seq, _ = self.model(batch["input_ids"], token_type_ids=batch["token_type_ids"], attention_mask=batch["attention_mask"])
-        loss = None
+        from visitron_b200 import rollout
+        enc_batch = dict(input_ids=batch["input_ids"], token_type_ids=batch["token_type_ids"], mask=batch["mask"], lengths=batch["lengths"])
         if wk == "turn_based":
-            ctx = seq[:, :, :VS_HID].contiguous()
-            ctx_mask = torch.zeros(ctx.shape[:2], dtype=torch.bool, device=ctx.device)
-            t_ = self.tb
-            dec = seq[:, :TB_STEPS, :VS_HID].contiguous()   # the stand-in decoder states: ONE slice of the encoder output, not one per step
-            for t in range(TB_STEPS):
-                _, _, l, _ = self._heads.turn_based_head(t_["w_in"], t_["w_out"], t_["w_a"], t_["b_a"], dec[:, t], ctx, ctx_mask,
-                                                         batch["no_forward"][t], batch["target"][t])
-                loss = l if loss is None else loss + l
-            return (loss,)
-        dec = seq[:, :VS_STEPS, :VS_HID].contiguous()   # the stand-in decoder states: ONE slice of the encoder output, not one per step
-        for t in range(VS_STEPS):
-            _, l, _ = self._heads.candidate_scores_ce(self.w_in, dec[:, t], batch["cand_feat"][t], batch["cand_len"][t], batch["target"][t])
-            loss = l if loss is None else loss + l
+            loss, _ = rollout.turn_based_rollout(self.encoder, self.decoder, enc_batch, batch, self.steps)
+        else:
+            loss, _ = rollout.viewpoint_rollout(self.encoder, self.decoder, enc_batch, batch, self.steps)
         return (loss,)
 
     def post_backward(self):
@@ -274,24 +251,24 @@ class Workload:
 def workload_desc(args):
     wk = args.workload
     if wk == "viewpoint_select":
-        return ("viewpoint_select_step: BertImgModelwithLocationEmbeds fwd+bwd as OscarEncoder calls it (T=511 text-only, token types, "
-                "~uint8 mask) + SoftDotAttention candidate scorer + masked CE at 10 decoder steps (12 candidates x 2052), bert-base "
-                "random init [BASELINE configs[1]; the agent's LSTM encoder/decoder are timed by --workload agent_vs, SURVEY 8f-N1]"), 511
+        return ("viewpoint_select_step: one fine-tuning iteration of the viewpoint-select agent (vs/agent.py:493-518): OscarEncoder (encoder "
+                "fwd+bwd at T=511 text-only with token types and the ~uint8 mask, nn.LSTM 768->512 over the 511 positions, decoder init) + "
+                "AttnDecoderLSTM rollout over a device-resident trace, 10 steps (attention over 36 views x 2052, LSTMCell, attention over the "
+                "511 context positions, SoftDotAttention candidate scorer over 12 candidates), teacher forcing, masked CE, bert-base random "
+                "init [BASELINE configs[1]]"), 511
     if wk == "turn_based":
-        return ("turn_based_step: encoder fwd+bwd at the full RxR text length (T=511 valid tokens) + turn-based head (SoftDotAttention over "
-                "the 511 context positions, tanh(W_out[.;h]), 6-way logits, forward masked, CE ignore 7) at 40 decoder steps, bert-base "
-                "random init [BASELINE configs[3]; the agent's LSTM encoder/decoder are timed by --workload agent_tb, SURVEY 8f-N1]"), 511
+        return ("turn_based_step: one fine-tuning iteration of the turn-based agent (tb/agent.py:405-430) at the full RxR text length "
+                "(T=511): OscarEncoder (encoder fwd+bwd, nn.LSTM 768->512 over 511 positions) + AttnDecoderLSTM rollout over a "
+                "device-resident trace, 40 steps (action embedding, LSTMCell over [32 ; 2048], attention over the 511 context positions, "
+                "6-way logits, forward masked, CE ignore 7), teacher forcing, bert-base random init [BASELINE configs[3]]"), 511
     if wk == "qa_classifier":
         return ("qa_classifier_step: encoder forward-only under no_grad (T=511) + question_linear (512->256->1, tanh) with "
                 "BCEWithLogits(pos_weight 5) masked mean, forward + backward [BASELINE configs[4]: sweep --batch]"), 511
-    if wk in ("agent_vs", "agent_tb"):
-        return AGENT_DESC[wk], 511
     return ("pretrain_step: PreTrainOscar fwd+bwd, bert-base random init, NDH-shaped batch (T=511 text + R=256 region slots, "
             "img_feature_dim 2054, 15% MLM + masked detector-class + 36-way action labels), all objectives [BASELINE configs[2]; "
             "configs[1] = --workload viewpoint_select]"), 767
 
 
-AGENT_DESC = {}
 
 
 def make_config(args, world):
@@ -498,8 +475,9 @@ def run_ours(args):
                          labelled_rows_per_sample=dict(mlm=round(labelled[0], 1), token=round(labelled[1], 1))),
     )
     line["optimizer"] = dict(kernel="adamw_kernel (multi-tensor, 1 launch)", ms_per_step=round(opt_ms, 3), elements=opt_elems,
-                             achieved_GBs=round(28.0 * opt_elems / (opt_ms / 1e3) / 1e9, 1), peak_GBs=pk["hbm"],
-                             note="not part of `value` (metric is fwd+bwd); 28 algorithmic bytes per element (read p,g,m,v; write p,m,v)")
+                             achieved_GBs=round(30.0 * opt_elems / (opt_ms / 1e3) / 1e9, 1), peak_GBs=pk["hbm"],
+                             note="not part of `value` (metric is fwd+bwd); 30 algorithmic bytes per element (read p,g,m,v; write p,m,v and the bf16 "
+                                  "operand copy of p, so that no cast pass follows)")
     if roof:
         line["roofline"] = roof
     if sync_check is not None:
@@ -509,7 +487,7 @@ def run_ours(args):
             line["gpu_eager_baseline"] = gpu_eager_baseline(args, device, value)
         except Exception as e:   # a comparison leg must never cost the line
             line["gpu_eager_baseline"] = dict(error="%s: %s" % (type(e).__name__, str(e)[:200]))
-    if world == 1 and not args.no_cpu_baseline and args.workload in ("pretrain", "viewpoint_select"):
+    if world == 1 and not args.no_cpu_baseline and args.workload in ("pretrain", "viewpoint_select", "turn_based"):
         line["cpu_baseline"] = cpu_baseline(args, steps=2)
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
@@ -612,19 +590,21 @@ def cpu_baseline(args, steps, warmup=1):
     oc = vo.OracleConfig(hidden_dropout_prob=args.dropout, attention_probs_dropout_prob=0.1 if args.dropout > 0 else 0.0)
     drop = vo.train_dropout if args.dropout > 0 else None
     b = 2
-    if args.workload == "viewpoint_select":
+    if args.workload in ("viewpoint_select", "turn_based"):
+        vs = args.workload == "viewpoint_select"
+        steps_ep = VS_STEPS if vs else TB_STEPS
         P = vo.clone_params(vo.init_params(oc, 88, pretrain_heads=False, perturb=False))
-        w_in = vo.clone_params(vo.init_head_params(88))["candidate_att_layer.linear_in.weight"]
-        enc = synthetic.finetune_encoder_batch(b, 88)
-        vsb = [synthetic.viewpoint_step_batch(b, 88 + 17 * t, candidates=VS_CAND, feat=VS_FEAT) for t in range(VS_STEPS)]
+        A, Dv, Dt = vo.init_agent_params(88, scale=0.02)
+        A, D = vo.clone_params(A), vo.clone_params(Dv if vs else Dt)
+        enc = synthetic.agent_batch(b, 88)
+        trace = synthetic.viewpoint_trace(steps_ep, b, 88, candidates=VS_CAND, feat=VS_FEAT) if vs else synthetic.turn_trace(steps_ep, b, 88)
 
         def one():
-            for v in list(P.values()) + [w_in]:
+            for v in list(P.values()) + list(A.values()) + list(D.values()):
                 v.grad = None
-            seq, _ = vo.bert_img_forward(P, oc, enc["input_ids"], enc["token_type_ids"], enc["attention_mask"], drop=drop)
-            loss = sum(vo.candidate_scores_ce(w_in, seq[:, t, :VS_HID], s["cand_feat"], s["cand_len"], s["target"])[1] for t, s in enumerate(vsb))
+            loss, _ = (vo.rollout_vs if vs else vo.rollout_tb)(P, oc, A, D, enc, trace, steps_ep)
             loss.backward()
-        what = "viewpoint_select workload at b=%d (S=511 encoder + 10 candidate-scorer steps)" % b
+        what = "%s workload at b=%d (S=511 encoder + 511-step LSTM + %d decoder steps; dropout off in the port)" % (args.workload, b, steps_ep)
     else:
         P = vo.clone_params(vo.init_params(oc, 88, perturb=False))
         batch = synthetic.pretrain_batch(b, 88)
