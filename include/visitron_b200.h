@@ -264,10 +264,12 @@ int vt_cast_f32_bf16_add(const float* x, const void* addend, int64_t n, void* y,
  * decoder2action (tb/agent_models.py:297,318), question_linear (vs/agent_models.py:455-459,503). */
 int vt_small_linear_fwd(const float* x1, int64_t ldx1, int64_t K1, const float* x2, int64_t ldx2, int64_t K2, const float* W,
                         int64_t ldw, const float* bias, int act, float* y, int64_t ldy, int64_t B, int64_t N, vt_stream stream);
-/* dx1 / dx2 / dW / dbias may be NULL (not needed); dW, dbias are overwritten, not accumulated. */
+/* dx1 / dx2 / dW / dbias may be NULL (not needed); dW, dbias are overwritten, not accumulated.  workspace: fp32 scratch of
+ * vt_small_linear_bwd_workspace(B, N, K1, K2) floats (0 for N <= 256: may be NULL) for the chunked, fixed-order dx reduction. */
+int64_t vt_small_linear_bwd_workspace(int64_t B, int64_t N, int64_t K1, int64_t K2);
 int vt_small_linear_bwd(const float* dy, int64_t lddy, const float* y, int64_t ldy, int act, const float* x1, int64_t ldx1, int64_t K1,
                         const float* x2, int64_t ldx2, int64_t K2, const float* W, int64_t ldw, float* dx1, int64_t lddx1, float* dx2,
-                        int64_t lddx2, float* dW, int64_t lddw, float* dbias, int64_t B, int64_t N, vt_stream stream);
+                        int64_t lddx2, float* dW, int64_t lddw, float* dbias, int64_t B, int64_t N, float* workspace, vt_stream stream);
 /* Context splits P the two calls below use; workspace floats: fwd B*P*(2+D), bwd B*L + B*P*D. */
 int64_t vt_softdot_splits(int64_t B, int64_t L);
 /* SoftDotAttention core (vs/agent_models.py:335-349): logit[b,l] = ctx[b,l,:].target[b,:], positions with mask != 0

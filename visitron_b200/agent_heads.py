@@ -80,9 +80,11 @@ class _SmallLinearFn(torch.autograd.Function):
         db = torch.empty(N, device=W.device, dtype=F32) if (ctx.has_bias and need[3]) else None
         if db is not None and dW is None:
             dW = torch.empty_like(W)  # the bias gradient is produced by the weight-gradient kernel
+        nws = int(L.vt_small_linear_bwd_workspace(B, N, K1, K2)) if (dx1 is not None or dx2 is not None) else 0
+        ws = torch.empty(nws, device=W.device, dtype=F32) if nws else None
         check(L.vt_small_linear_bwd(ptr(dy), dy.stride(0), ptr(y), y.stride(0), ctx.act, ptr(x1), x1.stride(0), K1, ptr(x2),
                                     0 if x2 is None else x2.stride(0), K2, ptr(W), W.stride(0), ptr(dx1), K1, ptr(dx2), K2, ptr(dW),
-                                    W.size(1), ptr(db), B, N, stream_ptr()), "vt_small_linear_bwd")
+                                    W.size(1), ptr(db), B, N, ptr(ws), stream_ptr()), "vt_small_linear_bwd")
         return dx1, dx2, (dW if need[2] else None), db, None
 
 

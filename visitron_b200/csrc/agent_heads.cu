@@ -82,7 +82,11 @@ small_linear_fwd_kernel(const float* __restrict__ x1, long long ldx1, int K1, co
 // output features n (W is read once per row tile, 128 contiguous bytes per group), and the groups' partial sums are added
 // through shared memory in group order, so the result is deterministic.  (One thread per output looping over all n left a
 // decoder step's dx on 4 CTAs: 2.1 ms for [32, 2052] x [2052, 512].)
-constexpr int DX_KT = 32, DX_NG = 32;
+// The output features are further cut into chunks of DX_NCH rows of W, one CTA each (blockIdx.z): the LSTMCell's [2048, 2116]
+// weight left a decoder step's dx on 65 CTAs that each walked 2048 rows (131 us of 21 MB at 6.5 TB/s = 3 us); with the chunks a
+// step's dx runs on ~500 CTAs.  Chunk partials go to a workspace [chunk][row][column] and small_linear_dx_reduce_kernel adds
+// them in chunk order: still deterministic.
+constexpr int DX_KT = 32, DX_NG = 32, DX_NCH = 256;
 
 __global__ void __launch_bounds__(256)
 small_linear_dx_kernel(const float* __restrict__ dy, long long lddy, const float* __restrict__ y, long long ldy, int act,
@@ -95,7 +99,9 @@ small_linear_dx_kernel(const float* __restrict__ dy, long long lddy, const float
 #pragma unroll
   for (int j = 0; j < LIN_BT; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
   const int kw = max(0, min(4, K - k));
-  for (int n = g; n < N; n += DX_NG) {
+  const int n_lo = blockIdx.z * DX_NCH, n_hi = min(N, n_lo + DX_NCH);
+  if (gridDim.z > 1) dx += (long long)blockIdx.z * B * lddx;      // this chunk's slice of the workspace
+  for (int n = n_lo + g; n < n_hi; n += DX_NG) {
     float wv[4];
     const float* wp = W + (long long)n * ldw + koff + k;
     if (vec && kw == 4) {
@@ -128,6 +134,15 @@ small_linear_dx_kernel(const float* __restrict__ dy, long long lddy, const float
     for (int gg = 0; gg < DX_NG; ++gg) sum += red[gg][j][c];
     dx[(long long)(b0 + j) * lddx + ko] = sum;
   }
+}
+
+__global__ void __launch_bounds__(256)
+small_linear_dx_reduce_kernel(const float* __restrict__ ws, int chunks, long long slice, int B, int K, float* __restrict__ dx, long long lddx) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= (long long)B * K) return;
+  float s = 0.f;
+  for (int c = 0; c < chunks; ++c) s += ws[c * slice + i];
+  dx[(i / K) * lddx + i % K] = s;
 }
 
 // dW[n, koff + k] = sum_b dy'(b, n) x[b, k];  dbias[n] = sum_b dy'(b, n)   (one thread per (n, k); b in order: deterministic)
@@ -537,10 +552,16 @@ extern "C" int vt_small_linear_fwd(const float* x1, int64_t ldx1, int64_t K1, co
   return VT_OK;
 }
 
+extern "C" int64_t vt_small_linear_bwd_workspace(int64_t B, int64_t N, int64_t K1, int64_t K2) {
+  const int64_t chunks = (N + DX_NCH - 1) / DX_NCH;
+  return chunks <= 1 ? 0 : chunks * B * (K1 > K2 ? K1 : K2);
+}
+
 extern "C" int vt_small_linear_bwd(const float* dy, int64_t lddy, const float* y, int64_t ldy, int act, const float* x1, int64_t ldx1, int64_t K1,
                                    const float* x2, int64_t ldx2, int64_t K2, const float* W, int64_t ldw, float* dx1, int64_t lddx1, float* dx2,
-                                   int64_t lddx2, float* dW, int64_t lddw, float* dbias, int64_t B, int64_t N, vt_stream stream) {
+                                   int64_t lddx2, float* dW, int64_t lddw, float* dbias, int64_t B, int64_t N, float* workspace, vt_stream stream) {
   VT_REQUIRE(dy && x1 && W && B >= 0 && N > 0 && K1 > 0 && K2 >= 0, "vt_small_linear_bwd: bad arguments");
+  VT_REQUIRE(N <= DX_NCH || workspace || (!dx1 && !dx2), "vt_small_linear_bwd: more than %d output features need the workspace (vt_small_linear_bwd_workspace)", DX_NCH);
   VT_REQUIRE(act == 0 || (act == 1 && y), "vt_small_linear_bwd: tanh backward needs the forward output");
   if (B == 0) return VT_OK;
   cudaStream_t st = (cudaStream_t)stream;
@@ -551,10 +572,18 @@ extern "C" int vt_small_linear_bwd(const float* dy, int64_t lddy, const float* y
     float* dx = seg ? dx2 : dx1;
     const int koff = seg ? (int)K1 : 0;
     if (dx) {
-      dim3 grid((unsigned)((K + DX_KT - 1) / DX_KT), (unsigned)((B + LIN_BT - 1) / LIN_BT));
+      const int chunks = (int)((N + DX_NCH - 1) / DX_NCH);
+      dim3 grid((unsigned)((K + DX_KT - 1) / DX_KT), (unsigned)((B + LIN_BT - 1) / LIN_BT), (unsigned)chunks);
       const int vec = (((uintptr_t)W & 15) == 0 && ldw % 4 == 0 && koff % 4 == 0) ? 1 : 0;
-      small_linear_dx_kernel<<<grid, 256, 0, st>>>(dy, lddy, y, ldy, act, W, ldw, koff, dx, seg ? lddx2 : lddx1, (int)B, (int)N, (int)K, vec);
-      ++launches;
+      const long long lddx = seg ? lddx2 : lddx1;
+      if (chunks == 1) {
+        small_linear_dx_kernel<<<grid, 256, 0, st>>>(dy, lddy, y, ldy, act, W, ldw, koff, dx, lddx, (int)B, (int)N, (int)K, vec);
+        ++launches;
+      } else {   // partials [chunk][B][K] (row pitch K), then the fixed-order sum
+        small_linear_dx_kernel<<<grid, 256, 0, st>>>(dy, lddy, y, ldy, act, W, ldw, koff, workspace, K, (int)B, (int)N, (int)K, vec);
+        small_linear_dx_reduce_kernel<<<(unsigned)((B * K + 255) / 256), 256, 0, st>>>(workspace, chunks, B * K, (int)B, (int)K, dx, lddx);
+        launches += 2;
+      }
     }
     if (dW) {
       dim3 grid((unsigned)((K + 255) / 256), (unsigned)N);
