@@ -446,8 +446,7 @@ def run_ours(args):
     sync_check = grad_sync_check(wl, model, dev_batches[0], device, world) if world > 1 else None
 
     if rank != 0:
-        if world > 1:
-            torch.distributed.destroy_process_group()
+        _leave(world, graphed)
         return
     S = wl.S
     fl, fl_done = wl.flops(), wl.flops(executed=True)
@@ -493,8 +492,21 @@ def run_ours(args):
     os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
     os.dup2(2, 1)
-    if world > 1:
-        torch.distributed.destroy_process_group()
+    _leave(world, graphed)
+
+
+def _leave(world, graphed):
+    """End of a multi-rank run.  destroy_process_group() on a communicator whose collectives live in a captured CUDA graph did not
+    return on the 2-GPU box (the run printed its line and then sat in the destructor until the timeout): every rank drains its
+    device, meets the others once more, and leaves the process without tearing NCCL down."""
+    if world <= 1:
+        return
+    torch.cuda.synchronize()
+    torch.distributed.barrier()
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
 
 
 def grad_sync_check(wl, model, batch, device, world):
