@@ -601,7 +601,7 @@ def cpu_baseline(args, steps, warmup=1):
     torch.set_num_threads(threads)
     oc = vo.OracleConfig(hidden_dropout_prob=args.dropout, attention_probs_dropout_prob=0.1 if args.dropout > 0 else 0.0)
     drop = vo.train_dropout if args.dropout > 0 else None
-    b = 2
+    b = max(1, int(getattr(args, "cpu_batch", 2)))
     if args.workload in ("viewpoint_select", "turn_based"):
         vs = args.workload == "viewpoint_select"
         steps_ep = VS_STEPS if vs else TB_STEPS
@@ -643,7 +643,7 @@ def run_reference(args):
     steps, warm = max(1, min(args.steps, 40)), max(1, min(args.warmup, 5))
     cb = cpu_baseline(args, steps, warm)
     line = dict(impl="reference", metric=METRIC, value=cb["value"], unit=UNIT, n_gpus=args.gpus, steps=steps, warmup=warm,
-                ms_per_step=round(2 / cb["value"] * 1e3, 1), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
+                ms_per_step=round(args.cpu_batch / cb["value"] * 1e3, 1), higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
                 config=make_config(args, args.gpus),
                 cpu_baseline=cb, e2e=dict(value=cb["value"], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
     print(json.dumps(line), flush=True)
@@ -666,6 +666,7 @@ def main():
     ap.add_argument("--feat-bf16", action="store_true", help="region features / location embeddings come from a bf16 cache (pretrain workload)")
     ap.add_argument("--no-clocks", action="store_true", help="diagnosis: do not sample clocks during the timed region")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-batch", type=int, default=2, help="batch of the CPU baseline's bounded sample (the scripts' per-GPU batch is 2; BASELINE C1 also asks for 8)")
     ap.add_argument("--no-gpu-eager", action="store_true", help="skip the oracle-on-the-GPU comparison leg (SURVEY 8d-D5)")
     ap.add_argument("--no-graph", action="store_true", help="time the eager path (~400 ctypes launches per step) instead of the captured CUDA graph")
     ap.add_argument("--no-roofline", action="store_true")

@@ -46,9 +46,21 @@ def _oracle_step(oc, P, batch):
     return out, aux, Pg
 
 
-@pytest.mark.parametrize("layers,b,imgln", [(12, 2, 0), (3, 4, 1)])
+def _report(line):
+    """Achieved parity numbers go to gpurun_out/r2_parity.txt (copied to profiles/ by the builder): VERDICT r1 asked for the
+    figures behind the pass / fail, not only the verdict."""
+    import os
+    d = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    os.makedirs(d, exist_ok=True)
+    with open(os.path.join(d, "r2_parity.txt"), "a") as f:
+        f.write(line + "\n")
+    print(line)
+
+
+@pytest.mark.parametrize("layers,b,imgln", [(12, 2, 0), (3, 4, 1), (12, 32, 0)])
 def test_bert_base_pretrain_step_vs_fp32_oracle(layers, b, imgln):
-    """Full bert-base widths (V = 30522, 1601 detector classes, T = 511, R = 256 -> S = 767)."""
+    """Full bert-base widths (V = 30522, 1601 detector classes, T = 511, R = 256 -> S = 767); the last case is the bench's own
+    size (12 layers, b = 32, dropout 0) against the fp32 oracle on the same GPU."""
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.allow_tf32 = False
     oc = vo.OracleConfig(num_hidden_layers=layers, use_img_layernorm=imgln)
@@ -76,15 +88,24 @@ def test_bert_base_pretrain_step_vs_fp32_oracle(layers, b, imgln):
     n_t = decided_argmax_equal(aux["predicted_tokens"], ref_tok.clamp_min(1e-30).log(), ref_tok.argmax(1), tol=0.3)
     n_a = decided_argmax_equal(aux["predicted_action"], ref_aux["action_scores"], ref_aux["action_scores"].argmax(1), tol=0.1)
     assert n_w >= ref_logits.size(0) // 4 and n_t >= ref_tok.size(0) // 4 and n_a >= 1, (n_w, n_t, n_a)
-    worst = (0.0, None)
+    worst, worst_cos = (0.0, None), (1.0, None)
     for k, p in model.named_parameters():
         if k == "mlmhead.predictions.decoder.weight":
             continue
         ref = Pg[k].grad
         assert (p.grad is None) == (ref is None), k
-        rel, _ = grad_close(k, p.grad, ref, floor=1e-4)  # key.bias has a mathematically zero gradient: rounding noise only
+        rel, cos = grad_close(k, p.grad, ref, floor=1e-4)  # key.bias has a mathematically zero gradient: rounding noise only
         worst = max(worst, (rel, k))
-    print("worst gradient rel-L2:", worst)
+        worst_cos = min(worst_cos, (cos, k))
+    top2 = ref_logits.float().topk(2, dim=-1).values
+    near_ties = int(((top2[:, 0] - top2[:, 1]) <= 2 * 4 * LOGIT_TOL).sum())
+    _report("pretrain step vs fp32 oracle: layers=%d b=%d S=767 imgln=%d | loss |d|=%.2e (rel %.2e) | mlm logits max|d|=%.3e (scaled x4) | "
+            "argmax: %d of %d MLM rows decided (%d near-ties excluded), all agree; %d token rows, %d action rows | worst grad rel-L2 %.4f (%s) | "
+            "worst grad cosine %.5f (%s)"
+            % (layers, b, imgln, abs(float(out[0].detach()) - float(ref_out[0].detach())),
+               abs(float(out[0].detach()) - float(ref_out[0].detach())) / max(1e-9, abs(float(ref_out[0].detach()))),
+               float((aux["mlm_logits"] - ref_logits).abs().max()), n_w, ref_logits.size(0), near_ties, n_t, n_a, worst[0], worst[1],
+               worst_cos[0], worst_cos[1]))
 
 
 def test_finetune_call_full_length_f6_mask():

@@ -117,6 +117,41 @@ def main():
     case("mlm mask         [B,511] ids -> ids', labels, attention", lambda i: ip.mask_tokens(r(tok, i), tcl, lut, 103, 0, seed + i), 0, B * T * (8 * 4 + 1.0))
     case("pack regions     180 -> [B,256,2054+128] fp32", lambda i: ip.pack_regions(*r(rag, i), offs, R), 0, 4.0 * B * (180 * 2 + 76) * (2054 + 128))
 
+    # the remaining HBM-bound kernels of the step (embeddings, cross-entropy over the labelled rows, AdamW) and the agents' LSTM
+    V, NLAB = 30522, 1408
+    word, posw, typw = torch.randn(V, H, device=dev) * 0.02, torch.randn(512, H, device=dev) * 0.02, torch.randn(2, H, device=dev) * 0.02
+    gword, gpos, gtyp = torch.zeros_like(word), torch.zeros_like(posw), torch.zeros_like(typw)
+    emb_out = torch.empty(B * S, H, dtype=BF16, device=dev)
+    case("embed+ln fwd     [B,511] ids -> [B*S,768]", lambda i: ops.embed_ln_fwd(r(tok, i), None, None, word, posw, typw, gamma, beta, 1e-12, emb_out, S, ph, seed, 1000),
+         0, B * T * (3 * H * 4 + H * 2.0))
+    case("embed+ln bwd     scatter-add into the fp32 tables", lambda i: ops.embed_ln_bwd(r(xs, i), r(tok, i), None, None, word, posw, typw, gamma, 1e-12, S, gword, gpos, gtyp,
+                                                                                       gvec[:H], gvec[H:2 * H], ph, seed, 1000), 0, B * T * (H * 2 + 3 * H * 4 + 2 * H * 4.0))
+    ldv = ops.roundup(V, 8)
+    logits = torch.randn(NLAB, ldv, device=dev)
+    clab = torch.randint(0, V, (NLAB,), device=dev)
+    g1 = torch.ones(1, device=dev)
+    _, _, cstats = ops.softmax_ce_fwd(logits[:, :V], V, clab)
+    case("softmax-ce fwd   [1408, 30522] fp32 logits", lambda i: ops.softmax_ce_fwd(logits[:, :V], V, clab), 0, NLAB * V * 4.0)
+    case("softmax-ce bwd   -> bf16 dlogits", lambda i: ops.softmax_ce_bwd(logits[:, :V], V, clab, cstats, 1.0 / NLAB, g1, ld_out=ldv), 0, NLAB * V * 6.0)
+    from visitron_b200 import optimization as vopt
+    pw = torch.nn.Parameter(torch.randn(113_000_000, device=dev) * 0.02)
+    pw.grad = torch.randn_like(pw) * 1e-3
+    opt = vopt.AdamW([pw], lr=1e-4, weight_decay=0.01)
+    case("adamw            113 M fp32 parameters, one launch", lambda i: opt.step(), 0, 28.0 * pw.numel())
+    from visitron_b200.agent_models import _LSTMSeqFn
+    LB, LT = 8, 511
+    lx = rnd(LB * LT, H)
+    lw = [torch.randn(2048, 768, device=dev) * 0.03, torch.randn(2048, 512, device=dev) * 0.03, torch.zeros(2048, device=dev), torch.zeros(2048, device=dev)]
+    for t_ in lw:
+        t_.requires_grad_(True)
+    llen = torch.full((LB,), LT, dtype=torch.int64, device=dev)
+
+    def lstm_fwd_bwd(i):
+        xi = lx.detach().requires_grad_(True)
+        c_, h_, cc_ = _LSTMSeqFn.apply(xi, llen, LB, LT, *lw)
+        (c_.sum() + h_.sum()).backward()
+    case("lstm 768->512    b=8, 511 steps, fwd + bwd (+ 4 GEMMs)", lstm_fwd_bwd, 3 * LB * LT * 2.0 * (768 + 512) * 2048)
+
     rows = []
     tot = 0.0
     if args.once:  # for `ncu --profile-from-start off`: one untimed pass, then one profiled launch of every case

@@ -61,7 +61,10 @@ __device__ __forceinline__ void mbar_expect_(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   do {
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+    // default semantics (acquire at CTA scope), as for TMA / multicast arrivals: the data is in THIS CTA's shared memory once the
+    // phase completes.  (.acquire.cluster made ptxas emit CCTL.IVALL -- an L1 invalidate -- in every poll: 21 % of the forward
+    // kernel's stall samples, profiles/r2_ncu_lstm.txt.)
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                  : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
   } while (!ok);
 }
@@ -155,7 +158,8 @@ lstm_seq_fwd_kernel(const SeqParams p) {
   const uint32_t sW_u = smem_addr(sW), sH_u = smem_addr(sH), sStage_u = smem_addr(sStage);
   // ldmatrix row address of this lane: row (lane % 8) + 8 ((lane / 8) % 2) of the warp's 16, k offset 8 (lane / 16)
   const uint32_t a_lane = sW_u + (uint32_t)(16 * warp + (lane & 7) + 8 * ((lane >> 3) & 1)) * WROW + (uint32_t)(lane >> 4) * 16u;
-  const uint32_t b_lane = (uint32_t)(lane >> 2) * WROW + (uint32_t)(lane & 3) * 4u;   // B fragment: sample lane / 4, k pair lane % 4
+  // B fragments of one k-step with ONE ldmatrix.x4: matrices (h hi, k 0-7), (hi, k 8-15), (lo, k 0-7), (lo, k 8-15), rows = samples
+  const uint32_t b_lane = (uint32_t)(lane & 7) * WROW + (uint32_t)((lane >> 3) & 1) * 16u + (uint32_t)(lane >> 4) * (NS * WROW);
 
   for (int t = 0; t < p.T; ++t) {
     const uint32_t hb = sH_u + (uint32_t)(t & 1) * (2 * NS * WROW);
@@ -176,9 +180,10 @@ lstm_seq_fwd_kernel(const SeqParams p) {
     for (int kk = 0; kk < H / 16; ++kk) {
       uint32_t a[4];
       ldmatrix_x4(a_lane + kk * 32, a);
-      const uint32_t bo = hb + b_lane + kk * 32;
-      mma_bf16(accq[kk & 3], a, lds32(bo), lds32(bo + 16));                                  // h hi
-      mma_bf16(accq[4 + (kk & 3)], a, lds32(bo + NS * WROW), lds32(bo + NS * WROW + 16));     // h lo
+      uint32_t bq[4];
+      ldmatrix_x4(hb + b_lane + kk * 32, bq);
+      mma_bf16(accq[kk & 3], a, bq[0], bq[1]);          // h hi
+      mma_bf16(accq[4 + (kk & 3)], a, bq[2], bq[3]);    // h lo
     }
     float acc[4];
 #pragma unroll
@@ -289,7 +294,8 @@ lstm_seq_bwd_kernel(const SeqParams p) {
   const uint32_t sWT_u = smem_addr(sWT), sD_u = smem_addr(sD);
   // A fragment rows: m-tile mt covers units 16 mt .. + 15; this warp contracts over gates [256 warp, + 256)
   const uint32_t a_lane = sWT_u + (uint32_t)((lane & 7) + 8 * ((lane >> 3) & 1)) * DROW + (uint32_t)(lane >> 4) * 16u + (uint32_t)warp * 512u;
-  const uint32_t b_lane = (uint32_t)(lane >> 2) * DROW + (uint32_t)(lane & 3) * 4u + (uint32_t)warp * 512u;
+  // B fragments of TWO k-steps with one ldmatrix.x4: matrices (k 0-7), (k 8-15), (k 16-23), (k 24-31), rows = samples
+  const uint32_t b_lane = (uint32_t)(lane & 7) * DROW + (uint32_t)(lane >> 3) * 16u + (uint32_t)warp * 512u;
 
   for (int t = p.T - 1; t >= 0; --t) {
     const bool active = t < len;
@@ -343,16 +349,22 @@ lstm_seq_bwd_kernel(const SeqParams p) {
     // dh_{t-1}[unit, sample] = sum_g W_hh[g, unit] dA_t[sample, g]: this warp's 256-gate slice, both 16-unit tiles
     const uint32_t db = sD_u + (uint32_t)(t & 1) * (NS * DROW);
     float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 4
-    for (int kk = 0; kk < 16; ++kk) {
-      uint32_t a0[4], a1[4];
-      ldmatrix_x4(a_lane + kk * 32, a0);
-      ldmatrix_x4(a_lane + 16 * DROW + kk * 32, a1);
-      const uint32_t bo = db + b_lane + kk * 32;
-      const uint32_t b0 = lds32(bo), b1 = lds32(bo + 16);
-      mma_bf16(acc0, a0, b0, b1);
-      mma_bf16(acc1, a1, b0, b1);
+    float acc2[4] = {0.f, 0.f, 0.f, 0.f}, acc3[4] = {0.f, 0.f, 0.f, 0.f};   // four independent chains
+#pragma unroll
+    for (int k2 = 0; k2 < 8; ++k2) {
+      uint32_t a0[4], a1[4], a2[4], a3[4], bq[4];
+      ldmatrix_x4(a_lane + k2 * 64, a0);
+      ldmatrix_x4(a_lane + 16 * DROW + k2 * 64, a1);
+      ldmatrix_x4(a_lane + k2 * 64 + 32, a2);
+      ldmatrix_x4(a_lane + 16 * DROW + k2 * 64 + 32, a3);
+      ldmatrix_x4(db + b_lane + k2 * 64, bq);
+      mma_bf16(acc0, a0, bq[0], bq[1]);
+      mma_bf16(acc1, a1, bq[0], bq[1]);
+      mma_bf16(acc2, a2, bq[2], bq[3]);
+      mma_bf16(acc3, a3, bq[2], bq[3]);
     }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { acc0[q] += acc2[q]; acc1[q] += acc3[q]; }
     {
       // fragment (row = lane / 4 (+ 8), col = 2 (lane % 4) (+ 1)) -> sPart[warp][unit][sample]
       float* pw = sPart + warp * (U * NS);
