@@ -69,6 +69,22 @@ int vt_compact_labels(const int64_t* labels_a, int64_t classes_a, const int64_t*
                       int64_t ignore_index, int64_t capacity, int64_t* idx_a, int64_t* lab_a, int64_t* idx_b, int64_t* lab_b,
                       int32_t* counts /* device int32[8] */, vt_stream stream);
 
+/* Packed rows (padding-free execution of the pre-training step).  The loader pads every sample to 511 + 256 positions
+ * (tasks/viewpoint_select/data_loader_pretrain.py:636-712); padded positions are masked as keys and carry no label, so neither the
+ * loss nor any gradient depends on them.  vt_pack_plan keeps position (b, s) iff its mask is non-zero (bias != -10000), it carries a
+ * label in either array, or s == 0, and lays the kept rows out sample after sample:
+ *   row_src [capacity] padded index of packed row r (-1 on the layout's own padding rows),  row_dst [B*S] the inverse (-1: dropped),
+ *   row_b [capacity] the sample of a packed row,  start [B+1] first packed row of every sample,  cls_rows [B] = start as int64,
+ *   counts {rows kept rounded up to 128 plus 128, rows kept}: the vt_set_row_limit block of every launch of the step,
+ *   bias_packed / labels_*_packed [capacity]: the key bias and the labels in packed order (-1 on padding rows).
+ * capacity: rows of every activation buffer, a multiple of 128, >= roundup(B*S, 128) + 128.  The *_packed entry points below take
+ * these maps; everything else runs under the row limit.  vt_zero_pad_rows clears rows [counts[1], counts[0]) of a buffer (the rows a
+ * per-sample kernel -- attention -- does not write, and which must be finite zeros where a GEMM contracts over rows). */
+int vt_pack_plan(const float* bias, const int64_t* labels_a, const int64_t* labels_b, int64_t B, int64_t S, int64_t capacity,
+                 int32_t* row_src, int32_t* row_dst, int32_t* row_b, int32_t* start, int32_t* counts, float* bias_packed,
+                 int64_t* labels_a_packed, int64_t* labels_b_packed, int64_t* cls_rows, vt_stream stream);
+int vt_zero_pad_rows(void* buf, int64_t pitch_bytes, int64_t row_bytes, const int32_t* counts, vt_stream stream);
+
 /* ------------------------------------------------------------------------------------------
  * Dense projections: one tcgen05/TMEM GEMM fed by TMA.
  *   D[M,N] = epilogue( alpha * sum_k A(m,k) * B(n,k) )
@@ -108,6 +124,9 @@ typedef struct {
    * (rows_in == 0 disables).  Used to write image rows behind the text rows of each sample
    * (replaces torch.cat, vs/encoder.py:287) and to scatter the pooler gradient to row 0. */
   int64_t remap_rows_in, remap_rows_out, remap_row_off;
+  /* optional second map (packed rows, vt_pack_plan): the row computed above is looked up in remap_index (int32); a negative entry
+   * drops the row.  With remap_rows_in == 0 the logical row m itself is looked up. */
+  const int32_t* remap_index;
 } vt_gemm_epilogue;
 
 int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void* B, int64_t ldb, int b_major,
@@ -155,12 +174,23 @@ int vt_embed_ln_fwd(const int64_t* ids, const int64_t* type_ids, const int64_t* 
                     const float* pos, const float* type, const float* gamma, const float* beta, float eps,
                     int64_t batch, int64_t T, int64_t out_rows_per_sample, int64_t hidden, void* y, float dropout_p,
                     uint64_t seed, uint32_t dropout_stream, vt_stream stream);
+/* the same into packed rows: position (s, t) is written to row row_dst[s * out_rows_per_sample + t], or skipped when negative */
+int vt_embed_ln_fwd_packed(const int64_t* ids, const int64_t* type_ids, const int64_t* pos_ids, const float* word,
+                           const float* pos, const float* type, const float* gamma, const float* beta, float eps,
+                           int64_t batch, int64_t T, int64_t out_rows_per_sample, int64_t hidden, void* y, float dropout_p,
+                           uint64_t seed, uint32_t dropout_stream, const int32_t* row_dst, vt_stream stream);
 /* Its backward: scatter-adds (fp32 atomics) into dword/dpos/dtype, accumulates dgamma/dbeta. */
 int vt_embed_ln_bwd(const void* dy, const int64_t* ids, const int64_t* type_ids, const int64_t* pos_ids, const float* word,
                     const float* pos, const float* type, const float* gamma, float eps, int64_t batch, int64_t T,
                     int64_t out_rows_per_sample, int64_t hidden, int64_t type_vocab, float* dword, float* dpos,
                     float* dtype, float* dgamma, float* dbeta, float* partials, float dropout_p, uint64_t seed,
                     uint32_t dropout_stream, vt_stream stream);
+
+int vt_embed_ln_bwd_packed(const void* dy, const int64_t* ids, const int64_t* type_ids, const int64_t* pos_ids, const float* word,
+                           const float* pos, const float* type, const float* gamma, float eps, int64_t batch, int64_t T,
+                           int64_t out_rows_per_sample, int64_t hidden, int64_t type_vocab, float* dword, float* dpos,
+                           float* dtype, float* dgamma, float* dbeta, float* partials, float dropout_p, uint64_t seed,
+                           uint32_t dropout_stream, const int32_t* row_dst, vt_stream stream);
 
 /* out[c] (+)= sum_r x[r, c]  for bf16 x [rows, ncols] -- bias gradients of the QKV and FFN-up layers.
  * partials: fp32 [vt_colsum_partials_rows(rows)][roundup8(ncols)]. */
@@ -183,6 +213,10 @@ int vt_pad_cast_concat_mixed(const void* a, int a_bf16, int64_t d0, const void* 
 int vt_dropout_rows(const void* x, int64_t ldx, int64_t rows, int64_t hidden, void* y, int64_t ldy, float dropout_p,
                     uint64_t seed, uint32_t dropout_stream, int64_t remap_rows_in, int64_t remap_rows_out,
                     int64_t remap_row_off, vt_stream stream);
+/* y[m] = x[row_dst[remap(m)]] * dropout_mask(m), zeros where that packed row does not exist */
+int vt_dropout_rows_packed(const void* x, int64_t ldx, int64_t rows, int64_t hidden, void* y, int64_t ldy, float dropout_p,
+                           uint64_t seed, uint32_t dropout_stream, int64_t remap_rows_in, int64_t remap_rows_out,
+                           int64_t remap_row_off, const int32_t* row_dst, vt_stream stream);
 /* dst[r] = src[idx[r]] ; dst[idx[r]] += src[r]   (compaction of the labelled rows for the MLM / token heads);
  * idx[r] < 0 (a padding row of vt_compact_labels): gathered as zeros, skipped by the scatter */
 int vt_gather_rows(const void* src, int64_t lds, const int64_t* idx, int64_t n, int64_t hidden, void* dst, int64_t ldd,
@@ -209,6 +243,18 @@ int vt_mask_bias(const void* mask, int mask_dtype, int64_t n, float* bias, vt_st
 int vt_attention_key_tiles(const float* bias, int64_t B, int64_t S, uint32_t* key_tiles, vt_stream stream);
 int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, int64_t B, int64_t S, int64_t heads,
                      int64_t head_dim, void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream);
+/* Packed rows (vt_pack_plan): sample b owns rows [start[b], start[b+1]) of qkv / ctx / dctx / dqkv (rows_cap rows each) and of the
+ * packed bias; S stays the bound of a sample's length and the stride of lse / dsum ([B, heads, S, .]).  Query and key tiles past a
+ * sample's end are not visited; row_b [rows_cap] gives the sample of a row (-1: padding row, its dQ is written as 0). */
+int vt_attention_key_tiles_packed(const float* bias_packed, const int32_t* start, int64_t B, int64_t S, uint32_t* key_tiles, vt_stream stream);
+int vt_attention_fwd_packed(const void* qkv, int64_t ld, const float* bias_packed, const uint32_t* key_tiles, const int32_t* start,
+                            int64_t rows_cap, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* ctx, float* lse, float dropout_p,
+                            uint64_t seed, uint32_t dropout_stream, vt_stream stream);
+int64_t vt_attention_bwd_workspace_packed(int64_t rows_cap, int64_t B, int64_t S, int64_t heads);
+int vt_attention_bwd_packed(const void* qkv, int64_t ld, const float* bias_packed, const uint32_t* key_tiles, const int32_t* start,
+                            const int32_t* row_b, int64_t rows_cap, const void* ctx, const void* dctx, const float* lse, float* dsum_ws,
+                            int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv, float dropout_p, uint64_t seed,
+                            uint32_t dropout_stream, vt_stream stream);
 int64_t vt_attention_bwd_workspace(int64_t B, int64_t S, int64_t heads);
 int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, const void* ctx, const void* dctx,
                      const float* lse, float* dsum_ws, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv,

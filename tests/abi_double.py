@@ -76,7 +76,7 @@ def _no_dropout(p):
 
 def gemm(A, B, *, a_major=0, b_major=0, out=None, out_dtype=BF16, bias=None, act=0, alpha=1.0, alpha_dev=None,
          residual=None, aux=None, aux_out=None, dropout_p=0.0, seed=0, dropout_stream=0, accumulate=False, split_k=0,
-         remap=None, M=None, N=None, K=None):
+         remap=None, remap_index=None, M=None, N=None, K=None):
     CALLS.append("gemm")
     assert A.dtype == BF16 and B.dtype == BF16
     _no_dropout(dropout_p)
@@ -102,24 +102,28 @@ def gemm(A, B, *, a_major=0, b_major=0, out=None, out_dtype=BF16, bias=None, act
         r = r + bias[:n]
     _dgelu = lambda x: 0.5 * (1.0 + torch.erf(x / math.sqrt(2.0))) + x * torch.exp(-0.5 * x * x) / math.sqrt(2.0 * math.pi)  # noqa: E731
     if aux_out is not None:
-        aux_out[:, :n].copy_((_dgelu(r) if act == 5 else r).to(BF16))
+        aux_out[: r.size(0), :n].copy_((_dgelu(r) if act == 5 else r).to(BF16))
     if act in (1, 5):
         r = r * 0.5 * (1.0 + torch.erf(r / math.sqrt(2.0)))
     elif act == 2:
         r = torch.tanh(r)
     elif act == 3:
-        x = aux.float()[:, :n]
+        x = aux.float()[: r.size(0), :n]
         r = r * (0.5 * (1.0 + torch.erf(x / math.sqrt(2.0))) + x * torch.exp(-0.5 * x * x) / math.sqrt(2.0 * math.pi))
     elif act == 4:
-        y = aux.float()[:, :n]
+        y = aux.float()[: r.size(0), :n]
         r = r * (1.0 - y * y)
     elif act == 6:
-        r = r * aux.float()[:, :n]
+        r = r * aux.float()[: r.size(0), :n]
     rows = _remap_rows(r.size(0), remap or (0, 0, 0), r.device)
+    if remap_index is not None:          # packed rows: look the row up, drop it when the map says -1
+        rows = remap_index.long()[rows]
+        live = rows >= 0
+        rows, r = rows[live], r[live]
     if residual is not None:
         r = r + residual[rows].float()[:, :n]
     if out is None:
-        assert remap is None
+        assert remap is None and remap_index is None
         if r.size(0) < m_full and not a_major:
             full = _nan_like((m_full, r.size(1)), out_dtype)
             full[: r.size(0)] = r.to(out_dtype)
@@ -179,18 +183,28 @@ def layernorm_bwd(dy, x, gamma, eps, dgamma, dbeta, dbias=None, want_dx=True, ou
     return res, res
 
 
-def embed_ln_fwd(ids, type_ids, pos_ids, word, pos, typ, gamma, beta, eps, out, rows_per_sample, dropout_p=0.0, seed=0, stream_id=0):
+def _embed_rows(b, T, rows_per_sample, row_dst):
+    """flat output row of every (sample, position) and which of them exist"""
+    o = (torch.arange(b)[:, None] * rows_per_sample + torch.arange(T)[None, :]).reshape(-1)
+    if row_dst is None:
+        return o, torch.ones_like(o, dtype=torch.bool)
+    o = row_dst.long()[o]
+    return o.clamp_min(0), o >= 0
+
+
+def embed_ln_fwd(ids, type_ids, pos_ids, word, pos, typ, gamma, beta, eps, out, rows_per_sample, dropout_p=0.0, seed=0, stream_id=0, row_dst=None):
     CALLS.append("embed_ln_fwd")
     _no_dropout(dropout_p)
     b, T = ids.shape
     p = torch.arange(T)[None].expand(b, T) if pos_ids is None else pos_ids
     e = word[ids] + pos[p] + (typ[type_ids] if type_ids is not None else typ[0])
-    out.view(b, rows_per_sample, H)[:, :T] = _ln(e, gamma, beta, eps).to(BF16)
+    o, live = _embed_rows(b, T, rows_per_sample, row_dst)
+    out[o[live]] = _ln(e, gamma, beta, eps).to(BF16).reshape(b * T, H)[live]
     return out
 
 
 def embed_ln_bwd(dy, ids, type_ids, pos_ids, word, pos, typ, gamma, eps, rows_per_sample, dword, dpos, dtype, dgamma, dbeta,
-                 dropout_p=0.0, seed=0, stream_id=0):
+                 dropout_p=0.0, seed=0, stream_id=0, row_dst=None):
     CALLS.append("embed_ln_bwd")
     _no_dropout(dropout_p)
     b, T = ids.shape
@@ -198,9 +212,11 @@ def embed_ln_bwd(dy, ids, type_ids, pos_ids, word, pos, typ, gamma, eps, rows_pe
     tt = torch.zeros_like(ids) if type_ids is None else type_ids
     ws = [t.detach().clone().requires_grad_(True) for t in (word, pos, typ, gamma)]
     beta = torch.zeros_like(gamma).requires_grad_(True)
+    o, live = _embed_rows(b, T, rows_per_sample, row_dst)
+    g = torch.where(live[:, None], dy[o].float(), torch.zeros(()))       # a dropped row has no gradient
     with torch.enable_grad():
         y = _ln(ws[0][ids] + ws[1][p] + ws[2][tt], ws[3], beta, eps)
-        y.backward(dy.view(b, rows_per_sample, H)[:, :T].float())
+        y.backward(g.view(b, T, H))
     dword += ws[0].grad
     dpos += ws[1].grad
     dtype += ws[2].grad
@@ -236,10 +252,15 @@ def pad_cast_concat(a, b, out):
     return out
 
 
-def dropout_rows(x, rows, out, dropout_p, seed, stream_id, remap=(0, 0, 0)):
+def dropout_rows(x, rows, out, dropout_p, seed, stream_id, remap=(0, 0, 0), row_dst=None):
     CALLS.append("dropout_rows")
     _no_dropout(dropout_p)
-    out[:rows] = x[_remap_rows(rows, remap, x.device)]
+    src = _remap_rows(rows, remap, x.device)
+    if row_dst is None:
+        out[:rows] = x[src]
+    else:
+        src = row_dst.long()[src]
+        out[:rows] = torch.where((src >= 0)[:, None], x[src.clamp_min(0)], torch.zeros((), dtype=x.dtype))
     return out
 
 
@@ -281,20 +302,93 @@ def attention_key_tiles(bias):
     return None
 
 
-def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None, key_tiles=None):
+class PackPlan:
+    pass
+
+
+def pack_plan(bias, labels_a, labels_b, B, S):
+    """CPU restatement of vt_pack_plan (csrc/pack.cu): keep a position iff mask != 0, labelled, or position 0."""
+    CALLS.append("pack_plan")
+    pl = PackPlan()
+    M = B * S
+    keep = bias.reshape(-1) != -10000.0
+    for lab in (labels_a, labels_b):
+        if lab is not None:
+            keep = keep | (lab.reshape(-1) != -1)
+    keep = keep | (torch.arange(M) % S == 0)
+    pl.B, pl.S = B, S
+    pl.cap = cap = (M + 127) // 128 * 128 + 128
+    src = torch.nonzero(keep).squeeze(1)
+    n = src.numel()
+    pl.row_src = torch.full((cap,), -1, dtype=torch.int32)
+    pl.row_src[:n] = src.int()
+    pl.row_dst = torch.full((M,), -1, dtype=torch.int32)
+    pl.row_dst[src] = torch.arange(n, dtype=torch.int32)
+    pl.row_b = torch.full((cap,), -1, dtype=torch.int32)
+    pl.row_b[:n] = (src // S).int()
+    per = keep.view(B, S).sum(1)
+    pl.start = torch.cat([torch.zeros(1, dtype=torch.long), per.cumsum(0)]).int()
+    pl.counts = torch.tensor([min(cap, (n + 127) // 128 * 128 + 128), n, 0, 0], dtype=torch.int32)
+    pl.bias = torch.zeros(cap)
+    pl.bias[:n] = bias.reshape(-1)[src]
+    pl.labels_a = pl.labels_b = None
+    if labels_a is not None:
+        pl.labels_a = torch.full((cap,), -1, dtype=torch.int64)
+        pl.labels_a[:n] = labels_a.reshape(-1)[src]
+    if labels_b is not None:
+        pl.labels_b = torch.full((cap,), -1, dtype=torch.int64)
+        pl.labels_b[:n] = labels_b.reshape(-1)[src]
+    pl.cls_rows = pl.start[:B].long()
+    pl.key_tiles = None
+    return pl
+
+
+def zero_pad_rows(buf, counts):
+    CALLS.append("zero_pad_rows")
+    buf[int(counts[1]): int(counts[0])] = 0
+    return buf
+
+
+def _attn_packed(qkv, plan, heads):
+    """per-sample attention over the packed rows; rows that belong to no sample stay NaN (the kernels never write them)"""
+    out = _nan_like((qkv.size(0), heads * 64), F32)
+    parts = []
+    for b in range(plan.B):
+        s0, s1 = int(plan.start[b]), int(plan.start[b + 1])
+        parts.append((s0, s1, _attn(qkv[s0:s1], plan.bias[None, s0:s1], 1, s1 - s0, heads)))
+    return out, parts
+
+
+def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None, key_tiles=None, plan=None):
     CALLS.append("attention_fwd")
     _no_dropout(dropout_p)
-    out = _attn(qkv.float(), bias, B, S, heads).to(BF16)
+    if plan is None:
+        out = _attn(qkv.float(), bias, B, S, heads).to(BF16)
+        return out, torch.zeros((B, heads, S, 2))
+    out, parts = _attn_packed(qkv.float(), plan, heads)
+    for s0, s1, o in parts:
+        out[s0:s1] = o
+    out = out.to(BF16)
+    zero_pad_rows(out, plan.counts)
     return out, torch.zeros((B, heads, S, 2))
 
 
-def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None, key_tiles=None):
+def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None, key_tiles=None, plan=None):
     CALLS.append("attention_bwd")
     _no_dropout(dropout_p)
     q = qkv.float().requires_grad_(True)
+    if plan is None:
+        with torch.enable_grad():
+            _attn(q, bias, B, S, heads).backward(dctx.float())
+        return q.grad.to(BF16)
     with torch.enable_grad():
-        _attn(q, bias, B, S, heads).backward(dctx.float())
-    return q.grad.to(BF16)
+        _, parts = _attn_packed(q, plan, heads)
+        sum((o * dctx[s0:s1].float()).sum() for s0, s1, o in parts).backward()
+    d = _nan_like(tuple(qkv.shape), BF16)
+    n = int(plan.counts[1])
+    d[:n] = q.grad[:n].to(BF16)
+    zero_pad_rows(d, plan.counts)
+    return d
 
 
 def softmax_ce_fwd(logits, ncols, labels, double_softmax=False):
@@ -412,6 +506,7 @@ def to_bf16(x, addend=None, out=None):
 _OPS = ["layernorm_fwd", "layernorm_bwd", "embed_ln_fwd", "embed_ln_bwd", "colsum", "cast_weight", "pad_cast_concat",
         "dropout_rows", "gather_rows", "scatter_add_rows", "mask_bias", "attention_key_tiles", "attention_fwd", "attention_bwd", "softmax_ce_fwd",
         "softmax_ce_bwd", "action_head_fwd", "action_head_bwd", "pretrain_finalize", "pretrain_finalize_counted", "compact_labels", "row_limit",
+        "pack_plan", "zero_pad_rows",
         "tanh_bwd", "gelu_bwd", "to_f32", "to_bf16"]
 
 

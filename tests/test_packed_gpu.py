@@ -1,0 +1,149 @@
+"""Padding-free (packed-row) execution on the B200: the plan kernel, the variable-length attention kernels and the whole
+pre-training step against the dense layout -- loss, all seven scalars and every gradient must be unchanged (the dropped rows
+are masked as keys and carry no label: vs/encoder.py:226-241,387-389, data_loader_pretrain.py:576,692)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+if torch.cuda.is_available():
+    from visitron_b200 import graph as vgraph, lib, modeling, ops, synthetic
+
+from oracle import visitron_oracle as vo
+from parity_common import load_params, make_config
+
+DEV = "cuda"
+BF = torch.bfloat16
+
+
+def _plan_inputs(B, S, seed, p_keep=0.7, p_lab=0.05):
+    g = torch.Generator().manual_seed(seed)
+    mask = (torch.rand(B, S, generator=g) < p_keep).long()
+    mask[0] = 1                       # a sample without padding
+    if B > 1:
+        mask[1, 1:] = 0               # a sample with only [CLS] left
+    lab = torch.where(torch.rand(B * S, generator=g) < p_lab, torch.randint(0, 100, (B * S,), generator=g), torch.tensor(-1))
+    tok = torch.where(torch.rand(B * S, generator=g) < p_lab / 2, torch.randint(0, 50, (B * S,), generator=g), torch.tensor(-1))
+    return mask, lab, tok
+
+
+@pytest.mark.parametrize("B,S", [(4, 100), (32, 767), (1, 1), (3, 129)])
+def test_pack_plan_matches_restatement(B, S):
+    mask, lab, tok = _plan_inputs(B, S, B * 7 + S)
+    bias = ops.mask_bias(mask.to(DEV))
+    pl = ops.pack_plan(bias, lab.to(DEV), tok.to(DEV), B, S)
+    keep = (mask.reshape(-1) != 0) | (lab != -1) | (tok != -1) | (torch.arange(B * S) % S == 0)
+    src = torch.nonzero(keep).squeeze(1)
+    n = src.numel()
+    c = pl.counts.cpu().tolist()
+    assert c[1] == n and c[0] == min(pl.cap, (n + 127) // 128 * 128 + 128) and pl.cap % 128 == 0
+    assert torch.equal(pl.row_src[:n].cpu().long(), src) and bool((pl.row_src[n:] == -1).all())
+    inv = torch.full((B * S,), -1, dtype=torch.long)
+    inv[src] = torch.arange(n)
+    assert torch.equal(pl.row_dst.cpu().long(), inv)
+    assert torch.equal(pl.row_b[:n].cpu().long(), src // S) and bool((pl.row_b[n:] == -1).all())
+    per = keep.view(B, S).sum(1)
+    assert torch.equal(pl.start.cpu().long(), torch.cat([torch.zeros(1, dtype=torch.long), per.cumsum(0)]))
+    assert torch.equal(pl.cls_rows.cpu(), pl.start[:B].cpu().long())
+    assert torch.equal(pl.bias[:n].cpu(), bias.reshape(-1).cpu()[src])
+    assert torch.equal(pl.labels_a[:n].cpu(), lab[src]) and bool((pl.labels_a[n:] == -1).all())
+    assert torch.equal(pl.labels_b[:n].cpu(), tok[src])
+
+
+@pytest.mark.parametrize("B,S,heads,p", [(5, 300, 3, 0.0), (32, 767, 12, 0.0), (4, 767, 2, 0.1), (2, 64, 1, 0.0)])
+def test_packed_attention_equals_dense_attention(B, S, heads, p):
+    """Same q / k / v values for every kept row, dense layout vs packed layout: ctx and dqkv of the kept rows must be identical (the
+    kernels visit the same tiles of every sample; dropped keys had probability exactly 0)."""
+    torch.manual_seed(B + S)
+    Hh = heads * 64
+    g = torch.Generator().manual_seed(5)
+    lens = torch.randint(1, S + 1, (B,), generator=g)
+    lens[0] = S
+    mask = (torch.arange(S)[None, :] < lens[:, None]).long()          # valid rows first: the packed rows are the dense prefix of each sample
+    bias = ops.mask_bias(mask.to(DEV))
+    qkv = torch.randn(B * S, 3 * Hh, device=DEV).to(BF)
+    dctx = torch.randn(B * S, Hh, device=DEV).to(BF)
+    seed, sid = 77, 3
+    ctx, lse = ops.attention_fwd(qkv, bias, B, S, heads, p, seed, sid, key_tiles=ops.attention_key_tiles(bias))
+    dqkv = ops.attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, p, seed, sid)
+    pl = ops.pack_plan(bias, None, None, B, S)
+    n = int(pl.counts[1])
+    src = pl.row_src[:n].long()
+    qkv_p = torch.zeros(pl.cap, 3 * Hh, device=DEV, dtype=BF)
+    dctx_p = torch.zeros(pl.cap, Hh, device=DEV, dtype=BF)
+    qkv_p[:n], dctx_p[:n] = qkv[src], dctx[src]
+    ctx_p, lse_p = ops.attention_fwd(qkv_p, None, B, S, heads, p, seed, sid, plan=pl)
+    dqkv_p = ops.attention_bwd(qkv_p, None, ctx_p, dctx_p, lse_p, B, S, heads, p, seed, sid, plan=pl)
+    torch.cuda.synchronize()
+    assert torch.equal(ctx_p[:n], ctx[src]), float((ctx_p[:n].float() - ctx[src].float()).abs().max())
+    assert bool((ctx_p[n:int(pl.counts[0])] == 0).all())
+    d = (dqkv_p[:n].float() - dqkv[src].float())
+    assert float(d.abs().max()) <= 1e-2 * float(dqkv[src].float().abs().max()), float(d.abs().max())
+    assert float(d.norm() / dqkv[src].float().norm()) < 2e-3
+    assert bool((dqkv_p[n:int(pl.counts[0])] == 0).all())
+
+
+def _model(layers=2, dropout=0.0):
+    oc = vo.OracleConfig(vocab_size=2048, num_hidden_layers=layers, max_position_embeddings=64, detector_classes=96,
+                         hidden_dropout_prob=dropout, attention_probs_dropout_prob=dropout / 3)
+    m = modeling.PreTrainOscar(make_config(oc))
+    load_params(m, vo.init_params(oc, 5))
+    return oc, m.to(DEV).train()
+
+
+@pytest.mark.parametrize("big", [False, True])
+def test_packed_step_equals_dense_step(big):
+    if big:
+        oc = vo.OracleConfig(num_hidden_layers=2)
+        model = modeling.PreTrainOscar(make_config(oc))
+        load_params(model, vo.init_params(oc, 9))
+        model.to(DEV).train()
+        batch = {k: v.to(DEV) for k, v in synthetic.pretrain_batch(8, 88).items()}
+    else:
+        oc, model = _model()
+        batch = {k: v.to(DEV) for k, v in synthetic.pretrain_batch(3, 88, text_len=40, regions=24, vocab=2048, detector_classes=96).items()}
+        batch["labels"] = batch["labels"].clone()
+        pads = torch.nonzero(batch["attention_mask"][:, :40] == 0)
+        assert pads.numel() > 0
+        b_, t_ = int(pads[0, 0]), int(pads[0, 1])
+        batch["labels"][b_, t_] = 7         # a label on a PADDED text position: the row must survive the packing (it is a query, never a key)
+    res = {}
+    for packed in (False, True):
+        model.vt_packed = packed
+        for p in model.parameters():
+            p.grad = None
+        n0 = lib.launch_count()
+        out = model(**batch)
+        out[0].backward()
+        torch.cuda.synchronize()
+        res[packed] = (torch.stack([o.detach() for o in out]).cpu(), {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None},
+                       lib.launch_count() - n0)
+        del out
+    (o0, g0, _), (o1, g1, _) = res[False], res[True]
+    torch.testing.assert_close(o1, o0, rtol=1e-4, atol=1e-5, equal_nan=True)
+    assert set(g0) == set(g1)
+    for k in g0:
+        d = float((g1[k] - g0[k]).norm()) / max(float(g0[k].norm()), 1e-12)
+        assert d < 2e-3, (k, d)
+    aux = model._vt_last_aux
+    lab = batch["labels"].reshape(-1)
+    assert torch.equal(aux["mlm_rows"].cpu(), torch.nonzero(lab.cpu() != -1).squeeze(1))      # reported in the caller's [B, S] numbering
+
+
+def test_packed_step_in_a_graph_with_dropout_and_changing_padding():
+    oc, model = _model(dropout=0.2)
+    batches = [{k: v.to(DEV) for k, v in synthetic.pretrain_batch(3, 88 + i, text_len=40, regions=24, vocab=2048, detector_classes=96).items()}
+               for i in range(3)]
+    step = vgraph.GraphedStep(model, batches[0], seed=11)
+    losses = [float(step(bt)[0]) for bt in batches + batches]
+    assert all(torch.isfinite(torch.tensor(losses))) and len(set(losses)) == len(losses)
+    # dropout off: the graph over packed rows reproduces the eager dense step on every batch (different row counts per batch)
+    oc, model = _model(dropout=0.0)
+    step = vgraph.GraphedStep(model, batches[0], seed=11)
+    model_d = model
+    for bt in batches:
+        got = float(step(bt)[0])
+        model_d.vt_packed = False
+        ref = float(model_d(**bt)[0])
+        model_d.vt_packed = True
+        assert abs(got - ref) < 1e-4 * max(1.0, abs(ref)), (got, ref)

@@ -44,11 +44,17 @@ __global__ void mask_bias_kernel(const T* __restrict__ mask, long long n, float*
 
 // backward prep: dsum[b, h, i] = sum_d dO[i, h, d] * O[i, h, d]
 __global__ void __launch_bounds__(256)
-attn_bwd_prep_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ out, float* __restrict__ dsum, int B, int S, int heads, int hidden) {
+attn_bwd_prep_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ out, float* __restrict__ dsum, int B, int S, int heads, int hidden,
+                     const int* __restrict__ start, const int* __restrict__ row_b, long long rows_cap) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const long long rows = (long long)B * S;
+  const long long rows = start ? rows_cap : (long long)B * S;
   for (long long m = (long long)blockIdx.x * 8 + warp; m < rows; m += (long long)gridDim.x * 8) {
-    const long long b = m / S, i = m % S;
+    long long b = m / S, i = m % S;
+    if (start) {           // packed rows: (sample, position) of row m; padding rows belong to nobody
+      b = row_b[m];
+      if (b < 0) continue;
+      i = m - start[b];
+    }
     for (int c = lane; c < hidden / 8; c += 32) {  // 8 lanes cover one 64-wide head
       float a[8], o[8];
       unpack8(__ldg(reinterpret_cast<const uint4*>(dout + m * hidden + c * 8)), a);
@@ -80,6 +86,11 @@ struct AttnTcParams {
   bf16* dqkv;          // [B*S, ld]
   long long ld;
   DropoutCfg drop;
+  // Packed rows (padding-free execution): sample b owns rows [start[b], start[b+1]) of the activation buffers instead of
+  // [b S, (b+1) S); S stays the bound (and the stride of lse / dsum).  null = the dense layout.
+  const int* start;    // [B + 1] or null
+  const int* row_b;    // [rows_cap] sample of a packed row, -1 for a padding row (backward prep / dQ reduction) or null
+  long long rows_cap;  // rows of one dQ workspace slice (B S when dense)
   int dbg;             // timing ablations only (VT_ATTN_DBG, results are garbage): 1 skip the element-wise arithmetic, 2 skip the exponentials
 };
 
@@ -137,16 +148,18 @@ constexpr int FWD_MAX_S = 2048;
 // gets the same uniform softmax as the reference).
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
-key_tile_plan_kernel(const float* __restrict__ bias, int S, uint32_t* __restrict__ plan) {
+key_tile_plan_kernel(const float* __restrict__ bias, int S, const int* __restrict__ start, uint32_t* __restrict__ plan) {
   __shared__ float tmax[32];
   const int b = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long base = start ? start[b] : (long long)b * S;   // packed rows: the sample's own range and length
+  if (start) S = start[b + 1] - start[b];
   const int nkt = (S + 63) / 64;
   for (int t = warp; t < 32; t += 4) {
     float m = -INFINITY;
     if (t < nkt) {
       const int k0 = t * 64 + lane, k1 = k0 + 32;
-      if (k0 < S) m = bias[(long long)b * S + k0];
-      if (k1 < S) m = fmaxf(m, bias[(long long)b * S + k1]);
+      if (k0 < S) m = bias[base + k0];
+      if (k1 < S) m = fmaxf(m, bias[base + k1]);
     }
     m = warp_max(m);
     if (lane == 0) tmax[t] = m;
@@ -155,38 +168,51 @@ key_tile_plan_kernel(const float* __restrict__ bias, int S, uint32_t* __restrict
   if (warp == 0) {
     const float m = warp_max(tmax[lane]);
     const uint32_t live = __ballot_sync(0xffffffffu, tmax[lane] > m - 5000.0f && lane < nkt);
-    if (lane == 0) plan[b] = live ? live : (nkt == 32 ? 0xffffffffu : (1u << nkt) - 1u);
+    if (lane == 0) plan[b] = live ? live : (nkt >= 32 ? 0xffffffffu : (1u << nkt) - 1u);
   }
 }
 
-// walks the live key tiles of a CTA's items in order (same sequence in the TMA, MMA and softmax roles)
+// walks the live key tiles of a CTA's items in order (same sequence in the TMA, MMA and softmax roles).  An item is a (128-query
+// tile, head, sample); with packed rows a sample may be shorter than S, and the query tiles past its end are skipped by every
+// role alike -- `lit` counts the items that were NOT skipped and drives the parities of the per-item barriers.
 struct TileCursor {
   const uint32_t* plan;
-  int item0, my_items, items_per_sample;
-  uint32_t dense;
-  int it;
+  const int* start;
+  int item0, my_items, nqt, heads, S;
+  int it, lit;
+  int qt, h, b, sb, len;     // the current item: query tile, head, sample, the sample's first row and length
   uint32_t full, rem;
   __device__ __forceinline__ void load() {
-    if (it < my_items) {
-      full = plan ? __ldg(plan + (item0 + it) / items_per_sample) : dense;
-      rem = full;
-    } else {
-      full = rem = 0;
+    while (it < my_items) {
+      const int id = item0 + it;
+      qt = id % nqt; h = (id / nqt) % heads; b = id / (nqt * heads);
+      sb = start ? __ldg(start + b) : b * S;
+      len = start ? __ldg(start + b + 1) - sb : S;
+      if (qt * FQ < len) {
+        const int nkt = (len + FK - 1) / FK;
+        const uint32_t dense = nkt >= 32 ? 0xffffffffu : (1u << nkt) - 1u;
+        full = plan ? (__ldg(plan + b) & dense) : dense;
+        if (!full) full = dense;
+        rem = full;
+        return;
+      }
+      ++it;
     }
+    full = rem = 0;
   }
-  __device__ __forceinline__ void init(const uint32_t* pl, int i0, int n, int ips, int nkt) {
-    plan = pl; item0 = i0; my_items = n; items_per_sample = ips;
-    dense = nkt == 32 ? 0xffffffffu : (1u << nkt) - 1u;
-    it = 0;
+  __device__ __forceinline__ void init(const AttnTcParams& p, int i0, int n, int nqt_) {
+    plan = p.key_tiles; start = p.start; item0 = i0; my_items = n; nqt = nqt_; heads = p.heads; S = p.S;
+    it = 0; lit = 0;
     load();
   }
   __device__ __forceinline__ bool done() const { return it >= my_items; }
   __device__ __forceinline__ int tile() const { return __ffs((int)rem) - 1; }
   __device__ __forceinline__ bool first() const { return rem == full; }
   __device__ __forceinline__ bool last() const { return (rem & (rem - 1)) == 0; }
+  __device__ __forceinline__ void next_item() { ++it; ++lit; load(); }
   __device__ __forceinline__ void next() {
     rem &= rem - 1;
-    if (!rem) { ++it; load(); }
+    if (!rem) next_item();
   }
 };
 
@@ -212,7 +238,6 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   const int n_items = nqt * p.heads * p.B;
   const int item0 = (int)((long long)n_items * blockIdx.x / gridDim.x), item1 = (int)((long long)n_items * (blockIdx.x + 1) / gridDim.x);
   const int my_items = item1 - item0;
-  auto decode = [&](int id, int& qt, int& h, int& b) { qt = id % nqt; h = (id / nqt) % p.heads; b = id / (nqt * p.heads); };
 
   if (warp == FWD_SM_WARPS && lane == 0) {
     prefetch_tensormap(&tmQ);
@@ -244,17 +269,16 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     // ---------------- TMA producer: runs ahead of the consumers across items, bounded by the rings ----------------
     if (lane == 0) {
       TileCursor c;
-      c.init(p.key_tiles, item0, my_items, nqt * p.heads, nkt);
-      int qt = 0, h = 0, b = 0;
+      c.init(p, item0, my_items, nqt);
       for (int g = 0; !c.done(); ++g, c.next()) {
+        const int h = c.h;
         if (c.first()) {
-          const int it = c.it, qb = it % FWD_QB;
-          decode(item0 + it, qt, h, b);
+          const int it = c.lit, qb = it % FWD_QB;
           if (it >= FWD_QB) mbar_wait_backoff(q_empty + 8 * qb, (uint32_t)((it / FWD_QB - 1) & 1), 32);
           mbar_arrive_expect_tx(q_full + 8 * qb, 16384);
-          tma_load_2d(sQ + qb * 16384, &tmQ, q_full + 8 * qb, h * 64, b * S + qt * FQ);
+          tma_load_2d(sQ + qb * 16384, &tmQ, q_full + 8 * qb, h * 64, c.sb + c.qt * FQ);
         }
-        const int j = c.tile(), row_base = b * S;
+        const int j = c.tile(), row_base = c.sb;
         const int st = g % FWD_KV;
         const uint32_t ph = (uint32_t)((g / FWD_KV - 1) & 1);
         if (g >= FWD_KV) mbar_wait_backoff(k_empty + 8 * st, ph, 32);
@@ -271,11 +295,11 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       constexpr uint32_t idesc_s = make_idesc_bf16(128, FK, 0, 0);   // S[128 q, 64 keys] = Q (K-major) x K (K-major)
       constexpr uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);   // O[128 q, 64 d]   = P (K-major) x V (MN-major)
       TileCursor ci, cc;   // ci: the next S to issue (runs two tiles ahead), cc: the next P.V
-      ci.init(p.key_tiles, item0, my_items, nqt * p.heads, nkt);
-      cc.init(p.key_tiles, item0, my_items, nqt * p.heads, nkt);
+      ci.init(p, item0, my_items, nqt);
+      cc.init(p, item0, my_items, nqt);
       int gi = 0;
       auto issue_s = [&]() {   // S(gi) -> TMEM buffer gi & 1; frees its K stage (and the item's Q buffer after its last tile)
-        const int it = ci.it, st = gi % FWD_KV, qb = it % FWD_QB;
+        const int it = ci.lit, st = gi % FWD_KV, qb = it % FWD_QB;
         if (ci.first()) mbar_wait_backoff(q_full + 8 * qb, (uint32_t)((it / FWD_QB) & 1), MMA_POLL_NS);
         mbar_wait_backoff(k_full + 8 * st, (uint32_t)((gi / FWD_KV) & 1), MMA_POLL_NS);
         tc_fence_after();
@@ -302,7 +326,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         const int vst = g % FWD_KV;
         mbar_wait_backoff(v_full + 8 * vst, (uint32_t)((g / FWD_KV) & 1), MMA_POLL_NS);
         const bool first = cc.first();
-        if (first && cc.it > 0) mbar_wait_backoff(o_free, (uint32_t)((cc.it - 1) & 1), MMA_POLL_NS);   // previous item's O drained
+        if (first && cc.lit > 0) mbar_wait_backoff(o_free, (uint32_t)((cc.lit - 1) & 1), MMA_POLL_NS);   // previous item's O drained
         tc_fence_after();
         const uint64_t a = make_smem_desc(sP + bf * 16384, 16, 1024), bd = make_smem_desc(sV + vst * 8192, 8192, 1024);
         if (!VT_DBG(16)) {
@@ -322,20 +346,20 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     const uint32_t lane_o = tmem_o + ((uint32_t)(quad * 32) << 16) + COLS * half;   // this thread's columns of O
     const DropoutCfg dcfg = resolve_dropout(p.drop);
     int g = 0, b_loaded = -1;
-    for (int it = 0; it < my_items; ++it) {
-      int qt, h, b;
-      decode(item0 + it, qt, h, b);
-      const int row_base = b * S;
+    TileCursor cs;
+    for (cs.init(p, item0, my_items, nqt); !cs.done(); cs.next_item()) {
+      const int qt = cs.qt, h = cs.h, b = cs.b;
+      const int row_base = cs.sb, len = cs.len;
       const int qi = qt * FQ + r;
       const uint32_t bh = (uint32_t)(b * p.heads + h);
       if (b != b_loaded) {   // a contiguous item range changes sample at most a few times per CTA
         asm volatile("bar.sync 9, %0;" ::"n"(FWD_SM_WARPS * 32) : "memory");   // every softmax warp has left the previous sample's last tile
-        for (int k = sm_tid; k < nkt * FK; k += FWD_SM_WARPS * 32) sBias[k] = k < S ? p.bias[(long long)b * S + k] : -INFINITY;
+        for (int k = sm_tid; k < nkt * FK; k += FWD_SM_WARPS * 32) sBias[k] = k < len ? p.bias[(long long)row_base + k] : -INFINITY;
         asm volatile("bar.sync 9, %0;" ::"n"(FWD_SM_WARPS * 32) : "memory");
         b_loaded = b;
       }
       float m_used = -INFINITY, l = 0.f;   // l: sum over this thread's columns only
-      const uint32_t live = p.key_tiles ? __ldg(p.key_tiles + b) : (nkt == 32 ? 0xffffffffu : (1u << nkt) - 1u);
+      const uint32_t live = cs.full;
       for (uint32_t rem = live; rem; rem &= rem - 1, ++g) {
         const int j = __ffs((int)rem) - 1;   // the tile's real index: bias columns and dropout counters do not move
         const int bf = g & 1;
@@ -455,7 +479,7 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       if (lane == 0) mbar_arrive(o_free);   // the next item's first P.V may overwrite O
       const float inv = 1.0f / l;
       const float onorm = dcfg.thresh16 ? inv * dcfg.scale : inv;
-      if (qi < S) {
+      if (qi < len) {
         bf16* dst = p.out + ((long long)row_base + qi) * p.hidden + h * 64 + COLS * half;
 #pragma unroll
         for (int ch = 0; ch < COLS / 8; ++ch) {
@@ -498,6 +522,29 @@ constexpr int BWD_SMEM_TILES = (8 + 2 * BWD_NST) * TILE16K;  // K[2], V[2], Q[NS
 // Registers: a CTA is allocated in whole warpgroups, so 18 warps cost as much as 20 and cap every thread at 96 registers
 // (a setmaxnreg split does not help: the MMA-issuing warp itself needs ~90).  The element-wise loop is arranged to fit: the
 // next tile's row statistics are requested only after the pair's arithmetic, when the S / dP values are dead.
+// This CTA's items (128-key tile, head, sample), round-robin over the grid, in order; with packed rows the key tiles past a
+// sample's end are skipped by every role alike.  `lit` numbers the items that were not skipped (K / V buffer and accumulator
+// parities), `nin` is the item's number of query tiles.
+struct BwdItemCursor {      // loop-invariant inputs (p, nin_max, n_items) are passed in, not stored: the element-wise warps run at a 96-register cap
+  int id, lit;
+  int kt, h, b, sb, len, nin;
+  __device__ __forceinline__ bool valid(int n_items) const { return id < n_items; }
+  __device__ __forceinline__ void settle(const AttnTcParams& p, int nin_max, int n_items) {     // moves to the first non-empty item at or after id
+    while (id < n_items) {
+      kt = id % nin_max; h = (id / nin_max) % p.heads; b = id / (nin_max * p.heads);
+      sb = p.start ? __ldg(p.start + b) : b * p.S;
+      len = p.start ? __ldg(p.start + b + 1) - sb : p.S;
+      if (kt * 128 < len) { nin = (len + 127) / 128; return; }
+      id += (int)gridDim.x;
+    }
+  }
+  __device__ __forceinline__ void init(const AttnTcParams& p, int nin_max, int n_items) {
+    id = (int)blockIdx.x; lit = 0;
+    settle(p, nin_max, n_items);
+  }
+  __device__ __forceinline__ void next(const AttnTcParams& p, int nin_max, int n_items) { id += (int)gridDim.x; ++lit; settle(p, nin_max, n_items); }
+};
+
 __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -515,11 +562,9 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  const int S = p.S;
-  const int nin = (S + 127) / 128;       // query tiles of a sample == key tiles of a sample
+  const int nin = (p.S + 127) / 128;     // key / query tiles of a full-length sample (the item numbering's bound)
   const int hid = p.hidden;
   const int n_items = nin * p.heads * p.B;
-  auto decode = [&](int id, int& kt, int& h, int& b) { kt = id % nin; h = (id / nin) % p.heads; b = id / (nin * p.heads); };
 
   if (warp == BWD_EW_WARPS && lane == 0) {
     prefetch_tensormap(&tmQKV);
@@ -549,16 +594,16 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
   if (warp == BWD_EW_WARPS) {
     // ---------------- TMA producer ----------------
     if (lane == 0) {
-      int n = 0, it = 0;
-      for (int id = blockIdx.x; id < n_items; id += gridDim.x, ++it) {
-        int kt, h, b;
-        decode(id, kt, h, b);
-        const int row_base = b * S, kvb = it & 1;
+      int n = 0;
+      BwdItemCursor c;
+      for (c.init(p, nin, n_items); c.valid(n_items); c.next(p, nin, n_items)) {
+        const int kt = c.kt, h = c.h, it = c.lit;
+        const int row_base = c.sb, kvb = it & 1;
         if (it >= 2) mbar_wait_backoff(kv_empty + 8 * kvb, (uint32_t)(((it >> 1) - 1) & 1), 64);
         mbar_arrive_expect_tx(kv_full + 8 * kvb, 2 * TILE16K);
         tma_load_2d(sK + kvb * TILE16K, &tmQKV, kv_full + 8 * kvb, hid + h * 64, row_base + kt * 128);
         tma_load_2d(sV + kvb * TILE16K, &tmQKV, kv_full + 8 * kvb, 2 * hid + h * 64, row_base + kt * 128);
-        for (int t = 0; t < nin; ++t, ++n) {
+        for (int t = 0; t < c.nin; ++t, ++n) {
           const int st = n % BWD_NST;
           if (n >= BWD_NST) mbar_wait_backoff(in_empty + 8 * st, (uint32_t)((n / BWD_NST - 1) & 1), 64);
           if (VT_DBG(512) && n >= BWD_NST) { mbar_arrive(in_full + 8 * st); continue; }
@@ -574,11 +619,10 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);
       constexpr uint32_t idesc_t = make_idesc_bf16(128, 64, 1, 1);  // acc[128 keys, 64] += X^T (MN-major A) x Y (MN-major B)
       constexpr uint32_t idesc_q = make_idesc_bf16(128, 64, 0, 1);  // dQ[128 q, 64]    = dS (K-major A) x K (MN-major B)
-      const int my_items = n_items > (int)blockIdx.x ? (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-      const int n_pairs = my_items * nin;
-      // pair n of this CTA: item n / nin (K / V buffer (n / nin) & 1), query tile n % nin, ring stage n % BWD_NST
-      auto issue_sdp = [&](int n) {
-        const int st = n % BWD_NST, kvb = (n / nin) & 1;
+      // pair n of this CTA = (live item cur.lit, query tile t): K / V buffer cur.lit & 1, ring stage n % BWD_NST.  `nxt` runs one
+      // pair ahead: S / dP of pair n + 1 are issued before the accumulations of pair n.
+      auto issue_sdp = [&](int n, int kvb) {
+        const int st = n % BWD_NST;
         // S = Q.K^T ; dP = dO.V^T   (A: query-side tile, B: key-side tile, both K-major over d = 64)
         const uint64_t qa = make_smem_desc(sQ + st * TILE16K, 16, 1024), kb = make_smem_desc(sK + kvb * TILE16K, 16, 1024);
         const uint64_t da = make_smem_desc(sDO + st * TILE16K, 16, 1024), vb = make_smem_desc(sV + kvb * TILE16K, 16, 1024);
@@ -590,21 +634,27 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         }
         umma_commit(sdp_full);
       };
-      if (n_pairs > 0) {
+      BwdItemCursor cur, nxt;
+      cur.init(p, nin, n_items);
+      nxt = cur;
+      int t = 0, t_nxt = 0;     // query tile of pair n / of pair n + 1
+      if (cur.valid(n_items)) {
         mbar_wait_backoff(kv_full, 0, MMA_POLL_NS);
         mbar_wait_backoff(in_full, 0, MMA_POLL_NS);
         tc_fence_after();
-        issue_sdp(0);
+        issue_sdp(0, 0);
       }
-      for (int n = 0; n < n_pairs; ++n) {
-        const int it = n / nin, t = n % nin, kvb = it & 1;
-        if (n + 1 < n_pairs) {
-          const int it1 = (n + 1) / nin;
-          if ((n + 1) % nin == 0) mbar_wait_backoff(kv_full + 8 * (it1 & 1), (uint32_t)((it1 >> 1) & 1), MMA_POLL_NS);
+      for (int n = 0; cur.valid(n_items); ++n) {
+        const int it = cur.lit, kvb = it & 1;
+        // advance the look-ahead cursor to pair n + 1
+        if (++t_nxt == nxt.nin) { nxt.next(p, nin, n_items); t_nxt = 0; }
+        if (nxt.valid(n_items)) {
+          const int it1 = nxt.lit;
+          if (t_nxt == 0) mbar_wait_backoff(kv_full + 8 * (it1 & 1), (uint32_t)((it1 >> 1) & 1), MMA_POLL_NS);
           mbar_wait_backoff(in_full + 8 * ((n + 1) % BWD_NST), (uint32_t)(((n + 1) / BWD_NST) & 1), MMA_POLL_NS);
           mbar_wait_backoff(sdp_free, (uint32_t)(n & 1), MMA_POLL_NS);
           tc_fence_after();
-          issue_sdp(n + 1);
+          issue_sdp(n + 1, it1 & 1);
         }
         mbar_wait_backoff(pds_ready, (uint32_t)(n & 1), MMA_POLL_NS);
         if (n >= 2) mbar_wait_backoff(dq_free + 8 * (n & 1), (uint32_t)(((n >> 1) - 1) & 1), MMA_POLL_NS);
@@ -634,10 +684,12 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         umma_commit(pds_free);
         umma_commit(in_empty + 8 * st);
         umma_commit(dq_full + 8 * dqb);
-        if (t == nin - 1) {
+        if (t == cur.nin - 1) {
           umma_commit(acc_full);
           umma_commit(kv_empty + 8 * kvb);
         }
+        // pair n + 1 becomes the current pair
+        if (++t == cur.nin) { cur = nxt; t = 0; }
       }
     }
   } else {
@@ -705,36 +757,44 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       }
       acc_pending = false;
     };
-    int n = 0, it = 0;
+    int n = 0;
     float2 lse_n = make_float2(0.f, 0.f);   // row statistics of the NEXT tile (fetched a tile, and across items an item, ahead)
     float dsum_n = 0.f;
     bf16* pend = nullptr;  // where the dQ partial of pair n - 1 goes (null: row past the end of the sample)
     // mask bias of the item's 128 keys: copied into the other half of sBias one item ahead with cp.async (no register is
     // held across the item and the global-load latency is not exposed at the item boundary)
-    auto fetch_bias = [&](int id2, int slot) {
-      if (ew_tid < 128 && id2 < n_items) {
-        int kt2, h2, b2;
-        decode(id2, kt2, h2, b2);
-        const int k = kt2 * 128 + ew_tid;
+    auto fetch_bias = [&](const BwdItemCursor& c2, int slot) {   // c2: the item the slot is for (nothing to do past the last one)
+      if (ew_tid < 128 && c2.valid(n_items)) {
+        const int k = c2.kt * 128 + ew_tid;
         float* dst = sBias + slot * 128 + ew_tid;
-        if (k < S) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(p.bias + (long long)b2 * S + k) : "memory");
+        if (k < c2.len) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(p.bias + (long long)c2.sb + k) : "memory");
         else *dst = -INFINITY;
       }
     };
-    fetch_bias((int)blockIdx.x, 0);
-    for (int id = blockIdx.x; id < n_items; id += gridDim.x, ++it) {
-      int kt, h, b;
-      decode(id, kt, h, b);
-      const int row_base = b * S;
+    BwdItemCursor cur;
+    cur.init(p, nin, n_items);
+    fetch_bias(cur, 0);
+    const int nin_max = nin;
+    for (; cur.valid(n_items); cur.next(p, nin_max, n_items)) {
+      const int kt = cur.kt, h = cur.h, b = cur.b, it = cur.lit;
+      const int S = cur.len;         // everything below is bounded by the SAMPLE's length (== p.S in the dense layout)
+      const int nin = cur.nin;
+      const int row_base = cur.sb;
       const uint32_t bh = (uint32_t)(b * p.heads + h);
-      const long long stat_base = ((long long)b * p.heads + h) * S;
+      const long long stat_base = ((long long)b * p.heads + h) * p.S;
       float* sB = sBias + (it & 1) * 128;
       asm volatile("cp.async.wait_all;" ::: "memory");
       asm volatile("bar.sync 1, %0;" ::"n"(BWD_EW_WARPS * 32) : "memory");  // element-wise warps only
-      fetch_bias(id + (int)gridDim.x, (it + 1) & 1);  // that half was last read in item it - 1, which every warp has left
+      long long next_stat = -1;        // where the NEXT live item's first-tile row statistics are (bias / statistics run an item ahead)
+      {
+        BwdItemCursor nxt = cur;
+        nxt.next(p, nin_max, n_items);
+        fetch_bias(nxt, (it + 1) & 1);  // that half was last read in item it - 1, which every warp has left
+        if (nxt.valid(n_items)) next_stat = ((long long)nxt.b * p.heads + nxt.h) * p.S + min(r, nxt.len - 1);
+      }
       const float* bias = sB + cq * 32;
       // this warp's 16 of the 64 dQ columns in this key tile's slice of the workspace
-      bf16* ws = p.dq_ws + ((long long)kt * p.B * S + row_base) * hid + h * 64 + 16 * cq;
+      bf16* ws = p.dq_ws + ((long long)kt * p.rows_cap + row_base) * hid + h * 64 + 16 * cq;
       auto load_stats = [&](int t, float2& lse, float& ds) {
         const int gc = min(t * 128 + r, S - 1);
         lse = *reinterpret_cast<const float2*>(p.lse + 2 * (stat_base + gc));
@@ -804,10 +864,8 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         // barrier round trip and the dQ drain below
         if (t + 1 < nin) {
           load_stats(t + 1, lse_n, dsum_n);
-        } else if (id + (int)gridDim.x < n_items) {   // the next item's first tile (its load latency was exposed at every item start)
-          int kt2, h2, b2;
-          decode(id + (int)gridDim.x, kt2, h2, b2);
-          const long long sb2 = ((long long)b2 * p.heads + h2) * S + min(r, S - 1);
+        } else if (next_stat >= 0) {   // the next item's first tile (its load latency was exposed at every item start)
+          const long long sb2 = next_stat;
           lse_n = *reinterpret_cast<const float2*>(p.lse + 2 * sb2);
           dsum_n = p.dsum[sb2];
         }
@@ -834,7 +892,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       acc_row = go < S ? p.dqkv + ((long long)row_base + go) * p.ld + h * 64 + 16 * cq : nullptr;
       acc_pending = true;
     }
-    if (acc_pending) drain_acc(it - 1);
+    if (acc_pending) drain_acc(cur.lit - 1);
     if (n > 0) drain_dq(n - 1, pend);
   }
   tc_fence_before();
@@ -845,13 +903,17 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
 // dQ[row, c] = factor * sum over key tiles of the workspace slices, in key-tile order (deterministic) -> bf16 into dqkv[:, 0:hidden]
 __global__ void __launch_bounds__(256)
 attn_dq_reduce_kernel(const bf16* __restrict__ ws, long long slice, int nkt, long long rows, int hidden, float factor, bf16* __restrict__ dqkv,
-                      long long ld) {
+                      long long ld, const int* __restrict__ start, const int* __restrict__ row_b) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   const long long per_row = hidden / 8;
   const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
   if (i >= rows * per_row) return;
   const long long row = i / per_row;
   const int c = (int)(i % per_row) * 8;
+  if (start) {   // packed rows: a row has partials from its own sample's key tiles only; padding rows get dQ = 0
+    const int b = row_b[row];
+    nkt = b < 0 ? 0 : (start[b + 1] - start[b] + 127) / 128;
+  }
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   for (int k = 0; k < nkt; ++k) {
     float f[8];
@@ -906,18 +968,26 @@ static int attn_dbg() {
   return v;
 }
 
-extern "C" int vt_attention_key_tiles(const float* bias, int64_t B, int64_t S, uint32_t* key_tiles, vt_stream stream) {
+static int key_tiles_impl(const float* bias, const int32_t* start, int64_t B, int64_t S, uint32_t* key_tiles, vt_stream stream) {
   VT_REQUIRE(bias && key_tiles && B > 0 && S > 0, "vt_attention_key_tiles: bad arguments");
   VT_REQUIRE(S <= 2048, "vt_attention_key_tiles: a plan is 32 tiles of 64 keys (S <= 2048); pass no plan for longer sequences");
-  launch_pdl(key_tile_plan_kernel, (unsigned)B, 128, 0, (cudaStream_t)stream, bias, (int)S, key_tiles);
+  launch_pdl(key_tile_plan_kernel, (unsigned)B, 128, 0, (cudaStream_t)stream, bias, (int)S, (const int*)start, key_tiles);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
 }
 
-extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, int64_t B, int64_t S, int64_t heads,
-                                int64_t head_dim, void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream,
-                                vt_stream stream) {
+extern "C" int vt_attention_key_tiles(const float* bias, int64_t B, int64_t S, uint32_t* key_tiles, vt_stream stream) {
+  return key_tiles_impl(bias, nullptr, B, S, key_tiles, stream);
+}
+extern "C" int vt_attention_key_tiles_packed(const float* bias, const int32_t* start, int64_t B, int64_t S, uint32_t* key_tiles, vt_stream stream) {
+  VT_REQUIRE(start, "vt_attention_key_tiles_packed: start required");
+  return key_tiles_impl(bias, start, B, S, key_tiles, stream);
+}
+
+static int attention_fwd_impl(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, const int32_t* start, int64_t rows_cap,
+                              int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* ctx, float* lse, float dropout_p, uint64_t seed,
+                              uint32_t dropout_stream, vt_stream stream) {
   int rc = check_attn_tc("vt_attention_fwd", qkv, ld, B, S, heads, head_dim);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
@@ -927,12 +997,15 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
   VT_REQUIRE(S <= FWD_MAX_S, "vt_attention_fwd: the tcgen05 kernel keeps the mask bias of a sample in shared memory (S <= %d)", FWD_MAX_S);
   const int64_t hidden = heads * 64;
   CUtensorMap tq, tkv;
-  rc = make_map(&tq, qkv, (uint64_t)(3 * hidden), (uint64_t)(B * S), (uint64_t)ld, 64, FQ);
+  const int64_t rows = start ? rows_cap : B * S;     // rows of the activation buffers (packed: the caller's capacity)
+  VT_REQUIRE(rows > 0 && rows < (1ll << 31), "vt_attention_fwd: bad row capacity");
+  rc = make_map(&tq, qkv, (uint64_t)(3 * hidden), (uint64_t)rows, (uint64_t)ld, 64, FQ);
   if (rc) return rc;
-  rc = make_map(&tkv, qkv, (uint64_t)(3 * hidden), (uint64_t)(B * S), (uint64_t)ld, 64, FK);
+  rc = make_map(&tkv, qkv, (uint64_t)(3 * hidden), (uint64_t)rows, (uint64_t)ld, 64, FK);
   if (rc) return rc;
   AttnTcParams p = {};
   p.B = (int)B; p.S = (int)S; p.heads = (int)heads; p.hidden = (int)hidden;
+  p.start = (const int*)start; p.rows_cap = rows;
   p.bias = bias; p.key_tiles = key_tiles; p.scale = 0.125f; p.out = (bf16*)ctx; p.lse = lse; p.ld = ld;
   p.drop = make_dropout(dropout_p, seed, dropout_stream);
   p.dbg = attn_dbg();
@@ -963,9 +1036,22 @@ extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, 
   return VT_OK;
 }
 
-extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, const void* ctx, const void* dctx,
-                                const float* lse, float* dsum_ws, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv,
-                                float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream) {
+extern "C" int vt_attention_fwd(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, int64_t B, int64_t S, int64_t heads,
+                                int64_t head_dim, void* ctx, float* lse, float dropout_p, uint64_t seed, uint32_t dropout_stream,
+                                vt_stream stream) {
+  return attention_fwd_impl(qkv, ld, bias, key_tiles, nullptr, 0, B, S, heads, head_dim, ctx, lse, dropout_p, seed, dropout_stream, stream);
+}
+extern "C" int vt_attention_fwd_packed(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, const int32_t* start,
+                                       int64_t rows_cap, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* ctx, float* lse,
+                                       float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream) {
+  VT_REQUIRE(start, "vt_attention_fwd_packed: start required");
+  return attention_fwd_impl(qkv, ld, bias, key_tiles, start, rows_cap, B, S, heads, head_dim, ctx, lse, dropout_p, seed, dropout_stream, stream);
+}
+
+static int attention_bwd_impl(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, const int32_t* start, const int32_t* row_b,
+                              int64_t rows_cap, const void* ctx, const void* dctx, const float* lse, float* dsum_ws, int64_t B, int64_t S,
+                              int64_t heads, int64_t head_dim, void* dqkv, float dropout_p, uint64_t seed, uint32_t dropout_stream,
+                              vt_stream stream) {
   int rc = check_attn_tc("vt_attention_bwd", qkv, ld, B, S, heads, head_dim);
   if (rc) return rc;
   VT_REQUIRE(((uintptr_t)dqkv & 15) == 0 && ((uintptr_t)ctx & 15) == 0 && ((uintptr_t)dctx & 15) == 0, "vt_attention_bwd: 16-byte alignment required");
@@ -974,14 +1060,17 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
   if (rc) return rc;
   const int64_t hidden = heads * 64;
   CUtensorMap tq, tdo;
-  rc = make_map(&tq, qkv, (uint64_t)(3 * hidden), (uint64_t)(B * S), (uint64_t)ld, 64, 128);
+  const int64_t rows_all = start ? rows_cap : B * S;
+  VT_REQUIRE(rows_all > 0 && rows_all < (1ll << 31) && (!start || row_b), "vt_attention_bwd: bad row capacity / row map");
+  rc = make_map(&tq, qkv, (uint64_t)(3 * hidden), (uint64_t)rows_all, (uint64_t)ld, 64, 128);
   if (rc) return rc;
-  rc = make_map(&tdo, dctx, (uint64_t)hidden, (uint64_t)(B * S), (uint64_t)hidden, 64, 128);
+  rc = make_map(&tdo, dctx, (uint64_t)hidden, (uint64_t)rows_all, (uint64_t)hidden, 64, 128);
   if (rc) return rc;
   {
-    const long long prows = B * S;
+    const long long prows = rows_all;
     long long pg = (prows + 7) / 8, cap = (long long)num_sms() * 8;
-    attn_bwd_prep_kernel<<<(int)(pg < cap ? pg : cap), 256, 0, st>>>((const bf16*)dctx, (const bf16*)ctx, dsum_ws, (int)B, (int)S, (int)heads, (int)hidden);
+    attn_bwd_prep_kernel<<<(int)(pg < cap ? pg : cap), 256, 0, st>>>((const bf16*)dctx, (const bf16*)ctx, dsum_ws, (int)B, (int)S, (int)heads, (int)hidden,
+                                                                     (const int*)start, (const int*)row_b, (long long)rows_all);
     count_launch(1);
     VT_CHECK_LAUNCH();
   }
@@ -994,6 +1083,7 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
   // a 128-key tile is dead as a whole for ~3 % of the items only.  Numbering the live items per sample (prefix table in shared
   // memory, binary search per item) was built and measured: 441 -> 445 us per layer, and the extra registers cost the dense case 6 %.
   (void)key_tiles;
+  p.start = (const int*)start; p.row_b = (const int*)row_b; p.rows_cap = rows_all;
   p.bias = bias; p.scale = 0.125f; p.lse = const_cast<float*>(lse); p.dsum = dsum_ws; p.dq_ws = reinterpret_cast<bf16*>(dsum_ws + dsum_floats);
   p.dqkv = (bf16*)dqkv; p.ld = ld;
   p.drop = make_dropout(dropout_p, seed, dropout_stream);
@@ -1008,11 +1098,31 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
   const long long n_items = (long long)nt * heads * B;
   const int sms = usable_sms();  // leaves the SMs of an overlapped gradient exchange alone (vt_reserve_sms)
   launch_pdl(attn_bwd_fused, (unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st, tq, tdo, p);
-  const long long rows = B * S;
+  const long long rows = rows_all;
   const long long items = rows * (hidden / 8);
   launch_pdl(attn_dq_reduce_kernel, (unsigned)((items + 255) / 256), 256, 0, st, p.dq_ws, rows * hidden, nt, rows, (int)hidden,
-                                                                         p.scale * (p.drop.thresh16 ? p.drop.scale : 1.0f), (bf16*)dqkv, ld);
+                                                                         p.scale * (p.drop.thresh16 ? p.drop.scale : 1.0f), (bf16*)dqkv, ld,
+                                                                         (const int*)start, (const int*)row_b);
   count_launch(2);
   VT_CHECK_LAUNCH();
   return VT_OK;
+}
+
+extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, const void* ctx, const void* dctx,
+                                const float* lse, float* dsum_ws, int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv,
+                                float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream) {
+  return attention_bwd_impl(qkv, ld, bias, key_tiles, nullptr, nullptr, 0, ctx, dctx, lse, dsum_ws, B, S, heads, head_dim, dqkv, dropout_p, seed,
+                            dropout_stream, stream);
+}
+extern "C" int64_t vt_attention_bwd_workspace_packed(int64_t rows_cap, int64_t B, int64_t S, int64_t heads) {
+  const int64_t dsum_floats = (B * heads * S + 3) & ~(int64_t)3;
+  return dsum_floats + ((S + 127) / 128) * rows_cap * heads * 64 / 2;
+}
+extern "C" int vt_attention_bwd_packed(const void* qkv, int64_t ld, const float* bias, const uint32_t* key_tiles, const int32_t* start,
+                                       const int32_t* row_b, int64_t rows_cap, const void* ctx, const void* dctx, const float* lse, float* dsum_ws,
+                                       int64_t B, int64_t S, int64_t heads, int64_t head_dim, void* dqkv, float dropout_p, uint64_t seed,
+                                       uint32_t dropout_stream, vt_stream stream) {
+  VT_REQUIRE(start && row_b, "vt_attention_bwd_packed: start and row_b required");
+  return attention_bwd_impl(qkv, ld, bias, key_tiles, start, row_b, rows_cap, ctx, dctx, lse, dsum_ws, B, S, heads, head_dim, dqkv, dropout_p, seed,
+                            dropout_stream, stream);
 }

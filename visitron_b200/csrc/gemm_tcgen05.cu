@@ -44,6 +44,8 @@ struct GemmParams {
   long long remap_in, remap_out, remap_off;
   // device-resident row count of the A operand (vt_set_row_limit): limits M when A is [M, K], K when A is [K, M]
   const int32_t* rows_dev;
+  // optional output row map (packed rows): logical row m is written to row remap_index[m], or nowhere when that is negative
+  const int32_t* remap_index;
 };
 
 template <int BN>
@@ -90,6 +92,10 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, const Dropou
   if (n0 >= p.N) return;
   long long orow = m;
   if (G && p.remap_in > 0) orow = (long long)(m / p.remap_in) * p.remap_out + p.remap_off + (m % p.remap_in);
+  if (G && p.remap_index) {
+    orow = __ldg(p.remap_index + orow);
+    if (orow < 0) return;
+  }
   const bool vec = G ? (p.vec_ok && ncols == 8) : true;
   if (G ? (p.bias != nullptr) : (EPI & EPI_BIAS) != 0) {
 #pragma unroll
@@ -603,6 +609,7 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   p.drop = make_dropout(ep->dropout_p, ep->seed, ep->dropout_stream);
   p.remap_in = ep->remap_rows_in; p.remap_out = ep->remap_rows_out; p.remap_off = ep->remap_row_off;
   p.rows_dev = row_limit();
+  p.remap_index = ep->remap_index;
   // 16-byte vector path: every row slice the epilogue touches must be 16-byte aligned
   const int ob = p.out_fp32 ? 4 : 2;
   bool vec = ((uintptr_t)D % 16 == 0) && ((ldd * ob) % 16 == 0);
@@ -624,7 +631,7 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   int grid = (int)(total < sms ? total : sms);
   cudaStream_t st = (cudaStream_t)stream;
   // the encoder's hot epilogues as compile-time kinds (see EPI_*); everything else takes the generic kernel
-  const bool fast_ok = BN == 256 && !p.out_fp32 && !p.accumulate && p.remap_in <= 0 && p.vec_ok && N % 8 == 0 && p.splits == 1;
+  const bool fast_ok = BN == 256 && !p.out_fp32 && !p.accumulate && p.remap_in <= 0 && !p.remap_index && p.vec_ok && N % 8 == 0 && p.splits == 1;
   if (fast_ok) {
     const bool bias = p.bias != nullptr, drop = p.drop.thresh16 != 0, res = p.residual != nullptr, auxo = p.aux_out != nullptr;
     if (!a_major && !b_major) {

@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(ROW_WARPS * 32)
 embed_ln_fwd_kernel(const long long* __restrict__ ids, const long long* __restrict__ type_ids, const long long* __restrict__ pos_ids,
                     const float* __restrict__ word, const float* __restrict__ pos, const float* __restrict__ type,
                     const float* __restrict__ gamma, const float* __restrict__ beta, float eps, long long batch, long long T,
-                    long long S_out, bf16* __restrict__ y, DropoutCfg drop) {
+                    long long S_out, bf16* __restrict__ y, DropoutCfg drop, const int32_t* __restrict__ row_dst) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   drop = resolve_dropout(drop);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -262,6 +262,11 @@ embed_ln_fwd_kernel(const long long* __restrict__ ids, const long long* __restri
   const long long rows = batch * T;
   for (long long m = (long long)blockIdx.x * ROW_WARPS + warp; m < rows; m += (long long)gridDim.x * ROW_WARPS) {
     const long long t = m % T, s = m / T;
+    long long orow = s * S_out + t;
+    if (row_dst) {                       // packed rows (vt_pack_plan): where the row lives, or nowhere
+      orow = row_dst[orow];
+      if (orow < 0) continue;
+    }
     const long long id = ids[m], tt = type_ids ? type_ids[m] : 0, p = pos_ids ? pos_ids[m] : t;
     float v[CH][8];
     load_vec_f32(word + id * H, lane, v);
@@ -274,7 +279,7 @@ embed_ln_fwd_kernel(const long long* __restrict__ ids, const long long* __restri
 #pragma unroll
       for (int j = 0; j < 8; ++j) v[c][j] = (v[c][j] - mean) * rstd * g[c][j] + b[c][j];
     apply_dropout_row(drop, m, lane, v);
-    store_row_bf16(y + (s * S_out + t) * H, lane, v);
+    store_row_bf16(y + orow * H, lane, v);
   }
 }
 
@@ -295,7 +300,7 @@ embed_ln_bwd_kernel(const bf16* __restrict__ dy, const long long* __restrict__ i
                     const long long* __restrict__ pos_ids, const float* __restrict__ word, const float* __restrict__ pos,
                     const float* __restrict__ type, const float* __restrict__ gamma, float eps, long long batch, long long T,
                     long long S_out, float* __restrict__ dword, float* __restrict__ dpos, float* __restrict__ dtype,
-                    float* __restrict__ partials, DropoutCfg drop) {
+                    float* __restrict__ partials, DropoutCfg drop, const int32_t* __restrict__ row_dst) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   drop = resolve_dropout(drop);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -311,12 +316,17 @@ embed_ln_bwd_kernel(const bf16* __restrict__ dy, const long long* __restrict__ i
   const long long rows = batch * T;
   for (long long m = (long long)blockIdx.x * ROW_WARPS + warp; m < rows; m += (long long)gridDim.x * ROW_WARPS) {
     const long long t = m % T, s = m / T;
+    long long orow = s * S_out + t;
+    if (row_dst) {                       // a dropped row reached no loss: it has no gradient
+      orow = row_dst[orow];
+      if (orow < 0) continue;
+    }
     const long long id = ids[m], tt = type_ids ? type_ids[m] : 0, p = pos_ids ? pos_ids[m] : t;
     float v[CH][8], d[CH][8];
     load_vec_f32(word + id * H, lane, v);
     add_vec_f32(pos + p * H, lane, v);
     add_vec_f32(type + tt * H, lane, v);
-    load_row_bf16(dy + (s * S_out + t) * H, lane, d);
+    load_row_bf16(dy + orow * H, lane, d);
     apply_dropout_row(drop, m, lane, d);
     float mean, rstd;
     row_stats(v, eps, mean, rstd);
@@ -475,13 +485,23 @@ __global__ void pad_cast_concat_kernel(const TA* __restrict__ a, long long d0, c
 // y[m] = x[remap(m)] * dropout_mask(m)    (768-wide rows; gathers the image rows of dX0 into a compact operand)
 __global__ void __launch_bounds__(ROW_WARPS * 32)
 dropout_rows_kernel(const bf16* __restrict__ x, long long ldx, long long rows, bf16* __restrict__ y, long long ldy, DropoutCfg drop,
-                    long long rin, long long rout, long long roff) {
+                    long long rin, long long rout, long long roff, const int32_t* __restrict__ row_dst) {
   pdl_sync();   // everything below is ordered after the previous kernel on the stream (common.cuh)
   drop = resolve_dropout(drop);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (long long m = (long long)blockIdx.x * ROW_WARPS + warp; m < rows; m += (long long)gridDim.x * ROW_WARPS) {
     float v[CH][8];
-    load_row_bf16(x + remap_row(m, rin, rout, roff) * ldx, lane, v);
+    long long src = remap_row(m, rin, rout, roff);
+    if (row_dst) src = row_dst[src];     // packed rows: the padded position's packed row, or none (the row was dropped: zeros)
+    if (src < 0) {
+#pragma unroll
+      for (int c = 0; c < CH; ++c)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[c][j] = 0.f;
+      store_row_bf16(y + m * ldy, lane, v);
+      continue;
+    }
+    load_row_bf16(x + src * ldx, lane, v);
     apply_dropout_row(drop, m, lane, v);
     store_row_bf16(y + m * ldy, lane, v);
   }
@@ -571,15 +591,55 @@ extern "C" int vt_layernorm_bwd(const void* dy, int64_t lddy, const void* x, int
   return VT_OK;
 }
 
-extern "C" int vt_embed_ln_fwd(const int64_t* ids, const int64_t* type_ids, const int64_t* pos_ids, const float* word,
-                               const float* pos, const float* type, const float* gamma, const float* beta, float eps,
-                               int64_t batch, int64_t T, int64_t out_rows_per_sample, int64_t hidden, void* y, float dropout_p,
-                               uint64_t seed, uint32_t dropout_stream, vt_stream stream) {
+static int embed_fwd_impl(const int64_t* ids, const int64_t* type_ids, const int64_t* pos_ids, const float* word,
+                          const float* pos, const float* type, const float* gamma, const float* beta, float eps,
+                          int64_t batch, int64_t T, int64_t out_rows_per_sample, int64_t hidden, void* y, float dropout_p,
+                          uint64_t seed, uint32_t dropout_stream, const int32_t* row_dst, vt_stream stream) {
   VT_REQUIRE(hidden == H, "vt_embed_ln_fwd: hidden size %lld outside the supported envelope (768)", (long long)hidden);
   VT_REQUIRE(aligned16(word) && aligned16(pos) && aligned16(type) && aligned16(y) && aligned16(gamma) && aligned16(beta), "vt_embed_ln_fwd: 16-byte alignment required");
   if (batch * T == 0) return VT_OK;
   launch_pdl(embed_ln_fwd_kernel, row_grid(batch * T), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const long long*)ids, (const long long*)type_ids, (const long long*)pos_ids, word, pos, type, gamma, beta, eps, batch, T,
-      out_rows_per_sample, (bf16*)y, make_dropout(dropout_p, seed, dropout_stream));
+      out_rows_per_sample, (bf16*)y, make_dropout(dropout_p, seed, dropout_stream), row_dst);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+extern "C" int vt_embed_ln_fwd(const int64_t* ids, const int64_t* type_ids, const int64_t* pos_ids, const float* word,
+                               const float* pos, const float* type, const float* gamma, const float* beta, float eps,
+                               int64_t batch, int64_t T, int64_t out_rows_per_sample, int64_t hidden, void* y, float dropout_p,
+                               uint64_t seed, uint32_t dropout_stream, vt_stream stream) {
+  return embed_fwd_impl(ids, type_ids, pos_ids, word, pos, type, gamma, beta, eps, batch, T, out_rows_per_sample, hidden, y, dropout_p, seed,
+                        dropout_stream, nullptr, stream);
+}
+extern "C" int vt_embed_ln_fwd_packed(const int64_t* ids, const int64_t* type_ids, const int64_t* pos_ids, const float* word,
+                                      const float* pos, const float* type, const float* gamma, const float* beta, float eps,
+                                      int64_t batch, int64_t T, int64_t out_rows_per_sample, int64_t hidden, void* y, float dropout_p,
+                                      uint64_t seed, uint32_t dropout_stream, const int32_t* row_dst, vt_stream stream) {
+  VT_REQUIRE(row_dst, "vt_embed_ln_fwd_packed: row_dst required");
+  return embed_fwd_impl(ids, type_ids, pos_ids, word, pos, type, gamma, beta, eps, batch, T, out_rows_per_sample, hidden, y, dropout_p, seed,
+                        dropout_stream, row_dst, stream);
+}
+
+static int embed_bwd_impl(const void* dy, const int64_t* ids, const int64_t* type_ids, const int64_t* pos_ids, const float* word,
+                          const float* pos, const float* type, const float* gamma, float eps, int64_t batch, int64_t T,
+                          int64_t out_rows_per_sample, int64_t hidden, int64_t type_vocab, float* dword, float* dpos,
+                          float* dtype, float* dgamma, float* dbeta, float* partials, float dropout_p, uint64_t seed,
+                          uint32_t dropout_stream, const int32_t* row_dst, vt_stream stream) {
+  VT_REQUIRE(hidden == H, "vt_embed_ln_bwd: hidden size %lld outside the supported envelope (768)", (long long)hidden);
+  VT_REQUIRE(aligned16(dy) && aligned16(dword) && aligned16(dpos) && aligned16(dtype) && aligned16(partials), "vt_embed_ln_bwd: 16-byte alignment required");
+  if (batch * T == 0) return VT_OK;
+  const int grid = row_grid(batch * T);
+  cudaStream_t st = (cudaStream_t)stream;
+  launch_pdl(embed_ln_bwd_kernel, grid, ROW_WARPS * 32, 0, st, (const bf16*)dy, (const long long*)ids, (const long long*)type_ids,
+                                                       (const long long*)pos_ids, word, pos, type, gamma, eps, batch, T,
+                                                       out_rows_per_sample, dword, dpos, dtype, partials,
+                                                       make_dropout(dropout_p, seed, dropout_stream), row_dst);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  ReduceOuts outs = {{dgamma, dbeta, dtype, type_vocab > 1 ? dtype + H : nullptr}};
+  const int splits = grid > 64 ? (grid + 63) / 64 < 16 ? (grid + 63) / 64 : 16 : 1;
+  launch_pdl(reduce_partials_multi_kernel, dim3(H / 32, splits, 4), dim3(32, 8), 0, st, partials, grid, 4, outs);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
@@ -590,23 +650,17 @@ extern "C" int vt_embed_ln_bwd(const void* dy, const int64_t* ids, const int64_t
                                int64_t out_rows_per_sample, int64_t hidden, int64_t type_vocab, float* dword, float* dpos,
                                float* dtype, float* dgamma, float* dbeta, float* partials, float dropout_p, uint64_t seed,
                                uint32_t dropout_stream, vt_stream stream) {
-  VT_REQUIRE(hidden == H, "vt_embed_ln_bwd: hidden size %lld outside the supported envelope (768)", (long long)hidden);
-  VT_REQUIRE(aligned16(dy) && aligned16(dword) && aligned16(dpos) && aligned16(dtype) && aligned16(partials), "vt_embed_ln_bwd: 16-byte alignment required");
-  if (batch * T == 0) return VT_OK;
-  const int grid = row_grid(batch * T);
-  cudaStream_t st = (cudaStream_t)stream;
-  launch_pdl(embed_ln_bwd_kernel, grid, ROW_WARPS * 32, 0, st, (const bf16*)dy, (const long long*)ids, (const long long*)type_ids,
-                                                       (const long long*)pos_ids, word, pos, type, gamma, eps, batch, T,
-                                                       out_rows_per_sample, dword, dpos, dtype, partials,
-                                                       make_dropout(dropout_p, seed, dropout_stream));
-  count_launch(1);
-  VT_CHECK_LAUNCH();
-  ReduceOuts outs = {{dgamma, dbeta, dtype, type_vocab > 1 ? dtype + H : nullptr}};
-  const int splits = grid > 64 ? (grid + 63) / 64 < 16 ? (grid + 63) / 64 : 16 : 1;
-  launch_pdl(reduce_partials_multi_kernel, dim3(H / 32, splits, 4), dim3(32, 8), 0, st, partials, grid, 4, outs);
-  count_launch(1);
-  VT_CHECK_LAUNCH();
-  return VT_OK;
+  return embed_bwd_impl(dy, ids, type_ids, pos_ids, word, pos, type, gamma, eps, batch, T, out_rows_per_sample, hidden, type_vocab, dword, dpos, dtype,
+                        dgamma, dbeta, partials, dropout_p, seed, dropout_stream, nullptr, stream);
+}
+extern "C" int vt_embed_ln_bwd_packed(const void* dy, const int64_t* ids, const int64_t* type_ids, const int64_t* pos_ids, const float* word,
+                                      const float* pos, const float* type, const float* gamma, float eps, int64_t batch, int64_t T,
+                                      int64_t out_rows_per_sample, int64_t hidden, int64_t type_vocab, float* dword, float* dpos,
+                                      float* dtype, float* dgamma, float* dbeta, float* partials, float dropout_p, uint64_t seed,
+                                      uint32_t dropout_stream, const int32_t* row_dst, vt_stream stream) {
+  VT_REQUIRE(row_dst, "vt_embed_ln_bwd_packed: row_dst required");
+  return embed_bwd_impl(dy, ids, type_ids, pos_ids, word, pos, type, gamma, eps, batch, T, out_rows_per_sample, hidden, type_vocab, dword, dpos, dtype,
+                        dgamma, dbeta, partials, dropout_p, seed, dropout_stream, row_dst, stream);
 }
 
 extern "C" int64_t vt_colsum_partials_rows(int64_t rows) {
@@ -664,15 +718,26 @@ extern "C" int vt_pad_cast_concat(const float* a, int64_t d0, const float* b, in
   return vt_pad_cast_concat_mixed(a, 0, d0, b, 0, d1, rows, out, ldo, stream);
 }
 
-extern "C" int vt_dropout_rows(const void* x, int64_t ldx, int64_t rows, int64_t hidden, void* y, int64_t ldy, float dropout_p,
-                               uint64_t seed, uint32_t dropout_stream, int64_t remap_rows_in, int64_t remap_rows_out,
-                               int64_t remap_row_off, vt_stream stream) {
+static int dropout_rows_impl(const void* x, int64_t ldx, int64_t rows, int64_t hidden, void* y, int64_t ldy, float dropout_p,
+                             uint64_t seed, uint32_t dropout_stream, int64_t remap_rows_in, int64_t remap_rows_out,
+                             int64_t remap_row_off, const int32_t* row_dst, vt_stream stream) {
   VT_REQUIRE(hidden == H && ldx % 8 == 0 && ldy % 8 == 0 && aligned16(x) && aligned16(y), "vt_dropout_rows: bad arguments");
   if (rows == 0) return VT_OK;
-  launch_pdl(dropout_rows_kernel, row_grid(rows), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const bf16*)x, ldx, rows, (bf16*)y, ldy, make_dropout(dropout_p, seed, dropout_stream), remap_rows_in, remap_rows_out, remap_row_off);
+  launch_pdl(dropout_rows_kernel, row_grid(rows), ROW_WARPS * 32, 0, (cudaStream_t)stream, (const bf16*)x, ldx, rows, (bf16*)y, ldy, make_dropout(dropout_p, seed, dropout_stream), remap_rows_in, remap_rows_out, remap_row_off, row_dst);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
+}
+extern "C" int vt_dropout_rows(const void* x, int64_t ldx, int64_t rows, int64_t hidden, void* y, int64_t ldy, float dropout_p,
+                               uint64_t seed, uint32_t dropout_stream, int64_t remap_rows_in, int64_t remap_rows_out,
+                               int64_t remap_row_off, vt_stream stream) {
+  return dropout_rows_impl(x, ldx, rows, hidden, y, ldy, dropout_p, seed, dropout_stream, remap_rows_in, remap_rows_out, remap_row_off, nullptr, stream);
+}
+extern "C" int vt_dropout_rows_packed(const void* x, int64_t ldx, int64_t rows, int64_t hidden, void* y, int64_t ldy, float dropout_p,
+                                      uint64_t seed, uint32_t dropout_stream, int64_t remap_rows_in, int64_t remap_rows_out,
+                                      int64_t remap_row_off, const int32_t* row_dst, vt_stream stream) {
+  VT_REQUIRE(row_dst, "vt_dropout_rows_packed: row_dst required");
+  return dropout_rows_impl(x, ldx, rows, hidden, y, ldy, dropout_p, seed, dropout_stream, remap_rows_in, remap_rows_out, remap_row_off, row_dst, stream);
 }
 
 extern "C" int vt_gather_rows(const void* src, int64_t lds, const int64_t* idx, int64_t n, int64_t hidden, void* dst, int64_t ldd,

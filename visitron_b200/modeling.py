@@ -17,6 +17,7 @@ fallback: without the library or off a B200 every forward raises.
 """
 from __future__ import annotations
 
+import contextlib
 import logging
 from typing import List, Optional
 
@@ -202,13 +203,15 @@ class BertPreTrainedModel(PreTrainedModel):
 # ------------------------------------------------------------------------------------------------
 class _Step:
     __slots__ = ("B", "T", "R", "S", "M", "seed", "p_hidden", "p_attn", "ids", "tt", "pos", "bias", "key_tiles", "has_img",
-                 "img_cat", "img_pre", "layers", "seq", "pooled", "began", "model", "need_grad", "hidden")
+                 "img_cat", "img_pre", "layers", "seq", "pooled", "began", "model", "need_grad", "hidden", "plan", "rows", "cls_in")
 
     def __init__(self):
         self.layers = []
         self.img_cat = self.img_pre = None
         self.began = False
         self.hidden = None
+        self.plan = None        # ops.PackPlan: the step runs on packed rows (padding-free); None = the dense [B, S] layout
+        self.cls_in = None
 
 
 # Set by visitron_b200.graph while a step is being captured: the dropout seed then lives in device memory (ops.set_seed_source)
@@ -338,8 +341,12 @@ class BertImgModelwithLocationEmbeds(BertPreTrainedModel):
         return (sequence_output, pooled)
 
     def _vt_forward(self, input_ids, token_type_ids=None, attention_mask=None, position_ids=None, head_mask=None,
-                    img_feats=None, img_location_embeddings=None, encoder_history_states=None):
-        """Returns (sequence_output as bf16 [B*S, 768], pooled_output fp32 [B, 768], step state)."""
+                    img_feats=None, img_location_embeddings=None, encoder_history_states=None, pack_labels=None):
+        """Returns (sequence_output as bf16 [rows, 768], pooled_output fp32 [B, 768], step state).
+
+        pack_labels = (labels, token_labels) flat int64 [B*S] asks for PADDING-FREE execution: the rows that are masked as keys and
+        carry no label are dropped on the device (ops.pack_plan) and the encoder runs on the packed rows; step.plan then maps between
+        the layouts and sequence_output is in packed order (only PreTrainOscar, whose heads read labelled rows, asks for it)."""
         cfg = self.config
         if head_mask is not None:
             raise NotImplementedError("head_mask is not supported by the fused attention kernel (no reference caller passes it)")
@@ -379,7 +386,13 @@ class BertImgModelwithLocationEmbeds(BertPreTrainedModel):
         if tuple(attention_mask.shape) != (B, step.S):
             raise ValueError("attention_mask must be [batch, text_len + regions] = %s, got %s" % ((B, step.S), tuple(attention_mask.shape)))
         step.bias = ops.mask_bias(attention_mask)
-        step.key_tiles = ops.attention_key_tiles(step.bias)   # once per step: the same padding for all layers, forward and backward
+        step.rows = step.M
+        if pack_labels is not None and not self.use_img_layernorm and not getattr(cfg, "output_hidden_states", False):
+            step.plan = ops.pack_plan(step.bias, pack_labels[0], pack_labels[1], B, step.S)
+            step.rows = step.plan.cap
+            step.key_tiles = step.plan.key_tiles
+        else:
+            step.key_tiles = ops.attention_key_tiles(step.bias)   # once per step: the same padding for all layers, forward and backward
         if step.has_img:
             if img_location_embeddings is None:
                 raise ValueError("img_location_embeddings is required with img_feats (vs/encoder.py:277-279)")
@@ -422,11 +435,15 @@ def _encoder_forward(step: _Step, st: FlatStore, img_feats, img_loc):
     nh = cfg.num_attention_heads
     I = cfg.intermediate_size
     save = step.need_grad
-    x = torch.empty((M, H), dtype=BF16, device=dev)
+    plan = step.plan
+    rows = step.rows                  # rows of every activation buffer: B*S, or the packed layout's capacity
+    row_dst = None if plan is None else plan.row_dst
+    # packed rows: the rows between the last sample's end and the row limit must be finite zeros (they ride along in every GEMM)
+    x = torch.empty((rows, H), dtype=BF16, device=dev) if plan is None else torch.zeros((rows, H), dtype=BF16, device=dev)
     ops.embed_ln_fwd(step.ids, step.tt, step.pos, st.w("embeddings.word_embeddings.weight"),
                      st.w("embeddings.position_embeddings.weight"), st.w("embeddings.token_type_embeddings.weight"),
                      st.w("embeddings.LayerNorm.weight"), st.w("embeddings.LayerNorm.bias"), eps, x, S,
-                     step.p_hidden, step.seed, STREAM_EMB)
+                     step.p_hidden, step.seed, STREAM_EMB, row_dst=row_dst)
     if step.has_img:
         wimg, bimg, kp = model._img_operands(st)
         cat = torch.empty((B * R, kp), dtype=BF16, device=dev)
@@ -438,14 +455,39 @@ def _encoder_forward(step: _Step, st: FlatStore, img_feats, img_loc):
             step.img_pre = pre if save else None
         else:
             lib.gemm(cat, wimg, bias=bimg, out=x, dropout_p=step.p_hidden, seed=step.seed, dropout_stream=STREAM_IMG,
-                     remap=(R, S, T))
+                     remap=(R, S, T), remap_index=row_dst)
         step.img_cat = cat if save else None
+    limit = ops.row_limit(plan.counts, 0) if plan is not None else contextlib.nullcontext()
+    with limit:
+        x = _encoder_layers_forward(step, st, x, save)
+    if step.hidden is not None:
+        step.hidden.append(x)
+    if plan is None:
+        cls_in = x[::S]
+    else:
+        cls_in = ops.gather_rows(x, plan.cls_rows)       # every sample's first row ([CLS]) in the packed layout
+        step.cls_in = cls_in if save else None
+    pooled = lib.gemm(cls_in, st.wb("pooler.dense.weight"), bias=st.w("pooler.dense.bias"), act=ACT_TANH, out_dtype=F32)
+    # detached ALIASES: autograd attaches this node to the returned tensor objects themselves, and node -> ctx.step -> step.seq
+    # -> grad_fn -> node would be a reference cycle that keeps every finished iteration's graph (and its AccumulateGrad nodes)
+    # alive until the cyclic collector runs
+    step.seq, step.pooled = x.detach(), pooled.detach()
+    return x, pooled
+
+
+def _encoder_layers_forward(step: _Step, st: FlatStore, x, save):
+    """The 12 layers (oscar/modeling_bert.py:145-155); under a row limit when the step runs on packed rows."""
+    cfg = step.model.config
+    B, S, nh, I = step.B, step.S, cfg.num_attention_heads, cfg.intermediate_size
+    M = step.rows
+    dev = x.device
+    eps = float(cfg.layer_norm_eps)
     for l in range(cfg.num_hidden_layers):
         p = "encoder.layer.%d." % l
         if step.hidden is not None:
             step.hidden.append(x)
         qkv = lib.gemm(x, st.wb(p + "attention.self.query.weight", 3 * H, H), bias=st.wspan(p + "attention.self.query.bias", 3 * H))
-        ctx, lse = ops.attention_fwd(qkv, step.bias, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles)
+        ctx, lse = ops.attention_fwd(qkv, step.bias, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles, plan=step.plan)
         x1 = lib.gemm(ctx, st.wb(p + "attention.output.dense.weight"), bias=st.w(p + "attention.output.dense.bias"),
                       dropout_p=step.p_hidden, seed=step.seed, dropout_stream=4 * l + 1, residual=x)
         y1 = ops.layernorm_fwd(x1, st.w(p + "attention.output.LayerNorm.weight"), st.w(p + "attention.output.LayerNorm.bias"), eps)
@@ -460,14 +502,7 @@ def _encoder_forward(step: _Step, st: FlatStore, img_feats, img_loc):
         if save:
             step.layers.append((x, qkv, ctx, lse, x1, y1, pre, z, x2))
         x = y2
-    if step.hidden is not None:
-        step.hidden.append(x)
-    pooled = lib.gemm(x[::S], st.wb("pooler.dense.weight"), bias=st.w("pooler.dense.bias"), act=ACT_TANH, out_dtype=F32)
-    # detached ALIASES: autograd attaches this node to the returned tensor objects themselves, and node -> ctx.step -> step.seq
-    # -> grad_fn -> node would be a reference cycle that keeps every finished iteration's graph (and its AccumulateGrad nodes)
-    # alive until the cyclic collector runs
-    step.seq, step.pooled = x.detach(), pooled.detach()
-    return x, pooled
+    return x
 
 
 def _begin_backward(step: _Step, stores: List[FlatStore]):
@@ -486,14 +521,54 @@ def _encoder_backward(step: _Step, st: FlatStore, d, dpooled):
     eps = float(cfg.layer_norm_eps)
     nh = cfg.num_attention_heads
     red = model._vt_reducer
+    plan = step.plan
+    row_dst = None if plan is None else plan.row_dst
     if d is None:
-        d = torch.zeros((M, H), dtype=BF16, device=step.ids.device)
+        d = torch.zeros((step.rows, H), dtype=BF16, device=step.ids.device)
     x_last = step.seq
     if dpooled is not None:
         dp = ops.tanh_bwd(dpooled.contiguous(), step.pooled)
-        lib.gemm(dp, x_last[::S], a_major=1, b_major=1, out=st.g("pooler.dense.weight"), accumulate=True)
+        cls_in = x_last[::S] if plan is None else step.cls_in
+        lib.gemm(dp, cls_in, a_major=1, b_major=1, out=st.g("pooler.dense.weight"), accumulate=True)
         ops.colsum(dp, st.g("pooler.dense.bias"))
-        lib.gemm(dp, st.wb("pooler.dense.weight"), b_major=1, out=d, residual=d, remap=(1, S, 0))
+        lib.gemm(dp, st.wb("pooler.dense.weight"), b_major=1, out=d, residual=d, remap=(1, S, 0), remap_index=row_dst)
+    limit = ops.row_limit(plan.counts, 0) if plan is not None else contextlib.nullcontext()
+    with limit:
+        d = _encoder_layers_backward(step, st, d)
+    if step.has_img:
+        cat = step.img_cat
+        if model.use_img_layernorm:
+            dimg, _ = ops.layernorm_bwd(d, step.img_pre, st.w("LayerNorm.weight"), float(cfg.img_layer_norm_eps),
+                                        st.g("LayerNorm.weight"), st.g("LayerNorm.bias"), st.g("img_embedding.bias"),
+                                        in_dropout_p=step.p_hidden, in_stream=STREAM_IMG, seed=step.seed, remap=(R, S, T))
+            st.g("location_embeds.bias").copy_(st.g("img_embedding.bias"))
+        else:
+            dimg = torch.empty((B * R, H), dtype=BF16, device=d.device)
+            ops.dropout_rows(d, B * R, dimg, step.p_hidden, step.seed, STREAM_IMG, remap=(R, S, T), row_dst=row_dst)
+            ops.colsum(dimg, st.g("img_embedding.bias"))
+            ops.colsum(dimg, st.g("location_embeds.bias"))
+        D = model.img_dim
+        lib.gemm(dimg, cat[:, LOC_DIM: LOC_DIM + D], a_major=1, b_major=1, out=st.g("img_embedding.weight"), accumulate=True)
+        lib.gemm(dimg, cat[:, :LOC_DIM], a_major=1, b_major=1, out=st.g("location_embeds.weight"), accumulate=True)
+    ops.embed_ln_bwd(d, step.ids, step.tt, step.pos, st.w("embeddings.word_embeddings.weight"),
+                     st.w("embeddings.position_embeddings.weight"), st.w("embeddings.token_type_embeddings.weight"),
+                     st.w("embeddings.LayerNorm.weight"), eps, S, st.g("embeddings.word_embeddings.weight"),
+                     st.g("embeddings.position_embeddings.weight"), st.g("embeddings.token_type_embeddings.weight"),
+                     st.g("embeddings.LayerNorm.weight"), st.g("embeddings.LayerNorm.bias"), step.p_hidden, step.seed, STREAM_EMB,
+                     row_dst=row_dst)
+    if red is not None:
+        red.reduce(st.grad_bucket(0), tail=True)  # embeddings (+ the tied MLM decoder's contribution) and the image projection
+        red.finish()
+
+
+def _encoder_layers_backward(step: _Step, st: FlatStore, d):
+    """Backward of the 12 layers; under a row limit when the step runs on packed rows."""
+    model = step.model
+    cfg = model.config
+    B, S = step.B, step.S
+    eps = float(cfg.layer_norm_eps)
+    nh = cfg.num_attention_heads
+    red = model._vt_reducer
     for l in reversed(range(cfg.num_hidden_layers)):
         p = "encoder.layer.%d." % l
         x_in, qkv, ctx, lse, x1, y1, pre, z, x2 = step.layers[l]
@@ -515,36 +590,14 @@ def _encoder_backward(step: _Step, st: FlatStore, d, dpooled):
                                       st.g(p + "attention.output.dense.bias"), out_dropout_p=ph, out_stream=4 * l + 1, seed=step.seed)
         lib.gemm(dx1d, ctx, a_major=1, b_major=1, out=st.g(p + "attention.output.dense.weight"), accumulate=True)
         dctx = lib.gemm(dx1d, st.wb(p + "attention.output.dense.weight"), b_major=1)
-        dqkv = ops.attention_bwd(qkv, step.bias, ctx, dctx, lse, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles)
+        dqkv = ops.attention_bwd(qkv, step.bias, ctx, dctx, lse, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles, plan=step.plan)
         ops.colsum(dqkv, st.g(p + "attention.self.query.bias", 3 * H))
         lib.gemm(dqkv, x_in, a_major=1, b_major=1, out=st.g(p + "attention.self.query.weight", 3 * H, H), accumulate=True)
         d = lib.gemm(dqkv, st.wb(p + "attention.self.query.weight", 3 * H, H), b_major=1, residual=dx1)
         del dqkv, dctx, dx1, dx1d, dy1, qkv, ctx, x1, y1, x_in
         if red is not None:  # this layer's slice (the last layer's also holds the pooler) is complete: exchange it now
             red.reduce(st.grad_bucket(st.bucket_of(p + "attention.self.query.weight")))
-    if step.has_img:
-        cat = step.img_cat
-        if model.use_img_layernorm:
-            dimg, _ = ops.layernorm_bwd(d, step.img_pre, st.w("LayerNorm.weight"), float(cfg.img_layer_norm_eps),
-                                        st.g("LayerNorm.weight"), st.g("LayerNorm.bias"), st.g("img_embedding.bias"),
-                                        in_dropout_p=step.p_hidden, in_stream=STREAM_IMG, seed=step.seed, remap=(R, S, T))
-            st.g("location_embeds.bias").copy_(st.g("img_embedding.bias"))
-        else:
-            dimg = torch.empty((B * R, H), dtype=BF16, device=d.device)
-            ops.dropout_rows(d, B * R, dimg, step.p_hidden, step.seed, STREAM_IMG, remap=(R, S, T))
-            ops.colsum(dimg, st.g("img_embedding.bias"))
-            ops.colsum(dimg, st.g("location_embeds.bias"))
-        D = model.img_dim
-        lib.gemm(dimg, cat[:, LOC_DIM: LOC_DIM + D], a_major=1, b_major=1, out=st.g("img_embedding.weight"), accumulate=True)
-        lib.gemm(dimg, cat[:, :LOC_DIM], a_major=1, b_major=1, out=st.g("location_embeds.weight"), accumulate=True)
-    ops.embed_ln_bwd(d, step.ids, step.tt, step.pos, st.w("embeddings.word_embeddings.weight"),
-                     st.w("embeddings.position_embeddings.weight"), st.w("embeddings.token_type_embeddings.weight"),
-                     st.w("embeddings.LayerNorm.weight"), eps, S, st.g("embeddings.word_embeddings.weight"),
-                     st.g("embeddings.position_embeddings.weight"), st.g("embeddings.token_type_embeddings.weight"),
-                     st.g("embeddings.LayerNorm.weight"), st.g("embeddings.LayerNorm.bias"), step.p_hidden, step.seed, STREAM_EMB)
-    if red is not None:
-        red.reduce(st.grad_bucket(0), tail=True)  # embeddings (+ the tied MLM decoder's contribution) and the image projection
-        red.finish()
+    return d
 
 
 class _EncoderFn(torch.autograd.Function):
@@ -602,6 +655,7 @@ class PreTrainOscar(BertPreTrainedModel):
         self._vt_store_key = None
         self._vt_reducer = None
         self._vt_aux_raw = None
+        self.vt_packed = True      # run the step on the rows that exist (visitron_b200/csrc/pack.cu); False: the dense [B, S] layout
 
     def tie_weights(self):
         self._tie_or_clone_weights(self.mlmhead.predictions.decoder, self.bert.embeddings.word_embeddings)
@@ -651,10 +705,14 @@ class PreTrainOscar(BertPreTrainedModel):
             raise ValueError("mlmhead.predictions.bias has %d entries for a decoder of %d rows" % (self.mlmhead.predictions.bias.numel(), V))
         lab = labels.reshape(-1).contiguous().long()
         tok = token_labels.reshape(-1).contiguous().long()
-        seq, pooled, step = self.bert._vt_forward(input_ids, token_type_ids, attention_mask, position_ids, head_mask,
-                                                  img_feats, img_location_embeddings)
-        if lab.numel() != step.M or tok.numel() != step.M:
+        S_all = input_ids.size(1) + (img_feats.size(1) if img_feats is not None else 0)
+        if lab.numel() != input_ids.size(0) * S_all or tok.numel() != lab.numel():
             raise ValueError("labels / token_labels must be [batch, text_len + regions]")
+        # padding-free execution (self.vt_packed, default on): the rows that are masked out and unlabelled are dropped on the device
+        seq, pooled, step = self.bert._vt_forward(input_ids, token_type_ids, attention_mask, position_ids, head_mask,
+                                                  img_feats, img_location_embeddings, pack_labels=(lab, tok) if self.vt_packed else None)
+        if step.plan is not None:
+            lab, tok = step.plan.labels_a, step.plan.labels_b      # the labels in packed row order (-1 on the layout's padding rows)
         hs = self._store()
         hs.refresh_bf16()
         na = None if next_action is None else next_action.contiguous().long()
@@ -669,6 +727,8 @@ class PreTrainOscar(BertPreTrainedModel):
         raw = self._vt_aux_raw
         c = raw["counts"].cpu()
         n, nt = int(c[1]), int(c[5])
+        if raw.get("row_src") is not None:      # packed rows: report the labelled rows in the caller's [B, S] numbering
+            raw = dict(raw, idx_mlm=raw["row_src"][raw["idx_mlm"][:n]].long(), idx_tok=raw["row_src"][raw["idx_tok"][:nt]].long())
         return dict(predicted_words=raw["predicted_words"][:n], predicted_tokens=raw["predicted_tokens"][:nt],
                     predicted_action=raw["predicted_action"], action_scores=raw["action_scores"],
                     mlm_logits=raw["mlm_logits"][:n], token_logits=raw["token_logits"][:nt],
@@ -689,7 +749,7 @@ class _HeadsFn(torch.autograd.Function):
         eps = float(cfg.layer_norm_eps)
         Dc = cfg.detector_classes
         dev = seq.device
-        cap = ops.roundup(step.M, 128)
+        cap = ops.roundup(lab.numel(), 128)
         idx_mlm, lab_mlm, idx_tok, lab_tok, counts = ops.compact_labels(lab, V, tok, Dc, cap)
         tied = "mlmhead.predictions.decoder.weight" not in hs.offset
         E = bs.wb("embeddings.word_embeddings.weight") if tied else hs.wb("mlmhead.predictions.decoder.weight")
@@ -724,7 +784,8 @@ class _HeadsFn(torch.autograd.Function):
         ctx.saved = (hm, pre_t, a, tl, logits, mlm_stats, ht, tlogits, tok_stats, scores, out8.detach(), pooled) if save else None
         ctx.shapes = (cap, ldv, ldt)
         model._vt_aux_raw = dict(predicted_words=mlm_arg, predicted_tokens=tok_arg, predicted_action=act_arg, action_scores=scores,
-                                 mlm_logits=logits[:, :V], token_logits=tlogits[:, :Dc], counts=counts, idx_mlm=idx_mlm, idx_tok=idx_tok)
+                                 mlm_logits=logits[:, :V], token_logits=tlogits[:, :Dc], counts=counts, idx_mlm=idx_mlm, idx_tok=idx_tok,
+                                 row_src=None if step.plan is None else step.plan.row_src)
         return out8
 
     @staticmethod
@@ -745,7 +806,7 @@ class _HeadsFn(torch.autograd.Function):
         g_mlm = (g8[0:1] + g8[1:2]).contiguous()
         g_next = (g8[0:1] + g8[2:3]).contiguous()
         g_tok = (g8[0:1] + g8[3:4]).contiguous()
-        dseq = torch.zeros((step.M, H), dtype=BF16, device=hm.device)
+        dseq = torch.zeros((step.rows, H), dtype=BF16, device=hm.device)
         E = bs.wb("embeddings.word_embeddings.weight") if tied else hs.wb("mlmhead.predictions.decoder.weight")
         dE = bs.g("embeddings.word_embeddings.weight") if tied else hs.g("mlmhead.predictions.decoder.weight")
         with ops.row_limit(counts, 0):

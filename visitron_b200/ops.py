@@ -53,22 +53,31 @@ def layernorm_bwd(dy, x, gamma, eps, dgamma, dbeta, dbias=None, want_dx=True, ou
     return dx, (dxd if dxd is not None else dx)
 
 
-def embed_ln_fwd(ids, type_ids, pos_ids, word, pos, typ, gamma, beta, eps, out, rows_per_sample, dropout_p=0.0, seed=0, stream_id=0):
+def embed_ln_fwd(ids, type_ids, pos_ids, word, pos, typ, gamma, beta, eps, out, rows_per_sample, dropout_p=0.0, seed=0, stream_id=0, row_dst=None):
     L = init()
     b, T = ids.shape
-    check(L.vt_embed_ln_fwd(ptr(ids), ptr(type_ids), ptr(pos_ids), ptr(word), ptr(pos), ptr(typ), ptr(gamma), ptr(beta), eps,
-                            b, T, rows_per_sample, word.size(1), ptr(out), dropout_p, seed, stream_id, stream_ptr()), "vt_embed_ln_fwd")
+    if row_dst is None:
+        check(L.vt_embed_ln_fwd(ptr(ids), ptr(type_ids), ptr(pos_ids), ptr(word), ptr(pos), ptr(typ), ptr(gamma), ptr(beta), eps,
+                                b, T, rows_per_sample, word.size(1), ptr(out), dropout_p, seed, stream_id, stream_ptr()), "vt_embed_ln_fwd")
+    else:
+        check(L.vt_embed_ln_fwd_packed(ptr(ids), ptr(type_ids), ptr(pos_ids), ptr(word), ptr(pos), ptr(typ), ptr(gamma), ptr(beta), eps,
+                                       b, T, rows_per_sample, word.size(1), ptr(out), dropout_p, seed, stream_id, ptr(row_dst), stream_ptr()),
+              "vt_embed_ln_fwd_packed")
     return out
 
 
 def embed_ln_bwd(dy, ids, type_ids, pos_ids, word, pos, typ, gamma, eps, rows_per_sample, dword, dpos, dtype, dgamma, dbeta,
-                 dropout_p=0.0, seed=0, stream_id=0):
+                 dropout_p=0.0, seed=0, stream_id=0, row_dst=None):
     L = init()
     b, T = ids.shape
     parts = _ws(dy.device, int(L.vt_row_partials_rows(b * T)) * 4 * H)
-    check(L.vt_embed_ln_bwd(ptr(dy), ptr(ids), ptr(type_ids), ptr(pos_ids), ptr(word), ptr(pos), ptr(typ), ptr(gamma), eps, b, T,
-                            rows_per_sample, word.size(1), typ.size(0), ptr(dword), ptr(dpos), ptr(dtype), ptr(dgamma), ptr(dbeta),
-                            ptr(parts), dropout_p, seed, stream_id, stream_ptr()), "vt_embed_ln_bwd")
+    args = (ptr(dy), ptr(ids), ptr(type_ids), ptr(pos_ids), ptr(word), ptr(pos), ptr(typ), ptr(gamma), eps, b, T,
+            rows_per_sample, word.size(1), typ.size(0), ptr(dword), ptr(dpos), ptr(dtype), ptr(dgamma), ptr(dbeta),
+            ptr(parts), dropout_p, seed, stream_id)
+    if row_dst is None:
+        check(L.vt_embed_ln_bwd(*args, stream_ptr()), "vt_embed_ln_bwd")
+    else:
+        check(L.vt_embed_ln_bwd_packed(*args, ptr(row_dst), stream_ptr()), "vt_embed_ln_bwd_packed")
 
 
 def colsum(x, out, ncols=None, accumulate=True):
@@ -100,10 +109,14 @@ def pad_cast_concat(a, b, out):
     return out
 
 
-def dropout_rows(x, rows, out, dropout_p, seed, stream_id, remap=(0, 0, 0)):
+def dropout_rows(x, rows, out, dropout_p, seed, stream_id, remap=(0, 0, 0), row_dst=None):
     L = init()
-    check(L.vt_dropout_rows(ptr(x), x.stride(0), rows, H, ptr(out), out.stride(0), dropout_p, seed, stream_id, *remap, stream_ptr()),
-          "vt_dropout_rows")
+    if row_dst is None:
+        check(L.vt_dropout_rows(ptr(x), x.stride(0), rows, H, ptr(out), out.stride(0), dropout_p, seed, stream_id, *remap, stream_ptr()),
+              "vt_dropout_rows")
+    else:
+        check(L.vt_dropout_rows_packed(ptr(x), x.stride(0), rows, H, ptr(out), out.stride(0), dropout_p, seed, stream_id, *remap, ptr(row_dst),
+                                       stream_ptr()), "vt_dropout_rows_packed")
     return out
 
 
@@ -142,23 +155,75 @@ def attention_key_tiles(bias: torch.Tensor) -> Optional[torch.Tensor]:
     return plan
 
 
-def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None, key_tiles=None):
+class PackPlan:
+    """Device-resident description of the packed row layout of one step (vt_pack_plan): no host sync, fixed shapes."""
+    __slots__ = ("B", "S", "cap", "row_src", "row_dst", "row_b", "start", "counts", "bias", "labels_a", "labels_b", "cls_rows", "key_tiles")
+
+
+def pack_plan(bias, labels_a, labels_b, B, S) -> PackPlan:
+    """Which rows of the padded [B, S] layout exist (mask != 0, labelled, or position 0) and where they live in the packed layout."""
     L = init()
+    dev = bias.device
+    pl = PackPlan()
+    pl.B, pl.S = B, S
+    pl.cap = cap = roundup(B * S, 128) + 128
+    i32 = torch.empty(2 * cap + B * S + (B + 1) + 4, device=dev, dtype=torch.int32)
+    pl.row_src, pl.row_b = i32[:cap], i32[cap:2 * cap]
+    pl.row_dst = i32[2 * cap: 2 * cap + B * S]
+    pl.start = i32[2 * cap + B * S: 2 * cap + B * S + B + 1]
+    pl.counts = torch.empty(8, device=dev, dtype=torch.int32)[:4]       # own 16-byte aligned allocation: it is a row-limit block
+    pl.bias = torch.empty(cap, device=dev, dtype=F32)
+    i64 = torch.empty(2 * cap + B, device=dev, dtype=torch.int64)
+    pl.labels_a = i64[:cap] if labels_a is not None else None
+    pl.labels_b = i64[cap:2 * cap] if labels_b is not None else None
+    pl.cls_rows = i64[2 * cap:]
+    check(L.vt_pack_plan(ptr(bias), ptr(labels_a), ptr(labels_b), B, S, cap, ptr(pl.row_src), ptr(pl.row_dst), ptr(pl.row_b), ptr(pl.start),
+                         ptr(pl.counts), ptr(pl.bias), ptr(pl.labels_a), ptr(pl.labels_b), ptr(pl.cls_rows), stream_ptr()), "vt_pack_plan")
+    pl.key_tiles = None
+    if S <= 2048:
+        pl.key_tiles = torch.empty(B, device=dev, dtype=torch.int32)
+        check(L.vt_attention_key_tiles_packed(ptr(pl.bias), ptr(pl.start), B, S, ptr(pl.key_tiles), stream_ptr()), "vt_attention_key_tiles_packed")
+    return pl
+
+
+def zero_pad_rows(buf, counts):
+    """rows [counts[1], counts[0]) of a 2-D row-major buffer := 0 (the packed layout's padding rows)."""
+    check(init().vt_zero_pad_rows(ptr(buf), buf.stride(0) * buf.element_size(), buf.size(1) * buf.element_size(), ptr(counts), stream_ptr()),
+          "vt_zero_pad_rows")
+    return buf
+
+
+def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None, key_tiles=None, plan: Optional[PackPlan] = None):
+    L = init()
+    rows = B * S if plan is None else plan.cap
     if ctx is None:
-        ctx = torch.empty((B * S, heads * 64), device=qkv.device, dtype=BF16)
+        ctx = torch.empty((rows, heads * 64), device=qkv.device, dtype=BF16)
     lse = torch.empty((B, heads, S, 2), device=qkv.device, dtype=F32)
-    check(L.vt_attention_fwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(key_tiles), B, S, heads, 64, ptr(ctx), ptr(lse), dropout_p, seed, stream_id,
-                             stream_ptr()), "vt_attention_fwd")
+    if plan is None:
+        check(L.vt_attention_fwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(key_tiles), B, S, heads, 64, ptr(ctx), ptr(lse), dropout_p, seed, stream_id,
+                                 stream_ptr()), "vt_attention_fwd")
+    else:
+        check(L.vt_attention_fwd_packed(ptr(qkv), qkv.stride(0), ptr(plan.bias), ptr(plan.key_tiles), ptr(plan.start), plan.cap, B, S, heads, 64,
+                                        ptr(ctx), ptr(lse), dropout_p, seed, stream_id, stream_ptr()), "vt_attention_fwd_packed")
+        zero_pad_rows(ctx, plan.counts)
     return ctx, lse
 
 
-def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None, key_tiles=None):
+def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None, key_tiles=None,
+                  plan: Optional[PackPlan] = None):
     L = init()
     if dqkv is None:
         dqkv = torch.empty_like(qkv)
-    ws = torch.empty(int(L.vt_attention_bwd_workspace(B, S, heads)), device=qkv.device, dtype=F32)
-    check(L.vt_attention_bwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(key_tiles), ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv),
-                             dropout_p, seed, stream_id, stream_ptr()), "vt_attention_bwd")
+    if plan is None:
+        ws = torch.empty(int(L.vt_attention_bwd_workspace(B, S, heads)), device=qkv.device, dtype=F32)
+        check(L.vt_attention_bwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(key_tiles), ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv),
+                                 dropout_p, seed, stream_id, stream_ptr()), "vt_attention_bwd")
+    else:
+        ws = torch.empty(int(L.vt_attention_bwd_workspace_packed(plan.cap, B, S, heads)), device=qkv.device, dtype=F32)
+        check(L.vt_attention_bwd_packed(ptr(qkv), qkv.stride(0), ptr(plan.bias), ptr(plan.key_tiles), ptr(plan.start), ptr(plan.row_b), plan.cap,
+                                        ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv), dropout_p, seed, stream_id, stream_ptr()),
+              "vt_attention_bwd_packed")
+        zero_pad_rows(dqkv, plan.counts)
     return dqkv
 
 
