@@ -124,6 +124,7 @@ def build_model(args, device):
         model = modeling.BertImgModelwithLocationEmbeds(cfg)   # what train.py hands the agent as `model.bert` (vs/train.py:47)
     else:
         model = modeling.PreTrainOscar(cfg)     # random-init bert-base (hf/modeling_bert.py:550-561), no checkpoint
+        model.vt_packed = not args.dense
     return model.to(device).train()
 
 
@@ -201,6 +202,12 @@ class Workload:
             self.labelled = (sum(int((hb["labels"] != -1).sum()) for hb in host) / (n_host * b),
                              sum(int((hb["token_labels"] != -1).sum()) for hb in host) / (n_host * b))
             self.heads_flops = None
+            # padding-free execution: the encoder runs on the rows that exist (mask != 0, labelled, or position 0)
+            keep = [((hb["attention_mask"] != 0) | (hb["labels"] != -1) | (hb["token_labels"] != -1)) for hb in host]
+            for k in keep:
+                k[:, 0] = True
+            lens = torch.cat([k.sum(1) for k in keep]).double()
+            self.valid_rows = (float(lens.mean()), float((lens * lens).mean()))     # E[S_valid], E[S_valid^2] per sample
         self.host = [{k: v.pin_memory() for k, v in hb.items()} for hb in host]
         self.n_host = n_host
         self.params = list(self.model.parameters()) + self.extra_params
@@ -240,8 +247,14 @@ class Workload:
         self.post_backward()
         return out
 
-    def flops(self, executed=False):
+    def flops(self, executed=False, valid_only=False):
         fl = flops_per_sample(self.S, self.R, all_rows_heads=not executed, labelled=self.labelled)
+        if valid_only and getattr(self, "valid_rows", None):   # the encoder on the rows that exist: GEMMs ~ E[S_valid], attention ~ E[S_valid^2]
+            sv, sv2 = self.valid_rows
+            fl["total"] -= fl["encoder_gemm"] + fl["attention"]
+            fl["encoder_gemm"] = 12 * 24 * sv * H * H
+            fl["attention"] = 12 * 4 * sv2 * H
+            fl["total"] += fl["encoder_gemm"] + fl["attention"]
         if self.heads_flops is not None:   # no pre-training heads, no image projection on this workload
             fl["total"] += self.heads_flops - fl["heads"] - fl["img"]
             fl["heads"], fl["img"] = self.heads_flops, 0
@@ -275,7 +288,11 @@ def make_config(args, world):
     """The `config` object of the JSON line: shared by both arms (the reference arm times bounded samples of THIS workload)."""
     desc, S = workload_desc(args)
     b = args.batch
-    return dict(workload=desc, per_gpu_batch=b, global_batch=b * world, seq_len=S, parallelism="dp%d" % world, dropout=args.dropout,
+    layout = {}
+    if args.workload == "pretrain":
+        layout = dict(layout="dense [B, S] rows (padding included)" if args.dense else
+                      "packed rows: padding-free execution, the rows that are masked out and unlabelled are dropped on the device")
+    return dict(workload=desc, per_gpu_batch=b, global_batch=b * world, seq_len=S, parallelism="dp%d" % world, dropout=args.dropout, **layout,
                 l2="per-step working set (%.1f GB of activations) >> 126 MB L2; 4 rotating batches" % (b * S * 24.5e3 * 12 / 1e9),
                 grad_allreduce="fp32, one bucket per encoder layer, overlapped with backward" if world > 1 else "none (1 GPU)")
 
@@ -417,8 +434,19 @@ def run_ours(args):
         timed(lambda i: step(dev_batches[i % n_host]), args.steps)
         evs, lib.GEMM_EVENTS = lib.GEMM_EVENTS, None
         torch.cuda.synchronize()
-        tot_ms = sum(a.elapsed_time(c) for a, c, _ in evs)
-        tot_fl = sum(f for _, _, f in evs)
+        # FLOPs EXECUTED per launch: a GEMM under a device-resident row limit (packed rows, labelled rows) walks min(rows, limit) rows
+        # (the limit is the count rounded up to 128 (+128 for the packed layout): those padding rows are computed and are counted here)
+        def executed_flops(ev):
+            _, _, M_, N_, K_, a_major, lim = ev
+            if lim is not None:
+                rows_dev = int(lim[0][4 * lim[1]])
+                if a_major:
+                    K_ = min(K_, rows_dev)
+                else:
+                    M_ = min(M_, rows_dev)
+            return 2.0 * M_ * N_ * K_
+        tot_ms = sum(ev[0].elapsed_time(ev[1]) for ev in evs)
+        tot_fl = sum(executed_flops(ev) for ev in evs)
         pk = peaks()
         ach = tot_fl / (tot_ms / 1e3) / 1e12 if tot_ms > 0 else 0.0
         traffic = None
@@ -429,7 +457,8 @@ def run_ours(args):
                     frac=round(ach / pk["tflops"], 4), traffic=traffic, peak_source=pk["src"], launches=len(evs),
                     gemm_ms_per_step=round(tot_ms / args.steps, 3), gemm_share_of_step=round(tot_ms / args.steps / (ms / args.steps), 3),
                     flops_per_launch_avg=tot_fl / max(len(evs), 1),
-                    note="algorithmic 2*M*N*K per launch / CUDA-event time per launch, separate pass of the same K steps")
+                    note="2*M*N*K EXECUTED per launch (M or K = the device-resident row count where a launch runs under a row limit) / CUDA-event "
+                         "time per launch, separate pass of the same K steps through the eager path")
 
     # ---- the step after backward, reported separately (the metric is fwd+bwd): fused AdamW, one launch ----
     from visitron_b200 import optimization as vopt
@@ -450,6 +479,8 @@ def run_ours(args):
         return
     S = wl.S
     fl, fl_done = wl.flops(), wl.flops(executed=True)
+    packed = args.workload == "pretrain" and getattr(model, "vt_packed", False)
+    fl_valid = wl.flops(executed=True, valid_only=True) if packed else fl_done
     n_out = 7 if args.workload == "pretrain" else 1
     pk = peaks()
     line = dict(
@@ -470,7 +501,13 @@ def run_ours(args):
                          per_sample_fwd_bwd_executed_GF=round(wl.flop_mult * fl_done["total"] / 1e9, 1),
                          achieved_TFLOPs_per_gpu_all_rows=round(value / world * wl.flop_mult * fl["total"] / 1e12, 1),
                          achieved_TFLOPs_per_gpu_executed=round(value / world * wl.flop_mult * fl_done["total"] / 1e12, 1),
-                         frac_of_peak_executed=round(value / world * wl.flop_mult * fl_done["total"] / 1e12 / pk["tflops"], 4),
+                         per_sample_fwd_bwd_executed_valid_rows_GF=round(wl.flop_mult * fl_valid["total"] / 1e9, 1),
+                         achieved_TFLOPs_per_gpu_executed_valid_rows=round(value / world * wl.flop_mult * fl_valid["total"] / 1e12, 1),
+                         frac_of_peak_executed=round(value / world * wl.flop_mult * fl_valid["total"] / 1e12 / pk["tflops"], 4),
+                         valid_rows_per_sample=(round(wl.valid_rows[0], 1) if getattr(wl, "valid_rows", None) else None),
+                         note="all_rows = the reference's work (every row through every head, SURVEY 8d-D4); executed = labelled rows only in the "
+                              "heads, all S rows in the encoder; executed_valid_rows = what runs: the encoder on the rows that exist (padding-free), "
+                              "frac_of_peak_executed is stated against it",
                          labelled_rows_per_sample=dict(mlm=round(labelled[0], 1), token=round(labelled[1], 1))),
     )
     line["optimizer"] = dict(kernel="adamw_kernel (multi-tensor, 1 launch)", ms_per_step=round(opt_ms, 3), elements=opt_elems,
@@ -668,6 +705,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-batch", type=int, default=2, help="batch of the CPU baseline's bounded sample (the scripts' per-GPU batch is 2; BASELINE C1 also asks for 8)")
     ap.add_argument("--no-gpu-eager", action="store_true", help="skip the oracle-on-the-GPU comparison leg (SURVEY 8d-D5)")
+    ap.add_argument("--dense", action="store_true", help="pre-training on the dense [B, S] layout (padding rows included) instead of packed rows")
     ap.add_argument("--no-graph", action="store_true", help="time the eager path (~400 ctypes launches per step) instead of the captured CUDA graph")
     ap.add_argument("--no-roofline", action="store_true")
     args = ap.parse_args()

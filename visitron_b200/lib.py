@@ -41,6 +41,9 @@ _inited = set()
 # bench.py's roofline pass: when a list, every GEMM launch is bracketed by CUDA events on the launching stream
 # and (start, end, 2*M*N*K) is appended
 GEMM_EVENTS = None
+# the row-limit block (counts tensor, which) that ops.row_limit has set on this thread, for the roofline pass only: the rows a GEMM
+# really walks are known on the device alone
+ACTIVE_LIMIT = threading.local()
 
 
 def load() -> C.CDLL:
@@ -193,5 +196,5 @@ def gemm(A: torch.Tensor, B: torch.Tensor, *, a_major: int = 0, b_major: int = 0
         check(rc, "vt_gemm_bf16")
     if GEMM_EVENTS is not None:
         e1.record()
-        GEMM_EVENTS.append((e0, e1, 2.0 * M * N * K))
+        GEMM_EVENTS.append((e0, e1, M, N, K, a_major, getattr(ACTIVE_LIMIT, "v", None)))
     return out

@@ -249,13 +249,16 @@ class row_limit:
 
     def __init__(self, counts, which=0):
         self.p = counts.data_ptr() + 16 * which
+        self.ref = (counts, which)
 
     def __enter__(self):
         init().vt_set_row_limit(self.p)
+        lib.ACTIVE_LIMIT.v = self.ref
         return self
 
     def __exit__(self, *exc):
         init().vt_set_row_limit(None)
+        lib.ACTIVE_LIMIT.v = None
         return False
 
 
