@@ -109,3 +109,50 @@ def test_product_refuses_cpu_tensors_without_the_double():
     model = modeling.BertImgModelwithLocationEmbeds(_cfg(oc))
     with pytest.raises(lib.VtError):
         model(torch.randint(1, 300, (2, 8)))
+
+
+def test_parameter_used_later_keeps_accumulated_gradient(monkeypatch):
+    """a parameter that gets its FIRST gradient in a later step (the next-action head when `next_action` is None in
+    step 1) with in-place zeroing ends up in another gradient buffer than its siblings; no later backward may wipe a live .grad, and
+    gradient accumulation must add, not double."""
+    emu.install(monkeypatch)
+    oc = vo.OracleConfig(vocab_size=300, num_hidden_layers=1, max_position_embeddings=16, detector_classes=20)
+    model = modeling.PreTrainOscar(_cfg(oc))
+    model.train()
+    batch = synthetic.pretrain_batch(2, 3, text_len=12, regions=8, vocab=300, detector_classes=20)
+    no_action = {k: v for k, v in batch.items() if k != "next_action"}
+
+    def grads():
+        return {k: (None if p.grad is None else p.grad.clone()) for k, p in model.named_parameters()}
+
+    model(**batch)[0].backward()
+    ref = grads()                                       # one full step from scratch
+    for p in model.parameters():
+        p.grad = None
+    model(**no_action)[0].backward()                    # step 1: the action head (and the pooler) get no gradient
+    assert model.next_action.linear.weight.grad is None
+    g_no = grads()
+    for p in model.parameters():                        # zero_grad(set_to_none=False)
+        if p.grad is not None:
+            p.grad.zero_()
+    model(**batch)[0].backward()                        # step 2: first gradient of the action head, the others accumulate into zeros
+    model(**batch)[0].backward()                        # step 3: accumulation on top of step 2
+    for k, p in model.named_parameters():
+        if ref[k] is None:
+            continue
+        torch.testing.assert_close(p.grad, 2 * ref[k], rtol=1e-4, atol=1e-6, msg=k)
+    assert g_no["bert.encoder.layer.0.output.dense.weight"] is not None
+
+
+def test_frozen_encoder_with_trainable_heads(monkeypatch):
+    """the heads must save their activations when only THEY require gradients."""
+    emu.install(monkeypatch)
+    oc = vo.OracleConfig(vocab_size=300, num_hidden_layers=1, max_position_embeddings=16, detector_classes=20)
+    model = modeling.PreTrainOscar(_cfg(oc))
+    model.train()
+    for p in model.bert.parameters():
+        p.requires_grad_(False)
+    batch = synthetic.pretrain_batch(2, 3, text_len=12, regions=8, vocab=300, detector_classes=20)
+    model(**batch)[0].backward()
+    assert model.token_head[0].weight.grad is not None and model.mlmhead.predictions.transform.dense.weight.grad is not None
+    assert model.bert.encoder.layer[0].output.dense.weight.grad is None
