@@ -551,11 +551,13 @@ def grad_sync_check(wl, model, batch, device, world):
     rank with dropout off, (a) every rank ends the step with bit-identical gradients, (b) they equal the mean over ranks of the
     gradients each rank computes on its own (the same step with the reducer detached, averaged by one plain all-reduce)."""
     dist = torch.distributed
-    was_training = model.training
-    model.eval()     # dropout off: the two passes draw no masks
+    mods = [model] + [m for m in (getattr(wl, "encoder", None), getattr(wl, "decoder", None)) if m is not None]
+    was_training = [m.training for m in mods]
+    for m in mods:
+        m.eval()     # dropout off (the encoder's and the agent modules'): the two passes draw no masks
     try:
         def flat_grads():
-            return torch.cat([p.grad.detach().float().reshape(-1) for p in model.parameters() if p.grad is not None])
+            return torch.cat([p.grad.detach().float().reshape(-1) for p in wl.params if p.grad is not None])
 
         def one():
             for p in wl.params:
@@ -585,7 +587,8 @@ def grad_sync_check(wl, model, batch, device, world):
         return dict(grad_sync_ok=bool(identical and rel < 1e-3), identical_across_ranks=identical, rel_l2_vs_mean_of_local=rel, elements=int(synced.numel()),
                     note="fixed batch per rank, dropout off; rel_l2 > 0 only from the fp32 summation order (split-K red.add, NCCL's reduction tree)")
     finally:
-        model.train(was_training)
+        for m, t in zip(mods, was_training):
+            m.train(t)
 
 
 def gpu_eager_baseline(args, device, our_value):
