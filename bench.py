@@ -559,20 +559,22 @@ def grad_sync_check(wl, model, batch, device, world):
         def flat_grads():
             return torch.cat([p.grad.detach().float().reshape(-1) for p in wl.params if p.grad is not None])
 
-        def one():
+        def one(sync):
             for p in wl.params:
                 p.grad = None
             with torch.enable_grad():
                 out = wl.forward(batch)
                 out[0].backward()
+                if sync:
+                    wl.post_backward()      # the agents' parameters outside the flat buffer
             torch.cuda.synchronize()
             return flat_grads()
-        synced = one()
+        synced = one(True)
         reducers = [(m, m._vt_reducer) for m in model.modules() if getattr(m, "_vt_reducer", None) is not None]
         for m, _ in reducers:
             m._vt_reducer = None
         try:
-            local = one()
+            local = one(False)
         finally:
             for m, r in reducers:
                 m._vt_reducer = r
