@@ -127,6 +127,10 @@ typedef struct {
   /* optional second map (packed rows, vt_pack_plan): the row computed above is looked up in remap_index (int32); a negative entry
    * drops the row.  With remap_rows_in == 0 the logical row m itself is looked up. */
   const int32_t* remap_index;
+  /* optional, a_major == 1 only (A is [K, M]: the weight-gradient form dW = dY^T X): colsum[m] += alpha * sum_k A[k, m], fp32,
+   * i.e. the bias gradient of the same layer (torch autograd's sum over rows of dY for F.linear, oscar/modeling_bert.py:43-45)
+   * from the dY tiles the GEMM has in shared memory anyway.  Always accumulates (split-K safe); needs block N <= 192. */
+  float* colsum;
 } vt_gemm_epilogue;
 
 int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void* B, int64_t ldb, int b_major,

@@ -76,7 +76,7 @@ def _no_dropout(p):
 
 def gemm(A, B, *, a_major=0, b_major=0, out=None, out_dtype=BF16, bias=None, act=0, alpha=1.0, alpha_dev=None,
          residual=None, aux=None, aux_out=None, dropout_p=0.0, seed=0, dropout_stream=0, accumulate=False, split_k=0,
-         remap=None, remap_index=None, M=None, N=None, K=None):
+         remap=None, remap_index=None, colsum=None, M=None, N=None, K=None):
     CALLS.append("gemm")
     assert A.dtype == BF16 and B.dtype == BF16
     _no_dropout(dropout_p)
@@ -90,6 +90,10 @@ def gemm(A, B, *, a_major=0, b_major=0, out=None, out_dtype=BF16, bias=None, act
         else:
             Af = Af[: _LIMIT[0]]
     r = alpha * (Af[:, :k] @ Bf[:k])
+    if colsum is not None:
+        assert a_major and colsum.dtype == F32
+        cs = alpha * Af[:, :k].sum(1)
+        colsum[: cs.numel()] += cs[: colsum.numel()] if M is None else cs[:M]
     if M is not None:
         r = r[:M]
     if N is not None:

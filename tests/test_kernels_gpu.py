@@ -87,6 +87,40 @@ def test_gemm_epilogues_and_splitk():
     assert float(out[:, 3001:].abs().max()) == 0.0
 
 
+@pytest.mark.parametrize("M,N,K,bn", [(2304, 768, 5000, 0), (3072, 768, 17500, 0), (3001, 768, 130, 0), (100, 200, 64, 0),
+                                      (768, 768, 32, 0), (520, 304, 1000, 64), (520, 304, 1000, 128), (520, 384, 1000, 192)])
+def test_gemm_weight_gradient_with_bias_gradient(M, N, K, bn):
+    """colsum: the bias gradient (sum over rows of dY) as a side product of dW = dY^T X; also under split-K, on partial row blocks,
+    with a padded leading dimension and under a device row limit (only the first `rows` rows of dY / X count)."""
+    torch.manual_seed(M + K)
+    ld = (M + 7) // 8 * 8 + 8
+    dY = torch.zeros(K, ld, device=DEV, dtype=BF)
+    dY[:, :M] = (torch.randn(K, M, device=DEV) * 0.2 + 0.05).to(BF)
+    X = (torch.randn(K, N, device=DEV) * 0.2).to(BF)
+    acc = torch.full((M, N), 0.5, device=DEV)
+    db = torch.full((M + 3,), 2.0, device=DEV)
+    lib.init().vt_debug_force_block_n(bn)
+    try:
+        lib.gemm(dY[:, :M], X, a_major=1, b_major=1, out=acc, accumulate=True, colsum=db)
+        close(acc, 0.5 + dY[:, :M].float().t() @ X.float(), rtol=1e-3, atol=2e-3, what="dW")
+        close(db[:M], 2.0 + dY[:, :M].float().sum(0), rtol=1e-3, atol=2e-3, what="db")
+        assert bool((db[M:] == 2.0).all())
+        if K >= 256:
+            rows = K - 200
+            lim = torch.tensor([(rows + 127) // 128 * 128, rows], device=DEV, dtype=torch.int32)
+            dY[rows:] = 0          # the pad-row rule: rows past the count are finite zeros (the last 64-row block is contracted whole)
+            acc.fill_(0.0)
+            db.fill_(0.0)
+            with ops.row_limit(lim, 0):
+                lib.gemm(dY[:, :M], X, a_major=1, b_major=1, out=acc, accumulate=True, colsum=db, alpha=0.5)
+            close(acc, 0.5 * (dY[:rows, :M].float().t() @ X[:rows].float()), rtol=1e-3, atol=2e-3, what="dW limited")
+            close(db[:M], 0.5 * dY[:rows, :M].float().sum(0), rtol=1e-3, atol=2e-3, what="db limited")
+    finally:
+        lib.init().vt_debug_force_block_n(0)
+    with pytest.raises(lib.VtError):
+        lib.gemm(X, X, out_dtype=torch.float32, colsum=db)      # K-major A: not the weight-gradient form
+
+
 def test_gemm_row_remap_and_strided_a():
     torch.manual_seed(3)
     b, R, S, T = 4, 24, 64, 40

@@ -92,16 +92,18 @@ def main():
                                      seed=seed, dx=out_h, dxd=out_h2), 0, 4.0 * M * H * 2)
     case("wgrad ffn-down   dW[768,3072] = dY^T Z", lambda i: lib.gemm(r(xs, i), r(zs, i), a_major=1, b_major=1, out=gW.view(H, I), accumulate=True), gemm_fl(I, H))
     case("dgrad ffn-down   [M,768]x[768,3072]  x saved gelu'", lambda i: lib.gemm(r(xs, i), W2, b_major=1, act=ACT_MUL_AUX, aux=r(zs, i), out=out_i), gemm_fl(I, H))
-    case("colsum           [M,3072]", lambda i: ops.colsum(r(zs, i), gvec[:I]), 0, 1.0 * M * I * 2)
+    case("colsum           [M,3072] (separate kernel, no longer in the step)", lambda i: ops.colsum(r(zs, i), gvec[:I]), 0, 1.0 * M * I * 2)
     case("wgrad ffn-up     dW[3072,768] = dPre^T Y", lambda i: lib.gemm(r(zs, i), r(xs, i), a_major=1, b_major=1, out=gW.view(I, H), accumulate=True), gemm_fl(I, H))
+    case("wgrad ffn-up     + bias gradient (column sums of dPre)", lambda i: lib.gemm(r(zs, i), r(xs, i), a_major=1, b_major=1, out=gW.view(I, H), accumulate=True, colsum=gvec[:I]), gemm_fl(I, H))
     case("dgrad ffn-up     [M,3072]x[3072,768] +residual", lambda i: lib.gemm(r(zs, i), W1, b_major=1, residual=r(xs, i), out=out_h), gemm_fl(I, H))
     case("wgrad attn-out   dW[768,768]", lambda i: lib.gemm(r(xs, i), r(xs, i + 1), a_major=1, b_major=1, out=gW[:H * H].view(H, H), accumulate=True), gemm_fl(H, H))
     case("dgrad attn-out   [M,768]x[768,768]", lambda i: lib.gemm(r(xs, i), Wo, b_major=1, out=out_h), gemm_fl(H, H))
     case("attn bwd         (prep + dK/dV + dQ)", lambda i: ops.attention_bwd(qkvs[0], bias, ctx0, r(xs, i), lse0, B, S, NH, pa, seed, 0, dqkv=out_q), 2.5 * attn_f)
     case("attn bwd         bench padding, masked key tiles skipped",
          lambda i: ops.attention_bwd(qkvs[0], bbias, ctx1, r(xs, i), lse1, B, S, NH, pa, seed, 0, dqkv=out_q, key_tiles=plan), 2.5 * attn_f)
-    case("colsum           [M,2304]", lambda i: ops.colsum(r(qkvs, i), gvec[:3 * H]), 0, 1.0 * M * 3 * H * 2)
+    case("colsum           [M,2304] (separate kernel, no longer in the step)", lambda i: ops.colsum(r(qkvs, i), gvec[:3 * H]), 0, 1.0 * M * 3 * H * 2)
     case("wgrad qkv        dW[2304,768]", lambda i: lib.gemm(r(qkvs, i), r(xs, i), a_major=1, b_major=1, out=gW[:3 * H * H].view(3 * H, H), accumulate=True), gemm_fl(3 * H, H))
+    case("wgrad qkv        + bias gradient", lambda i: lib.gemm(r(qkvs, i), r(xs, i), a_major=1, b_major=1, out=gW[:3 * H * H].view(3 * H, H), accumulate=True, colsum=gvec[:3 * H]), gemm_fl(3 * H, H))
     case("dgrad qkv        [M,2304]x[2304,768] +residual", lambda i: lib.gemm(r(qkvs, i), Wqkv, b_major=1, residual=r(xs, i), out=out_h), gemm_fl(3 * H, H))
 
     # the step before forward (input_pipeline.py), outside the layer total
@@ -181,7 +183,10 @@ def main():
         e1.record()
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) * 1e3 / args.iters
-        tot += us if ci < n_layer and not (name.startswith("attn") and "skipped" not in name) else 0.0
+        # the layer total counts what the step launches: attention with the key-tile plan, the bias gradients inside the wgrad GEMMs
+        skip = (name.startswith("attn") and "skipped" not in name) or "no longer in the step" in name or \
+            name.startswith("wgrad ffn-up     dW") or name.startswith("wgrad qkv        dW")
+        tot += us if ci < n_layer and not skip else 0.0
         rate = "%7.0f TFLOP/s" % (fl / us / 1e6) if fl else "%7.0f GB/s   " % (by / us / 1e3)
         print("%-62s %8.1f us  %s" % (name, us, rate), flush=True)
         rows.append(dict(name=name.split("  ")[0].strip(), us=round(us, 1), tflops=round(fl / us / 1e6, 1) if fl else None,

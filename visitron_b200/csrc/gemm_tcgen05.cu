@@ -46,18 +46,28 @@ struct GemmParams {
   const int32_t* rows_dev;
   // optional output row map (packed rows): logical row m is written to row remap_index[m], or nowhere when that is negative
   const int32_t* remap_index;
+  // weight-gradient form only (A is [K, M]): colsum[m] += alpha * sum over k of A[k, m] -- the bias gradient of the layer whose
+  // weight gradient this GEMM is, taken from the A tiles that are in shared memory anyway (16 more columns of ones on the B side)
+  float* colsum;
 };
 
-template <int BN>
+// CS = 1: the column-sum variant.  Every stage's B tile is followed by a block of bf16 ones (written once; TMA never touches it), so
+// that for the first column block of a row block the MMA simply runs with N = BN + 16: accumulator columns BN .. BN + 15 all
+// receive sum_k A[k, m].  (A separate N = 16 MMA per k step re-read the whole A tile from shared memory: +33 % on those tiles.)
+template <int BN, int CS = 0>
 struct GemmCfg {
+  static_assert(!CS || BN <= 192, "the column-sum variant needs 16 accumulator columns next to the tile");
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
-  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int ONES_BYTES = CS ? 64 * BK * 2 : 0;   // one MN-major 64-column chunk (a K-major B needs only 16 rows of it)
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES + ONES_BYTES;
+  static constexpr int ACC_STRIDE = !CS ? BN : (BN + 16 <= 128 ? 128 : 256);   // TMEM columns per accumulator stage
   static constexpr int EPI_BYTES = NUM_EPI_WARPS * 32 * 32 * 4;  // per-warp fp32 [32][32] transpose buffer (XOR-swizzled)
   static constexpr int BAR_BYTES = 256;
   static constexpr int BUDGET = 227 * 1024 - 1024 - BAR_BYTES - EPI_BYTES;  // 1024: slack for 1024-B alignment
   static constexpr int STAGES = BUDGET / STAGE_BYTES > 8 ? 8 : BUDGET / STAGE_BYTES;
-  static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  static constexpr int TMEM_NEED = 2 * ACC_STRIDE;
+  static constexpr int TMEM_COLS = (TMEM_NEED <= 32) ? 32 : (TMEM_NEED <= 64) ? 64 : (TMEM_NEED <= 128) ? 128 : (TMEM_NEED <= 256) ? 256 : 512;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;
 };
 
@@ -211,10 +221,11 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, const Dropou
   }
 }
 
-template <int BN, int A_MN, int B_MN, int EPI>
+template <int BN, int A_MN, int B_MN, int EPI, int CS = 0>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+  static_assert(!CS || A_MN, "column sums are taken over the rows of a [K, M] A operand");
+  using Cfg = GemmCfg<BN, CS>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -248,6 +259,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 2) {
     tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
     tmem_relinquish();
+  }
+  if (CS && warp == 3) {   // bf16 1.0 everywhere behind every stage's B tile: no swizzle or major can misplace an element
+    constexpr uint32_t one2 = 0x3f803f80u;
+    for (int s = 0; s < STAGES; ++s) {
+      const uint32_t ob = smem_base + s * Cfg::STAGE_BYTES + Cfg::A_BYTES + Cfg::B_BYTES;
+      for (int i = lane; i < Cfg::ONES_BYTES / 16; i += 32) st_shared_v4(ob + 16u * (uint32_t)i, one2, one2, one2, one2);
+    }
+    fence_proxy_async();
   }
   tc_fence_before();
   __syncthreads();
@@ -284,7 +303,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int kb1 = min(kb0 + kbps, k_blocks);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
-          mbar_arrive_expect_tx(full_bar(stage), Cfg::STAGE_BYTES);
+          mbar_arrive_expect_tx(full_bar(stage), Cfg::A_BYTES + Cfg::B_BYTES);   // the ones block behind B is not TMA's
           const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
           const uint32_t sb = sa + Cfg::A_BYTES;
           if (A_MN) {
@@ -306,6 +325,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1) {
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+      constexpr uint32_t idesc_cs = make_idesc_bf16(BM, BN + 16, A_MN, B_MN);   // the tile plus 16 columns of ones
       // K-major, 128B swizzle: 8-row groups 1024 B apart (SBO); LBO unused (encoded 1).
       // MN-major, 128B swizzle: 64-element MN chunks one TMA box (64*BK*2 B) apart (LBO),
       //                         8-row K groups 1024 B apart (SBO).
@@ -318,9 +338,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int split = t / mn_tiles;
         const int kb0 = split * kbps;
         const int kb1 = min(kb0 + kbps, k_blocks);
+        const uint32_t idesc_t = (CS && ((t % mn_tiles) % p.n_blocks) == 0) ? idesc_cs : idesc;   // once per (row block of A, split)
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * Cfg::ACC_STRIDE);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
@@ -329,7 +350,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint64_t b_desc = make_smem_desc(sa + Cfg::A_BYTES, B_LBO, 1024);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k)
-            umma_bf16(d_tmem, a_desc + (uint64_t)(k * A_KSTEP), b_desc + (uint64_t)(k * B_KSTEP), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            umma_bf16(d_tmem, a_desc + (uint64_t)(k * A_KSTEP), b_desc + (uint64_t)(k * B_KSTEP), idesc_t, (kb > kb0 || k > 0) ? 1u : 0u);
           umma_commit(empty_bar(stage));
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
@@ -379,9 +400,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int m_blk = mn / p.n_blocks, n_blk = mn % p.n_blocks;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+      const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * Cfg::ACC_STRIDE);
       uint32_t v[32];
       tmem_ld_32x32(t_addr + (uint32_t)(c_begin * 32), v);
+      if (CS && n_blk == 0 && half == 0) {
+        // the column sums of this row block of A over the tile's k range: one value per TMEM lane, i.e. per m
+        uint32_t cv[4];
+        tmem_ld_32x4(t_addr + (uint32_t)BN, cv);
+        tmem_ld_wait();
+        const int m = m_blk * BM + q * 32 + lane;
+        if (m < M) atomicAdd(p.colsum + m, __uint_as_float(cv[0]) * alpha);
+      }
       tmem_ld_wait();
 #pragma unroll 1
       for (int c = c_begin; c < c_end; ++c) {
@@ -488,11 +517,11 @@ int make_map(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, u
   return VT_OK;
 }
 
-template <int BN, int A_MN, int B_MN, int EPI = EPI_GENERIC>
+template <int BN, int A_MN, int B_MN, int EPI = EPI_GENERIC, int CS = 0>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t st) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, CS>;
   static bool attr_set = false;
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, EPI>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, EPI, CS>;
   if (!attr_set) {
     VT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set = true;
@@ -505,6 +534,9 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
 
 template <int BN>
 static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t st) {
+  if constexpr (BN <= 192) {
+    if (p.colsum) return b_mn ? launch_gemm<BN, 1, 1, EPI_GENERIC, 1>(ta, tb, p, grid, st) : launch_gemm<BN, 1, 0, EPI_GENERIC, 1>(ta, tb, p, grid, st);
+  }
   if (!a_mn && !b_mn) return launch_gemm<BN, 0, 0>(ta, tb, p, grid, st);
   if (!a_mn && b_mn) return launch_gemm<BN, 0, 1>(ta, tb, p, grid, st);
   if (a_mn && b_mn) return launch_gemm<BN, 1, 1>(ta, tb, p, grid, st);
@@ -573,6 +605,11 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
       }
     }
   }
+  if (ep->colsum) {
+    VT_REQUIRE(a_major == 1, "vt_gemm_bf16: colsum is the column sum of a [K, M] A operand (weight-gradient form)");
+    if (BN == 256 && !g_force_bn) BN = (N % 192 == 0) ? 192 : 128;
+    VT_REQUIRE(BN != 256, "vt_gemm_bf16: colsum needs block N <= 192 (TMEM columns)");
+  }
   VT_REQUIRE(BN == 64 || BN == 128 || BN == 192 || BN == 256, "vt_gemm_bf16: bad block N %d", BN);
 
   GemmParams p;
@@ -610,6 +647,7 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   p.remap_in = ep->remap_rows_in; p.remap_out = ep->remap_rows_out; p.remap_off = ep->remap_row_off;
   p.rows_dev = row_limit();
   p.remap_index = ep->remap_index;
+  p.colsum = ep->colsum;
   // 16-byte vector path: every row slice the epilogue touches must be 16-byte aligned
   const int ob = p.out_fp32 ? 4 : 2;
   bool vec = ((uintptr_t)D % 16 == 0) && ((ldd * ob) % 16 == 0);

@@ -33,6 +33,7 @@ class GemmEpilogue(C.Structure):
         ("dropout_p", C.c_float), ("seed", C.c_uint64), ("dropout_stream", C.c_uint32),
         ("remap_rows_in", C.c_int64), ("remap_rows_out", C.c_int64), ("remap_row_off", C.c_int64),
         ("remap_index", C.c_void_p),
+        ("colsum", C.c_void_p),
     ]
 
 
@@ -132,10 +133,11 @@ def gemm(A: torch.Tensor, B: torch.Tensor, *, a_major: int = 0, b_major: int = 0
          out: Optional[torch.Tensor] = None, out_dtype=torch.bfloat16, bias=None, act: int = ACT_NONE,
          alpha: float = 1.0, alpha_dev=None, residual=None, aux=None, aux_out=None,
          dropout_p: float = 0.0, seed: int = 0, dropout_stream: int = 0, accumulate: bool = False,
-         split_k: int = 0, remap=None, remap_index=None, M=None, N=None, K=None) -> torch.Tensor:
+         split_k: int = 0, remap=None, remap_index=None, colsum=None, M=None, N=None, K=None) -> torch.Tensor:
     """D = epilogue(alpha * A x B^T) on the tcgen05 GEMM (see vt_gemm_bf16 in the header).
 
     a_major/b_major = 0: A is [M,K] / B is [N,K]; = 1: A is [K,M] / B is [K,N] (row-major).
+    colsum (fp32 [M], a_major = 1 only): += alpha * column sums of A -- the bias gradient next to the weight gradient.
     """
     lib = init()
     assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16
@@ -188,6 +190,12 @@ def gemm(A: torch.Tensor, B: torch.Tensor, *, a_major: int = 0, b_major: int = 0
     ep.dropout_p, ep.seed, ep.dropout_stream = dropout_p, seed, dropout_stream
     ep.remap_rows_in, ep.remap_rows_out, ep.remap_row_off = remap if remap is not None else (0, 0, 0)
     ep.remap_index = None if remap_index is None else remap_index.data_ptr()
+    if colsum is not None:
+        if not a_major or colsum.dtype is not torch.float32 or not colsum.is_contiguous() or colsum.numel() < M:
+            raise VtError("colsum: fp32 contiguous [M] next to a [K, M] A operand")
+        ep.colsum = colsum.data_ptr()
+    else:
+        ep.colsum = None
     if GEMM_EVENTS is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()

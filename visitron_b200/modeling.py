@@ -529,8 +529,7 @@ def _encoder_backward(step: _Step, st: FlatStore, d, dpooled):
     if dpooled is not None:
         dp = ops.tanh_bwd(dpooled.contiguous(), step.pooled)
         cls_in = x_last[::S] if plan is None else step.cls_in
-        lib.gemm(dp, cls_in, a_major=1, b_major=1, out=st.g("pooler.dense.weight"), accumulate=True)
-        ops.colsum(dp, st.g("pooler.dense.bias"))
+        lib.gemm(dp, cls_in, a_major=1, b_major=1, out=st.g("pooler.dense.weight"), accumulate=True, colsum=st.g("pooler.dense.bias"))
         lib.gemm(dp, st.wb("pooler.dense.weight"), b_major=1, out=d, residual=d, remap=(1, S, 0), remap_index=row_dst)
     limit = ops.row_limit(plan.counts, 0) if plan is not None else contextlib.nullcontext()
     with limit:
@@ -580,8 +579,9 @@ def _encoder_layers_backward(step: _Step, st: FlatStore, d):
                                       out_dropout_p=ph, out_stream=4 * l + 2, seed=step.seed)
         lib.gemm(dx2d, z, a_major=1, b_major=1, out=st.g(p + "output.dense.weight"), accumulate=True)
         dpre = lib.gemm(dx2d, st.wb(p + "output.dense.weight"), b_major=1, act=ACT_MUL_AUX, aux=pre)   # pre holds gelu'(pre-activation)
-        ops.colsum(dpre, st.g(p + "intermediate.dense.bias"))
-        lib.gemm(dpre, y1, a_major=1, b_major=1, out=st.g(p + "intermediate.dense.weight"), accumulate=True)
+        # the bias gradients ride on the weight-gradient GEMMs (column sums of the dY tiles they stage anyway)
+        lib.gemm(dpre, y1, a_major=1, b_major=1, out=st.g(p + "intermediate.dense.weight"), accumulate=True,
+                 colsum=st.g(p + "intermediate.dense.bias"))
         dy1 = lib.gemm(dpre, st.wb(p + "intermediate.dense.weight"), b_major=1, residual=dx2)
         del dpre, dx2, dx2d, pre, z, x2
         # LN1 and the attention block
@@ -591,8 +591,8 @@ def _encoder_layers_backward(step: _Step, st: FlatStore, d):
         lib.gemm(dx1d, ctx, a_major=1, b_major=1, out=st.g(p + "attention.output.dense.weight"), accumulate=True)
         dctx = lib.gemm(dx1d, st.wb(p + "attention.output.dense.weight"), b_major=1)
         dqkv = ops.attention_bwd(qkv, step.bias, ctx, dctx, lse, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles, plan=step.plan)
-        ops.colsum(dqkv, st.g(p + "attention.self.query.bias", 3 * H))
-        lib.gemm(dqkv, x_in, a_major=1, b_major=1, out=st.g(p + "attention.self.query.weight", 3 * H, H), accumulate=True)
+        lib.gemm(dqkv, x_in, a_major=1, b_major=1, out=st.g(p + "attention.self.query.weight", 3 * H, H), accumulate=True,
+                 colsum=st.g(p + "attention.self.query.bias", 3 * H))
         d = lib.gemm(dqkv, st.wb(p + "attention.self.query.weight", 3 * H, H), b_major=1, residual=dx1)
         del dqkv, dctx, dx1, dx1d, dy1, qkv, ctx, x1, y1, x_in
         if red is not None:  # this layer's slice (the last layer's also holds the pooler) is complete: exchange it now
@@ -812,22 +812,20 @@ class _HeadsFn(torch.autograd.Function):
         with ops.row_limit(counts, 0):
             # the mean's 1 / n is applied on the device (the count lives there); padding rows of dlog are zeros
             dlog = ops.softmax_ce_bwd(logits[:, :V], V, lab_mlm, mlm_stats, 1.0, g_mlm, ld_out=ldv)
-            ops.colsum(dlog, hs.g("mlmhead.predictions.bias"), ncols=V)
-            lib.gemm(dlog[:, :V], tl, a_major=1, b_major=1, out=dE, accumulate=True)
+            lib.gemm(dlog[:, :V], tl, a_major=1, b_major=1, out=dE, accumulate=True, colsum=hs.g("mlmhead.predictions.bias"))
             dtl = lib.gemm(dlog[:, :V], E, b_major=1)
             del dlog
             da, _ = ops.layernorm_bwd(dtl, a, hs.w("mlmhead.predictions.transform.LayerNorm.weight"), eps,
                                       hs.g("mlmhead.predictions.transform.LayerNorm.weight"),
                                       hs.g("mlmhead.predictions.transform.LayerNorm.bias"), None)
             dpre = ops.gelu_bwd(da, pre_t)
-            ops.colsum(dpre, hs.g("mlmhead.predictions.transform.dense.bias"))
-            lib.gemm(dpre, hm, a_major=1, b_major=1, out=hs.g("mlmhead.predictions.transform.dense.weight"), accumulate=True)
+            lib.gemm(dpre, hm, a_major=1, b_major=1, out=hs.g("mlmhead.predictions.transform.dense.weight"), accumulate=True,
+                     colsum=hs.g("mlmhead.predictions.transform.dense.bias"))
             dhm = lib.gemm(dpre, hs.wb("mlmhead.predictions.transform.dense.weight"), b_major=1)
             ops.scatter_add_rows(dhm, idx_mlm, dseq)
         with ops.row_limit(counts, 1):
             dlt = ops.softmax_ce_bwd(tlogits[:, :Dc], Dc, lab_tok, tok_stats, 1.0, g_tok, double_softmax=True, ld_out=ldt)
-            ops.colsum(dlt, hs.g("token_head.0.bias"), ncols=Dc)
-            lib.gemm(dlt[:, :Dc], ht, a_major=1, b_major=1, out=hs.g("token_head.0.weight"), accumulate=True)
+            lib.gemm(dlt[:, :Dc], ht, a_major=1, b_major=1, out=hs.g("token_head.0.weight"), accumulate=True, colsum=hs.g("token_head.0.bias"))
             dht = lib.gemm(dlt[:, :Dc], hs.wb("token_head.0.weight"), b_major=1)
             ops.scatter_add_rows(dht, idx_tok, dseq)
         dpooled = None
