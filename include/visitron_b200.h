@@ -60,6 +60,13 @@ void vt_reset_launch_count(void);
 void vt_set_seed_source(const uint64_t* seed_dev);
 int vt_seed_advance(uint64_t* state /* device uint64[2] */, vt_stream stream);
 void vt_set_row_limit(const int32_t* rows_dev /* device int32[2] = {rows padded to 128, rows} */);
+/* Keep-bit store of the attention-probability dropout (oscar/modeling_bert.py:64 `self.dropout(attention_probs)`; autograd keeps
+ * the mask of that nn.Dropout between forward and backward).  While a store is set ON THE CALLING THREAD, vt_attention_fwd*
+ * (dropout_p > 0) also writes the keep decisions it draws -- uint32 [B * heads][4 * ceil(S / 128)][S]: bit c of word (bh, g, i)
+ * = key 32 g + c of query row i kept -- and vt_attention_bwd* reads them instead of running the counter generator again.  Same
+ * mask either way (the bits ARE the generator's output); NULL (the default) regenerates.  vt_attention_keep_bits_words = words. */
+void vt_set_attention_keep_bits(uint32_t* bits);
+int64_t vt_attention_keep_bits_words(int64_t B, int64_t S, int64_t heads);
 /* Compaction of the labelled rows (replaces torch.nonzero(labels != -1) + labels[idx] in front of the MLM / token heads,
  * vs/encoder.py:387-389,381-385, whose data-dependent sizes cost a sync per step).  For each of the two label arrays
  * (int64 [n]; either may be NULL): idx[r] / lab[r] = position / label of the r-th label != ignore_index in ascending order

@@ -363,7 +363,7 @@ def _attn_packed(qkv, plan, heads):
     return out, parts
 
 
-def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None, key_tiles=None, plan=None):
+def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None, key_tiles=None, plan=None, keep_bits=None):
     CALLS.append("attention_fwd")
     _no_dropout(dropout_p)
     if plan is None:
@@ -377,7 +377,7 @@ def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ct
     return out, torch.zeros((B, heads, S, 2))
 
 
-def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None, key_tiles=None, plan=None):
+def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None, key_tiles=None, plan=None, keep_bits=None):
     CALLS.append("attention_bwd")
     _no_dropout(dropout_p)
     q = qkv.float().requires_grad_(True)

@@ -314,6 +314,21 @@ def test_attention_dropout_fwd_bwd_same_mask():
     ref.backward(dctx.float())
     dqkv = ops.attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=p, seed=seed, stream_id=sid)
     assert rel_l2(dqkv, qr.grad) < 2e-2, rel_l2(dqkv, qr.grad)
+    # the stored keep bits are the generator's decisions: the bits agree with the recovered mask, the forward's output does not
+    # change, and the backward that reads them returns the very same bits as the one that draws them again
+    bits = ops.attention_keep_bits(B, S, heads, DEV)
+    bits.fill_(0x55555555)
+    ctx_b, lse_b = ops.attention_fwd(qkv, bias, B, S, heads, dropout_p=p, seed=seed, stream_id=sid, keep_bits=bits)
+    assert torch.equal(ctx_b, ctx) and torch.equal(lse_b, lse)
+    G = 4 * ((S + 127) // 128)
+    w = bits.view(B * heads, G, S).long() & 0xffffffff
+    unpacked = ((w[:, :, :, None] >> torch.arange(32, device=DEV)) & 1).permute(0, 2, 1, 3).reshape(B, heads, S, G * 32)[..., :S]
+    assert torch.equal(unpacked.float(), mask)
+    dqkv_b = ops.attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=p, seed=seed, stream_id=sid, keep_bits=bits)
+    assert torch.equal(dqkv_b, dqkv)
+    bits.zero_()      # ... and it really reads them: with every probability dropped only the -P.rowsum(dO.O) term is left
+    dqkv_0 = ops.attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=p, seed=seed, stream_id=sid, keep_bits=bits)
+    assert not torch.equal(dqkv_0, dqkv) and float(dqkv_0[:, 2 * Hh:].abs().max()) == 0.0
 
 
 @pytest.mark.parametrize("ncols,double", [(30522, False), (1601, True), (96, True), (5, False)])

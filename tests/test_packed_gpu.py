@@ -75,8 +75,16 @@ def test_packed_attention_equals_dense_attention(B, S, heads, p):
     qkv_p = torch.zeros(pl.cap, 3 * Hh, device=DEV, dtype=BF)
     dctx_p = torch.zeros(pl.cap, Hh, device=DEV, dtype=BF)
     qkv_p[:n], dctx_p[:n] = qkv[src], dctx[src]
-    ctx_p, lse_p = ops.attention_fwd(qkv_p, None, B, S, heads, p, seed, sid, plan=pl)
-    dqkv_p = ops.attention_bwd(qkv_p, None, ctx_p, dctx_p, lse_p, B, S, heads, p, seed, sid, plan=pl)
+    bits = ops.attention_keep_bits(B, S, heads, DEV) if p > 0 else None      # the model's path: keep bits stored by the forward
+    ctx_p, lse_p = ops.attention_fwd(qkv_p, None, B, S, heads, p, seed, sid, plan=pl, keep_bits=bits)
+    dqkv_p = ops.attention_bwd(qkv_p, None, ctx_p, dctx_p, lse_p, B, S, heads, p, seed, sid, plan=pl, keep_bits=bits)
+    if bits is not None:
+        regen = ops.attention_bwd(qkv_p, None, ctx_p, dctx_p, lse_p, B, S, heads, p, seed, sid, plan=pl)
+        # same mask, same arithmetic; the two template instances are scheduled differently and one dS element in ~2 M lands on the
+        # other side of a bf16 rounding (measured: 2 of 985 k outputs differ by one ulp, tools/keepbits_diag.py)
+        a_, b_ = dqkv_p[:n].float(), regen[:n].float()
+        assert int((a_ != b_).sum()) <= 1e-5 * a_.numel() and float((a_ - b_).abs().max()) <= 2 ** -7 * float(b_.abs().max())
+        assert bool((dqkv_p[n:int(pl.counts[0])] == 0).all())
     torch.cuda.synchronize()
     assert torch.equal(ctx_p[:n], ctx[src]), float((ctx_p[:n].float() - ctx[src].float()).abs().max())
     assert bool((ctx_p[n:int(pl.counts[0])] == 0).all())

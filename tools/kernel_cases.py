@@ -81,6 +81,10 @@ def main():
     case("gemm qkv         [M,768]x[2304,768]  bias", lambda i: lib.gemm(r(xs, i), Wqkv, bias=bqkv, out=out_q), gemm_fl(3 * H, H))
     case("attn fwd         S=%d d=64 p=%.1f" % (S, pa), lambda i: ops.attention_fwd(r(qkvs, i), bias, B, S, NH, pa, seed, 0, ctx=out_h), attn_f)
     case("attn fwd         bench padding, masked key tiles skipped", lambda i: ops.attention_fwd(r(qkvs, i), bbias, B, S, NH, pa, seed, 0, ctx=out_h, key_tiles=plan), attn_f)
+    kbits = ops.attention_keep_bits(B, S, NH, dev) if pa > 0 else None
+    if kbits is not None:
+        ops.attention_fwd(qkvs[0], bbias, B, S, NH, pa, seed, 0, key_tiles=plan, keep_bits=kbits)
+        case("attn fwd         ... storing the keep bits", lambda i: ops.attention_fwd(r(qkvs, i), bbias, B, S, NH, pa, seed, 0, ctx=out_h, key_tiles=plan, keep_bits=kbits), attn_f)
     case("gemm attn-out    [M,768]x[768,768]   bias+dropout+residual",
          lambda i: lib.gemm(r(xs, i), Wo, bias=bo, dropout_p=ph, seed=seed, dropout_stream=1, residual=r(xs, i + 1), out=out_h), gemm_fl(H, H))
     case("ln fwd           [M,768]", lambda i: ops.layernorm_fwd(r(xs, i), gamma, beta, 1e-12, out=out_h), 0, 2.0 * M * H * 2)
@@ -101,6 +105,9 @@ def main():
     case("attn bwd         (prep + dK/dV + dQ)", lambda i: ops.attention_bwd(qkvs[0], bias, ctx0, r(xs, i), lse0, B, S, NH, pa, seed, 0, dqkv=out_q), 2.5 * attn_f)
     case("attn bwd         bench padding, masked key tiles skipped",
          lambda i: ops.attention_bwd(qkvs[0], bbias, ctx1, r(xs, i), lse1, B, S, NH, pa, seed, 0, dqkv=out_q, key_tiles=plan), 2.5 * attn_f)
+    if kbits is not None:
+        case("attn bwd         ... reading the keep bits",
+             lambda i: ops.attention_bwd(qkvs[0], bbias, ctx1, r(xs, i), lse1, B, S, NH, pa, seed, 0, dqkv=out_q, key_tiles=plan, keep_bits=kbits), 2.5 * attn_f)
     case("colsum           [M,2304] (separate kernel, no longer in the step)", lambda i: ops.colsum(r(qkvs, i), gvec[:3 * H]), 0, 1.0 * M * 3 * H * 2)
     case("wgrad qkv        dW[2304,768]", lambda i: lib.gemm(r(qkvs, i), r(xs, i), a_major=1, b_major=1, out=gW[:3 * H * H].view(3 * H, H), accumulate=True), gemm_fl(3 * H, H))
     case("wgrad qkv        + bias gradient", lambda i: lib.gemm(r(qkvs, i), r(xs, i), a_major=1, b_major=1, out=gW[:3 * H * H].view(3 * H, H), accumulate=True, colsum=gvec[:3 * H]), gemm_fl(3 * H, H))
@@ -184,7 +191,7 @@ def main():
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) * 1e3 / args.iters
         # the layer total counts what the step launches: attention with the key-tile plan, the bias gradients inside the wgrad GEMMs
-        skip = (name.startswith("attn") and "skipped" not in name) or "no longer in the step" in name or \
+        skip = (name.startswith("attn") and "keep bits" not in name) or "no longer in the step" in name or \
             name.startswith("wgrad ffn-up     dW") or name.startswith("wgrad qkv        dW")
         tot += us if ci < n_layer and not skip else 0.0
         rate = "%7.0f TFLOP/s" % (fl / us / 1e6) if fl else "%7.0f GB/s   " % (by / us / 1e3)

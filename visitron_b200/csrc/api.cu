@@ -55,6 +55,8 @@ static std::atomic<const uint32_t*> g_seed_source{nullptr};
 static thread_local const int32_t* g_row_limit = nullptr;
 const uint32_t* seed_source() { return g_seed_source.load(std::memory_order_relaxed); }
 const int32_t* row_limit() { return g_row_limit; }
+static thread_local uint32_t* g_keep_bits = nullptr;
+uint32_t* attention_keep_bits() { return g_keep_bits; }
 
 // state[0] += golden ratio; state[1] = splitmix64(state[0]): one thread, first node of a captured step
 __global__ void seed_advance_kernel(unsigned long long* state) {
@@ -71,6 +73,8 @@ extern "C" const char* vt_last_error(void) { return vt::g_err; }
 extern "C" int vt_num_sms(void) { return vt::num_sms(); }
 extern "C" void vt_reserve_sms(int n) { vt::g_reserved_sms.store(n < 0 ? 0 : n); }
 
+extern "C" void vt_set_attention_keep_bits(uint32_t* bits) { vt::g_keep_bits = bits; }
+extern "C" int64_t vt_attention_keep_bits_words(int64_t B, int64_t S, int64_t heads) { return B * heads * 4 * ((S + 127) / 128) * S; }
 extern "C" void vt_set_seed_source(const uint64_t* seed_dev) { vt::g_seed_source.store(reinterpret_cast<const uint32_t*>(seed_dev)); }
 extern "C" void vt_set_row_limit(const int32_t* rows_dev) { vt::g_row_limit = rows_dev; }
 extern "C" int vt_seed_advance(uint64_t* state, vt_stream stream) {

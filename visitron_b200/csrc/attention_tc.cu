@@ -91,6 +91,10 @@ struct AttnTcParams {
   const int* start;    // [B + 1] or null
   const int* row_b;    // [rows_cap] sample of a packed row, -1 for a padding row (backward prep / dQ reduction) or null
   long long rows_cap;  // rows of one dQ workspace slice (B S when dense)
+  // optional keep-bit store of the probability dropout (vt_set_attention_keep_bits): [B * heads][4 * ceil(S / 128) groups][S rows]
+  // words, bit c of word (bh, g, i) = key 32 g + c of query row i was kept.  The forward writes it next to drawing the mask, the
+  // backward reads it instead of running the generator again (16 % of the backward's time at p = 0.1).  null: regenerate.
+  uint32_t* keep_bits;
   int dbg;             // timing ablations only (VT_ATTN_DBG, results are garbage): 1 skip the element-wise arithmetic, 2 skip the exponentials
 };
 
@@ -415,17 +419,21 @@ attn_fwd_tc(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
           const uint32_t thi = dcfg.thresh16 << 16;
 #pragma unroll
           for (int gq = 0; gq < COLS / 32; ++gq) {
+            const uint32_t grp = (uint32_t)(j * 2 + (HV == 2 ? half : gq));
+            uint32_t kept = 0xffffffffu;
 #pragma unroll
             for (uint32_t t = 0; t < 4; ++t) {
-              const uint4 rr = attn_dropout_rand(dcfg, bh, (uint32_t)qi, (uint32_t)(j * 2 + (HV == 2 ? half : gq)), t);
+              const uint4 rr = attn_dropout_rand(dcfg, bh, (uint32_t)qi, grp, t);
               const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
                 const int c0 = 32 * gq + 8 * q + 2 * (int)t;
-                if ((w[q] << 16) < thi) sv[c0] = 0u;
-                if (w[q] < thi) sv[c0 + 1] = 0u;
+                if ((w[q] << 16) < thi) { sv[c0] = 0u; kept &= ~(1u << (8 * q + 2 * (int)t)); }
+                if (w[q] < thi) { sv[c0 + 1] = 0u; kept &= ~(2u << (8 * q + 2 * (int)t)); }
               }
             }
+            // lanes = consecutive rows: one 128-byte store per warp and group
+            if (p.keep_bits && qi < len) p.keep_bits[((size_t)bh * (size_t)(4 * ((S + 127) / 128)) + grp) * (size_t)S + (size_t)qi] = kept;
           }
         }
         if (__any_sync(0xffffffffu, resc)) {
@@ -545,6 +553,8 @@ struct BwdItemCursor {      // loop-invariant inputs (p, nin_max, n_items) are p
   __device__ __forceinline__ void next(const AttnTcParams& p, int nin_max, int n_items) { id += (int)gridDim.x; ++lit; settle(p, nin_max, n_items); }
 };
 
+// BITS = 1: the probability-dropout decisions are read from AttnTcParams::keep_bits (written by the forward) instead of being drawn again
+template <int BITS>
 __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -760,6 +770,8 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
     int n = 0;
     float2 lse_n = make_float2(0.f, 0.f);   // row statistics of the NEXT tile (fetched a tile, and across items an item, ahead)
     float dsum_n = 0.f;
+    uint32_t kw_n = 0u;    // keep bits of this thread's 32 keys in the NEXT tile's row (BITS)
+    const int kb_groups = 4 * nin;
     bf16* pend = nullptr;  // where the dQ partial of pair n - 1 goes (null: row past the end of the sample)
     // mask bias of the item's 128 keys: copied into the other half of sBias one item ahead with cp.async (no register is
     // held across the item and the global-load latency is not exposed at the item boundary)
@@ -786,11 +798,16 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       asm volatile("cp.async.wait_all;" ::: "memory");
       asm volatile("bar.sync 1, %0;" ::"n"(BWD_EW_WARPS * 32) : "memory");  // element-wise warps only
       long long next_stat = -1;        // where the NEXT live item's first-tile row statistics are (bias / statistics run an item ahead)
+      int next_kb = 0;
+      const int kb_off = BITS ? ((int)bh * kb_groups + kt * 4 + cq) * p.S : 0;   // this thread's word column of the keep-bit store
       {
         BwdItemCursor nxt = cur;
         nxt.next(p, nin_max, n_items);
         fetch_bias(nxt, (it + 1) & 1);  // that half was last read in item it - 1, which every warp has left
-        if (nxt.valid(n_items)) next_stat = ((long long)nxt.b * p.heads + nxt.h) * p.S + min(r, nxt.len - 1);
+        if (nxt.valid(n_items)) {
+          next_stat = ((long long)nxt.b * p.heads + nxt.h) * p.S + min(r, nxt.len - 1);
+          if (BITS) next_kb = ((nxt.b * p.heads + nxt.h) * kb_groups + nxt.kt * 4 + cq) * p.S + min(r, nxt.len - 1);
+        }
       }
       const float* bias = sB + cq * 32;
       // this warp's 16 of the 64 dQ columns in this key tile's slice of the workspace
@@ -799,12 +816,14 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         const int gc = min(t * 128 + r, S - 1);
         lse = *reinterpret_cast<const float2*>(p.lse + 2 * (stat_base + gc));
         ds = p.dsum[stat_base + gc];
+        if (BITS) kw_n = __ldg(p.keep_bits + kb_off + gc);
       };
       if (it == 0) load_stats(0, lse_n, dsum_n);   // later items: requested during the previous item's last pair
       for (int t = 0; t < nin; ++t, ++n) {
         const int gi = t * 128 + r;
         const float2 lse = lse_n;
         const float dsp = dsum_n * inv_dscale;
+        const uint32_t kw = kw_n;
         // P = exp2(v log2e - mb) / sum with mb rounded exactly as in the forward (the F6 mask bias of 2.54e6 leaves 0.25 ulp:
         // any other rounding of the reference point would rescale the whole row); rows past the end of the sample get P = dS = 0
         const float mb = lse.x * kLog2e;
@@ -838,7 +857,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
           for (int t2 = 0; t2 < 2; ++t2) {
             const uint32_t tt = (uint32_t)(2 * hf + t2);
             uint4 rr = make_uint4(0u, 0u, 0u, 0u);
-            if (drop) rr = attn_dropout_rand(dcfg, bh, (uint32_t)gi, (uint32_t)(kt * 4 + cq), tt);
+            if (!BITS && drop) rr = attn_dropout_rand(dcfg, bh, (uint32_t)gi, (uint32_t)(kt * 4 + cq), tt);
             const uint32_t w[4] = {rr.x, rr.y, rr.z, rr.w};
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -850,7 +869,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
                 const float v = fmaf(__uint_as_float(sv[ix]), p.scale, bias[cc]);
                 const float x = fmaf(v, kLog2e, -mb);
                 const float pr = (VT_DBG(2) ? x : ex2_approx(x)) * inv;
-                const bool keep = e == 0 ? ((w[q] << 16) >= thi) : (w[q] >= thi);
+                const bool keep = BITS ? ((kw >> cc) & 1u) != 0u : (e == 0 ? ((w[q] << 16) >= thi) : (w[q] >= thi));
                 const float dpm = keep ? __uint_as_float(dv[ix]) : 0.f;
                 pe[e] = keep ? pr : 0.f;
                 de[e] = pr * (dpm - dsp);
@@ -868,6 +887,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
           const long long sb2 = next_stat;
           lse_n = *reinterpret_cast<const float2*>(p.lse + 2 * sb2);
           dsum_n = p.dsum[sb2];
+          if (BITS) kw_n = __ldg(p.keep_bits + next_kb);
         }
         if (n > 0) mbar_wait(pds_free, (uint32_t)((n - 1) & 1));
 #pragma unroll
@@ -1008,6 +1028,7 @@ static int attention_fwd_impl(const void* qkv, int64_t ld, const float* bias, co
   p.start = (const int*)start; p.rows_cap = rows;
   p.bias = bias; p.key_tiles = key_tiles; p.scale = 0.125f; p.out = (bf16*)ctx; p.lse = lse; p.ld = ld;
   p.drop = make_dropout(dropout_p, seed, dropout_stream);
+  p.keep_bits = p.drop.thresh16 ? attention_keep_bits() : nullptr;
   p.dbg = attn_dbg();
   const int nkt = (int)((S + FK - 1) / FK);
   const size_t smem = 1024 + FWD_SMEM_TILES + 256 + 3072 + (size_t)nkt * FK * sizeof(float);
@@ -1092,12 +1113,16 @@ static int attention_bwd_impl(const void* qkv, int64_t ld, const float* bias, co
   const size_t smem = 1024 + BWD_SMEM_TILES + 256 + 2 * 128 * sizeof(float);
   static bool attr = false;
   if (!attr) {
-    VT_CUDA(cudaFuncSetAttribute(attn_bwd_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(1024 + BWD_SMEM_TILES + 256 + 1024)));
+    VT_CUDA(cudaFuncSetAttribute(attn_bwd_fused<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(1024 + BWD_SMEM_TILES + 256 + 1024)));
+    VT_CUDA(cudaFuncSetAttribute(attn_bwd_fused<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(1024 + BWD_SMEM_TILES + 256 + 1024)));
     attr = true;
   }
   const long long n_items = (long long)nt * heads * B;
   const int sms = usable_sms();  // leaves the SMs of an overlapped gradient exchange alone (vt_reserve_sms)
-  launch_pdl(attn_bwd_fused, (unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st, tq, tdo, p);
+  p.keep_bits = p.drop.thresh16 ? attention_keep_bits() : nullptr;
+  VT_REQUIRE(!p.keep_bits || B * heads * 4 * nt * S < (1ll << 31), "vt_attention_bwd: keep-bit store too large for 32-bit word offsets");
+  if (p.keep_bits) launch_pdl(attn_bwd_fused<1>, (unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st, tq, tdo, p);
+  else launch_pdl(attn_bwd_fused<0>, (unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st, tq, tdo, p);
   const long long rows = rows_all;
   const long long items = rows * (hidden / 8);
   launch_pdl(attn_dq_reduce_kernel, (unsigned)((items + 255) / 256), 256, 0, st, p.dq_ws, rows * hidden, nt, rows, (int)hidden,

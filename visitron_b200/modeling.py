@@ -487,7 +487,10 @@ def _encoder_layers_forward(step: _Step, st: FlatStore, x, save):
         if step.hidden is not None:
             step.hidden.append(x)
         qkv = lib.gemm(x, st.wb(p + "attention.self.query.weight", 3 * H, H), bias=st.wspan(p + "attention.self.query.bias", 3 * H))
-        ctx, lse = ops.attention_fwd(qkv, step.bias, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles, plan=step.plan)
+        # the probability dropout's keep decisions are stored (1 bit each) for the backward, which then does not draw them again
+        bits = ops.attention_keep_bits(B, S, nh, dev) if (save and step.p_attn > 0) else None
+        ctx, lse = ops.attention_fwd(qkv, step.bias, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles, plan=step.plan,
+                                     keep_bits=bits)
         x1 = lib.gemm(ctx, st.wb(p + "attention.output.dense.weight"), bias=st.w(p + "attention.output.dense.bias"),
                       dropout_p=step.p_hidden, seed=step.seed, dropout_stream=4 * l + 1, residual=x)
         y1 = ops.layernorm_fwd(x1, st.w(p + "attention.output.LayerNorm.weight"), st.w(p + "attention.output.LayerNorm.bias"), eps)
@@ -500,7 +503,7 @@ def _encoder_layers_forward(step: _Step, st: FlatStore, x, save):
                       dropout_p=step.p_hidden, seed=step.seed, dropout_stream=4 * l + 2, residual=y1)
         y2 = ops.layernorm_fwd(x2, st.w(p + "output.LayerNorm.weight"), st.w(p + "output.LayerNorm.bias"), eps)
         if save:
-            step.layers.append((x, qkv, ctx, lse, x1, y1, pre, z, x2))
+            step.layers.append((x, qkv, ctx, lse, x1, y1, pre, z, x2, bits))
         x = y2
     return x
 
@@ -570,7 +573,7 @@ def _encoder_layers_backward(step: _Step, st: FlatStore, d):
     red = model._vt_reducer
     for l in reversed(range(cfg.num_hidden_layers)):
         p = "encoder.layer.%d." % l
-        x_in, qkv, ctx, lse, x1, y1, pre, z, x2 = step.layers[l]
+        x_in, qkv, ctx, lse, x1, y1, pre, z, x2, bits = step.layers[l]
         step.layers[l] = None
         ph = step.p_hidden
         # LN2 and the FFN
@@ -590,7 +593,8 @@ def _encoder_layers_backward(step: _Step, st: FlatStore, d):
                                       st.g(p + "attention.output.dense.bias"), out_dropout_p=ph, out_stream=4 * l + 1, seed=step.seed)
         lib.gemm(dx1d, ctx, a_major=1, b_major=1, out=st.g(p + "attention.output.dense.weight"), accumulate=True)
         dctx = lib.gemm(dx1d, st.wb(p + "attention.output.dense.weight"), b_major=1)
-        dqkv = ops.attention_bwd(qkv, step.bias, ctx, dctx, lse, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles, plan=step.plan)
+        dqkv = ops.attention_bwd(qkv, step.bias, ctx, dctx, lse, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles, plan=step.plan,
+                                 keep_bits=bits)
         lib.gemm(dqkv, x_in, a_major=1, b_major=1, out=st.g(p + "attention.self.query.weight", 3 * H, H), accumulate=True,
                  colsum=st.g(p + "attention.self.query.bias", 3 * H))
         d = lib.gemm(dqkv, st.wb(p + "attention.self.query.weight", 3 * H, H), b_major=1, residual=dx1)

@@ -193,36 +193,63 @@ def zero_pad_rows(buf, counts):
     return buf
 
 
-def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None, key_tiles=None, plan: Optional[PackPlan] = None):
+def attention_keep_bits(B, S, heads, device):
+    """Store for the keep decisions of one attention call's probability dropout (see vt_set_attention_keep_bits): pass it to
+    attention_fwd (which fills it) and to the matching attention_bwd (which then skips the generator)."""
+    return torch.empty(int(init().vt_attention_keep_bits_words(B, S, heads)), device=device, dtype=torch.int32)
+
+
+class _keep_bits:
+    def __init__(self, bits):
+        self.bits = bits
+
+    def __enter__(self):
+        if self.bits is not None:
+            init().vt_set_attention_keep_bits(self.bits.data_ptr())
+
+    def __exit__(self, *exc):
+        if self.bits is not None:
+            init().vt_set_attention_keep_bits(None)
+        return False
+
+
+def attention_fwd(qkv, bias, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, ctx=None, key_tiles=None, plan: Optional[PackPlan] = None,
+                  keep_bits=None):
     L = init()
+    if keep_bits is not None and keep_bits.numel() < int(L.vt_attention_keep_bits_words(B, S, heads)):
+        raise lib.VtError("keep_bits: too small, see attention_keep_bits")
     rows = B * S if plan is None else plan.cap
     if ctx is None:
         ctx = torch.empty((rows, heads * 64), device=qkv.device, dtype=BF16)
     lse = torch.empty((B, heads, S, 2), device=qkv.device, dtype=F32)
-    if plan is None:
-        check(L.vt_attention_fwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(key_tiles), B, S, heads, 64, ptr(ctx), ptr(lse), dropout_p, seed, stream_id,
-                                 stream_ptr()), "vt_attention_fwd")
-    else:
-        check(L.vt_attention_fwd_packed(ptr(qkv), qkv.stride(0), ptr(plan.bias), ptr(plan.key_tiles), ptr(plan.start), plan.cap, B, S, heads, 64,
-                                        ptr(ctx), ptr(lse), dropout_p, seed, stream_id, stream_ptr()), "vt_attention_fwd_packed")
+    with _keep_bits(keep_bits):
+        if plan is None:
+            check(L.vt_attention_fwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(key_tiles), B, S, heads, 64, ptr(ctx), ptr(lse), dropout_p, seed, stream_id,
+                                     stream_ptr()), "vt_attention_fwd")
+        else:
+            check(L.vt_attention_fwd_packed(ptr(qkv), qkv.stride(0), ptr(plan.bias), ptr(plan.key_tiles), ptr(plan.start), plan.cap, B, S, heads, 64,
+                                            ptr(ctx), ptr(lse), dropout_p, seed, stream_id, stream_ptr()), "vt_attention_fwd_packed")
+    if plan is not None:
         zero_pad_rows(ctx, plan.counts)
     return ctx, lse
 
 
 def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0, stream_id=0, dqkv=None, key_tiles=None,
-                  plan: Optional[PackPlan] = None):
+                  plan: Optional[PackPlan] = None, keep_bits=None):
     L = init()
     if dqkv is None:
         dqkv = torch.empty_like(qkv)
-    if plan is None:
-        ws = torch.empty(int(L.vt_attention_bwd_workspace(B, S, heads)), device=qkv.device, dtype=F32)
-        check(L.vt_attention_bwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(key_tiles), ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv),
-                                 dropout_p, seed, stream_id, stream_ptr()), "vt_attention_bwd")
-    else:
-        ws = torch.empty(int(L.vt_attention_bwd_workspace_packed(plan.cap, B, S, heads)), device=qkv.device, dtype=F32)
-        check(L.vt_attention_bwd_packed(ptr(qkv), qkv.stride(0), ptr(plan.bias), ptr(plan.key_tiles), ptr(plan.start), ptr(plan.row_b), plan.cap,
-                                        ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv), dropout_p, seed, stream_id, stream_ptr()),
-              "vt_attention_bwd_packed")
+    with _keep_bits(keep_bits):
+        if plan is None:
+            ws = torch.empty(int(L.vt_attention_bwd_workspace(B, S, heads)), device=qkv.device, dtype=F32)
+            check(L.vt_attention_bwd(ptr(qkv), qkv.stride(0), ptr(bias), ptr(key_tiles), ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv),
+                                     dropout_p, seed, stream_id, stream_ptr()), "vt_attention_bwd")
+        else:
+            ws = torch.empty(int(L.vt_attention_bwd_workspace_packed(plan.cap, B, S, heads)), device=qkv.device, dtype=F32)
+            check(L.vt_attention_bwd_packed(ptr(qkv), qkv.stride(0), ptr(plan.bias), ptr(plan.key_tiles), ptr(plan.start), ptr(plan.row_b), plan.cap,
+                                            ptr(ctx), ptr(dctx), ptr(lse), ptr(ws), B, S, heads, 64, ptr(dqkv), dropout_p, seed, stream_id, stream_ptr()),
+                  "vt_attention_bwd_packed")
+    if plan is not None:
         zero_pad_rows(dqkv, plan.counts)
     return dqkv
 
