@@ -833,6 +833,63 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         // Two halves of 16 columns, chosen to match the dropout counter layout (half hf = Philox calls 2 hf and 2 hf + 1 =
         // columns 8 q + 4 hf .. + 3 of each 8-column chunk q): only 16 + 16 accumulator values are live at a time, and the
         // first half is already packed to bf16 when the second is loaded (the whole tile at once needed > 96 registers).
+        if constexpr (BITS) {
+          // Without the generator there is no counter layout to follow: 8-column chunks (one 16-byte row piece of the staged P / dS
+          // each), all four chunks' loads in flight before the second is needed, every chunk staged as soon as it is computed
+          // (16 packed registers never accumulate), so the only exposed TMEM round trip of the pair is the first.
+          uint32_t sv[4][8], dv[4][8];
+          auto ld_chunk = [&](int q) {
+            tmem_ld_32x8(lane_addr + cq * 32 + 8 * q, sv[q]);
+            tmem_ld_32x8(lane_addr + 128 + cq * 32 + 8 * q, dv[q]);
+          };
+          ld_chunk(0);
+          ld_chunk(1);
+          tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (q < 2) ld_chunk(q + 2);
+            if (q == 2) {
+              tmem_ld_wait();
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(sdp_free);
+            }
+            uint32_t pp[4], dd[4];
+#pragma unroll
+            for (int j2 = 0; j2 < 4; ++j2) {
+              float pe[2], de[2];
+#pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                const int cc = 8 * q + 2 * j2 + e;     // column within the warp's 32
+                const int ix = 2 * j2 + e;
+                const float v = fmaf(__uint_as_float(sv[q][ix]), p.scale, bias[cc]);
+                const float x = fmaf(v, kLog2e, -mb);
+                const float pr = (VT_DBG(2) ? x : ex2_approx(x)) * inv;
+                const bool keep = ((kw >> cc) & 1u) != 0u;
+                const float dpm = keep ? __uint_as_float(dv[q][ix]) : 0.f;
+                pe[e] = keep ? pr : 0.f;
+                de[e] = pr * (dpm - dsp);
+              }
+              pp[j2] = pack_bf16(pe[0], pe[1]);
+              dd[j2] = pack_bf16(de[0], de[1]);
+            }
+            if (q == 0) {
+              // next tile's statistics (see below), requested as early as their registers are free
+              if (t + 1 < nin) {
+                load_stats(t + 1, lse_n, dsum_n);
+              } else if (next_stat >= 0) {
+                const long long sb2 = next_stat;
+                lse_n = *reinterpret_cast<const float2*>(p.lse + 2 * sb2);
+                dsum_n = p.dsum[sb2];
+                kw_n = __ldg(p.keep_bits + next_kb);
+              }
+              if (n > 0) mbar_wait(pds_free, (uint32_t)((n - 1) & 1));
+            }
+            const uint32_t off = st_off + (((ch0 + (uint32_t)q) ^ (uint32_t)(r & 7)) << 4);
+            st_shared_v4(sDS + off, dd[0], dd[1], dd[2], dd[3]);
+            st_shared_v4(sPD + off, pp[0], pp[1], pp[2], pp[3]);
+          }
+        } else {
         uint32_t pk_p[2][8], pk_d[2][8];   // [half][2 q + (0: columns +0,+1 | 1: columns +2,+3)]
 #pragma unroll
         for (int hf = 0; hf < 2; ++hf) {
@@ -896,6 +953,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
           st_shared_v4(sDS + off, pk_d[0][2 * ch], pk_d[0][2 * ch + 1], pk_d[1][2 * ch], pk_d[1][2 * ch + 1]);
           st_shared_v4(sPD + off, pk_p[0][2 * ch], pk_p[0][2 * ch + 1], pk_p[1][2 * ch], pk_p[1][2 * ch + 1]);
         }
+        }   // !BITS
         fence_proxy_async();
         tc_fence_before();
         __syncwarp();
