@@ -105,6 +105,21 @@ def main():
     case("attn bwd         (prep + dK/dV + dQ)", lambda i: ops.attention_bwd(qkvs[0], bias, ctx0, r(xs, i), lse0, B, S, NH, pa, seed, 0, dqkv=out_q), 2.5 * attn_f)
     case("attn bwd         bench padding, masked key tiles skipped",
          lambda i: ops.attention_bwd(qkvs[0], bbias, ctx1, r(xs, i), lse1, B, S, NH, pa, seed, 0, dqkv=out_q, key_tiles=plan), 2.5 * attn_f)
+    # the step's own layout: packed rows (the padding rows of the bench batch dropped), keep bits stored / read
+    pplan = ops.pack_plan(bbias, None, None, B, S)
+    n_rows = int(pplan.counts[1])
+    lens_p = (pplan.start[1:] - pplan.start[:-1]).double()
+    attn_fp = float(4.0 * NH * 64 * (lens_p * lens_p).sum())
+    qkv_pk = torch.zeros(pplan.cap, 3 * H, dtype=BF16, device=dev)
+    qkv_pk[:n_rows] = qkvs[0][pplan.row_src[:n_rows].long()]
+    dctx_pk = torch.zeros(pplan.cap, H, dtype=BF16, device=dev)
+    dctx_pk[:n_rows] = xs[0][pplan.row_src[:n_rows].long()]
+    ctx_pk, lse_pk = ops.attention_fwd(qkv_pk, None, B, S, NH, pa, seed, 0, plan=pplan, keep_bits=kbits)
+    dq_pk = torch.empty_like(qkv_pk)
+    case("attn fwd         packed rows (%d of %d), keep bits stored" % (n_rows, M),
+         lambda i: ops.attention_fwd(qkv_pk, None, B, S, NH, pa, seed, 0, ctx=ctx_pk, plan=pplan, keep_bits=kbits), attn_fp)
+    case("attn bwd         packed rows, keep bits read",
+         lambda i: ops.attention_bwd(qkv_pk, None, ctx_pk, dctx_pk, lse_pk, B, S, NH, pa, seed, 0, dqkv=dq_pk, plan=pplan, keep_bits=kbits), 2.5 * attn_fp)
     if kbits is not None:
         case("attn bwd         ... reading the keep bits",
              lambda i: ops.attention_bwd(qkvs[0], bbias, ctx1, r(xs, i), lse1, B, S, NH, pa, seed, 0, dqkv=out_q, key_tiles=plan, keep_bits=kbits), 2.5 * attn_f)
@@ -191,7 +206,7 @@ def main():
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) * 1e3 / args.iters
         # the layer total counts what the step launches: attention with the key-tile plan, the bias gradients inside the wgrad GEMMs
-        skip = (name.startswith("attn") and "keep bits" not in name) or "no longer in the step" in name or \
+        skip = (name.startswith("attn") and "packed rows" not in name) or "no longer in the step" in name or \
             name.startswith("wgrad ffn-up     dW") or name.startswith("wgrad qkv        dW")
         tot += us if ci < n_layer and not skip else 0.0
         rate = "%7.0f TFLOP/s" % (fl / us / 1e6) if fl else "%7.0f GB/s   " % (by / us / 1e3)

@@ -553,7 +553,12 @@ struct BwdItemCursor {      // loop-invariant inputs (p, nin_max, n_items) are p
   __device__ __forceinline__ void next(const AttnTcParams& p, int nin_max, int n_items) { id += (int)gridDim.x; ++lit; settle(p, nin_max, n_items); }
 };
 
-// BITS = 1: the probability-dropout decisions are read from AttnTcParams::keep_bits (written by the forward) instead of being drawn again
+// BITS = 1: the probability-dropout decisions are read from AttnTcParams::keep_bits (written by the forward) instead of being drawn
+// again; also the variant for dropout_p == 0 (keep_bits null: every bit set).  BITS = 0 draws them with the counter generator.
+// Tried on this variant and measured slower or equal, not kept (same-box A/B, tools/r2_call19.sh / r2_call20.sh): draining the dQ
+// partial at the top of the pair two pairs behind (412 vs 397 us), staging chunk 0 behind chunk 1 (no change), skipping the
+// arithmetic of key groups past a packed sample's end (305 -> 302 us), and in the forward letting the warps whose rows lie past the
+// sample's end only keep the barrier protocol (165 -> 188 us: the polling warps take more issue slots than the arithmetic did).
 template <int BITS>
 __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
@@ -770,7 +775,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
     int n = 0;
     float2 lse_n = make_float2(0.f, 0.f);   // row statistics of the NEXT tile (fetched a tile, and across items an item, ahead)
     float dsum_n = 0.f;
-    uint32_t kw_n = 0u;    // keep bits of this thread's 32 keys in the NEXT tile's row (BITS)
+    uint32_t kw_n = 0xffffffffu;    // keep bits of this thread's 32 keys in the NEXT tile's row (BITS; all ones without dropout)
     const int kb_groups = 4 * nin;
     bf16* pend = nullptr;  // where the dQ partial of pair n - 1 goes (null: row past the end of the sample)
     // mask bias of the item's 128 keys: copied into the other half of sBias one item ahead with cp.async (no register is
@@ -816,7 +821,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         const int gc = min(t * 128 + r, S - 1);
         lse = *reinterpret_cast<const float2*>(p.lse + 2 * (stat_base + gc));
         ds = p.dsum[stat_base + gc];
-        if (BITS) kw_n = __ldg(p.keep_bits + kb_off + gc);
+        if (BITS && p.keep_bits) kw_n = __ldg(p.keep_bits + kb_off + gc);
       };
       if (it == 0) load_stats(0, lse_n, dsum_n);   // later items: requested during the previous item's last pair
       for (int t = 0; t < nin; ++t, ++n) {
@@ -881,7 +886,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
                 const long long sb2 = next_stat;
                 lse_n = *reinterpret_cast<const float2*>(p.lse + 2 * sb2);
                 dsum_n = p.dsum[sb2];
-                kw_n = __ldg(p.keep_bits + next_kb);
+                if (p.keep_bits) kw_n = __ldg(p.keep_bits + next_kb);
               }
               if (n > 0) mbar_wait(pds_free, (uint32_t)((n - 1) & 1));
             }
@@ -1179,7 +1184,7 @@ static int attention_bwd_impl(const void* qkv, int64_t ld, const float* bias, co
   const int sms = usable_sms();  // leaves the SMs of an overlapped gradient exchange alone (vt_reserve_sms)
   p.keep_bits = p.drop.thresh16 ? attention_keep_bits() : nullptr;
   VT_REQUIRE(!p.keep_bits || B * heads * 4 * nt * S < (1ll << 31), "vt_attention_bwd: keep-bit store too large for 32-bit word offsets");
-  if (p.keep_bits) launch_pdl(attn_bwd_fused<1>, (unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st, tq, tdo, p);
+  if (p.keep_bits || !p.drop.thresh16) launch_pdl(attn_bwd_fused<1>, (unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st, tq, tdo, p);
   else launch_pdl(attn_bwd_fused<0>, (unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st, tq, tdo, p);
   const long long rows = rows_all;
   const long long items = rows * (hidden / 8);
