@@ -67,6 +67,14 @@ void vt_set_row_limit(const int32_t* rows_dev /* device int32[2] = {rows padded 
  * mask either way (the bits ARE the generator's output); NULL (the default) regenerates.  vt_attention_keep_bits_words = words. */
 void vt_set_attention_keep_bits(uint32_t* bits);
 int64_t vt_attention_keep_bits_words(int64_t B, int64_t S, int64_t heads);
+/* Item schedule of the persistent attention backward on packed rows: with samples of different lengths a (key tile, head, sample)
+ * item costs its sample's number of query tiles, and round-robin assignment leaves the busiest CTA ~30 % over the mean.
+ * vt_attention_bwd_schedule writes int32 sched[ctas + 1], ctas = vt_attention_bwd_schedule_ctas(B, S, heads): CTA i works on the
+ * items [sched[i], sched[i + 1]) -- contiguous ranges of equal total cost -- from the device-resident sample starts (no host sync).
+ * While set ON THE CALLING THREAD, vt_attention_bwd_packed follows it (ignored if its grid differs from `ctas`); NULL: round-robin. */
+int64_t vt_attention_bwd_schedule_ctas(int64_t B, int64_t S, int64_t heads);
+int vt_attention_bwd_schedule(const int32_t* start, int64_t B, int64_t S, int64_t heads, int32_t* sched, vt_stream stream);
+void vt_set_attention_bwd_schedule(const int32_t* sched, int64_t ctas);
 /* Compaction of the labelled rows (replaces torch.nonzero(labels != -1) + labels[idx] in front of the MLM / token heads,
  * vs/encoder.py:387-389,381-385, whose data-dependent sizes cost a sync per step).  For each of the two label arrays
  * (int64 [n]; either may be NULL): idx[r] / lab[r] = position / label of the r-th label != ignore_index in ascending order

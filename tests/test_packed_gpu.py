@@ -94,6 +94,27 @@ def test_packed_attention_equals_dense_attention(B, S, heads, p):
     assert bool((dqkv_p[n:int(pl.counts[0])] == 0).all())
 
 
+@pytest.mark.parametrize("B,S,heads", [(32, 767, 12), (3, 300, 2), (1, 64, 1), (200, 129, 4)])
+def test_attention_backward_schedule_balances_the_ctas(B, S, heads):
+    """vt_attention_bwd_schedule: contiguous item ranges, every item exactly once, the busiest CTA within one item of the mean."""
+    g = torch.Generator().manual_seed(B + S)
+    lens = torch.randint(1, S + 1, (B,), generator=g)
+    start = torch.cat([torch.zeros(1, dtype=torch.long), lens.cumsum(0)]).to(torch.int32).to(DEV)
+    L = lib.init()
+    ctas = int(L.vt_attention_bwd_schedule_ctas(B, S, heads))
+    sched = torch.full((ctas + 1,), -7, device=DEV, dtype=torch.int32)
+    lib.check(L.vt_attention_bwd_schedule(start.data_ptr(), B, S, heads, sched.data_ptr(), lib.stream_ptr()), "vt_attention_bwd_schedule")
+    sc = sched.cpu().tolist()
+    nin = (S + 127) // 128
+    n_items = nin * heads * B
+    assert sc[0] == 0 and sc[-1] == n_items and all(a <= b for a, b in zip(sc, sc[1:]))
+    nt = ((lens + 127) // 128).tolist()
+    cost = [(nt[i // (nin * heads)] + 1) if (i % nin) < nt[i // (nin * heads)] else 0 for i in range(n_items)]
+    per = [sum(cost[a:b]) for a, b in zip(sc, sc[1:])]
+    assert sum(per) == sum(cost)
+    assert max(per) <= sum(cost) / ctas + max(cost) + 1, (max(per), sum(cost) / ctas)
+
+
 def _model(layers=2, dropout=0.0):
     oc = vo.OracleConfig(vocab_size=2048, num_hidden_layers=layers, max_position_embeddings=64, detector_classes=96,
                          hidden_dropout_prob=dropout, attention_probs_dropout_prob=dropout / 3)

@@ -57,6 +57,9 @@ const uint32_t* seed_source() { return g_seed_source.load(std::memory_order_rela
 const int32_t* row_limit() { return g_row_limit; }
 static thread_local uint32_t* g_keep_bits = nullptr;
 uint32_t* attention_keep_bits() { return g_keep_bits; }
+static thread_local const int32_t* g_bwd_sched = nullptr;
+static thread_local int g_bwd_sched_ctas = 0;
+const int32_t* attention_bwd_schedule(int* ctas) { *ctas = g_bwd_sched_ctas; return g_bwd_sched; }
 
 // state[0] += golden ratio; state[1] = splitmix64(state[0]): one thread, first node of a captured step
 __global__ void seed_advance_kernel(unsigned long long* state) {
@@ -73,6 +76,7 @@ extern "C" const char* vt_last_error(void) { return vt::g_err; }
 extern "C" int vt_num_sms(void) { return vt::num_sms(); }
 extern "C" void vt_reserve_sms(int n) { vt::g_reserved_sms.store(n < 0 ? 0 : n); }
 
+extern "C" void vt_set_attention_bwd_schedule(const int32_t* sched, int64_t ctas) { vt::g_bwd_sched = sched; vt::g_bwd_sched_ctas = sched ? (int)ctas : 0; }
 extern "C" void vt_set_attention_keep_bits(uint32_t* bits) { vt::g_keep_bits = bits; }
 extern "C" int64_t vt_attention_keep_bits_words(int64_t B, int64_t S, int64_t heads) { return B * heads * 4 * ((S + 127) / 128) * S; }
 extern "C" void vt_set_seed_source(const uint64_t* seed_dev) { vt::g_seed_source.store(reinterpret_cast<const uint32_t*>(seed_dev)); }

@@ -95,6 +95,7 @@ struct AttnTcParams {
   // words, bit c of word (bh, g, i) = key 32 g + c of query row i was kept.  The forward writes it next to drawing the mask, the
   // backward reads it instead of running the generator again (16 % of the backward's time at p = 0.1).  null: regenerate.
   uint32_t* keep_bits;
+  const int* sched;    // backward: [ctas + 1] item ranges of the CTAs (vt_attention_bwd_schedule) or null = round-robin
   int dbg;             // timing ablations only (VT_ATTN_DBG, results are garbage): 1 skip the element-wise arithmetic, 2 skip the exponentials
 };
 
@@ -537,20 +538,20 @@ struct BwdItemCursor {      // loop-invariant inputs (p, nin_max, n_items) are p
   int id, lit;
   int kt, h, b, sb, len, nin;
   __device__ __forceinline__ bool valid(int n_items) const { return id < n_items; }
-  __device__ __forceinline__ void settle(const AttnTcParams& p, int nin_max, int n_items) {     // moves to the first non-empty item at or after id
+  __device__ __forceinline__ void settle(const AttnTcParams& p, int nin_max, int n_items, int step) {     // moves to the first non-empty item at or after id
     while (id < n_items) {
       kt = id % nin_max; h = (id / nin_max) % p.heads; b = id / (nin_max * p.heads);
       sb = p.start ? __ldg(p.start + b) : b * p.S;
       len = p.start ? __ldg(p.start + b + 1) - sb : p.S;
       if (kt * 128 < len) { nin = (len + 127) / 128; return; }
-      id += (int)gridDim.x;
+      id += step;
     }
   }
-  __device__ __forceinline__ void init(const AttnTcParams& p, int nin_max, int n_items) {
-    id = (int)blockIdx.x; lit = 0;
-    settle(p, nin_max, n_items);
+  __device__ __forceinline__ void init(const AttnTcParams& p, int nin_max, int n_items, int begin, int step) {
+    id = begin; lit = 0;
+    settle(p, nin_max, n_items, step);
   }
-  __device__ __forceinline__ void next(const AttnTcParams& p, int nin_max, int n_items) { id += (int)gridDim.x; ++lit; settle(p, nin_max, n_items); }
+  __device__ __forceinline__ void next(const AttnTcParams& p, int nin_max, int n_items, int step) { id += step; ++lit; settle(p, nin_max, n_items, step); }
 };
 
 // BITS = 1: the probability-dropout decisions are read from AttnTcParams::keep_bits (written by the forward) instead of being drawn
@@ -579,7 +580,10 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
   const int lane = threadIdx.x & 31;
   const int nin = (p.S + 127) / 128;     // key / query tiles of a full-length sample (the item numbering's bound)
   const int hid = p.hidden;
-  const int n_items = nin * p.heads * p.B;
+  // This CTA's items: round-robin over the grid, or -- with a schedule (vt_attention_bwd_schedule: packed rows, where a sample's
+  // items cost its own number of query tiles) -- the contiguous range [sched[cta], sched[cta + 1]) of equal total cost.  Below,
+  // n_items is the END of the CTA's range.
+  int n_items = nin * p.heads * p.B, it_begin = (int)blockIdx.x, it_step = (int)gridDim.x;   // (the schedule is read behind pdl_sync)
 
   if (warp == BWD_EW_WARPS && lane == 0) {
     prefetch_tensormap(&tmQKV);
@@ -604,6 +608,11 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   pdl_sync();   // the prologue above overlapped the tail of the previous kernel; global memory is touched only below
+  if (p.sched) {
+    it_begin = __ldg(p.sched + blockIdx.x);
+    n_items = __ldg(p.sched + blockIdx.x + 1);
+    it_step = 1;
+  }
   const uint32_t tmem_base = *tmem_slot_ptr;
 
   if (warp == BWD_EW_WARPS) {
@@ -611,7 +620,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
     if (lane == 0) {
       int n = 0;
       BwdItemCursor c;
-      for (c.init(p, nin, n_items); c.valid(n_items); c.next(p, nin, n_items)) {
+      for (c.init(p, nin, n_items, it_begin, it_step); c.valid(n_items); c.next(p, nin, n_items, it_step)) {
         const int kt = c.kt, h = c.h, it = c.lit;
         const int row_base = c.sb, kvb = it & 1;
         if (it >= 2) mbar_wait_backoff(kv_empty + 8 * kvb, (uint32_t)(((it >> 1) - 1) & 1), 64);
@@ -650,7 +659,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
         umma_commit(sdp_full);
       };
       BwdItemCursor cur, nxt;
-      cur.init(p, nin, n_items);
+      cur.init(p, nin, n_items, it_begin, it_step);
       nxt = cur;
       int t = 0, t_nxt = 0;     // query tile of pair n / of pair n + 1
       if (cur.valid(n_items)) {
@@ -662,7 +671,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       for (int n = 0; cur.valid(n_items); ++n) {
         const int it = cur.lit, kvb = it & 1;
         // advance the look-ahead cursor to pair n + 1
-        if (++t_nxt == nxt.nin) { nxt.next(p, nin, n_items); t_nxt = 0; }
+        if (++t_nxt == nxt.nin) { nxt.next(p, nin, n_items, it_step); t_nxt = 0; }
         if (nxt.valid(n_items)) {
           const int it1 = nxt.lit;
           if (t_nxt == 0) mbar_wait_backoff(kv_full + 8 * (it1 & 1), (uint32_t)((it1 >> 1) & 1), MMA_POLL_NS);
@@ -789,10 +798,10 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       }
     };
     BwdItemCursor cur;
-    cur.init(p, nin, n_items);
+    cur.init(p, nin, n_items, it_begin, it_step);
     fetch_bias(cur, 0);
     const int nin_max = nin;
-    for (; cur.valid(n_items); cur.next(p, nin_max, n_items)) {
+    for (; cur.valid(n_items); cur.next(p, nin_max, n_items, it_step)) {
       const int kt = cur.kt, h = cur.h, b = cur.b, it = cur.lit;
       const int S = cur.len;         // everything below is bounded by the SAMPLE's length (== p.S in the dense layout)
       const int nin = cur.nin;
@@ -807,7 +816,7 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
       const int kb_off = BITS ? ((int)bh * kb_groups + kt * 4 + cq) * p.S : 0;   // this thread's word column of the keep-bit store
       {
         BwdItemCursor nxt = cur;
-        nxt.next(p, nin_max, n_items);
+        nxt.next(p, nin_max, n_items, it_step);
         fetch_bias(nxt, (it + 1) & 1);  // that half was last read in item it - 1, which every warp has left
         if (nxt.valid(n_items)) {
           next_stat = ((long long)nxt.b * p.heads + nxt.h) * p.S + min(r, nxt.len - 1);
@@ -981,6 +990,41 @@ attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant_
   tc_fence_before();
   __syncthreads();
   if (warp == BWD_EW_WARPS + 1) tmem_dealloc(tmem_base, BWD_TMEM_COLS);
+}
+
+// Cost-balanced item ranges for the persistent backward on packed rows.  Item (key tile kt, head h, sample b) costs the sample's
+// number of query tiles (+ 1 for the item switch) when kt lies inside the sample and nothing otherwise; round-robin assignment
+// left the busiest CTA 31 % over the mean on the benchmark's batch (lengths 389 .. 686).  CTA i gets the items whose cost
+// prefix lies in [i, i + 1) * total / ctas: sched[i] = first item id (ids as in BwdItemCursor), sched[ctas] = all items.
+__global__ void __launch_bounds__(256)
+attn_bwd_schedule_kernel(const int* __restrict__ start, int B, int S, int heads, int ctas, int* __restrict__ sched) {
+  extern __shared__ long long pre[];   // [B + 1] cost prefix over samples
+  const int nin = (S + 127) / 128;
+  if (threadIdx.x == 0) {
+    long long acc = 0;
+    pre[0] = 0;
+    for (int b = 0; b < B; ++b) {
+      const int nt = (start[b + 1] - start[b] + 127) / 128;
+      acc += (long long)heads * nt * (nt + 1);
+      pre[b + 1] = acc;
+    }
+  }
+  __syncthreads();
+  const long long total = pre[B];
+  for (int i = threadIdx.x; i <= ctas; i += blockDim.x) {
+    if (i == ctas || total == 0) { sched[i] = i == ctas ? nin * heads * B : 0; continue; }
+    const long long T = total * i / ctas;
+    int lo = 0, hi = B;            // the sample with pre[b] <= T < pre[b + 1]
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (pre[mid] <= T) lo = mid; else hi = mid;
+    }
+    while (lo + 1 < B && pre[lo + 1] <= T) ++lo;   // samples without items (never with [CLS] kept, but cheap)
+    const int nt = (start[lo + 1] - start[lo] + 127) / 128;
+    int k = nt > 0 ? (int)((T - pre[lo]) / (nt + 1)) : 0;   // live item of the sample, numbered h * nt + kt
+    if (nt > 0 && k >= heads * nt) k = heads * nt - 1;
+    sched[i] = nt > 0 ? (lo * heads + k / nt) * nin + k % nt : lo * heads * nin;
+  }
 }
 
 // dQ[row, c] = factor * sum over key tiles of the workspace slices, in key-tile order (deterministic) -> bf16 into dqkv[:, 0:hidden]
@@ -1184,6 +1228,11 @@ static int attention_bwd_impl(const void* qkv, int64_t ld, const float* bias, co
   const int sms = usable_sms();  // leaves the SMs of an overlapped gradient exchange alone (vt_reserve_sms)
   p.keep_bits = p.drop.thresh16 ? attention_keep_bits() : nullptr;
   VT_REQUIRE(!p.keep_bits || B * heads * 4 * nt * S < (1ll << 31), "vt_attention_bwd: keep-bit store too large for 32-bit word offsets");
+  {   // a schedule built for another grid (the SM reserve changed in between) is ignored: round-robin is always valid
+    int sched_ctas = 0;
+    const int32_t* sc = attention_bwd_schedule(&sched_ctas);
+    p.sched = (start && sc && sched_ctas == (int)(n_items < sms ? n_items : sms)) ? sc : nullptr;
+  }
   if (p.keep_bits || !p.drop.thresh16) launch_pdl(attn_bwd_fused<1>, (unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st, tq, tdo, p);
   else launch_pdl(attn_bwd_fused<0>, (unsigned)(n_items < sms ? n_items : sms), BWD_THREADS, smem, st, tq, tdo, p);
   const long long rows = rows_all;
@@ -1201,6 +1250,19 @@ extern "C" int vt_attention_bwd(const void* qkv, int64_t ld, const float* bias, 
                                 float dropout_p, uint64_t seed, uint32_t dropout_stream, vt_stream stream) {
   return attention_bwd_impl(qkv, ld, bias, key_tiles, nullptr, nullptr, 0, ctx, dctx, lse, dsum_ws, B, S, heads, head_dim, dqkv, dropout_p, seed,
                             dropout_stream, stream);
+}
+extern "C" int64_t vt_attention_bwd_schedule_ctas(int64_t B, int64_t S, int64_t heads) {
+  const int64_t n_items = ((S + 127) / 128) * heads * B;
+  const int64_t sms = usable_sms();
+  return n_items < sms ? n_items : sms;
+}
+extern "C" int vt_attention_bwd_schedule(const int32_t* start, int64_t B, int64_t S, int64_t heads, int32_t* sched, vt_stream stream) {
+  VT_REQUIRE(start && sched && B > 0 && B <= 4000 && S > 0 && heads > 0, "vt_attention_bwd_schedule: bad arguments (B <= 4000)");
+  const int ctas = (int)vt_attention_bwd_schedule_ctas(B, S, heads);
+  attn_bwd_schedule_kernel<<<1, 256, (size_t)(B + 1) * sizeof(long long), (cudaStream_t)stream>>>((const int*)start, (int)B, (int)S, (int)heads, ctas, sched);
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
 }
 extern "C" int64_t vt_attention_bwd_workspace_packed(int64_t rows_cap, int64_t B, int64_t S, int64_t heads) {
   const int64_t dsum_floats = (B * heads * S + 3) & ~(int64_t)3;

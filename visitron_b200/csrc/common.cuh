@@ -169,6 +169,7 @@ struct DropoutCfg {
 };
 
 const uint32_t* seed_source();   // api.cu: the pointer set by vt_set_seed_source (null = seeds are passed by value only)
+const int32_t* attention_bwd_schedule(int* ctas);   // api.cu: the calling thread's item schedule for vt_attention_bwd_packed or null
 uint32_t* attention_keep_bits();  // api.cu: the calling thread's keep-bit store for the next attention launches (vt_set_attention_keep_bits) or null
 const int32_t* row_limit();      // api.cu: the calling thread's device-resident row count {rows_padded, rows} (vt_set_row_limit) or null
 

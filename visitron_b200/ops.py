@@ -5,6 +5,8 @@ in Python.  `lib.gemm` lives in lib.py.
 """
 from __future__ import annotations
 
+import os
+
 from typing import Optional, Tuple
 
 import torch
@@ -157,7 +159,7 @@ def attention_key_tiles(bias: torch.Tensor) -> Optional[torch.Tensor]:
 
 class PackPlan:
     """Device-resident description of the packed row layout of one step (vt_pack_plan): no host sync, fixed shapes."""
-    __slots__ = ("B", "S", "cap", "row_src", "row_dst", "row_b", "start", "counts", "bias", "labels_a", "labels_b", "cls_rows", "key_tiles")
+    __slots__ = ("B", "S", "cap", "row_src", "row_dst", "row_b", "start", "counts", "bias", "labels_a", "labels_b", "cls_rows", "key_tiles", "bwd_sched")
 
 
 def pack_plan(bias, labels_a, labels_b, B, S) -> PackPlan:
@@ -179,6 +181,7 @@ def pack_plan(bias, labels_a, labels_b, B, S) -> PackPlan:
     pl.cls_rows = i64[2 * cap:]
     check(L.vt_pack_plan(ptr(bias), ptr(labels_a), ptr(labels_b), B, S, cap, ptr(pl.row_src), ptr(pl.row_dst), ptr(pl.row_b), ptr(pl.start),
                          ptr(pl.counts), ptr(pl.bias), ptr(pl.labels_a), ptr(pl.labels_b), ptr(pl.cls_rows), stream_ptr()), "vt_pack_plan")
+    pl.bwd_sched = {}      # heads -> (int32 [ctas + 1], ctas): cost-balanced item ranges of the attention backward, built on first use
     pl.key_tiles = None
     if S <= 2048:
         pl.key_tiles = torch.empty(B, device=dev, dtype=torch.int32)
@@ -191,6 +194,9 @@ def zero_pad_rows(buf, counts):
     check(init().vt_zero_pad_rows(ptr(buf), buf.stride(0) * buf.element_size(), buf.size(1) * buf.element_size(), ptr(counts), stream_ptr()),
           "vt_zero_pad_rows")
     return buf
+
+
+_NO_BWD_SCHED = bool(int(os.environ.get("VT_NO_BWD_SCHED", "0")))    # A/B switch: round-robin items in the packed attention backward
 
 
 def attention_keep_bits(B, S, heads, device):
@@ -239,6 +245,24 @@ def attention_bwd(qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p=0.0, seed=0,
     L = init()
     if dqkv is None:
         dqkv = torch.empty_like(qkv)
+    sched = None
+    if plan is not None and B <= 4000 and not _NO_BWD_SCHED:
+        sched = plan.bwd_sched.get(heads)
+        if sched is None:
+            ctas = int(L.vt_attention_bwd_schedule_ctas(B, S, heads))
+            buf = torch.empty(ctas + 1, device=qkv.device, dtype=torch.int32)
+            check(L.vt_attention_bwd_schedule(ptr(plan.start), B, S, heads, ptr(buf), stream_ptr()), "vt_attention_bwd_schedule")
+            sched = plan.bwd_sched[heads] = (buf, ctas)
+        L.vt_set_attention_bwd_schedule(sched[0].data_ptr(), sched[1])
+    try:
+        dqkv = _attention_bwd_launch(L, qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p, seed, stream_id, dqkv, key_tiles, plan, keep_bits)
+    finally:
+        if sched is not None:
+            L.vt_set_attention_bwd_schedule(None, 0)
+    return dqkv
+
+
+def _attention_bwd_launch(L, qkv, bias, ctx, dctx, lse, B, S, heads, dropout_p, seed, stream_id, dqkv, key_tiles, plan, keep_bits):
     with _keep_bits(keep_bits):
         if plan is None:
             ws = torch.empty(int(L.vt_attention_bwd_workspace(B, S, heads)), device=qkv.device, dtype=F32)
