@@ -94,7 +94,10 @@ def main():
     case("ln bwd           [M,768] (+dropped copy, dgamma/dbeta/dbias)",
          lambda i: ops.layernorm_bwd(r(xs, i), r(xs, i + 1), gamma, 1e-12, gvec[:H], gvec[H:2 * H], gvec[2 * H:3 * H], out_dropout_p=ph, out_stream=2,
                                      seed=seed, dx=out_h, dxd=out_h2), 0, 4.0 * M * H * 2)
-    case("wgrad ffn-down   dW[768,3072] = dY^T Z", lambda i: lib.gemm(r(xs, i), r(zs, i), a_major=1, b_major=1, out=gW.view(H, I), accumulate=True), gemm_fl(I, H))
+    case("ln bwd           [M,768] (+dropped copy, dgamma/dbeta; bias gradient left to the wgrad GEMM)",
+         lambda i: ops.layernorm_bwd(r(xs, i), r(xs, i + 1), gamma, 1e-12, gvec[:H], gvec[H:2 * H], None, out_dropout_p=ph, out_stream=2,
+                                     seed=seed, dx=out_h, dxd=out_h2), 0, 4.0 * M * H * 2)
+    case("wgrad ffn-down   dW[768,3072] = dY^T Z (+ bias gradient)", lambda i: lib.gemm(r(xs, i), r(zs, i), a_major=1, b_major=1, out=gW.view(H, I), accumulate=True, colsum=gvec[:H]), gemm_fl(I, H))
     case("dgrad ffn-down   [M,768]x[768,3072]  x saved gelu'", lambda i: lib.gemm(r(xs, i), W2, b_major=1, act=ACT_MUL_AUX, aux=r(zs, i), out=out_i), gemm_fl(I, H))
     case("colsum           [M,3072] (separate kernel, no longer in the step)", lambda i: ops.colsum(r(zs, i), gvec[:I]), 0, 1.0 * M * I * 2)
     case("wgrad ffn-up     dW[3072,768] = dPre^T Y", lambda i: lib.gemm(r(zs, i), r(xs, i), a_major=1, b_major=1, out=gW.view(I, H), accumulate=True), gemm_fl(I, H))
@@ -207,7 +210,7 @@ def main():
         us = e0.elapsed_time(e1) * 1e3 / args.iters
         # the layer total counts what the step launches: attention with the key-tile plan, the bias gradients inside the wgrad GEMMs
         skip = (name.startswith("attn") and "packed rows" not in name) or "no longer in the step" in name or \
-            name.startswith("wgrad ffn-up     dW") or name.startswith("wgrad qkv        dW")
+            name.startswith("wgrad ffn-up     dW") or name.startswith("wgrad qkv        dW") or "dgamma/dbeta/dbias" in name
         tot += us if ci < n_layer and not skip else 0.0
         rate = "%7.0f TFLOP/s" % (fl / us / 1e6) if fl else "%7.0f GB/s   " % (by / us / 1e3)
         print("%-62s %8.1f us  %s" % (name, us, rate), flush=True)

@@ -165,6 +165,9 @@ ln_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict
 // ---------------------------------------------------------------------------------------------
 // One CTA (8 warps) per SM at ~230 registers: the next row's x and dy are prefetched (packed, 24 registers)
 // while the current row is processed, which doubles the bytes in flight per warp.
+// NACC = 3 also accumulates the column sums of dx (the bias gradient of the Linear in front of the LayerNorm); NACC = 2 leaves
+// that to the weight-gradient GEMM's colsum side product and spends the 24 registers on a second row of prefetch (DEPTH = 2).
+template <int NACC, int DEPTH>
 __global__ void __launch_bounds__(ROW_WARPS * 32, 1)
 ln_bwd_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restrict__ x, long long ldx,
               const float* __restrict__ gamma, float eps, long long rows, bf16* __restrict__ dx, long long lddx,
@@ -177,36 +180,44 @@ ln_bwd_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restric
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float g[CH][8];
   load_vec_f32(gamma, lane, g);
-  float acc[3][CH][8];
+  float acc[NACC][CH][8];
 #pragma unroll
-  for (int a = 0; a < 3; ++a)
+  for (int a = 0; a < NACC; ++a)
 #pragma unroll
     for (int c = 0; c < CH; ++c)
 #pragma unroll
       for (int j = 0; j < 8; ++j) acc[a][c][j] = 0.f;
   const long long stride = (long long)gridDim.x * ROW_WARPS;
   long long m = (long long)blockIdx.x * ROW_WARPS + warp;
-  uint4 xq[CH], dq[CH];
-  if (m < rows) {
+  uint4 xq[DEPTH][CH], dq[DEPTH][CH];
 #pragma unroll
-    for (int c = 0; c < CH; ++c) {
-      xq[c] = __ldg(reinterpret_cast<const uint4*>(x + m * ldx + chunk_col(lane, c)));
-      dq[c] = __ldg(reinterpret_cast<const uint4*>(dy + remap_row(m, rin, rout, roff) * lddy + chunk_col(lane, c)));
+  for (int k = 0; k < DEPTH; ++k) {
+    const long long mk = m + k * stride;
+    if (mk < rows) {
+#pragma unroll
+      for (int c = 0; c < CH; ++c) {
+        xq[k][c] = __ldg(reinterpret_cast<const uint4*>(x + mk * ldx + chunk_col(lane, c)));
+        dq[k][c] = __ldg(reinterpret_cast<const uint4*>(dy + remap_row(mk, rin, rout, roff) * lddy + chunk_col(lane, c)));
+      }
     }
   }
   for (; m < rows; m += stride) {
     float v[CH][8], d[CH][8];
 #pragma unroll
     for (int c = 0; c < CH; ++c) {
-      unpack8(xq[c], v[c]);
-      unpack8(dq[c], d[c]);
+      unpack8(xq[0][c], v[c]);
+      unpack8(dq[0][c], d[c]);
     }
-    const long long mn = m + stride;
+#pragma unroll
+    for (int k = 0; k + 1 < DEPTH; ++k)
+#pragma unroll
+      for (int c = 0; c < CH; ++c) { xq[k][c] = xq[k + 1][c]; dq[k][c] = dq[k + 1][c]; }
+    const long long mn = m + DEPTH * stride;
     if (mn < rows) {
 #pragma unroll
       for (int c = 0; c < CH; ++c) {
-        xq[c] = __ldg(reinterpret_cast<const uint4*>(x + mn * ldx + chunk_col(lane, c)));
-        dq[c] = __ldg(reinterpret_cast<const uint4*>(dy + remap_row(mn, rin, rout, roff) * lddy + chunk_col(lane, c)));
+        xq[DEPTH - 1][c] = __ldg(reinterpret_cast<const uint4*>(x + mn * ldx + chunk_col(lane, c)));
+        dq[DEPTH - 1][c] = __ldg(reinterpret_cast<const uint4*>(dy + remap_row(mn, rin, rout, roff) * lddy + chunk_col(lane, c)));
       }
     }
     apply_dropout_row(drop_in, m, lane, d);
@@ -237,12 +248,14 @@ ln_bwd_kernel(const bf16* __restrict__ dy, long long lddy, const bf16* __restric
       apply_dropout_row(drop_out, m, lane, d);
       store_row_bf16(dxd + m * lddxd, lane, d);
     }
+    if (NACC > 2) {
 #pragma unroll
-    for (int c = 0; c < CH; ++c)
+      for (int c = 0; c < CH; ++c)
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[2][c][j] += d[c][j];
+        for (int j = 0; j < 8; ++j) acc[NACC - 1][c][j] += d[c][j];
+    }
   }
-  flush_partials<3>(acc, partials, lane, warp);
+  flush_partials<NACC>(acc, partials, lane, warp);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -576,7 +589,14 @@ extern "C" int vt_layernorm_bwd(const void* dy, int64_t lddy, const void* x, int
   if (rows == 0) return VT_OK;
   const int grid = ln_bwd_grid(rows);
   cudaStream_t st = (cudaStream_t)stream;
-  launch_pdl(ln_bwd_kernel, grid, ROW_WARPS * 32, 0, st, (const bf16*)dy, lddy, (const bf16*)x, ldx, gamma, eps, rows, (bf16*)dx, lddx,
+  const int nacc = dbias ? 3 : 2;
+  if (dbias)
+    launch_pdl(ln_bwd_kernel<3, 1>, grid, ROW_WARPS * 32, 0, st, (const bf16*)dy, lddy, (const bf16*)x, ldx, gamma, eps, rows, (bf16*)dx, lddx,
+                                                 (bf16*)dx_dropped, lddxd, partials, make_dropout(in_dropout_p, seed, in_dropout_stream),
+                                                 make_dropout(out_dropout_p, seed, out_dropout_stream), remap_rows_in, remap_rows_out,
+                                                 remap_row_off, row_limit());
+  else
+    launch_pdl(ln_bwd_kernel<2, 2>, grid, ROW_WARPS * 32, 0, st, (const bf16*)dy, lddy, (const bf16*)x, ldx, gamma, eps, rows, (bf16*)dx, lddx,
                                                  (bf16*)dx_dropped, lddxd, partials, make_dropout(in_dropout_p, seed, in_dropout_stream),
                                                  make_dropout(out_dropout_p, seed, out_dropout_stream), remap_rows_in, remap_rows_out,
                                                  remap_row_off, row_limit());
@@ -585,7 +605,7 @@ extern "C" int vt_layernorm_bwd(const void* dy, int64_t lddy, const void* x, int
   // second stage: accumulate into the fp32 gradient buffers
   ReduceOuts outs = {{dgamma, dbeta, dbias, nullptr}};
   const int splits = grid > 64 ? (grid + 63) / 64 < 16 ? (grid + 63) / 64 : 16 : 1;
-  launch_pdl(reduce_partials_multi_kernel, dim3(H / 32, splits, 3), dim3(32, 8), 0, st, partials, grid, 3, outs);
+  launch_pdl(reduce_partials_multi_kernel, dim3(H / 32, splits, nacc), dim3(32, 8), 0, st, partials, grid, nacc, outs);
   count_launch(1);
   VT_CHECK_LAUNCH();
   return VT_OK;
