@@ -165,6 +165,9 @@ ln_fwd_kernel(const bf16* __restrict__ x, long long ldx, const float* __restrict
 // ---------------------------------------------------------------------------------------------
 // One CTA (8 warps) per SM at ~230 registers: the next row's x and dy are prefetched (packed, 24 registers)
 // while the current row is processed, which doubles the bytes in flight per warp.
+// Tried and measured equal, not kept (same-box A/B, tools/r2_call24.sh): 16 warps per CTA with the column sums in per-warp shared-memory
+// slices (42.1 vs 42.6 us incl. the partial reduction) -- the kernel is not short of rows in flight; under ncu it moves 4.1 TB/s
+// over its 26 us, the rest of the case's time is the launch ramp and the reduction of the partials.
 // NACC = 3 also accumulates the column sums of dx (the bias gradient of the Linear in front of the LayerNorm); NACC = 2 leaves
 // that to the weight-gradient GEMM's colsum side product and spends the 24 registers on a second row of prefetch (DEPTH = 2).
 template <int NACC, int DEPTH>
