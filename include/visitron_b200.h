@@ -216,6 +216,14 @@ int vt_embed_ln_bwd_packed(const void* dy, const int64_t* ids, const int64_t* ty
 int64_t vt_colsum_partials_rows(int64_t rows);
 int vt_colsum_bf16(const void* x, int64_t ldx, int64_t rows, int64_t ncols, float* partials, float* out, int accumulate,
                    vt_stream stream);
+/* The same without a caller workspace and without any allocation (no cudaMalloc / cudaFree / allocating library call), for callers
+ * that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that forbid it.  No counterpart in the
+ * reference.  The partial sums go to a static device array inside the library
+ * (4.6 MiB on every GPU that loads it, until exit): ncols (rounded up to 8) must not exceed vt_colsum_bf16_static_max_cols() = 4096,
+ * larger calls are rejected with VT_ERR_BAD_ARGUMENT (vt_last_error says why).  Every call shares that array: calls that may overlap on the GPU (two streams with no
+ * ordering between them) race; calls on one stream, or ordered by events, are safe.  Same result as vt_colsum_bf16. */
+int64_t vt_colsum_bf16_static_max_cols(void);
+int vt_colsum_bf16_static(const void* x, int64_t ldx, int64_t rows, int64_t ncols, float* out, int accumulate, vt_stream stream);
 
 /* fp32 [rows, cols] -> bf16 copy (dst, may be NULL) and/or bf16 transpose (dst_t, may be NULL):
  * the per-step cast of the fp32 master weights into tensor-core operands. */

@@ -6,6 +6,8 @@
 //     dbeta / dbias partial sums)
 //   * column sums (bias gradients), partial-sum reduction, row gather / scatter-add
 // BertLayerNorm is the TF flavour: biased variance, eps inside the sqrt (hf/modeling_bert.py:227-240).
+#include <mutex>
+
 #include "common.cuh"
 
 namespace vt {
@@ -702,6 +704,60 @@ extern "C" int vt_colsum_bf16(const void* x, int64_t ldx, int64_t rows, int64_t 
   const int threads = 128;
   const int gx = (int)((npad / 8 + threads - 1) / threads);
   launch_pdl(colsum_partial_kernel, dim3(gx, gy), threads, 0, st, (const bf16*)x, ldx, rows, npad, partials, row_limit());
+  launch_pdl(reduce_partials_kernel, reduce_grid(ncols, gy, accumulate), dim3(32, 8), 0, st, partials, gy, npad, ncols, out, accumulate);
+  count_launch(2);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// vt_colsum_bf16_static: vt_colsum_bf16 for callers that cannot allocate (no counterpart in the reference).
+// The first-stage partial sums live in a file-scope device array instead of a caller workspace.  The
+// array is one per GPU that loads the library (4.6 MiB each, held until exit) and is shared by every call: the first stage writes
+// every partial the second stage reads (nothing has to start at zero, stale contents of an earlier call are never read), but two
+// calls that overlap on the GPU (different streams without an ordering between them) race on it.
+// ---------------------------------------------------------------------------------------------
+constexpr long long COLSUM_STATIC_MAX_COLS = 4096;                                   // padded columns per call
+constexpr long long COLSUM_STATIC_FLOATS = 296 * COLSUM_STATIC_MAX_COLS;             // = 2 CTAs x 148 SMs rows of partials
+static __device__ __align__(256) float g_colsum_scratch[COLSUM_STATIC_FLOATS];
+
+// In host code `g_colsum_scratch` is only a handle: the device address is looked up once per device, with that device current.
+static int colsum_scratch_ptr(float** out) {
+  constexpr int MAX_DEV = 64;
+  static float* ptrs[MAX_DEV] = {};
+  static std::mutex mu;
+  int dev = -1;
+  VT_CUDA(cudaGetDevice(&dev));
+  VT_REQUIRE(dev >= 0 && dev < MAX_DEV, "vt_colsum_bf16_static: device index %d outside the table", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    float* p = nullptr;
+    VT_CUDA(cudaGetSymbolAddress((void**)&p, g_colsum_scratch));
+    VT_REQUIRE(p, "vt_colsum_bf16_static: cudaGetSymbolAddress returned a null address");
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return VT_OK;
+}
+
+extern "C" int64_t vt_colsum_bf16_static_max_cols(void) { return COLSUM_STATIC_MAX_COLS; }
+
+extern "C" int vt_colsum_bf16_static(const void* x, int64_t ldx, int64_t rows, int64_t ncols, float* out, int accumulate, vt_stream stream) {
+  const long long npad = (ncols + 7) / 8 * 8;
+  VT_REQUIRE(x && out && rows >= 0 && ncols >= 0, "vt_colsum_bf16_static: null pointer or negative size");
+  VT_REQUIRE(npad <= COLSUM_STATIC_MAX_COLS, "vt_colsum_bf16_static: %lld columns exceed the static scratch (at most %lld; use vt_colsum_bf16 with a workspace)",
+             (long long)ncols, COLSUM_STATIC_MAX_COLS);
+  VT_REQUIRE(ldx % 8 == 0 && ldx >= npad && aligned16(x), "vt_colsum_bf16_static: ldx must be a multiple of 8 covering the padded row and x 16-byte aligned");
+  if (ncols == 0) return VT_OK;
+  float* partials = nullptr;
+  int rc = colsum_scratch_ptr(&partials);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  long long gy = vt_colsum_partials_rows(rows);
+  if (gy * npad > COLSUM_STATIC_FLOATS) gy = COLSUM_STATIC_FLOATS / npad;   // a GPU with more SMs than the array was sized for
+  const int threads = 128;
+  const int gx = (int)((npad / 8 + threads - 1) / threads);
+  launch_pdl(colsum_partial_kernel, dim3(gx, (unsigned)gy), threads, 0, st, (const bf16*)x, ldx, rows, npad, partials, row_limit());
   launch_pdl(reduce_partials_kernel, reduce_grid(ncols, gy, accumulate), dim3(32, 8), 0, st, partials, gy, npad, ncols, out, accumulate);
   count_launch(2);
   VT_CHECK_LAUNCH();
