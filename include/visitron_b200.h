@@ -154,6 +154,9 @@ int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void* B, int64_t
 
 /* Debug hook for tests: force the GEMM tile width (0 = heuristic; 64/128/192/256). */
 void vt_debug_force_block_n(int bn);
+/* CTA pairs (tcgen05.mma.cta_group::2, two SMs per 256 x 256 tile) in vt_gemm_bf16: -1 = where they pay (default), 0 = never,
+ * 1 = wherever supported (tests / A-B timing). */
+void vt_debug_pair_mode(int mode);
 /* The persistent GEMM launches one CTA per SM.  While a gradient all-reduce runs beside the backward GEMMs its CTAs hold
  * a few SMs; a full-width GEMM grid would then run its last CTAs as a second wave.  n > 0 makes the GEMM leave n SMs free
  * (visitron_b200/parallel.py sets it for the span of the overlapped exchange); 0 restores the full grid. */

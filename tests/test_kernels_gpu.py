@@ -46,6 +46,45 @@ def test_gemm_majors(a_major, b_major, bn):
     close(out, A.float() @ B.float().t(), rtol=1e-3, atol=1e-3, what="gemm")
 
 
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (300, 768, 264), (1000, 304, 3072), (5000, 2304, 768)])
+@pytest.mark.parametrize("b_major", [0, 1])
+def test_gemm_cta_pair_equals_single_cta(M, N, K, b_major):
+    """tcgen05.mma.cta_group::2 (two SMs per 256 x 256 tile): same accumulation order per output element as the single-CTA kernel, so
+    the results are bit-identical -- plain, with the fused epilogues, with a partial last row block and under a device row limit."""
+    torch.manual_seed(M + K)
+    A = (torch.randn(M, K, device=DEV) * 0.5).to(BF)
+    B = (torch.randn(N, K, device=DEV) * 0.1).to(BF)
+    Bin = B.t().contiguous() if b_major else B
+    bias = torch.randn(N, device=DEV)
+    res = torch.randn(M, N, device=DEV).to(BF)
+    L = lib.init()
+    outs = {}
+    try:
+        for mode in (0, 1):
+            L.vt_debug_pair_mode(mode)
+            o = [lib.gemm(A, Bin, b_major=b_major, out_dtype=torch.float32)]
+            aux = torch.zeros(M, N, device=DEV, dtype=BF)
+            o.append(lib.gemm(A, Bin, b_major=b_major, bias=bias, act=lib.ACT_GELU_SAVE_GRAD, aux_out=aux))
+            o.append(aux)
+            o.append(lib.gemm(A, Bin, b_major=b_major, bias=bias, residual=res, dropout_p=0.25, seed=5, dropout_stream=3))
+            o.append(lib.gemm(A, Bin, b_major=b_major, act=lib.ACT_MUL_AUX, aux=res))
+            if M >= 512:
+                rows = M - 200
+                lim = torch.tensor([(rows + 127) // 128 * 128, rows], device=DEV, dtype=torch.int32)
+                buf = torch.full((M, N), 7.0, device=DEV, dtype=BF)
+                with ops.row_limit(lim, 0):
+                    lib.gemm(A, Bin, b_major=b_major, bias=bias, out=buf)
+                assert bool((buf[(rows + 127) // 128 * 128:] == 7.0).all())      # rows past the limit are not written
+                o.append(buf[:rows].clone())
+            torch.cuda.synchronize()
+            outs[mode] = o
+    finally:
+        L.vt_debug_pair_mode(-1)
+    close(outs[1][0], A.float() @ B.float().t(), rtol=1e-3, atol=1e-3, what="pair gemm")
+    for a, b in zip(outs[0], outs[1]):
+        assert torch.equal(a, b)
+
+
 def test_gemm_epilogues_and_splitk():
     torch.manual_seed(2)
     M, N, K = 640, 768, 768

@@ -11,6 +11,7 @@
 // what lets data-gradient GEMMs reuse the forward weight and weight-gradient GEMMs read dY and X
 // in place, with no transposed copies in HBM (see include/visitron_b200.h).
 #include <atomic>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "ptx.cuh"
@@ -54,11 +55,16 @@ struct GemmParams {
 // CS = 1: the column-sum variant.  Every stage's B tile is followed by a block of bf16 ones (written once; TMA never touches it), so
 // that for the first column block of a row block the MMA simply runs with N = BN + 16: accumulator columns BN .. BN + 15 all
 // receive sum_k A[k, m].  (A separate N = 16 MMA per k step re-read the whole A tile from shared memory: +33 % on those tiles.)
-template <int BN, int CS = 0>
+// PAIR = 1: two CTAs of a cluster (the two SMs of a TPC) work on one 256 x BN tile with tcgen05.mma.cta_group::2: each stages its own
+// 128 rows of A and HALF of the B tile (BN / 2 columns), the leader issues one M = 256 MMA that reads both shared memories and
+// writes rows 0-127 of the accumulator to its own TMEM and rows 128-255 to the peer's.  Per SM the B traffic (L2 -> shared memory
+// and shared memory -> tensor core) halves and the ring gets 6 stages instead of 4.
+template <int BN, int CS = 0, int PAIR = 0>
 struct GemmCfg {
   static_assert(!CS || BN <= 192, "the column-sum variant needs 16 accumulator columns next to the tile");
+  static_assert(!PAIR || (!CS && BN == 256), "CTA pairs: 256 x 256 tiles, no column sums");
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int B_BYTES = (PAIR ? BN / 2 : BN) * BK * 2;
   static constexpr int ONES_BYTES = CS ? 64 * BK * 2 : 0;   // one MN-major 64-column chunk (a K-major B needs only 16 rows of it)
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES + ONES_BYTES;
   static constexpr int ACC_STRIDE = !CS ? BN : (BN + 16 <= 128 ? 128 : 256);   // TMEM columns per accumulator stage
@@ -221,11 +227,13 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, const Dropou
   }
 }
 
-template <int BN, int A_MN, int B_MN, int EPI, int CS = 0>
+template <int BN, int A_MN, int B_MN, int EPI, int CS = 0, int PAIR = 0>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
   static_assert(!CS || A_MN, "column sums are taken over the rows of a [K, M] A operand");
-  using Cfg = GemmCfg<BN, CS>;
+  static_assert(!PAIR || !A_MN, "CTA pairs: A is [M, K]");
+  using Cfg = GemmCfg<BN, CS, PAIR>;
+  const uint32_t rank = PAIR ? pair_rank() : 0u;   // CTA of the pair: 0 = leader (issues the MMAs, owns the full / accumulator-empty barriers)
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -252,13 +260,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), NUM_EPI_WARPS);
+      mbar_init(tempty_bar(a), NUM_EPI_WARPS * (PAIR ? 2 : 1));   // pair: the leader's barrier counts both CTAs' epilogue warps
     }
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
-    tmem_relinquish();
+    if constexpr (PAIR) { tmem_alloc_pair(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish_pair(); }
+    else { tmem_alloc(tmem_slot, Cfg::TMEM_COLS); tmem_relinquish(); }
   }
   if (CS && warp == 3) {   // bf16 1.0 everywhere behind every stage's B tile: no swizzle or major can misplace an element
     constexpr uint32_t one2 = 0x3f803f80u;
@@ -269,7 +277,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     fence_proxy_async();
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) pair_sync();   // the peer's barriers exist before anything (its TMA, the leader's commits) can arrive on them
+  else __syncthreads();
   tc_fence_after();
   pdl_sync();   // the prologue above overlapped the tail of the previous kernel; global memory is touched only below
   const uint32_t tmem_base = *tmem_slot_ptr;
@@ -289,23 +298,41 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       m_blocks = (M + BM - 1) / BM;
     }
   }
+  if constexpr (PAIR) m_blocks = (M + 2 * BM - 1) / (2 * BM);   // a pair's tile is 256 rows: this CTA's 128-row block is 2 * (tile row) + rank
   const int mn_tiles = m_blocks * p.n_blocks;
   const int total_tiles = mn_tiles * splits;
+  const int t_first = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, t_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  auto row_block = [&](int mn) { return PAIR ? 2 * (mn / p.n_blocks) + (int)rank : mn / p.n_blocks; };
 
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      for (int t = t_first; t < total_tiles; t += t_step) {
         const int split = t / mn_tiles, mn = t % mn_tiles;
-        const int m_blk = mn / p.n_blocks, n_blk = mn % p.n_blocks;
+        const int m_blk = row_block(mn), n_blk = mn % p.n_blocks;
         const int kb0 = split * kbps;
         const int kb1 = min(kb0 + kbps, k_blocks);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
-          mbar_arrive_expect_tx(full_bar(stage), Cfg::A_BYTES + Cfg::B_BYTES);   // the ones block behind B is not TMA's
           const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
           const uint32_t sb = sa + Cfg::A_BYTES;
+          if constexpr (PAIR) {
+            // both CTAs load into their own shared memory; all bytes of the stage (2 x (A + half B)) are counted on the LEADER's barrier
+            const uint32_t lbar = pair_map(full_bar(stage), 0);
+            if (rank == 0) mbar_arrive_expect_tx(full_bar(stage), 2 * (Cfg::A_BYTES + Cfg::B_BYTES));
+            tma_load_2d_pair(sa, &tmA, lbar, kb * BK, m_blk * BM);
+            const int n0 = n_blk * BN + (int)rank * (BN / 2);
+            if (B_MN) {
+#pragma unroll
+              for (int c = 0; c < BN / 128; ++c) tma_load_2d_pair(sb + c * (64 * BK * 2), &tmB, lbar, n0 + c * 64, kb * BK);
+            } else {
+              tma_load_2d_pair(sb, &tmB, lbar, kb * BK, n0);
+            }
+            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+            continue;
+          }
+          mbar_arrive_expect_tx(full_bar(stage), Cfg::A_BYTES + Cfg::B_BYTES);   // the ones block behind B is not TMA's
           if (A_MN) {
 #pragma unroll
             for (int c = 0; c < BM / 64; ++c) tma_load_2d(sa + c * (64 * BK * 2), &tmA, full_bar(stage), m_blk * BM + c * 64, kb * BK);
@@ -323,8 +350,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(PAIR ? 2 * BM : BM, BN, A_MN, B_MN);
       constexpr uint32_t idesc_cs = make_idesc_bf16(BM, BN + 16, A_MN, B_MN);   // the tile plus 16 columns of ones
       // K-major, 128B swizzle: 8-row groups 1024 B apart (SBO); LBO unused (encoded 1).
       // MN-major, 128B swizzle: 64-element MN chunks one TMA box (64*BK*2 B) apart (LBO),
@@ -334,7 +361,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       constexpr uint32_t B_KSTEP = B_MN ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      for (int t = t_first; t < total_tiles; t += t_step) {
         const int split = t / mn_tiles;
         const int kb0 = split * kbps;
         const int kb1 = min(kb0 + kbps, k_blocks);
@@ -349,12 +376,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint64_t a_desc = make_smem_desc(sa, A_LBO, 1024);
           const uint64_t b_desc = make_smem_desc(sa + Cfg::A_BYTES, B_LBO, 1024);
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k)
-            umma_bf16(d_tmem, a_desc + (uint64_t)(k * A_KSTEP), b_desc + (uint64_t)(k * B_KSTEP), idesc_t, (kb > kb0 || k > 0) ? 1u : 0u);
-          umma_commit(empty_bar(stage));
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            if constexpr (PAIR) umma_bf16_pair(d_tmem, a_desc + (uint64_t)(k * A_KSTEP), b_desc + (uint64_t)(k * B_KSTEP), idesc_t, (kb > kb0 || k > 0) ? 1u : 0u);
+            else umma_bf16(d_tmem, a_desc + (uint64_t)(k * A_KSTEP), b_desc + (uint64_t)(k * B_KSTEP), idesc_t, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          if constexpr (PAIR) umma_commit_pair(empty_bar(stage));   // frees the stage in BOTH CTAs
+          else umma_commit(empty_bar(stage));
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(tfull_bar(acc));
+        if constexpr (PAIR) umma_commit_pair(tfull_bar(acc));       // both CTAs' epilogue warps read their half of the rows
+        else umma_commit(tfull_bar(acc));
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
       }
@@ -391,13 +422,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int acc = 0;
     uint32_t acc_phase = 0;
     uint4 ext[4] = {}, ext_next[4] = {};
-    if (EXT && (int)blockIdx.x < total_tiles) {
-      const int mn = (int)blockIdx.x % mn_tiles;
-      load_ext(ext, mn / p.n_blocks, mn % p.n_blocks, c_begin);
+    const uint32_t tempty_leader = PAIR ? pair_map(tempty_bar(0), 0) : 0u;
+    if (EXT && t_first < total_tiles) {
+      const int mn = t_first % mn_tiles;
+      load_ext(ext, row_block(mn), mn % p.n_blocks, c_begin);
     }
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    for (int t = t_first; t < total_tiles; t += t_step) {
       const int mn = t % mn_tiles;
-      const int m_blk = mn / p.n_blocks, n_blk = mn % p.n_blocks;
+      const int m_blk = row_block(mn), n_blk = mn % p.n_blocks;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * Cfg::ACC_STRIDE);
@@ -426,10 +458,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           // the accumulator stage is drained: hand it back to the MMA warp before the post-processing
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tempty_bar(acc));
-          if (EXT && t + (int)gridDim.x < total_tiles) {
-            const int mn2 = (t + (int)gridDim.x) % mn_tiles;
-            load_ext(ext_next, mn2 / p.n_blocks, mn2 % p.n_blocks, c_begin);
+          if (lane == 0) {
+            if constexpr (PAIR) mbar_arrive_remote(tempty_leader + 8u * (uint32_t)acc);
+            else mbar_arrive(tempty_bar(acc));
+          }
+          if (EXT && t + t_step < total_tiles) {
+            const int mn2 = (t + t_step) % mn_tiles;
+            load_ext(ext_next, row_block(mn2), mn2 % p.n_blocks, c_begin);
           }
         }
         const int n0 = n_blk * BN + c * 32 + 8 * c4;
@@ -472,8 +507,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
 
   tc_fence_before();
-  __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  if constexpr (PAIR) pair_sync();   // the leader's MMAs read the peer's shared memory and write its TMEM: neither CTA leaves before both are done
+  else __syncthreads();
+  if (warp == 2) {
+    if constexpr (PAIR) tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS);
+    else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -532,6 +571,34 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   return VT_OK;
 }
 
+// CTA-pair launch (see GemmCfg): a cluster of two CTAs per 256 x 256 tile, grid = 2 x min(tiles, SMs / 2)
+template <int B_MN, int EPI>
+static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int sms, cudaStream_t st) {
+  using Cfg = GemmCfg<256, 0, 1>;
+  static bool attr_set = false;
+  auto kern = gemm_bf16_kernel<256, 0, B_MN, EPI, 0, 1>;
+  if (!attr_set) {
+    VT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  const long long tiles = (long long)((p.M + 2 * BM - 1) / (2 * BM)) * p.n_blocks;
+  const long long pairs = tiles < sms / 2 ? tiles : sms / 2;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(2 * pairs));
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  VT_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
+  count_launch(1);
+  VT_CHECK_LAUNCH();
+  return VT_OK;
+}
+
 template <int BN>
 static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t st) {
   if constexpr (BN <= 192) {
@@ -544,12 +611,15 @@ static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& ta, const CUten
 }
 
 static int g_force_bn = 0;
+// -1: CTA pairs where they pay (large M), 0: never, 1: wherever the kernel supports them (vt_debug_pair_mode; VT_GEMM_PAIR at load time)
+static int g_pair_mode = [] { const char* e = getenv("VT_GEMM_PAIR"); return e ? atoi(e) : -1; }();
 
 }  // namespace vt
 
 using namespace vt;
 
 extern "C" void vt_debug_force_block_n(int bn) { vt::g_force_bn = bn; }
+extern "C" void vt_debug_pair_mode(int mode) { vt::g_pair_mode = mode; }
 extern "C" int64_t vt_launch_count(void) { return (int64_t)vt::g_launches.load(); }
 extern "C" void vt_reset_launch_count(void) { vt::g_launches.store(0); }
 
@@ -657,18 +727,39 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   if (p.aux_out) vec = vec && ((uintptr_t)p.aux_out % 16 == 0) && (p.ldaux_out % 8 == 0);
   p.vec_ok = vec ? 1 : 0;
 
+  // CTA pairs: [M, K] A operand, 256-wide tiles, one pass over K, no output row maps; by default only where a launch is many waves of
+  // tiles (below ~4 k rows the 256-row granularity and the cluster launch cost more than the halved B traffic gains)
+  const bool pair_ok = !a_major && BN == 256 && p.splits == 1 && !p.accumulate && p.remap_in <= 0 && !p.remap_index && sms >= 2;
+  // measured at M = 24.5 k (tools/r2_call25.sh): +3 .. +6 % where the main loop bounds the tile (K >= 2304, or N >= 2304 with a light
+  // epilogue), -4 % on [M,768]x[768,768] with the dropout + residual epilogue (both CTAs' epilogues must finish before an accumulator
+  // stage is reused), so the small square shapes stay single-CTA
+  const bool pair = pair_ok && (g_pair_mode == 1 || (g_pair_mode < 0 && M >= 4096 && !g_force_bn && (K > 1024 || N > 1024)));
   CUtensorMap ta, tb;
   if (a_major) rc = make_map(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK);
   else rc = make_map(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
   if (rc) return rc;
   if (b_major) rc = make_map(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK);
-  else rc = make_map(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)BN);
+  else rc = make_map(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)(pair ? BN / 2 : BN));
   if (rc) return rc;
 
   long long total = (long long)p.m_blocks * p.n_blocks * p.splits;
   int grid = (int)(total < sms ? total : sms);
   cudaStream_t st = (cudaStream_t)stream;
   // the encoder's hot epilogues as compile-time kinds (see EPI_*); everything else takes the generic kernel
+  if (pair) {
+    const bool fast = !p.out_fp32 && p.vec_ok && N % 8 == 0;
+    const bool bias = p.bias != nullptr, drop = p.drop.thresh16 != 0, res = p.residual != nullptr, auxo = p.aux_out != nullptr;
+    if (fast && !b_major) {
+      if (bias && p.act == VT_ACT_NONE && !res && !drop && !auxo) return launch_gemm_pair<0, EPI_BIAS>(ta, tb, p, sms, st);
+      if (bias && p.act == VT_ACT_GELU_SAVE_GRAD && !res && !drop && auxo) return launch_gemm_pair<0, EPI_BIAS | EPI_GELU_SG>(ta, tb, p, sms, st);
+      if (bias && p.act == VT_ACT_NONE && res && !auxo) return launch_gemm_pair<0, EPI_BIAS | EPI_DROP | EPI_RESID>(ta, tb, p, sms, st);
+    } else if (fast && b_major && !bias && !drop && !auxo) {
+      if (p.act == VT_ACT_MUL_AUX && !res) return launch_gemm_pair<1, EPI_MUL_AUX>(ta, tb, p, sms, st);
+      if (p.act == VT_ACT_NONE && res) return launch_gemm_pair<1, EPI_RESID>(ta, tb, p, sms, st);
+      if (p.act == VT_ACT_NONE && !res) return launch_gemm_pair<1, 0>(ta, tb, p, sms, st);
+    }
+    return b_major ? launch_gemm_pair<1, EPI_GENERIC>(ta, tb, p, sms, st) : launch_gemm_pair<0, EPI_GENERIC>(ta, tb, p, sms, st);
+  }
   const bool fast_ok = BN == 256 && !p.out_fp32 && !p.accumulate && p.remap_in <= 0 && !p.remap_index && p.vec_ok && N % 8 == 0 && p.splits == 1;
   if (fast_ok) {
     const bool bias = p.bias != nullptr, drop = p.drop.thresh16 != 0, res = p.residual != nullptr, auxo = p.aux_out != nullptr;
