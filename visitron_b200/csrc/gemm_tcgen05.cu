@@ -16,6 +16,14 @@
 #include "common.cuh"
 #include "ptx.cuh"
 
+// Timing-ablation switches (results are garbage): compiled in only with -DVT_ATTN_ABLATE (VT_BUILD_ABLATE=1), read from VT_GEMM_DBG:
+// 1 epilogue only drains TMEM (no staging, arithmetic or stores), 2 no global stores, 4 no MMAs, 8 no TMA loads
+#ifdef VT_ATTN_ABLATE
+#define VT_GDBG(bit) ((p.dbg & (bit)) != 0)
+#else
+#define VT_GDBG(bit) false
+#endif
+
 namespace vt {
 
 using namespace ptx;
@@ -50,6 +58,7 @@ struct GemmParams {
   // weight-gradient form only (A is [K, M]): colsum[m] += alpha * sum over k of A[k, m] -- the bias gradient of the layer whose
   // weight gradient this GEMM is, taken from the A tiles that are in shared memory anyway (16 more columns of ones on the B side)
   float* colsum;
+  int dbg;
 };
 
 // CS = 1: the column-sum variant.  Every stage's B tile is followed by a block of bf16 ones (written once; TMA never touches it), so
@@ -59,6 +68,10 @@ struct GemmParams {
 // 128 rows of A and HALF of the B tile (BN / 2 columns), the leader issues one M = 256 MMA that reads both shared memories and
 // writes rows 0-127 of the accumulator to its own TMEM and rows 128-255 to the peer's.  Per SM the B traffic (L2 -> shared memory
 // and shared memory -> tensor core) halves and the ring gets 6 stages instead of 4.
+// What bounds the K = 768 GEMMs (timing ablations, VT_GEMM_DBG, FFN-up with the GELU + gelu' epilogue at M = 24.5 k: 133 us whole, 77 us
+// with the epilogue reduced to draining TMEM, 95 us for the epilogue alone without MMAs and loads): the epilogue's ~17 arithmetic
+// instructions per element, issued by two warps per scheduler at 77 % issue utilisation.  Tried without gain: 16 epilogue warps
+// (same time: issue-bound, not latency-bound), packed f32x2 arithmetic (FFMA2 issues at half rate), CTA pairs for these shapes.
 template <int BN, int CS = 0, int PAIR = 0>
 struct GemmCfg {
   static_assert(!CS || BN <= 192, "the column-sum variant needs 16 accumulator columns next to the tile");
@@ -123,7 +136,8 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, const Dropou
 #pragma unroll
     for (int j = 0; j < 8; ++j) gelu_fwd_grad(x[j], x[j], dy[j]);
     bf16* ao = p.aux_out + (long long)m * p.ldaux_out + n0;
-    if (vec) {
+    if (VT_GDBG(2) && dy[0] != 1234.5f) {
+    } else if (vec) {
       *reinterpret_cast<uint4*>(ao) = pack8(dy);
     } else {
 #pragma unroll
@@ -217,7 +231,8 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, const Dropou
     }
   } else {
     bf16* d = reinterpret_cast<bf16*>(p.D) + orow * p.ldd + n0;
-    if (vec) {
+    if (VT_GDBG(2) && x[0] != 1234.5f) {
+    } else if (vec) {
       *reinterpret_cast<uint4*>(d) = pack8(x);
     } else {
 #pragma unroll
@@ -332,6 +347,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (++stage == STAGES) { stage = 0; phase ^= 1u; }
             continue;
           }
+          if (VT_GDBG(8)) { mbar_arrive(full_bar(stage)); if (++stage == STAGES) { stage = 0; phase ^= 1u; } continue; }
           mbar_arrive_expect_tx(full_bar(stage), Cfg::A_BYTES + Cfg::B_BYTES);   // the ones block behind B is not TMA's
           if (A_MN) {
 #pragma unroll
@@ -377,6 +393,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint64_t b_desc = make_smem_desc(sa + Cfg::A_BYTES, B_LBO, 1024);
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
+            if (VT_GDBG(4)) break;
             if constexpr (PAIR) umma_bf16_pair(d_tmem, a_desc + (uint64_t)(k * A_KSTEP), b_desc + (uint64_t)(k * B_KSTEP), idesc_t, (kb > kb0 || k > 0) ? 1u : 0u);
             else umma_bf16(d_tmem, a_desc + (uint64_t)(k * A_KSTEP), b_desc + (uint64_t)(k * B_KSTEP), idesc_t, (kb > kb0 || k > 0) ? 1u : 0u);
           }
@@ -446,6 +463,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       tmem_ld_wait();
 #pragma unroll 1
       for (int c = c_begin; c < c_end; ++c) {
+        if (VT_GDBG(1)) {
+          if (c + 1 < c_end) { tmem_ld_32x32(t_addr + (uint32_t)((c + 1) * 32), v); tmem_ld_wait(); }
+          else {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { if constexpr (PAIR) mbar_arrive_remote(pair_map(tempty_bar(acc), 0)); else mbar_arrive(tempty_bar(acc)); }
+          }
+          continue;
+        }
         // row-per-lane (TMEM) layout -> staging: lane = row, 16-byte chunk j at physical chunk j ^ (row & 7)
 #pragma unroll
         for (int j = 0; j < 8; ++j)
@@ -718,6 +744,8 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   p.rows_dev = row_limit();
   p.remap_index = ep->remap_index;
   p.colsum = ep->colsum;
+  static const int dbg = [] { const char* e = getenv("VT_GEMM_DBG"); return e ? atoi(e) : 0; }();
+  p.dbg = dbg;
   // 16-byte vector path: every row slice the epilogue touches must be 16-byte aligned
   const int ob = p.out_fp32 ? 4 : 2;
   bool vec = ((uintptr_t)D % 16 == 0) && ((ldd * ob) % 16 == 0);
