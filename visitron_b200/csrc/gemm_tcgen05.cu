@@ -111,9 +111,9 @@ struct EpiK {
 // Epilogue of 8 consecutive columns of one output row, in the COALESCED layout: after the in-warp shared-memory
 // transpose lane L owns columns [8 (L & 3), +8) of row (L >> 2) + 8 i, i = 0..3, of the 32 x 32 chunk, so one warp-wide
 // 16-byte access covers 8 rows x 64 contiguous bytes (whole 32-byte sectors) of every bf16 operand -- saved
-// pre-activation, residual, output -- instead of 32 rows x 16 bytes.  x arrives as alpha * acc.
+// pre-activation, residual, output -- instead of 32 rows x 16 bytes.  x arrives as the raw accumulator.
 template <int EPI>
-__device__ __forceinline__ void epilogue_rows8(const GemmParams& p, const DropoutCfg& drop, int M, int m, int n0, float* x, const float* bias8,
+__device__ __forceinline__ void epilogue_rows8(const GemmParams& p, const DropoutCfg& drop, int M, int m, int n0, float* x, float alpha, const float* bias8,
                                                const uint4& ext) {
   constexpr bool G = EpiK<EPI>::generic;
   if (m >= M) return;
@@ -126,9 +126,13 @@ __device__ __forceinline__ void epilogue_rows8(const GemmParams& p, const Dropou
     if (orow < 0) return;
   }
   const bool vec = G ? (p.vec_ok && ncols == 8) : true;
+  // x arrives as the raw accumulator: alpha and the bias are one fma (alpha == 1: the same bits as acc + bias)
   if (G ? (p.bias != nullptr) : (EPI & EPI_BIAS) != 0) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) x[j] += bias8[j];
+    for (int j = 0; j < 8; ++j) x[j] = fmaf(x[j], alpha, bias8[j]);
+  } else if (alpha != 1.0f) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[j] *= alpha;
   }
   const bool save_grad = G ? (p.act == VT_ACT_GELU_SAVE_GRAD) : (EPI & EPI_GELU_SG) != 0;
   if (save_grad) {   // D = gelu(x), aux_out = gelu'(x)
@@ -516,9 +520,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          float x[8] = {__uint_as_float(lo[i].x) * alpha, __uint_as_float(lo[i].y) * alpha, __uint_as_float(lo[i].z) * alpha, __uint_as_float(lo[i].w) * alpha,
-                        __uint_as_float(hi[i].x) * alpha, __uint_as_float(hi[i].y) * alpha, __uint_as_float(hi[i].z) * alpha, __uint_as_float(hi[i].w) * alpha};
-          epilogue_rows8<EPI>(p, drop, M, m_blk * BM + q * 32 + r8 + 8 * i, n0, x, bias8, ext[i]);
+          float x[8] = {__uint_as_float(lo[i].x), __uint_as_float(lo[i].y), __uint_as_float(lo[i].z), __uint_as_float(lo[i].w),
+                        __uint_as_float(hi[i].x), __uint_as_float(hi[i].y), __uint_as_float(hi[i].z), __uint_as_float(hi[i].w)};
+          epilogue_rows8<EPI>(p, drop, M, m_blk * BM + q * 32 + r8 + 8 * i, n0, x, alpha, bias8, ext[i]);
         }
         if (EXT) {
 #pragma unroll
