@@ -33,14 +33,26 @@ import torch.distributed as dist
 # an exchange is in flight, so that neither side waits for the other's CTAs to retire.  NVSwitch reduces in the switch
 # (NVLS), so a 28 MB bucket needs few CTAs to run far faster than the backward of the next layer.  Measured at b = 32 per GPU
 # (ms per step, cap 2 / 4 / 8 / 16): 2 GPUs 25.0 / 24.7 / 26.5 / 25.9; 8 GPUs - / 25.3 / 26.7 / - (1 GPU: 23.7-24.1).
-NCCL_MAX_CTAS = int(os.environ.get("VT_NCCL_MAX_CTAS", "4"))
+# Round 2 (17 ms step, `tools/r2_call30.sh` / `r2_call31.sh`): 2 GPUs 17.87 / 18.38 ms with 4 / 8 CTAs, 8 GPUs 19.33 / 18.69 / 18.99 ms with 4 / 8 / 16
+# -- an 8-rank all-reduce moves 1.75x the bytes of a 2-rank one per GPU and falls behind the backward with 4 CTAs.  Hence 4 CTAs
+# up to 3 ranks and 8 from 4 ranks on (VT_NCCL_MAX_CTAS overrides).  Skipping the step's last (101 MB) all-reduce altogether gains
+# 0.0 ms at 2 GPUs and 0.34 ms at 8: what is left above the 1-GPU step is the overlapped exchange's share of SMs, HBM and power.
+NCCL_MAX_CTAS = int(os.environ.get("VT_NCCL_MAX_CTAS", "0"))
 
 
-def _exchange_group():
-    """A NCCL communicator of its own for the gradient exchange, capped at NCCL_MAX_CTAS CTAs."""
+def _max_ctas(world_size: int) -> int:
+    return NCCL_MAX_CTAS if NCCL_MAX_CTAS > 0 else (4 if world_size < 4 else 8)
+
+
+_DBG_SKIP_TAIL = os.environ.get("VT_DBG_SKIP_TAIL", "0") == "1"
+_DBG_NO_RESERVE = os.environ.get("VT_DBG_NO_RESERVE", "0") == "1"
+
+
+def _exchange_group(max_ctas: int):
+    """A NCCL communicator of its own for the gradient exchange, capped at `max_ctas` CTAs."""
     try:
         opts = dist.ProcessGroupNCCL.Options()
-        opts.config.max_ctas = NCCL_MAX_CTAS
+        opts.config.max_ctas = max_ctas
         opts.config.min_ctas = 1
         return dist.new_group(backend="nccl", pg_options=opts)
     except Exception:  # older torch without ncclConfig plumbing: the default communicator
@@ -56,8 +68,8 @@ class GradReducer:
         self.reserve = 0
         caller_group = process_group
         if self.backend == "nccl" and process_group is None and overlap and self.world_size > 1:
-            process_group = _exchange_group()
-            self.reserve = NCCL_MAX_CTAS if process_group is not None else 0
+            process_group = _exchange_group(_max_ctas(self.world_size))
+            self.reserve = _max_ctas(self.world_size) if process_group is not None else 0
         # the LAST bucket of a step (embeddings, 101 MB) has no backward kernels left to hide behind: it goes through the
         # caller's (uncapped) communicator at full speed instead of the 8-CTA one
         self.tail_group = caller_group
@@ -76,10 +88,12 @@ class GradReducer:
             return
         self.calls += 1
         self.bytes_reduced += bucket.numel() * bucket.element_size()
+        if tail and _DBG_SKIP_TAIL:      # timing ablation only (wrong gradients): what the step's last all-reduce costs
+            return
         if tail and self.tail_full_speed and self.reserve and self.backend == "nccl":
             self._works.append(dist.all_reduce(bucket, op=dist.ReduceOp.AVG, group=self.tail_group, async_op=True))
             return
-        if self.reserve and not self._reserved:
+        if self.reserve and not self._reserved and not _DBG_NO_RESERVE:
             from . import lib
             lib.load().vt_reserve_sms(self.reserve)
             self._reserved = True
