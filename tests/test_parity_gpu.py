@@ -293,3 +293,69 @@ def test_ragged_shapes_and_missing_objectives_vs_oracle(b, text_len, regions, dr
                 assert p.grad is None or float(p.grad.abs().max()) == 0.0, k
                 continue
             grad_close(k, p.grad, ref, floor=1e-4)
+
+
+def test_dropout_step_vs_oracle_with_the_kernels_own_masks(monkeypatch):
+    """Model-level check with dropout ON: the keep decisions of every dropout site of a step -- embeddings,
+    region projection, attention probabilities (the stored keep bits), attention-output and FFN-output dropout of every layer --
+    are exported from the kernels for the step's seed and fed to the fp32 oracle as its `drop` callable; loss, the seven scalars
+    and every gradient must then agree as they do without dropout.  Dense rows, so that the masks' indices are the caller's."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    from visitron_b200 import ops
+    SEED, PH, PA, LAYERS, B = 0x1234ABCD5, 0.3, 0.1, 2, 2
+    oc = vo.OracleConfig(num_hidden_layers=LAYERS, hidden_dropout_prob=PH, attention_probs_dropout_prob=PA)
+    P = vo.init_params(oc, 77)
+    batch = synthetic.pretrain_batch(B, 91)
+    T, R = batch["input_ids"].size(1), batch["img_feats"].size(1)
+    S, Hd, nh = T + R, oc.hidden_size, oc.num_attention_heads
+    model = modeling.PreTrainOscar(make_config(oc))
+    load_params(model, P)
+    model.to(DEV).train()
+    model.vt_packed = False
+    monkeypatch.setattr(modeling, "_draw_seed", lambda: SEED)
+    out = model(**_to(batch, DEV))
+    out[0].backward()
+    torch.cuda.synchronize()
+
+    def hidden_mask(rows, stream):       # the multiplier (0 or 1 / (1 - p)) of every element of a [rows, H] dropout site
+        ones = torch.ones(rows, Hd, device=DEV, dtype=torch.bfloat16)
+        return ops.dropout_rows(ones, rows, torch.empty_like(ones), PH, SEED, stream).float()
+
+    def probs_mask(stream):              # the attention forward's stored keep bits -> [B, heads, S, S] multipliers
+        bits = ops.attention_keep_bits(B, S, nh, DEV)
+        bits.zero_()
+        qkv = torch.zeros(B * S, 3 * Hd, device=DEV, dtype=torch.bfloat16)
+        ops.attention_fwd(qkv, torch.zeros(B, S, device=DEV), B, S, nh, PA, SEED, stream, keep_bits=bits)
+        G = 4 * ((S + 127) // 128)
+        w = bits.view(B * nh, G, S).long() & 0xffffffff
+        keep = ((w[:, :, :, None] >> torch.arange(32, device=DEV)) & 1).permute(0, 2, 1, 3).reshape(B, nh, S, G * 32)[..., :S]
+        return keep.float() / (1.0 - round(PA * 65536) / 65536)
+
+    masks = [hidden_mask(B * T, modeling.STREAM_EMB).view(B, T, Hd), hidden_mask(B * R, modeling.STREAM_IMG).view(B, R, Hd)]
+    for l in range(LAYERS):
+        masks += [probs_mask(4 * l), hidden_mask(B * S, 4 * l + 1).view(B, S, Hd), hidden_mask(B * S, 4 * l + 2).view(B, S, Hd)]
+    assert abs(float((masks[0] != 0).float().mean()) - (1 - PH)) < 5e-3 and abs(float((masks[2] != 0).float().mean()) - (1 - PA)) < 5e-3
+    it = iter(masks)
+
+    def drop(x, p):
+        m = next(it)
+        assert m.shape == x.shape, (m.shape, x.shape)
+        return x * m
+
+    Pg = vo.clone_params(P, device=DEV)
+    ref_out = vo.pretrain_forward(Pg, oc, drop=drop, **_to(batch, DEV))
+    ref_out[0].backward()
+    assert next(it, None) is None        # every exported mask was consumed, in the oracle's own order of dropout sites
+    for name, a, r in zip(("loss", "mask", "next", "token", "wacc", "aacc", "tacc"), out, ref_out):
+        assert abs(_f(a) - _f(r)) <= LOSS_RTOL * max(1.0, abs(_f(r))), (name, _f(a), _f(r))
+    worst, worst_cos = (0.0, None), (1.0, None)
+    for k, p in model.named_parameters():
+        if k == "mlmhead.predictions.decoder.weight":
+            continue
+        rel, cos = grad_close(k, p.grad, Pg[k].grad, floor=1e-4)
+        worst, worst_cos = max(worst, (rel, k)), min(worst_cos, (cos, k))
+    _report("pretrain step WITH dropout (p = %.1f / %.1f) vs fp32 oracle fed the kernels' exported masks: layers=%d b=%d S=%d | loss |d|=%.2e "
+            "(rel %.2e) | worst grad rel-L2 %.4f (%s) | worst grad cosine %.5f (%s)"
+            % (PH, PA, LAYERS, B, S, abs(_f(out[0]) - _f(ref_out[0])), abs(_f(out[0]) - _f(ref_out[0])) / max(1e-9, abs(_f(ref_out[0]))),
+               worst[0], worst[1], worst_cos[0], worst_cos[1]))
