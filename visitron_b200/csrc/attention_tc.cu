@@ -559,7 +559,8 @@ struct BwdItemCursor {      // loop-invariant inputs (p, nin_max, n_items) are p
 // Tried on this variant and measured slower or equal, not kept (same-box A/B, tools/r2_call19.sh / r2_call20.sh): draining the dQ
 // partial at the top of the pair two pairs behind (412 vs 397 us), staging chunk 0 behind chunk 1 (no change), skipping the
 // arithmetic of key groups past a packed sample's end (305 -> 302 us), and in the forward letting the warps whose rows lie past the
-// sample's end only keep the barrier protocol (165 -> 188 us: the polling warps take more issue slots than the arithmetic did).
+// sample's end only keep the barrier protocol (165 -> 188 us: the polling warps take more issue slots than the arithmetic did);
+// four interleaved chains for the forward's running maximum / sum instead of one (+1 %: the single chain already uses FMNMX3).
 template <int BITS>
 __global__ void __launch_bounds__(BWD_THREADS, 1)
 attn_bwd_fused(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO, const AttnTcParams p) {
