@@ -85,6 +85,37 @@ def test_gemm_cta_pair_equals_single_cta(M, N, K, b_major):
         assert torch.equal(a, b)
 
 
+@pytest.mark.parametrize("M,N,K", [(768, 768, 5000), (768, 3072, 9000), (520, 1000, 4100), (256, 256, 130)])
+def test_gemm_weight_gradient_cta_pair(M, N, K):
+    """dW = dY^T X with both operands MN-major on CTA pairs (256 x 256 tiles, split-K, fp32 red.add) against the single-CTA kernel and
+    fp32 torch; also under a device row limit (the contraction stops at the row count)."""
+    torch.manual_seed(M + K)
+    dY = (torch.randn(K, M, device=DEV) * 0.2).to(BF)
+    X = (torch.randn(K, N, device=DEV) * 0.2).to(BF)
+    ref = dY.float().t() @ X.float()
+    L = lib.init()
+    outs = {}
+    try:
+        for mode in (0, 1):
+            L.vt_debug_pair_mode(mode)
+            acc = torch.full((M, N), 0.25, device=DEV)
+            lib.gemm(dY, X, a_major=1, b_major=1, out=acc, accumulate=True, alpha=0.5)
+            outs[mode] = acc
+            if mode == 1 and K >= 512:
+                rows = K - 300
+                lim = torch.tensor([(rows + 127) // 128 * 128, rows], device=DEV, dtype=torch.int32)
+                dZ = dY.clone()
+                dZ[rows:] = 0
+                acc2 = torch.zeros(M, N, device=DEV)
+                with ops.row_limit(lim, 0):
+                    lib.gemm(dZ, X, a_major=1, b_major=1, out=acc2, accumulate=True)
+                close(acc2, dY[:rows].float().t() @ X[:rows].float(), rtol=1e-3, atol=3e-3, what="pair wgrad under a row limit")
+    finally:
+        L.vt_debug_pair_mode(-1)
+    close(outs[1], 0.25 + 0.5 * ref, rtol=1e-3, atol=3e-3, what="pair wgrad")
+    close(outs[1], outs[0], rtol=1e-4, atol=1e-3, what="pair vs single wgrad")
+
+
 def test_gemm_epilogues_and_splitk():
     torch.manual_seed(2)
     M, N, K = 640, 768, 768

@@ -97,6 +97,7 @@ def main():
     case("ln bwd           [M,768] (+dropped copy, dgamma/dbeta; bias gradient left to the wgrad GEMM)",
          lambda i: ops.layernorm_bwd(r(xs, i), r(xs, i + 1), gamma, 1e-12, gvec[:H], gvec[H:2 * H], None, out_dropout_p=ph, out_stream=2,
                                      seed=seed, dx=out_h, dxd=out_h2), 0, 4.0 * M * H * 2)
+    case("wgrad ffn-down   dW[768,3072] = dY^T Z (CTA pairs, bias gradient from the LayerNorm backward)", lambda i: lib.gemm(r(xs, i), r(zs, i), a_major=1, b_major=1, out=gW.view(H, I), accumulate=True), gemm_fl(I, H))
     case("wgrad ffn-down   dW[768,3072] = dY^T Z (+ bias gradient)", lambda i: lib.gemm(r(xs, i), r(zs, i), a_major=1, b_major=1, out=gW.view(H, I), accumulate=True, colsum=gvec[:H]), gemm_fl(I, H))
     case("dgrad ffn-down   [M,768]x[768,3072]  x saved gelu'", lambda i: lib.gemm(r(xs, i), W2, b_major=1, act=ACT_MUL_AUX, aux=r(zs, i), out=out_i), gemm_fl(I, H))
     case("colsum           [M,3072] (separate kernel, no longer in the step)", lambda i: ops.colsum(r(zs, i), gvec[:I]), 0, 1.0 * M * I * 2)

@@ -250,7 +250,6 @@ template <int BN, int A_MN, int B_MN, int EPI, int CS = 0, int PAIR = 0>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
   static_assert(!CS || A_MN, "column sums are taken over the rows of a [K, M] A operand");
-  static_assert(!PAIR || !A_MN, "CTA pairs: A is [M, K]");
   using Cfg = GemmCfg<BN, CS, PAIR>;
   const uint32_t rank = PAIR ? pair_rank() : 0u;   // CTA of the pair: 0 = leader (issues the MMAs, owns the full / accumulator-empty barriers)
   constexpr int STAGES = Cfg::STAGES;
@@ -340,7 +339,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // both CTAs load into their own shared memory; all bytes of the stage (2 x (A + half B)) are counted on the LEADER's barrier
             const uint32_t lbar = pair_map(full_bar(stage), 0);
             if (rank == 0) mbar_arrive_expect_tx(full_bar(stage), 2 * (Cfg::A_BYTES + Cfg::B_BYTES));
-            tma_load_2d_pair(sa, &tmA, lbar, kb * BK, m_blk * BM);
+            if (A_MN) {
+#pragma unroll
+              for (int c = 0; c < BM / 64; ++c) tma_load_2d_pair(sa + c * (64 * BK * 2), &tmA, lbar, m_blk * BM + c * 64, kb * BK);
+            } else {
+              tma_load_2d_pair(sa, &tmA, lbar, kb * BK, m_blk * BM);
+            }
             const int n0 = n_blk * BN + (int)rank * (BN / 2);
             if (B_MN) {
 #pragma unroll
@@ -602,16 +606,16 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
 }
 
 // CTA-pair launch (see GemmCfg): a cluster of two CTAs per 256 x 256 tile, grid = 2 x min(tiles, SMs / 2)
-template <int B_MN, int EPI>
+template <int B_MN, int EPI, int A_MN = 0>
 static int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int sms, cudaStream_t st) {
   using Cfg = GemmCfg<256, 0, 1>;
   static bool attr_set = false;
-  auto kern = gemm_bf16_kernel<256, 0, B_MN, EPI, 0, 1>;
+  auto kern = gemm_bf16_kernel<256, A_MN, B_MN, EPI, 0, 1>;
   if (!attr_set) {
     VT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set = true;
   }
-  const long long tiles = (long long)((p.M + 2 * BM - 1) / (2 * BM)) * p.n_blocks;
+  const long long tiles = (long long)((p.M + 2 * BM - 1) / (2 * BM)) * p.n_blocks * p.splits;
   const long long pairs = tiles < sms / 2 ? tiles : sms / 2;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(2 * pairs));
@@ -682,6 +686,12 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
              "vt_gemm_bf16: split-K supports only the alpha epilogue");
 
   const int sms = usable_sms();  // see vt_reserve_sms
+  // Weight gradients dW[M, N] = A^T B over K = rows, both operands MN-major: the timing ablations (VT_GEMM_DBG, tools/r2_call35.sh)
+  // show them bound by operand traffic -- the TMA loads alone take 84 of 108 us for dW[3072, 768] at 24.5 k rows, 18 TB/s out of
+  // L2 with 128 x 192 tiles.  A CTA pair's 256 x 256 tile moves 40 % fewer bytes per flop.  Not with the column-sum side product
+  // (its 16 extra B columns do not fit a pair's N <= 256): those launches stay single-CTA.
+  const bool wgrad_pair = a_major && b_major && ep->accumulate && ep->out_fp32 && ep->split_k != 1 && !ep->colsum && !g_force_bn && sms >= 2 &&
+                          (g_pair_mode == 1 || (g_pair_mode < 0 && K >= 4096 && M >= 512 && N >= 512));
   int BN = 256;
   const int m_blocks = (int)((M + BM - 1) / BM);
   if (g_force_bn) {
@@ -689,6 +699,7 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   } else {
     if (N <= 64) BN = 64;
     else if (N <= 128) BN = 128;
+    else if (wgrad_pair) BN = 256;
     else if (ep->accumulate && ep->split_k != 1) BN = (N % 192 == 0) ? 192 : 256;  // weight gradients: split-K fills the SMs
     else {
       // widest tile that keeps every SM busy with the least padded columns (192 divides 768/2304/3072)
@@ -723,13 +734,14 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
     if (ep->accumulate) {
       // the split count whose work items fill whole waves of the SMs best (96 tiles: 3 splits = 288 items = 1.95 waves,
       // where floor(148 / 96) = 1 would leave a third of the SMs idle); ties go to fewer splits (less red.add traffic)
-      const long long tiles = (long long)p.m_blocks * p.n_blocks;
+      const long long tiles = wgrad_pair ? (long long)((p.m_blocks + 1) / 2) * p.n_blocks : (long long)p.m_blocks * p.n_blocks;
+      const int units = wgrad_pair ? sms / 2 : sms;   // CTA pairs: a work item occupies two SMs
       const int max_splits = p.k_blocks / 8 < 1 ? 1 : (p.k_blocks / 8 > 16 ? 16 : p.k_blocks / 8);
       double best = -1.0;
       for (int s = 1; s <= max_splits; ++s) {
         const long long items = tiles * s;
-        const long long waves = (items + sms - 1) / sms;
-        const double eff = (double)items / (double)(waves * sms) - 0.004 * (s - 1);
+        const long long waves = (items + units - 1) / units;
+        const double eff = (double)items / (double)(waves * units) - 0.004 * (s - 1);
         if (eff > best + 1e-9) { best = eff; splits = s; }
       }
     }
@@ -765,7 +777,7 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   // measured at M = 24.5 k (tools/r2_call25.sh): +3 .. +6 % where the main loop bounds the tile (K >= 2304, or N >= 2304 with a light
   // epilogue), -4 % on [M,768]x[768,768] with the dropout + residual epilogue (both CTAs' epilogues must finish before an accumulator
   // stage is reused), so the small square shapes stay single-CTA
-  const bool pair = pair_ok && (g_pair_mode == 1 || (g_pair_mode < 0 && M >= 4096 && !g_force_bn && (K > 1024 || N > 1024)));
+  const bool pair = wgrad_pair || (pair_ok && (g_pair_mode == 1 || (g_pair_mode < 0 && M >= 4096 && !g_force_bn && (K > 1024 || N > 1024))));
   CUtensorMap ta, tb;
   if (a_major) rc = make_map(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK);
   else rc = make_map(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
@@ -778,6 +790,7 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   int grid = (int)(total < sms ? total : sms);
   cudaStream_t st = (cudaStream_t)stream;
   // the encoder's hot epilogues as compile-time kinds (see EPI_*); everything else takes the generic kernel
+  if (wgrad_pair) return launch_gemm_pair<1, EPI_GENERIC, 1>(ta, tb, p, sms, st);
   if (pair) {
     const bool fast = !p.out_fp32 && p.vec_ok && N % 8 == 0;
     const bool bias = p.bias != nullptr, drop = p.drop.thresh16 != 0, res = p.residual != nullptr, auxo = p.aux_out != nullptr;

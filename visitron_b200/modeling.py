@@ -578,9 +578,11 @@ def _encoder_layers_backward(step: _Step, st: FlatStore, d):
         ph = step.p_hidden
         # LN2 and the FFN
         dx2, dx2d = ops.layernorm_bwd(d, x2, st.w(p + "output.LayerNorm.weight"), eps, st.g(p + "output.LayerNorm.weight"),
-                                      st.g(p + "output.LayerNorm.bias"), None,
+                                      st.g(p + "output.LayerNorm.bias"), st.g(p + "output.dense.bias"),
                                       out_dropout_p=ph, out_stream=4 * l + 2, seed=step.seed)
-        lib.gemm(dx2d, z, a_major=1, b_major=1, out=st.g(p + "output.dense.weight"), accumulate=True, colsum=st.g(p + "output.dense.bias"))
+        # (these two bias gradients come from the LayerNorm backward's third accumulator: without the column-sum side product the
+        # weight-gradient GEMM can run on CTA pairs, 109 -> 87 us for dW[768, 3072] at 24.5 k rows)
+        lib.gemm(dx2d, z, a_major=1, b_major=1, out=st.g(p + "output.dense.weight"), accumulate=True)
         dpre = lib.gemm(dx2d, st.wb(p + "output.dense.weight"), b_major=1, act=ACT_MUL_AUX, aux=pre)   # pre holds gelu'(pre-activation)
         # the bias gradients ride on the weight-gradient GEMMs (column sums of the dY tiles they stage anyway)
         lib.gemm(dpre, y1, a_major=1, b_major=1, out=st.g(p + "intermediate.dense.weight"), accumulate=True,
@@ -590,9 +592,8 @@ def _encoder_layers_backward(step: _Step, st: FlatStore, d):
         # LN1 and the attention block
         dx1, dx1d = ops.layernorm_bwd(dy1, x1, st.w(p + "attention.output.LayerNorm.weight"), eps,
                                       st.g(p + "attention.output.LayerNorm.weight"), st.g(p + "attention.output.LayerNorm.bias"),
-                                      None, out_dropout_p=ph, out_stream=4 * l + 1, seed=step.seed)
-        lib.gemm(dx1d, ctx, a_major=1, b_major=1, out=st.g(p + "attention.output.dense.weight"), accumulate=True,
-                 colsum=st.g(p + "attention.output.dense.bias"))
+                                      st.g(p + "attention.output.dense.bias"), out_dropout_p=ph, out_stream=4 * l + 1, seed=step.seed)
+        lib.gemm(dx1d, ctx, a_major=1, b_major=1, out=st.g(p + "attention.output.dense.weight"), accumulate=True)
         dctx = lib.gemm(dx1d, st.wb(p + "attention.output.dense.weight"), b_major=1)
         dqkv = ops.attention_bwd(qkv, step.bias, ctx, dctx, lse, B, S, nh, step.p_attn, step.seed, 4 * l, key_tiles=step.key_tiles, plan=step.plan,
                                  keep_bits=bits)
