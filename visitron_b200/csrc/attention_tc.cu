@@ -55,17 +55,31 @@ attn_bwd_prep_kernel(const bf16* __restrict__ dout, const bf16* __restrict__ out
       if (b < 0) continue;
       i = m - start[b];
     }
-    for (int c = lane; c < hidden / 8; c += 32) {  // 8 lanes cover one 64-wide head
-      float a[8], o[8];
-      unpack8(__ldg(reinterpret_cast<const uint4*>(dout + m * hidden + c * 8)), a);
-      unpack8(__ldg(reinterpret_cast<const uint4*>(out + m * hidden + c * 8)), o);
-      float s = 0.f;
+    for (int c0 = lane; c0 < hidden / 8; c0 += 96) {  // 8 lanes cover one 64-wide head; three 32-chunk groups (a 768-wide row) loaded at once
+      uint4 qa[3], qo[3];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) s += a[j] * o[j];
-      s += __shfl_xor_sync(0xffffffffu, s, 1);
-      s += __shfl_xor_sync(0xffffffffu, s, 2);
-      s += __shfl_xor_sync(0xffffffffu, s, 4);
-      if ((lane & 7) == 0) dsum[(b * heads + c / 8) * S + i] = s;
+      for (int u = 0; u < 3; ++u) {
+        const int c = c0 + 32 * u;
+        if (c < hidden / 8) {
+          qa[u] = __ldg(reinterpret_cast<const uint4*>(dout + m * hidden + c * 8));
+          qo[u] = __ldg(reinterpret_cast<const uint4*>(out + m * hidden + c * 8));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        const int c = c0 + 32 * u;
+        if (c - lane < hidden / 8) {      // warp-uniform (hidden is a multiple of 64): the shuffles below need the whole warp
+          float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          if (c < hidden / 8) { unpack8(qa[u], a); unpack8(qo[u], o); }
+          float s = 0.f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) s += a[j] * o[j];
+          s += __shfl_xor_sync(0xffffffffu, s, 1);
+          s += __shfl_xor_sync(0xffffffffu, s, 2);
+          s += __shfl_xor_sync(0xffffffffu, s, 4);
+          if ((lane & 7) == 0 && c < hidden / 8) dsum[(b * heads + c / 8) * S + i] = s;
+        }
+      }
     }
   }
 }
@@ -1043,11 +1057,21 @@ attn_dq_reduce_kernel(const bf16* __restrict__ ws, long long slice, int nkt, lon
     nkt = b < 0 ? 0 : (start[b + 1] - start[b] + 127) / 128;
   }
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (int k = 0; k < nkt; ++k) {
-    float f[8];
-    unpack8(__ldcs(reinterpret_cast<const uint4*>(ws + k * slice + row * hidden + c)), f);
+  // groups of 8 slices with every load of the group in flight before the first add (S <= 1024 is one group); same order of additions
+  for (int k0 = 0; k0 < nkt; k0 += 8) {
+    uint4 q[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    for (int u = 0; u < 8; ++u)
+      if (k0 + u < nkt) q[u] = __ldcs(reinterpret_cast<const uint4*>(ws + (long long)(k0 + u) * slice + row * hidden + c));
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (k0 + u < nkt) {
+        float f[8];
+        unpack8(q[u], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    }
   }
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[j] *= factor;
