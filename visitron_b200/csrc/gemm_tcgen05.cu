@@ -72,6 +72,10 @@ struct GemmParams {
 // with the epilogue reduced to draining TMEM, 95 us for the epilogue alone without MMAs and loads): the epilogue's ~17 arithmetic
 // instructions per element, issued by two warps per scheduler at 77 % issue utilisation.  Tried without gain: 16 epilogue warps
 // (same time: issue-bound, not latency-bound), packed f32x2 arithmetic (FFMA2 issues at half rate), CTA pairs for these shapes.
+// The data-gradient GEMM with the saved-gelu' multiply ([M,768]x[768,3072], 119 us) is different: its epilogue alone takes 103 us with or
+// without the stores at ~12 % issue utilisation, i.e. it waits for the per-element operand; pulling the next tile's slice of it into L2 a
+// tile ahead (cp.async.bulk.prefetch.L2, 256 B per row) changed nothing (121.9 vs 119.3 us), so the loads' queueing is not DRAM page
+// locality either -- open.
 template <int BN, int CS = 0, int PAIR = 0>
 struct GemmCfg {
   static_assert(!CS || BN <= 192, "the column-sum variant needs 16 accumulator columns next to the tile");
