@@ -473,7 +473,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (m < M) atomicAdd(p.colsum + m, __uint_as_float(cv[0]) * alpha);
       }
       tmem_ld_wait();
-#pragma unroll 1
+      // With a per-element operand the chunk loop is unrolled over the half tile: rolled up, the hand-over `ext = ext_next` at the end
+      // of a chunk is a register move that waits for the prefetch issued in the SAME chunk -- one full memory latency per chunk (the
+      // MUL_AUX epilogue alone took 103 us at 12 % issue utilisation); unrolled, the compiler renames the registers and the loads
+      // really run a chunk ahead.
+      constexpr int CHUNK_UNROLL = EXT ? CH_PER_HALF : 1;
+#pragma unroll CHUNK_UNROLL
       for (int c = c_begin; c < c_end; ++c) {
         if (VT_GDBG(1)) {
           if (c + 1 < c_end) { tmem_ld_32x32(t_addr + (uint32_t)((c + 1) * 32), v); tmem_ld_wait(); }
