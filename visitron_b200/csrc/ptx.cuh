@@ -87,9 +87,12 @@ __device__ __forceinline__ uint32_t pair_map(uint32_t saddr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
   return r;
 }
-// arrive on a barrier of another CTA of the cluster (address from pair_map)
+// arrive on a barrier of another CTA of the cluster (address from pair_map).  RELAXED: what the arrival publishes is "this warp's
+// tcgen05.ld of the accumulator stage has completed", which tcgen05.wait::ld + tcgen05.fence::before_thread_sync in front of it
+// already guarantee; a .release.cluster arrive compiles to MEMBAR.ALL.CTA + ERRBAR and waits for every global store of the epilogue
+// (13 % of the pair kernel's stall samples, profiles/r2_ncu_gemm_dgrad_pair.txt).
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
 // TMA load issued by either CTA of a pair into ITS OWN shared memory; the bytes are counted on `cluster_bar` (the leader's barrier)
 __device__ __forceinline__ void tma_load_2d_pair(uint32_t smem_dst, const CUtensorMap* m, uint32_t cluster_bar, int c0, int c1) {
