@@ -783,10 +783,10 @@ extern "C" int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void*
   // CTA pairs: [M, K] A operand, 256-wide tiles, one pass over K, no output row maps; by default only where a launch is many waves of
   // tiles (below ~4 k rows the 256-row granularity and the cluster launch cost more than the halved B traffic gains)
   const bool pair_ok = !a_major && BN == 256 && p.splits == 1 && !p.accumulate && p.remap_in <= 0 && !p.remap_index && sms >= 2;
-  // measured at M = 24.5 k (tools/r2_call25.sh): +3 .. +6 % where the main loop bounds the tile (K >= 2304, or N >= 2304 with a light
-  // epilogue), -4 % on [M,768]x[768,768] with the dropout + residual epilogue (both CTAs' epilogues must finish before an accumulator
-  // stage is reused), so the small square shapes stay single-CTA
-  const bool pair = wgrad_pair || (pair_ok && (g_pair_mode == 1 || (g_pair_mode < 0 && M >= 4096 && !g_force_bn && (K > 1024 || N > 1024))));
+  // measured at M = 24.5 k (tools/r2_call25.sh and later): +3 .. +6 % where the main loop bounds the tile (K >= 2304, or N >= 2304 with a light
+  // epilogue); the small square shapes [M,768]x[768,768] are neutral (dropout + residual epilogue) to +6 % (plain) since the accumulator
+  // hand-back is a relaxed arrive (it cost them 4 % before)
+  const bool pair = wgrad_pair || (pair_ok && (g_pair_mode == 1 || (g_pair_mode < 0 && M >= 4096 && !g_force_bn)));
   CUtensorMap ta, tb;
   if (a_major) rc = make_map(&ta, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK);
   else rc = make_map(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
