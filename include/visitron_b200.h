@@ -148,6 +148,9 @@ typedef struct {
   float* colsum;
 } vt_gemm_epilogue;
 
+/* Scheduling inside (no effect on the interface; results are bit-identical for the [M, K] forms): launches with at least 4096 rows of a
+ * K-major A, and weight-gradient launches (a_major = b_major = 1, accumulate, no colsum) over at least 4096 rows, run on CTA pairs
+ * (tcgen05.mma.cta_group::2, one 256 x 256 tile per two SMs); everything else on one CTA per 128 x BN tile. */
 int vt_gemm_bf16(const void* A, int64_t lda, int a_major, const void* B, int64_t ldb, int b_major,
                  void* D, int64_t ldd, int64_t M, int64_t N, int64_t K, const vt_gemm_epilogue* ep,
                  vt_stream stream);
