@@ -156,3 +156,12 @@ def test_frozen_encoder_with_trainable_heads(monkeypatch):
     model(**batch)[0].backward()
     assert model.token_head[0].weight.grad is not None and model.mlmhead.predictions.transform.dense.weight.grad is not None
     assert model.bert.encoder.layer[0].output.dense.weight.grad is None
+
+
+def test_exchange_cta_cap_follows_the_world_size(monkeypatch):
+    """parallel._max_ctas: 4 NCCL CTAs up to 3 ranks, 8 from 4 ranks on (measured, see parallel.py); VT_NCCL_MAX_CTAS overrides."""
+    from visitron_b200 import parallel
+    monkeypatch.setattr(parallel, "NCCL_MAX_CTAS", 0)
+    assert [parallel._max_ctas(w) for w in (1, 2, 3, 4, 8)] == [4, 4, 4, 8, 8]
+    monkeypatch.setattr(parallel, "NCCL_MAX_CTAS", 6)
+    assert parallel._max_ctas(2) == 6 and parallel._max_ctas(8) == 6
